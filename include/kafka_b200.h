@@ -1,0 +1,207 @@
+/* kafka_b200.h — C ABI of libkafka_b200.so, the sm_100a completion engine that sits under the
+ * reference's LLMProvider plugin API.
+ *
+ * What this boundary replaces.  In egrigokhan/kafka-llm-service the provider plugin is a Python ABC
+ * (src/llm/base.py:67 LLMProvider; stream_completion src/llm/base.py:166-219; completion
+ * src/llm/base.py:222-262) whose only implementation hands the arithmetic to a remote gateway
+ * (src/llm/portkey.py:379 and :616, `await client.chat.completions.create(**params)`).  There is no
+ * FFI in the reference; the functions below are what a local provider binds (via ctypes, see
+ * INTEGRATION.md) in place of that network hop.  Each entry point cites the reference call site whose
+ * work it takes over.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types.
+ *   - every device pointer and every stream is allocated by the caller (PyTorch in this repo) and
+ *     BORROWED; the library allocates nothing on the device.
+ *   - every call only enqueues work on the given stream (no hidden synchronisation).
+ *   - return 0 on success; non-zero on failure, message via kb_last_error() (thread-local).
+ *   - one engine per device, driven by one host thread at a time.
+ *   - there is no CPU fallback in this library.
+ */
+#ifndef KAFKA_B200_H
+#define KAFKA_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KB_ABI_VERSION 1
+#define KB_BLOCK_TOKENS 64 /* tokens per KV block (one TMA bulk tile = 64 tokens x head_dim) */
+#define KB_MAX_SPLITS 16   /* upper bound on split-KV partitions of one sequence in decode attention */
+
+#define KB_OK 0
+#define KB_ERR_INVALID 1
+#define KB_ERR_CUDA 2
+
+typedef void* kb_stream; /* a cudaStream_t */
+
+typedef struct kb_engine kb_engine;
+
+/* Llama-family architecture (the shapes SURVEY.md §8d lists; nothing like it exists in the reference,
+ * whose `model` is just a string forwarded to the gateway, src/llm/portkey.py:267). */
+typedef struct kb_model_cfg {
+    int32_t hidden;     /* model width, multiple of 64 */
+    int32_t n_layers;
+    int32_t n_heads;    /* query heads */
+    int32_t n_kv_heads; /* n_heads / n_kv_heads in {1,2,4,8,16} */
+    int32_t head_dim;   /* 64 or 128 */
+    int32_t ffn;        /* MLP inner width, multiple of 64 */
+    int32_t vocab;      /* multiple of 8 */
+    int32_t max_pos;    /* context limit; beyond it the host raises a context-length error */
+    float rope_theta;
+    float rms_eps;
+} kb_model_cfg;
+
+/* bf16 device pointers, row-major [out_features, in_features] like torch.nn.Linear.weight.
+ *   wqkv      : [(n_heads + 2 n_kv_heads) * head_dim, hidden]   rows = q heads, k heads, v heads
+ *   wo        : [hidden, n_heads * head_dim]
+ *   w_gate_up : [2 * ffn, hidden]   row 2j = gate_j, row 2j+1 = up_j (interleaved for the SwiGLU epilogue)
+ *   w_down    : [hidden, ffn]
+ */
+typedef struct kb_layer_weights {
+    const void* attn_norm; /* [hidden] bf16 */
+    const void* wqkv;
+    const void* wo;
+    const void* mlp_norm;  /* [hidden] bf16 */
+    const void* w_gate_up;
+    const void* w_down;
+} kb_layer_weights;
+
+typedef struct kb_weight_ptrs {
+    const void* embed;      /* [vocab, hidden] bf16 */
+    const void* final_norm; /* [hidden] bf16 */
+    const void* lm_head;    /* [vocab, hidden] bf16 */
+    const kb_layer_weights* layers; /* host array of n_layers entries */
+} kb_weight_ptrs;
+
+typedef struct kb_sampling {
+    float temperature; /* <= 0 : greedy argmax (ties -> lowest id) */
+    uint64_t seed;     /* Gumbel-max sampling stream when temperature > 0 */
+    uint64_t step;     /* caller-incremented counter mixed into the stream */
+    int32_t banned_token; /* token id never produced (e.g. EOS masked while benchmarking), -1 = none */
+    /* Optional restriction of the candidate set to ids in [allowed_lo, allowed_hi) plus up to two
+     * extra ids (e.g. newline and <|eot_id|>); allowed_hi <= allowed_lo means "whole vocabulary". */
+    int32_t allowed_lo, allowed_hi;
+    int32_t extra_a, extra_b; /* -1 = unused */
+} kb_sampling;
+
+/* ---- engine lifetime ------------------------------------------------------------------------- */
+
+/* Takes over: provider construction, src/kafka/v1.py:177-181 (PortkeyLLMProvider(...)). */
+int kb_engine_create(int device, const kb_model_cfg* cfg, kb_engine** out);
+void kb_engine_destroy(kb_engine* e);
+
+/* Takes over: nothing in the reference (weights live behind the gateway). Pointers are borrowed. */
+int kb_bind_weights(kb_engine* e, const kb_weight_ptrs* w);
+
+/* KV pools, layout [layer][block][kv_head][token_in_block][head_dim] bf16 with the 16-byte chunks of
+ * each token row XOR-swizzled by (token & 7).  k_pool and v_pool each hold
+ * n_layers * n_blocks * n_kv_heads * KB_BLOCK_TOKENS * head_dim bf16.
+ * Takes over: the thread history the reference re-sends in full on every call
+ * (src/agents/base.py:222-223) — here it stays resident in HBM. */
+int kb_bind_kv_pool(kb_engine* e, void* k_pool, void* v_pool, int32_t n_blocks);
+
+/* Activation workspace for up to max_tokens packed tokens / max_seqs sequences per call. */
+size_t kb_workspace_bytes(const kb_model_cfg* cfg, int32_t max_tokens, int32_t max_seqs);
+int kb_bind_workspace(kb_engine* e, void* ws, size_t bytes, int32_t max_tokens, int32_t max_seqs);
+
+/* ---- the hot path ------------------------------------------------------------------------------
+ * Both calls run embed -> n_layers x (RMSNorm, QKV GEMM, RoPE + KV append, paged attention,
+ * O GEMM + residual, RMSNorm, gate/up GEMM + SwiGLU, down GEMM + residual) -> final RMSNorm of the
+ * last position of each sequence -> lm_head GEMM -> sampling.
+ *
+ * Takes over: `response = await client.chat.completions.create(**params)` + the chunk loop,
+ * src/llm/portkey.py:379 and :425-475 (streaming) / :616 (non-streaming).
+ *
+ * kb_prefill: incremental prefill of packed new tokens of n_seqs sequences.
+ *   tokens       [n_tokens] int32 device   new token ids, sequences back to back
+ *   cu_seqlens   [n_seqs+1] int32 device   prefix sums of new-token counts
+ *   ctx_lens     [n_seqs]   int32 device   tokens already resident in KV per sequence
+ *   block_tables [n_seqs, max_blocks] int32 device   KV block ids per sequence
+ *   max_new      largest new-token count of any sequence (host knows it)
+ *   logits_last  fp32 [n_seqs, vocab] device or NULL
+ *   out_tokens   int32 [n_seqs] device or NULL  (sampled from the last position)
+ */
+int kb_prefill(kb_engine* e, const int32_t* tokens, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+               const int32_t* block_tables, int32_t n_seqs, int32_t n_tokens, int32_t max_blocks,
+               int32_t max_new, const kb_sampling* sampling, float* logits_last, int32_t* out_tokens,
+               kb_stream stream);
+
+/* kb_decode: one token per sequence.  last_tokens may be the previous call's out_tokens (device
+ * feedback, no host round trip).  If advance_ctx != 0 the call finishes by ctx_lens[i] += 1 so the
+ * same arguments can be replayed for the next step.  max_ctx = largest ctx_lens[i] the host knows of
+ * (only used to decide how many split-KV partitions to launch; 0 = assume max_blocks full). */
+int kb_decode(kb_engine* e, const int32_t* last_tokens, int32_t* ctx_lens, const int32_t* block_tables,
+              int32_t batch, int32_t max_blocks, int32_t max_ctx, const kb_sampling* sampling,
+              int32_t* out_tokens, float* logits_dbg, int32_t advance_ctx, kb_stream stream);
+
+/* ---- per-kernel entry points (unit parity tests; same kernels the hot path launches) ----------- */
+
+/* y[t,:] = bf16( x[t,:] * rsqrt(mean(x^2) + eps) * w ),  x fp32 [n, hidden] */
+int kb_rmsnorm(const float* x, const void* w_bf16, void* y_bf16, int32_t n, int32_t hidden, float eps,
+               kb_stream stream);
+
+/* x[t,:] = float(embed[token[t], :]) */
+int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x, int32_t n, int32_t hidden,
+             int32_t vocab, kb_stream stream);
+
+/* D = A[M,K] * W[N,K]^T on tcgen05 tensor cores, fp32 accumulation in TMEM.
+ * epilogue: 0 = bf16 out[M,N]; 1 = fp32 out[M,N]; 2 = fp32 out[M,N] = resid[M,N] + D (out may alias
+ * resid); 3 = SwiGLU on interleaved columns, bf16 out[M,N/2] = silu(D[:,2j]) * D[:,2j+1]. */
+#define KB_EPI_BF16 0
+#define KB_EPI_F32 1
+#define KB_EPI_RESID_F32 2
+#define KB_EPI_SWIGLU_BF16 3
+int kb_gemm(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,
+            int32_t K, int32_t epilogue, kb_stream stream);
+/* Same, with the output tile width forced to tile_n in {64, 128, 256} (0 = heuristic); for tuning and
+ * for tests that must cover every instantiation. */
+int kb_gemm_ex(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,
+               int32_t K, int32_t epilogue, int32_t tile_n, kb_stream stream);
+
+/* Rotate q and k (HF rotate-half convention), write q in place and k,v into the paged pools.
+ *   qkv [n_tokens, (n_heads + 2 n_kv_heads) * head_dim] bf16;  token t of sequence s sits at position
+ *   ctx_lens[s] + (t - cu_seqlens[s]).  k_pool_layer / v_pool_layer point at ONE layer's pool. */
+int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+                   const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,
+                   int32_t n_tokens, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
+                   int32_t head_dim, float rope_theta, kb_stream stream);
+
+/* Paged attention, one query token per sequence, over kv_lens[s] + kv_len_bias cached tokens.
+ *   q   [batch, q_stride] bf16 (first n_heads*head_dim columns are the heads), out [batch, n_heads*head_dim] bf16
+ *   max_kv_len : host-side bound on kv_lens[s] + kv_len_bias (0 = max_blocks * KB_BLOCK_TOKENS)
+ *   scratch    : optional device buffer for split-KV partials (kb_attn_decode_scratch_bytes); NULL = no
+ *                cross-CTA split (small batches then use fewer SMs).
+ * The pools must hold finite values everywhere (zero-initialise them once): masked tail positions of
+ * the last block are multiplied by an exact 0. */
+size_t kb_attn_decode_scratch_bytes(int32_t batch, int32_t n_heads, int32_t head_dim);
+int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
+                   const int32_t* kv_lens, int32_t kv_len_bias, const int32_t* block_tables, void* out_bf16,
+                   int32_t batch, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads, int32_t head_dim,
+                   int32_t max_kv_len, void* scratch, size_t scratch_bytes, kb_stream stream);
+
+/* Paged causal attention for packed new tokens (incremental prefill): query i of sequence s attends
+ * to the ctx_lens[s] cached tokens plus new tokens 0..i. K/V of the new tokens must already be
+ * appended (kb_rope_append). */
+int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
+                    const int32_t* cu_seqlens, const int32_t* ctx_lens, const int32_t* block_tables,
+                    void* out_bf16, int32_t n_seqs, int32_t n_tokens, int32_t max_new, int32_t max_blocks,
+                    int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, kb_stream stream);
+
+/* out_tokens[s] = argmax_j (logits[s,j] / T + gumbel(seed, step, s, j)); greedy when T <= 0. */
+int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,
+              int32_t* out_tokens, kb_stream stream);
+
+/* ---- diagnostics ------------------------------------------------------------------------------- */
+const char* kb_last_error(void);
+int kb_abi_version(void);
+/* Number of kernels this library has enqueued since load (bench.py's gpu_launches). */
+unsigned long long kb_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KAFKA_B200_H */

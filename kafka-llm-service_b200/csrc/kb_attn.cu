@@ -1,0 +1,585 @@
+// kb_attn.cu — paged attention over the HBM-resident per-thread KV blocks (sm_100a).
+//
+// Takes over the part of the remote completion (src/llm/portkey.py:379) that dominates decode:
+// every generated token re-reads the whole conversation's K and V.  In the reference the whole
+// conversation is re-sent as text on every call (src/agents/base.py:222-223); here it is
+// (ctx_len x 2 x n_kv_heads x head_dim) bf16 per layer, gathered block by block.
+//
+// Decode kernel (HBM-bound; algorithmic bytes = kv_len * n_kv_heads * head_dim * 2 * 2 per sequence
+// per layer):
+//   * one CTA per (kv head, sequence[, split]); the GROUP = n_heads / n_kv_heads query heads that share
+//     the KV head are the (zero-padded) 16 rows of a warp-level m16n8k16 MMA, so each K/V byte is
+//     fetched once for all of them;
+//   * every warp is its own producer and consumer: lane 0 issues cp.async.bulk (TMA, 1-D) copies of
+//     32-token half-blocks of K and V into a private ring of stages, completion by mbarrier tx-count;
+//     no CTA-wide barrier in the main loop;
+//   * tiles arrive pre-swizzled (the KV-append kernel stores 16-byte chunks XOR (token & 7)), so
+//     ldmatrix from the staged tile is bank-conflict free without a tensor map;
+//   * online softmax in fp32 with quad shuffles, cross-warp merge through shared memory, optional
+//     cross-CTA split-KV merge through a caller-provided scratch buffer.
+//
+// Prefill kernel (incremental: new tokens attend to cached prefix + themselves): one CTA per
+// (q tile, kv head, sequence), 4 consumer warps x 16 rows (rows = query token x GROUP head) sharing a
+// CTA-wide 3-stage ring of 64-token K/V tiles fed by a producer warp.
+#include "kb_common.cuh"
+
+namespace kb {
+
+constexpr float LOG2E = 1.4426950408889634f;
+
+// One warp: S = Q K^T over an NT-token tile, online softmax, O += P V.
+//   o  : [HD/8][4] accumulators (m16n8 C layout; [0],[1] = row g, [2],[3] = row g+8)
+//   qa : [HD/16][4] Q A-fragments (pre-loaded)
+//   ks, vs : shared addresses of the swizzled K / V tiles ([token][HD] bf16)
+//   tok0 : absolute position of the tile's first token; lim0/lim1: exclusive position limit of
+//          rows g / g+8 (causal + length mask), applied only when need_mask.
+template <int HD, int NT, bool UPPER>
+__device__ __forceinline__ void attn_tile(float (&o)[HD / 8][4], float (&m)[2], float (&l)[2],
+                                          const uint32_t (&qa)[HD / 16][4], uint32_t ks, uint32_t vs, int tok0,
+                                          int lim0, int lim1, float sc, bool need_mask, int lane) {
+    constexpr int NJ = NT / 8;
+    constexpr int ROW_BYTES = HD * 2;
+    const int lrow = lane & 7;
+    const int lmat = lane >> 3;
+    const int t = lane & 3;
+
+    float s[NJ][4];
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
+
+#pragma unroll
+    for (int kk2 = 0; kk2 < HD / 32; ++kk2) {
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+            const int token = 8 * j + lrow;
+            const int chunk = (4 * kk2 + lmat) ^ lrow;
+            uint32_t b0, b1, b2, b3;
+            ldsm_x4(ks + token * ROW_BYTES + chunk * 16, b0, b1, b2, b3);
+            mma_bf16_16816(s[j], qa[2 * kk2][0], qa[2 * kk2][1], qa[2 * kk2][2], qa[2 * kk2][3], b0, b1);
+            mma_bf16_16816(s[j], qa[2 * kk2 + 1][0], qa[2 * kk2 + 1][1], qa[2 * kk2 + 1][2], qa[2 * kk2 + 1][3], b2,
+                           b3);
+        }
+    }
+
+    // scale + mask + row max
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int pos = tok0 + 8 * j + 2 * t + e;
+            float v0 = s[j][e] * sc;
+            if (need_mask && pos >= lim0) v0 = -INFINITY;
+            s[j][e] = v0;
+            mx0 = fmaxf(mx0, v0);
+            if (UPPER) {
+                float v1 = s[j][2 + e] * sc;
+                if (need_mask && pos >= lim1) v1 = -INFINITY;
+                s[j][2 + e] = v1;
+                mx1 = fmaxf(mx1, v1);
+            }
+        }
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    const float mn0 = fmaxf(m[0], mx0);
+    const float corr0 = exp2f(m[0] - mn0);
+    m[0] = mn0;
+    float mn1 = 0.f, corr1 = 1.f;
+    if (UPPER) {
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        mn1 = fmaxf(m[1], mx1);
+        corr1 = exp2f(m[1] - mn1);
+        m[1] = mn1;
+    }
+    float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const float p0 = exp2f(s[j][e] - mn0);
+            s[j][e] = p0;
+            sum0 += p0;
+            if (UPPER) {
+                const float p1 = exp2f(s[j][2 + e] - mn1);
+                s[j][2 + e] = p1;
+                sum1 += p1;
+            }
+        }
+    }
+    l[0] = l[0] * corr0 + sum0;
+    if (UPPER) l[1] = l[1] * corr1 + sum1;
+#pragma unroll
+    for (int d = 0; d < HD / 8; ++d) {
+        o[d][0] *= corr0;
+        o[d][1] *= corr0;
+        if (UPPER) {
+            o[d][2] *= corr1;
+            o[d][3] *= corr1;
+        }
+    }
+
+    // O += P V
+#pragma unroll
+    for (int kk = 0; kk < NT / 16; ++kk) {
+        const uint32_t a0 = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
+        const uint32_t a1 = UPPER ? pack_bf16(s[2 * kk][2], s[2 * kk][3]) : 0u;
+        const uint32_t a2 = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        const uint32_t a3 = UPPER ? pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]) : 0u;
+#pragma unroll
+        for (int d2 = 0; d2 < HD / 16; ++d2) {
+            const int token = 16 * kk + (lmat & 1) * 8 + lrow;
+            const int chunk = (2 * d2 + (lmat >> 1)) ^ lrow;
+            uint32_t b0, b1, b2, b3;
+            ldsm_x4_t(vs + token * ROW_BYTES + chunk * 16, b0, b1, b2, b3);
+            mma_bf16_16816(o[2 * d2], a0, a1, a2, a3, b0, b1);
+            mma_bf16_16816(o[2 * d2 + 1], a0, a1, a2, a3, b2, b3);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// decode
+// ---------------------------------------------------------------------------------------------
+template <int HD>
+struct DecodeCfg {
+    static constexpr int NT = 32;                        // tokens per stage (half a KV block)
+    static constexpr int WARPS = (HD == 128) ? 2 : 4;    // 2 CTAs/SM either way
+    static constexpr int STAGES = 3;
+    static constexpr int TILE_BYTES = NT * HD * 2;       // one of K or V
+    static constexpr int RING_BYTES = WARPS * STAGES * 2 * TILE_BYTES;
+    static constexpr int MERGE_FLOATS = WARPS * 8 * (HD + 2);
+    static constexpr int SMEM_BYTES = RING_BYTES + MERGE_FLOATS * 4 + WARPS * STAGES * 8 + 128;
+};
+
+template <int HD, int GROUP>
+__global__ void __launch_bounds__(DecodeCfg<HD>::WARPS * 32)
+attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
+                   const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ kv_lens, int kv_len_bias,
+                   const int* __restrict__ block_tables, __nv_bfloat16* __restrict__ out, float* __restrict__ part_o,
+                   float* __restrict__ part_ml, int max_blocks, int n_heads, int n_kv_heads, int n_splits,
+                   int halves_per_split) {
+    using Cfg = DecodeCfg<HD>;
+    constexpr int NT = Cfg::NT, W = Cfg::WARPS, S = Cfg::STAGES;
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* ring = smem;
+    float* merge = reinterpret_cast<float*>(smem + Cfg::RING_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::RING_BYTES + Cfg::MERGE_FLOATS * 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int kvh = blockIdx.x, seq = blockIdx.y, split = blockIdx.z;
+
+    const int kv_len = kv_lens[seq] + kv_len_bias;
+    const int n_half = (kv_len + NT - 1) / NT;
+    const int h_begin = split * halves_per_split;
+    const int h_end = min(n_half, h_begin + halves_per_split);
+
+    uint64_t* my_bars = bars + warp * S;
+    uint8_t* my_ring = ring + warp * (S * 2 * Cfg::TILE_BYTES);
+    if (lane == 0) {
+        for (int s = 0; s < S; ++s) mbar_init(&my_bars[s], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    // Q fragments: rows g < GROUP are the query heads of this KV head; the rest are zero.
+    uint32_t qa[HD / 16][4];
+    {
+        const __nv_bfloat16* qp = q + (size_t)seq * q_stride + (size_t)(kvh * GROUP + g) * HD;
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+            qa[kk][1] = 0u;
+            qa[kk][3] = 0u;
+            if (g < GROUP) {
+                qa[kk][0] = *reinterpret_cast<const uint32_t*>(qp + 16 * kk + 2 * t);
+                qa[kk][2] = *reinterpret_cast<const uint32_t*>(qp + 16 * kk + 8 + 2 * t);
+            } else {
+                qa[kk][0] = 0u;
+                qa[kk][2] = 0u;
+            }
+        }
+    }
+
+    const int* bt = block_tables + (size_t)seq * max_blocks;
+    auto issue = [&](int h, int stage) {
+        // lane 0 only
+        const int phys = bt[h >> 1];
+        const size_t off = (((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS + (size_t)(h & 1) * NT) * HD;
+        uint8_t* ks = my_ring + stage * 2 * Cfg::TILE_BYTES;
+        mbar_arrive_expect_tx(&my_bars[stage], 2 * Cfg::TILE_BYTES);
+        bulk_g2s(ks, kpool + off, Cfg::TILE_BYTES, &my_bars[stage]);
+        bulk_g2s(ks + Cfg::TILE_BYTES, vpool + off, Cfg::TILE_BYTES, &my_bars[stage]);
+    };
+
+    float o[HD / 8][4];
+#pragma unroll
+    for (int d = 0; d < HD / 8; ++d) { o[d][0] = o[d][1] = o[d][2] = o[d][3] = 0.f; }
+    float m[2] = {-INFINITY, -INFINITY};
+    float l[2] = {0.f, 0.f};
+    const float sc = LOG2E * rsqrtf((float)HD);
+
+    // this warp's half-tiles: h_begin + warp, + W, ...
+    const int first = h_begin + warp;
+    const int n_mine = (first < h_end) ? (h_end - first + W - 1) / W : 0;
+    if (lane == 0) {
+        for (int i = 0; i < S && i < n_mine; ++i) issue(first + i * W, i);
+    }
+    for (int i = 0; i < n_mine; ++i) {
+        const int stage = i % S;
+        const uint32_t phase = (uint32_t)((i / S) & 1);
+        const int h = first + i * W;
+        mbar_wait(&my_bars[stage], phase);
+        const uint32_t ks = smem_u32(my_ring + stage * 2 * Cfg::TILE_BYTES);
+        const bool tail = (h + 1) * NT > kv_len;
+        attn_tile<HD, NT, false>(o, m, l, qa, ks, ks + Cfg::TILE_BYTES, h * NT, kv_len, kv_len, sc, tail, lane);
+        __syncwarp();
+        if (lane == 0 && i + S < n_mine) issue(first + (i + S) * W, stage);
+    }
+
+    // quad-reduce the row sums, publish this warp's partial (m, l, O) for rows < GROUP
+    l[0] += __shfl_xor_sync(0xffffffffu, l[0], 1);
+    l[0] += __shfl_xor_sync(0xffffffffu, l[0], 2);
+    float* mw = merge + warp * 8 * (HD + 2);
+    if (g < GROUP) {
+        float* row = mw + g * (HD + 2);
+        if (t == 0) {
+            row[HD] = m[0];
+            row[HD + 1] = l[0];
+        }
+#pragma unroll
+        for (int d = 0; d < HD / 8; ++d) {
+            row[8 * d + 2 * t] = o[d][0];
+            row[8 * d + 2 * t + 1] = o[d][1];
+        }
+    }
+    __syncthreads();
+
+    for (int idx = threadIdx.x; idx < GROUP * HD; idx += W * 32) {
+        const int r = idx / HD, dim = idx % HD;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < W; ++w) M = fmaxf(M, merge[(w * 8 + r) * (HD + 2) + HD]);
+        float L = 0.f, val = 0.f;
+        if (M != -INFINITY) {
+#pragma unroll
+            for (int w = 0; w < W; ++w) {
+                const float* row = merge + (w * 8 + r) * (HD + 2);
+                const float wgt = exp2f(row[HD] - M);
+                L += wgt * row[HD + 1];
+                val += wgt * row[dim];
+            }
+        }
+        const int head = kvh * GROUP + r;
+        if (n_splits == 1) {
+            out[((size_t)seq * n_heads + head) * HD + dim] = __float2bfloat16(val / L);
+        } else {
+            const size_t p = ((size_t)seq * n_heads + head) * n_splits + split;
+            part_o[p * HD + dim] = val;
+            if (dim == 0) {
+                part_ml[p * 2] = M;
+                part_ml[p * 2 + 1] = L;
+            }
+        }
+    }
+}
+
+// merge the split-KV partials: one block per (sequence, head)
+template <int HD>
+__global__ void __launch_bounds__(HD)
+attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
+                        __nv_bfloat16* __restrict__ out, int n_splits) {
+    const size_t sh = blockIdx.x;
+    const int dim = threadIdx.x;
+    float M = -INFINITY;
+    for (int s = 0; s < n_splits; ++s) M = fmaxf(M, part_ml[(sh * n_splits + s) * 2]);
+    float L = 0.f, val = 0.f;
+    for (int s = 0; s < n_splits; ++s) {
+        const float ms = part_ml[(sh * n_splits + s) * 2];
+        if (ms == -INFINITY) continue;
+        const float wgt = exp2f(ms - M);
+        L += wgt * part_ml[(sh * n_splits + s) * 2 + 1];
+        val += wgt * part_o[(sh * n_splits + s) * HD + dim];
+    }
+    out[sh * HD + dim] = __float2bfloat16(val / L);
+}
+
+// ---------------------------------------------------------------------------------------------
+// prefill (incremental, causal)
+// ---------------------------------------------------------------------------------------------
+template <int HD>
+struct PrefillCfg {
+    static constexpr int NT = 64;
+    static constexpr int STAGES = (HD == 128) ? 3 : 4;
+    static constexpr int TILE_BYTES = NT * HD * 2;
+    static constexpr int RING_BYTES = STAGES * 2 * TILE_BYTES;
+    static constexpr int SMEM_BYTES = RING_BYTES + 2 * STAGES * 8 + 128;
+    static constexpr int THREADS = 160;  // 4 consumer warps + 1 producer warp
+};
+
+template <int HD, int GROUP>
+__global__ void __launch_bounds__(PrefillCfg<HD>::THREADS)
+attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
+                    const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+                    const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
+                    __nv_bfloat16* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads) {
+    using Cfg = PrefillCfg<HD>;
+    constexpr int NT = Cfg::NT, S = Cfg::STAGES;
+    constexpr int TQ = 64 / GROUP;  // query tokens per CTA
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::RING_BYTES);
+    uint64_t* empty_bar = full_bar + S;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int seq = blockIdx.z, kvh = blockIdx.y;
+    const int tok_begin = cu_seqlens[seq];
+    const int n_new = cu_seqlens[seq + 1] - tok_begin;
+    const int q0 = blockIdx.x * TQ;
+    if (q0 >= n_new) return;
+    const int ctx = ctx_lens[seq];
+    const int q_end = min(n_new, q0 + TQ);
+    const int kv_end = ctx + q_end;  // keys visible to the last query of this CTA
+    const int n_tiles = (kv_end + NT - 1) / NT;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 4);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    if (warp == 4) {
+        // ===== producer =====
+        if (lane == 0) {
+            const int* bt = block_tables + (size_t)seq * max_blocks;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int i = 0; i < n_tiles; ++i) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                const int phys = bt[i];
+                const size_t off = ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * HD;
+                uint8_t* ks = smem + stage * 2 * Cfg::TILE_BYTES;
+                mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::TILE_BYTES);
+                bulk_g2s(ks, kpool + off, Cfg::TILE_BYTES, &full_bar[stage]);
+                bulk_g2s(ks + Cfg::TILE_BYTES, vpool + off, Cfg::TILE_BYTES, &full_bar[stage]);
+                if (++stage == S) { stage = 0; phase ^= 1; }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers: warp w owns rows 16w .. 16w+15; row r = (query token q0 + r / GROUP, head r % GROUP)
+    const int g = lane >> 2, t = lane & 3;
+    const int r0 = warp * 16 + g, r1 = r0 + 8;
+    const int tl0 = q0 + r0 / GROUP, tl1 = q0 + r1 / GROUP;
+    const int hd0 = kvh * GROUP + r0 % GROUP, hd1 = kvh * GROUP + r1 % GROUP;
+    const bool v0 = tl0 < n_new, v1 = tl1 < n_new;
+    const int lim0 = v0 ? ctx + tl0 + 1 : kv_end;
+    const int lim1 = v1 ? ctx + tl1 + 1 : kv_end;
+    // smallest limit of any row of this warp decides when masking starts
+    const int warp_first_tl = q0 + (warp * 16) / GROUP;
+    const int warp_min_lim = (warp_first_tl < n_new) ? ctx + warp_first_tl + 1 : kv_end;
+
+    uint32_t qa[HD / 16][4];
+    {
+        const __nv_bfloat16* qp0 = q + (size_t)(tok_begin + tl0) * q_stride + (size_t)hd0 * HD;
+        const __nv_bfloat16* qp1 = q + (size_t)(tok_begin + tl1) * q_stride + (size_t)hd1 * HD;
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk) {
+            qa[kk][0] = v0 ? *reinterpret_cast<const uint32_t*>(qp0 + 16 * kk + 2 * t) : 0u;
+            qa[kk][2] = v0 ? *reinterpret_cast<const uint32_t*>(qp0 + 16 * kk + 8 + 2 * t) : 0u;
+            qa[kk][1] = v1 ? *reinterpret_cast<const uint32_t*>(qp1 + 16 * kk + 2 * t) : 0u;
+            qa[kk][3] = v1 ? *reinterpret_cast<const uint32_t*>(qp1 + 16 * kk + 8 + 2 * t) : 0u;
+        }
+    }
+
+    float o[HD / 8][4];
+#pragma unroll
+    for (int d = 0; d < HD / 8; ++d) { o[d][0] = o[d][1] = o[d][2] = o[d][3] = 0.f; }
+    float m[2] = {-INFINITY, -INFINITY};
+    float l[2] = {0.f, 0.f};
+    const float sc = LOG2E * rsqrtf((float)HD);
+
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < n_tiles; ++i) {
+        mbar_wait(&full_bar[stage], phase);
+        const uint32_t ks = smem_u32(smem + stage * 2 * Cfg::TILE_BYTES);
+        const bool need_mask = (i + 1) * NT > warp_min_lim;
+        attn_tile<HD, NT, true>(o, m, l, qa, ks, ks + Cfg::TILE_BYTES, i * NT, lim0, lim1, sc, need_mask, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[stage]);
+        if (++stage == S) { stage = 0; phase ^= 1; }
+    }
+
+    l[0] += __shfl_xor_sync(0xffffffffu, l[0], 1);
+    l[0] += __shfl_xor_sync(0xffffffffu, l[0], 2);
+    l[1] += __shfl_xor_sync(0xffffffffu, l[1], 1);
+    l[1] += __shfl_xor_sync(0xffffffffu, l[1], 2);
+    const float inv0 = 1.f / l[0], inv1 = 1.f / l[1];
+    if (v0) {
+        __nv_bfloat16* op = out + ((size_t)(tok_begin + tl0) * n_heads + hd0) * HD;
+#pragma unroll
+        for (int d = 0; d < HD / 8; ++d)
+            *reinterpret_cast<uint32_t*>(op + 8 * d + 2 * t) = pack_bf16(o[d][0] * inv0, o[d][1] * inv0);
+    }
+    if (v1) {
+        __nv_bfloat16* op = out + ((size_t)(tok_begin + tl1) * n_heads + hd1) * HD;
+#pragma unroll
+        for (int d = 0; d < HD / 8; ++d)
+            *reinterpret_cast<uint32_t*>(op + 8 * d + 2 * t) = pack_bf16(o[d][2] * inv1, o[d][3] * inv1);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------------------------
+template <int HD, int GROUP>
+static int launch_decode(const void* q, int q_stride, const void* kp, const void* vp, const int* kv_lens, int bias,
+                         const int* bt, void* out, float* part_o, float* part_ml, int batch, int max_blocks,
+                         int n_heads, int n_kv_heads, int n_splits, int halves_per_split, cudaStream_t stream) {
+    using Cfg = DecodeCfg<HD>;
+    auto kern = attn_decode_kernel<HD, GROUP>;
+    static bool configured[64] = {};
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    dim3 grid(n_kv_heads, batch, n_splits);
+    kern<<<grid, Cfg::WARPS * 32, Cfg::SMEM_BYTES, stream>>>(
+        (const __nv_bfloat16*)q, q_stride, (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, kv_lens, bias, bt,
+        (__nv_bfloat16*)out, part_o, part_ml, max_blocks, n_heads, n_kv_heads, n_splits, halves_per_split);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    if (n_splits > 1) {
+        attn_split_merge_kernel<HD><<<batch * n_heads, HD, 0, stream>>>(part_o, part_ml, (__nv_bfloat16*)out,
+                                                                         n_splits);
+        count_launch();
+        KB_LAUNCH_CHECK();
+    }
+    return KB_OK;
+}
+
+size_t attn_decode_scratch_bytes(int batch, int n_heads, int head_dim, int n_splits) {
+    return (size_t)batch * n_heads * n_splits * (head_dim + 2) * sizeof(float);
+}
+
+// Number of KV splits: enough CTAs to cover the SMs twice over when batch * n_kv_heads alone cannot.
+int attn_decode_pick_splits(int batch, int n_kv_heads, int max_kv_len, int sms) {
+    const int base = batch * n_kv_heads;
+    const int n_half = (max_kv_len + 31) / 32;
+    int splits = 1;
+    if (base < 2 * sms) {
+        splits = (4 * sms + base - 1) / base;
+        const int max_by_len = n_half / 8 > 1 ? n_half / 8 : 1;  // at least 8 half-tiles (256 tokens) per split
+        if (splits > max_by_len) splits = max_by_len;
+        if (splits > KB_MAX_SPLITS) splits = KB_MAX_SPLITS;
+        if (splits < 1) splits = 1;
+    }
+    return splits;
+}
+
+int attn_decode(const void* q, int q_stride, const void* kp, const void* vp, const int* kv_lens, int bias,
+                const int* bt, void* out, int batch, int max_blocks, int n_heads, int n_kv_heads, int head_dim,
+                int max_kv_len, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+    KB_CHECK(batch > 0 && max_blocks > 0, "kb_attn_decode: empty batch");
+    KB_CHECK(n_kv_heads > 0 && n_heads % n_kv_heads == 0, "kb_attn_decode: n_heads %% n_kv_heads != 0");
+    KB_CHECK(batch <= 65535, "kb_attn_decode: batch %d > 65535", batch);
+    const int group = n_heads / n_kv_heads;
+    int sms = 148;
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    if (max_kv_len <= 0) max_kv_len = max_blocks * KB_BLOCK_TOKENS;
+    int n_splits = scratch ? attn_decode_pick_splits(batch, n_kv_heads, max_kv_len, sms) : 1;
+    while (n_splits > 1 && attn_decode_scratch_bytes(batch, n_heads, head_dim, n_splits) > scratch_bytes) --n_splits;
+    const int n_half = (max_kv_len + 31) / 32;
+    const int hps = (n_half + n_splits - 1) / n_splits;
+    float* part_o = reinterpret_cast<float*>(scratch);
+    float* part_ml = part_o ? part_o + (size_t)batch * n_heads * n_splits * head_dim : nullptr;
+
+#define KB_DECODE_CASE(HD_, G_)                                                                                   \
+    if (head_dim == HD_ && group == G_)                                                                           \
+        return launch_decode<HD_, G_>(q, q_stride, kp, vp, kv_lens, bias, bt, out, part_o, part_ml, batch,        \
+                                      max_blocks, n_heads, n_kv_heads, n_splits, hps, stream);
+    KB_DECODE_CASE(128, 1) KB_DECODE_CASE(128, 2) KB_DECODE_CASE(128, 4) KB_DECODE_CASE(128, 8)
+    KB_DECODE_CASE(64, 1) KB_DECODE_CASE(64, 2) KB_DECODE_CASE(64, 4) KB_DECODE_CASE(64, 8)
+#undef KB_DECODE_CASE
+    set_error("kb_attn_decode: unsupported head_dim=%d group=%d (head_dim in {64,128}, group in {1,2,4,8})", head_dim,
+              group);
+    return KB_ERR_INVALID;
+}
+
+template <int HD, int GROUP>
+static int launch_prefill(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+                          const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads,
+                          int n_kv_heads, cudaStream_t stream) {
+    using Cfg = PrefillCfg<HD>;
+    auto kern = attn_prefill_kernel<HD, GROUP>;
+    static bool configured[64] = {};
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    constexpr int TQ = 64 / GROUP;
+    dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>((const __nv_bfloat16*)q, q_stride,
+                                                          (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, cu, ctx,
+                                                          bt, (__nv_bfloat16*)out, max_blocks, n_heads, n_kv_heads);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+                 const int* bt, void* out, int n_seqs, int n_tokens, int max_new, int max_blocks, int n_heads,
+                 int n_kv_heads, int head_dim, cudaStream_t stream) {
+    KB_CHECK(n_seqs > 0 && n_tokens > 0 && max_new > 0, "kb_attn_prefill: empty batch");
+    KB_CHECK(n_kv_heads > 0 && n_heads % n_kv_heads == 0, "kb_attn_prefill: n_heads %% n_kv_heads != 0");
+    KB_CHECK(n_seqs <= 65535, "kb_attn_prefill: n_seqs %d > 65535", n_seqs);
+    const int group = n_heads / n_kv_heads;
+#define KB_PREFILL_CASE(HD_, G_)                                                                               \
+    if (head_dim == HD_ && group == G_)                                                                        \
+        return launch_prefill<HD_, G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks,    \
+                                       n_heads, n_kv_heads, stream);
+    KB_PREFILL_CASE(128, 1) KB_PREFILL_CASE(128, 2) KB_PREFILL_CASE(128, 4) KB_PREFILL_CASE(128, 8)
+    KB_PREFILL_CASE(64, 1) KB_PREFILL_CASE(64, 2) KB_PREFILL_CASE(64, 4) KB_PREFILL_CASE(64, 8)
+#undef KB_PREFILL_CASE
+    set_error("kb_attn_prefill: unsupported head_dim=%d group=%d", head_dim, group);
+    return KB_ERR_INVALID;
+}
+
+}  // namespace kb
+
+extern "C" size_t kb_attn_decode_scratch_bytes(int32_t batch, int32_t n_heads, int32_t head_dim) {
+    return kb::attn_decode_scratch_bytes(batch, n_heads, head_dim, KB_MAX_SPLITS);
+}
+
+extern "C" int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+                              const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
+                              const int32_t* block_tables, void* out_bf16, int32_t batch, int32_t max_blocks,
+                              int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t max_kv_len,
+                              void* scratch, size_t scratch_bytes, kb_stream stream) {
+    return kb::attn_decode(q_bf16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out_bf16,
+                           batch, max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, scratch, scratch_bytes,
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+                               const void* v_pool_layer, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+                               const int32_t* block_tables, void* out_bf16, int32_t n_seqs, int32_t n_tokens,
+                               int32_t max_new, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
+                               int32_t head_dim, kb_stream stream) {
+    return kb::attn_prefill(q_bf16, q_stride, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tables, out_bf16,
+                            n_seqs, n_tokens, max_new, max_blocks, n_heads, n_kv_heads, head_dim,
+                            reinterpret_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,302 @@
+// kb_elementwise.cu — the HBM-bound glue kernels of the completion path (sm_100a):
+// token embedding gather, RMSNorm, RoPE + paged KV append, sampling.
+//
+// Takes over pieces of the remote completion (src/llm/portkey.py:379); the reference has no local
+// arithmetic.  All kernels are pure streaming: one pass over their inputs with 128-bit accesses.
+#include "kb_common.cuh"
+
+namespace kb {
+
+// ---------------------------------------------------------------------------------------------
+// embed: x[t,:] = float(E[token[t],:])        bytes/token = hidden * (2 + 4)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+embed_kernel(const int* __restrict__ tokens, const __nv_bfloat16* __restrict__ embed, float* __restrict__ x,
+             int hidden, int vocab) {
+    const int t = blockIdx.x;
+    int tok = tokens[t];
+    tok = tok < 0 ? 0 : (tok >= vocab ? vocab - 1 : tok);
+    const uint4* src = reinterpret_cast<const uint4*>(embed + (size_t)tok * hidden);
+    float4* dst = reinterpret_cast<float4*>(x + (size_t)t * hidden);
+    for (int i = threadIdx.x; i < hidden / 8; i += blockDim.x) {
+        const uint4 v = src[i];
+        const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&v);
+        const float2 a = __bfloat1622float2(p[0]), b = __bfloat1622float2(p[1]);
+        const float2 c = __bfloat1622float2(p[2]), d = __bfloat1622float2(p[3]);
+        dst[2 * i] = make_float4(a.x, a.y, b.x, b.y);
+        dst[2 * i + 1] = make_float4(c.x, c.y, d.x, d.y);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// rmsnorm: y[i,:] = bf16(x[row(i),:] * rsqrt(mean(x^2) + eps) * w)
+//   row(i) = i, or cu_seqlens[i+1]-1 when last_rows != nullptr (final norm of each sequence's last token)
+//   bytes/row = hidden * (4 + 2) (+ w, L2-resident)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+rmsnorm_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ y,
+               const int* __restrict__ last_rows, int hidden, float eps) {
+    const int i = blockIdx.x;
+    const int row = last_rows ? last_rows[i + 1] - 1 : i;
+    const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * hidden);
+    const int n4 = hidden / 4;
+    __shared__ float red[8];
+    float ss = 0.f;
+    for (int j = threadIdx.x; j < n4; j += blockDim.x) {
+        const float4 v = xr[j];
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tot += (k < (int)(blockDim.x >> 5)) ? red[k] : 0.f;
+    const float inv = rsqrtf(tot / (float)hidden + eps);
+    const uint2* wr = reinterpret_cast<const uint2*>(w);
+    uint2* yr = reinterpret_cast<uint2*>(y + (size_t)i * hidden);
+    for (int j = threadIdx.x; j < n4; j += blockDim.x) {
+        const float4 v = xr[j];
+        const uint2 wv = wr[j];
+        const float2 w0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv.x));
+        const float2 w1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv.y));
+        uint2 o;
+        o.x = pack_bf16(v.x * inv * w0.x, v.y * inv * w0.y);
+        o.y = pack_bf16(v.z * inv * w1.x, v.w * inv * w1.y);
+        yr[j] = o;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// rope + KV append.  One block per token.
+//   q heads : rotated in place in qkv
+//   k heads : rotated, written to k_pool (swizzled paged layout)
+//   v heads : copied to v_pool
+// HF "rotate_half" convention: pairs (i, i + hd/2), angle = pos * theta^(-2i/hd), fp32 math.
+//   bytes/token = (n_heads*2 + n_kv_heads*2*2) * head_dim * 2  (read+write q, read k/v, write pools)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+rope_append_kernel(__nv_bfloat16* __restrict__ qkv, const int* __restrict__ cu_seqlens,
+                   const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
+                   __nv_bfloat16* __restrict__ kpool, __nv_bfloat16* __restrict__ vpool, int n_seqs, int max_blocks,
+                   int n_heads, int n_kv_heads, int head_dim, float log2_theta) {
+    const int tkn = blockIdx.x;
+    __shared__ float s_cos[64], s_sin[64];
+    __shared__ int s_seq, s_pos;
+    if (threadIdx.x == 0) {
+        int seq, pos;
+        if (cu_seqlens == nullptr) {
+            seq = tkn;
+            pos = ctx_lens[seq];
+        } else {
+            int lo = 0, hi = n_seqs;  // find seq with cu[seq] <= tkn < cu[seq+1]
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (cu_seqlens[mid] <= tkn) lo = mid; else hi = mid;
+            }
+            seq = lo;
+            pos = ctx_lens[seq] + (tkn - cu_seqlens[seq]);
+        }
+        s_seq = seq;
+        s_pos = pos;
+    }
+    __syncthreads();
+    const int seq = s_seq, pos = s_pos;
+    const int half = head_dim >> 1;
+    if ((int)threadIdx.x < half) {
+        // inv_freq = theta^(-2i/hd)
+        const float inv_freq = exp2f(-log2_theta * (float)(2 * threadIdx.x) / (float)head_dim);
+        float sn, cs;
+        sincosf((float)pos * inv_freq, &sn, &cs);
+        s_cos[threadIdx.x] = cs;
+        s_sin[threadIdx.x] = sn;
+    }
+    __syncthreads();
+
+    const int qkv_dim = (n_heads + 2 * n_kv_heads) * head_dim;
+    __nv_bfloat16* row = qkv + (size_t)tkn * qkv_dim;
+    const int blk = pos / KB_BLOCK_TOKENS, tib = pos % KB_BLOCK_TOKENS;
+    const int phys = block_tables[(size_t)seq * max_blocks + blk];
+    const int cph = head_dim >> 4;  // 16-byte chunks per half head
+
+    // rotate q and k heads: work item = (head, chunk of the lower half)
+    const int n_rot = (n_heads + n_kv_heads) * cph;
+    for (int it = threadIdx.x; it < n_rot; it += blockDim.x) {
+        const int head = it / cph, c = it % cph;
+        __nv_bfloat16* hp = row + (size_t)head * head_dim;
+        uint4 lo4 = *reinterpret_cast<const uint4*>(hp + c * 8);
+        uint4 hi4 = *reinterpret_cast<const uint4*>(hp + half + c * 8);
+        __nv_bfloat162* lo2 = reinterpret_cast<__nv_bfloat162*>(&lo4);
+        __nv_bfloat162* hi2 = reinterpret_cast<__nv_bfloat162*>(&hi4);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 a = __bfloat1622float2(lo2[j]);
+            const float2 b = __bfloat1622float2(hi2[j]);
+            const int i0 = c * 8 + 2 * j;
+            const float c0 = s_cos[i0], n0 = s_sin[i0], c1 = s_cos[i0 + 1], n1 = s_sin[i0 + 1];
+            lo2[j] = __floats2bfloat162_rn(a.x * c0 - b.x * n0, a.y * c1 - b.y * n1);
+            hi2[j] = __floats2bfloat162_rn(b.x * c0 + a.x * n0, b.y * c1 + a.y * n1);
+        }
+        if (head < n_heads) {
+            *reinterpret_cast<uint4*>(hp + c * 8) = lo4;
+            *reinterpret_cast<uint4*>(hp + half + c * 8) = hi4;
+        } else {
+            const int kvh = head - n_heads;
+            __nv_bfloat16* tile = kpool + ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * head_dim;
+            *reinterpret_cast<uint4*>(tile + kv_swizzled_elem(tib, c * 8, head_dim)) = lo4;
+            *reinterpret_cast<uint4*>(tile + kv_swizzled_elem(tib, half + c * 8, head_dim)) = hi4;
+        }
+    }
+    // copy v heads
+    const int n_v = n_kv_heads * (head_dim >> 3);
+    const __nv_bfloat16* vsrc = row + (size_t)(n_heads + n_kv_heads) * head_dim;
+    for (int it = threadIdx.x; it < n_v; it += blockDim.x) {
+        const int kvh = it / (head_dim >> 3), c = it % (head_dim >> 3);
+        const uint4 v = *reinterpret_cast<const uint4*>(vsrc + (size_t)kvh * head_dim + c * 8);
+        __nv_bfloat16* tile = vpool + ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * head_dim;
+        *reinterpret_cast<uint4*>(tile + kv_swizzled_elem(tib, c * 8, head_dim)) = v;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// sampling: argmax_j (logit_j / T + gumbel_j);  greedy when T <= 0 (ties -> lowest id).
+//   bytes/sequence = vocab * 4
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+    x += 0x9e3779b97f4a7c15ull;
+    x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+    x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+    return x ^ (x >> 31);
+}
+
+__global__ void __launch_bounds__(1024)
+sample_kernel(const float* __restrict__ logits, int vocab, float temperature, uint64_t seed, uint64_t step,
+              int banned, int lo, int hi, int extra_a, int extra_b, int* __restrict__ out_tokens,
+              int* __restrict__ ctx_lens_advance) {
+    const int seq = blockIdx.x;
+    const float* lg = logits + (size_t)seq * vocab;
+    const bool greedy = !(temperature > 0.f);
+    const float inv_t = greedy ? 1.f : 1.f / temperature;
+    const uint64_t base = splitmix64(seed ^ splitmix64(step * 0x100000001b3ull + (uint64_t)seq));
+    float best = -INFINITY;
+    int best_i = 0x7fffffff;
+    // candidates: ids in [lo, hi) followed by the (at most two) extra ids
+    const int n_range = hi - lo;
+    const int n_cand = n_range + (extra_a >= 0 ? 1 : 0) + (extra_b >= 0 ? 1 : 0);
+    for (int c = threadIdx.x; c < n_cand; c += blockDim.x) {
+        int j;
+        if (c < n_range) j = lo + c;
+        else if (c == n_range && extra_a >= 0) j = extra_a;
+        else j = extra_b;
+        float v = lg[j] * inv_t;
+        if (!greedy) {
+            const uint64_t r = splitmix64(base + (uint64_t)j);
+            const float u = ((float)(r >> 40) + 0.5f) * (1.0f / 16777216.0f);  // (0,1)
+            v += -__logf(-__logf(u));
+        }
+        if (j == banned) v = -INFINITY;
+        if (v > best || (v == best && j < best_i)) { best = v; best_i = j; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+        if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+    }
+    __shared__ float sv[32];
+    __shared__ int si[32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sv[warp] = best; si[warp] = best_i; }
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+        best = lane < nw ? sv[lane] : -INFINITY;
+        best_i = lane < nw ? si[lane] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+            if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
+        }
+        if (lane == 0) {
+            out_tokens[seq] = best_i == 0x7fffffff ? 0 : best_i;
+            if (ctx_lens_advance) ctx_lens_advance[seq] += 1;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------------------------
+int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, int vocab, cudaStream_t stream) {
+    KB_CHECK(n > 0 && hidden % 8 == 0, "kb_embed: bad shape n=%d hidden=%d", n, hidden);
+    embed_kernel<<<n, 256, 0, stream>>>(tokens, (const __nv_bfloat16*)embed_w, x, hidden, vocab);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps,
+            cudaStream_t stream) {
+    KB_CHECK(n > 0 && hidden % 4 == 0, "kb_rmsnorm: bad shape n=%d hidden=%d", n, hidden);
+    rmsnorm_kernel<<<n, 256, 0, stream>>>(x, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, last_rows, hidden, eps);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* kp, void* vp, int n_seqs,
+                int n_tokens, int max_blocks, int n_heads, int n_kv_heads, int head_dim, float theta,
+                cudaStream_t stream) {
+    KB_CHECK(n_tokens > 0 && n_seqs > 0, "kb_rope_append: empty batch");
+    KB_CHECK(head_dim == 64 || head_dim == 128, "kb_rope_append: head_dim must be 64 or 128 (got %d)", head_dim);
+    KB_CHECK(cu != nullptr || n_tokens == n_seqs, "kb_rope_append: cu_seqlens == NULL means one token per sequence");
+    rope_append_kernel<<<n_tokens, 128, 0, stream>>>((__nv_bfloat16*)qkv, cu, ctx, bt, (__nv_bfloat16*)kp,
+                                                      (__nv_bfloat16*)vp, n_seqs, max_blocks, n_heads, n_kv_heads,
+                                                      head_dim, log2f(theta));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, int* out_tokens, int* ctx_advance,
+           cudaStream_t stream) {
+    KB_CHECK(n_seqs > 0 && vocab > 0 && sp != nullptr && out_tokens != nullptr, "kb_sample: bad arguments");
+    int lo = 0, hi = vocab, ea = -1, eb = -1;
+    if (sp->allowed_hi > sp->allowed_lo) {
+        lo = sp->allowed_lo < 0 ? 0 : sp->allowed_lo;
+        hi = sp->allowed_hi > vocab ? vocab : sp->allowed_hi;
+        ea = (sp->extra_a >= 0 && sp->extra_a < vocab && (sp->extra_a < lo || sp->extra_a >= hi)) ? sp->extra_a : -1;
+        eb = (sp->extra_b >= 0 && sp->extra_b < vocab && (sp->extra_b < lo || sp->extra_b >= hi) &&
+              sp->extra_b != ea) ? sp->extra_b : -1;
+        KB_CHECK(hi > lo, "kb_sample: empty allowed range");
+    }
+    sample_kernel<<<n_seqs, 1024, 0, stream>>>(logits, vocab, sp->temperature, sp->seed, sp->step, sp->banned_token,
+                                               lo, hi, ea, eb, out_tokens, ctx_advance);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+}  // namespace kb
+
+extern "C" int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x, int32_t n, int32_t hidden,
+                        int32_t vocab, kb_stream stream) {
+    return kb::embed(tokens, embed_bf16, x, n, hidden, vocab, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int kb_rmsnorm(const float* x, const void* w_bf16, void* y_bf16, int32_t n, int32_t hidden, float eps,
+                          kb_stream stream) {
+    return kb::rmsnorm(x, w_bf16, y_bf16, nullptr, n, hidden, eps, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+                              const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,
+                              int32_t n_tokens, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
+                              int32_t head_dim, float rope_theta, kb_stream stream) {
+    return kb::rope_append(qkv_bf16, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_seqs, n_tokens,
+                           max_blocks, n_heads, n_kv_heads, head_dim, rope_theta,
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,
+                         int32_t* out_tokens, kb_stream stream) {
+    return kb::sample(logits, n_seqs, vocab, sampling, out_tokens, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}

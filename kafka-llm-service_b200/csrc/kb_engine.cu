@@ -1,0 +1,272 @@
+// kb_engine.cu — the per-GPU engine behind the C ABI: borrowed weights / KV pool / workspace and the
+// forward pass (prefill and decode) that chains the kernels of kb_gemm.cu, kb_attn.cu and
+// kb_elementwise.cu on one stream.
+//
+// Takes over `await client.chat.completions.create(**params)` (src/llm/portkey.py:379, :616).
+#include "kb_common.cuh"
+
+#include <vector>
+#include <new>
+#include <string.h>
+
+namespace kb {
+
+thread_local char g_err[512] = {0};
+unsigned long long g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+// implemented in the other translation units
+int gemm(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi,
+         cudaStream_t stream);
+int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, int vocab, cudaStream_t stream);
+int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps,
+            cudaStream_t stream);
+int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* kp, void* vp, int n_seqs,
+                int n_tokens, int max_blocks, int n_heads, int n_kv_heads, int head_dim, float theta,
+                cudaStream_t stream);
+int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, int* out_tokens, int* ctx_advance,
+           cudaStream_t stream);
+int attn_decode(const void* q, int q_stride, const void* kp, const void* vp, const int* kv_lens, int bias,
+                const int* bt, void* out, int batch, int max_blocks, int n_heads, int n_kv_heads, int head_dim,
+                int max_kv_len, void* scratch, size_t scratch_bytes, cudaStream_t stream);
+int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+                 const int* bt, void* out, int n_seqs, int n_tokens, int max_new, int max_blocks, int n_heads,
+                 int n_kv_heads, int head_dim, cudaStream_t stream);
+size_t attn_decode_scratch_bytes(int batch, int n_heads, int head_dim, int n_splits);
+
+static inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+struct Workspace {
+    float* x = nullptr;           // [T, hidden] fp32 residual stream
+    __nv_bfloat16* xn = nullptr;  // [T, hidden] normed activations (GEMM A operand)
+    __nv_bfloat16* qkv = nullptr; // [T, qkv_dim]
+    __nv_bfloat16* attn = nullptr;// [T, n_heads*head_dim]
+    __nv_bfloat16* h = nullptr;   // [T, ffn]
+    __nv_bfloat16* xl = nullptr;  // [S, hidden] final-normed last rows
+    float* logits = nullptr;      // [S, vocab]
+    void* split = nullptr;        // split-KV partials
+    size_t split_bytes = 0;
+    size_t total = 0;
+};
+
+static void layout_workspace(const kb_model_cfg& c, int T, int S, uint8_t* base, Workspace* w) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        uint8_t* p = base ? base + off : nullptr;
+        off += align256(bytes);
+        return p;
+    };
+    const size_t qkv_dim = (size_t)(c.n_heads + 2 * c.n_kv_heads) * c.head_dim;
+    w->x = reinterpret_cast<float*>(take((size_t)T * c.hidden * 4));
+    w->xn = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.hidden * 2));
+    w->qkv = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * qkv_dim * 2));
+    w->attn = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.n_heads * c.head_dim * 2));
+    w->h = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.ffn * 2));
+    w->xl = reinterpret_cast<__nv_bfloat16*>(take((size_t)S * c.hidden * 2));
+    w->logits = reinterpret_cast<float*>(take((size_t)S * c.vocab * 4));
+    w->split_bytes = attn_decode_scratch_bytes(S, c.n_heads, c.head_dim, KB_MAX_SPLITS);
+    w->split = take(w->split_bytes);
+    w->total = off;
+}
+
+static int check_cfg(const kb_model_cfg* c) {
+    KB_CHECK(c != nullptr, "null model cfg");
+    KB_CHECK(c->hidden > 0 && c->hidden % 64 == 0, "hidden=%d must be a positive multiple of 64", c->hidden);
+    KB_CHECK(c->ffn > 0 && c->ffn % 64 == 0, "ffn=%d must be a positive multiple of 64", c->ffn);
+    KB_CHECK(c->head_dim == 64 || c->head_dim == 128, "head_dim=%d must be 64 or 128", c->head_dim);
+    KB_CHECK(c->n_layers > 0 && c->n_heads > 0 && c->n_kv_heads > 0, "bad layer/head counts");
+    KB_CHECK(c->n_heads % c->n_kv_heads == 0, "n_heads %% n_kv_heads != 0");
+    const int g = c->n_heads / c->n_kv_heads;
+    KB_CHECK(g == 1 || g == 2 || g == 4 || g == 8, "GQA group %d not in {1,2,4,8}", g);
+    KB_CHECK((c->n_heads * c->head_dim) % 64 == 0, "n_heads*head_dim must be a multiple of 64");
+    KB_CHECK(c->vocab > 0 && c->vocab % 8 == 0, "vocab=%d must be a positive multiple of 8", c->vocab);
+    KB_CHECK(c->rope_theta > 1.f && c->rms_eps > 0.f, "bad rope_theta / rms_eps");
+    return KB_OK;
+}
+
+}  // namespace kb
+
+struct kb_engine {
+    int device = 0;
+    kb_model_cfg cfg{};
+    std::vector<kb_layer_weights> layers;
+    const void* embed = nullptr;
+    const void* final_norm = nullptr;
+    const void* lm_head = nullptr;
+    bool have_weights = false;
+    __nv_bfloat16* k_pool = nullptr;
+    __nv_bfloat16* v_pool = nullptr;
+    int n_blocks = 0;
+    kb::Workspace ws;
+    int max_tokens = 0, max_seqs = 0;
+};
+
+namespace kb {
+
+// One forward pass over n_tokens packed tokens of n_seqs sequences.
+//   decode == true : one token per sequence, cu_seqlens == nullptr
+static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* ctx_lens, const int* block_tables,
+                   int n_seqs, int n_tokens, int max_blocks, int max_new, int max_ctx, bool decode,
+                   const kb_sampling* sampling, float* logits_out, int* out_tokens, bool advance_ctx,
+                   cudaStream_t stream) {
+    KB_CHECK(e != nullptr, "null engine");
+    KB_CHECK(e->have_weights, "weights not bound (kb_bind_weights)");
+    KB_CHECK(e->k_pool && e->v_pool, "KV pool not bound (kb_bind_kv_pool)");
+    KB_CHECK(e->ws.x != nullptr, "workspace not bound (kb_bind_workspace)");
+    KB_CHECK(n_seqs > 0 && n_tokens >= n_seqs, "bad batch: n_seqs=%d n_tokens=%d", n_seqs, n_tokens);
+    KB_CHECK(n_tokens <= e->max_tokens, "n_tokens=%d exceeds workspace max_tokens=%d", n_tokens, e->max_tokens);
+    KB_CHECK(n_seqs <= e->max_seqs, "n_seqs=%d exceeds workspace max_seqs=%d", n_seqs, e->max_seqs);
+    KB_CHECK(tokens && ctx_lens && block_tables, "null token / ctx_lens / block_tables pointer");
+    KB_CHECK(decode || cu_seqlens != nullptr, "prefill needs cu_seqlens");
+    KB_CHECK(out_tokens == nullptr || sampling != nullptr, "out_tokens requested without sampling params");
+    int dev = -1;
+    KB_CUDA(cudaGetDevice(&dev));
+    KB_CHECK(dev == e->device, "engine belongs to device %d but current device is %d", e->device, dev);
+
+    const kb_model_cfg& c = e->cfg;
+    Workspace& w = e->ws;
+    const int qdim = c.n_heads * c.head_dim;
+    const int qkv_dim = (c.n_heads + 2 * c.n_kv_heads) * c.head_dim;
+    const size_t layer_stride = (size_t)e->n_blocks * c.n_kv_heads * KB_BLOCK_TOKENS * c.head_dim;
+    int rc;
+
+    if ((rc = embed(tokens, e->embed, w.x, n_tokens, c.hidden, c.vocab, stream))) return rc;
+    for (int L = 0; L < c.n_layers; ++L) {
+        const kb_layer_weights& lw = e->layers[L];
+        __nv_bfloat16* kp = e->k_pool + (size_t)L * layer_stride;
+        __nv_bfloat16* vp = e->v_pool + (size_t)L * layer_stride;
+        if ((rc = rmsnorm(w.x, lw.attn_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, stream))) return rc;
+        if ((rc = gemm(w.xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16, stream))) return rc;
+        if ((rc = rope_append(w.qkv, cu_seqlens, ctx_lens, block_tables, kp, vp, n_seqs, n_tokens, max_blocks,
+                              c.n_heads, c.n_kv_heads, c.head_dim, c.rope_theta, stream)))
+            return rc;
+        if (decode) {
+            rc = attn_decode(w.qkv, qkv_dim, kp, vp, ctx_lens, /*bias=*/1, block_tables, w.attn, n_seqs, max_blocks,
+                             c.n_heads, c.n_kv_heads, c.head_dim, max_ctx > 0 ? max_ctx + 1 : 0, w.split,
+                             w.split_bytes, stream);
+        } else {
+            rc = attn_prefill(w.qkv, qkv_dim, kp, vp, cu_seqlens, ctx_lens, block_tables, w.attn, n_seqs, n_tokens,
+                              max_new, max_blocks, c.n_heads, c.n_kv_heads, c.head_dim, stream);
+        }
+        if (rc) return rc;
+        if ((rc = gemm(w.attn, lw.wo, w.x, w.x, n_tokens, c.hidden, qdim, KB_EPI_RESID_F32, stream))) return rc;
+        if ((rc = rmsnorm(w.x, lw.mlp_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, stream))) return rc;
+        if ((rc = gemm(w.xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden, KB_EPI_SWIGLU_BF16, stream)))
+            return rc;
+        if ((rc = gemm(w.h, lw.w_down, w.x, w.x, n_tokens, c.hidden, c.ffn, KB_EPI_RESID_F32, stream))) return rc;
+    }
+    if (logits_out == nullptr && out_tokens == nullptr) return KB_OK;  // KV fill only
+    // final norm on the last row of every sequence, lm_head, sampling
+    if ((rc = rmsnorm(w.x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, n_seqs, c.hidden, c.rms_eps, stream)))
+        return rc;
+    float* lg = logits_out ? logits_out : w.logits;
+    if ((rc = gemm(w.xl, e->lm_head, lg, nullptr, n_seqs, c.vocab, c.hidden, KB_EPI_F32, stream))) return rc;
+    if (out_tokens) {
+        if ((rc = sample(lg, n_seqs, c.vocab, sampling, out_tokens, advance_ctx ? ctx_lens : nullptr, stream)))
+            return rc;
+    }
+    return KB_OK;
+}
+
+}  // namespace kb
+
+// ---------------------------------------------------------------------------------------------
+// extern "C"
+// ---------------------------------------------------------------------------------------------
+extern "C" const char* kb_last_error(void) { return kb::g_err; }
+extern "C" int kb_abi_version(void) { return KB_ABI_VERSION; }
+extern "C" unsigned long long kb_launch_count(void) { return kb::g_launches; }
+
+extern "C" int kb_engine_create(int device, const kb_model_cfg* cfg, kb_engine** out) {
+    KB_CHECK(out != nullptr, "kb_engine_create: null out");
+    *out = nullptr;
+    int rc = kb::check_cfg(cfg);
+    if (rc) return rc;
+    int count = 0;
+    cudaError_t ce = cudaGetDeviceCount(&count);
+    if (ce != cudaSuccess || count <= 0) {
+        kb::set_error("kb_engine_create: no CUDA device available (%s); this library has no CPU fallback",
+                      cudaGetErrorString(ce));
+        return KB_ERR_CUDA;
+    }
+    KB_CHECK(device >= 0 && device < count, "kb_engine_create: device %d out of range (%d devices)", device, count);
+    cudaDeviceProp prop;
+    KB_CUDA(cudaGetDeviceProperties(&prop, device));
+    KB_CHECK(prop.major == 10, "kb_engine_create: device %d is sm_%d%d; this library is built for sm_100a only", device,
+             prop.major, prop.minor);
+    kb_engine* e = new (std::nothrow) kb_engine();
+    KB_CHECK(e != nullptr, "kb_engine_create: out of host memory");
+    e->device = device;
+    e->cfg = *cfg;
+    *out = e;
+    return KB_OK;
+}
+
+extern "C" void kb_engine_destroy(kb_engine* e) { delete e; }
+
+extern "C" int kb_bind_weights(kb_engine* e, const kb_weight_ptrs* w) {
+    KB_CHECK(e && w && w->layers, "kb_bind_weights: null argument");
+    KB_CHECK(w->embed && w->final_norm && w->lm_head, "kb_bind_weights: null embed / final_norm / lm_head");
+    e->layers.assign(w->layers, w->layers + e->cfg.n_layers);
+    for (int i = 0; i < e->cfg.n_layers; ++i) {
+        const kb_layer_weights& l = e->layers[i];
+        KB_CHECK(l.attn_norm && l.wqkv && l.wo && l.mlp_norm && l.w_gate_up && l.w_down,
+                 "kb_bind_weights: null pointer in layer %d", i);
+    }
+    e->embed = w->embed;
+    e->final_norm = w->final_norm;
+    e->lm_head = w->lm_head;
+    e->have_weights = true;
+    return KB_OK;
+}
+
+extern "C" int kb_bind_kv_pool(kb_engine* e, void* k_pool, void* v_pool, int32_t n_blocks) {
+    KB_CHECK(e && k_pool && v_pool && n_blocks > 0, "kb_bind_kv_pool: bad arguments");
+    KB_CHECK((reinterpret_cast<uintptr_t>(k_pool) & 127) == 0 && (reinterpret_cast<uintptr_t>(v_pool) & 127) == 0,
+             "kb_bind_kv_pool: pools must be 128-byte aligned");
+    e->k_pool = reinterpret_cast<__nv_bfloat16*>(k_pool);
+    e->v_pool = reinterpret_cast<__nv_bfloat16*>(v_pool);
+    e->n_blocks = n_blocks;
+    return KB_OK;
+}
+
+extern "C" size_t kb_workspace_bytes(const kb_model_cfg* cfg, int32_t max_tokens, int32_t max_seqs) {
+    if (kb::check_cfg(cfg) || max_tokens <= 0 || max_seqs <= 0) return 0;
+    kb::Workspace w;
+    kb::layout_workspace(*cfg, max_tokens, max_seqs, nullptr, &w);
+    return w.total;
+}
+
+extern "C" int kb_bind_workspace(kb_engine* e, void* ws, size_t bytes, int32_t max_tokens, int32_t max_seqs) {
+    KB_CHECK(e && ws && max_tokens > 0 && max_seqs > 0, "kb_bind_workspace: bad arguments");
+    KB_CHECK((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "kb_bind_workspace: workspace must be 256-byte aligned");
+    kb::Workspace w;
+    kb::layout_workspace(e->cfg, max_tokens, max_seqs, reinterpret_cast<uint8_t*>(ws), &w);
+    KB_CHECK(w.total <= bytes, "kb_bind_workspace: need %zu bytes, got %zu", w.total, bytes);
+    e->ws = w;
+    e->max_tokens = max_tokens;
+    e->max_seqs = max_seqs;
+    return KB_OK;
+}
+
+extern "C" int kb_prefill(kb_engine* e, const int32_t* tokens, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+                          const int32_t* block_tables, int32_t n_seqs, int32_t n_tokens, int32_t max_blocks,
+                          int32_t max_new, const kb_sampling* sampling, float* logits_last, int32_t* out_tokens,
+                          kb_stream stream) {
+    return kb::forward(e, tokens, cu_seqlens, const_cast<int32_t*>(ctx_lens), block_tables, n_seqs, n_tokens,
+                       max_blocks, max_new, 0, false, sampling, logits_last, out_tokens, false,
+                       reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int kb_decode(kb_engine* e, const int32_t* last_tokens, int32_t* ctx_lens, const int32_t* block_tables,
+                         int32_t batch, int32_t max_blocks, int32_t max_ctx, const kb_sampling* sampling,
+                         int32_t* out_tokens, float* logits_dbg, int32_t advance_ctx, kb_stream stream) {
+    return kb::forward(e, last_tokens, nullptr, ctx_lens, block_tables, batch, batch, max_blocks, 1, max_ctx, true,
+                       sampling, logits_dbg, out_tokens, advance_ctx != 0, reinterpret_cast<cudaStream_t>(stream));
+}

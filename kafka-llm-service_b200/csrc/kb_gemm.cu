@@ -1,0 +1,416 @@
+// kb_gemm.cu — D = A[M,K] * W[N,K]^T on the 5th-gen tensor cores (tcgen05), sm_100a.
+//
+// Takes over the projections (QKV / O / gate-up / down / lm_head) of the completion the reference
+// obtains remotely (src/llm/portkey.py:379). There is no reference kernel to translate; the design
+// is the Blackwell-native one:
+//
+//   * persistent CTAs (one per SM), static tile schedule, M-fastest so the CTAs that run
+//     concurrently share one weight tile through L2;
+//   * warp 0   : TMA producer  (cp.async.bulk.tensor.2d, SWIZZLE_128B boxes, mbarrier tx-count)
+//     warp 1   : MMA issuer    (one elected thread, tcgen05.mma.cta_group::1.kind::f16, 128 x BN x 16)
+//     warp 2   : TMEM allocator (2 accumulators of BN fp32 columns -> epilogue overlaps next tile)
+//     warps 4-7: epilogue      (tcgen05.ld 32x32b.x32 -> registers -> fused epilogue -> global)
+//   * three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue).
+//
+// Roofline: tensor pipe for M >= ~256 rows, weight bandwidth below that.
+// Algorithmic FLOPs per launch = 2*M*N*K.
+#include "kb_common.cuh"
+
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <cudaTypedefs.h>
+#include <stdlib.h>
+
+namespace kb {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_BK = 64;  // 64 bf16 = 128 bytes = one SWIZZLE_128B row
+constexpr int GEMM_THREADS = 256;
+
+template <int BN>
+struct GemmCfg {
+    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
+    static constexpr int B_BYTES = BN * GEMM_BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;  // power of two: 128/256/512
+    static constexpr int BAR_BYTES = 256;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // +1024: manual alignment
+};
+
+// Shared-memory matrix descriptor for a K-major tile stored as rows of 128 bytes with the
+// 128-byte swizzle TMA applied (8-row atoms of 1024 bytes).
+__device__ __forceinline__ uint64_t make_sw128_kmajor_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);  // start address, 16-byte units
+    d |= (uint64_t)1 << 16;                    // leading byte offset: unused for swizzled K-major
+    d |= (uint64_t)(1024 >> 4) << 32;          // stride byte offset: next 8-row atom
+    d |= (uint64_t)1 << 46;                    // descriptor version 1 (Blackwell)
+    d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
+    return d;
+}
+
+// kind::f16 instruction descriptor: A=B=bf16 (K-major both), D=fp32, M=128, N=BN.
+__host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n) {
+    return (1u << 4)                       // D format  fp32
+           | (1u << 7)                     // A format  bf16
+           | (1u << 10)                    // B format  bf16
+           | ((uint32_t)(n >> 3) << 17)    // N / 8
+           | ((uint32_t)(m >> 4) << 24);   // M / 16
+}
+
+__device__ __forceinline__ float silu_f(float g) { return g / (1.0f + __expf(-g)); }
+
+template <int EPI>
+__device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* out, const float* resid, int row,
+                                                 int col0, int N) {
+    // 32 consecutive fp32 accumulator columns [col0, col0+32) of one row. N % 8 == 0.
+    if (EPI == KB_EPI_BF16) {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (size_t)row * N + col0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (col0 + j * 8 < N) {
+                uint4 v;
+                v.x = pack_bf16(__uint_as_float(r[j * 8 + 0]), __uint_as_float(r[j * 8 + 1]));
+                v.y = pack_bf16(__uint_as_float(r[j * 8 + 2]), __uint_as_float(r[j * 8 + 3]));
+                v.z = pack_bf16(__uint_as_float(r[j * 8 + 4]), __uint_as_float(r[j * 8 + 5]));
+                v.w = pack_bf16(__uint_as_float(r[j * 8 + 6]), __uint_as_float(r[j * 8 + 7]));
+                *reinterpret_cast<uint4*>(o + j * 8) = v;
+            }
+        }
+    } else if (EPI == KB_EPI_F32 || EPI == KB_EPI_RESID_F32) {
+        float* o = reinterpret_cast<float*>(out) + (size_t)row * N + col0;
+        const float* rs = resid + (size_t)row * N + col0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (col0 + j * 4 < N) {
+                float4 v = make_float4(__uint_as_float(r[j * 4 + 0]), __uint_as_float(r[j * 4 + 1]),
+                                       __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
+                if (EPI == KB_EPI_RESID_F32) {
+                    float4 q = *reinterpret_cast<const float4*>(rs + j * 4);
+                    v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
+                }
+                *reinterpret_cast<float4*>(o + j * 4) = v;
+            }
+        }
+    } else {  // KB_EPI_SWIGLU_BF16: columns (2j, 2j+1) = (gate_j, up_j) -> out[:, j]
+        const int No = N >> 1;
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (size_t)row * No + (col0 >> 1);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            if (col0 + j * 16 < N) {
+                float h[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float g = __uint_as_float(r[j * 16 + 2 * i]);
+                    float u = __uint_as_float(r[j * 16 + 2 * i + 1]);
+                    h[i] = silu_f(g) * u;
+                }
+                uint4 v;
+                v.x = pack_bf16(h[0], h[1]);
+                v.y = pack_bf16(h[2], h[3]);
+                v.z = pack_bf16(h[4], h[5]);
+                v.w = pack_bf16(h[6], h[7]);
+                *reinterpret_cast<uint4*>(o + j * 8) = v;
+            }
+        }
+    }
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, void* out,
+                    const float* resid, int M, int N, int K) {
+    using Cfg = GemmCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + Cfg::STAGES;
+    uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
+    const int num_n = (N + BN - 1) / BN;
+    const int num_tiles = num_m * num_n;
+    const int num_k = K / GEMM_BK;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            tma_prefetch_desc(&tmA);
+            tma_prefetch_desc(&tmB);
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            for (int s = 0; s < Cfg::STAGES; ++s) {
+                mbar_init(&full_bar[s], 1);
+                mbar_init(&empty_bar[s], 1);
+            }
+            for (int a = 0; a < 2; ++a) {
+                mbar_init(&tmem_full_bar[a], 1);
+                mbar_init(&tmem_empty_bar[a], 4);  // one arrive per epilogue warp
+            }
+            fence_mbar_init();
+        }
+    } else if (warp == 2) {
+        tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m_blk = tile % num_m;
+                const int n_blk = tile / num_m;
+                for (int kb = 0; kb < num_k; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+                    uint8_t* sb = sa + Cfg::A_BYTES;
+                    mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                    tma_load_2d(sa, &tmA, kb * GEMM_BK, m_blk * GEMM_BM, &full_bar[stage]);
+                    tma_load_2d(sb, &tmB, kb * GEMM_BK, n_blk * BN, &full_bar[stage]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (elect_one()) {
+            constexpr uint32_t idesc = make_idesc_bf16(GEMM_BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);  // epilogue drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = 0; kb < num_k; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);  // TMA bytes landed
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+                    const uint64_t adesc = make_sw128_kmajor_desc(sa);
+                    const uint64_t bdesc = make_sw128_kmajor_desc(sa + Cfg::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k) {
+                        // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in 16-byte units
+                        umma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                                  (uint32_t)((kb | k) != 0));
+                    }
+                    umma_commit(&empty_bar[stage]);  // smem slot free once these MMAs retire
+                    if (kb == num_k - 1) umma_commit(&tmem_full_bar[acc]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: TMEM -> registers -> global =====
+        const int ew = warp - 4;  // == warp % 4: the TMEM lane quarter this warp may read
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m_blk = tile % num_m;
+            const int n_blk = tile / num_m;
+            mbar_wait(&tmem_full_bar[acc], acc_phase);
+            tc_fence_after();
+            const int row = m_blk * GEMM_BM + ew * 32 + lane;
+            const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(t_row + (uint32_t)c, r);
+                tmem_ld_wait();
+                const int col0 = n_blk * BN + c;
+                if (row < M && col0 < N) epilogue_store32<EPI>(r, out, resid, row, col0, N);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
+static std::mutex g_map_mu;
+
+struct MapKey {
+    const void* ptr;
+    uint64_t rows, cols;
+    uint32_t box_rows;
+    bool operator==(const MapKey& o) const {
+        return ptr == o.ptr && rows == o.rows && cols == o.cols && box_rows == o.box_rows;
+    }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        size_t h = std::hash<const void*>()(k.ptr);
+        h ^= std::hash<uint64_t>()(k.rows * 1000003ull + k.cols) + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+        h ^= std::hash<uint32_t>()(k.box_rows) + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+        return h;
+    }
+};
+static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+
+static int get_tensor_map(const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows, CUtensorMap* out) {
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        KB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+        KB_CHECK(fn != nullptr && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled not available");
+        g_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+    }
+    MapKey key{ptr, rows, cols, box_rows};
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) {
+        *out = it->second;
+        return KB_OK;
+    }
+    if (g_maps.size() > 65536) g_maps.clear();
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * 2};
+    cuuint32_t box[2] = {(cuuint32_t)GEMM_BK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUtensorMap m;
+    CUresult r = g_encode(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    KB_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%llu cols=%llu box=%u", (int)r,
+             (unsigned long long)rows, (unsigned long long)cols, box_rows);
+    g_maps.emplace(key, m);
+    *out = m;
+    return KB_OK;
+}
+
+static int g_num_sms = 0;
+static int num_sms() {
+    if (g_num_sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        if (g_num_sms <= 0) g_num_sms = 148;
+    }
+    return g_num_sms;
+}
+
+template <int BN, int EPI>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M, int N,
+                       int K, cudaStream_t stream) {
+    using Cfg = GemmCfg<BN>;
+    static bool configured[64] = {};
+    auto kern = gemm_tcgen05_kernel<BN, EPI>;
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    const int num_tiles = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + BN - 1) / BN);
+    int grid = num_tiles < num_sms() ? num_tiles : num_sms();
+    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+template <int BN>
+static int dispatch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M, int N,
+                        int K, int epi, cudaStream_t stream) {
+    switch (epi) {
+        case KB_EPI_BF16: return launch_gemm<BN, KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, stream);
+        case KB_EPI_F32: return launch_gemm<BN, KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, stream);
+        case KB_EPI_RESID_F32: return launch_gemm<BN, KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, stream);
+        case KB_EPI_SWIGLU_BF16: return launch_gemm<BN, KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, stream);
+    }
+    set_error("kb_gemm: unknown epilogue %d", epi);
+    return KB_ERR_INVALID;
+}
+
+// Tile width: minimise (tiles per busiest CTA) x BN under the static persistent schedule.
+static int pick_bn(int M, int N) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* s = getenv("KB_GEMM_BN");
+        forced = s ? atoi(s) : 0;
+    }
+    if (forced == 64 || forced == 128 || forced == 256) return forced;
+    const int sms = num_sms();
+    const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
+    long best_cost = -1;
+    int best = 128;
+    const int cands[3] = {256, 128, 64};
+    for (int i = 0; i < 3; ++i) {
+        const int bn = cands[i];
+        const long tiles = (long)num_m * ((N + bn - 1) / bn);
+        const long per_cta = (tiles + sms - 1) / sms;
+        // narrower tiles pay more A re-reads and smem bandwidth per flop: small penalty
+        const long cost = per_cta * bn * (bn == 256 ? 100 : (bn == 128 ? 104 : 125));
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
+    }
+    return best;
+}
+
+int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi, int tile_n,
+            cudaStream_t stream) {
+    KB_CHECK(M > 0 && N > 0 && K > 0, "kb_gemm: bad shape M=%d N=%d K=%d", M, N, K);
+    KB_CHECK(K % GEMM_BK == 0, "kb_gemm: K=%d must be a multiple of %d", K, GEMM_BK);
+    KB_CHECK(N % 8 == 0, "kb_gemm: N=%d must be a multiple of 8", N);
+    KB_CHECK(epi != KB_EPI_SWIGLU_BF16 || N % 16 == 0, "kb_gemm: SwiGLU needs N %% 16 == 0");
+    KB_CHECK(epi != KB_EPI_RESID_F32 || resid != nullptr, "kb_gemm: residual epilogue needs resid");
+    KB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+             "kb_gemm: pointers must be 16-byte aligned");
+    KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256, "kb_gemm: tile_n=%d not in {0,64,128,256}",
+             tile_n);
+    const int bn = tile_n ? tile_n : pick_bn(M, N);
+    CUtensorMap tmA, tmB;
+    int rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, GEMM_BM, &tmA);
+    if (rc) return rc;
+    rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)bn, &tmB);
+    if (rc) return rc;
+    if (bn == 256) return dispatch_epi<256>(tmA, tmB, out, resid, M, N, K, epi, stream);
+    if (bn == 128) return dispatch_epi<128>(tmA, tmB, out, resid, M, N, K, epi, stream);
+    return dispatch_epi<64>(tmA, tmB, out, resid, M, N, K, epi, stream);
+}
+
+int gemm(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi,
+         cudaStream_t stream) {
+    return gemm_ex(a, w, out, resid, M, N, K, epi, 0, stream);
+}
+
+}  // namespace kb
+
+extern "C" int kb_gemm_ex(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M,
+                          int32_t N, int32_t K, int32_t epilogue, int32_t tile_n, kb_stream stream) {
+    return kb::gemm_ex(a_bf16, w_bf16, out, resid, M, N, K, epilogue, tile_n, reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int kb_gemm(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,
+                       int32_t K, int32_t epilogue, kb_stream stream) {
+    return kb::gemm(a_bf16, w_bf16, out, resid, M, N, K, epilogue, reinterpret_cast<cudaStream_t>(stream));
+}

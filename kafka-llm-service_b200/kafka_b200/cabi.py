@@ -1,0 +1,226 @@
+"""ctypes binding of libkafka_b200.so (the C ABI declared in include/kafka_b200.h).
+
+This is the only place Python touches the CUDA path. Tensors are passed as raw device pointers
+(``tensor.data_ptr()``) and the current torch CUDA stream as a ``cudaStream_t``; PyTorch is used for
+allocation and streams only. There is deliberately no fallback: if the shared library is missing or
+a call fails, ``KafkaB200Error`` is raised.
+
+Reference counterpart: none — the reference's provider boundary is a Python ABC
+(/root/reference/src/llm/base.py:67) whose implementation is an HTTPS call
+(/root/reference/src/llm/portkey.py:379). INTEGRATION.md shows the stub a maintainer would add.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+from typing import Optional
+
+KB_BLOCK_TOKENS = 64
+KB_MAX_SPLITS = 16
+KB_ABI_VERSION = 1
+
+EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_SWIGLU_BF16 = 0, 1, 2, 3
+
+_LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libkafka_b200.so"
+
+
+class KafkaB200Error(RuntimeError):
+    """Raised when the CUDA library is missing or a C-ABI call returns non-zero."""
+
+
+class ModelCfg(C.Structure):
+    _fields_ = [
+        ("hidden", C.c_int32), ("n_layers", C.c_int32), ("n_heads", C.c_int32), ("n_kv_heads", C.c_int32),
+        ("head_dim", C.c_int32), ("ffn", C.c_int32), ("vocab", C.c_int32), ("max_pos", C.c_int32),
+        ("rope_theta", C.c_float), ("rms_eps", C.c_float),
+    ]
+
+
+class LayerWeights(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("attn_norm", "wqkv", "wo", "mlp_norm", "w_gate_up", "w_down")]
+
+
+class WeightPtrs(C.Structure):
+    _fields_ = [("embed", C.c_void_p), ("final_norm", C.c_void_p), ("lm_head", C.c_void_p),
+                ("layers", C.POINTER(LayerWeights))]
+
+
+class Sampling(C.Structure):
+    _fields_ = [("temperature", C.c_float), ("seed", C.c_uint64), ("step", C.c_uint64),
+                ("banned_token", C.c_int32), ("allowed_lo", C.c_int32), ("allowed_hi", C.c_int32),
+                ("extra_a", C.c_int32), ("extra_b", C.c_int32)]
+
+
+# name -> (restype, argtypes); kept in one table so tests can check every symbol the header declares.
+_i32, _vp, _sz, _f = C.c_int32, C.c_void_p, C.c_size_t, C.c_float
+SIGNATURES = {
+    "kb_engine_create": (C.c_int, [C.c_int, C.POINTER(ModelCfg), C.POINTER(_vp)]),
+    "kb_engine_destroy": (None, [_vp]),
+    "kb_bind_weights": (C.c_int, [_vp, C.POINTER(WeightPtrs)]),
+    "kb_bind_kv_pool": (C.c_int, [_vp, _vp, _vp, _i32]),
+    "kb_workspace_bytes": (_sz, [C.POINTER(ModelCfg), _i32, _i32]),
+    "kb_bind_workspace": (C.c_int, [_vp, _vp, _sz, _i32, _i32]),
+    "kb_prefill": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.POINTER(Sampling), _vp, _vp, _vp]),
+    "kb_decode": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, C.POINTER(Sampling), _vp, _vp, _i32, _vp]),
+    "kb_rmsnorm": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _f, _vp]),
+    "kb_embed": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
+    "kb_gemm": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+    "kb_gemm_ex": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "kb_rope_append": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _f, _vp]),
+    "kb_attn_decode_scratch_bytes": (_sz, [_i32, _i32, _i32]),
+    "kb_attn_decode": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
+                                 _vp, _sz, _vp]),
+    "kb_attn_prefill": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
+                                  _i32, _vp]),
+    "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
+    "kb_last_error": (C.c_char_p, []),
+    "kb_abi_version": (C.c_int, []),
+    "kb_launch_count": (C.c_ulonglong, []),
+}
+
+_lib: Optional[C.CDLL] = None
+
+
+def lib_path() -> Path:
+    return Path(os.environ.get("KAFKA_B200_LIB", str(_LIB_PATH)))
+
+
+def load() -> C.CDLL:
+    """Load the shared library once; raise loudly if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not path.exists():
+        raise KafkaB200Error(
+            f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback for the completion path.")
+    try:
+        lib = C.CDLL(str(path))
+    except OSError as e:  # missing libcudart etc.
+        raise KafkaB200Error(f"cannot load {path}: {e}") from e
+    for name, (res, args) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as e:
+            raise KafkaB200Error(f"{path} does not export {name}") from e
+        fn.restype = res
+        fn.argtypes = args
+    if lib.kb_abi_version() != KB_ABI_VERSION:
+        raise KafkaB200Error(f"ABI mismatch: library {lib.kb_abi_version()} vs binding {KB_ABI_VERSION}")
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return (load().kb_last_error() or b"").decode("utf-8", "replace")
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise KafkaB200Error(f"{what} failed (rc={rc}): {last_error()}")
+
+
+def launch_count() -> int:
+    return int(load().kb_launch_count())
+
+
+def _ptr(t) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ------------------------------------------------------------------------------------------------
+# thin tensor-level wrappers of the per-kernel entry points (used by tests, smoke and the engine)
+# ------------------------------------------------------------------------------------------------
+def rmsnorm(x, w, eps: float):
+    import torch
+    n, hidden = x.shape
+    y = torch.empty((n, hidden), dtype=torch.bfloat16, device=x.device)
+    check(load().kb_rmsnorm(_ptr(x), _ptr(w), _ptr(y), n, hidden, eps, _stream()), "kb_rmsnorm")
+    return y
+
+
+def embed(tokens, table):
+    import torch
+    n = tokens.numel()
+    vocab, hidden = table.shape
+    x = torch.empty((n, hidden), dtype=torch.float32, device=table.device)
+    check(load().kb_embed(_ptr(tokens), _ptr(table), _ptr(x), n, hidden, vocab, _stream()), "kb_embed")
+    return x
+
+
+def gemm(a, w, epilogue: int = EPI_BF16, resid=None, out=None, tile_n: int = 0):
+    """out = a[M,K] @ w[N,K]^T with the fused epilogue (see include/kafka_b200.h)."""
+    import torch
+    M, K = a.shape
+    N, K2 = w.shape
+    assert K == K2
+    if out is None:
+        if epilogue == EPI_BF16:
+            out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+        elif epilogue == EPI_SWIGLU_BF16:
+            out = torch.empty((M, N // 2), dtype=torch.bfloat16, device=a.device)
+        else:
+            out = torch.empty((M, N), dtype=torch.float32, device=a.device)
+    check(load().kb_gemm_ex(_ptr(a), _ptr(w), _ptr(out), _ptr(resid), M, N, K, epilogue, tile_n, _stream()),
+          "kb_gemm")
+    return out
+
+
+def rope_append(qkv, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_heads, n_kv_heads,
+                head_dim, theta):
+    n_tokens = qkv.shape[0]
+    n_seqs, max_blocks = block_tables.shape
+    check(load().kb_rope_append(_ptr(qkv), _ptr(cu_seqlens), _ptr(ctx_lens), _ptr(block_tables),
+                                _ptr(k_pool_layer), _ptr(v_pool_layer), n_seqs, n_tokens, max_blocks, n_heads,
+                                n_kv_heads, head_dim, theta, _stream()), "kb_rope_append")
+
+
+def attn_decode(q, k_pool_layer, v_pool_layer, kv_lens, block_tables, n_heads, n_kv_heads, head_dim,
+                kv_len_bias: int = 0, max_kv_len: int = 0, scratch=None):
+    import torch
+    batch, max_blocks = block_tables.shape
+    out = torch.empty((batch, n_heads * head_dim), dtype=torch.bfloat16, device=q.device)
+    sb = 0 if scratch is None else scratch.numel() * scratch.element_size()
+    check(load().kb_attn_decode(_ptr(q), q.stride(0), _ptr(k_pool_layer), _ptr(v_pool_layer), _ptr(kv_lens),
+                                kv_len_bias, _ptr(block_tables), _ptr(out), batch, max_blocks, n_heads, n_kv_heads,
+                                head_dim, max_kv_len, _ptr(scratch), sb, _stream()), "kb_attn_decode")
+    return out
+
+
+def attn_decode_scratch_bytes(batch: int, n_heads: int, head_dim: int) -> int:
+    return int(load().kb_attn_decode_scratch_bytes(batch, n_heads, head_dim))
+
+
+def attn_prefill(q, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tables, max_new, n_heads, n_kv_heads,
+                 head_dim):
+    import torch
+    n_tokens = q.shape[0]
+    n_seqs, max_blocks = block_tables.shape
+    out = torch.empty((n_tokens, n_heads * head_dim), dtype=torch.bfloat16, device=q.device)
+    check(load().kb_attn_prefill(_ptr(q), q.stride(0), _ptr(k_pool_layer), _ptr(v_pool_layer), _ptr(cu_seqlens),
+                                 _ptr(ctx_lens), _ptr(block_tables), _ptr(out), n_seqs, n_tokens, max_new,
+                                 max_blocks, n_heads, n_kv_heads, head_dim, _stream()), "kb_attn_prefill")
+    return out
+
+
+def make_sampling(temperature: float = 0.0, seed: int = 0, step: int = 0, banned_token: int = -1,
+                  allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1) -> Sampling:
+    return Sampling(float(temperature), int(seed), int(step), int(banned_token), int(allowed_lo), int(allowed_hi),
+                    int(extra_a), int(extra_b))
+
+
+def sample(logits, temperature: float = 0.0, seed: int = 0, step: int = 0, banned_token: int = -1,
+           allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1):
+    import torch
+    n, vocab = logits.shape
+    out = torch.empty((n,), dtype=torch.int32, device=logits.device)
+    sp = make_sampling(temperature, seed, step, banned_token, allowed_lo, allowed_hi, extra_a, extra_b)
+    check(load().kb_sample(_ptr(logits), n, vocab, C.byref(sp), _ptr(out), _stream()), "kb_sample")
+    return out

@@ -1,0 +1,109 @@
+"""EngineCore — one GPU's model replica behind the C ABI.
+
+Owns (through PyTorch, which is only the allocator here) the fused bf16 weights, the paged KV pools
+and the activation workspace, binds them into a ``kb_engine`` and exposes the two hot-path calls
+(``prefill`` / ``decode``) on device tensors. No arithmetic happens in Python.
+
+Takes over what `/root/reference/src/llm/portkey.py:379` delegates to a remote service.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import torch
+
+from . import cabi
+from .cabi import KB_BLOCK_TOKENS, KafkaB200Error
+from .model_config import LlamaConfig
+from .kv_layout import pool_shape
+
+
+class EngineCore:
+    def __init__(self, cfg: LlamaConfig, fused_weights: Dict[str, torch.Tensor], device: torch.device,
+                 n_blocks: int, max_tokens: int, max_seqs: int):
+        if not torch.cuda.is_available():
+            raise KafkaB200Error("EngineCore needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = cabi.load()
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.n_blocks = int(n_blocks)
+        self.max_tokens = int(max_tokens)
+        self.max_seqs = int(max_seqs)
+        torch.cuda.set_device(self.device)
+
+        self.weights = fused_weights  # keep the tensors alive: the library only borrows pointers
+        for name, t in fused_weights.items():
+            if t.device != self.device or t.dtype != torch.bfloat16 or not t.is_contiguous():
+                raise KafkaB200Error(f"weight {name} must be a contiguous bf16 tensor on {self.device}")
+
+        self._cfg_c = cabi.ModelCfg(cfg.hidden, cfg.n_layers, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn,
+                                    cfg.vocab, cfg.max_pos, cfg.rope_theta, cfg.rms_eps)
+        handle = C.c_void_p()
+        cabi.check(self.lib.kb_engine_create(self.device.index or 0, C.byref(self._cfg_c), C.byref(handle)),
+                   "kb_engine_create")
+        self._h = handle
+
+        layers = (cabi.LayerWeights * cfg.n_layers)()
+        for i in range(cfg.n_layers):
+            p = f"l{i}."
+            layers[i] = cabi.LayerWeights(*(fused_weights[p + k].data_ptr() for k in
+                                            ("attn_norm", "wqkv", "wo", "mlp_norm", "w_gate_up", "w_down")))
+        self._layers_c = layers
+        wp = cabi.WeightPtrs(fused_weights["embed"].data_ptr(), fused_weights["final_norm"].data_ptr(),
+                             fused_weights["lm_head"].data_ptr(), layers)
+        cabi.check(self.lib.kb_bind_weights(self._h, C.byref(wp)), "kb_bind_weights")
+
+        # KV pools: zero-initialised so masked tail positions are finite (see kb_attn_decode's contract)
+        shape = pool_shape(cfg.n_layers, self.n_blocks, cfg.n_kv_heads, cfg.head_dim)
+        self.k_pool = torch.zeros(shape, dtype=torch.bfloat16, device=self.device)
+        self.v_pool = torch.zeros(shape, dtype=torch.bfloat16, device=self.device)
+        cabi.check(self.lib.kb_bind_kv_pool(self._h, self.k_pool.data_ptr(), self.v_pool.data_ptr(), self.n_blocks),
+                   "kb_bind_kv_pool")
+
+        ws_bytes = int(self.lib.kb_workspace_bytes(C.byref(self._cfg_c), self.max_tokens, self.max_seqs))
+        if ws_bytes == 0:
+            raise KafkaB200Error(f"kb_workspace_bytes rejected the configuration: {cabi.last_error()}")
+        self.workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device)
+        cabi.check(self.lib.kb_bind_workspace(self._h, self.workspace.data_ptr(), ws_bytes, self.max_tokens,
+                                              self.max_seqs), "kb_bind_workspace")
+
+    # ---- sizing helpers ----------------------------------------------------------------------
+    @staticmethod
+    def kv_block_bytes(cfg: LlamaConfig) -> int:
+        """Bytes one KV block occupies over all layers, K and V."""
+        return 2 * cfg.n_layers * cfg.n_kv_heads * KB_BLOCK_TOKENS * cfg.head_dim * 2
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self.lib.kb_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- hot path ----------------------------------------------------------------------------
+    def prefill(self, tokens: torch.Tensor, cu_seqlens: torch.Tensor, ctx_lens: torch.Tensor,
+                block_tables: torch.Tensor, max_new: int, sampling: Optional[cabi.Sampling] = None,
+                logits_out: Optional[torch.Tensor] = None, out_tokens: Optional[torch.Tensor] = None) -> None:
+        n_seqs, max_blocks = block_tables.shape
+        cabi.check(self.lib.kb_prefill(self._h, tokens.data_ptr(), cu_seqlens.data_ptr(), ctx_lens.data_ptr(),
+                                       block_tables.data_ptr(), n_seqs, tokens.numel(), max_blocks, int(max_new),
+                                       C.byref(sampling) if sampling is not None else None,
+                                       None if logits_out is None else logits_out.data_ptr(),
+                                       None if out_tokens is None else out_tokens.data_ptr(),
+                                       torch.cuda.current_stream().cuda_stream), "kb_prefill")
+
+    def decode(self, last_tokens: torch.Tensor, ctx_lens: torch.Tensor, block_tables: torch.Tensor,
+               sampling: cabi.Sampling, out_tokens: torch.Tensor, max_ctx: int = 0,
+               logits_out: Optional[torch.Tensor] = None, advance_ctx: bool = False) -> None:
+        batch, max_blocks = block_tables.shape
+        cabi.check(self.lib.kb_decode(self._h, last_tokens.data_ptr(), ctx_lens.data_ptr(),
+                                      block_tables.data_ptr(), batch, max_blocks, int(max_ctx), C.byref(sampling),
+                                      out_tokens.data_ptr(),
+                                      None if logits_out is None else logits_out.data_ptr(),
+                                      1 if advance_ctx else 0, torch.cuda.current_stream().cuda_stream),
+                   "kb_decode")

@@ -1,0 +1,133 @@
+"""Seeded random-init Llama weights shared by the B200 provider and the CPU oracle.
+
+There are no checkpoints offline, so both sides build the *same* bf16-representable tensors from a
+seed: every tensor is drawn from its own ``torch.Generator`` (seed mixed with the tensor name),
+rounded to bf16, and handed out either as bf16 (GPU) or widened to fp32 (oracle) — identical values.
+
+Two initialisations:
+
+``iid``     N(0, 0.02) projections, N(0, 1) embedding, independent lm_head. With independent
+            Gaussian logits the top-2 gap is ~ sigma / sqrt(2 ln V), so a bf16 engine and an fp32
+            oracle flip greedy near-ties at a percent-level rate per step no matter how exact the
+            kernels are. Used for logit-tolerance tests and benchmarks.
+``margin``  same, except lm_head rows of the *generable* ids are a seeded permutation of embedding
+            rows (scaled so the other logits have sigma ~ 1): the last token's own embedding
+            dominates the residual stream, so the arg-max has a margin of ~10 sigma and greedy
+            decoding is reproducible across precisions, while every other logit still depends on
+            the full attention/MLP arithmetic (and is what the 2e-2 logit tolerance checks).
+            Used for the greedy-agreement parity configuration (BASELINE config 2).
+
+Reference counterpart: none (the reference's models are remote, /root/reference/src/llm/portkey.py:379).
+"""
+from __future__ import annotations
+
+import hashlib
+from typing import Dict, Optional, Sequence
+
+import torch
+
+from .model_config import LlamaConfig
+
+
+def _seed_for(seed: int, name: str) -> int:
+    h = hashlib.blake2b(f"{seed}:{name}".encode(), digest_size=8).digest()
+    return int.from_bytes(h, "little") & 0x7FFFFFFFFFFFFFFF
+
+
+def _randn(shape, seed: int, name: str, std: float, device: str, mean: float = 0.0) -> torch.Tensor:
+    g = torch.Generator(device=device)
+    g.manual_seed(_seed_for(seed, name))
+    t = torch.randn(shape, generator=g, device=device, dtype=torch.float32)
+    t = t.mul_(std).add_(mean)
+    return t.to(torch.bfloat16)
+
+
+def generable_ids(cfg: LlamaConfig) -> torch.Tensor:
+    """Token ids the sampler may emit by default: printable ASCII, newline, and <|eot_id|>."""
+    ids = list(range(32, 127)) + [10, cfg.vocab - 1]
+    return torch.tensor(ids, dtype=torch.long)
+
+
+def generate_weights(cfg: LlamaConfig, seed: int = 0, device: str = "cpu", init: str = "iid",
+                     layers: Optional[Sequence[int]] = None) -> Dict[str, torch.Tensor]:
+    """Canonical (unfused) bf16 tensors, HF naming in spirit:
+
+    embed [V,H]; per layer i: l{i}.attn_norm [H], l{i}.wq [Hq,H], l{i}.wk [Hkv,H], l{i}.wv [Hkv,H],
+    l{i}.wo [H,Hq], l{i}.mlp_norm [H], l{i}.w_gate [F,H], l{i}.w_up [F,H], l{i}.w_down [H,F];
+    final_norm [H]; lm_head [V,H].
+
+    ``device='cpu'`` is the canonical stream (what parity tests use on both sides). A CUDA device
+    gives a different but equally distributed stream and is only meant for benchmarks of the large
+    shapes, where no oracle comparison is made.
+    """
+    if init not in ("iid", "margin"):
+        raise ValueError(f"unknown init {init!r}")
+    H, F = cfg.hidden, cfg.ffn
+    w: Dict[str, torch.Tensor] = {}
+    w["embed"] = _randn((cfg.vocab, H), seed, "embed", 1.0, device)
+    for i in (range(cfg.n_layers) if layers is None else layers):
+        p = f"l{i}."
+        w[p + "attn_norm"] = _randn((H,), seed, p + "attn_norm", 0.1, device, mean=1.0)
+        w[p + "wq"] = _randn((cfg.q_dim, H), seed, p + "wq", 0.02, device)
+        w[p + "wk"] = _randn((cfg.kv_dim, H), seed, p + "wk", 0.02, device)
+        w[p + "wv"] = _randn((cfg.kv_dim, H), seed, p + "wv", 0.02, device)
+        w[p + "wo"] = _randn((H, cfg.q_dim), seed, p + "wo", 0.02, device)
+        w[p + "mlp_norm"] = _randn((H,), seed, p + "mlp_norm", 0.1, device, mean=1.0)
+        w[p + "w_gate"] = _randn((F, H), seed, p + "w_gate", 0.02, device)
+        w[p + "w_up"] = _randn((F, H), seed, p + "w_up", 0.02, device)
+        w[p + "w_down"] = _randn((H, F), seed, p + "w_down", 0.02, device)
+    w["final_norm"] = _randn((H,), seed, "final_norm", 0.1, device, mean=1.0)
+    # sigma(logit) ~ |row| = std * sqrt(H); keep it ~1 so the 2e-2 absolute tolerance is meaningful
+    lm_std = 1.0 / (H ** 0.5)
+    w["lm_head"] = _randn((cfg.vocab, H), seed, "lm_head", lm_std, device)
+    if init == "margin":
+        ids = generable_ids(cfg).to(device)
+        g = torch.Generator(device="cpu")
+        g.manual_seed(_seed_for(seed, "margin_perm"))
+        perm = torch.randperm(ids.numel(), generator=g).to(device)
+        # next(ids[k]) = ids[perm[k]]: the row of the *next* token holds the embedding of the current one
+        rows = w["embed"][ids].float() * lm_std
+        lm = w["lm_head"].float()
+        lm[ids[perm]] = rows
+        w["lm_head"] = lm.to(torch.bfloat16)
+    return w
+
+
+def fuse_for_engine(cfg: LlamaConfig, w: Dict[str, torch.Tensor], device) -> Dict[str, torch.Tensor]:
+    """Lay the canonical tensors out the way include/kafka_b200.h wants them (bf16, contiguous):
+
+    l{i}.wqkv = cat(wq, wk, wv) rows;  l{i}.w_gate_up = rows interleaved (2j = gate_j, 2j+1 = up_j).
+    """
+    out: Dict[str, torch.Tensor] = {}
+    for k in ("embed", "final_norm", "lm_head"):
+        out[k] = w[k].to(device=device, dtype=torch.bfloat16).contiguous()
+    for i in range(cfg.n_layers):
+        p = f"l{i}."
+        out[p + "attn_norm"] = w[p + "attn_norm"].to(device).contiguous()
+        out[p + "mlp_norm"] = w[p + "mlp_norm"].to(device).contiguous()
+        out[p + "wqkv"] = torch.cat([w[p + "wq"], w[p + "wk"], w[p + "wv"]], dim=0).to(device).contiguous()
+        out[p + "wo"] = w[p + "wo"].to(device).contiguous()
+        gu = torch.stack([w[p + "w_gate"], w[p + "w_up"]], dim=1).reshape(2 * cfg.ffn, cfg.hidden)
+        out[p + "w_gate_up"] = gu.to(device).contiguous()
+        out[p + "w_down"] = w[p + "w_down"].to(device).contiguous()
+    return out
+
+
+def generate_fused_on_device(cfg: LlamaConfig, seed: int, device) -> Dict[str, torch.Tensor]:
+    """Benchmark path for the large shapes: draw the fused tensors directly on the GPU, layer by
+    layer, so that no 16-140 GB host copy is ever made. Distribution as in ``iid``."""
+    dev = str(device)
+    out: Dict[str, torch.Tensor] = {}
+    H, F = cfg.hidden, cfg.ffn
+    out["embed"] = _randn((cfg.vocab, H), seed, "embed", 1.0, dev)
+    out["final_norm"] = _randn((H,), seed, "final_norm", 0.1, dev, mean=1.0)
+    out["lm_head"] = _randn((cfg.vocab, H), seed, "lm_head", 1.0 / (H ** 0.5), dev)
+    for i in range(cfg.n_layers):
+        p = f"l{i}."
+        out[p + "attn_norm"] = _randn((H,), seed, p + "attn_norm", 0.1, dev, mean=1.0)
+        out[p + "mlp_norm"] = _randn((H,), seed, p + "mlp_norm", 0.1, dev, mean=1.0)
+        out[p + "wqkv"] = _randn((cfg.qkv_dim, H), seed, p + "wqkv", 0.02, dev)
+        out[p + "wo"] = _randn((H, cfg.q_dim), seed, p + "wo", 0.02, dev)
+        out[p + "w_gate_up"] = _randn((2 * F, H), seed, p + "w_gate_up", 0.02, dev)
+        out[p + "w_down"] = _randn((H, F), seed, p + "w_down", 0.02, dev)
+    return out

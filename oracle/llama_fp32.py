@@ -1,0 +1,139 @@
+"""ORACLE — fp32 CPU eager forward of the Llama architecture.  TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference``
+legs may import this module; the product (``kafka-llm-service_b200/``) never does, and fails loudly
+when its CUDA library is missing instead of falling back to anything here.
+
+PARITY UNPINNED.  The reference (egrigokhan/kafka-llm-service) holds no arithmetic for this path: its
+only provider forwards the conversation to a remote gateway
+(/root/reference/src/llm/portkey.py:379 and :616) and it ships no tests, golden vectors or fixtures
+for completions.  BASELINE.json's north_star therefore *defines* the oracle as an
+fp32 PyTorch CPU eager forward of the same random-init architecture; this file is that restatement of
+the published Llama algorithm (RMSNorm -> GQA attention with rotate-half RoPE -> SwiGLU MLP).  What
+pins it instead: ``tests/test_oracle.py`` checks it against ``transformers.LlamaForCausalLM`` (an
+independent implementation present in the image) on random-init weights, and the generating script
+``tests/golden/make_golden.py`` freezes its outputs as fixtures.
+
+Shapes follow kafka_b200.model_config.LlamaConfig; weights follow kafka_b200.weights.generate_weights
+(canonical, unfused names).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+
+def rmsnorm(x: torch.Tensor, w: torch.Tensor, eps: float) -> torch.Tensor:
+    var = x.pow(2).mean(-1, keepdim=True)
+    return x * torch.rsqrt(var + eps) * w
+
+
+def rope_cos_sin(positions: torch.Tensor, head_dim: int, theta: float):
+    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32) / head_dim))
+    freqs = positions.to(torch.float32)[:, None] * inv_freq[None, :]
+    return freqs.cos(), freqs.sin()  # [T, hd/2]
+
+
+def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
+    """x: [T, n_heads, hd]; HF rotate-half convention (pairs i, i + hd/2)."""
+    half = x.shape[-1] // 2
+    x1, x2 = x[..., :half], x[..., half:]
+    c, s = cos[:, None, :], sin[:, None, :]
+    return torch.cat([x1 * c - x2 * s, x2 * c + x1 * s], dim=-1)
+
+
+class KVCache:
+    """Contiguous per-sequence cache: k[layer], v[layer] of shape [len, n_kv_heads, head_dim] (fp32)."""
+
+    def __init__(self, n_layers: int):
+        self.k: List[Optional[torch.Tensor]] = [None] * n_layers
+        self.v: List[Optional[torch.Tensor]] = [None] * n_layers
+
+    @property
+    def length(self) -> int:
+        return 0 if self.k[0] is None else self.k[0].shape[0]
+
+    def truncate(self, n: int) -> None:
+        for i in range(len(self.k)):
+            if self.k[i] is not None:
+                self.k[i] = self.k[i][:n]
+                self.v[i] = self.v[i][:n]
+
+
+class OracleLlama:
+    """fp32 forward. ``weights`` are the canonical bf16-representable tensors, widened to fp32."""
+
+    def __init__(self, cfg, weights: Dict[str, torch.Tensor]):
+        self.cfg = cfg
+        self.w = {k: v.detach().to("cpu", torch.float32) for k, v in weights.items()}
+
+    def new_cache(self) -> KVCache:
+        return KVCache(self.cfg.n_layers)
+
+    @torch.no_grad()
+    def forward(self, tokens: torch.Tensor, cache: KVCache, all_logits: bool = False,
+                taps: Optional[Dict[str, torch.Tensor]] = None) -> torch.Tensor:
+        """Append ``tokens`` [T] to ``cache`` and return logits of the last position [V]
+        (or of every new position [T, V] when all_logits)."""
+        cfg, w = self.cfg, self.w
+        T = tokens.numel()
+        past = cache.length
+        pos = torch.arange(past, past + T)
+        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta)
+        x = w["embed"][tokens.long()]
+        scale = cfg.head_dim ** -0.5
+        for i in range(cfg.n_layers):
+            p = f"l{i}."
+            h = rmsnorm(x, w[p + "attn_norm"], cfg.rms_eps)
+            q = (h @ w[p + "wq"].T).view(T, cfg.n_heads, cfg.head_dim)
+            k = (h @ w[p + "wk"].T).view(T, cfg.n_kv_heads, cfg.head_dim)
+            v = (h @ w[p + "wv"].T).view(T, cfg.n_kv_heads, cfg.head_dim)
+            q = apply_rope(q, cos, sin)
+            k = apply_rope(k, cos, sin)
+            cache.k[i] = k if cache.k[i] is None else torch.cat([cache.k[i], k], 0)
+            cache.v[i] = v if cache.v[i] is None else torch.cat([cache.v[i], v], 0)
+            K = cache.k[i].repeat_interleave(cfg.group, dim=1)  # [L, n_heads, hd]
+            V = cache.v[i].repeat_interleave(cfg.group, dim=1)
+            s = torch.einsum("thd,lhd->htl", q, K) * scale      # [n_heads, T, L]
+            L = K.shape[0]
+            causal = torch.arange(L)[None, :] > (past + torch.arange(T))[:, None]
+            s = s.masked_fill(causal[None], float("-inf"))
+            a = torch.softmax(s, dim=-1)
+            o = torch.einsum("htl,lhd->thd", a, V).reshape(T, cfg.q_dim)
+            if taps is not None and i == 0:
+                taps["q0"], taps["attn0"] = q.clone(), o.clone()
+            x = x + o @ w[p + "wo"].T
+            h = rmsnorm(x, w[p + "mlp_norm"], cfg.rms_eps)
+            g = h @ w[p + "w_gate"].T
+            u = h @ w[p + "w_up"].T
+            x = x + (torch.nn.functional.silu(g) * u) @ w[p + "w_down"].T
+        xl = x if all_logits else x[-1:]
+        logits = rmsnorm(xl, w["final_norm"], cfg.rms_eps) @ w["lm_head"].T
+        return logits if all_logits else logits[0]
+
+    @torch.no_grad()
+    def greedy(self, prompt: torch.Tensor, n_new: int, cache: Optional[KVCache] = None,
+               allowed: Optional[torch.Tensor] = None, eos: Optional[int] = None):
+        """Greedy decode; returns (tokens, logits per step [n, V]). Ties -> lowest id (like kb_sample)."""
+        cache = cache or self.new_cache()
+        toks: List[int] = []
+        lgs: List[torch.Tensor] = []
+        cur = prompt
+        for _ in range(n_new):
+            lg = self.forward(cur, cache)
+            lgs.append(lg)
+            t = masked_argmax(lg, allowed)
+            toks.append(t)
+            if eos is not None and t == eos:
+                break
+            cur = torch.tensor([t])
+        return toks, torch.stack(lgs)
+
+
+def masked_argmax(logits: torch.Tensor, allowed: Optional[torch.Tensor]) -> int:
+    if allowed is None:
+        return int(torch.argmax(logits))
+    sub = logits[allowed]
+    best = sub.max()
+    return int(allowed[sub == best].min())

@@ -1,0 +1,329 @@
+"""Per-kernel parity on the B200: every CUDA kernel, called through the C ABI, against a plain fp32
+PyTorch statement of the same op on the same seeded inputs.
+
+Tolerances (written where used): outputs that are rounded to bf16 are compared with rtol = atol = 2e-2
+of the fp32 result (bf16 has 8 mantissa bits, 2^-8 = 3.9e-3 per rounding, a few roundings per op);
+fp32 outputs of bf16-input GEMMs with rtol = atol = 2e-3.
+"""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def kb():
+    from kafka_b200 import cabi
+    cabi.load()
+    return cabi
+
+
+def _bf16(t):
+    return t.to(torch.bfloat16)
+
+
+# ------------------------------------------------------------------------------------------------
+def test_embed(kb, cuda):
+    g = torch.Generator(device="cpu").manual_seed(0)
+    table = _bf16(torch.randn(300, 256, generator=g)).to(cuda)
+    toks = torch.randint(0, 300, (37,), generator=g, dtype=torch.int32).to(cuda)
+    x = kb.embed(toks, table)
+    torch.cuda.synchronize()
+    assert torch.equal(x, table[toks.long()].float())  # exact: a gather + widening
+
+
+@pytest.mark.parametrize("n,hidden", [(1, 256), (5, 2048), (33, 4096), (7, 8192)])
+def test_rmsnorm(kb, cuda, n, hidden):
+    g = torch.Generator(device="cpu").manual_seed(n * 1000 + hidden)
+    x = (torch.randn(n, hidden, generator=g) * 3).to(cuda)
+    w = _bf16(1 + 0.1 * torch.randn(hidden, generator=g)).to(cuda)
+    y = kb.rmsnorm(x, w, 1e-5)
+    ref = x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-5) * w.float()
+    torch.testing.assert_close(y.float(), ref, rtol=2e-2, atol=2e-2)
+
+
+# ------------------------------------------------------------------------------------------------
+GEMM_SHAPES = [
+    # M, N, K
+    (128, 256, 64),
+    (128, 128, 128),
+    (1, 512, 256),
+    (17, 136, 192),      # partial M and N tiles
+    (300, 1000, 320),    # partial everything, N % 8 == 0
+    (512, 4096, 4096),   # decode-step O projection
+    (512, 6144, 4096),   # decode-step QKV
+    (64, 512, 14336),    # long K
+    (1000, 768, 512),    # many M tiles
+]
+
+
+@pytest.mark.parametrize("tile_n", [0, 64, 128, 256])
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_bf16(kb, cuda, M, N, K, tile_n):
+    g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
+    a = _bf16(torch.randn(M, K, generator=g)).to(cuda)
+    w = _bf16(torch.randn(N, K, generator=g) / math.sqrt(K)).to(cuda)
+    out = kb.gemm(a, w, kb.EPI_BF16, tile_n=tile_n)
+    ref = a.float() @ w.float().T
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("tile_n", [64, 128, 256])
+@pytest.mark.parametrize("M,N,K", [(17, 136, 192), (300, 1000, 320), (512, 4096, 1024)])
+def test_gemm_f32_and_residual(kb, cuda, M, N, K, tile_n):
+    g = torch.Generator(device="cpu").manual_seed(M + N + K)
+    a = _bf16(torch.randn(M, K, generator=g)).to(cuda)
+    w = _bf16(torch.randn(N, K, generator=g) / math.sqrt(K)).to(cuda)
+    ref = a.float() @ w.float().T
+    out = kb.gemm(a, w, kb.EPI_F32, tile_n=tile_n)
+    torch.testing.assert_close(out, ref, rtol=2e-3, atol=2e-3)
+    resid = torch.randn(M, N, generator=g).to(cuda)
+    want = resid + ref
+    out2 = kb.gemm(a, w, kb.EPI_RESID_F32, resid=resid, tile_n=tile_n)
+    torch.testing.assert_close(out2, want, rtol=2e-3, atol=2e-3)
+    # in place: out aliases resid (how the engine uses it)
+    r2 = resid.clone()
+    kb.gemm(a, w, kb.EPI_RESID_F32, resid=r2, out=r2, tile_n=tile_n)
+    torch.testing.assert_close(r2, want, rtol=2e-3, atol=2e-3)
+
+
+@pytest.mark.parametrize("tile_n", [64, 128, 256])
+@pytest.mark.parametrize("M,F,K", [(17, 80, 192), (300, 512, 256), (512, 1408, 1024)])
+def test_gemm_swiglu(kb, cuda, M, F, K, tile_n):
+    g = torch.Generator(device="cpu").manual_seed(M + F + K)
+    a = _bf16(torch.randn(M, K, generator=g)).to(cuda)
+    wg = _bf16(torch.randn(F, K, generator=g) / math.sqrt(K)).to(cuda)
+    wu = _bf16(torch.randn(F, K, generator=g) / math.sqrt(K)).to(cuda)
+    w = torch.stack([wg, wu], dim=1).reshape(2 * F, K).contiguous()
+    out = kb.gemm(a, w, kb.EPI_SWIGLU_BF16, tile_n=tile_n)
+    ref = torch.nn.functional.silu(a.float() @ wg.float().T) * (a.float() @ wu.float().T)
+    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
+
+
+def test_gemm_rejects_bad_shapes(kb, cuda):
+    a = torch.zeros(4, 100, dtype=torch.bfloat16, device=cuda)
+    w = torch.zeros(8, 100, dtype=torch.bfloat16, device=cuda)
+    with pytest.raises(kb.KafkaB200Error, match="multiple of 64"):
+        kb.gemm(a, w)
+
+
+# ------------------------------------------------------------------------------------------------
+def _rope_ref(x, pos, theta):
+    """x [T, H, hd] fp32, HF rotate-half."""
+    hd = x.shape[-1]
+    inv = 1.0 / (theta ** (torch.arange(0, hd, 2, dtype=torch.float32, device=x.device) / hd))
+    f = pos.float()[:, None] * inv[None]
+    c, s = f.cos()[:, None, :], f.sin()[:, None, :]
+    x1, x2 = x[..., : hd // 2], x[..., hd // 2:]
+    return torch.cat([x1 * c - x2 * s, x2 * c + x1 * s], -1)
+
+
+def _alloc_pool(n_blocks, n_kv, hd, device, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    k = _bf16(torch.randn(n_blocks, n_kv, 64 * hd, generator=g)).to(device)
+    v = _bf16(torch.randn(n_blocks, n_kv, 64 * hd, generator=g)).to(device)
+    return k, v
+
+
+@pytest.mark.parametrize("hd,n_heads,n_kv,theta", [(64, 4, 2, 10000.0), (128, 8, 2, 500000.0)])
+def test_rope_append(kb, cuda, hd, n_heads, n_kv, theta):
+    from kafka_b200 import kv_layout
+    g = torch.Generator(device="cpu").manual_seed(hd)
+    new = [5, 70, 1]          # new tokens per sequence
+    ctx = [0, 60, 130]        # cached tokens per sequence (second one crosses a block boundary)
+    n_seqs, T = len(new), sum(new)
+    max_blocks = 4
+    # distinct, shuffled physical blocks
+    perm = torch.randperm(n_seqs * max_blocks, generator=g).view(n_seqs, max_blocks).int()
+    kp, vp = _alloc_pool(n_seqs * max_blocks, n_kv, hd, cuda, 1)
+    kp0, vp0 = kp.clone(), vp.clone()
+    qkv = _bf16(torch.randn(T, (n_heads + 2 * n_kv) * hd, generator=g)).to(cuda)
+    qkv0 = qkv.clone()
+    cu = torch.tensor([0] + list(torch.tensor(new).cumsum(0)), dtype=torch.int32, device=cuda)
+    ctx_t = torch.tensor(ctx, dtype=torch.int32, device=cuda)
+    bt = perm.to(cuda)
+    kb.rope_append(qkv, cu, ctx_t, bt, kp, vp, n_heads, n_kv, hd, theta)
+    torch.cuda.synchronize()
+
+    pos = torch.cat([torch.arange(c, c + n) for c, n in zip(ctx, new)]).to(cuda)
+    q0 = qkv0[:, : n_heads * hd].float().view(T, n_heads, hd)
+    k0 = qkv0[:, n_heads * hd: (n_heads + n_kv) * hd].float().view(T, n_kv, hd)
+    v0 = qkv0[:, (n_heads + n_kv) * hd:].view(T, n_kv, hd)
+    q_ref = _rope_ref(q0, pos, theta)
+    k_ref = _rope_ref(k0, pos, theta)
+    # tolerance: one bf16 rounding of an O(1) value plus fp32 sin/cos of angles up to ~200 rad
+    torch.testing.assert_close(qkv[:, : n_heads * hd].float().view(T, n_heads, hd), q_ref, rtol=2e-2, atol=2e-2)
+    # v columns of qkv untouched
+    assert torch.equal(qkv[:, (n_heads + n_kv) * hd:], qkv0[:, (n_heads + n_kv) * hd:])
+    off = 0
+    touched_k = torch.zeros_like(kp, dtype=torch.bool)
+    for s in range(n_seqs):
+        L = ctx[s] + new[s]
+        k_all = kv_layout.read_tokens(kp, perm[s].tolist(), L, hd)
+        v_all = kv_layout.read_tokens(vp, perm[s].tolist(), L, hd)
+        torch.testing.assert_close(k_all[ctx[s]:].float(), k_ref[off: off + new[s]], rtol=2e-2, atol=2e-2)
+        assert torch.equal(v_all[ctx[s]:], v0[off: off + new[s]])  # V is a pure copy
+        # cached prefix untouched
+        k_before = kv_layout.read_tokens(kp0, perm[s].tolist(), L, hd)
+        assert torch.equal(k_all[: ctx[s]], k_before[: ctx[s]])
+        off += new[s]
+    # nothing outside the appended rows changed: count of changed elements == appended elements
+    changed = (kp != kp0).sum().item()
+    assert changed <= T * n_kv * hd
+    del touched_k
+
+
+# ------------------------------------------------------------------------------------------------
+def _attn_ref(q, K, V, n_heads, n_kv, q_pos):
+    """q [Tq, n_heads, hd], K/V [L, n_kv, hd] fp32; query i sees keys 0..q_pos[i]."""
+    hd = q.shape[-1]
+    grp = n_heads // n_kv
+    Kh = K.repeat_interleave(grp, dim=1)
+    Vh = V.repeat_interleave(grp, dim=1)
+    s = torch.einsum("thd,lhd->htl", q, Kh) / math.sqrt(hd)
+    L = K.shape[0]
+    mask = torch.arange(L, device=q.device)[None, :] > q_pos[:, None]
+    s = s.masked_fill(mask[None], float("-inf"))
+    return torch.einsum("htl,lhd->thd", torch.softmax(s, -1), Vh)
+
+
+DECODE_CASES = [
+    # hd, n_heads, n_kv, kv_lens
+    (128, 8, 2, [1, 31, 32, 33, 64, 65, 200]),
+    (128, 4, 4, [7, 130]),            # group 1
+    (128, 16, 2, [2112, 17, 1000]),   # group 8, long
+    (64, 8, 2, [1, 63, 64, 65, 500]),
+    (64, 32, 4, [300, 2049]),         # TinyLlama grouping (8)
+    (64, 4, 2, [90]),                 # group 2
+]
+
+
+@pytest.mark.parametrize("use_scratch", [False, True])
+@pytest.mark.parametrize("hd,n_heads,n_kv,kv_lens", DECODE_CASES)
+def test_attn_decode(kb, cuda, hd, n_heads, n_kv, kv_lens, use_scratch):
+    from kafka_b200 import kv_layout
+    g = torch.Generator(device="cpu").manual_seed(sum(kv_lens) + hd)
+    B = len(kv_lens)
+    max_blocks = (max(kv_lens) + 63) // 64 + 1
+    n_blocks = B * max_blocks
+    perm = torch.randperm(n_blocks, generator=g).view(B, max_blocks).int()
+    kp = torch.zeros(n_blocks, n_kv, 64 * hd, dtype=torch.bfloat16, device=cuda)
+    vp = torch.zeros_like(kp)
+    Ks, Vs = [], []
+    for s, L in enumerate(kv_lens):
+        K = _bf16(torch.randn(L, n_kv, hd, generator=g)).to(cuda)
+        V = _bf16(torch.randn(L, n_kv, hd, generator=g)).to(cuda)
+        kv_layout.write_tokens(kp, perm[s].tolist(), 0, K)
+        kv_layout.write_tokens(vp, perm[s].tolist(), 0, V)
+        Ks.append(K.float())
+        Vs.append(V.float())
+    # q lives inside a wider row (as in the fused qkv buffer)
+    qkv = _bf16(torch.randn(B, (n_heads + 2 * n_kv) * hd, generator=g)).to(cuda)
+    lens = torch.tensor(kv_lens, dtype=torch.int32, device=cuda)
+    scratch = None
+    if use_scratch:
+        scratch = torch.empty(kb.attn_decode_scratch_bytes(B, n_heads, hd), dtype=torch.uint8, device=cuda)
+    out = kb.attn_decode(qkv, kp, vp, lens, perm.to(cuda), n_heads, n_kv, hd, kv_len_bias=0,
+                         max_kv_len=max(kv_lens), scratch=scratch)
+    torch.cuda.synchronize()
+    for s, L in enumerate(kv_lens):
+        q = qkv[s, : n_heads * hd].float().view(1, n_heads, hd)
+        ref = _attn_ref(q, Ks[s], Vs[s], n_heads, n_kv, torch.tensor([L - 1], device=cuda))
+        # P and the output are rounded to bf16: 2e-2
+        torch.testing.assert_close(out[s].float().view(1, n_heads, hd), ref, rtol=2e-2, atol=2e-2)
+
+
+def test_attn_decode_bias_matches_explicit_length(kb, cuda):
+    """kv_len_bias=1 over ctx_lens must equal kv_lens = ctx_lens + 1 (how the engine calls it)."""
+    from kafka_b200 import kv_layout
+    g = torch.Generator(device="cpu").manual_seed(3)
+    hd, n_heads, n_kv = 128, 8, 2
+    lens = [40, 129]
+    perm = torch.arange(8).view(2, 4).int()
+    kp, vp = _alloc_pool(8, n_kv, hd, cuda, 5)
+    q = _bf16(torch.randn(2, n_heads * hd, generator=g)).to(cuda)
+    a = kb.attn_decode(q, kp, vp, torch.tensor(lens, dtype=torch.int32, device=cuda), perm.to(cuda), n_heads, n_kv, hd)
+    b = kb.attn_decode(q, kp, vp, torch.tensor([l - 1 for l in lens], dtype=torch.int32, device=cuda), perm.to(cuda),
+                       n_heads, n_kv, hd, kv_len_bias=1)
+    assert torch.equal(a, b)
+    del kv_layout
+
+
+PREFILL_CASES = [
+    # hd, n_heads, n_kv, [(ctx, new), ...]
+    (128, 8, 2, [(0, 5), (100, 64), (60, 9)]),
+    (128, 8, 2, [(2048, 64)]),
+    (128, 4, 4, [(0, 130)]),            # group 1: 64 query tokens per CTA
+    (64, 32, 4, [(0, 77), (500, 3)]),   # group 8
+    (64, 4, 2, [(63, 2), (0, 1)]),
+    (128, 16, 2, [(10, 200)]),
+]
+
+
+@pytest.mark.parametrize("hd,n_heads,n_kv,seqs", PREFILL_CASES)
+def test_attn_prefill(kb, cuda, hd, n_heads, n_kv, seqs):
+    from kafka_b200 import kv_layout
+    g = torch.Generator(device="cpu").manual_seed(hd + len(seqs) + seqs[0][1])
+    B = len(seqs)
+    max_blocks = max((c + n + 63) // 64 for c, n in seqs) + 1
+    n_blocks = B * max_blocks
+    perm = torch.randperm(n_blocks, generator=g).view(B, max_blocks).int()
+    kp = torch.zeros(n_blocks, n_kv, 64 * hd, dtype=torch.bfloat16, device=cuda)
+    vp = torch.zeros_like(kp)
+    T = sum(n for _, n in seqs)
+    qkv = _bf16(torch.randn(T, (n_heads + 2 * n_kv) * hd, generator=g)).to(cuda)
+    refs = []
+    off = 0
+    for s, (c, n) in enumerate(seqs):
+        K = _bf16(torch.randn(c + n, n_kv, hd, generator=g)).to(cuda)
+        V = _bf16(torch.randn(c + n, n_kv, hd, generator=g)).to(cuda)
+        kv_layout.write_tokens(kp, perm[s].tolist(), 0, K)
+        kv_layout.write_tokens(vp, perm[s].tolist(), 0, V)
+        q = qkv[off: off + n, : n_heads * hd].float().view(n, n_heads, hd)
+        refs.append(_attn_ref(q, K.float(), V.float(), n_heads, n_kv, torch.arange(c, c + n, device=cuda)))
+        off += n
+    cu = torch.tensor([0] + list(torch.tensor([n for _, n in seqs]).cumsum(0)), dtype=torch.int32, device=cuda)
+    ctx = torch.tensor([c for c, _ in seqs], dtype=torch.int32, device=cuda)
+    out = kb.attn_prefill(qkv, kp, vp, cu, ctx, perm.to(cuda), max(n for _, n in seqs), n_heads, n_kv, hd)
+    torch.cuda.synchronize()
+    ref = torch.cat(refs, 0)
+    torch.testing.assert_close(out.float().view(T, n_heads, hd), ref, rtol=2e-2, atol=2e-2)
+
+
+# ------------------------------------------------------------------------------------------------
+def test_sample_greedy_and_masks(kb, cuda):
+    g = torch.Generator(device="cpu").manual_seed(11)
+    logits = torch.randn(9, 32000, generator=g).to(cuda)
+    logits[3, 100] = logits[3, 7] = 50.0  # tie -> lowest id
+    out = kb.sample(logits)
+    ref = torch.argmax(logits, -1).int()
+    ref[3] = 7
+    assert torch.equal(out, ref)
+    # banned token
+    out_b = kb.sample(logits, banned_token=int(ref[0]))
+    l0 = logits[0].clone()
+    l0[int(ref[0])] = float("-inf")
+    assert int(out_b[0]) == int(torch.argmax(l0))
+    # allowed range + extras
+    out_r = kb.sample(logits, allowed_lo=32, allowed_hi=127, extra_a=10, extra_b=31999)
+    allowed = torch.tensor(list(range(32, 127)) + [10, 31999], device=cuda)
+    want = allowed[torch.argmax(logits[:, allowed], -1)].int()
+    assert torch.equal(out_r, want)
+
+
+def test_sample_temperature_distribution(kb, cuda):
+    """Gumbel-max sampling: deterministic per (seed, step), and frequencies follow softmax(logits / T)."""
+    probs = torch.tensor([0.5, 0.25, 0.125, 0.125])
+    T = 0.7
+    logits = (probs.log() * T).repeat(4096, 1).to(cuda).contiguous()  # softmax(logits / T) == probs
+    # vocab must be a multiple of 8 for the engine, not for kb_sample itself
+    a = kb.sample(logits, temperature=T, seed=1, step=5)
+    b = kb.sample(logits, temperature=T, seed=1, step=5)
+    c = kb.sample(logits, temperature=T, seed=1, step=6)
+    assert torch.equal(a, b)
+    assert not torch.equal(a, c)
+    freq = torch.bincount(a.long(), minlength=4).float().cpu() / 4096
+    # 4096 draws: std of a frequency <= sqrt(.25/4096) = 0.0078; allow 5 sigma
+    assert torch.all((freq - probs).abs() < 0.04), freq
