@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""bench.py — decode tokens/s of the B200 completion path (BASELINE.json metric).
+
+Workload (BASELINE.json configs[2], thread-sharded): Llama-3-8B bf16, per GPU `--threads` concurrent
+synthetic threads (default 512 = 4096 / 8, the share one GPU owns at 8 GPUs and the most that is
+resident in 180 GB), each with a 2 048-token history resident in paged KV, a 64-token user message
+prefilled incrementally, then greedy decode.  A *step* is one decode step over all threads of the
+rank (B tokens).  Weak scaling: per-GPU work is fixed, ranks share nothing (no collective on the
+data path), value = N * B * K / max-over-ranks time.
+
+Legs (all on the same resident state, CUDA-event timed on the launching stream):
+  value      device-resident decode loop (token feedback on the device)
+  roofline   the same loop with CUDA events between kernels -> per-kernel time; the dominant kernel
+             (paged attention decode) reported as achieved HBM GB/s against MEASURED_PEAKS.json
+  e2e        the same step driven through the C ABI with HOST buffers: pinned H2D of the step's
+             input tokens and D2H of the sampled tokens inside the timed region
+  cpu_baseline (rank 0, N=1 only)  the fp32 oracle on the host cores on a bounded sample
+`--impl reference` times the reference arm: the CPU oracle port of the path (the reference's own
+implementation is a remote service, unavailable offline — BASELINE.md §1).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT / "kafka-llm-service_b200"))
+sys.path.insert(0, str(ROOT))
+
+import torch  # noqa: E402
+
+METRIC = "decode tokens/s (whole box)"
+UNIT = "tokens/s"
+
+
+# ------------------------------------------------------------------------------------------------
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="llama-3-8b")
+    ap.add_argument("--threads", type=int, default=512, help="concurrent threads per GPU")
+    ap.add_argument("--history", type=int, default=2048)
+    ap.add_argument("--user-tokens", type=int, default=64)
+    ap.add_argument("--cpu-threads", type=int, default=8, help="threads in the CPU sample")
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-profile", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return float(d["hbm_gbs"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+    return 6650.0, 1590.0, "fallback"  # B200_PROFILING.md fallback
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.rows = []
+        self.proc = None
+        try:
+            uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+            sel = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+        except Exception:
+            sel = str(device_index)
+        self.cmd = ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", sel]
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(self.cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1):
+    """The fp32 oracle (oracle/llama_fp32.py) decoding `n_threads` threads at context `ctx` on the host
+    cores. To stay bounded in time and host memory, ONE layer's fp32 weight tensors (872 MB for
+    Llama-3-8B, far larger than the last-level cache) are shared by all layers and embed/lm_head share
+    one table: same shapes, same FLOPs and DRAM traffic per step, values irrelevant for timing."""
+    from oracle.llama_fp32 import OracleLlama
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    g = torch.Generator().manual_seed(0)
+    H, F = cfg.hidden, cfg.ffn
+
+    def rn(*shape, std=0.02):
+        return torch.empty(*shape).normal_(0, std, generator=g)
+
+    table = rn(cfg.vocab, H, std=1.0 / H ** 0.5)
+    shared = {"attn_norm": torch.ones(H), "mlp_norm": torch.ones(H), "wq": rn(cfg.q_dim, H),
+              "wk": rn(cfg.kv_dim, H), "wv": rn(cfg.kv_dim, H), "wo": rn(H, cfg.q_dim), "w_gate": rn(F, H),
+              "w_up": rn(F, H), "w_down": rn(H, F)}
+    w = {"embed": table, "lm_head": table, "final_norm": torch.ones(H)}
+    for i in range(cfg.n_layers):
+        for k, v in shared.items():
+            w[f"l{i}.{k}"] = v
+    oracle = OracleLlama(cfg, w)
+    caches = []
+    for _ in range(n_threads):
+        c = oracle.new_cache()
+        for i in range(cfg.n_layers):
+            # distinct memory per (thread, layer) so the cache streams from DRAM; values are irrelevant
+            c._k[i] = torch.full((ctx + steps + warmup + 8, cfg.n_kv_heads, cfg.head_dim), 0.01)
+            c._v[i] = torch.full((ctx + steps + warmup + 8, cfg.n_kv_heads, cfg.head_dim), 0.02)
+            c._len[i] = ctx
+        caches.append(c)
+    toks = torch.randint(0, 256, (n_threads,), generator=g)
+    for _ in range(warmup):
+        toks = oracle.decode_batch(toks, caches).argmax(-1)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        toks = oracle.decode_batch(toks, caches).argmax(-1)
+    dt = time.perf_counter() - t0
+    return {"value": n_threads * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{n_threads} threads x {steps} decode steps at context {ctx}, fp32 torch eager oracle, "
+                      f"{cfg.name} shapes, one layer's weights shared by all {cfg.n_layers} layers",
+            "ms_per_step": dt / steps * 1e3}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from kafka_b200.model_config import get_config
+    cfg = get_config(args.model)
+    ctx = args.history + args.user_tokens
+    steps = max(1, min(args.steps, 8))
+    cb = cpu_baseline(cfg, args.cpu_threads, ctx, steps, warmup=max(1, min(args.warmup, 2)))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{cfg.name} decode, {args.cpu_threads} threads x {args.history}-token history "
+                               f"+ {args.user_tokens}-token turn (bounded CPU sample of the {args.threads}-thread "
+                               "workload)", "threads": args.cpu_threads, "context": ctx},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference's own path is a remote gateway call (src/llm/portkey.py:379), not runnable offline; "
+                "this arm is the CPU oracle port run on all host cores",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200(args, rank, world, local_rank):
+    from kafka_b200 import cabi
+    from kafka_b200.cabi import KB_BLOCK_TOKENS
+    from kafka_b200.engine_core import EngineCore
+    from kafka_b200.model_config import get_config
+    from kafka_b200.weights import generate_fused_on_device
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device; there is no CPU fallback")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    cfg = get_config(args.model)
+    K, W = args.steps, max(args.warmup, 3)
+    passes = 1 + (0 if args.no_profile else 1) + (0 if args.no_e2e else 1)
+    tokens_per_thread = args.history + args.user_tokens + W * passes + K * passes + 8
+    bpt = (tokens_per_thread + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
+    B = args.threads
+
+    weights = generate_fused_on_device(cfg, seed=rank, device=dev)
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    free, total = torch.cuda.mem_get_info(dev)
+    block_bytes = EngineCore.kv_block_bytes(cfg)
+    prefill_chunk = 8192
+    ws_guess = 3 * (1 << 30)
+    fit = int((free - ws_guess) // (block_bytes * bpt))
+    resident_note = None
+    if fit < B:
+        resident_note = f"only {fit} of {B} threads fit in {free / 2**30:.0f} GiB free HBM"
+        B = fit
+    eng = EngineCore(cfg, weights, dev, n_blocks=B * bpt, max_tokens=max(prefill_chunk, B), max_seqs=B)
+    # synthetic resident history: random K/V in every block (values do not affect timing)
+    for L in range(cfg.n_layers):
+        eng.k_pool[L].normal_(0, 1)
+        eng.v_pool[L].normal_(0, 1)
+    g = torch.Generator(device="cpu").manual_seed(1234 + rank)
+    block_ids = torch.randperm(B * bpt, generator=g).int().view(B, bpt).to(dev)  # scattered blocks
+    ctx_lens = torch.full((B,), args.history, dtype=torch.int32, device=dev)
+    sp = cabi.make_sampling(temperature=0.0, banned_token=cfg.vocab - 1)  # greedy, EOS masked
+
+    # ---- the turn's incremental prefill (64 new tokens per thread), chunked --------------------
+    U = args.user_tokens
+    user = torch.randint(0, 256, (B, U), generator=g, dtype=torch.int32).to(dev)
+    first = torch.empty(B, dtype=torch.int32, device=dev)
+    per_chunk = max(1, prefill_chunk // U)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = cabi.launch_count()
+    ev0.record()
+    for s0 in range(0, B, per_chunk):
+        s1 = min(B, s0 + per_chunk)
+        n = s1 - s0
+        cu = torch.arange(0, (n + 1) * U, U, dtype=torch.int32, device=dev)
+        eng.prefill(user[s0:s1].reshape(-1), cu, ctx_lens[s0:s1], block_ids[s0:s1], U, sp, None, first[s0:s1])
+    ev1.record()
+    torch.cuda.synchronize()
+    prefill_ms = ev0.elapsed_time(ev1)
+    ctx_lens += U
+    ctx0 = args.history + U
+    prefill_flops = B * (U * 2 * cfg.matmul_params() + 2 * cfg.lm_head_params()
+                         + 4 * cfg.head_dim * cfg.n_heads * cfg.n_layers * (args.history * U + U * U / 2))
+
+    bufs = [first, torch.empty_like(first)]
+    state = {"cur": 0, "ctx": ctx0}
+
+    def decode_steps(n, host_io=False, pinned_in=None, pinned_out=None):
+        for _ in range(n):
+            a, b = bufs[state["cur"]], bufs[state["cur"] ^ 1]
+            if host_io:
+                a.copy_(pinned_in, non_blocking=True)           # H2D of this step's input tokens
+            eng.decode(a, ctx_lens, block_ids, sp, b, max_ctx=state["ctx"], advance_ctx=True)
+            if host_io:
+                pinned_out.copy_(b, non_blocking=True)          # D2H of the sampled tokens
+                torch.cuda.current_stream().synchronize()
+                pinned_in.copy_(pinned_out)                     # host feeds the next step
+            state["cur"] ^= 1
+            state["ctx"] += 1
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+
+    def timed(n, **kw):
+        """K steps between barrier+sync, CUDA events on the launching stream; max over ranks."""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ctx_start = state["ctx"]
+        e0.record()
+        decode_steps(n, **kw)
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, ctx_start
+
+    # ---- value: device-resident decode -----------------------------------------------------------
+    decode_steps(W)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = cabi.launch_count()
+    ms_total, ctx_start = timed(K)
+    gpu_launches = cabi.launch_count() - l0
+    clocks = sampler.stop()
+    ms_step = ms_total / K
+    value = world * B * K / (ms_total / 1e3)
+
+    kv_tok = cfg.kv_bytes_per_token
+    hbm_peak, tf_peak, peak_kind = peaks()
+
+    def step_bytes(ctx):  # W + sum (ctx_i + 1) kv_tok + B kv_tok
+        return cfg.weight_bytes() + B * (ctx + 1) * kv_tok + B * kv_tok
+
+    avg_step_bytes = sum(step_bytes(ctx_start + i) for i in range(K)) / K
+    step_gbs = avg_step_bytes / (ms_step / 1e3) / 1e9
+
+    # ---- roofline: per-kernel times from CUDA events between launches ----------------------------
+    roofline = None
+    kernels = None
+    if not args.no_profile:
+        decode_steps(W)
+        barrier()
+        ctx_p = state["ctx"]
+        eng.profile_begin()
+        decode_steps(K)
+        prof = eng.profile_end()
+        kernels = {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]}
+        attn_ms, attn_n = prof["attention"]
+        # algorithmic bytes of one attention launch = K and V of every cached token of every thread, one layer
+        avg_kv_len = ctx_p + (K - 1) / 2 + 1
+        attn_bytes = B * avg_kv_len * cfg.kv_dim * 2 * 2
+        achieved = attn_bytes / (attn_ms / attn_n / 1e3) / 1e9
+        gemm_ms = sum(prof[k][0] for k in ("gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down")) / K
+        gemm_tf = B * 2 * cfg.matmul_params() / (gemm_ms / 1e3) / 1e12
+        roofline = {
+            "bound": "hbm", "kernel": "attn_decode_kernel<128,4>", "achieved": achieved, "peak": hbm_peak,
+            "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_kind": peak_kind,
+            "bytes_per_launch": attn_bytes, "us_per_launch": attn_ms / attn_n * 1e3,
+            "share_of_step": attn_ms / sum(v[0] for v in prof.values()),
+            "step": {"algorithmic_bytes": avg_step_bytes, "achieved": step_gbs, "frac": step_gbs / hbm_peak},
+            "gemm": {"bound": "tensor", "achieved": gemm_tf, "peak": tf_peak, "unit": "TFLOP/s",
+                     "frac": gemm_tf / tf_peak, "ms_per_step": gemm_ms},
+        }
+
+    # ---- e2e: host buffers through the C ABI -----------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        pin_in = torch.empty(B, dtype=torch.int32, pin_memory=True)
+        pin_out = torch.empty(B, dtype=torch.int32, pin_memory=True)
+        pin_in.copy_(bufs[state["cur"]].cpu())
+        decode_steps(W, host_io=True, pinned_in=pin_in, pinned_out=pin_out)
+        ms_e2e, _ = timed(K, host_io=True, pinned_in=pin_in, pinned_out=pin_out)
+        e2e = {"value": world * B * K / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": B * 4,
+               "d2h_bytes_per_step": B * 4, "ms_per_step": ms_e2e / K,
+               "api": "kb_decode via ctypes, pinned host token buffers, per-step stream sync"}
+
+    cb = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline(cfg, args.cpu_threads, ctx0, args.cpu_steps)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {
+                "workload": f"{cfg.name} bf16 decode, {B} resident threads/GPU x {args.history}-token history + "
+                            f"{U}-token turn (BASELINE configs[2], thread-sharded: 4096 threads at 8 GPUs)",
+                "model": cfg.name, "threads_per_gpu": B, "history": args.history, "user_tokens": U,
+                "context_at_start": ctx_start, "kv_block_tokens": KB_BLOCK_TOKENS,
+                "l2": "inputs larger than L2 (KV read per step >> 126 MB); no explicit flush",
+                "parallelism": f"replica per GPU, thread-sharded x{world}, no collective",
+                "resident_note": resident_note,
+            },
+            "clocks": clocks, "gpu_launches": gpu_launches, "e2e": e2e, "roofline": roofline, "kernels": kernels,
+            "cpu_baseline": cb,
+            "prefill": {"ms": prefill_ms, "tokens": B * U, "tflops": prefill_flops / (prefill_ms / 1e3) / 1e12,
+                        "frac_of_tensor_peak": prefill_flops / (prefill_ms / 1e3) / 1e12 / tf_peak,
+                        "launches": l0 - launches0},
+        }
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_b200(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

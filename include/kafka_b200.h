@@ -196,6 +196,25 @@ int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampl
               int32_t* out_tokens, kb_stream stream);
 
 /* ---- diagnostics ------------------------------------------------------------------------------- */
+/* Per-kernel timing of the hot path with CUDA events recorded on the call's own stream between
+ * launches (bench.py's roofline numbers).  kb_profile_begin arms it; every kb_prefill / kb_decode
+ * until kb_profile_end adds its intervals; kb_profile_end synchronises on the last event, returns
+ * the summed milliseconds and launch counts per category and disarms.  Events are host objects;
+ * no device memory is allocated. */
+#define KB_PROF_EMBED 0
+#define KB_PROF_RMSNORM 1
+#define KB_PROF_GEMM_QKV 2
+#define KB_PROF_ROPE_APPEND 3
+#define KB_PROF_ATTENTION 4
+#define KB_PROF_GEMM_O 5
+#define KB_PROF_GEMM_GATE_UP 6
+#define KB_PROF_GEMM_DOWN 7
+#define KB_PROF_LM_HEAD 8
+#define KB_PROF_SAMPLE 9
+#define KB_PROF_CATS 10
+int kb_profile_begin(kb_engine* e);
+int kb_profile_end(kb_engine* e, float* ms_by_cat, int32_t* launches_by_cat);
+
 const char* kb_last_error(void);
 int kb_abi_version(void);
 /* Number of kernels this library has enqueued since load (bench.py's gpu_launches). */

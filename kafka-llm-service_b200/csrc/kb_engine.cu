@@ -105,6 +105,13 @@ struct kb_engine {
     int n_blocks = 0;
     kb::Workspace ws;
     int max_tokens = 0, max_seqs = 0;
+    // profiling: one event before every kernel (+ one closing event per call)
+    bool prof_on = false;
+    std::vector<cudaEvent_t> prof_pool;  // reusable events
+    size_t prof_used = 0;
+    std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> prof_iv;  // (cat, (start, stop))
+    cudaEvent_t prof_last = nullptr;
+    int prof_last_cat = -1;
 };
 
 namespace kb {
@@ -129,6 +136,20 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     KB_CUDA(cudaGetDevice(&dev));
     KB_CHECK(dev == e->device, "engine belongs to device %d but current device is %d", e->device, dev);
 
+    // profiling marks: an event before each kernel closes the previous interval and opens the next
+    auto mark = [&](int cat) {
+        if (!e->prof_on) return;
+        if (e->prof_used == e->prof_pool.size()) {
+            cudaEvent_t ev;
+            if (cudaEventCreate(&ev) != cudaSuccess) return;
+            e->prof_pool.push_back(ev);
+        }
+        cudaEvent_t ev = e->prof_pool[e->prof_used++];
+        cudaEventRecord(ev, stream);
+        if (e->prof_last_cat >= 0) e->prof_iv.push_back({e->prof_last_cat, {e->prof_last, ev}});
+        e->prof_last = ev;
+        e->prof_last_cat = cat;
+    };
     const kb_model_cfg& c = e->cfg;
     Workspace& w = e->ws;
     const int qdim = c.n_heads * c.head_dim;
@@ -136,16 +157,21 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     const size_t layer_stride = (size_t)e->n_blocks * c.n_kv_heads * KB_BLOCK_TOKENS * c.head_dim;
     int rc;
 
+    mark(KB_PROF_EMBED);
     if ((rc = embed(tokens, e->embed, w.x, n_tokens, c.hidden, c.vocab, stream))) return rc;
     for (int L = 0; L < c.n_layers; ++L) {
         const kb_layer_weights& lw = e->layers[L];
         __nv_bfloat16* kp = e->k_pool + (size_t)L * layer_stride;
         __nv_bfloat16* vp = e->v_pool + (size_t)L * layer_stride;
+        mark(KB_PROF_RMSNORM);
         if ((rc = rmsnorm(w.x, lw.attn_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, stream))) return rc;
+        mark(KB_PROF_GEMM_QKV);
         if ((rc = gemm(w.xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16, stream))) return rc;
+        mark(KB_PROF_ROPE_APPEND);
         if ((rc = rope_append(w.qkv, cu_seqlens, ctx_lens, block_tables, kp, vp, n_seqs, n_tokens, max_blocks,
                               c.n_heads, c.n_kv_heads, c.head_dim, c.rope_theta, stream)))
             return rc;
+        mark(KB_PROF_ATTENTION);
         if (decode) {
             rc = attn_decode(w.qkv, qkv_dim, kp, vp, ctx_lens, /*bias=*/1, block_tables, w.attn, n_seqs, max_blocks,
                              c.n_heads, c.n_kv_heads, c.head_dim, max_ctx > 0 ? max_ctx + 1 : 0, w.split,
@@ -155,22 +181,33 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
                               max_new, max_blocks, c.n_heads, c.n_kv_heads, c.head_dim, stream);
         }
         if (rc) return rc;
+        mark(KB_PROF_GEMM_O);
         if ((rc = gemm(w.attn, lw.wo, w.x, w.x, n_tokens, c.hidden, qdim, KB_EPI_RESID_F32, stream))) return rc;
+        mark(KB_PROF_RMSNORM);
         if ((rc = rmsnorm(w.x, lw.mlp_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, stream))) return rc;
+        mark(KB_PROF_GEMM_GATE_UP);
         if ((rc = gemm(w.xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden, KB_EPI_SWIGLU_BF16, stream)))
             return rc;
+        mark(KB_PROF_GEMM_DOWN);
         if ((rc = gemm(w.h, lw.w_down, w.x, w.x, n_tokens, c.hidden, c.ffn, KB_EPI_RESID_F32, stream))) return rc;
     }
-    if (logits_out == nullptr && out_tokens == nullptr) return KB_OK;  // KV fill only
+    if (logits_out == nullptr && out_tokens == nullptr) {  // KV fill only
+        mark(-1);
+        return KB_OK;
+    }
+    mark(KB_PROF_RMSNORM);
     // final norm on the last row of every sequence, lm_head, sampling
     if ((rc = rmsnorm(w.x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, n_seqs, c.hidden, c.rms_eps, stream)))
         return rc;
     float* lg = logits_out ? logits_out : w.logits;
+    mark(KB_PROF_LM_HEAD);
     if ((rc = gemm(w.xl, e->lm_head, lg, nullptr, n_seqs, c.vocab, c.hidden, KB_EPI_F32, stream))) return rc;
     if (out_tokens) {
+        mark(KB_PROF_SAMPLE);
         if ((rc = sample(lg, n_seqs, c.vocab, sampling, out_tokens, advance_ctx ? ctx_lens : nullptr, stream)))
             return rc;
     }
+    mark(-1);
     return KB_OK;
 }
 
@@ -208,7 +245,39 @@ extern "C" int kb_engine_create(int device, const kb_model_cfg* cfg, kb_engine**
     return KB_OK;
 }
 
-extern "C" void kb_engine_destroy(kb_engine* e) { delete e; }
+extern "C" void kb_engine_destroy(kb_engine* e) {
+    if (!e) return;
+    for (cudaEvent_t ev : e->prof_pool) cudaEventDestroy(ev);
+    delete e;
+}
+
+extern "C" int kb_profile_begin(kb_engine* e) {
+    KB_CHECK(e != nullptr, "kb_profile_begin: null engine");
+    e->prof_on = true;
+    e->prof_used = 0;
+    e->prof_iv.clear();
+    e->prof_last = nullptr;
+    e->prof_last_cat = -1;
+    return KB_OK;
+}
+
+extern "C" int kb_profile_end(kb_engine* e, float* ms_by_cat, int32_t* launches_by_cat) {
+    KB_CHECK(e != nullptr && ms_by_cat != nullptr && launches_by_cat != nullptr, "kb_profile_end: null argument");
+    e->prof_on = false;
+    for (int i = 0; i < KB_PROF_CATS; ++i) { ms_by_cat[i] = 0.f; launches_by_cat[i] = 0; }
+    if (e->prof_last) KB_CUDA(cudaEventSynchronize(e->prof_last));
+    for (auto& iv : e->prof_iv) {
+        float ms = 0.f;
+        KB_CUDA(cudaEventElapsedTime(&ms, iv.second.first, iv.second.second));
+        if (iv.first >= 0 && iv.first < KB_PROF_CATS) {
+            ms_by_cat[iv.first] += ms;
+            launches_by_cat[iv.first] += 1;
+        }
+    }
+    e->prof_iv.clear();
+    e->prof_used = 0;
+    return KB_OK;
+}
 
 extern "C" int kb_bind_weights(kb_engine* e, const kb_weight_ptrs* w) {
     KB_CHECK(e && w && w->layers, "kb_bind_weights: null argument");

@@ -19,6 +19,8 @@ from typing import Optional
 KB_BLOCK_TOKENS = 64
 KB_MAX_SPLITS = 16
 KB_ABI_VERSION = 1
+PROF_CATS = ("embed", "rmsnorm", "gemm_qkv", "rope_append", "attention", "gemm_o", "gemm_gate_up", "gemm_down",
+             "lm_head", "sample")
 
 EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_SWIGLU_BF16 = 0, 1, 2, 3
 
@@ -74,6 +76,8 @@ SIGNATURES = {
     "kb_attn_prefill": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                   _i32, _vp]),
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
+    "kb_profile_begin": (C.c_int, [_vp]),
+    "kb_profile_end": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "kb_last_error": (C.c_char_p, []),
     "kb_abi_version": (C.c_int, []),
     "kb_launch_count": (C.c_ulonglong, []),

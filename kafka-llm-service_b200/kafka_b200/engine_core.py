@@ -85,6 +85,18 @@ class EngineCore:
         except Exception:
             pass
 
+    # ---- per-kernel timing (CUDA events between launches; bench.py) ------------------------------
+    def profile_begin(self) -> None:
+        cabi.check(self.lib.kb_profile_begin(self._h), "kb_profile_begin")
+
+    def profile_end(self):
+        """-> {category: (milliseconds, launches)} summed over the calls since profile_begin."""
+        n = len(cabi.PROF_CATS)
+        ms = (C.c_float * n)()
+        cnt = (C.c_int32 * n)()
+        cabi.check(self.lib.kb_profile_end(self._h, ms, cnt), "kb_profile_end")
+        return {name: (float(ms[i]), int(cnt[i])) for i, name in enumerate(cabi.PROF_CATS)}
+
     # ---- hot path ----------------------------------------------------------------------------
     def prefill(self, tokens: torch.Tensor, cu_seqlens: torch.Tensor, ctx_lens: torch.Tensor,
                 block_tables: torch.Tensor, max_new: int, sampling: Optional[cabi.Sampling] = None,

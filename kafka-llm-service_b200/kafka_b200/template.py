@@ -1,0 +1,74 @@
+"""Chat template: messages (+ tool schemas) -> token ids, prefix-stably.
+
+The reference never templates anything: it forwards `[m.to_dict() for m in messages]` plus the tool
+list to the gateway (/root/reference/src/llm/portkey.py:263, :317-319). A local engine has to choose
+a rendering; this one is Llama-3-shaped and has the one property KV reuse depends on:
+
+    render(messages[:k]) is a token PREFIX of render(messages[:k+1])      (add_generation_prompt=False)
+
+because each message renders independently of what follows, and the tool block sits before all
+messages. Every field the reference's Message carries (role, content, name, tool_calls, tool_call_id
+— /root/reference/src/llm/types.py:47-51) is rendered, tool_calls as canonical JSON
+(sort_keys, compact separators) so equal structures give equal tokens.
+"""
+from __future__ import annotations
+
+import json
+from typing import Any, Dict, List, Optional, Sequence
+
+from .tokenizer import ByteTokenizer
+
+
+def canonical_json(obj: Any) -> str:
+    return json.dumps(obj, sort_keys=True, separators=(",", ":"), ensure_ascii=False)
+
+
+def _field(msg: Any, key: str):
+    return msg.get(key) if isinstance(msg, dict) else getattr(msg, key, None)
+
+
+class ChatTemplate:
+    def __init__(self, tokenizer: ByteTokenizer):
+        self.tok = tokenizer
+
+    # ---- pieces ------------------------------------------------------------------------------
+    def _header(self, label: str) -> List[int]:
+        t = self.tok
+        return [t.start_header_id] + t.encode(label) + [t.end_header_id] + t.encode("\n\n")
+
+    def render_tools(self, tools: Optional[Sequence[Dict[str, Any]]]) -> List[int]:
+        if not tools:
+            return []
+        return self._header("tools") + self.tok.encode(canonical_json(list(tools))) + [self.tok.eot_id]
+
+    def message_body(self, msg: Any) -> str:
+        content = _field(msg, "content")
+        body = content if isinstance(content, str) else ("" if content is None else canonical_json(content))
+        tool_calls = _field(msg, "tool_calls")
+        if tool_calls:
+            body += "\n<tool_calls>" + canonical_json(tool_calls) + "</tool_calls>"
+        return body
+
+    def render_message(self, msg: Any) -> List[int]:
+        label = str(_field(msg, "role"))
+        name = _field(msg, "name")
+        if name:
+            label += f" name={name}"
+        tcid = _field(msg, "tool_call_id")
+        if tcid:
+            label += f" tool_call_id={tcid}"
+        return self._header(label) + self.tok.encode(self.message_body(msg)) + [self.tok.eot_id]
+
+    def generation_prompt(self) -> List[int]:
+        return self._header("assistant")
+
+    # ---- whole conversation ------------------------------------------------------------------
+    def render(self, messages: Sequence[Any], tools: Optional[Sequence[Dict[str, Any]]] = None,
+               add_generation_prompt: bool = True) -> List[int]:
+        ids: List[int] = [self.tok.bos_id]
+        ids += self.render_tools(tools)
+        for m in messages:
+            ids += self.render_message(m)
+        if add_generation_prompt:
+            ids += self.generation_prompt()
+        return ids

@@ -44,21 +44,41 @@ def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.T
 
 
 class KVCache:
-    """Contiguous per-sequence cache: k[layer], v[layer] of shape [len, n_kv_heads, head_dim] (fp32)."""
+    """Contiguous per-sequence cache, fp32: per layer a [capacity, n_kv_heads, head_dim] buffer of
+    which the first ``length`` rows are valid (amortised-doubling append, so a decode step costs
+    O(1) copies like a real server's cache would)."""
 
     def __init__(self, n_layers: int):
-        self.k: List[Optional[torch.Tensor]] = [None] * n_layers
-        self.v: List[Optional[torch.Tensor]] = [None] * n_layers
+        self._k: List[Optional[torch.Tensor]] = [None] * n_layers
+        self._v: List[Optional[torch.Tensor]] = [None] * n_layers
+        self._len = [0] * n_layers
 
     @property
     def length(self) -> int:
-        return 0 if self.k[0] is None else self.k[0].shape[0]
+        return self._len[0]
+
+    def k(self, i: int) -> torch.Tensor:
+        return self._k[i][: self._len[i]]
+
+    def v(self, i: int) -> torch.Tensor:
+        return self._v[i][: self._len[i]]
+
+    def append(self, i: int, k: torch.Tensor, v: torch.Tensor) -> None:
+        n, need = k.shape[0], self._len[i] + k.shape[0]
+        if self._k[i] is None or need > self._k[i].shape[0]:
+            cap = max(need, 2 * (0 if self._k[i] is None else self._k[i].shape[0]), 64)
+            nk = torch.empty((cap,) + tuple(k.shape[1:]), dtype=k.dtype)
+            nv = torch.empty_like(nk)
+            if self._len[i]:
+                nk[: self._len[i]] = self._k[i][: self._len[i]]
+                nv[: self._len[i]] = self._v[i][: self._len[i]]
+            self._k[i], self._v[i] = nk, nv
+        self._k[i][self._len[i]: need] = k
+        self._v[i][self._len[i]: need] = v
+        self._len[i] = need
 
     def truncate(self, n: int) -> None:
-        for i in range(len(self.k)):
-            if self.k[i] is not None:
-                self.k[i] = self.k[i][:n]
-                self.v[i] = self.v[i][:n]
+        self._len = [min(n, l) for l in self._len]
 
 
 class OracleLlama:
@@ -91,10 +111,9 @@ class OracleLlama:
             v = (h @ w[p + "wv"].T).view(T, cfg.n_kv_heads, cfg.head_dim)
             q = apply_rope(q, cos, sin)
             k = apply_rope(k, cos, sin)
-            cache.k[i] = k if cache.k[i] is None else torch.cat([cache.k[i], k], 0)
-            cache.v[i] = v if cache.v[i] is None else torch.cat([cache.v[i], v], 0)
-            K = cache.k[i].repeat_interleave(cfg.group, dim=1)  # [L, n_heads, hd]
-            V = cache.v[i].repeat_interleave(cfg.group, dim=1)
+            cache.append(i, k, v)
+            K = cache.k(i).repeat_interleave(cfg.group, dim=1)  # [L, n_heads, hd]
+            V = cache.v(i).repeat_interleave(cfg.group, dim=1)
             s = torch.einsum("thd,lhd->htl", q, K) * scale      # [n_heads, T, L]
             L = K.shape[0]
             causal = torch.arange(L)[None, :] > (past + torch.arange(T))[:, None]
@@ -111,6 +130,34 @@ class OracleLlama:
         xl = x if all_logits else x[-1:]
         logits = rmsnorm(xl, w["final_norm"], cfg.rms_eps) @ w["lm_head"].T
         return logits if all_logits else logits[0]
+
+    @torch.no_grad()
+    def decode_batch(self, tokens: torch.Tensor, caches: List[KVCache]) -> torch.Tensor:
+        """One decode step for B sequences at once (projections batched over B, attention per
+        sequence). Same arithmetic as ``forward`` with T=1 per sequence; returns logits [B, V].
+        Used by bench.py's CPU baseline so the host cores see one [B,H]x[H,N] GEMM per projection."""
+        cfg, w = self.cfg, self.w
+        B = tokens.numel()
+        pos = torch.tensor([c.length for c in caches])
+        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta)
+        x = w["embed"][tokens.long()]
+        scale = cfg.head_dim ** -0.5
+        for i in range(cfg.n_layers):
+            p = f"l{i}."
+            h = rmsnorm(x, w[p + "attn_norm"], cfg.rms_eps)
+            q = apply_rope((h @ w[p + "wq"].T).view(B, cfg.n_heads, cfg.head_dim), cos, sin)
+            k = apply_rope((h @ w[p + "wk"].T).view(B, cfg.n_kv_heads, cfg.head_dim), cos, sin)
+            v = (h @ w[p + "wv"].T).view(B, cfg.n_kv_heads, cfg.head_dim)
+            o = torch.empty(B, cfg.n_heads, cfg.head_dim)
+            for b, c in enumerate(caches):
+                c.append(i, k[b:b + 1], v[b:b + 1])
+                qb = q[b].view(cfg.n_kv_heads, cfg.group, cfg.head_dim)
+                s = torch.einsum("kgd,lkd->kgl", qb, c.k(i)) * scale
+                o[b] = torch.einsum("kgl,lkd->kgd", torch.softmax(s, -1), c.v(i)).reshape(cfg.n_heads, cfg.head_dim)
+            x = x + o.view(B, cfg.q_dim) @ w[p + "wo"].T
+            h = rmsnorm(x, w[p + "mlp_norm"], cfg.rms_eps)
+            x = x + (torch.nn.functional.silu(h @ w[p + "w_gate"].T) * (h @ w[p + "w_up"].T)) @ w[p + "w_down"].T
+        return rmsnorm(x, w["final_norm"], cfg.rms_eps) @ w["lm_head"].T
 
     @torch.no_grad()
     def greedy(self, prompt: torch.Tensor, n_new: int, cache: Optional[KVCache] = None,

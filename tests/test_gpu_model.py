@@ -85,7 +85,7 @@ def test_greedy_agreement_margin_init(cuda):
     BASELINE north_star: tokens agree over 32 steps on >= 99% of threads."""
     from kafka_b200 import cabi
     from kafka_b200.weights import generable_ids
-    cfg, eng, oracle = _setup("tiny-test", cuda, init="margin", n_blocks=16 * 3, max_seqs=16)
+    cfg, eng, oracle = _setup("tiny-test", cuda, init="margin", n_blocks=16 * 3, max_tokens=2048, max_seqs=16)
     g = torch.Generator().manual_seed(5)
     B, max_blocks = 16, 3
     lens = [int(x) for x in torch.randint(4, 90, (B,), generator=g)]
