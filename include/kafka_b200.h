@@ -86,6 +86,10 @@ typedef struct kb_sampling {
      * extra ids (e.g. newline and <|eot_id|>); allowed_hi <= allowed_lo means "whole vocabulary". */
     int32_t allowed_lo, allowed_hi;
     int32_t extra_a, extra_b; /* -1 = unused */
+    /* Optional per-sequence overrides for a continuous batch whose requests differ (device arrays of
+     * n_seqs entries, NULL = use the scalars above): temperature and a seed XOR-ed into `seed`. */
+    const float* seq_temperature;
+    const uint64_t* seq_seed;
 } kb_sampling;
 
 /* ---- engine lifetime ------------------------------------------------------------------------- */

@@ -171,10 +171,13 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
 
 __global__ void __launch_bounds__(1024)
 sample_kernel(const float* __restrict__ logits, int vocab, float temperature, uint64_t seed, uint64_t step,
-              int banned, int lo, int hi, int extra_a, int extra_b, int* __restrict__ out_tokens,
+              int banned, int lo, int hi, int extra_a, int extra_b, const float* __restrict__ seq_temperature,
+              const uint64_t* __restrict__ seq_seed, int* __restrict__ out_tokens,
               int* __restrict__ ctx_lens_advance) {
     const int seq = blockIdx.x;
     const float* lg = logits + (size_t)seq * vocab;
+    if (seq_temperature) temperature = seq_temperature[seq];
+    if (seq_seed) seed ^= seq_seed[seq];
     const bool greedy = !(temperature > 0.f);
     const float inv_t = greedy ? 1.f : 1.f / temperature;
     const uint64_t base = splitmix64(seed ^ splitmix64(step * 0x100000001b3ull + (uint64_t)seq));
@@ -272,7 +275,8 @@ int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, in
         KB_CHECK(hi > lo, "kb_sample: empty allowed range");
     }
     sample_kernel<<<n_seqs, 1024, 0, stream>>>(logits, vocab, sp->temperature, sp->seed, sp->step, sp->banned_token,
-                                               lo, hi, ea, eb, out_tokens, ctx_advance);
+                                               lo, hi, ea, eb, sp->seq_temperature, sp->seq_seed, out_tokens,
+                                               ctx_advance);
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
