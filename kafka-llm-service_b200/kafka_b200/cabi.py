@@ -51,7 +51,8 @@ class WeightPtrs(C.Structure):
 class Sampling(C.Structure):
     _fields_ = [("temperature", C.c_float), ("seed", C.c_uint64), ("step", C.c_uint64),
                 ("banned_token", C.c_int32), ("allowed_lo", C.c_int32), ("allowed_hi", C.c_int32),
-                ("extra_a", C.c_int32), ("extra_b", C.c_int32)]
+                ("extra_a", C.c_int32), ("extra_b", C.c_int32),
+                ("seq_temperature", C.c_void_p), ("seq_seed", C.c_void_p)]
 
 
 # name -> (restype, argtypes); kept in one table so tests can check every symbol the header declares.
@@ -215,9 +216,11 @@ def attn_prefill(q, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tabl
 
 
 def make_sampling(temperature: float = 0.0, seed: int = 0, step: int = 0, banned_token: int = -1,
-                  allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1) -> Sampling:
+                  allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1,
+                  seq_temperature=None, seq_seed=None) -> Sampling:
+    """seq_temperature (float32) / seq_seed (int64 bit patterns) are optional per-sequence device tensors."""
     return Sampling(float(temperature), int(seed), int(step), int(banned_token), int(allowed_lo), int(allowed_hi),
-                    int(extra_a), int(extra_b))
+                    int(extra_a), int(extra_b), _ptr(seq_temperature), _ptr(seq_seed))
 
 
 def sample(logits, temperature: float = 0.0, seed: int = 0, step: int = 0, banned_token: int = -1,
