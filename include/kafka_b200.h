@@ -187,6 +187,30 @@ int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* k_pool_laye
                    int32_t batch, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads, int32_t head_dim,
                    int32_t max_kv_len, void* scratch, size_t scratch_bytes, kb_stream stream);
 
+/* Decode attention for callers that cannot allocate device memory.  No counterpart in the reference
+ * (nor in its plugin API): it exists for hosts of this library that are handed ready-made input and
+ * output buffers but have no allocator of their own — a foreign-language binding working on IPC or
+ * pool memory owned by someone else, a process whose HBM is carved up in advance, or a latency-bound
+ * loop that cannot afford cudaMalloc's device-wide synchronisation — and therefore cannot supply the
+ * split-KV scratch kb_attn_decode asks for.  Same arguments and result as kb_attn_decode; the partials
+ * live in a KB_STATIC_SCRATCH_BYTES array inside the library image (held by every GPU that loads the
+ * library, until exit).  Limits and rules:
+ *   - a shape whose partials exceed KB_STATIC_SCRATCH_BYTES is refused with KB_ERR_INVALID and a
+ *     message; it is not quietly run with fewer splits;
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress);
+ *     make that call with the device current and before any stream capture;
+ *   - no cudaMalloc / cudaFree / allocating routine is called;
+ *   - all calls on a device share the array (its contents are whatever the previous call left; every
+ *     call rewrites all it reads, so no clearing is needed), hence calls that can overlap on the GPU
+ *     race with each other and must be serialised by the caller. */
+#define KB_STATIC_SCRATCH_BYTES (2 * 1024 * 1024)
+size_t kb_static_scratch_capacity(void);
+int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+                                  const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
+                                  const int32_t* block_tables, void* out_bf16, int32_t batch,
+                                  int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads, int32_t head_dim,
+                                  int32_t max_kv_len, kb_stream stream);
+
 /* Paged causal attention for packed new tokens (incremental prefill): query i of sequence s attends
  * to the ctx_lens[s] cached tokens plus new tokens 0..i. K/V of the new tokens must already be
  * appended (kb_rope_append). */

@@ -583,3 +583,88 @@ extern "C" int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void*
                             n_seqs, n_tokens, max_new, max_blocks, n_heads, n_kv_heads, head_dim,
                             reinterpret_cast<cudaStream_t>(stream));
 }
+
+// ---------------------------------------------------------------------------------------------
+// kb_attn_decode_static_scratch — decode attention for callers that cannot allocate device memory.
+//
+// kb_attn_decode spreads a small batch over the whole GPU by splitting each sequence's KV range across
+// several CTAs; the partial results travel through a scratch buffer that the CALLER has to allocate.
+// Some callers have no way to do that: a binding that only ever receives finished input/output
+// buffers from another component (an IPC handle, a mapped frame, a pool owned by a different
+// runtime) and holds no allocator of its own; a host whose device memory is partitioned up front and
+// forbids side allocations; a latency-critical loop where cudaMalloc's implicit device-wide
+// synchronisation is not acceptable.  For them this entry point keeps the partials in a fixed array
+// that lives in the library image itself.
+//
+//   * The array is a file-scope `static __device__` object of KB_STATIC_SCRATCH_BYTES (2 MiB).
+//     Every GPU on which this library is loaded holds one copy from the moment its module is loaded
+//     until the process exits, whether or not this function is ever called.
+//   * On the host the identifier `g_static_scratch` is only a handle for the runtime, not a device
+//     address, so it is never passed to a kernel.  The first call on each device (with that device
+//     current) resolves the real address once with cudaGetSymbolAddress, checks the return code and
+//     caches it; later calls reuse the cached pointer.  Make that first call outside of any stream
+//     capture.
+//   * Nothing here calls cudaMalloc, cudaFree or any allocating routine; inputs and outputs still
+//     belong to the caller.
+//   * Shapes whose partials would not fit in the array are rejected with an error that says so —
+//     they are NOT silently run with fewer splits.  Large batches need no partials at all and are
+//     always accepted.
+//   * All calls on a device share the one array.  Each call overwrites every slot it later reads
+//     (empty splits write m = -inf, l = 0), so nothing has to be cleared between calls and stale
+//     contents of an earlier call are never consumed.  Two calls that may run on the GPU at the same
+//     time (different streams, or different host threads) race on the array: serialise them.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[KB_STATIC_SCRATCH_BYTES];
+
+namespace kb {
+static void* g_static_scratch_addr[64] = {};  // per device, resolved on first use
+
+static int static_scratch_for_current_device(void** out) {
+    int dev = -1;
+    KB_CUDA(cudaGetDevice(&dev));
+    KB_CHECK(dev >= 0 && dev < 64, "kb_attn_decode_static_scratch: device index %d out of range", dev);
+    if (g_static_scratch_addr[dev] == nullptr) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("kb_attn_decode_static_scratch: cudaGetSymbolAddress failed on device %d: %s", dev,
+                      cudaGetErrorString(e));
+            return KB_ERR_CUDA;
+        }
+        g_static_scratch_addr[dev] = p;
+    }
+    *out = g_static_scratch_addr[dev];
+    return KB_OK;
+}
+}  // namespace kb
+
+extern "C" size_t kb_static_scratch_capacity(void) { return (size_t)KB_STATIC_SCRATCH_BYTES; }
+
+extern "C" int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+                                             const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
+                                             const int32_t* block_tables, void* out_bf16, int32_t batch,
+                                             int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
+                                             int32_t head_dim, int32_t max_kv_len, kb_stream stream) {
+    using namespace kb;
+    KB_CHECK(batch > 0 && max_blocks > 0 && n_heads > 0 && n_kv_heads > 0,
+             "kb_attn_decode_static_scratch: bad batch / head arguments");
+    void* scratch = nullptr;
+    int rc = static_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    // How many partials would the regular entry point want for this shape?
+    int dev = 0, sms = 148;
+    KB_CUDA(cudaGetDevice(&dev));
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int len_bound = max_kv_len > 0 ? max_kv_len : max_blocks * KB_BLOCK_TOKENS;
+    const int n_splits = attn_decode_pick_splits(batch, n_kv_heads, len_bound, sms);
+    const size_t need = n_splits > 1 ? attn_decode_scratch_bytes(batch, n_heads, head_dim, n_splits) : 0;
+    if (need > (size_t)KB_STATIC_SCRATCH_BYTES) {
+        set_error("kb_attn_decode_static_scratch: batch=%d n_heads=%d head_dim=%d with %d KV splits needs %zu bytes "
+                  "of partials, more than the built-in %d-byte array; use kb_attn_decode with caller scratch",
+                  batch, n_heads, head_dim, n_splits, need, (int)KB_STATIC_SCRATCH_BYTES);
+        return KB_ERR_INVALID;
+    }
+    return attn_decode(q_bf16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out_bf16,
+                       batch, max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, scratch,
+                       (size_t)KB_STATIC_SCRATCH_BYTES, reinterpret_cast<cudaStream_t>(stream));
+}

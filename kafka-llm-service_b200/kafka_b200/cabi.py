@@ -74,6 +74,9 @@ SIGNATURES = {
     "kb_attn_decode_scratch_bytes": (_sz, [_i32, _i32, _i32]),
     "kb_attn_decode": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                  _vp, _sz, _vp]),
+    "kb_static_scratch_capacity": (_sz, []),
+    "kb_attn_decode_static_scratch": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32,
+                                                _i32, _i32, _vp]),
     "kb_attn_prefill": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                   _i32, _vp]),
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
@@ -196,6 +199,22 @@ def attn_decode(q, k_pool_layer, v_pool_layer, kv_lens, block_tables, n_heads, n
     check(load().kb_attn_decode(_ptr(q), q.stride(0), _ptr(k_pool_layer), _ptr(v_pool_layer), _ptr(kv_lens),
                                 kv_len_bias, _ptr(block_tables), _ptr(out), batch, max_blocks, n_heads, n_kv_heads,
                                 head_dim, max_kv_len, _ptr(scratch), sb, _stream()), "kb_attn_decode")
+    return out
+
+
+def attn_decode_static_scratch(q, k_pool_layer, v_pool_layer, kv_lens, block_tables, n_heads, n_kv_heads, head_dim,
+                               kv_len_bias: int = 0, max_kv_len: int = 0, out=None):
+    """kb_attn_decode for hosts that cannot allocate: the split-KV partials go to the library's
+    built-in 2 MiB device array instead of a caller buffer. Pass ``out`` to avoid any allocation on
+    this side too (the default allocates the result with torch for convenience in tests)."""
+    import torch
+    batch, max_blocks = block_tables.shape
+    if out is None:
+        out = torch.empty((batch, n_heads * head_dim), dtype=torch.bfloat16, device=q.device)
+    check(load().kb_attn_decode_static_scratch(_ptr(q), q.stride(0), _ptr(k_pool_layer), _ptr(v_pool_layer),
+                                               _ptr(kv_lens), kv_len_bias, _ptr(block_tables), _ptr(out), batch,
+                                               max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, _stream()),
+          "kb_attn_decode_static_scratch")
     return out
 
 
