@@ -1,0 +1,188 @@
+"""B200LLMProvider — the drop-in for the reference's PortkeyLLMProvider on local Llama models.
+
+Same plugin surface as /root/reference/src/llm/portkey.py (stream_completion :225-483, completion
+:485-669, get_model_info :671, close :691) and the same chunk conventions the reference's agent
+reads (/root/reference/src/agents/base.py:274-348): a first chunk with role="assistant", content
+chunks (content is None — never "" — when absent), a final chunk whose finish_reason is "stop" or
+"length", `id` and `model` on every chunk. Failures surface as LLMProviderError(provider="B200")
+(:477-483); an over-long prompt raises an error that is_context_length_error
+(/root/reference/src/llm/context_compaction/base.py:10-65) recognises, so the agent's compaction
+retry still fires.
+
+What differs by design: the completion is computed on this box (engine.py -> C ABI -> sm_100a
+kernels), one StreamChunk per generated token, and the conversation's KV stays resident between
+calls — the prompt is re-templated and matched against resident token prefixes, so only the new
+messages are prefilled.
+"""
+from __future__ import annotations
+
+import asyncio
+import uuid
+from typing import Any, AsyncGenerator, Dict, List, Optional
+
+from .llm.base import LLMProvider
+from .llm.types import CompletionResponse, LLMProviderError, Message, StreamChunk
+from .scheduler import ContextLengthError, SamplingParams
+from .template import ChatTemplate
+from .tokenizer import ByteTokenizer
+
+PROVIDER_NAME = "B200"
+
+
+class B200LLMProvider(LLMProvider):
+    def __init__(self, engine, tokenizer: ByteTokenizer, model: str, tool_provider: Optional[Any] = None,
+                 default_temperature: float = 0.7, default_max_tokens: Optional[int] = None,
+                 thread_id: Optional[str] = None, seed: int = 0):
+        super().__init__(tool_provider=tool_provider)
+        self.engine = engine            # Engine or ShardedEngine (process-wide, shared by providers)
+        self.tokenizer = tokenizer
+        self.template = ChatTemplate(tokenizer)
+        self.model = model
+        self.default_temperature = default_temperature
+        self.default_max_tokens = default_max_tokens
+        self.thread_id = thread_id
+        self.seed = seed
+
+    # ---- helpers -------------------------------------------------------------------------------
+    def render(self, messages: List[Message], tools: Optional[List[Dict[str, Any]]]) -> List[int]:
+        return self.template.render(messages, tools=tools or None, add_generation_prompt=True)
+
+    @staticmethod
+    def _first_stop(text: str, stop: Optional[List[str]]) -> int:
+        if not stop:
+            return -1
+        hits = [i for i in (text.find(s) for s in stop if s) if i >= 0]
+        return min(hits) if hits else -1
+
+    # ---- the plugin API ------------------------------------------------------------------------
+    async def stream_completion(self, messages: List[Message], *, temperature: Optional[float] = None,
+                                max_tokens: Optional[int] = None, stop: Optional[List[str]] = None,
+                                **kwargs: Any) -> AsyncGenerator[StreamChunk, None]:
+        validated = self.validate_messages(messages)          # ValueError on empty, like the reference
+        model = kwargs.pop("model", None) or self.model
+        thread_id = kwargs.pop("thread_id", None) or self.thread_id
+        seed = int(kwargs.pop("seed", self.seed) or 0)
+        usage_out = kwargs.pop("_usage_out", None)            # completion() collects usage through this
+        completion_id = f"chatcmpl-{uuid.uuid4().hex[:24]}"
+        req = None
+        try:
+            tools = await self.get_tools()
+            prompt = self.render(validated, tools)
+            temp = self.default_temperature if temperature is None else float(temperature)
+            limit = max_tokens if max_tokens is not None else (self.default_max_tokens or 512)
+            loop = asyncio.get_running_loop()
+            events: "asyncio.Queue" = asyncio.Queue()
+
+            def on_event(ev, _loop=loop, _q=events):
+                _loop.call_soon_threadsafe(_q.put_nowait, ev)
+
+            req = self.engine.submit(prompt, SamplingParams(temperature=temp, seed=seed, max_tokens=int(limit)),
+                                     on_event, thread_hint=thread_id)
+        except ContextLengthError as e:
+            raise LLMProviderError(str(e), status_code=400, provider=PROVIDER_NAME, original_error=e) from e
+        except (ValueError, LLMProviderError):
+            raise
+        except Exception as e:
+            raise LLMProviderError(str(e), provider=PROVIDER_NAME, original_error=e) from e
+
+        try:
+            yield StreamChunk(role="assistant", model=model, id=completion_id)
+            decoder = self.tokenizer.stream_decoder()
+            text = ""
+            emitted = 0
+            hold = max((len(s) for s in stop), default=1) - 1 if stop else 0
+            while True:
+                ev = await events.get()
+                kind = ev[0]
+                if kind == "token":
+                    text += decoder.push(ev[1])
+                    cut = self._first_stop(text, stop)
+                    if cut >= 0:
+                        if cut > emitted:
+                            yield StreamChunk(content=text[emitted:cut], model=model, id=completion_id)
+                        req.cancelled = True
+                        yield StreamChunk(finish_reason="stop", model=model, id=completion_id)
+                        return
+                    upto = len(text) - hold            # keep back what could still grow into a stop string
+                    if upto > emitted:
+                        yield StreamChunk(content=text[emitted:upto], model=model, id=completion_id)
+                        emitted = upto
+                elif kind == "finish":
+                    text += decoder.flush()
+                    if len(text) > emitted:
+                        yield StreamChunk(content=text[emitted:], model=model, id=completion_id)
+                    if usage_out is not None:
+                        usage_out.update(ev[2])
+                    yield StreamChunk(finish_reason=ev[1], model=model, id=completion_id)
+                    return
+                else:  # ("error", exc)
+                    exc = ev[1]
+                    raise LLMProviderError(str(exc), provider=PROVIDER_NAME, original_error=exc)
+        finally:
+            # abandoned mid-stream (client disconnect / aclose): free the slot, keep the KV computed so far
+            if req is not None:
+                req.cancelled = True
+
+    async def completion(self, messages: List[Message], *, temperature: Optional[float] = None,
+                         max_tokens: Optional[int] = None, stop: Optional[List[str]] = None,
+                         **kwargs: Any) -> CompletionResponse:
+        usage: Dict[str, int] = {}
+        parts: List[str] = []
+        finish = None
+        cid = model = None
+        async for ch in self.stream_completion(messages, temperature=temperature, max_tokens=max_tokens, stop=stop,
+                                               _usage_out=usage, **kwargs):
+            if ch.content:
+                parts.append(ch.content)
+            finish = ch.finish_reason or finish
+            cid, model = ch.id, ch.model
+        return CompletionResponse(content="".join(parts), finish_reason=finish, model=model, id=cid,
+                                  usage=usage or None)
+
+    def get_model_info(self) -> Dict[str, Any]:
+        return {"model": self.model, "provider": PROVIDER_NAME, "max_context_tokens": self.engine.max_pos,
+                "supports_vision": False, "supports_tools": False, "default_temperature": self.default_temperature}
+
+    async def close(self) -> None:
+        """The engine is process-wide and outlives provider objects (one is built per request on
+        /agent/run, /root/reference/server.py:237-245), so closing a provider is a no-op like the
+        reference's (/root/reference/src/llm/portkey.py:691-701)."""
+        return None
+
+    def _create_client_for_provider(self, provider_name: str):
+        """/root/reference/src/kafka/v1.py:185 reaches into this private method to build the compaction
+        client. There is no remote client here; returning None makes summarisation unavailable, and the
+        construction code should pick TruncationCompactionProvider."""
+        return None
+
+
+class EchoLLMProvider(LLMProvider):
+    """Returns the last user message. Host-plumbing stand-in for BASELINE config 1 (thread replay on
+    CPU: history load / assembly / persistence without any model)."""
+
+    def __init__(self, model: str = "echo", tool_provider: Optional[Any] = None):
+        super().__init__(tool_provider=tool_provider)
+        self.model = model
+
+    async def stream_completion(self, messages, *, temperature=None, max_tokens=None, stop=None, **kwargs):
+        validated = self.validate_messages(messages)
+        model = kwargs.pop("model", None) or self.model
+        cid = f"chatcmpl-{uuid.uuid4().hex[:24]}"
+        last_user = next((m.content for m in reversed(validated) if m.role == "user" and m.content), "")
+        yield StreamChunk(role="assistant", model=model, id=cid)
+        if last_user:
+            yield StreamChunk(content=last_user, model=model, id=cid)
+        yield StreamChunk(finish_reason="stop", model=model, id=cid)
+
+    async def completion(self, messages, *, temperature=None, max_tokens=None, stop=None, **kwargs):
+        parts, finish, cid, model = [], None, None, None
+        async for ch in self.stream_completion(messages, **kwargs):
+            if ch.content:
+                parts.append(ch.content)
+            finish, cid, model = ch.finish_reason or finish, ch.id, ch.model
+        text = "".join(parts)
+        return CompletionResponse(content=text, finish_reason=finish, model=model, id=cid,
+                                  usage={"prompt_tokens": 0, "completion_tokens": len(text), "total_tokens": len(text)})
+
+    async def close(self) -> None:
+        return None

@@ -1,0 +1,251 @@
+"""Host logic of one replica: block allocation, thread -> KV residency, longest-prefix reuse,
+continuous batching, eviction, cancellation — on CPU against FakeStepper (tests/fakes.py)."""
+import threading
+import time
+
+import pytest
+
+from fakes import FakeStepper, expected_tokens
+from kafka_b200.engine import Engine, ShardedEngine
+from kafka_b200.scheduler import (BLOCK_TOKENS, BlockAllocator, ContextLengthError, KVEntry, PrefixIndex,
+                                  SamplingParams, shard_of, stable_hash64)
+
+EOS = 511
+
+
+class Collector:
+    def __init__(self):
+        self.tokens, self.finish, self.usage, self.error = [], None, None, None
+        self.done = threading.Event()
+
+    def __call__(self, ev):
+        if ev[0] == "token":
+            self.tokens.append(ev[1])
+        elif ev[0] == "finish":
+            self.finish, self.usage = ev[1], ev[2]
+            self.done.set()
+        else:
+            self.error = ev[1]
+            self.done.set()
+
+    def wait(self, t=10):
+        assert self.done.wait(t), "request did not finish"
+        return self
+
+
+def run(engine, prompt, n=8, hint=None, **kw):
+    c = Collector()
+    engine.submit(prompt, SamplingParams(max_tokens=n, **kw), c, thread_hint=hint)
+    return c.wait()
+
+
+@pytest.fixture
+def engine():
+    st = FakeStepper(n_blocks=64, max_seqs=8, max_tokens=256, max_pos=1024, eos_id=EOS)
+    e = Engine(st, max_prefill_tokens=128)
+    yield e
+    e.shutdown()
+
+
+def test_block_allocator():
+    a = BlockAllocator(8)
+    x = a.alloc(3)
+    y = a.alloc(5)
+    assert sorted(x + y) == list(range(8)) and a.alloc(1) is None and a.alloc(0) == []
+    a.free(x)
+    assert a.n_free == 3 and sorted(a.alloc(3)) == sorted(x)
+
+
+def test_stable_hash_and_sharding():
+    assert stable_hash64(b"thread-1") == stable_hash64(b"thread-1")
+    assert stable_hash64(b"bench-0001") == 0xE1133E67972CA3C7   # pinned: must never depend on the process
+    assert [shard_of(f"bench-{i:04d}", [], 8) for i in range(8)] == [6, 7, 7, 2, 4, 4, 5, 4]
+    owners = [shard_of(f"bench-{i:04d}", [1, 2, 3], 8) for i in range(4096)]
+    counts = [owners.count(g) for g in range(8)]
+    assert min(counts) > 400 and max(counts) < 620            # 4096 threads spread over 8 GPUs
+    assert shard_of("t", [1], 1) == 0
+    assert shard_of(None, list(range(300)), 4) == shard_of(None, list(range(256)) + [9] * 44, 4)  # first 256 tokens
+
+
+def test_prefix_index_longest_match():
+    idx = PrefixIndex()
+    base = list(range(200))
+    e1 = KVEntry(1, tokens=base[:130], blocks=[0, 1, 2])
+    e2 = KVEntry(2, tokens=base[:70] + [999] * 30, blocks=[3, 4])
+    e3 = KVEntry(3, tokens=[7, 7, 7], blocks=[5], thread_hint="short")
+    for e in (e1, e2, e3):
+        idx.add(e)
+    e, n = idx.lookup(base[:150], None)
+    assert e is e1 and n == 130
+    e, n = idx.lookup(base[:70] + [999] * 10 + [5], None)
+    assert e is e2 and n == 80
+    e, n = idx.lookup([7, 7, 8], "short")                      # shorter than a block: found through the hint
+    assert e is e3 and n == 2
+    e1.busy = True
+    e, n = idx.lookup(base[:150], None)
+    assert e is e2 and n == 70                                  # busy entries are never shared
+    idx.remove(e2)
+    e1.busy = False
+    idx.remove(e1)
+    assert idx.lookup(base[:150], None) == (None, 0)
+
+
+def test_single_request_matches_pure_function(engine):
+    prompt = list(range(40, 140))
+    c = run(engine, prompt, n=12)
+    assert c.tokens == expected_tokens(prompt, 12, EOS) and c.finish == "length"
+    assert c.usage == {"prompt_tokens": 100, "completion_tokens": 12, "total_tokens": 112, "cached_tokens": 0}
+
+
+def test_turns_reuse_resident_prefix(engine):
+    """Second turn = first prompt + the generated reply + a new user message: only the new part is prefilled."""
+    st = engine.stepper
+    p1 = list(range(50, 250))                                    # 200 tokens
+    c1 = run(engine, p1, n=10, hint="thread-A")
+    before = st.prefilled_tokens
+    p2 = p1 + c1.tokens + [EOS] + list(range(60, 90))            # reply is re-templated: tokens + <eot> + new msg
+    c2 = run(engine, p2, n=10, hint="thread-A")
+    assert c2.tokens == expected_tokens(p2, 10, EOS)
+    # resident: p1 + first 9 generated tokens (the 10th was sampled but never fed back)
+    assert c2.usage["cached_tokens"] == len(p1) + 9
+    assert st.prefilled_tokens - before == len(p2) - (len(p1) + 9)
+    # without the hint the prefix is still found (the reference never forwards thread ids)
+    p3 = p2 + c2.tokens + [EOS, 65, 66]
+    c3 = run(engine, p3, n=4)
+    assert c3.usage["cached_tokens"] == len(p2) + 9 and c3.tokens == expected_tokens(p3, 4, EOS)
+
+
+def test_divergent_history_reprefills_from_divergence(engine):
+    p1 = list(range(30, 230))
+    run(engine, p1, n=6, hint="t")
+    p2 = p1[:150] + [400, 401, 402] + list(range(70, 100))       # history edited at position 150 (compaction etc.)
+    c2 = run(engine, p2, n=6, hint="t")
+    assert c2.usage["cached_tokens"] == 150 and c2.tokens == expected_tokens(p2, 6, EOS)
+
+
+def test_identical_prompt_recomputes_last_token(engine):
+    p = list(range(100, 190))
+    a = run(engine, p, n=3, hint="x")
+    b = run(engine, p, n=3, hint="x")                           # whole prompt resident: one token still runs
+    assert a.tokens == b.tokens and b.usage["cached_tokens"] == len(p) - 1
+
+
+def test_concurrent_requests_batch_and_stay_isolated(engine):
+    prompts = [list(range(33 + i, 33 + i + 70 + 13 * i)) for i in range(8)]
+    cols = [Collector() for _ in prompts]
+    for p, c in zip(prompts, cols):
+        engine.submit(p, SamplingParams(max_tokens=20), c, thread_hint=None)
+    for p, c in zip(prompts, cols):
+        c.wait()
+        assert c.tokens == expected_tokens(p, 20, EOS)
+    assert max(engine.stepper.decode_batches) > 1               # they really shared decode steps
+    assert all(sum(call) <= 128 for call in engine.stepper.prefill_calls)   # chunked to the token budget
+
+
+def test_more_requests_than_slots_queue_up(engine):
+    prompts = [[40 + i] * 30 for i in range(20)]                 # 20 requests, 8 slots
+    cols = [Collector() for _ in prompts]
+    for p, c in zip(prompts, cols):
+        engine.submit(p, SamplingParams(max_tokens=5), c)
+    for p, c in zip(prompts, cols):
+        assert c.wait().tokens == expected_tokens(p, 5, EOS)
+    assert max(engine.stepper.decode_batches) <= 8
+
+
+def test_eos_finishes_with_stop():
+    st = FakeStepper(eos_id=EOS, eos_every=4)
+    e = Engine(st)
+    try:
+        p = list(range(60, 100))
+        want = expected_tokens(p, 64, EOS, eos_every=4)
+        assert want[-1] == EOS
+        c = run(e, p, n=64)
+        assert c.finish == "stop" and c.tokens == want[:-1]      # the EOS itself is not streamed
+        assert c.usage["completion_tokens"] == len(want)
+    finally:
+        e.shutdown()
+
+
+def test_lru_eviction_when_pool_is_full():
+    st = FakeStepper(n_blocks=8, max_seqs=2, max_tokens=256, max_pos=512, eos_id=EOS)
+    e = Engine(st)
+    try:
+        pa, pb, pc = [50] * 150, [60] * 150, [70] * 150          # 3 blocks each (+ generation) -> only two fit
+        run(e, pa, n=4, hint="a")
+        run(e, pb, n=4, hint="b")
+        run(e, pc, n=4, hint="c")                                # evicts "a" (least recently used)
+        assert e.sched.stats["evictions"] >= 1
+        hints = {x["thread_id"] for x in e.sched.residency()}
+        assert "a" not in hints and {"b", "c"} <= hints
+        c = run(e, pa + [1, 2], n=4, hint="a")                   # evicted thread: full re-prefill, same tokens
+        assert c.usage["cached_tokens"] == 0 and c.tokens == expected_tokens(pa + [1, 2], 4, EOS)
+    finally:
+        e.shutdown()
+
+
+def test_context_overflow_message_triggers_reference_compaction(engine):
+    with pytest.raises(ContextLengthError) as ei:
+        engine.submit(list(range(2000)), SamplingParams(), lambda ev: None)
+    msg = str(ei.value).lower()
+    assert "maximum context length" in msg and "context_length_exceeded" in msg
+
+
+def test_max_tokens_clamped_to_context(engine):
+    c = run(engine, [65] * 1000, n=500)
+    assert c.usage["completion_tokens"] == 24                    # 1024 - 1000
+
+
+def test_cancellation_frees_slot_and_keeps_kv(engine):
+    got = []
+    gate = threading.Event()
+
+    def on_event(ev):
+        got.append(ev)
+        if len(got) == 3:
+            gate.set()
+
+    req = engine.submit([80] * 100, SamplingParams(max_tokens=500), on_event, thread_hint="c")
+    assert gate.wait(10)
+    req.cancelled = True
+    deadline = time.time() + 10
+    while engine.sched.running and time.time() < deadline:
+        time.sleep(0.01)
+    assert not engine.sched.running
+    res = {x["thread_id"]: x for x in engine.sched.residency()}
+    assert res["c"]["n_tokens"] >= 100                           # prompt + what was generated stays resident
+    c = run(engine, [80] * 100 + [1], n=2, hint="c")
+    assert c.usage["cached_tokens"] >= 100
+
+
+def test_engine_failure_reaches_every_request():
+    class Boom(FakeStepper):
+        def decode(self, reqs):
+            raise RuntimeError("device fault")
+    e = Engine(Boom(eos_id=EOS))
+    try:
+        c = run(e, [70] * 10, n=5)
+        assert isinstance(c.error, RuntimeError)
+        with pytest.raises(RuntimeError, match="engine thread died"):
+            e.submit([1, 2], SamplingParams(), lambda ev: None)
+    finally:
+        e.shutdown()
+
+
+def test_sharded_engine_routes_by_thread():
+    engines = [Engine(FakeStepper(eos_id=EOS)) for _ in range(4)]
+    se = ShardedEngine(engines)
+    try:
+        for i in range(16):
+            tid = f"bench-{i:04d}"
+            c = run(se, [40 + i] * 70, n=3, hint=tid)
+            assert c.tokens == expected_tokens([40 + i] * 70, 3, EOS)
+        for i in range(16):
+            tid = f"bench-{i:04d}"
+            owner = shard_of(tid, [], 4)
+            hints = {x["thread_id"] for x in engines[owner].sched.residency()}
+            assert tid in hints
+            for g in range(4):
+                if g != owner:
+                    assert tid not in {x["thread_id"] for x in engines[g].sched.residency()}
+    finally:
+        se.shutdown()
