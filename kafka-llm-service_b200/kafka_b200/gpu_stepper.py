@@ -79,7 +79,7 @@ class GpuStepper(Stepper):
         self.core = core
         cfg = core.cfg
         self.max_seqs, self.max_tokens, self.n_blocks = core.max_seqs, core.max_tokens, core.n_blocks
-        self.max_pos, self.eos_id = cfg.max_pos, tokenizer.eos_id
+        self.max_pos, self.eos_id = cfg.max_pos, tokenizer.eot_id
         self.max_blocks = (cfg.max_pos + BLOCK_TOKENS - 1) // BLOCK_TOKENS
         self.stream = torch.cuda.Stream(device=core.device)
         self.st_prefill = _Staging(torch, core.device, core.max_tokens, core.max_seqs, self.max_blocks)
