@@ -55,7 +55,8 @@ typedef struct kb_model_cfg {
     float rms_eps;
 } kb_model_cfg;
 
-/* bf16 device pointers, row-major [out_features, in_features] like torch.nn.Linear.weight.
+/* Device pointers, row-major [out_features, in_features] like torch.nn.Linear.weight.  The five GEMM
+ * operands (wqkv, wo, w_gate_up, w_down, lm_head) are FP16 (see KB_GEMM_F16); norms and embed are bf16.
  *   wqkv      : [(n_heads + 2 n_kv_heads) * head_dim, hidden]   rows = q heads, k heads, v heads
  *   wo        : [hidden, n_heads * head_dim]
  *   w_gate_up : [2 * ffn, hidden]   row 2j = gate_j, row 2j+1 = up_j (interleaved for the SwiGLU epilogue)
@@ -73,7 +74,7 @@ typedef struct kb_layer_weights {
 typedef struct kb_weight_ptrs {
     const void* embed;      /* [vocab, hidden] bf16 */
     const void* final_norm; /* [hidden] bf16 */
-    const void* lm_head;    /* [vocab, hidden] bf16 */
+    const void* lm_head;    /* [vocab, hidden] fp16 */
     const kb_layer_weights* layers; /* host array of n_layers entries */
 } kb_weight_ptrs;
 
@@ -144,9 +145,9 @@ int kb_decode(kb_engine* e, const int32_t* last_tokens, int32_t* ctx_lens, const
 
 /* ---- per-kernel entry points (unit parity tests; same kernels the hot path launches) ----------- */
 
-/* y[t,:] = bf16( x[t,:] * rsqrt(mean(x^2) + eps) * w ),  x fp32 [n, hidden] */
-int kb_rmsnorm(const float* x, const void* w_bf16, void* y_bf16, int32_t n, int32_t hidden, float eps,
-               kb_stream stream);
+/* y[t,:] = x[t,:] * rsqrt(mean(x^2) + eps) * w,  x fp32 [n, hidden], y fp16 (out_f16 != 0) or bf16 */
+int kb_rmsnorm(const float* x, const void* w_bf16, void* y, int32_t n, int32_t hidden, float eps,
+               int32_t out_f16, kb_stream stream);
 
 /* x[t,:] = float(embed[token[t], :]) */
 int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x, int32_t n, int32_t hidden,
@@ -159,6 +160,14 @@ int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x, int32_t n,
 #define KB_EPI_F32 1
 #define KB_EPI_RESID_F32 2
 #define KB_EPI_SWIGLU_BF16 3
+#define KB_EPI_SWIGLU_F16 4 /* same, fp16 out (the hot path's activation format, see KB_GEMM_A_F16) */
+/* OR into `epilogue`: BOTH operands are fp16 instead of bf16 (tcgen05 kind::f16 requires A and B to
+ * share one format; mixing traps).  The hot path keeps its GEMM activations (normed hidden states,
+ * attention output, MLP inner) in fp16 — 10 mantissa bits against bf16's 7 — because their rounding is
+ * the largest error term of a bf16 pipeline, and therefore binds the projection weights
+ * as fp16 re-encodings of the bf16 values (exact for |w| >= 2^-14).  q/k/v, the KV cache and the
+ * attention arithmetic stay bf16; accumulation is fp32 throughout. */
+#define KB_GEMM_F16 0x100
 int kb_gemm(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,
             int32_t K, int32_t epilogue, kb_stream stream);
 /* Same, with the output tile width forced to tile_n in {64, 128, 256} (0 = heuristic); for tuning and
@@ -175,7 +184,8 @@ int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx
                    int32_t head_dim, float rope_theta, kb_stream stream);
 
 /* Paged attention, one query token per sequence, over kv_lens[s] + kv_len_bias cached tokens.
- *   q   [batch, q_stride] bf16 (first n_heads*head_dim columns are the heads), out [batch, n_heads*head_dim] bf16
+ *   q   [batch, q_stride] bf16 (first n_heads*head_dim columns are the heads);
+ *   out [batch, n_heads*head_dim], fp16 when out_f16 != 0 (the hot path), else bf16
  *   max_kv_len : host-side bound on kv_lens[s] + kv_len_bias (0 = max_blocks * KB_BLOCK_TOKENS)
  *   scratch    : optional device buffer for split-KV partials (kb_attn_decode_scratch_bytes); NULL = no
  *                cross-CTA split (small batches then use fewer SMs).
@@ -185,7 +195,7 @@ size_t kb_attn_decode_scratch_bytes(int32_t batch, int32_t n_heads, int32_t head
 int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
                    const int32_t* kv_lens, int32_t kv_len_bias, const int32_t* block_tables, void* out_bf16,
                    int32_t batch, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads, int32_t head_dim,
-                   int32_t max_kv_len, void* scratch, size_t scratch_bytes, kb_stream stream);
+                   int32_t max_kv_len, void* scratch, size_t scratch_bytes, int32_t out_f16, kb_stream stream);
 
 /* Decode attention for callers that cannot allocate device memory.  No counterpart in the reference
  * (nor in its plugin API): it exists for hosts of this library that are handed ready-made input and
@@ -209,7 +219,7 @@ int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_stride, const vo
                                   const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
                                   const int32_t* block_tables, void* out_bf16, int32_t batch,
                                   int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads, int32_t head_dim,
-                                  int32_t max_kv_len, kb_stream stream);
+                                  int32_t max_kv_len, int32_t out_f16, kb_stream stream);
 
 /* Paged causal attention for packed new tokens (incremental prefill): query i of sequence s attends
  * to the ctx_lens[s] cached tokens plus new tokens 0..i. K/V of the new tokens must already be
@@ -217,7 +227,7 @@ int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_stride, const vo
 int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
                     const int32_t* cu_seqlens, const int32_t* ctx_lens, const int32_t* block_tables,
                     void* out_bf16, int32_t n_seqs, int32_t n_tokens, int32_t max_new, int32_t max_blocks,
-                    int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, kb_stream stream);
+                    int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t out_f16, kb_stream stream);
 
 /* out_tokens[s] = argmax_j (logits[s,j] / T + gumbel(seed, step, s, j)); greedy when T <= 0. */
 int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,

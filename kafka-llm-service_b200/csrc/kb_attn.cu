@@ -27,6 +27,12 @@ namespace kb {
 
 constexpr float LOG2E = 1.4426950408889634f;
 
+// one 16-bit activation: fp16 when f16 != 0, else bf16
+__device__ __forceinline__ uint16_t act16(float v, int f16) {
+    if (f16) return __half_as_ushort(__float2half_rn(v));
+    return __bfloat16_as_ushort(__float2bfloat16(v));
+}
+
 // One warp: S = Q K^T over an NT-token tile, online softmax, O += P V.
 //   o  : [HD/8][4] accumulators (m16n8 C layout; [0],[1] = row g, [2],[3] = row g+8)
 //   qa : [HD/16][4] Q A-fragments (pre-loaded)
@@ -157,9 +163,9 @@ template <int HD, int GROUP>
 __global__ void __launch_bounds__(DecodeCfg<HD>::WARPS * 32)
 attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
                    const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ kv_lens, int kv_len_bias,
-                   const int* __restrict__ block_tables, __nv_bfloat16* __restrict__ out, float* __restrict__ part_o,
+                   const int* __restrict__ block_tables, uint16_t* __restrict__ out, float* __restrict__ part_o,
                    float* __restrict__ part_ml, int max_blocks, int n_heads, int n_kv_heads, int n_splits,
-                   int halves_per_split) {
+                   int halves_per_split, int out_f16) {
     using Cfg = DecodeCfg<HD>;
     constexpr int NT = Cfg::NT, W = Cfg::WARPS, S = Cfg::STAGES;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -273,7 +279,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv
         }
         const int head = kvh * GROUP + r;
         if (n_splits == 1) {
-            out[((size_t)seq * n_heads + head) * HD + dim] = __float2bfloat16(val / L);
+            out[((size_t)seq * n_heads + head) * HD + dim] = act16(val / L, out_f16);
         } else {
             const size_t p = ((size_t)seq * n_heads + head) * n_splits + split;
             part_o[p * HD + dim] = val;
@@ -289,7 +295,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv
 template <int HD>
 __global__ void __launch_bounds__(HD)
 attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
-                        __nv_bfloat16* __restrict__ out, int n_splits) {
+                        uint16_t* __restrict__ out, int n_splits, int out_f16) {
     const size_t sh = blockIdx.x;
     const int dim = threadIdx.x;
     float M = -INFINITY;
@@ -302,7 +308,7 @@ attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restric
         L += wgt * part_ml[(sh * n_splits + s) * 2 + 1];
         val += wgt * part_o[(sh * n_splits + s) * HD + dim];
     }
-    out[sh * HD + dim] = __float2bfloat16(val / L);
+    out[sh * HD + dim] = act16(val / L, out_f16);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -323,7 +329,7 @@ __global__ void __launch_bounds__(PrefillCfg<HD>::THREADS)
 attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
                     const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ cu_seqlens,
                     const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
-                    __nv_bfloat16* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads) {
+                    uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
     using Cfg = PrefillCfg<HD>;
     constexpr int NT = Cfg::NT, S = Cfg::STAGES;
     constexpr int TQ = 64 / GROUP;  // query tokens per CTA
@@ -421,16 +427,16 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __n
     l[1] += __shfl_xor_sync(0xffffffffu, l[1], 2);
     const float inv0 = 1.f / l[0], inv1 = 1.f / l[1];
     if (v0) {
-        __nv_bfloat16* op = out + ((size_t)(tok_begin + tl0) * n_heads + hd0) * HD;
+        uint16_t* op = out + ((size_t)(tok_begin + tl0) * n_heads + hd0) * HD;
 #pragma unroll
         for (int d = 0; d < HD / 8; ++d)
-            *reinterpret_cast<uint32_t*>(op + 8 * d + 2 * t) = pack_bf16(o[d][0] * inv0, o[d][1] * inv0);
+            *reinterpret_cast<uint32_t*>(op + 8 * d + 2 * t) = pack_act(o[d][0] * inv0, o[d][1] * inv0, out_f16);
     }
     if (v1) {
-        __nv_bfloat16* op = out + ((size_t)(tok_begin + tl1) * n_heads + hd1) * HD;
+        uint16_t* op = out + ((size_t)(tok_begin + tl1) * n_heads + hd1) * HD;
 #pragma unroll
         for (int d = 0; d < HD / 8; ++d)
-            *reinterpret_cast<uint32_t*>(op + 8 * d + 2 * t) = pack_bf16(o[d][2] * inv1, o[d][3] * inv1);
+            *reinterpret_cast<uint32_t*>(op + 8 * d + 2 * t) = pack_act(o[d][2] * inv1, o[d][3] * inv1, out_f16);
     }
 }
 
@@ -440,7 +446,8 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __n
 template <int HD, int GROUP>
 static int launch_decode(const void* q, int q_stride, const void* kp, const void* vp, const int* kv_lens, int bias,
                          const int* bt, void* out, float* part_o, float* part_ml, int batch, int max_blocks,
-                         int n_heads, int n_kv_heads, int n_splits, int halves_per_split, cudaStream_t stream) {
+                         int n_heads, int n_kv_heads, int n_splits, int halves_per_split, int out_f16,
+                         cudaStream_t stream) {
     using Cfg = DecodeCfg<HD>;
     auto kern = attn_decode_kernel<HD, GROUP>;
     static bool configured[64] = {};
@@ -453,12 +460,12 @@ static int launch_decode(const void* q, int q_stride, const void* kp, const void
     dim3 grid(n_kv_heads, batch, n_splits);
     kern<<<grid, Cfg::WARPS * 32, Cfg::SMEM_BYTES, stream>>>(
         (const __nv_bfloat16*)q, q_stride, (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, kv_lens, bias, bt,
-        (__nv_bfloat16*)out, part_o, part_ml, max_blocks, n_heads, n_kv_heads, n_splits, halves_per_split);
+        (uint16_t*)out, part_o, part_ml, max_blocks, n_heads, n_kv_heads, n_splits, halves_per_split, out_f16);
     count_launch();
     KB_LAUNCH_CHECK();
     if (n_splits > 1) {
-        attn_split_merge_kernel<HD><<<batch * n_heads, HD, 0, stream>>>(part_o, part_ml, (__nv_bfloat16*)out,
-                                                                         n_splits);
+        attn_split_merge_kernel<HD><<<batch * n_heads, HD, 0, stream>>>(part_o, part_ml, (uint16_t*)out, n_splits,
+                                                                         out_f16);
         count_launch();
         KB_LAUNCH_CHECK();
     }
@@ -486,7 +493,7 @@ int attn_decode_pick_splits(int batch, int n_kv_heads, int max_kv_len, int sms) 
 
 int attn_decode(const void* q, int q_stride, const void* kp, const void* vp, const int* kv_lens, int bias,
                 const int* bt, void* out, int batch, int max_blocks, int n_heads, int n_kv_heads, int head_dim,
-                int max_kv_len, void* scratch, size_t scratch_bytes, cudaStream_t stream) {
+                int max_kv_len, void* scratch, size_t scratch_bytes, int out_f16, cudaStream_t stream) {
     KB_CHECK(batch > 0 && max_blocks > 0, "kb_attn_decode: empty batch");
     KB_CHECK(n_kv_heads > 0 && n_heads % n_kv_heads == 0, "kb_attn_decode: n_heads %% n_kv_heads != 0");
     KB_CHECK(batch <= 65535, "kb_attn_decode: batch %d > 65535", batch);
@@ -508,7 +515,7 @@ int attn_decode(const void* q, int q_stride, const void* kp, const void* vp, con
 #define KB_DECODE_CASE(HD_, G_)                                                                                   \
     if (head_dim == HD_ && group == G_)                                                                           \
         return launch_decode<HD_, G_>(q, q_stride, kp, vp, kv_lens, bias, bt, out, part_o, part_ml, batch,        \
-                                      max_blocks, n_heads, n_kv_heads, n_splits, hps, stream);
+                                      max_blocks, n_heads, n_kv_heads, n_splits, hps, out_f16, stream);
     KB_DECODE_CASE(128, 1) KB_DECODE_CASE(128, 2) KB_DECODE_CASE(128, 4) KB_DECODE_CASE(128, 8)
     KB_DECODE_CASE(64, 1) KB_DECODE_CASE(64, 2) KB_DECODE_CASE(64, 4) KB_DECODE_CASE(64, 8)
 #undef KB_DECODE_CASE
@@ -520,7 +527,7 @@ int attn_decode(const void* q, int q_stride, const void* kp, const void* vp, con
 template <int HD, int GROUP>
 static int launch_prefill(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
                           const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads,
-                          int n_kv_heads, cudaStream_t stream) {
+                          int n_kv_heads, int out_f16, cudaStream_t stream) {
     using Cfg = PrefillCfg<HD>;
     auto kern = attn_prefill_kernel<HD, GROUP>;
     static bool configured[64] = {};
@@ -534,7 +541,8 @@ static int launch_prefill(const void* q, int q_stride, const void* kp, const voi
     dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>((const __nv_bfloat16*)q, q_stride,
                                                           (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, cu, ctx,
-                                                          bt, (__nv_bfloat16*)out, max_blocks, n_heads, n_kv_heads);
+                                                          bt, (uint16_t*)out, max_blocks, n_heads, n_kv_heads,
+                                                          out_f16);
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -542,7 +550,7 @@ static int launch_prefill(const void* q, int q_stride, const void* kp, const voi
 
 int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
                  const int* bt, void* out, int n_seqs, int n_tokens, int max_new, int max_blocks, int n_heads,
-                 int n_kv_heads, int head_dim, cudaStream_t stream) {
+                 int n_kv_heads, int head_dim, int out_f16, cudaStream_t stream) {
     KB_CHECK(n_seqs > 0 && n_tokens > 0 && max_new > 0, "kb_attn_prefill: empty batch");
     KB_CHECK(n_kv_heads > 0 && n_heads % n_kv_heads == 0, "kb_attn_prefill: n_heads %% n_kv_heads != 0");
     KB_CHECK(n_seqs <= 65535, "kb_attn_prefill: n_seqs %d > 65535", n_seqs);
@@ -550,7 +558,7 @@ int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, co
 #define KB_PREFILL_CASE(HD_, G_)                                                                               \
     if (head_dim == HD_ && group == G_)                                                                        \
         return launch_prefill<HD_, G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks,    \
-                                       n_heads, n_kv_heads, stream);
+                                       n_heads, n_kv_heads, out_f16, stream);
     KB_PREFILL_CASE(128, 1) KB_PREFILL_CASE(128, 2) KB_PREFILL_CASE(128, 4) KB_PREFILL_CASE(128, 8)
     KB_PREFILL_CASE(64, 1) KB_PREFILL_CASE(64, 2) KB_PREFILL_CASE(64, 4) KB_PREFILL_CASE(64, 8)
 #undef KB_PREFILL_CASE
@@ -568,19 +576,19 @@ extern "C" int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* 
                               const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
                               const int32_t* block_tables, void* out_bf16, int32_t batch, int32_t max_blocks,
                               int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t max_kv_len,
-                              void* scratch, size_t scratch_bytes, kb_stream stream) {
+                              void* scratch, size_t scratch_bytes, int32_t out_f16, kb_stream stream) {
     return kb::attn_decode(q_bf16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out_bf16,
                            batch, max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, scratch, scratch_bytes,
-                           reinterpret_cast<cudaStream_t>(stream));
+                           out_f16, reinterpret_cast<cudaStream_t>(stream));
 }
 
 extern "C" int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
                                const void* v_pool_layer, const int32_t* cu_seqlens, const int32_t* ctx_lens,
                                const int32_t* block_tables, void* out_bf16, int32_t n_seqs, int32_t n_tokens,
                                int32_t max_new, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
-                               int32_t head_dim, kb_stream stream) {
+                               int32_t head_dim, int32_t out_f16, kb_stream stream) {
     return kb::attn_prefill(q_bf16, q_stride, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tables, out_bf16,
-                            n_seqs, n_tokens, max_new, max_blocks, n_heads, n_kv_heads, head_dim,
+                            n_seqs, n_tokens, max_new, max_blocks, n_heads, n_kv_heads, head_dim, out_f16,
                             reinterpret_cast<cudaStream_t>(stream));
 }
 
@@ -644,7 +652,8 @@ extern "C" int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_strid
                                              const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
                                              const int32_t* block_tables, void* out_bf16, int32_t batch,
                                              int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
-                                             int32_t head_dim, int32_t max_kv_len, kb_stream stream) {
+                                             int32_t head_dim, int32_t max_kv_len, int32_t out_f16,
+                                             kb_stream stream) {
     using namespace kb;
     KB_CHECK(batch > 0 && max_blocks > 0 && n_heads > 0 && n_kv_heads > 0,
              "kb_attn_decode_static_scratch: bad batch / head arguments");
@@ -666,5 +675,5 @@ extern "C" int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_strid
     }
     return attn_decode(q_bf16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out_bf16,
                        batch, max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, scratch,
-                       (size_t)KB_STATIC_SCRATCH_BYTES, reinterpret_cast<cudaStream_t>(stream));
+                       (size_t)KB_STATIC_SCRATCH_BYTES, out_f16, reinterpret_cast<cudaStream_t>(stream));
 }

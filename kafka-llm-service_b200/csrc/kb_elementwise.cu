@@ -29,13 +29,13 @@ embed_kernel(const int* __restrict__ tokens, const __nv_bfloat16* __restrict__ e
 }
 
 // ---------------------------------------------------------------------------------------------
-// rmsnorm: y[i,:] = bf16(x[row(i),:] * rsqrt(mean(x^2) + eps) * w)
+// rmsnorm: y[i,:] = act16(x[row(i),:] * rsqrt(mean(x^2) + eps) * w)   (act16 = fp16 or bf16)
 //   row(i) = i, or cu_seqlens[i+1]-1 when last_rows != nullptr (final norm of each sequence's last token)
 //   bytes/row = hidden * (4 + 2) (+ w, L2-resident)
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-rmsnorm_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ y,
-               const int* __restrict__ last_rows, int hidden, float eps) {
+rmsnorm_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w, uint16_t* __restrict__ y,
+               const int* __restrict__ last_rows, int hidden, float eps, int out_f16) {
     const int i = blockIdx.x;
     const int row = last_rows ? last_rows[i + 1] - 1 : i;
     const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * hidden);
@@ -61,8 +61,8 @@ rmsnorm_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w,
         const float2 w0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv.x));
         const float2 w1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv.y));
         uint2 o;
-        o.x = pack_bf16(v.x * inv * w0.x, v.y * inv * w0.y);
-        o.y = pack_bf16(v.z * inv * w1.x, v.w * inv * w1.y);
+        o.x = pack_act(v.x * inv * w0.x, v.y * inv * w0.y, out_f16);
+        o.y = pack_act(v.z * inv * w1.x, v.w * inv * w1.y, out_f16);
         yr[j] = o;
     }
 }
@@ -239,10 +239,10 @@ int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, i
     return KB_OK;
 }
 
-int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps,
+int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps, int out_f16,
             cudaStream_t stream) {
     KB_CHECK(n > 0 && hidden % 4 == 0, "kb_rmsnorm: bad shape n=%d hidden=%d", n, hidden);
-    rmsnorm_kernel<<<n, 256, 0, stream>>>(x, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, last_rows, hidden, eps);
+    rmsnorm_kernel<<<n, 256, 0, stream>>>(x, (const __nv_bfloat16*)w, (uint16_t*)y, last_rows, hidden, eps, out_f16);
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -288,9 +288,9 @@ extern "C" int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x,
                         int32_t vocab, kb_stream stream) {
     return kb::embed(tokens, embed_bf16, x, n, hidden, vocab, reinterpret_cast<cudaStream_t>(stream));
 }
-extern "C" int kb_rmsnorm(const float* x, const void* w_bf16, void* y_bf16, int32_t n, int32_t hidden, float eps,
-                          kb_stream stream) {
-    return kb::rmsnorm(x, w_bf16, y_bf16, nullptr, n, hidden, eps, reinterpret_cast<cudaStream_t>(stream));
+extern "C" int kb_rmsnorm(const float* x, const void* w_bf16, void* y, int32_t n, int32_t hidden, float eps,
+                          int32_t out_f16, kb_stream stream) {
+    return kb::rmsnorm(x, w_bf16, y, nullptr, n, hidden, eps, out_f16, reinterpret_cast<cudaStream_t>(stream));
 }
 extern "C" int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
                               const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,

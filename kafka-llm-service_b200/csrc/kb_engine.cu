@@ -25,7 +25,7 @@ void set_error(const char* fmt, ...) {
 int gemm(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi,
          cudaStream_t stream);
 int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, int vocab, cudaStream_t stream);
-int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps,
+int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps, int out_f16,
             cudaStream_t stream);
 int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* kp, void* vp, int n_seqs,
                 int n_tokens, int max_blocks, int n_heads, int n_kv_heads, int head_dim, float theta,
@@ -34,10 +34,10 @@ int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, in
            cudaStream_t stream);
 int attn_decode(const void* q, int q_stride, const void* kp, const void* vp, const int* kv_lens, int bias,
                 const int* bt, void* out, int batch, int max_blocks, int n_heads, int n_kv_heads, int head_dim,
-                int max_kv_len, void* scratch, size_t scratch_bytes, cudaStream_t stream);
+                int max_kv_len, void* scratch, size_t scratch_bytes, int out_f16, cudaStream_t stream);
 int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
                  const int* bt, void* out, int n_seqs, int n_tokens, int max_new, int max_blocks, int n_heads,
-                 int n_kv_heads, int head_dim, cudaStream_t stream);
+                 int n_kv_heads, int head_dim, int out_f16, cudaStream_t stream);
 size_t attn_decode_scratch_bytes(int batch, int n_heads, int head_dim, int n_splits);
 
 static inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
@@ -164,9 +164,10 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         __nv_bfloat16* kp = e->k_pool + (size_t)L * layer_stride;
         __nv_bfloat16* vp = e->v_pool + (size_t)L * layer_stride;
         mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(w.x, lw.attn_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, stream))) return rc;
+        if ((rc = rmsnorm(w.x, lw.attn_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
         mark(KB_PROF_GEMM_QKV);
-        if ((rc = gemm(w.xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16, stream))) return rc;
+        if ((rc = gemm(w.xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16 | KB_GEMM_F16, stream)))
+            return rc;
         mark(KB_PROF_ROPE_APPEND);
         if ((rc = rope_append(w.qkv, cu_seqlens, ctx_lens, block_tables, kp, vp, n_seqs, n_tokens, max_blocks,
                               c.n_heads, c.n_kv_heads, c.head_dim, c.rope_theta, stream)))
@@ -175,21 +176,24 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         if (decode) {
             rc = attn_decode(w.qkv, qkv_dim, kp, vp, ctx_lens, /*bias=*/1, block_tables, w.attn, n_seqs, max_blocks,
                              c.n_heads, c.n_kv_heads, c.head_dim, max_ctx > 0 ? max_ctx + 1 : 0, w.split,
-                             w.split_bytes, stream);
+                             w.split_bytes, /*out_f16=*/1, stream);
         } else {
             rc = attn_prefill(w.qkv, qkv_dim, kp, vp, cu_seqlens, ctx_lens, block_tables, w.attn, n_seqs, n_tokens,
-                              max_new, max_blocks, c.n_heads, c.n_kv_heads, c.head_dim, stream);
+                              max_new, max_blocks, c.n_heads, c.n_kv_heads, c.head_dim, /*out_f16=*/1, stream);
         }
         if (rc) return rc;
         mark(KB_PROF_GEMM_O);
-        if ((rc = gemm(w.attn, lw.wo, w.x, w.x, n_tokens, c.hidden, qdim, KB_EPI_RESID_F32, stream))) return rc;
+        if ((rc = gemm(w.attn, lw.wo, w.x, w.x, n_tokens, c.hidden, qdim, KB_EPI_RESID_F32 | KB_GEMM_F16, stream)))
+            return rc;
         mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(w.x, lw.mlp_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, stream))) return rc;
+        if ((rc = rmsnorm(w.x, lw.mlp_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
         mark(KB_PROF_GEMM_GATE_UP);
-        if ((rc = gemm(w.xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden, KB_EPI_SWIGLU_BF16, stream)))
+        if ((rc = gemm(w.xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden,
+                       KB_EPI_SWIGLU_F16 | KB_GEMM_F16, stream)))
             return rc;
         mark(KB_PROF_GEMM_DOWN);
-        if ((rc = gemm(w.h, lw.w_down, w.x, w.x, n_tokens, c.hidden, c.ffn, KB_EPI_RESID_F32, stream))) return rc;
+        if ((rc = gemm(w.h, lw.w_down, w.x, w.x, n_tokens, c.hidden, c.ffn, KB_EPI_RESID_F32 | KB_GEMM_F16, stream)))
+            return rc;
     }
     if (logits_out == nullptr && out_tokens == nullptr) {  // KV fill only
         mark(-1);
@@ -197,11 +201,13 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     }
     mark(KB_PROF_RMSNORM);
     // final norm on the last row of every sequence, lm_head, sampling
-    if ((rc = rmsnorm(w.x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, n_seqs, c.hidden, c.rms_eps, stream)))
+    if ((rc = rmsnorm(w.x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, n_seqs, c.hidden, c.rms_eps, 1,
+                      stream)))
         return rc;
     float* lg = logits_out ? logits_out : w.logits;
     mark(KB_PROF_LM_HEAD);
-    if ((rc = gemm(w.xl, e->lm_head, lg, nullptr, n_seqs, c.vocab, c.hidden, KB_EPI_F32, stream))) return rc;
+    if ((rc = gemm(w.xl, e->lm_head, lg, nullptr, n_seqs, c.vocab, c.hidden, KB_EPI_F32 | KB_GEMM_F16, stream)))
+        return rc;
     if (out_tokens) {
         mark(KB_PROF_SAMPLE);
         if ((rc = sample(lg, n_seqs, c.vocab, sampling, out_tokens, advance_ctx ? ctx_lens : nullptr, stream)))

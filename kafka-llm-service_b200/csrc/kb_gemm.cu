@@ -51,11 +51,15 @@ __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(uint32_t saddr) {
     return d;
 }
 
-// kind::f16 instruction descriptor: A=B=bf16 (K-major both), D=fp32, M=128, N=BN.
-__host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n) {
+// kind::f16 instruction descriptor: A and B both bf16 or both fp16 (K-major), D = fp32, M = 128, N = BN.
+// The descriptor has separate A/B format fields, but sm_100a traps (illegal instruction) when they
+// differ — measured, round 1 — so the hot path, which wants fp16 activations for their 10 mantissa bits
+// (error budget), also stores its projection weights as fp16 re-encodings of the bf16
+// values (exact for |w| >= 2^-14).
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n, uint32_t is_bf16) {
     return (1u << 4)                       // D format  fp32
-           | (1u << 7)                     // A format  bf16
-           | (1u << 10)                    // B format  bf16
+           | (is_bf16 << 7)                // A format  0 = fp16, 1 = bf16
+           | (is_bf16 << 10)               // B format  (must equal A's)
            | ((uint32_t)(n >> 3) << 17)    // N / 8
            | ((uint32_t)(m >> 4) << 24);   // M / 16
 }
@@ -94,9 +98,9 @@ __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* 
                 *reinterpret_cast<float4*>(o + j * 4) = v;
             }
         }
-    } else {  // KB_EPI_SWIGLU_BF16: columns (2j, 2j+1) = (gate_j, up_j) -> out[:, j]
+    } else {  // KB_EPI_SWIGLU_{BF16,F16}: columns (2j, 2j+1) = (gate_j, up_j) -> out[:, j]
         const int No = N >> 1;
-        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (size_t)row * No + (col0 >> 1);
+        uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)row * No + (col0 >> 1);
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             if (col0 + j * 16 < N) {
@@ -108,10 +112,17 @@ __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* 
                     h[i] = silu_f(g) * u;
                 }
                 uint4 v;
-                v.x = pack_bf16(h[0], h[1]);
-                v.y = pack_bf16(h[2], h[3]);
-                v.z = pack_bf16(h[4], h[5]);
-                v.w = pack_bf16(h[6], h[7]);
+                if (EPI == KB_EPI_SWIGLU_F16) {
+                    v.x = pack_f16(h[0], h[1]);
+                    v.y = pack_f16(h[2], h[3]);
+                    v.z = pack_f16(h[4], h[5]);
+                    v.w = pack_f16(h[6], h[7]);
+                } else {
+                    v.x = pack_bf16(h[0], h[1]);
+                    v.y = pack_bf16(h[2], h[3]);
+                    v.z = pack_bf16(h[4], h[5]);
+                    v.w = pack_bf16(h[6], h[7]);
+                }
                 *reinterpret_cast<uint4*>(o + j * 8) = v;
             }
         }
@@ -121,7 +132,7 @@ __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, void* out,
-                    const float* resid, int M, int N, int K) {
+                    const float* resid, int M, int N, int K, uint32_t a_is_bf16) {
     using Cfg = GemmCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -187,7 +198,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (elect_one()) {
-            constexpr uint32_t idesc = make_idesc_bf16(GEMM_BM, BN);
+            const uint32_t idesc = make_idesc(GEMM_BM, BN, a_is_bf16);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -320,7 +331,7 @@ static int num_sms() {
 
 template <int BN, int EPI>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M, int N,
-                       int K, cudaStream_t stream) {
+                       int K, uint32_t a_is_bf16, cudaStream_t stream) {
     using Cfg = GemmCfg<BN>;
     static bool configured[64] = {};
     auto kern = gemm_tcgen05_kernel<BN, EPI>;
@@ -332,7 +343,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out
     }
     const int num_tiles = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + BN - 1) / BN);
     int grid = num_tiles < num_sms() ? num_tiles : num_sms();
-    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K);
+    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K, a_is_bf16);
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -340,12 +351,13 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out
 
 template <int BN>
 static int dispatch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M, int N,
-                        int K, int epi, cudaStream_t stream) {
+                        int K, int epi, uint32_t ab, cudaStream_t stream) {
     switch (epi) {
-        case KB_EPI_BF16: return launch_gemm<BN, KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, stream);
-        case KB_EPI_F32: return launch_gemm<BN, KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, stream);
-        case KB_EPI_RESID_F32: return launch_gemm<BN, KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, stream);
-        case KB_EPI_SWIGLU_BF16: return launch_gemm<BN, KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, stream);
+        case KB_EPI_BF16: return launch_gemm<BN, KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_F32: return launch_gemm<BN, KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_RESID_F32: return launch_gemm<BN, KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_SWIGLU_BF16: return launch_gemm<BN, KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_SWIGLU_F16: return launch_gemm<BN, KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
     }
     set_error("kb_gemm: unknown epilogue %d", epi);
     return KB_ERR_INVALID;
@@ -375,12 +387,15 @@ static int pick_bn(int M, int N) {
     return best;
 }
 
-int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi, int tile_n,
-            cudaStream_t stream) {
+int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi_flags,
+            int tile_n, cudaStream_t stream) {
+    const int epi = epi_flags & 0xff;
+    const uint32_t a_is_bf16 = (epi_flags & KB_GEMM_F16) ? 0u : 1u;  // both operands share the format
     KB_CHECK(M > 0 && N > 0 && K > 0, "kb_gemm: bad shape M=%d N=%d K=%d", M, N, K);
     KB_CHECK(K % GEMM_BK == 0, "kb_gemm: K=%d must be a multiple of %d", K, GEMM_BK);
     KB_CHECK(N % 8 == 0, "kb_gemm: N=%d must be a multiple of 8", N);
-    KB_CHECK(epi != KB_EPI_SWIGLU_BF16 || N % 16 == 0, "kb_gemm: SwiGLU needs N %% 16 == 0");
+    KB_CHECK((epi != KB_EPI_SWIGLU_BF16 && epi != KB_EPI_SWIGLU_F16) || N % 16 == 0,
+             "kb_gemm: SwiGLU needs N %% 16 == 0");
     KB_CHECK(epi != KB_EPI_RESID_F32 || resid != nullptr, "kb_gemm: residual epilogue needs resid");
     KB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(out) & 15) == 0,
@@ -393,9 +408,9 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     if (rc) return rc;
     rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)bn, &tmB);
     if (rc) return rc;
-    if (bn == 256) return dispatch_epi<256>(tmA, tmB, out, resid, M, N, K, epi, stream);
-    if (bn == 128) return dispatch_epi<128>(tmA, tmB, out, resid, M, N, K, epi, stream);
-    return dispatch_epi<64>(tmA, tmB, out, resid, M, N, K, epi, stream);
+    if (bn == 256) return dispatch_epi<256>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);
+    if (bn == 128) return dispatch_epi<128>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);
+    return dispatch_epi<64>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);
 }
 
 int gemm(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi,

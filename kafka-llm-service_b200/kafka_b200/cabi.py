@@ -22,7 +22,8 @@ KB_ABI_VERSION = 1
 PROF_CATS = ("embed", "rmsnorm", "gemm_qkv", "rope_append", "attention", "gemm_o", "gemm_gate_up", "gemm_down",
              "lm_head", "sample")
 
-EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_SWIGLU_BF16 = 0, 1, 2, 3
+EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_SWIGLU_BF16, EPI_SWIGLU_F16 = 0, 1, 2, 3, 4
+GEMM_F16 = 0x100  # OR into the epilogue: both operands are fp16 instead of bf16 (formats must match)
 
 _LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libkafka_b200.so"
 
@@ -66,19 +67,19 @@ SIGNATURES = {
     "kb_bind_workspace": (C.c_int, [_vp, _vp, _sz, _i32, _i32]),
     "kb_prefill": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, C.POINTER(Sampling), _vp, _vp, _vp]),
     "kb_decode": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, C.POINTER(Sampling), _vp, _vp, _i32, _vp]),
-    "kb_rmsnorm": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _f, _vp]),
+    "kb_rmsnorm": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _f, _i32, _vp]),
     "kb_embed": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
     "kb_gemm": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "kb_gemm_ex": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "kb_rope_append": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _f, _vp]),
     "kb_attn_decode_scratch_bytes": (_sz, [_i32, _i32, _i32]),
     "kb_attn_decode": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
-                                 _vp, _sz, _vp]),
+                                 _vp, _sz, _i32, _vp]),
     "kb_static_scratch_capacity": (_sz, []),
     "kb_attn_decode_static_scratch": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32,
-                                                _i32, _i32, _vp]),
+                                                _i32, _i32, _i32, _vp]),
     "kb_attn_prefill": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
-                                  _i32, _vp]),
+                                  _i32, _i32, _vp]),
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
     "kb_profile_begin": (C.c_int, [_vp]),
     "kb_profile_end": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
@@ -146,11 +147,11 @@ def _stream() -> int:
 # ------------------------------------------------------------------------------------------------
 # thin tensor-level wrappers of the per-kernel entry points (used by tests, smoke and the engine)
 # ------------------------------------------------------------------------------------------------
-def rmsnorm(x, w, eps: float):
+def rmsnorm(x, w, eps: float, out_f16: bool = False):
     import torch
     n, hidden = x.shape
-    y = torch.empty((n, hidden), dtype=torch.bfloat16, device=x.device)
-    check(load().kb_rmsnorm(_ptr(x), _ptr(w), _ptr(y), n, hidden, eps, _stream()), "kb_rmsnorm")
+    y = torch.empty((n, hidden), dtype=torch.float16 if out_f16 else torch.bfloat16, device=x.device)
+    check(load().kb_rmsnorm(_ptr(x), _ptr(w), _ptr(y), n, hidden, eps, int(out_f16), _stream()), "kb_rmsnorm")
     return y
 
 
@@ -169,11 +170,18 @@ def gemm(a, w, epilogue: int = EPI_BF16, resid=None, out=None, tile_n: int = 0):
     M, K = a.shape
     N, K2 = w.shape
     assert K == K2
+    if a.dtype != w.dtype:
+        raise KafkaB200Error(f"kb_gemm: operand formats must match (A {a.dtype}, W {w.dtype})")
+    if a.dtype == torch.float16:
+        epilogue |= GEMM_F16
     if out is None:
-        if epilogue == EPI_BF16:
+        epi = epilogue & 0xFF
+        if epi == EPI_BF16:
             out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
-        elif epilogue == EPI_SWIGLU_BF16:
+        elif epi == EPI_SWIGLU_BF16:
             out = torch.empty((M, N // 2), dtype=torch.bfloat16, device=a.device)
+        elif epi == EPI_SWIGLU_F16:
+            out = torch.empty((M, N // 2), dtype=torch.float16, device=a.device)
         else:
             out = torch.empty((M, N), dtype=torch.float32, device=a.device)
     check(load().kb_gemm_ex(_ptr(a), _ptr(w), _ptr(out), _ptr(resid), M, N, K, epilogue, tile_n, _stream()),
@@ -191,14 +199,15 @@ def rope_append(qkv, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_la
 
 
 def attn_decode(q, k_pool_layer, v_pool_layer, kv_lens, block_tables, n_heads, n_kv_heads, head_dim,
-                kv_len_bias: int = 0, max_kv_len: int = 0, scratch=None):
+                kv_len_bias: int = 0, max_kv_len: int = 0, scratch=None, out_f16: bool = False):
     import torch
     batch, max_blocks = block_tables.shape
-    out = torch.empty((batch, n_heads * head_dim), dtype=torch.bfloat16, device=q.device)
+    out = torch.empty((batch, n_heads * head_dim), dtype=torch.float16 if out_f16 else torch.bfloat16,
+                      device=q.device)
     sb = 0 if scratch is None else scratch.numel() * scratch.element_size()
     check(load().kb_attn_decode(_ptr(q), q.stride(0), _ptr(k_pool_layer), _ptr(v_pool_layer), _ptr(kv_lens),
                                 kv_len_bias, _ptr(block_tables), _ptr(out), batch, max_blocks, n_heads, n_kv_heads,
-                                head_dim, max_kv_len, _ptr(scratch), sb, _stream()), "kb_attn_decode")
+                                head_dim, max_kv_len, _ptr(scratch), sb, int(out_f16), _stream()), "kb_attn_decode")
     return out
 
 
@@ -213,7 +222,8 @@ def attn_decode_static_scratch(q, k_pool_layer, v_pool_layer, kv_lens, block_tab
         out = torch.empty((batch, n_heads * head_dim), dtype=torch.bfloat16, device=q.device)
     check(load().kb_attn_decode_static_scratch(_ptr(q), q.stride(0), _ptr(k_pool_layer), _ptr(v_pool_layer),
                                                _ptr(kv_lens), kv_len_bias, _ptr(block_tables), _ptr(out), batch,
-                                               max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, _stream()),
+                                               max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len,
+                                               1 if out.dtype == torch.float16 else 0, _stream()),
           "kb_attn_decode_static_scratch")
     return out
 
@@ -223,14 +233,16 @@ def attn_decode_scratch_bytes(batch: int, n_heads: int, head_dim: int) -> int:
 
 
 def attn_prefill(q, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tables, max_new, n_heads, n_kv_heads,
-                 head_dim):
+                 head_dim, out_f16: bool = False):
     import torch
     n_tokens = q.shape[0]
     n_seqs, max_blocks = block_tables.shape
-    out = torch.empty((n_tokens, n_heads * head_dim), dtype=torch.bfloat16, device=q.device)
+    out = torch.empty((n_tokens, n_heads * head_dim), dtype=torch.float16 if out_f16 else torch.bfloat16,
+                      device=q.device)
     check(load().kb_attn_prefill(_ptr(q), q.stride(0), _ptr(k_pool_layer), _ptr(v_pool_layer), _ptr(cu_seqlens),
                                  _ptr(ctx_lens), _ptr(block_tables), _ptr(out), n_seqs, n_tokens, max_new,
-                                 max_blocks, n_heads, n_kv_heads, head_dim, _stream()), "kb_attn_prefill")
+                                 max_blocks, n_heads, n_kv_heads, head_dim, int(out_f16), _stream()),
+          "kb_attn_prefill")
     return out
 
 

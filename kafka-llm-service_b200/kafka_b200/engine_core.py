@@ -33,9 +33,11 @@ class EngineCore:
         torch.cuda.set_device(self.device)
 
         self.weights = fused_weights  # keep the tensors alive: the library only borrows pointers
+        from .weights import GEMM_WEIGHT_DTYPE, GEMM_WEIGHT_NAMES
         for name, t in fused_weights.items():
-            if t.device != self.device or t.dtype != torch.bfloat16 or not t.is_contiguous():
-                raise KafkaB200Error(f"weight {name} must be a contiguous bf16 tensor on {self.device}")
+            want = GEMM_WEIGHT_DTYPE if name.split(".")[-1] in GEMM_WEIGHT_NAMES else torch.bfloat16
+            if t.device != self.device or t.dtype != want or not t.is_contiguous():
+                raise KafkaB200Error(f"weight {name} must be a contiguous {want} tensor on {self.device}")
 
         self._cfg_c = cabi.ModelCfg(cfg.hidden, cfg.n_layers, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn,
                                     cfg.vocab, cfg.max_pos, cfg.rope_theta, cfg.rms_eps)

@@ -30,6 +30,8 @@ from .model_config import LlamaConfig
 
 
 MARGIN_TARGET_LOGIT = 4.5
+GEMM_WEIGHT_DTYPE = torch.float16   # projection weights as the engine binds them (see fuse_for_engine)
+GEMM_WEIGHT_NAMES = ("wqkv", "wo", "w_gate_up", "w_down", "lm_head")
 
 
 def _seed_for(seed: int, name: str) -> int:
@@ -105,19 +107,25 @@ def fuse_for_engine(cfg: LlamaConfig, w: Dict[str, torch.Tensor], device) -> Dic
     """Lay the canonical tensors out the way include/kafka_b200.h wants them (bf16, contiguous):
 
     l{i}.wqkv = cat(wq, wk, wv) rows;  l{i}.w_gate_up = rows interleaved (2j = gate_j, 2j+1 = up_j).
+
+    The five GEMM operands are re-encoded bf16 -> fp16 (KB_GEMM_F16): every bf16 value with
+    2^-14 <= |w| < 65504 is exactly representable in fp16, smaller ones fall on fp16's subnormal grid
+    (absolute error <= 3e-8), so the engine multiplies the same numbers the fp32 oracle does.
     """
     out: Dict[str, torch.Tensor] = {}
-    for k in ("embed", "final_norm", "lm_head"):
+    f16 = GEMM_WEIGHT_DTYPE
+    for k in ("embed", "final_norm"):
         out[k] = w[k].to(device=device, dtype=torch.bfloat16).contiguous()
+    out["lm_head"] = w["lm_head"].to(device=device, dtype=f16).contiguous()
     for i in range(cfg.n_layers):
         p = f"l{i}."
         out[p + "attn_norm"] = w[p + "attn_norm"].to(device).contiguous()
         out[p + "mlp_norm"] = w[p + "mlp_norm"].to(device).contiguous()
-        out[p + "wqkv"] = torch.cat([w[p + "wq"], w[p + "wk"], w[p + "wv"]], dim=0).to(device).contiguous()
-        out[p + "wo"] = w[p + "wo"].to(device).contiguous()
+        out[p + "wqkv"] = torch.cat([w[p + "wq"], w[p + "wk"], w[p + "wv"]], dim=0).to(device, f16).contiguous()
+        out[p + "wo"] = w[p + "wo"].to(device, f16).contiguous()
         gu = torch.stack([w[p + "w_gate"], w[p + "w_up"]], dim=1).reshape(2 * cfg.ffn, cfg.hidden)
-        out[p + "w_gate_up"] = gu.to(device).contiguous()
-        out[p + "w_down"] = w[p + "w_down"].to(device).contiguous()
+        out[p + "w_gate_up"] = gu.to(device, f16).contiguous()
+        out[p + "w_down"] = w[p + "w_down"].to(device, f16).contiguous()
     return out
 
 
@@ -129,13 +137,14 @@ def generate_fused_on_device(cfg: LlamaConfig, seed: int, device) -> Dict[str, t
     H, F = cfg.hidden, cfg.ffn
     out["embed"] = _randn((cfg.vocab, H), seed, "embed", 1.0, dev)
     out["final_norm"] = _randn((H,), seed, "final_norm", 0.1, dev, mean=1.0)
-    out["lm_head"] = _randn((cfg.vocab, H), seed, "lm_head", 1.0 / (H ** 0.5), dev)
+    f16 = GEMM_WEIGHT_DTYPE
+    out["lm_head"] = _randn((cfg.vocab, H), seed, "lm_head", 1.0 / (H ** 0.5), dev).to(f16)
     for i in range(cfg.n_layers):
         p = f"l{i}."
         out[p + "attn_norm"] = _randn((H,), seed, p + "attn_norm", 0.1, dev, mean=1.0)
         out[p + "mlp_norm"] = _randn((H,), seed, p + "mlp_norm", 0.1, dev, mean=1.0)
-        out[p + "wqkv"] = _randn((cfg.qkv_dim, H), seed, p + "wqkv", 0.02, dev)
-        out[p + "wo"] = _randn((H, cfg.q_dim), seed, p + "wo", 0.02, dev)
-        out[p + "w_gate_up"] = _randn((2 * F, H), seed, p + "w_gate_up", 0.02, dev)
-        out[p + "w_down"] = _randn((H, F), seed, p + "w_down", 0.02, dev)
+        out[p + "wqkv"] = _randn((cfg.qkv_dim, H), seed, p + "wqkv", 0.02, dev).to(f16)
+        out[p + "wo"] = _randn((H, cfg.q_dim), seed, p + "wo", 0.02, dev).to(f16)
+        out[p + "w_gate_up"] = _randn((2 * F, H), seed, p + "w_gate_up", 0.02, dev).to(f16)
+        out[p + "w_down"] = _randn((H, F), seed, p + "w_down", 0.02, dev).to(f16)
     return out

@@ -102,6 +102,60 @@ def test_gemm_swiglu(kb, cuda, M, F, K, tile_n):
     torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
 
 
+@pytest.mark.parametrize("tile_n", [64, 128, 256])
+def test_gemm_fp16_operands(kb, cuda, tile_n):
+    """The hot path's operand format: A (activations) and W (bf16 values re-encoded as fp16) both fp16,
+    fp32 accumulate. The fp32 epilogue must match an fp32 matmul of the same values to
+    accumulation-order error only (rtol = atol = 2e-3 as for the bf16 case)."""
+    g = torch.Generator(device="cpu").manual_seed(99 + tile_n)
+    M, N, K = 300, 1000, 320
+    a = torch.randn(M, K, generator=g).half().to(cuda)
+    w = _bf16(torch.randn(N, K, generator=g) / math.sqrt(K)).half().to(cuda)
+    assert torch.equal(w.float(), w.float().bfloat16().float())      # still exactly the bf16 values
+    ref = a.float() @ w.float().T
+    torch.testing.assert_close(kb.gemm(a, w, kb.EPI_F32, tile_n=tile_n), ref, rtol=2e-3, atol=2e-3)
+    with pytest.raises(kb.KafkaB200Error, match="formats must match"):
+        kb.gemm(a, w.bfloat16())
+    torch.testing.assert_close(kb.gemm(a, w, kb.EPI_BF16, tile_n=tile_n).float(), ref, rtol=2e-2, atol=2e-2)
+    F = 256
+    wg = _bf16(torch.randn(F, K, generator=g) / math.sqrt(K)).half().to(cuda)
+    wu = _bf16(torch.randn(F, K, generator=g) / math.sqrt(K)).half().to(cuda)
+    wi = torch.stack([wg, wu], dim=1).reshape(2 * F, K).contiguous()
+    h = kb.gemm(a, wi, kb.EPI_SWIGLU_F16, tile_n=tile_n)
+    assert h.dtype == torch.float16
+    want = torch.nn.functional.silu(a.float() @ wg.float().T) * (a.float() @ wu.float().T)
+    # fp16 output: 2^-11 relative rounding -> 2e-3
+    torch.testing.assert_close(h.float(), want, rtol=2e-3, atol=2e-3)
+
+
+def test_fp16_activation_outputs_of_norm_and_attention(kb, cuda):
+    from kafka_b200 import kv_layout
+    g = torch.Generator(device="cpu").manual_seed(5)
+    x = (torch.randn(9, 2048, generator=g) * 3).to(cuda)
+    w = _bf16(1 + 0.1 * torch.randn(2048, generator=g)).to(cuda)
+    y = kb.rmsnorm(x, w, 1e-5, out_f16=True)
+    ref = x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-5) * w.float()
+    assert y.dtype == torch.float16
+    torch.testing.assert_close(y.float(), ref, rtol=2e-3, atol=2e-3)
+    # attention: the fp16 output must equal the bf16 output up to the output rounding
+    hd, n_heads, n_kv = 128, 8, 2
+    kp, vp = _alloc_pool(8, n_kv, hd, cuda, 6)
+    bt = torch.arange(8, dtype=torch.int32, device=cuda).view(2, 4)
+    q = _bf16(torch.randn(2, n_heads * hd, generator=g)).to(cuda)
+    lens = torch.tensor([200, 77], dtype=torch.int32, device=cuda)
+    a16 = kb.attn_decode(q, kp, vp, lens, bt, n_heads, n_kv, hd, out_f16=True)
+    ab = kb.attn_decode(q, kp, vp, lens, bt, n_heads, n_kv, hd)
+    assert a16.dtype == torch.float16
+    torch.testing.assert_close(a16.float(), ab.float(), rtol=1e-2, atol=1e-2)
+    cu = torch.tensor([0, 5, 12], dtype=torch.int32, device=cuda)
+    ctx = torch.tensor([100, 3], dtype=torch.int32, device=cuda)
+    qq = _bf16(torch.randn(12, n_heads * hd, generator=g)).to(cuda)
+    p16 = kb.attn_prefill(qq, kp, vp, cu, ctx, bt, 7, n_heads, n_kv, hd, out_f16=True)
+    pb = kb.attn_prefill(qq, kp, vp, cu, ctx, bt, 7, n_heads, n_kv, hd)
+    torch.testing.assert_close(p16.float(), pb.float(), rtol=1e-2, atol=1e-2)
+    del kv_layout
+
+
 def test_gemm_rejects_bad_shapes(kb, cuda):
     a = torch.zeros(4, 100, dtype=torch.bfloat16, device=cuda)
     w = torch.zeros(8, 100, dtype=torch.bfloat16, device=cuda)
