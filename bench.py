@@ -56,6 +56,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-provider", action="store_true", help="skip the provider-level (plugin API) turn")
+    ap.add_argument("--gen-tokens", type=int, default=128, help="new tokens per turn in the provider-level leg")
     return ap.parse_args()
 
 
@@ -165,6 +167,102 @@ def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1):
 
 
 # ------------------------------------------------------------------------------------------------
+def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen_tokens: int, seed: int):
+    """The call a user makes: B200LLMProvider.stream_completion for `n_threads` concurrent threads.
+
+    Untimed set-up: every thread's ~`history`-token conversation is prefilled once through the provider
+    (a first completion of 1 token), which leaves its KV resident. Timed: one turn of every thread —
+    the conversation re-sent in full plus a new `user_tokens`-char user message, `gen_tokens` new tokens,
+    streamed chunk by chunk. The engine finds the resident prefix, prefills only the new messages and
+    decodes with continuous batching. Wall-clock around asyncio.gather; TTFT = first content chunk."""
+    import asyncio
+    import random
+    import statistics as st
+    from kafka_b200.engine import Engine
+    from kafka_b200.gpu_stepper import GpuStepper
+    from kafka_b200.llm import Message
+    from kafka_b200.provider import B200LLMProvider
+    from kafka_b200.tokenizer import ByteTokenizer
+
+    tok = ByteTokenizer(cfg.vocab)
+    stepper = GpuStepper(core, tok, generable_only=True)
+    stepper.banned_token = tok.eot_id                   # EOS masked: every turn generates gen_tokens tokens
+    stepper.close = lambda: None                        # the core outlives this leg
+    engine = Engine(stepper, max_prefill_tokens=core.max_tokens)
+    provider = B200LLMProvider(engine, tok, model=cfg.name, default_temperature=0.0)
+
+    def text(rnd, n):
+        return "".join(chr(rnd.randrange(32, 127)) for _ in range(n))
+
+    def make_history(i):
+        rnd = random.Random(seed * 100003 + i)
+        msgs = [Message(role="system", content="You are a helpful assistant.")]
+        role = "user"
+        while True:
+            msgs.append(Message(role=role, content=text(rnd, 180)))
+            n = len(provider.render(msgs, None))
+            if n >= history - 220 and role == "user":
+                break
+            role = "assistant" if role == "user" else "user"
+        msgs.append(Message(role="assistant", content=text(rnd, 60)))
+        short = history - len(provider.render(msgs + [Message(role="user", content="")], None))
+        msgs.append(Message(role="user", content=text(rnd, max(1, short))))
+        return msgs
+
+    async def run():
+        hist = [make_history(i) for i in range(n_threads)]
+        n_hist = [len(provider.render(h, None)) for h in hist]
+        t0 = time.perf_counter()
+        first = await asyncio.gather(*[provider.completion(h, temperature=0.0, max_tokens=1, thread_id=f"bench-{i:04d}")
+                                       for i, h in enumerate(hist)])
+        setup_s = time.perf_counter() - t0
+        turns = []
+        for i, (h, r) in enumerate(zip(hist, first)):
+            rnd = random.Random(seed * 7 + i)
+            turns.append(h + [r.to_message(), Message(role="user", content=text(rnd, user_tokens))])
+        stats0 = engine.stats()
+        h2d0, d2h0, l0 = stepper.h2d_bytes, stepper.d2h_bytes, __import__("kafka_b200.cabi", fromlist=["x"]).launch_count()
+
+        async def one(i, msgs):
+            t_call = time.perf_counter()
+            ttft, n = None, 0
+            async for ch in provider.stream_completion(msgs, temperature=0.0, max_tokens=gen_tokens,
+                                                       thread_id=f"bench-{i:04d}"):
+                if ch.content:
+                    if ttft is None:
+                        ttft = time.perf_counter() - t_call
+                    n += len(ch.content)
+            return ttft, n, time.perf_counter() - t_call
+
+        t0 = time.perf_counter()
+        res = await asyncio.gather(*[one(i, m) for i, m in enumerate(turns)])
+        wall = time.perf_counter() - t0
+        s1 = engine.stats()
+        steps = max(1, s1["decode_steps"] - stats0["decode_steps"])
+        new_tok = sum(n for _, n, _ in res)
+        cached = s1["cached_tokens"] - stats0["cached_tokens"]
+        prompt = s1["prompt_tokens"] - stats0["prompt_tokens"]
+        ttfts = sorted(t for t, _, _ in res if t is not None)
+        from kafka_b200 import cabi as _c
+        return {
+            "value": new_tok / wall, "unit": UNIT, "wall_s": wall, "new_tokens": new_tok,
+            "h2d_bytes_per_step": (stepper.h2d_bytes - h2d0) / steps, "d2h_bytes_per_step": (stepper.d2h_bytes - d2h0) / steps,
+            "decode_steps": steps, "gpu_launches": _c.launch_count() - l0,
+            "ttft_p50_ms": 1e3 * st.median(ttfts), "ttft_p99_ms": 1e3 * ttfts[int(0.99 * (len(ttfts) - 1))],
+            "history_tokens_mean": sum(n_hist) / len(n_hist), "cached_fraction_of_prompt": cached / max(1, prompt),
+            "prefilled_new_tokens": prompt - cached, "setup_prefill_s": setup_s,
+            "engine_prefill_s": s1["prefill_s"] - stats0["prefill_s"], "engine_decode_s": s1["decode_s"] - stats0["decode_s"],
+            "api": "B200LLMProvider.stream_completion (LLMProvider plugin API), one coroutine per thread, "
+                   "pinned H2D of token ids / block tables and D2H of sampled ids every step",
+        }
+
+    try:
+        return asyncio.run(run())
+    finally:
+        engine.shutdown()
+
+
+# ------------------------------------------------------------------------------------------------
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -204,6 +302,8 @@ def run_b200(args, rank, world, local_rank):
     K, W = args.steps, max(args.warmup, 3)
     passes = 1 + (0 if args.no_profile else 1) + (0 if args.no_e2e else 1)
     tokens_per_thread = args.history + args.user_tokens + W * passes + K * passes + 8
+    if not args.no_provider:  # the provider-level turn: history + re-templated turn (~90 tokens) + gen_tokens
+        tokens_per_thread = max(tokens_per_thread, args.history + 112 + args.gen_tokens)
     bpt = (tokens_per_thread + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
     B = args.threads
 
@@ -328,6 +428,9 @@ def run_b200(args, rank, world, local_rank):
         roofline = {
             "bound": "hbm", "kernel": "attn_decode_kernel<128,4>", "achieved": achieved, "peak": hbm_peak,
             "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_kind": peak_kind,
+            "traffic_note": "ncu --set full cannot replay with the 140 GB pool resident; at 128 threads the same kernel "
+                            "moved 1.131 GB of DRAM traffic per launch for 1.110 GB algorithmic (x1.019, "
+                            "profiles/r01_ncu_attn_decode_full_metrics.csv)",
             "bytes_per_launch": attn_bytes, "us_per_launch": attn_ms / attn_n * 1e3,
             "share_of_step": attn_ms / sum(v[0] for v in prof.values()),
             "step": {"algorithmic_bytes": avg_step_bytes, "achieved": step_gbs, "frac": step_gbs / hbm_peak},
@@ -347,6 +450,20 @@ def run_b200(args, rank, world, local_rank):
                "d2h_bytes_per_step": B * 4, "ms_per_step": ms_e2e / K,
                "api": "kb_decode via ctypes, pinned host token buffers, per-step stream sync"}
 
+    # ---- e2e through the plugin API (the call a user makes) ----------------------------------------
+    e2e_cabi = e2e
+    if not args.no_provider:
+        barrier()
+        pt = provider_turn(eng, cfg, B, args.history, U, args.gen_tokens, seed=rank)
+        wall = pt["wall_s"]
+        if world > 1:
+            t = torch.tensor([wall], device=dev)
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            wall = float(t.item())
+        pt["value"] = world * pt["new_tokens"] / wall
+        pt["ms_per_step"] = 1e3 * wall / pt["decode_steps"]
+        e2e = pt
+
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cb = cpu_baseline(cfg, args.cpu_threads, ctx0, args.cpu_steps)
@@ -355,7 +472,8 @@ def run_b200(args, rank, world, local_rank):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic",
+            "dtype": "16-bit float operands (bf16 KV cache / q,k,v / attention; fp16 projection operands holding "
+                     "the bf16 weight values), fp32 accumulate and residual", "data": "synthetic",
             "config": {
                 "workload": f"{cfg.name} bf16 decode, {B} resident threads/GPU x {args.history}-token history + "
                             f"{U}-token turn (BASELINE configs[2], thread-sharded: 4096 threads at 8 GPUs)",
@@ -365,7 +483,8 @@ def run_b200(args, rank, world, local_rank):
                 "parallelism": f"replica per GPU, thread-sharded x{world}, no collective",
                 "resident_note": resident_note,
             },
-            "clocks": clocks, "gpu_launches": gpu_launches, "e2e": e2e, "roofline": roofline, "kernels": kernels,
+            "clocks": clocks, "gpu_launches": gpu_launches, "e2e": e2e, "e2e_cabi": e2e_cabi, "roofline": roofline,
+            "kernels": kernels,
             "cpu_baseline": cb,
             "prefill": {"ms": prefill_ms, "tokens": B * U, "tflops": prefill_flops / (prefill_ms / 1e3) / 1e12,
                         "frac_of_tensor_peak": prefill_flops / (prefill_ms / 1e3) / 1e12 / tf_peak,

@@ -87,13 +87,15 @@ class GpuStepper(Stepper):
         self.step_no = 0
         lo, hi, nl, eot = tokenizer.generable_range()
         self.cand = (lo, hi, nl, eot) if generable_only else (0, 0, -1, -1)
+        self.banned_token = -1   # e.g. the EOS id while benchmarking fixed-length turns
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
     def _sampling(self, st: _Staging):
         self.step_no += 1
         lo, hi, ea, eb = self.cand
-        return self.cabi.make_sampling(temperature=0.0, seed=0, step=self.step_no, banned_token=-1, allowed_lo=lo,
+        return self.cabi.make_sampling(temperature=0.0, seed=0, step=self.step_no, banned_token=self.banned_token,
+                                       allowed_lo=lo,
                                        allowed_hi=hi, extra_a=ea, extra_b=eb, seq_temperature=st.d_temp,
                                        seq_seed=st.d_seed)
 
