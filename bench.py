@@ -197,14 +197,10 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
     def make_history(i):
         rnd = random.Random(seed * 100003 + i)
         msgs = [Message(role="system", content="You are a helpful assistant.")]
-        role = "user"
-        while True:
-            msgs.append(Message(role=role, content=text(rnd, 180)))
-            n = len(provider.render(msgs, None))
-            if n >= history - 220 and role == "user":
-                break
-            role = "assistant" if role == "user" else "user"
-        msgs.append(Message(role="assistant", content=text(rnd, 60)))
+        while len(provider.render(msgs, None)) < history - 700:      # ~200 tokens per rendered message
+            msgs.append(Message(role="user", content=text(rnd, 180)))
+            msgs.append(Message(role="assistant", content=text(rnd, 180)))
+        # the last user message is sized so that the rendered prompt is exactly `history` tokens
         short = history - len(provider.render(msgs + [Message(role="user", content="")], None))
         msgs.append(Message(role="user", content=text(rnd, max(1, short))))
         return msgs
@@ -303,7 +299,7 @@ def run_b200(args, rank, world, local_rank):
     passes = 1 + (0 if args.no_profile else 1) + (0 if args.no_e2e else 1)
     tokens_per_thread = args.history + args.user_tokens + W * passes + K * passes + 8
     if not args.no_provider:  # the provider-level turn: history + re-templated turn (~90 tokens) + gen_tokens
-        tokens_per_thread = max(tokens_per_thread, args.history + 112 + args.gen_tokens)
+        tokens_per_thread = max(tokens_per_thread, args.history + 192 + args.gen_tokens)
     bpt = (tokens_per_thread + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
     B = args.threads
 

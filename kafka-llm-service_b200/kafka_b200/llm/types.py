@@ -87,3 +87,21 @@ class LLMProviderError(Exception):
         if self.status_code:
             parts.append(f"(status: {self.status_code})")
         return " ".join(parts)
+
+
+_osa = object.__setattr__
+
+
+def content_chunk(content: str, model: Optional[str], id: Optional[str]) -> StreamChunk:
+    """StreamChunk(content=..., model=..., id=...) without pydantic's validation machinery.
+
+    One chunk is built per generated token per stream (tens of thousands per second); the values are
+    produced right here and need no validation. Equivalent to ``StreamChunk.model_construct`` with every
+    field given (tests/test_host_path.py checks equality with the validated constructor)."""
+    m = StreamChunk.__new__(StreamChunk)
+    _osa(m, "__dict__", {"content": content, "role": None, "tool_calls": None, "finish_reason": None,
+                         "model": model, "id": id})
+    _osa(m, "__pydantic_fields_set__", {"content", "model", "id"})
+    _osa(m, "__pydantic_extra__", None)
+    _osa(m, "__pydantic_private__", None)
+    return m

@@ -17,16 +17,51 @@ messages are prefilled.
 from __future__ import annotations
 
 import asyncio
+import collections
 import uuid
+import weakref
 from typing import Any, AsyncGenerator, Dict, List, Optional
 
 from .llm.base import LLMProvider
-from .llm.types import CompletionResponse, LLMProviderError, Message, StreamChunk
+from .llm.types import CompletionResponse, LLMProviderError, Message, StreamChunk, content_chunk
 from .scheduler import ContextLengthError, SamplingParams
 from .template import ChatTemplate
 from .tokenizer import ByteTokenizer
 
 PROVIDER_NAME = "B200"
+
+
+class _LoopMailbox:
+    """Engine thread -> event loop hand-off, batched: a decode step produces one event for each of
+    hundreds of streams; instead of one `call_soon_threadsafe` (a lock and a wake-up write) per event,
+    events are appended to a deque and the loop is woken once per batch."""
+    _by_loop: "weakref.WeakKeyDictionary" = weakref.WeakKeyDictionary()
+
+    def __init__(self, loop: asyncio.AbstractEventLoop):
+        self.loop = loop
+        self.items: "collections.deque" = collections.deque()
+        self.scheduled = False
+
+    @classmethod
+    def for_running_loop(cls) -> "_LoopMailbox":
+        loop = asyncio.get_running_loop()
+        mb = cls._by_loop.get(loop)
+        if mb is None:
+            mb = cls._by_loop[loop] = cls(loop)
+        return mb
+
+    def post(self, queue: "asyncio.Queue", ev) -> None:        # any thread
+        self.items.append((queue, ev))
+        if not self.scheduled:                                  # a redundant wake-up is harmless
+            self.scheduled = True
+            self.loop.call_soon_threadsafe(self._drain)
+
+    def _drain(self) -> None:                                   # event-loop thread
+        self.scheduled = False
+        items = self.items
+        while items:
+            queue, ev = items.popleft()
+            queue.put_nowait(ev)
 
 
 class B200LLMProvider(LLMProvider):
@@ -70,11 +105,11 @@ class B200LLMProvider(LLMProvider):
             prompt = self.render(validated, tools)
             temp = self.default_temperature if temperature is None else float(temperature)
             limit = max_tokens if max_tokens is not None else (self.default_max_tokens or 512)
-            loop = asyncio.get_running_loop()
             events: "asyncio.Queue" = asyncio.Queue()
+            mailbox = _LoopMailbox.for_running_loop()
 
-            def on_event(ev, _loop=loop, _q=events):
-                _loop.call_soon_threadsafe(_q.put_nowait, ev)
+            def on_event(ev, _post=mailbox.post, _q=events):
+                _post(_q, ev)
 
             req = self.engine.submit(prompt, SamplingParams(temperature=temp, seed=seed, max_tokens=int(limit)),
                                      on_event, thread_hint=thread_id)
@@ -105,7 +140,7 @@ class B200LLMProvider(LLMProvider):
                         return
                     upto = len(text) - hold            # keep back what could still grow into a stop string
                     if upto > emitted:
-                        yield StreamChunk(content=text[emitted:upto], model=model, id=completion_id)
+                        yield content_chunk(text[emitted:upto], model, completion_id)   # per-token hot spot
                         emitted = upto
                 elif kind == "finish":
                     text += decoder.flush()

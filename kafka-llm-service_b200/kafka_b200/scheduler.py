@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import hashlib
 import itertools
+from array import array
 import struct
 import time
 from dataclasses import dataclass, field
@@ -84,9 +85,14 @@ def _chain_hashes(tokens: Sequence[int], prev: Optional[List[int]] = None, start
     """Rolling hash per full block: h_k = H(h_{k-1} || block_k)."""
     out = list(prev[:start_block]) if prev else []
     h = out[-1] if out else 0
-    for k in range(start_block, len(tokens) // BLOCK_TOKENS):
-        blk = tokens[k * BLOCK_TOKENS:(k + 1) * BLOCK_TOKENS]
-        h = stable_hash64(struct.pack(f"<Q{BLOCK_TOKENS}i", h, *blk))
+    n_full = len(tokens) // BLOCK_TOKENS
+    if n_full <= start_block:
+        return out
+    raw = array("i", tokens[start_block * BLOCK_TOKENS: n_full * BLOCK_TOKENS]).tobytes()  # one conversion
+    step = 4 * BLOCK_TOKENS
+    for k in range(n_full - start_block):
+        h = int.from_bytes(hashlib.blake2b(h.to_bytes(8, "little") + raw[k * step:(k + 1) * step],
+                                           digest_size=8).digest(), "little")
         out.append(h)
     return out
 
@@ -128,6 +134,8 @@ class PrefixIndex:
     def _lcp(a: Sequence[int], b: Sequence[int], start: int = 0) -> int:
         n = min(len(a), len(b))
         i = start
+        while i + 256 <= n and a[i:i + 256] == b[i:i + 256]:   # slice compares run in C
+            i += 256
         while i < n and a[i] == b[i]:
             i += 1
         return i

@@ -36,6 +36,9 @@ def test_types_behave_like_the_reference():
     c = StreamChunk()
     assert c.content is None and c.delta == "" and not c.is_final
     assert StreamChunk(finish_reason="stop").is_final
+    from kafka_b200.llm.types import content_chunk
+    fast, slow = content_chunk("tok", "m", "chatcmpl-1"), StreamChunk(content="tok", model="m", id="chatcmpl-1")
+    assert fast == slow and fast.model_dump_json() == slow.model_dump_json() and not fast.is_final
     r = CompletionResponse(content="hi", tool_calls=None)
     assert r.role == "assistant" and r.to_message().to_dict() == {"role": "assistant", "content": "hi"}
     assert str(LLMProviderError("boom", status_code=400, provider="B200")) == "[B200] boom (status: 400)"
