@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-provider", action="store_true", help="skip the provider-level (plugin API) turn")
     ap.add_argument("--gen-tokens", type=int, default=128, help="new tokens per turn in the provider-level leg")
+    ap.add_argument("--no-ttft-sweep", action="store_true")
     return ap.parse_args()
 
 
@@ -459,6 +460,16 @@ def run_b200(args, rank, world, local_rank):
         pt["value"] = world * pt["new_tokens"] / wall
         pt["ms_per_step"] = 1e3 * wall / pt["decode_steps"]
         e2e = pt
+        # per-turn TTFT against history length (north_star: independent of it): 16 concurrent threads
+        if rank == 0 and not args.no_ttft_sweep:
+            sweep = {}
+            for h in (256, 1024, 2048, 4096):
+                if h + 192 + 32 > cfg.max_pos:
+                    continue
+                r = provider_turn(eng, cfg, 16, h, U, 32, seed=1000 + h)
+                sweep[str(h)] = {"ttft_p50_ms": r["ttft_p50_ms"], "cached_fraction": r["cached_fraction_of_prompt"],
+                                 "prefilled_new_tokens": r["prefilled_new_tokens"]}
+            e2e["ttft_vs_history_16_threads"] = sweep
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -499,6 +510,9 @@ def main():
         return
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL is used for the barrier / max-over-ranks only; keep its version banner off stdout, which
+        # must carry exactly one JSON line
+        os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "WARN")
         torch.cuda.set_device(local_rank)
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:

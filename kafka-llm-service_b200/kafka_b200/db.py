@@ -209,6 +209,22 @@ class ThreadStore:
         db.commit()
         return n
 
+    async def upsert_residency(self, row: Dict[str, Any], gpu: int = 0) -> None:
+        """Insert or refresh ONE thread's row (what the server does after each turn)."""
+        if not row.get("thread_id"):
+            return
+        blob = struct.pack(f"<{len(row['block_ids'])}i", *row["block_ids"])
+        db = self._db()
+        db.execute("INSERT OR REPLACE INTO kv_residency VALUES (?, ?, ?, ?, ?, ?)",
+                   (row["thread_id"], gpu, int(row["n_tokens"]), f"{int(row['prefix_hash']):016x}", blob,
+                    float(row["last_used"])))
+        db.commit()
+
+    async def drop_residency(self, thread_id: str) -> None:
+        db = self._db()
+        db.execute("DELETE FROM kv_residency WHERE thread_id = ?", (thread_id,))
+        db.commit()
+
     async def get_residency(self, thread_id: str) -> Optional[Dict[str, Any]]:
         row = self._db().execute("SELECT * FROM kv_residency WHERE thread_id = ?", (thread_id,)).fetchone()
         if row is None:

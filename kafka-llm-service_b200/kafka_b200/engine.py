@@ -89,6 +89,17 @@ class Engine:
     def max_pos(self) -> int:
         return self.stepper.max_pos
 
+    def residency(self, thread_id: Optional[str] = None) -> List[Dict]:
+        """Which threads' KV is resident (for the SQLite kv_residency directory); one thread's row when
+        `thread_id` is given. Read from another thread while the engine mutates its index: retry if a
+        dict changed size mid-iteration."""
+        for _ in range(8):
+            try:
+                return self.sched.residency(thread_id)
+            except RuntimeError:
+                continue
+        return []
+
     # ---- engine thread -------------------------------------------------------------------------
     def _drain(self, block: bool) -> None:
         try:
@@ -154,6 +165,9 @@ class ShardedEngine:
 
     def stats(self) -> Dict:
         return {f"gpu{i}": e.stats() for i, e in enumerate(self.engines)}
+
+    def residency_by_gpu(self, thread_id: Optional[str] = None) -> Dict[int, List[Dict]]:
+        return {i: e.residency(thread_id) for i, e in enumerate(self.engines)}
 
     @property
     def max_pos(self) -> int:

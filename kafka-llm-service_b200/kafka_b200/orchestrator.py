@@ -23,8 +23,23 @@ from .llm.types import Message
 
 
 class ThreadRunner:
-    def __init__(self, agent: Any, store: Any, thread_id: str):
-        self.agent, self.store, self.thread_id = agent, store, thread_id
+    def __init__(self, agent: Any, store: Any, thread_id: str, engine: Any = None):
+        self.agent, self.store, self.thread_id, self.engine = agent, store, thread_id, engine
+
+    async def _record_residency(self) -> None:
+        """Refresh the thread -> KV-block directory (kv_residency table) from the engine(s)."""
+        eng = self.engine
+        if eng is None or not hasattr(self.store, "record_residency"):
+            return
+        tid = self.thread_id
+        by_gpu = eng.residency_by_gpu(tid) if hasattr(eng, "residency_by_gpu") else {0: eng.residency(tid)}
+        found = False
+        for gpu, rows in by_gpu.items():
+            for row in rows:
+                await self.store.upsert_residency(row, gpu=gpu)
+                found = True
+        if not found:
+            await self.store.drop_residency(tid)
 
     async def run(self, new_messages: Iterable[Any], model: str, temperature: float = 0.7,
                   max_tokens: Optional[int] = None, save_to_thread: bool = True,
@@ -88,3 +103,4 @@ class ThreadRunner:
             await store.add_messages(tid, to_save)
             if final_content and not any(m.role == "assistant" and m.content == final_content for m in to_save):
                 await store.add_message(tid, Message(role="assistant", content=final_content))
+        await self._record_residency()

@@ -221,3 +221,90 @@ class EchoLLMProvider(LLMProvider):
 
     async def close(self) -> None:
         return None
+
+
+class ScriptedToolCallProvider(LLMProvider):
+    """Deterministic tool-calling policy layered on a real provider (BASELINE config 4).
+
+    A random-init model never emits a parseable tool call, yet the agent loop's defining load pattern
+    is "several provider calls per turn, each re-sending a conversation that grew by the previous
+    output, a tool call and its result" (/root/reference/src/agents/base.py:210-433). This wrapper makes
+    that pattern reproducible: while fewer than `tool_rounds` tool results follow the last user message
+    it lets the inner provider generate `think_tokens` tokens of text and then appends one scripted
+    call to `tool_name` (finish_reason "tool_calls"); afterwards it delegates unchanged, so the last
+    round is an ordinary text completion. Every round runs real prefill + decode on the engine, and
+    because each round's prompt extends the previous one, only the new messages are prefilled.
+    """
+
+    def __init__(self, inner: LLMProvider, tool_name: str, tool_args: Optional[Dict[str, Any]] = None,
+                 tool_rounds: int = 2, think_tokens: int = 16):
+        super().__init__(tool_provider=inner.tool_provider)
+        self.inner, self.tool_name, self.tool_args = inner, tool_name, dict(tool_args or {})
+        self.tool_rounds, self.think_tokens = tool_rounds, think_tokens
+        self.model = getattr(inner, "model", None)
+
+    @property
+    def tool_provider(self):
+        return self.inner.tool_provider
+
+    @tool_provider.setter
+    def tool_provider(self, provider) -> None:
+        self._tool_provider = provider
+        if hasattr(self, "inner"):
+            self.inner.tool_provider = provider
+
+    @staticmethod
+    def _rounds_done(messages: List[Message]) -> int:
+        n = 0
+        for m in reversed(messages):
+            if m.role == "user":
+                break
+            if m.role == "tool":
+                n += 1
+        return n
+
+    async def stream_completion(self, messages: List[Message], *, temperature: Optional[float] = None,
+                                max_tokens: Optional[int] = None, stop: Optional[List[str]] = None,
+                                **kwargs: Any) -> AsyncGenerator[StreamChunk, None]:
+        done = self._rounds_done(self.validate_messages(messages))
+        if done >= self.tool_rounds:
+            async for ch in self.inner.stream_completion(messages, temperature=temperature, max_tokens=max_tokens,
+                                                         stop=stop, **kwargs):
+                yield ch
+            return
+        last = None
+        async for ch in self.inner.stream_completion(messages, temperature=temperature,
+                                                     max_tokens=self.think_tokens, stop=stop, **kwargs):
+            if ch.finish_reason is None:
+                yield ch
+            last = ch
+        import json as _json
+        call_id = f"call_{uuid.uuid4().hex[:12]}"
+        yield StreamChunk(tool_calls=[{"index": 0, "id": call_id, "type": "function",
+                                       "function": {"name": self.tool_name, "arguments": ""}}],
+                          model=last.model if last else self.model, id=last.id if last else None)
+        yield StreamChunk(tool_calls=[{"index": 0, "function": {"arguments": _json.dumps(self.tool_args)}}],
+                          model=last.model if last else self.model, id=last.id if last else None)
+        yield StreamChunk(finish_reason="tool_calls", model=last.model if last else self.model,
+                          id=last.id if last else None)
+
+    async def completion(self, messages: List[Message], **kwargs: Any) -> CompletionResponse:
+        parts: List[str] = []
+        calls: Dict[int, Dict[str, Any]] = {}
+        finish = cid = model = None
+        async for ch in self.stream_completion(messages, **kwargs):
+            if ch.content:
+                parts.append(ch.content)
+            for tc in ch.tool_calls or []:
+                slot = calls.setdefault(tc.get("index", 0), {"id": "", "type": "function",
+                                                             "function": {"name": "", "arguments": ""}})
+                fn = tc.get("function") or {}
+                slot["id"] = tc.get("id") or slot["id"]
+                slot["function"]["name"] = fn.get("name") or slot["function"]["name"]
+                slot["function"]["arguments"] += fn.get("arguments") or ""
+            finish, cid, model = ch.finish_reason or finish, ch.id, ch.model
+        return CompletionResponse(content="".join(parts) or None, finish_reason=finish, model=model, id=cid,
+                                  tool_calls=[calls[i] for i in sorted(calls)] or None)
+
+    async def close(self) -> None:
+        await self.inner.close()

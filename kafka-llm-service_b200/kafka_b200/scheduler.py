@@ -366,10 +366,15 @@ class Scheduler:
     def idle(self) -> bool:
         return not (self.waiting or self.prefilling or self.running)
 
-    def residency(self) -> List[Dict]:
-        """Snapshot for the SQLite kv_residency table (db.py)."""
+    def residency(self, thread_id: Optional[str] = None) -> List[Dict]:
+        """Snapshot for the SQLite kv_residency table (db.py): all entries, or one thread's."""
         out = []
-        for e in self.index.entries.values():
+        if thread_id is not None:
+            e = self.index.by_hint.get(thread_id)
+            entries = [e] if e is not None else []
+        else:
+            entries = list(self.index.entries.values())
+        for e in entries:
             out.append({"thread_id": e.thread_hint, "entry_id": e.entry_id, "n_tokens": len(e.tokens),
                         "prefix_hash": e.chain[-1] if e.chain else 0, "block_ids": list(e.blocks),
                         "last_used": e.last_used})

@@ -114,6 +114,12 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
         provider = provider_factory(model, tool_provider=tool_provider, thread_id=thread_id)
         return StreamingAgent(provider, tool_provider, system_prompt=system_prompt)
 
+    def make_runner(model: str, thread_id: str) -> ThreadRunner:
+        agent = make_agent(model, thread_id)
+        prov = agent.llm_provider
+        engine = getattr(prov, "engine", None) or getattr(getattr(prov, "inner", None), "engine", None)
+        return ThreadRunner(agent, store, thread_id, engine=engine)   # engine: feeds the kv_residency table
+
     def temperature_of(req: ChatCompletionRequest) -> float:
         return 0.7 if req.temperature is None else req.temperature
 
@@ -169,7 +175,7 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
     # ---- completions -----------------------------------------------------------------------------
     @app.post("/v1/threads/{thread_id}/chat/completions")
     async def chat_completions(thread_id: str, request: ChatCompletionRequest):
-        runner = ThreadRunner(make_agent(request.model, thread_id), store, thread_id)
+        runner = make_runner(request.model, thread_id)
         events = runner.run(request.messages, model=request.model, temperature=temperature_of(request),
                             max_tokens=request.max_tokens)
         if request.stream:
@@ -204,7 +210,7 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
 
     @app.post("/v1/threads/{thread_id}/agent/run")
     async def run_agent_with_thread(thread_id: str, request: AgentRunRequest):
-        runner = ThreadRunner(make_agent(request.model, thread_id), store, thread_id)
+        runner = make_runner(request.model, thread_id)
         return StreamingResponse(agent_stream(runner.run(request.messages, model=request.model,
                                                          temperature=request.temperature,
                                                          max_tokens=request.max_tokens)),

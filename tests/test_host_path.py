@@ -438,3 +438,42 @@ def test_echo_provider():
         r = await p.completion([Message(role="user", content="ping"), Message(role="assistant", content="x")])
         assert r.content == "ping" and r.finish_reason == "stop"
     asyncio.run(go())
+
+
+def test_config4_scripted_tool_rounds_prefill_incrementally():
+    """BASELINE config 4 shape: two tool rounds then text, through the streaming agent. Each round's
+    prompt extends the previous one, so after round 1 almost everything is served from resident KV."""
+    from kafka_b200.provider import ScriptedToolCallProvider
+    tok = ByteTokenizer(512)
+    eng = Engine(FakeStepper(eos_id=tok.eot_id, n_blocks=128, max_pos=4096, max_tokens=2048))
+    provider = B200LLMProvider(eng, tok, model="tiny-test", default_temperature=0.0)
+    try:
+        _config4_body(provider)
+    finally:
+        eng.shutdown()
+
+
+def _config4_body(provider):
+    from kafka_b200.provider import ScriptedToolCallProvider
+
+    async def lookup(key: str):
+        return "v" * 64                                           # a 64-token tool result
+
+    tools = LocalToolProvider([Tool("lookup", "look something up",
+                                    {"type": "object", "properties": {"key": {"type": "string"}}}, lookup)])
+    scripted = ScriptedToolCallProvider(provider, "lookup", {"key": "k"}, tool_rounds=2, think_tokens=8)
+    agent = StreamingAgent(scripted, tools, system_prompt="SYS")
+    st = provider.engine.stepper
+
+    async def go():
+        return [ev async for ev in agent.run([Message(role="user", content="use the tool twice")], model="tiny-test",
+                                             temperature=0.0, max_tokens=24, thread_id="agent-1")]
+    events = asyncio.run(go())
+    finishes = [e["choices"][0]["finish_reason"] for e in events if e.get("choices") and e["choices"][0]["finish_reason"]]
+    assert finishes == ["tool_calls", "tool_calls", "length"]
+    results = [e for e in events if e.get("type") == "tool_result" and e["is_complete"]]
+    assert len(results) == 2 and events[-1]["type"] == "agent_done" and len(events[-1]["final_content"]) == 24
+    # 3 provider calls; the 2nd and 3rd found the earlier rounds resident
+    assert provider.engine.sched.stats["requests"] == 3
+    cached, prompt = provider.engine.sched.stats["cached_tokens"], provider.engine.sched.stats["prompt_tokens"]
+    assert cached / prompt > 0.45 and st.prefilled_tokens == prompt - cached

@@ -141,7 +141,11 @@ def test_agent_run_stream_with_thread(fake_engine_app):
             msgs = (await c.get("/v1/threads/A1/messages")).json()["messages"]
             assert [m["role"] for m in msgs] == ["user", "assistant"] and msgs[1]["content"] == text
             kv = (await c.get("/v1/threads/A1/kv")).json()
-            assert kv == {"thread_id": "A1", "resident": False, "residency": None}
+            # the turn left the thread's KV resident and the server recorded it in kv_residency
+            assert kv["resident"] and kv["residency"]["gpu"] == 0 and kv["residency"]["n_tokens"] > 300
+            assert len(kv["residency"]["block_ids"]) == (kv["residency"]["n_tokens"] + 63) // 64
+            assert (await c.get("/v1/threads/nope/kv")).json() == {"thread_id": "nope", "resident": False,
+                                                                   "residency": None}
     asyncio.run(go())
 
 
