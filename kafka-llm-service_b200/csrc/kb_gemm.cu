@@ -380,8 +380,12 @@ static int pick_bn(int M, int N) {
         const int bn = cands[i];
         const long tiles = (long)num_m * ((N + bn - 1) / bn);
         const long per_cta = (tiles + sms - 1) / sms;
-        // narrower tiles pay more A re-reads and smem bandwidth per flop: small penalty
-        const long cost = per_cta * bn * (bn == 256 ? 100 : (bn == 128 ? 104 : 125));
+        // Per k-block a 1-CTA tile moves (16 KB of A + bn*128 B of B) into shared memory by TMA and out
+        // again into the tensor core: 2*(128 + bn) cycles at the 128 B/clk shared-memory port, always
+        // more than the 2*bn cycles the MMA itself needs. So the tile time is ~ (256 + 2 bn) per
+        // k-block (measured: tools/gemm_bench.py, profiles/r01_gemm_bench.md) and wide tiles win
+        // unless they leave SMs idle.
+        const long cost = per_cta * (256 + 2 * bn);
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
     }
     return best;
