@@ -53,6 +53,7 @@ class BlockAllocator:
     def __init__(self, n_blocks: int):
         self.n_blocks = n_blocks
         self._free = list(range(n_blocks - 1, -1, -1))
+        self.refs = [0] * n_blocks     # reference counts: a block shared by several conversations is read-only
 
     @property
     def n_free(self) -> int:
@@ -63,10 +64,24 @@ class BlockAllocator:
             return None
         out = self._free[-n:][::-1] if n else []
         del self._free[len(self._free) - n:]
+        for b in out:
+            self.refs[b] = 1
         return out
 
+    def share(self, blocks: Sequence[int]) -> None:
+        """Another conversation starts reading these (already written, immutable) blocks."""
+        for b in blocks:
+            self.refs[b] += 1
+
+    def is_shared(self, block: int) -> bool:
+        return self.refs[block] > 1
+
     def free(self, blocks: Sequence[int]) -> None:
-        self._free.extend(blocks)
+        """Drop one reference per block; a block returns to the pool when nobody reads it any more."""
+        for b in blocks:
+            self.refs[b] -= 1
+            if self.refs[b] == 0:
+                self._free.append(b)
 
 
 @dataclass
@@ -140,13 +155,29 @@ class PrefixIndex:
             i += 1
         return i
 
-    def lookup(self, prompt: Sequence[int], thread_hint: Optional[str]) -> Tuple[Optional[KVEntry], int]:
+    def donor(self, chain: Sequence[int], exclude: Optional[KVEntry] = None) -> Tuple[Optional[KVEntry], int]:
+        """Entry (idle OR busy) whose leading full blocks equal the prompt's, and how many. Those blocks
+        are immutable — a conversation only ever appends beyond what it registered — so another
+        conversation may read them (shared-prefix KV: a common system prompt is prefilled once)."""
+        for k in range(len(chain) - 1, -1, -1):
+            cands = self.by_hash.get(chain[k])
+            if not cands:
+                continue
+            for e in cands.values():
+                if e is not exclude and len(e.blocks) > k:
+                    return e, k + 1
+        return None, 0
+
+    def lookup(self, prompt: Sequence[int], thread_hint: Optional[str],
+               chain: Optional[Sequence[int]] = None) -> Tuple[Optional[KVEntry], int]:
+        """Idle entry to continue IN PLACE (exclusive reuse) and the length of the common prefix."""
         best, best_len = None, 0
         if thread_hint:
             e = self.by_hint.get(thread_hint)
             if e is not None and not e.busy:
                 best, best_len = e, self._lcp(e.tokens, prompt)
-        chain = _chain_hashes(prompt)
+        if chain is None:
+            chain = _chain_hashes(prompt)
         for k in range(len(chain) - 1, -1, -1):
             if (k + 1) * BLOCK_TOKENS <= best_len:
                 break
@@ -156,6 +187,8 @@ class PrefixIndex:
             for e in cands.values():
                 if e.busy:
                     continue
+                if thread_hint and e.thread_hint and e.thread_hint != thread_hint:
+                    continue  # another thread's conversation: never taken over, only read (donor())
                 n = self._lcp(e.tokens, prompt, (k + 1) * BLOCK_TOKENS)
                 if n > best_len:
                     best, best_len = e, n
@@ -219,7 +252,7 @@ class Scheduler:
         self.running: List[Request] = []
         self._ids = itertools.count(1)
         self.stats = {"requests": 0, "prompt_tokens": 0, "cached_tokens": 0, "generated_tokens": 0,
-                      "evictions": 0, "prefill_calls": 0, "decode_steps": 0}
+                      "evictions": 0, "prefill_calls": 0, "decode_steps": 0, "shared_tokens": 0}
 
     # ---- admission ---------------------------------------------------------------------------
     def add(self, req: Request) -> None:
@@ -229,10 +262,10 @@ class Scheduler:
         self.waiting.append(req)
         self.stats["requests"] += 1
 
-    def _evict_until(self, need_blocks: int, keep: Optional[KVEntry]) -> bool:
+    def _evict_until(self, need_blocks: int, keep: Sequence[Optional[KVEntry]] = ()) -> bool:
         if self.alloc.n_free >= need_blocks:
             return True
-        idle = sorted((e for e in self.index.entries.values() if not e.busy and e is not keep),
+        idle = sorted((e for e in self.index.entries.values() if not e.busy and all(e is not k for k in keep)),
                       key=lambda e: e.last_used)
         for e in idle:
             self.index.remove(e)
@@ -252,27 +285,52 @@ class Scheduler:
             if len(self.prefilling) + len(self.running) >= self.max_seqs:
                 still.append(req)
                 continue
-            entry, lcp = self.index.lookup(req.prompt, req.thread_hint)
+            chain = _chain_hashes(req.prompt)
+            entry, lcp = self.index.lookup(req.prompt, req.thread_hint, chain)
             lcp = min(lcp, len(req.prompt) - 1)  # at least one token must run to produce logits
+            donor, d_blocks = self.index.donor(chain, exclude=entry)
+            d_blocks = min(d_blocks, (len(req.prompt) - 1) // BLOCK_TOKENS)
             total = len(req.prompt) + req.params.max_tokens
             need_total = (total + BLOCK_TOKENS - 1) // BLOCK_TOKENS
-            have = len(entry.blocks) if entry is not None else 0
-            extra = max(0, need_total - have)
-            if not self._evict_until(extra, keep=entry):
-                if entry is None and not self.index.entries and not self.prefilling and not self.running:
+            share = donor is not None and d_blocks * BLOCK_TOKENS > lcp
+            if share:
+                # read the donor's leading blocks, own everything after them
+                entry, lcp = None, d_blocks * BLOCK_TOKENS
+                extra, replace = need_total - d_blocks, []
+            else:
+                # continue this conversation's own entry in place. Blocks it shares with others are
+                # read-only: if writing resumes inside one, fall back to its first token and take fresh
+                # blocks from there on (copy-on-write by re-prefill of at most 63 tokens)
+                blocks = entry.blocks if entry is not None else []
+                first = lcp // BLOCK_TOKENS
+                if first < len(blocks) and self.alloc.is_shared(blocks[first]):
+                    lcp = first * BLOCK_TOKENS
+                replace = [i for i in range(lcp // BLOCK_TOKENS, len(blocks)) if self.alloc.is_shared(blocks[i])]
+                extra = max(0, need_total - len(blocks)) + len(replace)
+            if not self._evict_until(extra, keep=(entry, donor)):
+                if not self.index.entries and not self.prefilling and not self.running:
                     req.on_event(("error", MemoryError(
                         f"request needs {need_total} KV blocks but the pool has {self.alloc.n_blocks}")))
                     continue
                 still.append(req)
                 continue
-            if entry is None:
+            if share:
+                entry = KVEntry(entry_id=next(self._ids), thread_hint=req.thread_hint,
+                                blocks=list(donor.blocks[:d_blocks]))
+                self.alloc.share(entry.blocks)
+                self.stats["shared_tokens"] += lcp
+            elif entry is None:
                 entry = KVEntry(entry_id=next(self._ids), thread_hint=req.thread_hint)
                 lcp = 0
             else:
-                self.index.remove(entry)          # re-registered (with its new tokens) on release
+                self.index.remove(entry)          # re-registered (with its new tokens) when prefilled
                 entry.thread_hint = req.thread_hint or entry.thread_hint
-            entry.blocks += self.alloc.alloc(extra)
-            entry.tokens = entry.tokens[:lcp]
+            fresh = self.alloc.alloc(extra)
+            for i in replace:                     # swap shared blocks that would be overwritten
+                self.alloc.free([entry.blocks[i]])
+                entry.blocks[i] = fresh.pop()
+            entry.blocks += fresh
+            entry.tokens = list(req.prompt[:lcp])
             entry.busy = True
             req.entry = entry
             req.n_cached = req.n_prefilled = lcp
@@ -303,6 +361,11 @@ class Scheduler:
             if it.is_last_chunk:
                 self.prefilling.remove(req)
                 self.running.append(req)
+                # the prompt's KV is complete and immutable from here on: let other conversations that
+                # start with the same blocks (a common system prompt) read it while this one decodes
+                if req.entry is not None:
+                    req.entry.tokens = list(req.prompt)
+                    self.index.add(req.entry)
                 self._on_token(req, int(tok))
         self._reap()
 
@@ -345,6 +408,7 @@ class Scheduler:
         if e is None:
             return
         req.entry = None
+        self.index.remove(e)   # registered as a read-only donor while it was running; re-added below
         # KV is resident for the prefilled prompt part and for every generated token that was fed back
         e.tokens = req.prompt[:req.n_prefilled] + req.generated[:max(0, len(req.generated) - 1)]
         keep = (len(e.tokens) + BLOCK_TOKENS - 1) // BLOCK_TOKENS

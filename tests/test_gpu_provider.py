@@ -120,6 +120,33 @@ def test_sampling_with_temperature_is_reproducible_per_seed(cuda):
         eng.shutdown()
 
 
+def test_shared_system_prompt_blocks_match_oracle(cuda):
+    """Shared-prefix KV on the real kernels: threads that start with the same system prompt read the
+    first thread's KV blocks (block tables of different sequences point at the same physical blocks)."""
+    from kafka_b200.llm import Message
+    cfg, eng, gpu, cpu = _build("tiny-test", cuda, "margin", n_blocks=128, max_seqs=8)
+    try:
+        system = Message(role="system", content="You are a careful assistant. " * 12)      # ~350 tokens
+
+        async def go():
+            first = await gpu.completion([system, Message(role="user", content="warm")], temperature=0.0,
+                                         max_tokens=8, thread_id="s0")
+            users = [Message(role="user", content=f"question number {i} " * (i + 1)) for i in range(6)]
+            got = await asyncio.gather(*[gpu.completion([system, u], temperature=0.0, max_tokens=24,
+                                                        thread_id=f"s{i + 1}") for i, u in enumerate(users)])
+            want = [await cpu.completion([system, u], temperature=0.0, max_tokens=24) for u in users]
+            return first, got, want
+        first, got, want = asyncio.run(go())
+        assert [g.content for g in got] == [w.content for w in want]
+        n_sys = len(gpu.render([system], None)) - 13                     # BOS + system message, no gen prompt
+        floor = n_sys // 64 * 64                                         # full blocks of the common prefix
+        cached = [g.usage["cached_tokens"] for g in got]
+        assert floor >= 256 and all(c >= floor and c % 64 == 0 for c in cached), (floor, cached)
+        assert eng.stats()["shared_tokens"] == sum(cached)
+    finally:
+        eng.shutdown()
+
+
 def test_tinyllama_shapes_against_oracle(cuda, tmp_path):
     """TinyLlama-1.1B shapes (22 layers, 32 q / 4 kv heads of 64, ffn 5632, vocab 32000)."""
     from kafka_b200 import cabi

@@ -249,3 +249,72 @@ def test_sharded_engine_routes_by_thread():
                     assert tid not in {x["thread_id"] for x in engines[g].sched.residency()}
     finally:
         se.shutdown()
+
+
+# ---- shared-prefix KV -----------------------------------------------------
+def test_common_system_prompt_is_prefilled_once(engine):
+    """The reference prepends one byte-identical system prompt to every thread: its
+    full blocks are computed by the first thread and only read by the others."""
+    st = engine.stepper
+    system = [300 + (i % 50) for i in range(200)]                 # 3 full blocks + 8 tokens
+    first = run(engine, system + [65, 66, 67], n=4, hint="t0")
+    assert first.usage["cached_tokens"] == 0
+    for i in range(1, 6):
+        p = system + [70 + i] * (5 + i)
+        before = st.prefilled_tokens
+        c = run(engine, p, n=6, hint=f"t{i}")
+        assert c.tokens == expected_tokens(p, 6, EOS)             # read back through the shared blocks
+        assert c.usage["cached_tokens"] == 192                    # 3 shared blocks, nothing recomputed
+        assert st.prefilled_tokens - before == len(p) - 192
+    assert engine.sched.stats["shared_tokens"] == 5 * 192
+    # every thread can still continue its own conversation in place
+    c = run(engine, system + [65, 66, 67] + first.tokens + [EOS, 90, 91], n=3, hint="t0")
+    assert c.usage["cached_tokens"] == 203 + 3 and c.tokens == expected_tokens(
+        system + [65, 66, 67] + first.tokens + [EOS, 90, 91], 3, EOS)
+
+
+def test_prefix_shared_from_a_conversation_that_is_still_decoding():
+    st = FakeStepper(n_blocks=64, max_seqs=4, max_tokens=512, max_pos=2048, eos_id=EOS)
+    e = Engine(st)
+    try:
+        system = [200 + (i % 31) for i in range(130)]             # 2 full blocks
+        slow, fast = Collector(), Collector()
+        e.submit(system + [65], SamplingParams(max_tokens=300), slow, thread_hint="slow")
+        while len(slow.tokens) < 3:                                # prefill done, decoding
+            time.sleep(0.005)
+        e.submit(system + [66, 67], SamplingParams(max_tokens=5), fast, thread_hint="fast")
+        fast.wait()
+        assert fast.usage["cached_tokens"] == 128 and fast.tokens == expected_tokens(system + [66, 67], 5, EOS)
+        slow.wait(30)
+        assert slow.tokens == expected_tokens(system + [65], 300, EOS)   # the donor was not disturbed
+    finally:
+        e.shutdown()
+
+
+def test_copy_on_write_when_a_shared_block_would_be_overwritten(engine):
+    a_prompt = [400 + (i % 17) for i in range(200)]
+    run(engine, a_prompt, n=4, hint="A")
+    b_prompt = a_prompt[:192] + [77] * 20                         # shares A's first 3 blocks
+    b = run(engine, b_prompt, n=4, hint="B")
+    assert b.usage["cached_tokens"] == 192
+    # A's history is edited at position 100, i.e. inside shared block 1: A must not write there
+    a2 = a_prompt[:100] + [88] * 60
+    c = run(engine, a2, n=5, hint="A")
+    assert c.usage["cached_tokens"] == 64                         # resumed from the block boundary
+    assert c.tokens == expected_tokens(a2, 5, EOS)
+    # B still reads intact blocks
+    b2 = b_prompt + b.tokens + [EOS, 65]
+    d = run(engine, b2, n=4, hint="B")
+    assert d.tokens == expected_tokens(b2, 4, EOS) and d.usage["cached_tokens"] == len(b_prompt) + 3
+
+
+def test_reference_counts_return_every_block(engine):
+    system = [250 + (i % 13) for i in range(150)]
+    for i in range(5):
+        run(engine, system + [65 + i] * 10, n=3, hint=f"r{i}")
+    sched = engine.sched
+    assert max(sched.alloc.refs) >= 2                             # something is shared
+    for e in list(sched.index.entries.values()):                  # evict everything
+        sched.index.remove(e)
+        sched.alloc.free(e.blocks)
+    assert sched.alloc.n_free == sched.alloc.n_blocks and set(sched.alloc.refs) == {0}
