@@ -29,6 +29,46 @@ from .template import ChatTemplate
 from .tokenizer import ByteTokenizer
 
 PROVIDER_NAME = "B200"
+TOOL_OPEN, TOOL_CLOSE = "<tool_calls>", "</tool_calls>"      # the block template.py renders tool calls in
+
+
+def parse_tool_calls(payload: str) -> Optional[List[Dict[str, Any]]]:
+    """JSON between the tool-call tags -> normalised OpenAI tool_calls, or None if it is not a list of
+    calls. Accepts both the full shape ({"id","type","function":{"name","arguments"}}) and the short
+    {"name","arguments"}; `arguments` may be an object (re-serialised) or a string."""
+    import json
+    try:
+        data = json.loads(payload)
+    except ValueError:
+        return None
+    if isinstance(data, dict):
+        data = [data]
+    if not isinstance(data, list) or not data:
+        return None
+    out = []
+    for item in data:
+        if not isinstance(item, dict):
+            return None
+        fn = item.get("function") if isinstance(item.get("function"), dict) else item
+        name, args = fn.get("name"), fn.get("arguments", {})
+        if not isinstance(name, str) or not name:
+            return None
+        if not isinstance(args, str):
+            args = json.dumps(args)
+        out.append({"id": item.get("id") or f"call_{uuid.uuid4().hex[:12]}", "type": "function",
+                    "function": {"name": name, "arguments": args}})
+    return out
+
+
+def tool_call_chunks(calls: List[Dict[str, Any]], model: Optional[str], cid: Optional[str]):
+    """Tool calls as the delta stream the reference's agent merges by `index`
+    (/root/reference/src/agents/base.py:286-331): id + name first, then the argument string."""
+    for i, c in enumerate(calls):
+        yield StreamChunk(tool_calls=[{"index": i, "id": c["id"], "type": "function",
+                                       "function": {"name": c["function"]["name"], "arguments": ""}}],
+                          model=model, id=cid)
+        yield StreamChunk(tool_calls=[{"index": i, "function": {"arguments": c["function"]["arguments"]}}],
+                          model=model, id=cid)
 
 
 class _LoopMailbox:
@@ -83,11 +123,23 @@ class B200LLMProvider(LLMProvider):
         return self.template.render(messages, tools=tools or None, add_generation_prompt=True)
 
     @staticmethod
-    def _first_stop(text: str, stop: Optional[List[str]]) -> int:
-        if not stop:
+    def _first_marker(text: str, markers: List[str], start: int) -> int:
+        if not markers:
             return -1
-        hits = [i for i in (text.find(s) for s in stop if s) if i >= 0]
+        hits = [i for i in (text.find(s, start) for s in markers) if i >= 0]
         return min(hits) if hits else -1
+
+    @staticmethod
+    def _partial_marker(text: str, markers: List[str], hold: int) -> int:
+        """Length of the longest suffix of `text` that is a proper prefix of some marker."""
+        if not markers:
+            return 0
+        for k in range(min(hold, len(text)), 0, -1):
+            tail = text[-k:]
+            for m in markers:
+                if m.startswith(tail):
+                    return k
+        return 0
 
     # ---- the plugin API ------------------------------------------------------------------------
     async def stream_completion(self, messages: List[Message], *, temperature: Optional[float] = None,
@@ -125,20 +177,45 @@ class B200LLMProvider(LLMProvider):
             decoder = self.tokenizer.stream_decoder()
             text = ""
             emitted = 0
-            hold = max((len(s) for s in stop), default=1) - 1 if stop else 0
+            # strings that end plain-text streaming: the caller's stop sequences and, when tools are on
+            # offer, the opening tag of a tool-call block (the syntax template.py renders tool calls in)
+            markers = [s for s in (stop or []) if s] + ([TOOL_OPEN] if tools else [])
+            hold = max((len(s) for s in markers), default=1) - 1   # longest partial marker a tail can be
+            collecting = -1                            # >= 0: index where a tool-call block opened
             while True:
                 ev = await events.get()
                 kind = ev[0]
                 if kind == "token":
                     text += decoder.push(ev[1])
-                    cut = self._first_stop(text, stop)
+                    if collecting >= 0:
+                        end = text.find(TOOL_CLOSE, collecting)
+                        if end < 0:
+                            continue
+                        calls = parse_tool_calls(text[collecting + len(TOOL_OPEN):end])
+                        if calls is None:              # not valid JSON after all: hand it over as text
+                            yield StreamChunk(content=text[emitted:], model=model, id=completion_id)
+                            emitted, collecting = len(text), -1
+                            continue
+                        req.cancelled = True
+                        for ch in tool_call_chunks(calls, model, completion_id):
+                            yield ch
+                        yield StreamChunk(finish_reason="tool_calls", model=model, id=completion_id)
+                        return
+                    cut = self._first_marker(text, markers, max(0, emitted - hold))
                     if cut >= 0:
+                        if tools and text.startswith(TOOL_OPEN, cut):
+                            body = text[emitted:cut].rstrip("\n")
+                            if body:
+                                yield StreamChunk(content=body, model=model, id=completion_id)
+                            emitted = collecting = cut
+                            continue
                         if cut > emitted:
                             yield StreamChunk(content=text[emitted:cut], model=model, id=completion_id)
                         req.cancelled = True
                         yield StreamChunk(finish_reason="stop", model=model, id=completion_id)
                         return
-                    upto = len(text) - hold            # keep back what could still grow into a stop string
+                    # keep back only a tail that is the beginning of a marker (usually nothing)
+                    upto = len(text) - self._partial_marker(text, markers, hold)
                     if upto > emitted:
                         yield content_chunk(text[emitted:upto], model, completion_id)   # per-token hot spot
                         emitted = upto
@@ -163,20 +240,28 @@ class B200LLMProvider(LLMProvider):
                          **kwargs: Any) -> CompletionResponse:
         usage: Dict[str, int] = {}
         parts: List[str] = []
+        calls: Dict[int, Dict[str, Any]] = {}
         finish = None
         cid = model = None
         async for ch in self.stream_completion(messages, temperature=temperature, max_tokens=max_tokens, stop=stop,
                                                _usage_out=usage, **kwargs):
             if ch.content:
                 parts.append(ch.content)
+            for tc in ch.tool_calls or []:
+                slot = calls.setdefault(tc.get("index", 0), {"id": "", "type": "function",
+                                                             "function": {"name": "", "arguments": ""}})
+                fn = tc.get("function") or {}
+                slot["id"] = tc.get("id") or slot["id"]
+                slot["function"]["name"] = fn.get("name") or slot["function"]["name"]
+                slot["function"]["arguments"] += fn.get("arguments") or ""
             finish = ch.finish_reason or finish
             cid, model = ch.id, ch.model
         return CompletionResponse(content="".join(parts), finish_reason=finish, model=model, id=cid,
-                                  usage=usage or None)
+                                  usage=usage or None, tool_calls=[calls[i] for i in sorted(calls)] or None)
 
     def get_model_info(self) -> Dict[str, Any]:
         return {"model": self.model, "provider": PROVIDER_NAME, "max_context_tokens": self.engine.max_pos,
-                "supports_vision": False, "supports_tools": False, "default_temperature": self.default_temperature}
+                "supports_vision": False, "supports_tools": True, "default_temperature": self.default_temperature}
 
     async def close(self) -> None:
         """The engine is process-wide and outlives provider objects (one is built per request on

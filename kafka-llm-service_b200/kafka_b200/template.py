@@ -46,7 +46,11 @@ class ChatTemplate:
         body = content if isinstance(content, str) else ("" if content is None else canonical_json(content))
         tool_calls = _field(msg, "tool_calls")
         if tool_calls:
-            body += "\n<tool_calls>" + canonical_json(tool_calls) + "</tool_calls>"
+            # on its own line unless the text already ends one (what a streamed reply that opened the
+            # block looks like when it comes back as history: the same tokens, so the KV prefix holds)
+            if body and not body.endswith("\n"):
+                body += "\n"
+            body += "<tool_calls>" + canonical_json(tool_calls) + "</tool_calls>"
         return body
 
     def render_message(self, msg: Any) -> List[int]:
