@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--no-provider", action="store_true", help="skip the provider-level (plugin API) turn")
     ap.add_argument("--gen-tokens", type=int, default=128, help="new tokens per turn in the provider-level leg")
     ap.add_argument("--no-ttft-sweep", action="store_true")
+    ap.add_argument("--tp", action="store_true",
+                    help="tensor-parallel: ONE model sharded over all ranks (config 5: --model llama-3-70b --history 8192)")
     return ap.parse_args()
 
 
@@ -500,6 +502,117 @@ def run_b200(args, rank, world, local_rank):
         print(json.dumps(line), flush=True)
 
 
+def run_tp(args, rank, world, local_rank):
+    """BASELINE config 5 shape: one model sharded over all `world` GPUs (tensor parallel, NCCL all-reduce
+    over NVLink after the O and down projections), all ranks stepping the same batch in lockstep."""
+    from kafka_b200 import cabi
+    from kafka_b200.cabi import KB_BLOCK_TOKENS
+    from kafka_b200.engine_core import EngineCore
+    from kafka_b200.model_config import get_config
+    from kafka_b200.tp import build_tp_core, local_config
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    cfg = get_config(args.model)
+    loc = local_config(cfg, world)
+    K, W = args.steps, max(args.warmup, 3)
+    U = args.user_tokens
+    bpt = (args.history + U + 2 * (W + K) + 8 + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
+    B = args.threads
+    # weights first (they decide how much HBM is left for KV); a 1-block core, then the real one
+    free0, _ = torch.cuda.mem_get_info(dev)
+    w_bytes = 2 * (loc.matmul_params() + 2 * cfg.vocab * cfg.hidden)
+    fit = int((free0 - w_bytes - 6 * (1 << 30)) // (EngineCore.kv_block_bytes(loc) * bpt))
+    fit_t = torch.tensor([fit], device=dev)
+    torch.distributed.all_reduce(fit_t, op=torch.distributed.ReduceOp.MIN)
+    fit = int(fit_t.item())
+    resident_note = None
+    if fit < B:
+        resident_note = f"only {fit} of {B} threads resident per the smallest rank's free HBM"
+        B = fit
+    core, grp = build_tp_core(cfg, rank, world, dev, n_blocks=B * bpt, max_tokens=max(4096, B), max_seqs=B, seed=0)
+    for L in range(loc.n_layers):
+        core.k_pool[L].normal_(0, 1)
+        core.v_pool[L].normal_(0, 1)
+    g = torch.Generator(device="cpu").manual_seed(1234)            # identical inputs on every rank
+    block_ids = torch.randperm(B * bpt, generator=g).int().view(B, bpt).to(dev)
+    ctx_lens = torch.full((B,), args.history, dtype=torch.int32, device=dev)
+    sp = cabi.make_sampling(temperature=0.0, banned_token=cfg.vocab - 1)
+    user = torch.randint(0, 256, (B, U), generator=g, dtype=torch.int32).to(dev)
+    first = torch.empty(B, dtype=torch.int32, device=dev)
+    per_chunk = max(1, 4096 // U)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.distributed.barrier()
+    e0.record()
+    for s0 in range(0, B, per_chunk):
+        s1 = min(B, s0 + per_chunk)
+        cu = torch.arange(0, (s1 - s0 + 1) * U, U, dtype=torch.int32, device=dev)
+        core.prefill(user[s0:s1].reshape(-1), cu, ctx_lens[s0:s1], block_ids[s0:s1], U, sp, None, first[s0:s1])
+    e1.record()
+    torch.cuda.synchronize()
+    prefill_ms = e0.elapsed_time(e1)
+    ctx_lens += U
+    bufs, cur, ctx = [first, torch.empty_like(first)], 0, args.history + U
+
+    def steps(n):
+        nonlocal cur, ctx
+        for _ in range(n):
+            core.decode(bufs[cur], ctx_lens, block_ids, sp, bufs[cur ^ 1], max_ctx=ctx, advance_ctx=True)
+            cur ^= 1
+            ctx += 1
+
+    steps(W)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    torch.cuda.synchronize()
+    torch.distributed.barrier()
+    l0 = cabi.launch_count()
+    ctx_start = ctx
+    e0.record()
+    steps(K)
+    e1.record()
+    torch.cuda.synchronize()
+    torch.distributed.barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms_total = float(t.item())
+    launches = cabi.launch_count() - l0
+    clocks = sampler.stop()
+    core.profile_begin()
+    ctx_p = ctx
+    steps(K)
+    prof = core.profile_end()
+    if rank != 0:
+        return
+    hbm_peak, tf_peak, peak_kind = peaks()
+    attn_ms, attn_n = prof["attention"]
+    attn_bytes = B * (ctx_p + (K - 1) / 2 + 1) * loc.kv_dim * 2 * 2
+    achieved = attn_bytes / (attn_ms / attn_n / 1e3) / 1e9
+    ar_ms, ar_n = prof["allreduce"]
+    ar_bytes = 4 * B * cfg.hidden
+    line = {
+        "metric": METRIC, "value": B * K / (ms_total / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "16-bit float operands (bf16 KV / attention, fp16 projections), fp32 accumulate", "data": "synthetic",
+        "config": {"workload": f"{cfg.name} tensor-parallel x{world} decode, {B} threads x {args.history}-token history "
+                               f"+ {U}-token turn (BASELINE configs[4])", "model": cfg.name, "threads": B,
+                   "history": args.history, "context_at_start": ctx_start, "resident_note": resident_note,
+                   "parallelism": f"tp{world}: heads/ffn sharded, 2 NCCL all-reduces of [T,{cfg.hidden}] fp32 per layer",
+                   "l2": "inputs larger than L2; no explicit flush"},
+        "clocks": clocks, "gpu_launches": launches, "e2e": None,
+        "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel<128,8>", "achieved": achieved, "peak": hbm_peak,
+                     "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_kind": peak_kind,
+                     "bytes_per_launch": attn_bytes, "us_per_launch": attn_ms / attn_n * 1e3,
+                     "share_of_step": attn_ms / sum(v[0] for v in prof.values())},
+        "allreduce": {"calls_per_step": ar_n / K, "ms_per_step": ar_ms / K, "bytes_per_call": ar_bytes,
+                      "busbw_GBps": (2 * (world - 1) / world) * ar_bytes / (ar_ms / ar_n / 1e3) / 1e9,
+                      "backend": "NCCL via torch.distributed on the kernels' stream"},
+        "kernels": {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]},
+        "prefill": {"ms": prefill_ms, "tokens": B * U}, "cpu_baseline": None,
+    }
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -516,7 +629,10 @@ def main():
         torch.cuda.set_device(local_rank)
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        run_b200(args, rank, world, local_rank)
+        if args.tp and world > 1:
+            run_tp(args, rank, world, local_rank)
+        else:
+            run_b200(args, rank, world, local_rank)
     finally:
         if world > 1:
             torch.distributed.destroy_process_group()

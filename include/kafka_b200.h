@@ -113,6 +113,19 @@ int kb_bind_kv_pool(kb_engine* e, void* k_pool, void* v_pool, int32_t n_blocks);
 size_t kb_workspace_bytes(const kb_model_cfg* cfg, int32_t max_tokens, int32_t max_seqs);
 int kb_bind_workspace(kb_engine* e, void* ws, size_t bytes, int32_t max_tokens, int32_t max_seqs);
 
+/* ---- tensor parallelism (BASELINE config 5: Llama-3-70B over 8 GPUs) ----------------------------
+ * Megatron-style sharding, one process and one engine per GPU: the engine is created with the LOCAL
+ * shapes of its rank (n_heads / tp, n_kv_heads / tp, ffn / tp; hidden and vocab unchanged), wqkv and
+ * w_gate_up hold this rank's rows, wo and w_down this rank's K-columns, embed / norms / lm_head are
+ * replicated.  The two row-sharded projections of every layer produce partial sums that must be added
+ * over the ranks; the engine calls `fn(ctx, buf, n, stream)` to do that in place on `buf` (n fp32,
+ * device) in stream order.  Rank 0 has already folded the residual into its partial, so the reduced
+ * buffer is the new residual stream on every rank.  In this repo the callback is NCCL over NVLink
+ * through torch.distributed (kafka_b200/tp.py); no counterpart exists in the reference.
+ * Every rank must make the same kb_prefill / kb_decode calls with the same arguments. */
+typedef int (*kb_allreduce_fn)(void* ctx, float* buf, size_t n, kb_stream stream);
+int kb_set_tensor_parallel(kb_engine* e, int32_t tp_rank, int32_t tp_size, kb_allreduce_fn fn, void* ctx);
+
 /* ---- the hot path ------------------------------------------------------------------------------
  * Both calls run embed -> n_layers x (RMSNorm, QKV GEMM, RoPE + KV append, paged attention,
  * O GEMM + residual, RMSNorm, gate/up GEMM + SwiGLU, down GEMM + residual) -> final RMSNorm of the
@@ -249,7 +262,8 @@ int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampl
 #define KB_PROF_GEMM_DOWN 7
 #define KB_PROF_LM_HEAD 8
 #define KB_PROF_SAMPLE 9
-#define KB_PROF_CATS 10
+#define KB_PROF_ALLREDUCE 10
+#define KB_PROF_CATS 11
 int kb_profile_begin(kb_engine* e);
 int kb_profile_end(kb_engine* e, float* ms_by_cat, int32_t* launches_by_cat);
 

@@ -44,6 +44,7 @@ static inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
 struct Workspace {
     float* x = nullptr;           // [T, hidden] fp32 residual stream
+    float* xr = nullptr;          // [T, hidden] fp32 partial sums of a row-sharded projection (tensor parallel)
     __nv_bfloat16* xn = nullptr;  // [T, hidden] normed activations (GEMM A operand)
     __nv_bfloat16* qkv = nullptr; // [T, qkv_dim]
     __nv_bfloat16* attn = nullptr;// [T, n_heads*head_dim]
@@ -64,6 +65,7 @@ static void layout_workspace(const kb_model_cfg& c, int T, int S, uint8_t* base,
     };
     const size_t qkv_dim = (size_t)(c.n_heads + 2 * c.n_kv_heads) * c.head_dim;
     w->x = reinterpret_cast<float*>(take((size_t)T * c.hidden * 4));
+    w->xr = reinterpret_cast<float*>(take((size_t)T * c.hidden * 4));
     w->xn = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.hidden * 2));
     w->qkv = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * qkv_dim * 2));
     w->attn = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.n_heads * c.head_dim * 2));
@@ -105,6 +107,10 @@ struct kb_engine {
     int n_blocks = 0;
     kb::Workspace ws;
     int max_tokens = 0, max_seqs = 0;
+    // tensor parallel (kb_set_tensor_parallel): cfg holds the LOCAL head / ffn counts of this rank
+    int tp_rank = 0, tp_size = 1;
+    kb_allreduce_fn allreduce = nullptr;
+    void* allreduce_ctx = nullptr;
     // profiling: one event before every kernel (+ one closing event per call)
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_pool;  // reusable events
@@ -132,6 +138,7 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     KB_CHECK(tokens && ctx_lens && block_tables, "null token / ctx_lens / block_tables pointer");
     KB_CHECK(decode || cu_seqlens != nullptr, "prefill needs cu_seqlens");
     KB_CHECK(out_tokens == nullptr || sampling != nullptr, "out_tokens requested without sampling params");
+    KB_CHECK(e->tp_size <= 1 || e->allreduce != nullptr, "tensor parallel engine without an all-reduce callback");
     int dev = -1;
     KB_CUDA(cudaGetDevice(&dev));
     KB_CHECK(dev == e->device, "engine belongs to device %d but current device is %d", e->device, dev);
@@ -156,15 +163,36 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     const int qkv_dim = (c.n_heads + 2 * c.n_kv_heads) * c.head_dim;
     const size_t layer_stride = (size_t)e->n_blocks * c.n_kv_heads * KB_BLOCK_TOKENS * c.head_dim;
     int rc;
+    float* x = w.x;    // residual stream; with tensor parallelism x and xr trade places after every all-reduce
+    float* xr = w.xr;
+
+    // x += a[T,K] * wt[hidden,K]^T.  Tensor parallel: this rank holds a K-slice of the projection, the
+    // partial sums go through the host-provided all-reduce; rank 0 folds the residual into its partial,
+    // so the reduced buffer IS the new residual stream (no separate add).
+    auto project_into_residual = [&](const void* a, const void* wt, int K) -> int {
+        if (e->tp_size <= 1)
+            return gemm(a, wt, x, x, n_tokens, c.hidden, K, KB_EPI_RESID_F32 | KB_GEMM_F16, stream);
+        int r = (e->tp_rank == 0)
+                    ? gemm(a, wt, xr, x, n_tokens, c.hidden, K, KB_EPI_RESID_F32 | KB_GEMM_F16, stream)
+                    : gemm(a, wt, xr, nullptr, n_tokens, c.hidden, K, KB_EPI_F32 | KB_GEMM_F16, stream);
+        if (r) return r;
+        mark(KB_PROF_ALLREDUCE);
+        if (e->allreduce(e->allreduce_ctx, xr, (size_t)n_tokens * c.hidden, stream) != 0) {
+            set_error("tensor-parallel all-reduce callback failed");
+            return KB_ERR_INVALID;
+        }
+        float* t = x; x = xr; xr = t;
+        return KB_OK;
+    };
 
     mark(KB_PROF_EMBED);
-    if ((rc = embed(tokens, e->embed, w.x, n_tokens, c.hidden, c.vocab, stream))) return rc;
+    if ((rc = embed(tokens, e->embed, x, n_tokens, c.hidden, c.vocab, stream))) return rc;
     for (int L = 0; L < c.n_layers; ++L) {
         const kb_layer_weights& lw = e->layers[L];
         __nv_bfloat16* kp = e->k_pool + (size_t)L * layer_stride;
         __nv_bfloat16* vp = e->v_pool + (size_t)L * layer_stride;
         mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(w.x, lw.attn_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+        if ((rc = rmsnorm(x, lw.attn_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
         mark(KB_PROF_GEMM_QKV);
         if ((rc = gemm(w.xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16 | KB_GEMM_F16, stream)))
             return rc;
@@ -183,17 +211,15 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         }
         if (rc) return rc;
         mark(KB_PROF_GEMM_O);
-        if ((rc = gemm(w.attn, lw.wo, w.x, w.x, n_tokens, c.hidden, qdim, KB_EPI_RESID_F32 | KB_GEMM_F16, stream)))
-            return rc;
+        if ((rc = project_into_residual(w.attn, lw.wo, qdim))) return rc;
         mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(w.x, lw.mlp_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+        if ((rc = rmsnorm(x, lw.mlp_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
         mark(KB_PROF_GEMM_GATE_UP);
         if ((rc = gemm(w.xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden,
                        KB_EPI_SWIGLU_F16 | KB_GEMM_F16, stream)))
             return rc;
         mark(KB_PROF_GEMM_DOWN);
-        if ((rc = gemm(w.h, lw.w_down, w.x, w.x, n_tokens, c.hidden, c.ffn, KB_EPI_RESID_F32 | KB_GEMM_F16, stream)))
-            return rc;
+        if ((rc = project_into_residual(w.h, lw.w_down, c.ffn))) return rc;
     }
     if (logits_out == nullptr && out_tokens == nullptr) {  // KV fill only
         mark(-1);
@@ -201,7 +227,7 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     }
     mark(KB_PROF_RMSNORM);
     // final norm on the last row of every sequence, lm_head, sampling
-    if ((rc = rmsnorm(w.x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, n_seqs, c.hidden, c.rms_eps, 1,
+    if ((rc = rmsnorm(x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, n_seqs, c.hidden, c.rms_eps, 1,
                       stream)))
         return rc;
     float* lg = logits_out ? logits_out : w.logits;
@@ -255,6 +281,18 @@ extern "C" void kb_engine_destroy(kb_engine* e) {
     if (!e) return;
     for (cudaEvent_t ev : e->prof_pool) cudaEventDestroy(ev);
     delete e;
+}
+
+extern "C" int kb_set_tensor_parallel(kb_engine* e, int32_t tp_rank, int32_t tp_size, kb_allreduce_fn fn, void* ctx) {
+    KB_CHECK(e != nullptr, "kb_set_tensor_parallel: null engine");
+    KB_CHECK(tp_size >= 1 && tp_rank >= 0 && tp_rank < tp_size, "kb_set_tensor_parallel: bad rank %d of %d", tp_rank,
+             tp_size);
+    KB_CHECK(tp_size == 1 || fn != nullptr, "kb_set_tensor_parallel: tp_size > 1 needs an all-reduce callback");
+    e->tp_rank = tp_rank;
+    e->tp_size = tp_size;
+    e->allreduce = fn;
+    e->allreduce_ctx = ctx;
+    return KB_OK;
 }
 
 extern "C" int kb_profile_begin(kb_engine* e) {

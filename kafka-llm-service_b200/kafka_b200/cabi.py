@@ -20,7 +20,8 @@ KB_BLOCK_TOKENS = 64
 KB_MAX_SPLITS = 16
 KB_ABI_VERSION = 1
 PROF_CATS = ("embed", "rmsnorm", "gemm_qkv", "rope_append", "attention", "gemm_o", "gemm_gate_up", "gemm_down",
-             "lm_head", "sample")
+             "lm_head", "sample", "allreduce")
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
 
 EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_SWIGLU_BF16, EPI_SWIGLU_F16 = 0, 1, 2, 3, 4
 GEMM_F16 = 0x100  # OR into the epilogue: both operands are fp16 instead of bf16 (formats must match)
@@ -81,6 +82,7 @@ SIGNATURES = {
     "kb_attn_prefill": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                   _i32, _i32, _vp]),
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
+    "kb_set_tensor_parallel": (C.c_int, [_vp, _i32, _i32, ALLREDUCE_FN, _vp]),
     "kb_profile_begin": (C.c_int, [_vp]),
     "kb_profile_end": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "kb_last_error": (C.c_char_p, []),

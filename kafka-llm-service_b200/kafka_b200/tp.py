@@ -1,0 +1,151 @@
+"""Tensor parallelism for models that do not fit one GPU (BASELINE config 5: Llama-3-70B over 8 B200).
+
+Megatron-style sharding, one process per GPU:
+
+    wq / wk / wv, w_gate / w_up   column-parallel: each rank owns n_heads/tp query heads, n_kv_heads/tp
+                                  KV heads and ffn/tp MLP columns (rows of the [out, in] weight)
+    wo, w_down                    row-parallel: each rank owns the matching K-slice; the partial sums are
+                                  added over the ranks — 2 all-reduces of [T, hidden] fp32 per layer
+    embed, norms, lm_head         replicated (every rank samples the same token, no gather)
+    KV cache                      sharded by KV head: each rank stores only its heads' blocks
+
+The engine itself is TP-agnostic: it is created with the rank's LOCAL shapes and calls back into
+`TPGroup.allreduce` where the sums are needed (include/kafka_b200.h, kb_set_tensor_parallel). The
+all-reduce is NCCL over NVLink/NVSwitch through torch.distributed on the call's stream. All ranks
+issue identical kb_prefill / kb_decode calls (SPMD).
+
+The reference has no counterpart: its models run behind a gateway (/root/reference/src/llm/portkey.py:379).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import replace
+from typing import Dict, Optional
+
+import torch
+
+from . import cabi
+from .model_config import LlamaConfig
+from .weights import GEMM_WEIGHT_DTYPE, _randn, fuse_for_engine
+
+
+def local_config(cfg: LlamaConfig, tp: int) -> LlamaConfig:
+    """Shapes one rank's engine is built with."""
+    if tp == 1:
+        return cfg
+    if cfg.n_heads % tp or cfg.n_kv_heads % tp or cfg.ffn % (64 * tp):
+        raise ValueError(f"{cfg.name}: heads {cfg.n_heads}/{cfg.n_kv_heads} and ffn {cfg.ffn} must divide by tp={tp} "
+                         "(ffn/tp a multiple of 64)")
+    return replace(cfg, name=f"{cfg.name}/tp{tp}", n_heads=cfg.n_heads // tp, n_kv_heads=cfg.n_kv_heads // tp,
+                   ffn=cfg.ffn // tp)
+
+
+def shard_weights(cfg: LlamaConfig, w: Dict[str, torch.Tensor], rank: int, tp: int) -> Dict[str, torch.Tensor]:
+    """Canonical (unfused) weights of the full model -> the canonical weights of rank `rank`'s shard."""
+    if tp == 1:
+        return w
+    loc = local_config(cfg, tp)
+    q0, q1 = rank * loc.q_dim, (rank + 1) * loc.q_dim
+    k0, k1 = rank * loc.kv_dim, (rank + 1) * loc.kv_dim
+    f0, f1 = rank * loc.ffn, (rank + 1) * loc.ffn
+    out = {k: w[k] for k in ("embed", "final_norm", "lm_head")}
+    for i in range(cfg.n_layers):
+        p = f"l{i}."
+        out[p + "attn_norm"], out[p + "mlp_norm"] = w[p + "attn_norm"], w[p + "mlp_norm"]
+        out[p + "wq"] = w[p + "wq"][q0:q1]
+        out[p + "wk"] = w[p + "wk"][k0:k1]
+        out[p + "wv"] = w[p + "wv"][k0:k1]
+        out[p + "wo"] = w[p + "wo"][:, q0:q1].contiguous()
+        out[p + "w_gate"] = w[p + "w_gate"][f0:f1]
+        out[p + "w_up"] = w[p + "w_up"][f0:f1]
+        out[p + "w_down"] = w[p + "w_down"][:, f0:f1].contiguous()
+    return out
+
+
+def generate_sharded_on_device(cfg: LlamaConfig, seed: int, rank: int, tp: int, device) -> Dict[str, torch.Tensor]:
+    """Benchmark path for shapes too large for the host: every rank draws the FULL tensor of a layer on
+    its GPU from the same per-tensor seed, keeps its slice and frees the rest — ranks agree on the model
+    without any transfer."""
+    dev = str(device)
+    loc = local_config(cfg, tp)
+    H, F, f16 = cfg.hidden, cfg.ffn, GEMM_WEIGHT_DTYPE
+    out: Dict[str, torch.Tensor] = {
+        "embed": _randn((cfg.vocab, H), seed, "embed", 1.0, dev),
+        "final_norm": _randn((H,), seed, "final_norm", 0.1, dev, mean=1.0),
+        "lm_head": _randn((cfg.vocab, H), seed, "lm_head", 1.0 / (H ** 0.5), dev).to(f16),
+    }
+    q0, k0, f0 = rank * loc.q_dim, rank * loc.kv_dim, rank * loc.ffn
+    for i in range(cfg.n_layers):
+        p = f"l{i}."
+        out[p + "attn_norm"] = _randn((H,), seed, p + "attn_norm", 0.1, dev, mean=1.0)
+        out[p + "mlp_norm"] = _randn((H,), seed, p + "mlp_norm", 0.1, dev, mean=1.0)
+        wq = _randn((cfg.q_dim, H), seed, p + "wq", 0.02, dev)[q0:q0 + loc.q_dim]
+        wk = _randn((cfg.kv_dim, H), seed, p + "wk", 0.02, dev)[k0:k0 + loc.kv_dim]
+        wv = _randn((cfg.kv_dim, H), seed, p + "wv", 0.02, dev)[k0:k0 + loc.kv_dim]
+        out[p + "wqkv"] = torch.cat([wq, wk, wv], 0).to(f16).contiguous()
+        out[p + "wo"] = _randn((H, cfg.q_dim), seed, p + "wo", 0.02, dev)[:, q0:q0 + loc.q_dim].to(f16).contiguous()
+        g = _randn((F, H), seed, p + "w_gate", 0.02, dev)[f0:f0 + loc.ffn]
+        u = _randn((F, H), seed, p + "w_up", 0.02, dev)[f0:f0 + loc.ffn]
+        out[p + "w_gate_up"] = torch.stack([g, u], 1).reshape(2 * loc.ffn, H).to(f16).contiguous()
+        out[p + "w_down"] = _randn((H, F), seed, p + "w_down", 0.02, dev)[:, f0:f0 + loc.ffn].to(f16).contiguous()
+        del wq, wk, wv, g, u
+    return out
+
+
+class TPGroup:
+    """The all-reduce the engine calls back into: NCCL (torch.distributed) on the current stream."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.size = dist.get_world_size(group)
+        self.calls = 0
+        self.bytes = 0
+        self._views: Dict[int, torch.Tensor] = {}
+        self._ws: Optional[torch.Tensor] = None
+        self._cb = cabi.ALLREDUCE_FN(self._callback)   # keep the ctypes thunk alive
+
+    def attach(self, core) -> None:
+        """Bind to an EngineCore built with local_config(): registers the callback in the library."""
+        self._ws = core.workspace
+        cabi.check(core.lib.kb_set_tensor_parallel(core._h, self.rank, self.size, self._cb, None),
+                   "kb_set_tensor_parallel")
+
+    def _callback(self, ctx, buf, n, stream) -> int:
+        try:
+            ws = self._ws
+            off = int(buf) - ws.data_ptr()
+            key = (off, int(n))
+            t = self._views.get(key)
+            if t is None:
+                if off < 0 or off + 4 * n > ws.numel():
+                    return 1
+                t = self._views[key] = ws[off:off + 4 * n].view(torch.float32)
+            if torch.cuda.current_stream().cuda_stream != int(stream or 0):
+                return 2        # the collective must be ordered on the stream the kernels run on
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+            self.calls += 1
+            self.bytes += 4 * int(n)
+            return 0
+        except Exception:       # never let an exception cross the C boundary
+            return 3
+
+
+def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, max_tokens: int, max_seqs: int,
+                  weights: Optional[Dict[str, torch.Tensor]] = None, seed: int = 0, group=None):
+    """EngineCore of one tensor-parallel rank (+ its TPGroup). `weights`: canonical FULL weights (tests);
+    None draws the shard on the device (benchmarks)."""
+    from .engine_core import EngineCore
+    loc = local_config(cfg, tp)
+    if weights is not None:
+        fused = fuse_for_engine(loc, shard_weights(cfg, weights, rank, tp), device)
+    else:
+        fused = generate_sharded_on_device(cfg, seed, rank, tp, device)
+    core = EngineCore(loc, fused, device, n_blocks=n_blocks, max_tokens=max_tokens, max_seqs=max_seqs)
+    grp = None
+    if tp > 1:
+        grp = TPGroup(group)
+        grp.attach(core)
+    return core, grp

@@ -84,9 +84,20 @@ class KVCache:
 class OracleLlama:
     """fp32 forward. ``weights`` are the canonical bf16-representable tensors, widened to fp32."""
 
-    def __init__(self, cfg, weights: Dict[str, torch.Tensor]):
+    def __init__(self, cfg, weights: Dict[str, torch.Tensor], allreduce=None, tp_rank: int = 0):
+        """`allreduce` / `tp_rank`: tensor-parallel restatement. With a shard's local cfg and weights
+        (kafka_b200.tp.local_config / shard_weights) the two row-parallel projections yield partial sums;
+        `allreduce(t)` must return their sum over the ranks. Rank 0 folds the residual in, exactly like
+        the engine (kb_set_tensor_parallel)."""
         self.cfg = cfg
         self.w = {k: v.detach().to("cpu", torch.float32) for k, v in weights.items()}
+        self.allreduce = allreduce
+        self.tp_rank = tp_rank
+
+    def _residual(self, x: torch.Tensor, delta: torch.Tensor) -> torch.Tensor:
+        if self.allreduce is None:
+            return x + delta
+        return self.allreduce(delta + x if self.tp_rank == 0 else delta)
 
     def new_cache(self) -> KVCache:
         return KVCache(self.cfg.n_layers)
@@ -122,11 +133,11 @@ class OracleLlama:
             o = torch.einsum("htl,lhd->thd", a, V).reshape(T, cfg.q_dim)
             if taps is not None and i == 0:
                 taps["q0"], taps["attn0"] = q.clone(), o.clone()
-            x = x + o @ w[p + "wo"].T
+            x = self._residual(x, o @ w[p + "wo"].T)
             h = rmsnorm(x, w[p + "mlp_norm"], cfg.rms_eps)
             g = h @ w[p + "w_gate"].T
             u = h @ w[p + "w_up"].T
-            x = x + (torch.nn.functional.silu(g) * u) @ w[p + "w_down"].T
+            x = self._residual(x, (torch.nn.functional.silu(g) * u) @ w[p + "w_down"].T)
         xl = x if all_logits else x[-1:]
         logits = rmsnorm(xl, w["final_norm"], cfg.rms_eps) @ w["lm_head"].T
         return logits if all_logits else logits[0]
@@ -154,9 +165,10 @@ class OracleLlama:
                 qb = q[b].view(cfg.n_kv_heads, cfg.group, cfg.head_dim)
                 s = torch.einsum("kgd,lkd->kgl", qb, c.k(i)) * scale
                 o[b] = torch.einsum("kgl,lkd->kgd", torch.softmax(s, -1), c.v(i)).reshape(cfg.n_heads, cfg.head_dim)
-            x = x + o.view(B, cfg.q_dim) @ w[p + "wo"].T
+            x = self._residual(x, o.view(B, cfg.q_dim) @ w[p + "wo"].T)
             h = rmsnorm(x, w[p + "mlp_norm"], cfg.rms_eps)
-            x = x + (torch.nn.functional.silu(h @ w[p + "w_gate"].T) * (h @ w[p + "w_up"].T)) @ w[p + "w_down"].T
+            x = self._residual(x, (torch.nn.functional.silu(h @ w[p + "w_gate"].T) * (h @ w[p + "w_up"].T))
+                               @ w[p + "w_down"].T)
         return rmsnorm(x, w["final_norm"], cfg.rms_eps) @ w["lm_head"].T
 
     @torch.no_grad()
