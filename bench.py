@@ -64,6 +64,19 @@ def parse_args():
     return ap.parse_args()
 
 
+_JSON_FD = None   # the real stdout, when fd 1 has been pointed at stderr (see main)
+
+
+def emit(line) -> None:
+    """Print THE one JSON line on the real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def peaks():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -282,7 +295,7 @@ def run_reference(args, rank, world):
         "note": "reference's own path is a remote gateway call (src/llm/portkey.py:379), not runnable offline; "
                 "this arm is the CPU oracle port run on all host cores",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -499,7 +512,7 @@ def run_b200(args, rank, world, local_rank):
                         "frac_of_tensor_peak": prefill_flops / (prefill_ms / 1e3) / 1e12 / tf_peak,
                         "launches": l0 - launches0},
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
 
 
 def run_tp(args, rank, world, local_rank):
@@ -610,7 +623,7 @@ def run_tp(args, rank, world, local_rank):
         "kernels": {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]},
         "prefill": {"ms": prefill_ms, "tokens": B * U}, "cpu_baseline": None,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -626,6 +639,12 @@ def main():
         # NCCL is used for the barrier / max-over-ranks only; keep its version banner off stdout, which
         # must carry exactly one JSON line
         os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "WARN")
+        # ...and whatever native code still prints (the NCCL version banner does) goes to stderr: fd 1 is
+        # pointed at stderr for the rest of the run and the JSON line is written to the saved descriptor
+        global _JSON_FD
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
         torch.cuda.set_device(local_rank)
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
