@@ -264,6 +264,173 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): a cluster of two CTAs owns a 256 x BN output tile.
+//
+// Why: a 1-CTA 128 x BN tile moves 16 KB of A plus BN*128 B of B through its shared-memory port twice
+// per k-block (TMA in, tensor core out) and is bound by that port, not by the MMA (profiles/
+// r01_gemm_bench.md). In a pair each CTA stages its own 128 rows of A but only HALF of B (BN/2 rows);
+// the tensor cores of both SMs read both halves, so the traffic per CTA drops to 16 KB + BN*64 B for
+// twice the rows: balanced with the MMA at BN = 256.
+//
+//   * both CTAs : TMA producer (own A rows, own half of B), completion bytes counted on the LEADER's
+//                 full barrier; epilogue of their own 128 accumulator rows (own TMEM).
+//   * leader    : the one MMA-issuing thread (tcgen05.mma.cta_group::2, M = 256); its commits arrive on
+//                 the slot-free and accumulator-full barriers of BOTH CTAs (multicast).
+//   * accumulator-free: the epilogue warps of both CTAs arrive on the leader's barrier (8 arrivals).
+// ---------------------------------------------------------------------------------------------
+template <int BN>
+struct Gemm2Cfg {
+    static constexpr int HALF_N = BN / 2;                       // B rows staged by one CTA
+    static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
+    static constexpr int B_BYTES = HALF_N * GEMM_BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;       // per CTA
+    static constexpr int STAGES = (BN == 256) ? 6 : 8;          // 192 KB either way
+    static constexpr int TMEM_COLS = 2 * BN;                    // double-buffered accumulator
+    static constexpr int BAR_BYTES = 256;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
+};
+
+template <int BN, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, void* out,
+                         const float* resid, int M, int N, int K, uint32_t is_bf16) {
+    using Cfg = Gemm2Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + Cfg::STAGES;
+    uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t cta = cluster_ctarank();          // 0 = leader
+    const int cluster_id = blockIdx.x >> 1;
+    const int num_clusters = gridDim.x >> 1;
+    const int num_mp = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
+    const int num_n = (N + BN - 1) / BN;
+    const int num_tiles = num_mp * num_n;
+    const int num_k = K / GEMM_BK;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            tma_prefetch_desc(&tmA);
+            tma_prefetch_desc(&tmB);
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            for (int s = 0; s < Cfg::STAGES; ++s) {
+                mbar_init(&full_bar[s], 1);      // leader's producer arms it; both CTAs' TMA bytes land on it
+                mbar_init(&empty_bar[s], 1);     // one multicast commit per use
+            }
+            for (int a = 0; a < 2; ++a) {
+                mbar_init(&tmem_full_bar[a], 1);
+                mbar_init(&tmem_empty_bar[a], 8);    // 4 epilogue warps x 2 CTAs (only the leader's is waited on)
+            }
+            fence_mbar_init();
+        }
+    } else if (warp == 2) {
+        tmem_alloc_2cta(tmem_slot, Cfg::TMEM_COLS);
+        tmem_relinquish_2cta();
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                              // peer barriers are initialised before anyone signals them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs) =====
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                const int mp = tile % num_mp;
+                const int n_blk = tile / num_mp;
+                const int row0 = mp * 2 * GEMM_BM + (int)cta * GEMM_BM;        // this CTA's 128 rows of A
+                const int nrow0 = n_blk * BN + (int)cta * Cfg::HALF_N;         // this CTA's half of B
+                for (int kb = 0; kb < num_k; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+                    uint8_t* sb = sa + Cfg::A_BYTES;
+                    if (cta == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+                    tma_load_2d_2cta(sa, &tmA, kb * GEMM_BK, row0, &full_bar[stage]);
+                    tma_load_2d_2cta(sb, &tmB, kb * GEMM_BK, nrow0, &full_bar[stage]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (cta == 0 && elect_one()) {
+            const uint32_t idesc = make_idesc(2 * GEMM_BM, BN, is_bf16);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = 0; kb < num_k; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+                    const uint64_t adesc = make_sw128_kmajor_desc(sa);
+                    const uint64_t bdesc = make_sw128_kmajor_desc(sa + Cfg::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k) {
+                        umma_f16_2cta(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                                      (uint32_t)((kb | k) != 0));
+                    }
+                    umma_commit_2cta(&empty_bar[stage]);
+                    if (kb == num_k - 1) umma_commit_2cta(&tmem_full_bar[acc]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue (both CTAs): own 128 rows =====
+        const int ew = warp - 4;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+            const int mp = tile % num_mp;
+            const int n_blk = tile / num_mp;
+            mbar_wait(&tmem_full_bar[acc], acc_phase);
+            tc_fence_after();
+            const int row = mp * 2 * GEMM_BM + (int)cta * GEMM_BM + ew * 32 + lane;
+            const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(t_row + (uint32_t)c, r);
+                tmem_ld_wait();
+                const int col0 = n_blk * BN + c;
+                if (row < M && col0 < N) epilogue_store32<EPI>(r, out, resid, row, col0, N);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[acc], 0);   // the leader's barrier
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();                              // nobody leaves while the peer may still touch its smem / TMEM
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc_2cta(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
@@ -363,14 +530,52 @@ static int dispatch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, void* ou
     return KB_ERR_INVALID;
 }
 
-// Tile width: minimise (tiles per busiest CTA) x BN under the static persistent schedule.
+template <int BN, int EPI>
+static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
+                            int N, int K, uint32_t is_bf16, cudaStream_t stream) {
+    using Cfg = Gemm2Cfg<BN>;
+    static bool configured[64] = {};
+    auto kern = gemm_tcgen05_2cta_kernel<BN, EPI>;
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    const int num_tiles = ((M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((N + BN - 1) / BN);
+    const int max_clusters = num_sms() / 2;
+    const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+    kern<<<2 * clusters, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K, is_bf16);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+template <int BN>
+static int dispatch_epi_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
+                             int N, int K, int epi, uint32_t ab, cudaStream_t stream) {
+    switch (epi) {
+        case KB_EPI_BF16: return launch_gemm_2cta<BN, KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_F32: return launch_gemm_2cta<BN, KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_RESID_F32: return launch_gemm_2cta<BN, KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_SWIGLU_BF16:
+            return launch_gemm_2cta<BN, KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_SWIGLU_F16:
+            return launch_gemm_2cta<BN, KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+    }
+    set_error("kb_gemm: unknown epilogue %d", epi);
+    return KB_ERR_INVALID;
+}
+
+// Tile choice: minimise the time of the busiest CTA (or CTA pair) under the static persistent schedule.
+// Returns BN for the 1-CTA kernel, -BN for the CTA-pair kernel.
 static int pick_bn(int M, int N) {
     static int forced = -1;
     if (forced < 0) {
         const char* s = getenv("KB_GEMM_BN");
         forced = s ? atoi(s) : 0;
     }
-    if (forced == 64 || forced == 128 || forced == 256) return forced;
+    if (forced == 64 || forced == 128 || forced == 256 || forced == -128 || forced == -256) return forced;
     const int sms = num_sms();
     const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
     long best_cost = -1;
@@ -388,6 +593,21 @@ static int pick_bn(int M, int N) {
         const long cost = per_cta * (256 + 2 * bn);
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
     }
+    if (M > GEMM_BM) {
+        // CTA pair, 256 x bn tile: each CTA stages 16 KB of A and bn*64 B of B per k-block -> 256 + bn
+        // cycles of shared-memory port against 2 bn cycles of MMA
+        const int num_mp = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
+        const int pairs = sms / 2;
+        const int cands2[2] = {256, 128};
+        for (int i = 0; i < 2; ++i) {
+            const int bn = cands2[i];
+            const long tiles = (long)num_mp * ((N + bn - 1) / bn);
+            const long per_pair = (tiles + pairs - 1) / pairs;
+            const long kblock = (2 * bn > 256 + bn) ? 2 * bn : 256 + bn;
+            const long cost = per_pair * kblock;
+            if (cost < best_cost) { best_cost = cost; best = -bn; }
+        }
+    }
     return best;
 }
 
@@ -404,12 +624,18 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     KB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(out) & 15) == 0,
              "kb_gemm: pointers must be 16-byte aligned");
-    KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256, "kb_gemm: tile_n=%d not in {0,64,128,256}",
-             tile_n);
+    KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256 || tile_n == -128 || tile_n == -256,
+             "kb_gemm: tile_n=%d not in {0, 64, 128, 256, -128, -256}", tile_n);
     const int bn = tile_n ? tile_n : pick_bn(M, N);
     CUtensorMap tmA, tmB;
     int rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, GEMM_BM, &tmA);
     if (rc) return rc;
+    if (bn < 0) {   // CTA pair: every CTA stages half of the tile's B rows
+        rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)(-bn / 2), &tmB);
+        if (rc) return rc;
+        if (bn == -256) return dispatch_epi_2cta<256>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);
+        return dispatch_epi_2cta<128>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);
+    }
     rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)bn, &tmB);
     if (rc) return rc;
     if (bn == 256) return dispatch_epi<256>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);

@@ -59,7 +59,7 @@ GEMM_SHAPES = [
 ]
 
 
-@pytest.mark.parametrize("tile_n", [0, 64, 128, 256])
+@pytest.mark.parametrize("tile_n", [0, 64, 128, 256, -128, -256])
 @pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
 def test_gemm_bf16(kb, cuda, M, N, K, tile_n):
     g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
@@ -70,7 +70,7 @@ def test_gemm_bf16(kb, cuda, M, N, K, tile_n):
     torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
 
 
-@pytest.mark.parametrize("tile_n", [64, 128, 256])
+@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256])
 @pytest.mark.parametrize("M,N,K", [(17, 136, 192), (300, 1000, 320), (512, 4096, 1024)])
 def test_gemm_f32_and_residual(kb, cuda, M, N, K, tile_n):
     g = torch.Generator(device="cpu").manual_seed(M + N + K)
@@ -89,7 +89,7 @@ def test_gemm_f32_and_residual(kb, cuda, M, N, K, tile_n):
     torch.testing.assert_close(r2, want, rtol=2e-3, atol=2e-3)
 
 
-@pytest.mark.parametrize("tile_n", [64, 128, 256])
+@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256])
 @pytest.mark.parametrize("M,F,K", [(17, 80, 192), (300, 512, 256), (512, 1408, 1024)])
 def test_gemm_swiglu(kb, cuda, M, F, K, tile_n):
     g = torch.Generator(device="cpu").manual_seed(M + F + K)
@@ -102,7 +102,7 @@ def test_gemm_swiglu(kb, cuda, M, F, K, tile_n):
     torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
 
 
-@pytest.mark.parametrize("tile_n", [64, 128, 256])
+@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256])
 def test_gemm_fp16_operands(kb, cuda, tile_n):
     """The hot path's operand format: A (activations) and W (bf16 values re-encoded as fp16) both fp16,
     fp32 accumulate. The fp32 epilogue must match an fp32 matmul of the same values to
