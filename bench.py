@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--no-provider", action="store_true", help="skip the provider-level (plugin API) turn")
     ap.add_argument("--gen-tokens", type=int, default=128, help="new tokens per turn in the provider-level leg")
     ap.add_argument("--no-ttft-sweep", action="store_true")
+    ap.add_argument("--no-pipeline", action="store_true",
+                    help="serving loop reads every step back before enqueueing the next (A/B of the pipelined loop)")
     ap.add_argument("--tp", action="store_true",
                     help="tensor-parallel: ONE model sharded over all ranks (config 5: --model llama-3-70b --history 8192)")
     return ap.parse_args()
@@ -183,7 +185,8 @@ def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1):
 
 
 # ------------------------------------------------------------------------------------------------
-def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen_tokens: int, seed: int):
+def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen_tokens: int, seed: int,
+                  pipeline: bool = True):
     """The call a user makes: B200LLMProvider.stream_completion for `n_threads` concurrent threads.
 
     Untimed set-up: every thread's ~`history`-token conversation is prefilled once through the provider
@@ -204,7 +207,7 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
     stepper = GpuStepper(core, tok, generable_only=True)
     stepper.banned_token = tok.eot_id                   # EOS masked: every turn generates gen_tokens tokens
     stepper.close = lambda: None                        # the core outlives this leg
-    engine = Engine(stepper, max_prefill_tokens=core.max_tokens)
+    engine = Engine(stepper, max_prefill_tokens=core.max_tokens, pipeline=pipeline)
     provider = B200LLMProvider(engine, tok, model=cfg.name, default_temperature=0.0)
 
     def text(rnd, n):
@@ -265,7 +268,8 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
             "prefilled_new_tokens": prompt - cached, "setup_prefill_s": setup_s,
             "engine_prefill_s": s1["prefill_s"] - stats0["prefill_s"], "engine_decode_s": s1["decode_s"] - stats0["decode_s"],
             "api": "B200LLMProvider.stream_completion (LLMProvider plugin API), one coroutine per thread, "
-                   "pinned H2D of token ids / block tables and D2H of sampled ids every step",
+                   "pinned H2D of step inputs (ctx lens, block tables on membership change) and D2H of sampled "
+                   "ids every step",
         }
 
     try:
@@ -466,7 +470,8 @@ def run_b200(args, rank, world, local_rank):
     e2e_cabi = e2e
     if not args.no_provider:
         barrier()
-        pt = provider_turn(eng, cfg, B, args.history, U, args.gen_tokens, seed=rank)
+        pt = provider_turn(eng, cfg, B, args.history, U, args.gen_tokens, seed=rank, pipeline=not args.no_pipeline)
+        pt["pipelined_loop"] = not args.no_pipeline
         wall = pt["wall_s"]
         if world > 1:
             t = torch.tensor([wall], device=dev)

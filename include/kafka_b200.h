@@ -247,6 +247,14 @@ int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void* k_pool_lay
 int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,
               int32_t* out_tokens, kb_stream stream);
 
+/* Device-side hand-over of sampled ids between two decode steps, so that step N+1 can be enqueued
+ * while step N is still running: dst[i] = prev_out[src_index[i]] where 0 <= src_index[i] < n_prev
+ * (sequence i was in step N's batch at that slot); other dst[i] keep what the host staged (sequences
+ * that just left prefill).  Reference counterpart: none — the reference awaits one HTTP response per
+ * call (/root/reference/src/llm/portkey.py:379) and has no step pipeline. */
+int kb_select_tokens(int32_t* dst, const int32_t* prev_out, const int32_t* src_index, int32_t n,
+                     int32_t n_prev, kb_stream stream);
+
 /* ---- diagnostics ------------------------------------------------------------------------------- */
 /* Per-kernel timing of the hot path with CUDA events recorded on the call's own stream between
  * launches (bench.py's roofline numbers).  kb_profile_begin arms it; every kb_prefill / kb_decode

@@ -229,8 +229,28 @@ sample_kernel(const float* __restrict__ logits, int vocab, float temperature, ui
 }
 
 // ---------------------------------------------------------------------------------------------
+// select_tokens: next step's input ids without a host round trip. dst[i] = prev_out[src[i]] where
+// src[i] >= 0 (the id sampled by the step still in flight), else dst[i] keeps the id the host staged.
+// ---------------------------------------------------------------------------------------------
+__global__ void select_tokens_kernel(int* __restrict__ dst, const int* __restrict__ prev_out,
+                                     const int* __restrict__ src, int n, int n_prev) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int s = src[i];
+    if (s >= 0 && s < n_prev) dst[i] = prev_out[s];
+}
+
+// ---------------------------------------------------------------------------------------------
 // host launchers
 // ---------------------------------------------------------------------------------------------
+int select_tokens(int* dst, const int* prev_out, const int* src, int n, int n_prev, cudaStream_t stream) {
+    KB_CHECK(n > 0 && n_prev > 0 && dst && prev_out && src, "kb_select_tokens: bad arguments");
+    select_tokens_kernel<<<(n + 255) / 256, 256, 0, stream>>>(dst, prev_out, src, n, n_prev);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
 int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, int vocab, cudaStream_t stream) {
     KB_CHECK(n > 0 && hidden % 8 == 0, "kb_embed: bad shape n=%d hidden=%d", n, hidden);
     embed_kernel<<<n, 256, 0, stream>>>(tokens, (const __nv_bfloat16*)embed_w, x, hidden, vocab);
@@ -303,4 +323,8 @@ extern "C" int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const i
 extern "C" int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,
                          int32_t* out_tokens, kb_stream stream) {
     return kb::sample(logits, n_seqs, vocab, sampling, out_tokens, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int kb_select_tokens(int32_t* dst, const int32_t* prev_out, const int32_t* src_index, int32_t n,
+                                int32_t n_prev, kb_stream stream) {
+    return kb::select_tokens(dst, prev_out, src_index, n, n_prev, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -82,6 +82,7 @@ SIGNATURES = {
     "kb_attn_prefill": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                   _i32, _i32, _vp]),
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
+    "kb_select_tokens": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp]),
     "kb_set_tensor_parallel": (C.c_int, [_vp, _i32, _i32, ALLREDUCE_FN, _vp]),
     "kb_profile_begin": (C.c_int, [_vp]),
     "kb_profile_end": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
@@ -264,3 +265,10 @@ def sample(logits, temperature: float = 0.0, seed: int = 0, step: int = 0, banne
     sp = make_sampling(temperature, seed, step, banned_token, allowed_lo, allowed_hi, extra_a, extra_b)
     check(load().kb_sample(_ptr(logits), n, vocab, C.byref(sp), _ptr(out), _stream()), "kb_sample")
     return out
+
+
+def select_tokens(dst, prev_out, src_index, stream=None):
+    """dst[i] = prev_out[src_index[i]] where src_index[i] >= 0 (device int32 tensors; in place)."""
+    check(load().kb_select_tokens(_ptr(dst), _ptr(prev_out), _ptr(src_index), dst.numel(), prev_out.numel(),
+                                  _stream() if stream is None else stream), "kb_select_tokens")
+    return dst

@@ -4,6 +4,10 @@ the arithmetic (through a Stepper) with continuous batching.
     asyncio coroutines --submit()--> inbox --engine thread--> admit -> packed incremental prefill
         -> batched decode step -> sampled ids D2H (pinned) -> per-request callbacks
 
+The loop is a two-stage pipeline: iteration k's prefill + decode are enqueued before iteration k-1's
+sampled ids are read back, the ids a step needs from its predecessor being handed over on the device
+(kb_select_tokens). A conversation that stops on EOS therefore costs at most two discarded steps.
+
 Callbacks are invoked on the engine thread; the provider trampolines them onto its event loop with
 ``loop.call_soon_threadsafe``. The CUDA calls release the GIL (ctypes), so the event loop keeps
 running while the GPU works.
@@ -24,29 +28,62 @@ from .scheduler import ContextLengthError, PrefillItem, Request, SamplingParams,
 
 class Stepper:
     """What the engine needs from the arithmetic side. gpu_stepper.GpuStepper binds the C ABI; tests
-    bind a deterministic fake to exercise the host logic without a GPU."""
+    bind a deterministic fake to exercise the host logic without a GPU.
+
+    Work is ENQUEUED with *_launch and its sampled ids are read back later with fetch(), so that the
+    engine can enqueue step N+1 while step N runs. Results live in numbered slots of a buffer the
+    stepper owns (see slot()): a conversation whose newest id is still in flight (Request.inflight >
+    0) is fed from Request.out_slot on the device, everything else from Request.generated[-1]."""
     max_seqs: int
     max_tokens: int
     n_blocks: int
     max_pos: int
     eos_id: int
 
-    def prefill(self, items: List[PrefillItem]) -> List[Optional[int]]:
+    def slot(self, parity: int, is_prefill: bool, i: int) -> int:
+        """Result slot of item i of the prefill / decode call enqueued with this parity (0 or 1; the
+        engine alternates, so a slot is rewritten only after the step that read it has retired)."""
+        return (parity * 2 + (1 if is_prefill else 0)) * self.max_seqs + i
+
+    def prefill_launch(self, items: List[PrefillItem], parity: int):
         raise NotImplementedError
 
-    def decode(self, reqs: List[Request]) -> List[int]:
+    def decode_launch(self, reqs: List[Request], parity: int):
         raise NotImplementedError
+
+    def fetch(self, handle) -> List[Optional[int]]:
+        """Wait for that call and return its ids (None for prefill items that are not a last chunk)."""
+        raise NotImplementedError
+
+    def prefill(self, items: List[PrefillItem]) -> List[Optional[int]]:
+        return self.fetch(self.prefill_launch(items, 0))
+
+    def decode(self, reqs: List[Request]) -> List[int]:
+        return self.fetch(self.decode_launch(reqs, 0))
 
     def close(self) -> None:
         pass
+
+
+class _Flight:
+    """One loop iteration's enqueued work, retired (read back) during the next iteration."""
+    __slots__ = ("items", "prefill_handle", "reqs", "decode_handle")
+
+    def __init__(self):
+        self.items: List[PrefillItem] = []
+        self.prefill_handle = None
+        self.reqs: List[Request] = []
+        self.decode_handle = None
 
 
 class Engine:
     """Serving loop of one replica. Thread-safe entry points: submit(), Request.cancelled = True,
     shutdown(), stats(). Everything else runs on the engine thread."""
 
-    def __init__(self, stepper: Stepper, max_prefill_tokens: Optional[int] = None, name: str = "kb-engine"):
+    def __init__(self, stepper: Stepper, max_prefill_tokens: Optional[int] = None, name: str = "kb-engine",
+                 pipeline: bool = True):
         self.stepper = stepper
+        self.pipeline = pipeline   # False: read every step back before enqueueing the next (for A/B timing)
         self.sched = Scheduler(n_blocks=stepper.n_blocks, max_pos=stepper.max_pos, eos_id=stepper.eos_id,
                                max_seqs=stepper.max_seqs,
                                max_prefill_tokens=max_prefill_tokens or stepper.max_tokens)
@@ -117,26 +154,57 @@ class Engine:
             except queue.Empty:
                 return
 
+    def _launch(self, parity: int) -> Optional[_Flight]:
+        sched, st = self.sched, self.stepper
+        f = _Flight()
+        f.items = sched.next_prefill_batch()
+        if f.items:
+            t0 = time.perf_counter()
+            f.prefill_handle = st.prefill_launch(f.items, parity)
+            sched.on_prefill_launched(f.items, [st.slot(parity, True, i) for i in range(len(f.items))])
+            self.timing["prefill_s"] += time.perf_counter() - t0
+            self.timing["prefill_tokens"] += sum(len(i.tokens) for i in f.items)
+        f.reqs = sched.next_decode_batch()   # includes conversations whose last prefill chunk was just enqueued
+        if f.reqs:
+            t0 = time.perf_counter()
+            f.decode_handle = st.decode_launch(f.reqs, parity)
+            sched.on_decode_launched(f.reqs, [st.slot(parity, False, i) for i in range(len(f.reqs))])
+            self.timing["decode_s"] += time.perf_counter() - t0
+            self.timing["decode_tokens"] += len(f.reqs)
+        return f if (f.items or f.reqs) else None
+
+    def _retire(self, f: _Flight) -> None:
+        sched, st = self.sched, self.stepper
+        if f.items:
+            t0 = time.perf_counter()
+            sampled = st.fetch(f.prefill_handle)
+            self.timing["prefill_s"] += time.perf_counter() - t0
+            sched.on_prefill_done(f.items, sampled)
+        if f.reqs:
+            t0 = time.perf_counter()
+            sampled = st.fetch(f.decode_handle)
+            self.timing["decode_s"] += time.perf_counter() - t0
+            sched.on_decode_done(f.reqs, sampled)
+
     def _run(self) -> None:
+        """Enqueue iteration k's work, then read iteration k-1's results back while the GPU runs k: the
+        host-side token handling (callbacks, stop checks, admission) is hidden behind GPU time."""
         sched = self.sched
+        pending: Optional[_Flight] = None
+        parity = 0
         try:
             while not self._stop.is_set():
-                self._drain(block=sched.idle())
+                self._drain(block=sched.idle() and pending is None)
                 sched.admit()
-                items = sched.next_prefill_batch()
-                if items:
-                    t0 = time.perf_counter()
-                    sampled = self.stepper.prefill(items)
-                    self.timing["prefill_s"] += time.perf_counter() - t0
-                    self.timing["prefill_tokens"] += sum(len(i.tokens) for i in items)
-                    sched.on_prefill_done(items, sampled)
-                reqs = sched.next_decode_batch()
-                if reqs:
-                    t0 = time.perf_counter()
-                    sampled = self.stepper.decode(reqs)
-                    self.timing["decode_s"] += time.perf_counter() - t0
-                    self.timing["decode_tokens"] += len(reqs)
-                    sched.on_decode_done(reqs, sampled)
+                flight = self._launch(parity)
+                if flight is not None:
+                    parity ^= 1
+                if pending is not None:
+                    self._retire(pending)
+                pending = flight
+                if not self.pipeline and pending is not None:
+                    self._retire(pending)
+                    pending = None
         except BaseException as e:  # never die silently: fail every pending request
             self._error = e
             for r in sched.waiting + sched.prefilling + sched.running:

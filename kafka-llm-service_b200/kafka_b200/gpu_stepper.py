@@ -2,9 +2,14 @@
 
 Per call it stages the small integer arguments (token ids, cu_seqlens, ctx_lens, block tables,
 per-sequence sampling parameters) in pinned host memory, copies them to persistent device buffers on
-its own stream, launches the call, and brings the sampled ids back through pinned memory. PyTorch
+its own stream, enqueues the call, and brings the sampled ids back through pinned memory. PyTorch
 is the allocator and stream provider only. Block tables and sampling arrays are re-uploaded only when
-the batch membership changes (decode steps of a stable batch upload 2 x B ints).
+the batch membership changes (decode steps of a stable batch upload B ints).
+
+Nothing here waits for the GPU except fetch(): *_launch only enqueues, and the ids a decode step needs
+from a step that has not been read back yet are taken on the device from the result slots
+(kb_select_tokens). There are two staging sets per path, alternated by the engine's parity, so the host
+never rewrites pinned memory that an enqueued copy may still read.
 
 Reference counterpart: none (the reference awaits a network call, /root/reference/src/llm/portkey.py:379).
 """
@@ -34,9 +39,11 @@ class _Staging:
         self.h_bt, self.d_bt = pair(S * max_blocks, i32)
         self.h_temp, self.d_temp = pair(S, torch.float32)
         self.h_seed, self.d_seed = pair(S, torch.int64)
-        self.h_out, self.d_out = pair(S, i32)
+        self.h_src, self.d_src = pair(S, i32)
         self.bt_key = None
         self.sp_key = None
+        self.src_key = None
+        self.event = torch.cuda.Event()
 
     @staticmethod
     def _up(h, d, values, dtype, torch):
@@ -45,10 +52,10 @@ class _Staging:
         d[:n].copy_(h[:n], non_blocking=True)
         return d[:n]
 
-    def stage(self, tokens: List[int], cu: Optional[List[int]], ctx: List[int], reqs: Sequence[Request]):
+    def stage(self, tokens: Optional[List[int]], cu: Optional[List[int]], ctx: List[int], reqs: Sequence[Request]):
         torch = self.torch
         n = len(reqs)
-        d_tok = self._up(self.h_tok, self.d_tok, tokens, torch.int32, torch)
+        d_tok = self._up(self.h_tok, self.d_tok, tokens, torch.int32, torch) if tokens is not None else self.d_tok[:n]
         d_cu = self._up(self.h_cu, self.d_cu, cu, torch.int32, torch) if cu is not None else None
         d_ctx = self._up(self.h_ctx, self.d_ctx, ctx, torch.int32, torch)
         key = tuple((r.req_id, len(r.entry.blocks)) for r in reqs)
@@ -70,6 +77,20 @@ class _Staging:
             self.sp_key = key
         return d_tok, d_cu, d_ctx, self.d_bt[:n * mb].view(n, mb)
 
+    def stage_src(self, src: List[int]):
+        """Result slots the in-flight conversations' ids come from (-1: the host staged the id)."""
+        if src != self.src_key:
+            self._up(self.h_src, self.d_src, src, self.torch.int32, self.torch)
+            self.src_key = src
+        return self.d_src[:len(src)]
+
+
+class _Handle:
+    __slots__ = ("event", "base", "n", "last")
+
+    def __init__(self, event, base, n, last):
+        self.event, self.base, self.n, self.last = event, base, n, last
+
 
 class GpuStepper(Stepper):
     def __init__(self, core, tokenizer, generable_only: bool = True):
@@ -82,8 +103,12 @@ class GpuStepper(Stepper):
         self.max_pos, self.eos_id = cfg.max_pos, tokenizer.eot_id
         self.max_blocks = (cfg.max_pos + BLOCK_TOKENS - 1) // BLOCK_TOKENS
         self.stream = torch.cuda.Stream(device=core.device)
-        self.st_prefill = _Staging(torch, core.device, core.max_tokens, core.max_seqs, self.max_blocks)
-        self.st_decode = _Staging(torch, core.device, core.max_seqs, core.max_seqs, self.max_blocks)
+        S = core.max_seqs
+        self.st_prefill = [_Staging(torch, core.device, core.max_tokens, S, self.max_blocks) for _ in range(2)]
+        self.st_decode = [_Staging(torch, core.device, S, S, self.max_blocks) for _ in range(2)]
+        # result slots (Stepper.slot): [parity][decode | prefill][max_seqs] sampled ids
+        self.d_res = torch.zeros(4 * S, dtype=torch.int32, device=core.device)
+        self.h_res = torch.zeros(4 * S, dtype=torch.int32, pin_memory=True)
         self.step_no = 0
         lo, hi, nl, eot = tokenizer.generable_range()
         self.cand = (lo, hi, nl, eot) if generable_only else (0, 0, -1, -1)
@@ -99,14 +124,24 @@ class GpuStepper(Stepper):
                                        allowed_hi=hi, extra_a=ea, extra_b=eb, seq_temperature=st.d_temp,
                                        seq_seed=st.d_seed)
 
-    def _fetch(self, st: _Staging, n: int) -> List[int]:
-        st.h_out[:n].copy_(st.d_out[:n], non_blocking=True)
-        self.stream.synchronize()
-        self.d2h_bytes += 4 * n
-        return st.h_out[:n].tolist()
+    def _finish_launch(self, st: _Staging, base: int, n: int, last) -> _Handle:
+        if n:
+            self.h_res[base:base + n].copy_(self.d_res[base:base + n], non_blocking=True)
+            self.d2h_bytes += 4 * n
+        st.event.record(self.stream)
+        return _Handle(st.event, base, n, last)
 
-    def prefill(self, items: List[PrefillItem]) -> List[Optional[int]]:
-        st = self.st_prefill
+    def fetch(self, h: _Handle) -> List[Optional[int]]:
+        h.event.synchronize()
+        if h.last is None:                      # decode step: one id per sequence
+            return self.h_res[h.base:h.base + h.n].tolist()
+        if not h.n:
+            return [None] * len(h.last)
+        out = self.h_res[h.base:h.base + h.n].tolist()
+        return [out[i] if is_last else None for i, is_last in enumerate(h.last)]
+
+    def prefill_launch(self, items: List[PrefillItem], parity: int) -> _Handle:
+        st = self.st_prefill[parity]
         with self.torch.cuda.stream(self.stream):
             toks: List[int] = []
             cu = [0]
@@ -116,23 +151,28 @@ class GpuStepper(Stepper):
             reqs = [it.req for it in items]
             d_tok, d_cu, d_ctx, d_bt = st.stage(toks, cu, [it.ctx_len for it in items], reqs)
             self.h2d_bytes += 4 * (len(toks) + 2 * len(items) + 1)
-            need = any(it.is_last_chunk for it in items)
+            last = [it.is_last_chunk for it in items]
+            n = len(items) if any(last) else 0
+            base = self.slot(parity, True, 0)
             self.core.prefill(d_tok, d_cu, d_ctx, d_bt, max(len(it.tokens) for it in items), self._sampling(st),
-                              None, st.d_out[:len(items)] if need else None)
-            if not need:
-                self.stream.synchronize()
-                return [None] * len(items)
-            out = self._fetch(st, len(items))
-        return [out[i] if it.is_last_chunk else None for i, it in enumerate(items)]
+                              None, self.d_res[base:base + n] if n else None)
+            return self._finish_launch(st, base, n, last)
 
-    def decode(self, reqs: List[Request]) -> List[int]:
-        st = self.st_decode
+    def decode_launch(self, reqs: List[Request], parity: int) -> _Handle:
+        st = self.st_decode[parity]
+        n = len(reqs)
         with self.torch.cuda.stream(self.stream):
             ctx = [r.ctx_len for r in reqs]
-            d_tok, _, d_ctx, d_bt = st.stage([r.generated[-1] for r in reqs], None, ctx, reqs)
-            self.h2d_bytes += 8 * len(reqs)
-            self.core.decode(d_tok, d_ctx, d_bt, self._sampling(st), st.d_out[:len(reqs)], max_ctx=max(ctx))
-            return self._fetch(st, len(reqs))
+            src = [r.out_slot if r.inflight > 0 else -1 for r in reqs]
+            n_dev = n - src.count(-1)
+            toks = None if n_dev == n else [r.generated[-1] if r.inflight == 0 else 0 for r in reqs]
+            d_tok, _, d_ctx, d_bt = st.stage(toks, None, ctx, reqs)
+            self.h2d_bytes += 4 * n + (4 * n if toks is not None else 0)
+            if n_dev:
+                self.cabi.select_tokens(d_tok, self.d_res, st.stage_src(src))
+            base = self.slot(parity, False, 0)
+            self.core.decode(d_tok, d_ctx, d_bt, self._sampling(st), self.d_res[base:base + n], max_ctx=max(ctx))
+            return self._finish_launch(st, base, n, None)
 
     def close(self) -> None:
         self.core.close()

@@ -215,16 +215,21 @@ class Request:
     on_event: Callable[[Tuple], None]     # ("token", id) | ("finish", reason, usage) | ("error", exc)
     entry: Optional[KVEntry] = None
     n_cached: int = 0                      # prompt tokens served from resident KV
-    n_prefilled: int = 0                   # prompt tokens whose KV is resident now (>= n_cached)
+    n_prefilled: int = 0                   # prompt tokens whose KV is known to be resident (>= n_cached)
+    n_launched: int = 0                    # prompt tokens whose prefill has been enqueued (>= n_prefilled)
+    inflight: int = 0                      # sampled ids enqueued on the GPU and not read back yet
+    out_slot: int = -1                     # result slot (Stepper.slot) of the newest in-flight id
     generated: List[int] = field(default_factory=list)
     cancelled: bool = False
+    done: bool = False                     # finished or released: results still in flight are dropped
     t_submit: float = 0.0
     t_first: Optional[float] = None
 
     @property
     def ctx_len(self) -> int:
-        """Tokens whose KV is resident for this request right now."""
-        return self.n_prefilled + max(0, len(self.generated) - 1)
+        """Position of the next token to feed = tokens whose KV is resident or enqueued to become so
+        (every id still in flight will have been fed by the time a newly enqueued step runs)."""
+        return self.n_launched + max(0, len(self.generated) + self.inflight - 1)
 
 
 @dataclass
@@ -333,49 +338,76 @@ class Scheduler:
             entry.tokens = list(req.prompt[:lcp])
             entry.busy = True
             req.entry = entry
-            req.n_cached = req.n_prefilled = lcp
+            req.n_cached = req.n_prefilled = req.n_launched = lcp
             self.stats["prompt_tokens"] += len(req.prompt)
             self.stats["cached_tokens"] += lcp
             self.prefilling.append(req)
         self.waiting = still
 
     # ---- batching ----------------------------------------------------------------------------
+    # The engine enqueues a step (next_*_batch -> Stepper.*_launch -> on_*_launched) and reads its
+    # results back one iteration later (Stepper.fetch -> on_*_done), after the following step has been
+    # enqueued. Everything the next launch needs (positions, membership) is therefore derived from
+    # launch-time counters; sampled ids are only needed on the host to detect EOS / stop conditions.
     def next_prefill_batch(self) -> List[PrefillItem]:
         items: List[PrefillItem] = []
         budget = self.max_prefill_tokens
         for req in self.prefilling:
             if req.cancelled or budget <= 0:
                 continue
-            remaining = len(req.prompt) - req.n_prefilled
+            remaining = len(req.prompt) - req.n_launched
             n = min(remaining, budget)
-            items.append(PrefillItem(req, req.prompt[req.n_prefilled:req.n_prefilled + n], req.n_prefilled,
+            if n <= 0:
+                continue
+            items.append(PrefillItem(req, req.prompt[req.n_launched:req.n_launched + n], req.n_launched,
                                      n == remaining))
             budget -= n
         return items
+
+    def on_prefill_launched(self, items: List[PrefillItem], slots: Sequence[int]) -> None:
+        for it, slot in zip(items, slots):
+            req = it.req
+            req.n_launched += len(it.tokens)
+            if it.is_last_chunk:                 # its first id is in flight: it can join decode steps now
+                self.prefilling.remove(req)
+                self.running.append(req)
+                req.inflight += 1
+                req.out_slot = slot
 
     def on_prefill_done(self, items: List[PrefillItem], sampled: Sequence[Optional[int]]) -> None:
         self.stats["prefill_calls"] += 1
         for it, tok in zip(items, sampled):
             req = it.req
+            if req.done:
+                continue
             req.n_prefilled += len(it.tokens)
             if it.is_last_chunk:
-                self.prefilling.remove(req)
-                self.running.append(req)
+                req.inflight -= 1
                 # the prompt's KV is complete and immutable from here on: let other conversations that
                 # start with the same blocks (a common system prompt) read it while this one decodes
                 if req.entry is not None:
                     req.entry.tokens = list(req.prompt)
                     self.index.add(req.entry)
-                self._on_token(req, int(tok))
+                if not req.cancelled:
+                    self._on_token(req, int(tok))
         self._reap()
 
     def next_decode_batch(self) -> List[Request]:
+        """Running conversations that still need a token beyond those already in flight."""
         self._reap()
-        return list(self.running)
+        return [r for r in self.running if len(r.generated) + r.inflight < r.params.max_tokens]
+
+    def on_decode_launched(self, reqs: List[Request], slots: Sequence[int]) -> None:
+        for req, slot in zip(reqs, slots):
+            req.inflight += 1
+            req.out_slot = slot
 
     def on_decode_done(self, reqs: List[Request], sampled: Sequence[int]) -> None:
         self.stats["decode_steps"] += 1
         for req, tok in zip(reqs, sampled):
+            if req.done:
+                continue                          # finished on an earlier id: this step's id is discarded
+            req.inflight -= 1
             if not req.cancelled:
                 self._on_token(req, int(tok))
         self._reap()
@@ -400,6 +432,7 @@ class Scheduler:
         self._release(req)
 
     def _release(self, req: Request) -> None:
+        req.done = True
         if req in self.running:
             self.running.remove(req)
         if req in self.prefilling:
@@ -410,6 +443,7 @@ class Scheduler:
         req.entry = None
         self.index.remove(e)   # registered as a read-only donor while it was running; re-added below
         # KV is resident for the prefilled prompt part and for every generated token that was fed back
+        # (steps still in flight only write beyond that, and anything enqueued later runs after them)
         e.tokens = req.prompt[:req.n_prefilled] + req.generated[:max(0, len(req.generated) - 1)]
         keep = (len(e.tokens) + BLOCK_TOKENS - 1) // BLOCK_TOKENS
         if keep < len(e.blocks):

@@ -43,6 +43,8 @@ class FakeStepper(Stepper):
         self.prefill_calls: List[List[int]] = []   # tokens per item of every prefill call
         self.decode_batches: List[int] = []
         self.prefilled_tokens = 0
+        self.res: dict = {}            # result slot -> sampled id
+        self.outstanding = 0           # launched calls not fetched yet
 
     def _write(self, blocks, pos, tok):
         self.kv[blocks[pos // BLOCK_TOKENS]][pos % BLOCK_TOKENS] = tok
@@ -52,28 +54,45 @@ class FakeStepper(Stepper):
         assert None not in seq, "read of a KV position that was never written"
         return seq
 
-    def prefill(self, items: List[PrefillItem]) -> List[Optional[int]]:
+    # Work is executed at launch time, in launch order — exactly what the CUDA stream does — and the
+    # results are parked in the slots the engine named, to be handed out by fetch().
+    def prefill_launch(self, items: List[PrefillItem], parity: int):
         assert sum(len(i.tokens) for i in items) <= self.max_tokens
         assert len(items) <= self.max_seqs
         self.prefill_calls.append([len(i.tokens) for i in items])
-        out: List[Optional[int]] = []
-        for it in items:
+        slots: List[Optional[int]] = []
+        for i, it in enumerate(items):
             blocks = it.req.entry.blocks
             for k, t in enumerate(it.tokens):
                 self._write(blocks, it.ctx_len + k, t)
             self.prefilled_tokens += len(it.tokens)
             if it.is_last_chunk:
-                out.append(next_token(self._read(blocks, it.ctx_len + len(it.tokens)), self.eos_id, self.eos_every))
+                s = self.slot(parity, True, i)
+                self.res[s] = next_token(self._read(blocks, it.ctx_len + len(it.tokens)), self.eos_id, self.eos_every)
+                slots.append(s)
             else:
-                out.append(None)
-        return out
+                slots.append(None)
+        self.outstanding += 1
+        assert self.outstanding <= 4, "engine enqueued more than two iterations without reading back"
+        return slots
 
-    def decode(self, reqs: List[Request]) -> List[int]:
+    def decode_launch(self, reqs: List[Request], parity: int):
         assert len(reqs) <= self.max_seqs
         self.decode_batches.append(len(reqs))
-        out = []
-        for r in reqs:
+        fed = []
+        for r in reqs:   # gather every input before any output is written (kb_select_tokens runs first)
+            fed.append(self.res[r.out_slot] if r.inflight > 0 else r.generated[-1])
+        slots = []
+        for i, (r, tok) in enumerate(zip(reqs, fed)):
             blocks = r.entry.blocks
-            self._write(blocks, r.ctx_len, r.generated[-1])
-            out.append(next_token(self._read(blocks, r.ctx_len + 1), self.eos_id, self.eos_every))
-        return out
+            self._write(blocks, r.ctx_len, tok)
+            s = self.slot(parity, False, i)
+            self.res[s] = next_token(self._read(blocks, r.ctx_len + 1), self.eos_id, self.eos_every)
+            slots.append(s)
+        self.outstanding += 1
+        assert self.outstanding <= 4, "engine enqueued more than two iterations without reading back"
+        return slots
+
+    def fetch(self, handle) -> List[Optional[int]]:
+        self.outstanding -= 1
+        return [None if s is None else self.res[s] for s in handle]

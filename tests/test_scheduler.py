@@ -219,7 +219,7 @@ def test_cancellation_frees_slot_and_keeps_kv(engine):
 
 def test_engine_failure_reaches_every_request():
     class Boom(FakeStepper):
-        def decode(self, reqs):
+        def decode_launch(self, reqs, parity):
             raise RuntimeError("device fault")
     e = Engine(Boom(eos_id=EOS))
     try:
@@ -318,3 +318,81 @@ def test_reference_counts_return_every_block(engine):
         sched.index.remove(e)
         sched.alloc.free(e.blocks)
     assert sched.alloc.n_free == sched.alloc.n_blocks and set(sched.alloc.refs) == {0}
+
+
+# ---- two-stage pipeline: step k+1 is enqueued before step k's ids are read back ---------------------
+class _CountingStepper(FakeStepper):
+    def __init__(self, **kw):
+        super().__init__(**kw)
+        self.max_outstanding = 0
+        self.discarded = 0
+
+    def decode_launch(self, reqs, parity):
+        h = super().decode_launch(reqs, parity)
+        self.max_outstanding = max(self.max_outstanding, self.outstanding)
+        return h
+
+
+@pytest.mark.parametrize("pipeline", [True, False])
+def test_pipelined_loop_gives_the_same_tokens(pipeline):
+    """Staggered arrivals, early EOS, max_tokens=1 and a follow-up turn on resident KV: ids must not
+    depend on whether results are read back before or after the next step is enqueued."""
+    st = _CountingStepper(n_blocks=128, max_seqs=8, max_tokens=256, max_pos=2048, eos_id=EOS, eos_every=9)
+    e = Engine(st, max_prefill_tokens=96, pipeline=pipeline)
+    try:
+        prompts = [list(range(33 + 3 * i, 33 + 3 * i + 40 + 29 * i)) for i in range(12)]
+        lens = [1, 2, 3, 17, 40, 5, 64, 9, 30, 2, 1, 25]
+        cols = [Collector() for _ in prompts]
+        for i, (p, c, n) in enumerate(zip(prompts, cols, lens)):
+            e.submit(p, SamplingParams(max_tokens=n), c, thread_hint=f"t{i}")
+            if i % 3 == 2:
+                time.sleep(0.002)                                 # arrive while others are mid-decode
+        outs = []
+        for p, c, n in zip(prompts, cols, lens):
+            c.wait()
+            want = expected_tokens(p, n, EOS, eos_every=9)
+            streamed = want[:-1] if want[-1] == EOS else want
+            assert c.tokens == streamed and c.finish == ("stop" if want[-1] == EOS else "length")
+            assert c.usage["completion_tokens"] == len(want)
+            outs.append(want)
+        # second turn of every thread continues on the KV the first one left behind
+        for i, (p, want) in enumerate(zip(prompts, outs)):
+            p2 = p + [t for t in want if t != EOS] + [35, 36, 37]
+            c = run(e, p2, n=6, hint=f"t{i}")
+            w2 = expected_tokens(p2, 6, EOS, eos_every=9)
+            assert c.tokens == (w2[:-1] if w2[-1] == EOS else w2)
+            assert c.usage["cached_tokens"] >= len(p) - 1
+        assert st.max_outstanding >= (2 if pipeline else 1)
+        if not pipeline:
+            assert st.max_outstanding <= 2                        # at most one iteration (prefill + decode)
+    finally:
+        e.shutdown()
+
+
+def test_cancel_with_a_step_in_flight_keeps_kv_consistent():
+    st = FakeStepper(n_blocks=32, max_seqs=4, max_tokens=256, max_pos=1024, eos_id=EOS)
+    e = Engine(st)
+    try:
+        p = list(range(50, 150))
+        c = Collector()
+        got = threading.Event()
+        orig = c.__call__
+
+        def on_event(ev):
+            orig(ev)
+            if len(c.tokens) == 5:
+                got.set()
+        r = e.submit(p, SamplingParams(max_tokens=200), on_event, thread_hint="c")
+        assert got.wait(10)
+        r.cancelled = True                                        # a step is in flight right now
+        deadline = time.time() + 10
+        while r.entry is not None and time.time() < deadline:
+            time.sleep(0.001)
+        assert r.entry is None and r.done
+        n = len(c.tokens)
+        p2 = p + c.tokens + [77]
+        c2 = run(e, p2, n=8, hint="c")                            # reuses what the cancelled turn left
+        assert c2.tokens == expected_tokens(p2, 8, EOS)
+        assert c2.usage["cached_tokens"] >= len(p) + n - 2
+    finally:
+        e.shutdown()

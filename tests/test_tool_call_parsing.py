@@ -26,14 +26,17 @@ class ScriptStepper(FakeStepper):
         if req.req_id not in self.by_req:
             self.by_req[req.req_id] = self.scripts[len(self.by_req) % len(self.scripts)]
         s = self.by_req[req.req_id]
-        i = len(req.generated)
+        i = len(req.generated) + req.inflight   # ids already read back + ids still in flight
         return s[i] if i < len(s) else self.eos_id
 
-    def prefill(self, items):
+    def prefill_launch(self, items, parity):
         return [self._next(it.req) if it.is_last_chunk else None for it in items]
 
-    def decode(self, reqs):
+    def decode_launch(self, reqs, parity):
         return [self._next(r) for r in reqs]
+
+    def fetch(self, handle):
+        return handle
 
 
 def _provider(scripts, tools):
