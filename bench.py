@@ -61,6 +61,10 @@ def parse_args():
     ap.add_argument("--no-ttft-sweep", action="store_true")
     ap.add_argument("--no-pipeline", action="store_true",
                     help="serving loop reads every step back before enqueueing the next (A/B of the pipelined loop)")
+    ap.add_argument("--tp-compare", action="store_true",
+                    help="tensor-parallel run: also time the other all-reduce implementations on the same state")
+    ap.add_argument("--tp-allreduce", default=None, choices=["peers", "peers-f16", "peers-p2p", "nccl"],
+                    help="all-reduce of the tensor-parallel run (default: own peer-memory kernel, NCCL if unavailable)")
     ap.add_argument("--tp", action="store_true",
                     help="tensor-parallel: ONE model sharded over all ranks (config 5: --model llama-3-70b --history 8192)")
     return ap.parse_args()
@@ -535,7 +539,8 @@ def run_tp(args, rank, world, local_rank):
     loc = local_config(cfg, world)
     K, W = args.steps, max(args.warmup, 3)
     U = args.user_tokens
-    bpt = (args.history + U + 2 * (W + K) + 8 + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
+    n_meas = 3 if args.tp_compare else 1
+    bpt = (args.history + U + n_meas * (W + 2 * K) + 8 + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
     B = args.threads
     # weights first (they decide how much HBM is left for KV); a 1-block core, then the real one
     free0, _ = torch.cuda.mem_get_info(dev)
@@ -548,7 +553,8 @@ def run_tp(args, rank, world, local_rank):
     if fit < B:
         resident_note = f"only {fit} of {B} threads resident per the smallest rank's free HBM"
         B = fit
-    core, grp = build_tp_core(cfg, rank, world, dev, n_blocks=B * bpt, max_tokens=max(4096, B), max_seqs=B, seed=0)
+    core, grp = build_tp_core(cfg, rank, world, dev, n_blocks=B * bpt, max_tokens=max(4096, B), max_seqs=B, seed=0,
+                              allreduce=args.tp_allreduce)
     for L in range(loc.n_layers):
         core.k_pool[L].normal_(0, 1)
         core.v_pool[L].normal_(0, 1)
@@ -579,27 +585,49 @@ def run_tp(args, rank, world, local_rank):
             cur ^= 1
             ctx += 1
 
-    steps(W)
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    torch.cuda.synchronize()
-    torch.distributed.barrier()
-    l0 = cabi.launch_count()
-    ctx_start = ctx
-    e0.record()
-    steps(K)
-    e1.record()
-    torch.cuda.synchronize()
-    torch.distributed.barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-    ms_total = float(t.item())
-    launches = cabi.launch_count() - l0
-    clocks = sampler.stop()
-    core.profile_begin()
-    ctx_p = ctx
-    steps(K)
-    prof = core.profile_end()
+    def measure():
+        """W warm-up steps, K timed steps (max over ranks), K more under the per-kernel event profile."""
+        nonlocal ctx
+        steps(W)
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+        l0 = cabi.launch_count()
+        c0 = ctx
+        e0.record()
+        steps(K)
+        e1.record()
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        n_launch = cabi.launch_count() - l0
+        clk = sampler.stop()
+        core.profile_begin()
+        cp = ctx
+        steps(K)
+        return {"ms_total": float(t.item()), "launches": n_launch, "clocks": clk, "prof": core.profile_end(),
+                "ctx_start": c0, "ctx_p": cp, "mode": grp.mode}
+
+    others = {}
+    if args.tp_compare and hasattr(grp, "peers"):
+        # the same resident state under the other all-reduce implementations (switchable at run time)
+        from kafka_b200.tp import TPGroup
+        blocks = int(os.environ.get("KAFKA_B200_TP_BLOCKS", "0"))
+        main_f16 = grp.wire_f16
+        nccl = TPGroup()
+        nccl.attach(core, extra_base=grp.buf)
+        saved_mode, grp.mode = grp.mode, "nccl"
+        r = measure()
+        others["nccl"] = {"ms_per_step": r["ms_total"] / K, "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K}
+        grp.attach(core, blocks, wire_f16=not main_f16)
+        r = measure()
+        others[grp.mode] = {"ms_per_step": r["ms_total"] / K, "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K}
+        grp.attach(core, blocks, wire_f16=main_f16)
+    m = measure()
+    ms_total, launches, clocks, prof, ctx_start, ctx_p = (m["ms_total"], m["launches"], m["clocks"], m["prof"],
+                                                          m["ctx_start"], m["ctx_p"])
     if rank != 0:
         return
     hbm_peak, tf_peak, peak_kind = peaks()
@@ -607,7 +635,7 @@ def run_tp(args, rank, world, local_rank):
     attn_bytes = B * (ctx_p + (K - 1) / 2 + 1) * loc.kv_dim * 2 * 2
     achieved = attn_bytes / (attn_ms / attn_n / 1e3) / 1e9
     ar_ms, ar_n = prof["allreduce"]
-    ar_bytes = 4 * B * cfg.hidden
+    ar_bytes = (2 if grp.mode.endswith("-f16") else 4) * B * cfg.hidden
     line = {
         "metric": METRIC, "value": B * K / (ms_total / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -615,7 +643,7 @@ def run_tp(args, rank, world, local_rank):
         "config": {"workload": f"{cfg.name} tensor-parallel x{world} decode, {B} threads x {args.history}-token history "
                                f"+ {U}-token turn (BASELINE configs[4])", "model": cfg.name, "threads": B,
                    "history": args.history, "context_at_start": ctx_start, "resident_note": resident_note,
-                   "parallelism": f"tp{world}: heads/ffn sharded, 2 NCCL all-reduces of [T,{cfg.hidden}] fp32 per layer",
+                   "parallelism": f"tp{world}: heads/ffn sharded, 2 all-reduces ({grp.mode}) of [T,{cfg.hidden}] per layer",
                    "l2": "inputs larger than L2; no explicit flush"},
         "clocks": clocks, "gpu_launches": launches, "e2e": None,
         "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel<128,8>", "achieved": achieved, "peak": hbm_peak,
@@ -624,7 +652,16 @@ def run_tp(args, rank, world, local_rank):
                      "share_of_step": attn_ms / sum(v[0] for v in prof.values())},
         "allreduce": {"calls_per_step": ar_n / K, "ms_per_step": ar_ms / K, "bytes_per_call": ar_bytes,
                       "busbw_GBps": (2 * (world - 1) / world) * ar_bytes / (ar_ms / ar_n / 1e3) / 1e9,
-                      "backend": "NCCL via torch.distributed on the kernels' stream"},
+                      "backend": {"nccl": "NCCL via torch.distributed on the kernels' stream",
+                                  "peers-multicast": "own kernel: multimem.ld_reduce / multimem.st over the NVSwitch "
+                                                     "multicast mapping of the residual buffers (kb_collective.cu)",
+                                  "peers-multicast-f16": "own kernel: fp16 partial sums, multimem.ld_reduce (fp32 "
+                                                         "accumulate in the switch) / multimem.st over the NVSwitch "
+                                                         "multicast mapping (kb_collective.cu); the sum is added "
+                                                         "to the fp32 residual by the following RMSNorm",
+                                  "peers-p2p-f16": "own kernel: fp16 partial sums, peer loads / stores over NVLink",
+                                  "peers-p2p": "own kernel: peer loads / stores over NVLink (kb_collective.cu)"}[grp.mode],
+                      "other_modes_same_state": others or None},
         "kernels": {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]},
         "prefill": {"ms": prefill_ms, "tokens": B * U}, "cpu_baseline": None,
     }

@@ -126,6 +126,37 @@ int kb_bind_workspace(kb_engine* e, void* ws, size_t bytes, int32_t max_tokens, 
 typedef int (*kb_allreduce_fn)(void* ctx, float* buf, size_t n, kb_stream stream);
 int kb_set_tensor_parallel(kb_engine* e, int32_t tp_rank, int32_t tp_size, kb_allreduce_fn fn, void* ctx);
 
+/* The same sums WITHOUT a library collective: one kernel per all-reduce that works directly on peer
+ * memory over NVLink / NVSwitch (csrc/kb_collective.cu).  The caller provides a SYMMETRIC region — the
+ * same allocation size on every rank, mapped into every rank's address space (CUDA IPC / fabric
+ * handles; kafka_b200/tp.py uses torch's symmetric-memory rendezvous for the mapping only):
+ *     peer_base[r]   this process's mapping of rank r's region (peer_base[own rank] = the local one)
+ *     mc_base        multicast (NVLS) mapping of the region, or NULL -> plain peer loads and stores
+ *     flags_offset   byte offset of KB_TP_FLAG_BYTES of barrier flags, zeroed on every rank before the
+ *                    first call (and a host barrier after zeroing)
+ * kb_set_tensor_parallel_peers moves the engine's residual stream and partial-sum buffer (2 x
+ * align256(max_tokens * hidden * 4) bytes from offset 0) into the region and replaces the callback;
+ * call it after kb_bind_workspace, on every rank.  kb_allreduce_peers is the bare collective (in
+ * place, n fp32 at offset_bytes; `epoch` must be odd, equal on all ranks and grow by 2 per call).
+ * A rank whose peers do not arrive within ~2 s traps instead of hanging.  No reference counterpart. */
+#define KB_TP_MAX_RANKS 8
+#define KB_TP_MAX_BLOCKS 64
+#define KB_TP_FLAG_BYTES (KB_TP_MAX_BLOCKS * KB_TP_MAX_RANKS * 4)
+typedef struct kb_tp_peers {
+    void* peer_base[KB_TP_MAX_RANKS];
+    void* mc_base;
+    size_t bytes;
+    size_t flags_offset;
+} kb_tp_peers;
+int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32_t tp_size, const kb_tp_peers* peers,
+                                 int32_t blocks /* grid of the collective, 0 = default */,
+                                 int32_t wire_f16 /* 0: fp32 partial sums, rank 0 folds the residual in;
+                                                     1: fp16 partial sums (KB_EPI_F16), added in fp32 by the
+                                                        switch, sum added to the residual by the next RMSNorm */);
+int kb_allreduce_peers(const kb_tp_peers* peers, int32_t rank, int32_t world, size_t offset_bytes, size_t n,
+                       int32_t f16 /* 0: n fp32; 1: n fp16, added in fp32 */, uint32_t epoch, int32_t blocks,
+                       kb_stream stream);
+
 /* ---- the hot path ------------------------------------------------------------------------------
  * Both calls run embed -> n_layers x (RMSNorm, QKV GEMM, RoPE + KV append, paged attention,
  * O GEMM + residual, RMSNorm, gate/up GEMM + SwiGLU, down GEMM + residual) -> final RMSNorm of the
@@ -174,6 +205,7 @@ int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x, int32_t n,
 #define KB_EPI_RESID_F32 2
 #define KB_EPI_SWIGLU_BF16 3
 #define KB_EPI_SWIGLU_F16 4 /* same, fp16 out (the hot path's activation format, see KB_GEMM_A_F16) */
+#define KB_EPI_F16 5        /* out[M,N] fp16 (tensor-parallel partial sums sent as fp16, see kb_tp_peers) */
 /* OR into `epilogue`: BOTH operands are fp16 instead of bf16 (tcgen05 kind::f16 requires A and B to
  * share one format; mixing traps).  The hot path keeps its GEMM activations (normed hidden states,
  * attention output, MLP inner) in fp16 — 10 mantissa bits against bf16's 7 — because their rounding is

@@ -34,17 +34,33 @@ embed_kernel(const int* __restrict__ tokens, const __nv_bfloat16* __restrict__ e
 //   bytes/row = hidden * (4 + 2) (+ w, L2-resident)
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-rmsnorm_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w, uint16_t* __restrict__ y,
-               const int* __restrict__ last_rows, int hidden, float eps, int out_f16) {
+rmsnorm_kernel(float* __restrict__ x, const __nv_bfloat16* __restrict__ w, uint16_t* __restrict__ y,
+               const int* __restrict__ last_rows, const __half* __restrict__ delta, int hidden, float eps,
+               int out_f16) {
     const int i = blockIdx.x;
     const int row = last_rows ? last_rows[i + 1] - 1 : i;
-    const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * hidden);
+    float4* xr = reinterpret_cast<float4*>(x + (size_t)row * hidden);
     const int n4 = hidden / 4;
     __shared__ float red[8];
     float ss = 0.f;
-    for (int j = threadIdx.x; j < n4; j += blockDim.x) {
-        const float4 v = xr[j];
-        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    if (delta != nullptr) {
+        // tensor parallel, fp16 wire: the reduced projection output has not been added to the residual
+        // stream yet — do it here (x += delta, written back) instead of in a kernel of its own
+        const uint2* dr = reinterpret_cast<const uint2*>(delta + (size_t)row * hidden);
+        for (int j = threadIdx.x; j < n4; j += blockDim.x) {
+            float4 v = xr[j];
+            const uint2 d = dr[j];
+            const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&d.x));
+            const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&d.y));
+            v.x += d0.x; v.y += d0.y; v.z += d1.x; v.w += d1.y;
+            xr[j] = v;   // re-read below by the same thread
+            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+        }
+    } else {
+        for (int j = threadIdx.x; j < n4; j += blockDim.x) {
+            const float4 v = xr[j];
+            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+        }
     }
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
@@ -259,10 +275,11 @@ int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, i
     return KB_OK;
 }
 
-int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps, int out_f16,
-            cudaStream_t stream) {
+int rmsnorm(float* x, const void* w, void* y, const int* last_rows, const void* delta_f16, int n, int hidden, float eps,
+            int out_f16, cudaStream_t stream) {
     KB_CHECK(n > 0 && hidden % 4 == 0, "kb_rmsnorm: bad shape n=%d hidden=%d", n, hidden);
-    rmsnorm_kernel<<<n, 256, 0, stream>>>(x, (const __nv_bfloat16*)w, (uint16_t*)y, last_rows, hidden, eps, out_f16);
+    rmsnorm_kernel<<<n, 256, 0, stream>>>(x, (const __nv_bfloat16*)w, (uint16_t*)y, last_rows,
+                                          (const __half*)delta_f16, hidden, eps, out_f16);
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -310,7 +327,8 @@ extern "C" int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x,
 }
 extern "C" int kb_rmsnorm(const float* x, const void* w_bf16, void* y, int32_t n, int32_t hidden, float eps,
                           int32_t out_f16, kb_stream stream) {
-    return kb::rmsnorm(x, w_bf16, y, nullptr, n, hidden, eps, out_f16, reinterpret_cast<cudaStream_t>(stream));
+    return kb::rmsnorm(const_cast<float*>(x), w_bf16, y, nullptr, nullptr, n, hidden, eps, out_f16,
+                       reinterpret_cast<cudaStream_t>(stream));
 }
 extern "C" int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
                               const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,

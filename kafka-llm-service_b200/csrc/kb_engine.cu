@@ -25,8 +25,8 @@ void set_error(const char* fmt, ...) {
 int gemm(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi,
          cudaStream_t stream);
 int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, int vocab, cudaStream_t stream);
-int rmsnorm(const float* x, const void* w, void* y, const int* last_rows, int n, int hidden, float eps, int out_f16,
-            cudaStream_t stream);
+int rmsnorm(float* x, const void* w, void* y, const int* last_rows, const void* delta_f16, int n, int hidden, float eps,
+            int out_f16, cudaStream_t stream);
 int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* kp, void* vp, int n_seqs,
                 int n_tokens, int max_blocks, int n_heads, int n_kv_heads, int head_dim, float theta,
                 cudaStream_t stream);
@@ -39,6 +39,8 @@ int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, co
                  const int* bt, void* out, int n_seqs, int n_tokens, int max_new, int max_blocks, int n_heads,
                  int n_kv_heads, int head_dim, int out_f16, cudaStream_t stream);
 size_t attn_decode_scratch_bytes(int batch, int n_heads, int head_dim, int n_splits);
+int allreduce_peers(const kb_tp_peers* P, int rank, int world, size_t offset_bytes, size_t n, int f16, uint32_t epoch,
+                    int blocks, cudaStream_t stream);
 
 static inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
@@ -111,6 +113,12 @@ struct kb_engine {
     int tp_rank = 0, tp_size = 1;
     kb_allreduce_fn allreduce = nullptr;
     void* allreduce_ctx = nullptr;
+    // ... or the in-kernel all-reduce over peer memory (kb_set_tensor_parallel_peers)
+    bool use_peers = false;
+    kb_tp_peers peers{};
+    int peer_blocks = 0;
+    bool peer_wire_f16 = false;   // partial sums travel as fp16 and are added to the residual by the next RMSNorm
+    uint32_t peer_epoch = 1;
     // profiling: one event before every kernel (+ one closing event per call)
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_pool;  // reusable events
@@ -138,7 +146,8 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     KB_CHECK(tokens && ctx_lens && block_tables, "null token / ctx_lens / block_tables pointer");
     KB_CHECK(decode || cu_seqlens != nullptr, "prefill needs cu_seqlens");
     KB_CHECK(out_tokens == nullptr || sampling != nullptr, "out_tokens requested without sampling params");
-    KB_CHECK(e->tp_size <= 1 || e->allreduce != nullptr, "tensor parallel engine without an all-reduce callback");
+    KB_CHECK(e->tp_size <= 1 || e->allreduce != nullptr || e->use_peers,
+             "tensor parallel engine without an all-reduce (kb_set_tensor_parallel / _peers)");
     int dev = -1;
     KB_CUDA(cudaGetDevice(&dev));
     KB_CHECK(dev == e->device, "engine belongs to device %d but current device is %d", e->device, dev);
@@ -165,19 +174,39 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     int rc;
     float* x = w.x;    // residual stream; with tensor parallelism x and xr trade places after every all-reduce
     float* xr = w.xr;
+    const void* delta = nullptr;   // fp16 wire: reduced projection output not yet added to x (next rmsnorm does)
 
     // x += a[T,K] * wt[hidden,K]^T.  Tensor parallel: this rank holds a K-slice of the projection, the
-    // partial sums go through the host-provided all-reduce; rank 0 folds the residual into its partial,
-    // so the reduced buffer IS the new residual stream (no separate add).
+    // partial sums go through the all-reduce. fp32 wire: rank 0 folds the residual into its partial, so
+    // the reduced buffer IS the new residual stream (no separate add). fp16 wire (half the NVLink
+    // bytes): the partials are stored as fp16, summed in fp32 inside the switch, and the fp16 sum is
+    // added to the fp32 residual by the RMSNorm that follows.
     auto project_into_residual = [&](const void* a, const void* wt, int K) -> int {
         if (e->tp_size <= 1)
             return gemm(a, wt, x, x, n_tokens, c.hidden, K, KB_EPI_RESID_F32 | KB_GEMM_F16, stream);
+        if (e->use_peers && e->peer_wire_f16) {
+            int r = gemm(a, wt, w.xr, nullptr, n_tokens, c.hidden, K, KB_EPI_F16 | KB_GEMM_F16, stream);
+            if (r) return r;
+            mark(KB_PROF_ALLREDUCE);
+            const size_t off = reinterpret_cast<char*>(w.xr) - static_cast<char*>(e->peers.peer_base[e->tp_rank]);
+            r = allreduce_peers(&e->peers, e->tp_rank, e->tp_size, off, (size_t)n_tokens * c.hidden, 1, e->peer_epoch,
+                                e->peer_blocks, stream);
+            e->peer_epoch += 2;
+            delta = w.xr;
+            return r;
+        }
         int r = (e->tp_rank == 0)
                     ? gemm(a, wt, xr, x, n_tokens, c.hidden, K, KB_EPI_RESID_F32 | KB_GEMM_F16, stream)
                     : gemm(a, wt, xr, nullptr, n_tokens, c.hidden, K, KB_EPI_F32 | KB_GEMM_F16, stream);
         if (r) return r;
         mark(KB_PROF_ALLREDUCE);
-        if (e->allreduce(e->allreduce_ctx, xr, (size_t)n_tokens * c.hidden, stream) != 0) {
+        if (e->use_peers) {
+            const size_t off = reinterpret_cast<char*>(xr) - static_cast<char*>(e->peers.peer_base[e->tp_rank]);
+            r = allreduce_peers(&e->peers, e->tp_rank, e->tp_size, off, (size_t)n_tokens * c.hidden, 0, e->peer_epoch,
+                                e->peer_blocks, stream);
+            e->peer_epoch += 2;
+            if (r) return r;
+        } else if (e->allreduce(e->allreduce_ctx, xr, (size_t)n_tokens * c.hidden, stream) != 0) {
             set_error("tensor-parallel all-reduce callback failed");
             return KB_ERR_INVALID;
         }
@@ -192,7 +221,8 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         __nv_bfloat16* kp = e->k_pool + (size_t)L * layer_stride;
         __nv_bfloat16* vp = e->v_pool + (size_t)L * layer_stride;
         mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(x, lw.attn_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+        if ((rc = rmsnorm(x, lw.attn_norm, w.xn, nullptr, delta, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+        delta = nullptr;
         mark(KB_PROF_GEMM_QKV);
         if ((rc = gemm(w.xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16 | KB_GEMM_F16, stream)))
             return rc;
@@ -213,7 +243,8 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         mark(KB_PROF_GEMM_O);
         if ((rc = project_into_residual(w.attn, lw.wo, qdim))) return rc;
         mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(x, lw.mlp_norm, w.xn, nullptr, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+        if ((rc = rmsnorm(x, lw.mlp_norm, w.xn, nullptr, delta, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+        delta = nullptr;
         mark(KB_PROF_GEMM_GATE_UP);
         if ((rc = gemm(w.xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden,
                        KB_EPI_SWIGLU_F16 | KB_GEMM_F16, stream)))
@@ -227,7 +258,7 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     }
     mark(KB_PROF_RMSNORM);
     // final norm on the last row of every sequence, lm_head, sampling
-    if ((rc = rmsnorm(x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, n_seqs, c.hidden, c.rms_eps, 1,
+    if ((rc = rmsnorm(x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, delta, n_seqs, c.hidden, c.rms_eps, 1,
                       stream)))
         return rc;
     float* lg = logits_out ? logits_out : w.logits;
@@ -283,6 +314,33 @@ extern "C" void kb_engine_destroy(kb_engine* e) {
     delete e;
 }
 
+extern "C" int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32_t tp_size, const kb_tp_peers* peers,
+                                            int32_t blocks, int32_t wire_f16) {
+    using namespace kb;
+    KB_CHECK(e != nullptr && peers != nullptr, "kb_set_tensor_parallel_peers: null argument");
+    KB_CHECK(tp_size >= 2 && tp_size <= KB_TP_MAX_RANKS && tp_rank >= 0 && tp_rank < tp_size,
+             "kb_set_tensor_parallel_peers: bad rank %d of %d (2..%d ranks)", tp_rank, tp_size, KB_TP_MAX_RANKS);
+    KB_CHECK(e->ws.x != nullptr, "kb_set_tensor_parallel_peers: bind the workspace first");
+    const size_t each = align256((size_t)e->max_tokens * e->cfg.hidden * 4);
+    KB_CHECK(peers->flags_offset >= 2 * each && peers->flags_offset % 256 == 0 &&
+                 peers->flags_offset + KB_TP_FLAG_BYTES <= peers->bytes,
+             "kb_set_tensor_parallel_peers: region of %zu bytes (flags at %zu) cannot hold 2 x %zu bytes + flags",
+             peers->bytes, peers->flags_offset, each);
+    for (int r = 0; r < tp_size; ++r)
+        KB_CHECK(peers->peer_base[r] != nullptr, "kb_set_tensor_parallel_peers: no mapping of rank %d", r);
+    e->tp_rank = tp_rank;
+    e->tp_size = tp_size;
+    e->peers = *peers;
+    e->peer_blocks = blocks;
+    e->peer_wire_f16 = wire_f16 != 0;
+    // peer_epoch is never reset: re-configuring (blocks, wire format, back from the callback) must continue
+    // the flag sequence of the region
+    e->use_peers = true;
+    e->ws.x = reinterpret_cast<float*>(peers->peer_base[tp_rank]);
+    e->ws.xr = reinterpret_cast<float*>(static_cast<char*>(peers->peer_base[tp_rank]) + each);
+    return KB_OK;
+}
+
 extern "C" int kb_set_tensor_parallel(kb_engine* e, int32_t tp_rank, int32_t tp_size, kb_allreduce_fn fn, void* ctx) {
     KB_CHECK(e != nullptr, "kb_set_tensor_parallel: null engine");
     KB_CHECK(tp_size >= 1 && tp_rank >= 0 && tp_rank < tp_size, "kb_set_tensor_parallel: bad rank %d of %d", tp_rank,
@@ -291,6 +349,7 @@ extern "C" int kb_set_tensor_parallel(kb_engine* e, int32_t tp_rank, int32_t tp_
     e->tp_rank = tp_rank;
     e->tp_size = tp_size;
     e->allreduce = fn;
+    e->use_peers = false;
     e->allreduce_ctx = ctx;
     return KB_OK;
 }

@@ -70,16 +70,17 @@ template <int EPI>
 __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* out, const float* resid, int row,
                                                  int col0, int N) {
     // 32 consecutive fp32 accumulator columns [col0, col0+32) of one row. N % 8 == 0.
-    if (EPI == KB_EPI_BF16) {
-        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (size_t)row * N + col0;
+    if (EPI == KB_EPI_BF16 || EPI == KB_EPI_F16) {
+        uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)row * N + col0;
+        constexpr int f16 = (EPI == KB_EPI_F16);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             if (col0 + j * 8 < N) {
                 uint4 v;
-                v.x = pack_bf16(__uint_as_float(r[j * 8 + 0]), __uint_as_float(r[j * 8 + 1]));
-                v.y = pack_bf16(__uint_as_float(r[j * 8 + 2]), __uint_as_float(r[j * 8 + 3]));
-                v.z = pack_bf16(__uint_as_float(r[j * 8 + 4]), __uint_as_float(r[j * 8 + 5]));
-                v.w = pack_bf16(__uint_as_float(r[j * 8 + 6]), __uint_as_float(r[j * 8 + 7]));
+                v.x = pack_act(__uint_as_float(r[j * 8 + 0]), __uint_as_float(r[j * 8 + 1]), f16);
+                v.y = pack_act(__uint_as_float(r[j * 8 + 2]), __uint_as_float(r[j * 8 + 3]), f16);
+                v.z = pack_act(__uint_as_float(r[j * 8 + 4]), __uint_as_float(r[j * 8 + 5]), f16);
+                v.w = pack_act(__uint_as_float(r[j * 8 + 6]), __uint_as_float(r[j * 8 + 7]), f16);
                 *reinterpret_cast<uint4*>(o + j * 8) = v;
             }
         }
@@ -525,6 +526,7 @@ static int dispatch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, void* ou
         case KB_EPI_RESID_F32: return launch_gemm<BN, KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, ab, stream);
         case KB_EPI_SWIGLU_BF16: return launch_gemm<BN, KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
         case KB_EPI_SWIGLU_F16: return launch_gemm<BN, KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_F16: return launch_gemm<BN, KB_EPI_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
     }
     set_error("kb_gemm: unknown epilogue %d", epi);
     return KB_ERR_INVALID;
@@ -562,6 +564,7 @@ static int dispatch_epi_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, voi
             return launch_gemm_2cta<BN, KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
         case KB_EPI_SWIGLU_F16:
             return launch_gemm_2cta<BN, KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_F16: return launch_gemm_2cta<BN, KB_EPI_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
     }
     set_error("kb_gemm: unknown epilogue %d", epi);
     return KB_ERR_INVALID;

@@ -23,7 +23,7 @@ PROF_CATS = ("embed", "rmsnorm", "gemm_qkv", "rope_append", "attention", "gemm_o
              "lm_head", "sample", "allreduce")
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
 
-EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_SWIGLU_BF16, EPI_SWIGLU_F16 = 0, 1, 2, 3, 4
+EPI_BF16, EPI_F32, EPI_RESID_F32, EPI_SWIGLU_BF16, EPI_SWIGLU_F16, EPI_F16 = 0, 1, 2, 3, 4, 5
 GEMM_F16 = 0x100  # OR into the epilogue: both operands are fp16 instead of bf16 (formats must match)
 
 _LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libkafka_b200.so"
@@ -57,6 +57,15 @@ class Sampling(C.Structure):
                 ("seq_temperature", C.c_void_p), ("seq_seed", C.c_void_p)]
 
 
+TP_MAX_RANKS, TP_MAX_BLOCKS = 8, 64
+TP_FLAG_BYTES = TP_MAX_BLOCKS * TP_MAX_RANKS * 4
+
+
+class TpPeers(C.Structure):
+    _fields_ = [("peer_base", C.c_void_p * TP_MAX_RANKS), ("mc_base", C.c_void_p), ("bytes", C.c_size_t),
+                ("flags_offset", C.c_size_t)]
+
+
 # name -> (restype, argtypes); kept in one table so tests can check every symbol the header declares.
 _i32, _vp, _sz, _f = C.c_int32, C.c_void_p, C.c_size_t, C.c_float
 SIGNATURES = {
@@ -84,6 +93,8 @@ SIGNATURES = {
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
     "kb_select_tokens": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp]),
     "kb_set_tensor_parallel": (C.c_int, [_vp, _i32, _i32, ALLREDUCE_FN, _vp]),
+    "kb_set_tensor_parallel_peers": (C.c_int, [_vp, _i32, _i32, C.POINTER(TpPeers), _i32, _i32]),
+    "kb_allreduce_peers": (C.c_int, [C.POINTER(TpPeers), _i32, _i32, _sz, _sz, _i32, C.c_uint32, _i32, _vp]),
     "kb_profile_begin": (C.c_int, [_vp]),
     "kb_profile_end": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "kb_last_error": (C.c_char_p, []),

@@ -104,25 +104,29 @@ class TPGroup:
         self.calls = 0
         self.bytes = 0
         self._views: Dict[int, torch.Tensor] = {}
-        self._ws: Optional[torch.Tensor] = None
+        self._bases = []
         self._cb = cabi.ALLREDUCE_FN(self._callback)   # keep the ctypes thunk alive
 
-    def attach(self, core) -> None:
-        """Bind to an EngineCore built with local_config(): registers the callback in the library."""
-        self._ws = core.workspace
+    def attach(self, core, extra_base: Optional[torch.Tensor] = None) -> None:
+        """Bind to an EngineCore built with local_config(): registers the callback in the library.
+        `extra_base`: another uint8 tensor the engine's buffers may live in (a PeerRegion's)."""
+        self._bases = [core.workspace] + ([extra_base] if extra_base is not None else [])
+        self.mode = "nccl"
         cabi.check(core.lib.kb_set_tensor_parallel(core._h, self.rank, self.size, self._cb, None),
                    "kb_set_tensor_parallel")
 
     def _callback(self, ctx, buf, n, stream) -> int:
         try:
-            ws = self._ws
-            off = int(buf) - ws.data_ptr()
-            key = (off, int(n))
+            key = (int(buf), int(n))
             t = self._views.get(key)
             if t is None:
-                if off < 0 or off + 4 * n > ws.numel():
+                for ws in self._bases:
+                    off = int(buf) - ws.data_ptr()
+                    if off >= 0 and off + 4 * n <= ws.numel():
+                        t = self._views[key] = ws[off:off + 4 * n].view(torch.float32)
+                        break
+                else:
                     return 1
-                t = self._views[key] = ws[off:off + 4 * n].view(torch.float32)
             if torch.cuda.current_stream().cuda_stream != int(stream or 0):
                 return 2        # the collective must be ordered on the stream the kernels run on
             self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
@@ -133,10 +137,79 @@ class TPGroup:
             return 3
 
 
+class PeerRegion:
+    """A symmetric allocation (same size on every rank) mapped into every rank's address space, for the
+    in-kernel all-reduce of csrc/kb_collective.cu. torch's symmetric-memory rendezvous is used for the
+    MAPPING only (allocation, handle exchange, multicast binding); the collective itself is our kernel.
+
+    Layout: [payload bytes | barrier flags (cabi.TP_FLAG_BYTES)]."""
+
+    def __init__(self, payload_bytes: int, device, group=None, use_multicast: bool = True):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        group = group if group is not None else dist.group.WORLD
+        self.rank, self.size = dist.get_rank(group), dist.get_world_size(group)
+        if self.size > cabi.TP_MAX_RANKS:
+            raise ValueError(f"at most {cabi.TP_MAX_RANKS} ranks")
+        self.flags_offset = (payload_bytes + 255) & ~255
+        self.bytes = self.flags_offset + cabi.TP_FLAG_BYTES
+        self.buf = symm_mem.empty(self.bytes, dtype=torch.uint8, device=device)
+        self.handle = symm_mem.rendezvous(self.buf, group)
+        ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        off = self.buf.data_ptr() - ptrs[self.rank]      # the tensor may sit inside a larger mapped block
+        mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        self.multicast = bool(mc) and use_multicast
+        self.peers = cabi.TpPeers()
+        for r in range(self.size):
+            self.peers.peer_base[r] = ptrs[r] + off
+        self.peers.mc_base = (mc + off) if self.multicast else None
+        self.peers.bytes = self.bytes
+        self.peers.flags_offset = self.flags_offset
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(group)                              # every rank's flags are zero before anyone signals
+        self.epoch = 1
+
+    def payload(self, dtype=torch.float32) -> torch.Tensor:
+        return self.buf[:self.flags_offset].view(dtype)
+
+    def allreduce_(self, offset_bytes: int, n: int, blocks: int = 0, f16: bool = False) -> None:
+        """In place on n fp32 (or fp16, added in fp32) at offset_bytes of the payload, on the current stream
+        (all ranks, same order)."""
+        cabi.check(cabi.load().kb_allreduce_peers(C.byref(self.peers), self.rank, self.size, offset_bytes, n,
+                                                  int(f16), self.epoch, blocks,
+                                                  torch.cuda.current_stream().cuda_stream),
+                   "kb_allreduce_peers")
+        self.epoch += 2
+
+    def attach(self, core, blocks: int = 0, wire_f16: bool = False) -> None:
+        """Move the engine's residual / partial-sum buffers into this region and switch it to the in-kernel
+        all-reduce (the region must hold 2 x align256(max_tokens * hidden * 4) bytes). May be called again
+        to change the grid or the wire format. wire_f16: partial sums cross NVLink as fp16 (added in fp32)."""
+        cabi.check(core.lib.kb_set_tensor_parallel_peers(core._h, self.rank, self.size, C.byref(self.peers), blocks,
+                                                         int(wire_f16)),
+                   "kb_set_tensor_parallel_peers")
+        self.wire_f16 = wire_f16
+        self.mode = ("peers-multicast" if self.multicast else "peers-p2p") + ("-f16" if wire_f16 else "")
+
+
+def residual_region_bytes(cfg: LlamaConfig, max_tokens: int) -> int:
+    each = (max_tokens * cfg.hidden * 4 + 255) & ~255
+    return 2 * each
+
+
 def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, max_tokens: int, max_seqs: int,
-                  weights: Optional[Dict[str, torch.Tensor]] = None, seed: int = 0, group=None):
-    """EngineCore of one tensor-parallel rank (+ its TPGroup). `weights`: canonical FULL weights (tests);
-    None draws the shard on the device (benchmarks)."""
+                  weights: Optional[Dict[str, torch.Tensor]] = None, seed: int = 0, group=None,
+                  allreduce: Optional[str] = None):
+    """EngineCore of one tensor-parallel rank (+ the object that owns its all-reduce). `weights`: canonical
+    FULL weights (tests); None draws the shard on the device (benchmarks).
+
+    allreduce: "peers" (our kernel over the NVSwitch multicast mapping, fp32 partial sums), "peers-f16" (same,
+    fp16 partial sums: half the NVLink bytes), "peers-p2p" (plain peer loads / stores, no multicast), "nccl"
+    (torch.distributed callback), or None = $KAFKA_B200_TP_ALLREDUCE, default "auto" = "peers-f16" with a
+    logged fall-back to NCCL when the symmetric mapping cannot be set up."""
+    import os
+    import sys
     from .engine_core import EngineCore
     loc = local_config(cfg, tp)
     if weights is not None:
@@ -146,6 +219,20 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
     core = EngineCore(loc, fused, device, n_blocks=n_blocks, max_tokens=max_tokens, max_seqs=max_seqs)
     grp = None
     if tp > 1:
-        grp = TPGroup(group)
-        grp.attach(core)
+        mode = allreduce or os.environ.get("KAFKA_B200_TP_ALLREDUCE", "auto")
+        if mode in ("auto", "peers", "peers-f16", "peers-p2p"):
+            try:
+                grp = PeerRegion(residual_region_bytes(loc, max_tokens), device, group,
+                                 use_multicast=(mode != "peers-p2p"))
+                grp.attach(core, int(os.environ.get("KAFKA_B200_TP_BLOCKS", "0")),
+                           wire_f16=mode in ("auto", "peers-f16"))
+            except Exception as e:
+                if mode != "auto":
+                    raise
+                print(f"[kafka_b200.tp] symmetric memory unavailable ({e!r}); all-reduce falls back to NCCL",
+                      file=sys.stderr)
+                grp = None
+        if grp is None:
+            grp = TPGroup(group)
+            grp.attach(core)
     return core, grp

@@ -1,7 +1,9 @@
 """Tensor parallelism on real GPUs (needs >= 2; skipped on the 1-GPU box): two ranks, each with the
-local-shape engine of its shard and NCCL all-reduce through the kb_set_tensor_parallel callback, must
-match the fp32 oracle of the FULL model within the logit tolerance (max-abs 2e-2), and sample
-identical tokens on every rank.  Run with:  gpurun --gpus 2 -- python -m pytest tests/test_gpu_tp.py -m gpu
+local-shape engine of its shard, must match the fp32 oracle of the FULL model within the logit tolerance
+(max-abs 2e-2) and sample identical tokens on every rank — with the all-reduce done by our own kernel
+over peer memory (multicast and plain peer-to-peer variants, csrc/kb_collective.cu) and by the NCCL
+callback.  The bare collective is also checked bit-exactly on integer-valued data.
+Run with:  gpurun --gpus 2 -- python -m pytest tests/test_gpu_tp.py -m gpu
 """
 import os
 
@@ -11,7 +13,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, port, ret):
+def _worker(rank, world, port, ret, mode):
     import torch.distributed as dist
     from kafka_b200 import cabi
     from kafka_b200.model_config import get_config
@@ -26,7 +28,8 @@ def _worker(rank, world, port, ret):
     try:
         cfg = get_config("tiny-test")
         w = generate_weights(cfg, seed=0)
-        core, grp = build_tp_core(cfg, rank, world, dev, n_blocks=16, max_tokens=512, max_seqs=4, weights=w)
+        core, grp = build_tp_core(cfg, rank, world, dev, n_blocks=16, max_tokens=512, max_seqs=4, weights=w,
+                                  allreduce=mode)
         assert core.cfg.n_heads == cfg.n_heads // world and core.k_pool.shape[2] == cfg.n_kv_heads // world
         g = torch.Generator().manual_seed(1)
         lens = [5, 70, 129]
@@ -60,18 +63,102 @@ def _worker(rank, world, port, ret):
         if rank == 0:
             ret["max_err"] = max(errs)
             ret["ranks_agree"] = all(torch.equal(gathered[0], x) for x in gathered)
-            ret["allreduce_calls"] = grp.calls
+            ret["allreduce_calls"] = getattr(grp, "calls", None)
+            ret["mode"] = grp.mode
         core.close()
+    except Exception as e:  # report instead of a bare spawn failure
+        ret[f"error{rank}"] = repr(e)
+        raise
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
-def test_two_gpu_tensor_parallel_matches_full_oracle():
+needs2 = pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
+
+
+def _spawn(fn, *args):
     import torch.multiprocessing as mp
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(2, 29650 + os.getpid() % 300, ret), nprocs=2, join=True)
+    world = min(torch.cuda.device_count(), 8)
+    world = 2 if world < 4 else (4 if world < 8 else 8)
+    try:
+        mp.spawn(fn, args=(world, 29650 + os.getpid() % 300, ret) + args, nprocs=world, join=True)
+    except Exception:
+        errs = {k: v for k, v in ret.items() if k.startswith("error")}
+        raise AssertionError(f"worker failed: {errs}")
+    return ret, world
+
+
+@needs2
+@pytest.mark.parametrize("mode", ["nccl", "peers", "peers-f16", "peers-p2p"])
+def test_tensor_parallel_matches_full_oracle(mode):
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    try:
+        mp.spawn(_worker, args=(2, 29650 + os.getpid() % 300, ret, mode), nprocs=2, join=True)
+    except Exception:
+        raise AssertionError(f"worker failed: { {k: v for k, v in ret.items() if k.startswith('error')} }")
     assert ret["max_err"] <= 2e-2, ret["max_err"]
     assert ret["ranks_agree"]
-    assert ret["allreduce_calls"] == 5 * 2 * 2        # 5 calls x 2 layers x 2 row-parallel projections
+    if mode == "nccl":
+        assert ret["allreduce_calls"] == 5 * 2 * 2    # 5 calls x 2 layers x 2 row-parallel projections
+    elif mode == "peers-p2p":
+        assert ret["mode"] == "peers-p2p"
+    elif mode == "peers-f16":
+        assert ret["mode"] in ("peers-multicast-f16", "peers-p2p-f16")
+    else:
+        assert ret["mode"] in ("peers-multicast", "peers-p2p")   # multicast where the box supports it
+
+
+def _allreduce_worker(rank, world, port, ret, use_multicast):
+    import torch.distributed as dist
+    from kafka_b200.tp import PeerRegion
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        n_max = 512 * 8192
+        reg = PeerRegion(2 * 4 * n_max, dev, use_multicast=use_multicast)
+        buf = reg.payload()
+        ok = True
+        g = torch.Generator(device="cpu").manual_seed(7)
+        # integer-valued fp32 so every summation order gives the same bits
+        for it, (n, off_elems, blocks) in enumerate([(n_max, 0, 0), (n_max, n_max, 0), (4, 0, 1), (1028, 256, 3),
+                                                     (8192 * 3 + 4, 64, 64), (n_max, 0, 8), (n_max, n_max, 48)] * 3):
+            parts = torch.randint(-1000, 1000, (world, n), generator=g).float()
+            buf[off_elems:off_elems + n].copy_(parts[rank].to(dev))
+            guard_lo = buf[off_elems - 4:off_elems].clone() if off_elems >= 4 else None
+            guard_hi = buf[off_elems + n:off_elems + n + 4].clone()
+            reg.allreduce_(4 * off_elems, n, blocks)
+            want = parts.sum(0).to(dev)
+            ok &= bool(torch.equal(buf[off_elems:off_elems + n], want))
+            ok &= bool(torch.equal(buf[off_elems + n:off_elems + n + 4], guard_hi))
+            if guard_lo is not None:
+                ok &= bool(torch.equal(buf[off_elems - 4:off_elems], guard_lo))
+        h = reg.payload(torch.float16)                   # fp16 on the wire, added in fp32
+        for n, off_elems, blocks in [(n_max, 0, 0), (8, 8, 1), (8192 * 5 + 8, 4096, 7), (n_max, 2 * n_max, 32)]:
+            parts = torch.randint(-100, 100, (world, n), generator=g).half()
+            h[off_elems:off_elems + n].copy_(parts[rank].to(dev))
+            reg.allreduce_(2 * off_elems, n, blocks, f16=True)
+            ok &= bool(torch.equal(h[off_elems:off_elems + n], parts.float().sum(0).half().to(dev)))
+        torch.cuda.synchronize()
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            ret["ok"] = bool(flag.item())
+            ret["multicast"] = reg.multicast
+    except Exception as e:
+        ret[f"error{rank}"] = repr(e)
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+@pytest.mark.parametrize("use_multicast", [True, False])
+def test_peer_allreduce_is_exact_on_integer_data(use_multicast):
+    ret, world = _spawn(_allreduce_worker, use_multicast)
+    assert ret["ok"], f"all-reduce over {world} ranks differs from the exact sum"
