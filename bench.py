@@ -63,7 +63,7 @@ def parse_args():
                     help="serving loop reads every step back before enqueueing the next (A/B of the pipelined loop)")
     ap.add_argument("--tp-compare", action="store_true",
                     help="tensor-parallel run: also time the other all-reduce implementations on the same state")
-    ap.add_argument("--tp-allreduce", default=None, choices=["peers", "peers-f16", "peers-p2p", "nccl"],
+    ap.add_argument("--tp-allreduce", default=None, choices=["peers", "peers-f16", "peers-fused", "peers-p2p", "nccl"],
                     help="all-reduce of the tensor-parallel run (default: own peer-memory kernel, NCCL if unavailable)")
     ap.add_argument("--tp", action="store_true",
                     help="tensor-parallel: ONE model sharded over all ranks (config 5: --model llama-3-70b --history 8192)")
@@ -539,7 +539,7 @@ def run_tp(args, rank, world, local_rank):
     loc = local_config(cfg, world)
     K, W = args.steps, max(args.warmup, 3)
     U = args.user_tokens
-    n_meas = 3 if args.tp_compare else 1
+    n_meas = 4 if args.tp_compare else 1
     bpt = (args.history + U + n_meas * (W + 2 * K) + 8 + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
     B = args.threads
     # weights first (they decide how much HBM is left for KV); a 1-block core, then the real one
@@ -615,16 +615,22 @@ def run_tp(args, rank, world, local_rank):
         # the same resident state under the other all-reduce implementations (switchable at run time)
         from kafka_b200.tp import TPGroup
         blocks = int(os.environ.get("KAFKA_B200_TP_BLOCKS", "0"))
-        main_f16 = grp.wire_f16
+        main_wire = grp.wire
         nccl = TPGroup()
         nccl.attach(core, extra_base=grp.buf)
-        saved_mode, grp.mode = grp.mode, "nccl"
+        grp.mode = "nccl"
         r = measure()
-        others["nccl"] = {"ms_per_step": r["ms_total"] / K, "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K}
-        grp.attach(core, blocks, wire_f16=not main_f16)
-        r = measure()
-        others[grp.mode] = {"ms_per_step": r["ms_total"] / K, "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K}
-        grp.attach(core, blocks, wire_f16=main_f16)
+        others["nccl"] = {"ms_per_step": r["ms_total"] / K, "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K,
+                          "rmsnorm_ms_per_step": r["prof"]["rmsnorm"][0] / K}
+        for wire in ("f32", "f16", "fused"):
+            if wire == main_wire:
+                continue
+            grp.attach(core, blocks, wire=wire)
+            r = measure()
+            others[grp.mode] = {"ms_per_step": r["ms_total"] / K,
+                                "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K,
+                                "rmsnorm_ms_per_step": r["prof"]["rmsnorm"][0] / K}
+        grp.attach(core, blocks, wire=main_wire)
     m = measure()
     ms_total, launches, clocks, prof, ctx_start, ctx_p = (m["ms_total"], m["launches"], m["clocks"], m["prof"],
                                                           m["ctx_start"], m["ctx_p"])
@@ -635,7 +641,7 @@ def run_tp(args, rank, world, local_rank):
     attn_bytes = B * (ctx_p + (K - 1) / 2 + 1) * loc.kv_dim * 2 * 2
     achieved = attn_bytes / (attn_ms / attn_n / 1e3) / 1e9
     ar_ms, ar_n = prof["allreduce"]
-    ar_bytes = (2 if grp.mode.endswith("-f16") else 4) * B * cfg.hidden
+    ar_bytes = (4 if grp.mode in ("nccl", "peers-multicast", "peers-p2p") else 2) * B * cfg.hidden
     line = {
         "metric": METRIC, "value": B * K / (ms_total / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -660,6 +666,12 @@ def run_tp(args, rank, world, local_rank):
                                                          "multicast mapping (kb_collective.cu); the sum is added "
                                                          "to the fp32 residual by the following RMSNorm",
                                   "peers-p2p-f16": "own kernel: fp16 partial sums, peer loads / stores over NVLink",
+                                  "peers-multicast-fused": "own kernel per projection: multimem.ld_reduce of the fp16 "
+                                                           "partial sums of this rank's rows + residual add + RMSNorm "
+                                                           "+ multimem.st of the normed fp16 rows to all ranks "
+                                                           "(kb_tp_reduce_norm_gather, kb_collective.cu)",
+                                  "peers-p2p-fused": "own kernel per projection: reduce + residual add + RMSNorm + "
+                                                     "gather over NVLink peer loads / stores",
                                   "peers-p2p": "own kernel: peer loads / stores over NVLink (kb_collective.cu)"}[grp.mode],
                       "other_modes_same_state": others or None},
         "kernels": {k: {"ms_per_step": v[0] / K, "launches_per_step": v[1] / K} for k, v in prof.items() if v[1]},

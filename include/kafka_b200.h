@@ -140,8 +140,8 @@ int kb_set_tensor_parallel(kb_engine* e, int32_t tp_rank, int32_t tp_size, kb_al
  * place, n fp32 at offset_bytes; `epoch` must be odd, equal on all ranks and grow by 2 per call).
  * A rank whose peers do not arrive within ~2 s traps instead of hanging.  No reference counterpart. */
 #define KB_TP_MAX_RANKS 8
-#define KB_TP_MAX_BLOCKS 64
-#define KB_TP_FLAG_BYTES (KB_TP_MAX_BLOCKS * KB_TP_MAX_RANKS * 4)
+#define KB_TP_MAX_BLOCKS 128 /* grid bound of the collectives: all blocks must be co-resident (148 SMs) */
+#define KB_TP_FLAG_BYTES 2048
 typedef struct kb_tp_peers {
     void* peer_base[KB_TP_MAX_RANKS];
     void* mc_base;
@@ -152,7 +152,20 @@ int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32_t tp_size,
                                  int32_t blocks /* grid of the collective, 0 = default */,
                                  int32_t wire_f16 /* 0: fp32 partial sums, rank 0 folds the residual in;
                                                      1: fp16 partial sums (KB_EPI_F16), added in fp32 by the
-                                                        switch, sum added to the residual by the next RMSNorm */);
+                                                        switch, sum added to the residual by the next RMSNorm
+                                                     2: fp16 partial sums, and the collective, the residual add
+                                                        and the RMSNorm are ONE kernel per projection
+                                                        (kb_tp_reduce_norm_gather): rank r keeps rows
+                                                        [r*ceil(T/size), ...) of the residual stream, norms them
+                                                        once and multicasts the normed fp16 rows; hidden <= 8192.
+                                                        Region use: x fp32 | partial fp16 | normed fp16 */);
+/* The fused kernel of mode 2 on its own (unit tests): reduces n_rows x hidden fp16 partial sums at
+ * partial_offset of the region over all ranks, adds the sums of this rank's rows to x (local fp32,
+ * [n_rows, hidden]), writes fp16(rmsnorm(x) * norm_w) of those rows to xn_offset on EVERY rank.
+ * `epoch` as for kb_allreduce_peers.  No reference counterpart. */
+int kb_tp_reduce_norm_gather(const kb_tp_peers* peers, int32_t rank, int32_t world, size_t partial_offset,
+                             size_t xn_offset, float* x, const void* norm_w_bf16, int32_t n_rows, int32_t hidden,
+                             float eps, uint32_t epoch, int32_t blocks, kb_stream stream);
 int kb_allreduce_peers(const kb_tp_peers* peers, int32_t rank, int32_t world, size_t offset_bytes, size_t n,
                        int32_t f16 /* 0: n fp32; 1: n fp16, added in fp32 */, uint32_t epoch, int32_t blocks,
                        kb_stream stream);

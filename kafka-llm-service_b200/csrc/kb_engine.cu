@@ -39,6 +39,11 @@ int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, co
                  const int* bt, void* out, int n_seqs, int n_tokens, int max_new, int max_blocks, int n_heads,
                  int n_kv_heads, int head_dim, int out_f16, cudaStream_t stream);
 size_t attn_decode_scratch_bytes(int batch, int n_heads, int head_dim, int n_splits);
+int tp_reduce_norm_gather(const kb_tp_peers* P, int rank, int world, size_t partial_off, size_t xn_off, float* x,
+                          const void* norm_w, int T, int hidden, float eps, uint32_t epoch, int blocks,
+                          cudaStream_t stream);
+int gather_last_rows(const void* src_f16, const int* cu_seqlens, void* dst_f16, int n_seqs, int hidden,
+                     cudaStream_t stream);
 int allreduce_peers(const kb_tp_peers* P, int rank, int world, size_t offset_bytes, size_t n, int f16, uint32_t epoch,
                     int blocks, cudaStream_t stream);
 
@@ -117,7 +122,8 @@ struct kb_engine {
     bool use_peers = false;
     kb_tp_peers peers{};
     int peer_blocks = 0;
-    bool peer_wire_f16 = false;   // partial sums travel as fp16 and are added to the residual by the next RMSNorm
+    int peer_wire = 0;            // 0 fp32 partial sums | 1 fp16, added to the residual by the next RMSNorm |
+                                  // 2 fp16, collective + residual add + RMSNorm fused (kb_tp_reduce_norm_gather)
     uint32_t peer_epoch = 1;
     // profiling: one event before every kernel (+ one closing event per call)
     bool prof_on = false;
@@ -184,7 +190,7 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     auto project_into_residual = [&](const void* a, const void* wt, int K) -> int {
         if (e->tp_size <= 1)
             return gemm(a, wt, x, x, n_tokens, c.hidden, K, KB_EPI_RESID_F32 | KB_GEMM_F16, stream);
-        if (e->use_peers && e->peer_wire_f16) {
+        if (e->use_peers && e->peer_wire == 1) {
             int r = gemm(a, wt, w.xr, nullptr, n_tokens, c.hidden, K, KB_EPI_F16 | KB_GEMM_F16, stream);
             if (r) return r;
             mark(KB_PROF_ALLREDUCE);
@@ -214,17 +220,37 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         return KB_OK;
     };
 
+    // Fused tensor-parallel mode: after each row-sharded projection ONE kernel reduces the fp16 partial
+    // sums, adds them to this rank's rows of the residual stream, norms those rows with the NEXT norm's
+    // weights and multicasts the normed rows — the following GEMM reads them from `xn`.
+    const bool fused = e->tp_size > 1 && e->use_peers && e->peer_wire == 2;
+    char* region = fused ? static_cast<char*>(e->peers.peer_base[e->tp_rank]) : nullptr;
+    const size_t part_off = fused ? static_cast<size_t>(reinterpret_cast<char*>(w.xr) - region) : 0;
+    const size_t xn_off = part_off + align256((size_t)e->max_tokens * c.hidden * 2);
+    void* xn = fused ? static_cast<void*>(region + xn_off) : static_cast<void*>(w.xn);
+    auto project_reduce_norm = [&](const void* a, const void* wt, int K, const void* next_norm) -> int {
+        int r = gemm(a, wt, w.xr, nullptr, n_tokens, c.hidden, K, KB_EPI_F16 | KB_GEMM_F16, stream);
+        if (r) return r;
+        mark(KB_PROF_ALLREDUCE);
+        r = tp_reduce_norm_gather(&e->peers, e->tp_rank, e->tp_size, part_off, xn_off, x, next_norm, n_tokens, c.hidden,
+                                  c.rms_eps, e->peer_epoch, e->peer_blocks, stream);
+        e->peer_epoch += 2;
+        return r;
+    };
+
     mark(KB_PROF_EMBED);
     if ((rc = embed(tokens, e->embed, x, n_tokens, c.hidden, c.vocab, stream))) return rc;
     for (int L = 0; L < c.n_layers; ++L) {
         const kb_layer_weights& lw = e->layers[L];
         __nv_bfloat16* kp = e->k_pool + (size_t)L * layer_stride;
         __nv_bfloat16* vp = e->v_pool + (size_t)L * layer_stride;
-        mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(x, lw.attn_norm, w.xn, nullptr, delta, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
-        delta = nullptr;
+        if (!fused || L == 0) {
+            mark(KB_PROF_RMSNORM);
+            if ((rc = rmsnorm(x, lw.attn_norm, xn, nullptr, delta, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+            delta = nullptr;
+        }
         mark(KB_PROF_GEMM_QKV);
-        if ((rc = gemm(w.xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16 | KB_GEMM_F16, stream)))
+        if ((rc = gemm(xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16 | KB_GEMM_F16, stream)))
             return rc;
         mark(KB_PROF_ROPE_APPEND);
         if ((rc = rope_append(w.qkv, cu_seqlens, ctx_lens, block_tables, kp, vp, n_seqs, n_tokens, max_blocks,
@@ -241,16 +267,25 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         }
         if (rc) return rc;
         mark(KB_PROF_GEMM_O);
-        if ((rc = project_into_residual(w.attn, lw.wo, qdim))) return rc;
-        mark(KB_PROF_RMSNORM);
-        if ((rc = rmsnorm(x, lw.mlp_norm, w.xn, nullptr, delta, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
-        delta = nullptr;
+        if (fused) {
+            if ((rc = project_reduce_norm(w.attn, lw.wo, qdim, lw.mlp_norm))) return rc;
+        } else {
+            if ((rc = project_into_residual(w.attn, lw.wo, qdim))) return rc;
+            mark(KB_PROF_RMSNORM);
+            if ((rc = rmsnorm(x, lw.mlp_norm, xn, nullptr, delta, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
+            delta = nullptr;
+        }
         mark(KB_PROF_GEMM_GATE_UP);
-        if ((rc = gemm(w.xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden,
+        if ((rc = gemm(xn, lw.w_gate_up, w.h, nullptr, n_tokens, 2 * c.ffn, c.hidden,
                        KB_EPI_SWIGLU_F16 | KB_GEMM_F16, stream)))
             return rc;
         mark(KB_PROF_GEMM_DOWN);
-        if ((rc = project_into_residual(w.h, lw.w_down, c.ffn))) return rc;
+        if (fused) {
+            const void* next_norm = (L + 1 < c.n_layers) ? e->layers[L + 1].attn_norm : e->final_norm;
+            if ((rc = project_reduce_norm(w.h, lw.w_down, c.ffn, next_norm))) return rc;
+        } else if ((rc = project_into_residual(w.h, lw.w_down, c.ffn))) {
+            return rc;
+        }
     }
     if (logits_out == nullptr && out_tokens == nullptr) {  // KV fill only
         mark(-1);
@@ -258,12 +293,17 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     }
     mark(KB_PROF_RMSNORM);
     // final norm on the last row of every sequence, lm_head, sampling
-    if ((rc = rmsnorm(x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, delta, n_seqs, c.hidden, c.rms_eps, 1,
-                      stream)))
+    const void* xl = w.xl;
+    if (fused) {   // every row is already final-normed in xn: decode uses it as is, prefill picks the last rows
+        if (decode) xl = xn;
+        else if ((rc = gather_last_rows(xn, cu_seqlens, w.xl, n_seqs, c.hidden, stream))) return rc;
+    } else if ((rc = rmsnorm(x, e->final_norm, w.xl, decode ? nullptr : cu_seqlens, delta, n_seqs, c.hidden, c.rms_eps,
+                             1, stream))) {
         return rc;
+    }
     float* lg = logits_out ? logits_out : w.logits;
     mark(KB_PROF_LM_HEAD);
-    if ((rc = gemm(w.xl, e->lm_head, lg, nullptr, n_seqs, c.vocab, c.hidden, KB_EPI_F32 | KB_GEMM_F16, stream)))
+    if ((rc = gemm(xl, e->lm_head, lg, nullptr, n_seqs, c.vocab, c.hidden, KB_EPI_F32 | KB_GEMM_F16, stream)))
         return rc;
     if (out_tokens) {
         mark(KB_PROF_SAMPLE);
@@ -332,7 +372,9 @@ extern "C" int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32
     e->tp_size = tp_size;
     e->peers = *peers;
     e->peer_blocks = blocks;
-    e->peer_wire_f16 = wire_f16 != 0;
+    KB_CHECK(wire_f16 >= 0 && wire_f16 <= 2, "kb_set_tensor_parallel_peers: wire mode %d not in {0,1,2}", wire_f16);
+    KB_CHECK(wire_f16 != 2 || e->cfg.hidden <= 8192, "kb_set_tensor_parallel_peers: fused mode needs hidden <= 8192");
+    e->peer_wire = wire_f16;
     // peer_epoch is never reset: re-configuring (blocks, wire format, back from the callback) must continue
     // the flag sequence of the region
     e->use_peers = true;

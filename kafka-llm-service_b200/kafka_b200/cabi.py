@@ -57,8 +57,8 @@ class Sampling(C.Structure):
                 ("seq_temperature", C.c_void_p), ("seq_seed", C.c_void_p)]
 
 
-TP_MAX_RANKS, TP_MAX_BLOCKS = 8, 64
-TP_FLAG_BYTES = TP_MAX_BLOCKS * TP_MAX_RANKS * 4
+TP_MAX_RANKS, TP_MAX_BLOCKS = 8, 128
+TP_FLAG_BYTES = 2048
 
 
 class TpPeers(C.Structure):
@@ -95,6 +95,8 @@ SIGNATURES = {
     "kb_set_tensor_parallel": (C.c_int, [_vp, _i32, _i32, ALLREDUCE_FN, _vp]),
     "kb_set_tensor_parallel_peers": (C.c_int, [_vp, _i32, _i32, C.POINTER(TpPeers), _i32, _i32]),
     "kb_allreduce_peers": (C.c_int, [C.POINTER(TpPeers), _i32, _i32, _sz, _sz, _i32, C.c_uint32, _i32, _vp]),
+    "kb_tp_reduce_norm_gather": (C.c_int, [C.POINTER(TpPeers), _i32, _i32, _sz, _sz, _vp, _vp, _i32, _i32, _f,
+                                           C.c_uint32, _i32, _vp]),
     "kb_profile_begin": (C.c_int, [_vp]),
     "kb_profile_end": (C.c_int, [_vp, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "kb_last_error": (C.c_char_p, []),

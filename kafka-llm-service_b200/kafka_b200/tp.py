@@ -182,20 +182,26 @@ class PeerRegion:
                    "kb_allreduce_peers")
         self.epoch += 2
 
-    def attach(self, core, blocks: int = 0, wire_f16: bool = False) -> None:
+    WIRE = {"f32": 0, "f16": 1, "fused": 2}
+
+    def attach(self, core, blocks: int = 0, wire: str = "f32") -> None:
         """Move the engine's residual / partial-sum buffers into this region and switch it to the in-kernel
-        all-reduce (the region must hold 2 x align256(max_tokens * hidden * 4) bytes). May be called again
-        to change the grid or the wire format. wire_f16: partial sums cross NVLink as fp16 (added in fp32)."""
+        collective (the region must hold residual_region_bytes()). May be called again to change the grid
+        or the wire format:
+          "f32"    fp32 partial sums all-reduced in place (rank 0 folds the residual in)
+          "f16"    fp16 partial sums (half the NVLink bytes, added in fp32), residual add in the next RMSNorm
+          "fused"  fp16 partial sums; reduce-scatter + residual add + RMSNorm + all-gather of the normed rows
+                   in one kernel per projection (each rank norms only its rows); hidden <= 8192"""
         cabi.check(core.lib.kb_set_tensor_parallel_peers(core._h, self.rank, self.size, C.byref(self.peers), blocks,
-                                                         int(wire_f16)),
+                                                         self.WIRE[wire]),
                    "kb_set_tensor_parallel_peers")
-        self.wire_f16 = wire_f16
-        self.mode = ("peers-multicast" if self.multicast else "peers-p2p") + ("-f16" if wire_f16 else "")
+        self.wire = wire
+        self.mode = ("peers-multicast" if self.multicast else "peers-p2p") + ("" if wire == "f32" else "-" + wire)
 
 
 def residual_region_bytes(cfg: LlamaConfig, max_tokens: int) -> int:
     each = (max_tokens * cfg.hidden * 4 + 255) & ~255
-    return 2 * each
+    return 2 * each + 512
 
 
 def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, max_tokens: int, max_seqs: int,
@@ -205,8 +211,9 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
     FULL weights (tests); None draws the shard on the device (benchmarks).
 
     allreduce: "peers" (our kernel over the NVSwitch multicast mapping, fp32 partial sums), "peers-f16" (same,
-    fp16 partial sums: half the NVLink bytes), "peers-p2p" (plain peer loads / stores, no multicast), "nccl"
-    (torch.distributed callback), or None = $KAFKA_B200_TP_ALLREDUCE, default "auto" = "peers-f16" with a
+    fp16 partial sums: half the NVLink bytes), "peers-fused" (fp16 partial sums; collective, residual add and
+    RMSNorm in one kernel), "peers-p2p" (plain peer loads / stores, no multicast, fp32), "nccl"
+    (torch.distributed callback), or None = $KAFKA_B200_TP_ALLREDUCE, default "auto" = "peers-fused" with a
     logged fall-back to NCCL when the symmetric mapping cannot be set up."""
     import os
     import sys
@@ -220,12 +227,13 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
     grp = None
     if tp > 1:
         mode = allreduce or os.environ.get("KAFKA_B200_TP_ALLREDUCE", "auto")
-        if mode in ("auto", "peers", "peers-f16", "peers-p2p"):
+        if mode in ("auto", "peers", "peers-f16", "peers-fused", "peers-p2p"):
             try:
                 grp = PeerRegion(residual_region_bytes(loc, max_tokens), device, group,
                                  use_multicast=(mode != "peers-p2p"))
                 grp.attach(core, int(os.environ.get("KAFKA_B200_TP_BLOCKS", "0")),
-                           wire_f16=mode in ("auto", "peers-f16"))
+                           wire={"peers-f16": "f16", "peers-fused": "fused",
+                                 "auto": "fused" if cfg.hidden <= 8192 else "f16"}.get(mode, "f32"))
             except Exception as e:
                 if mode != "auto":
                     raise

@@ -91,7 +91,7 @@ def _spawn(fn, *args):
 
 
 @needs2
-@pytest.mark.parametrize("mode", ["nccl", "peers", "peers-f16", "peers-p2p"])
+@pytest.mark.parametrize("mode", ["nccl", "peers", "peers-f16", "peers-fused", "peers-p2p"])
 def test_tensor_parallel_matches_full_oracle(mode):
     import torch.multiprocessing as mp
     mgr = mp.Manager()
@@ -106,8 +106,8 @@ def test_tensor_parallel_matches_full_oracle(mode):
         assert ret["allreduce_calls"] == 5 * 2 * 2    # 5 calls x 2 layers x 2 row-parallel projections
     elif mode == "peers-p2p":
         assert ret["mode"] == "peers-p2p"
-    elif mode == "peers-f16":
-        assert ret["mode"] in ("peers-multicast-f16", "peers-p2p-f16")
+    elif mode in ("peers-f16", "peers-fused"):
+        assert ret["mode"] in ("peers-multicast-" + mode[6:], "peers-p2p-" + mode[6:])
     else:
         assert ret["mode"] in ("peers-multicast", "peers-p2p")   # multicast where the box supports it
 
@@ -162,3 +162,67 @@ def _allreduce_worker(rank, world, port, ret, use_multicast):
 def test_peer_allreduce_is_exact_on_integer_data(use_multicast):
     ret, world = _spawn(_allreduce_worker, use_multicast)
     assert ret["ok"], f"all-reduce over {world} ranks differs from the exact sum"
+
+
+def _fused_worker(rank, world, port, ret, use_multicast):
+    """kb_tp_reduce_norm_gather against torch: partial sums are small integers (exact in fp16, so the
+    reduced values and the fp32 residual rows must be bit-exact); the normed rows within one fp16 ulp."""
+    import ctypes as C
+    import torch.distributed as dist
+    from kafka_b200 import cabi
+    from kafka_b200.tp import PeerRegion
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        ok, worst = True, 0.0
+        g = torch.Generator(device="cpu").manual_seed(11)
+        t_max, h_max = 600, 8192
+        half = (t_max * h_max * 2 + 255) & ~255
+        reg = PeerRegion(2 * half, dev, use_multicast=use_multicast)
+        pay16 = reg.payload(torch.float16)
+        for T, H, blocks in [(473, 8192, 0), (5, 256, 3), (64, 4096, 8), (600, 2048, 64), (1, 64, 1), (37, 8192, 16)]:
+            parts = torch.randint(-8, 9, (world, T, H), generator=g).half()
+            x0 = torch.randn(T, H, generator=g)
+            w = (1.0 + 0.1 * torch.randn(H, generator=g)).bfloat16()
+            pay16[:T * H].copy_(parts[rank].reshape(-1).to(dev))
+            pay16[half // 2:half // 2 + T * H].fill_(-77.0)                     # xn area: must be overwritten
+            x = x0.to(dev).clone()
+            wd = w.to(dev)
+            torch.cuda.synchronize()
+            dist.barrier()
+            cabi.check(cabi.load().kb_tp_reduce_norm_gather(C.byref(reg.peers), rank, world, 0, half, x.data_ptr(),
+                                                            wd.data_ptr(), T, H, 1e-5, reg.epoch, blocks,
+                                                            torch.cuda.current_stream().cuda_stream), "fused")
+            reg.epoch += 2
+            torch.cuda.synchronize()
+            per = (T + world - 1) // world
+            lo, hi = rank * per, min(T, (rank + 1) * per)
+            d = parts.float().sum(0)
+            want_x = x0.clone()
+            want_x[lo:hi] += d[lo:hi]                                           # only this rank's rows change
+            ok &= bool(torch.equal(x.cpu(), want_x))
+            full = x0 + d
+            want_n = (full * torch.rsqrt(full.pow(2).mean(-1, keepdim=True) + 1e-5) * w.float())
+            got_n = pay16[half // 2:half // 2 + T * H].view(T, H).float().cpu()
+            err = ((got_n - want_n).abs() / (want_n.abs() + 1e-2)).max().item()
+            worst = max(worst, err)
+            ok &= err < 2e-3
+            dist.barrier()
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            ret["ok"], ret["worst"] = bool(flag.item()), worst
+    except Exception as e:
+        ret[f"error{rank}"] = repr(e)
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+@pytest.mark.parametrize("use_multicast", [True, False])
+def test_fused_reduce_norm_gather_matches_torch(use_multicast):
+    ret, world = _spawn(_fused_worker, use_multicast)
+    assert ret["ok"], f"fused reduce + residual + RMSNorm + gather over {world} ranks: worst rel err {ret['worst']}"

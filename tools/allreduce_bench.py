@@ -70,6 +70,23 @@ def main():
         ours = [(v, k) for k, v in row.items() if k.startswith("peers")]
         for name, reg in regions.items():                # the same T x hidden message as fp16 (half the bytes)
             row[f"f16_{name}_us"] = min(timed(lambda: reg.allreduce_(0, n, b, f16=True)) for b in args.blocks[-2:])
+        # reduce-scatter + residual add + RMSNorm + all-gather in one kernel (the engine's default mode)
+        if args.hidden <= 8192 and "peers-multicast" in regions:
+            import ctypes as C
+            from kafka_b200 import cabi
+            reg = regions["peers-multicast"]
+            xres = torch.zeros(n, dtype=torch.float32, device=dev)
+            wn = torch.ones(args.hidden, dtype=torch.bfloat16, device=dev)
+            xn_off = (2 * n + 255) & ~255
+
+            def fused(b):
+                cabi.check(cabi.load().kb_tp_reduce_norm_gather(C.byref(reg.peers), reg.rank, reg.size, 0, xn_off,
+                                                                xres.data_ptr(), wn.data_ptr(), T, args.hidden, 1e-5,
+                                                                reg.epoch, b, torch.cuda.current_stream().cuda_stream),
+                           "fused")
+                reg.epoch += 2
+            for b in args.blocks:
+                row[f"fused_b{b}_us"] = timed(lambda: fused(b))
         half = nccl_buf[:n // 2].view(torch.float16)
         row["f16_nccl_us"] = timed(lambda: dist.all_reduce(half))
         if ours:
