@@ -450,7 +450,7 @@ def run_b200(args, rank, world, local_rank):
             "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_kind": peak_kind,
             "traffic_note": "ncu --set full cannot replay with the 140 GB pool resident; at 128 threads the same kernel "
                             "moved 1.131 GB of DRAM traffic per launch for 1.110 GB algorithmic (x1.019, "
-                            "profiles/r01_ncu_attn_decode_full_metrics.csv)",
+                            "profiles/r01b_ncu_attn_decode_metrics.csv)",
             "bytes_per_launch": attn_bytes, "us_per_launch": attn_ms / attn_n * 1e3,
             "share_of_step": attn_ms / sum(v[0] for v in prof.values()),
             "step": {"algorithmic_bytes": avg_step_bytes, "achieved": step_gbs, "frac": step_gbs / hbm_peak},
@@ -525,8 +525,9 @@ def run_b200(args, rank, world, local_rank):
 
 
 def run_tp(args, rank, world, local_rank):
-    """BASELINE config 5 shape: one model sharded over all `world` GPUs (tensor parallel, NCCL all-reduce
-    over NVLink after the O and down projections), all ranks stepping the same batch in lockstep."""
+    """BASELINE config 5 shape: one model sharded over all `world` GPUs (tensor parallel; the sums after the
+    O and down projections by our own kernels over NVSwitch multicast memory, see kafka_b200/tp.py), all
+    ranks stepping the same batch in lockstep."""
     from kafka_b200 import cabi
     from kafka_b200.cabi import KB_BLOCK_TOKENS
     from kafka_b200.engine_core import EngineCore

@@ -5,14 +5,17 @@ Megatron-style sharding, one process per GPU:
     wq / wk / wv, w_gate / w_up   column-parallel: each rank owns n_heads/tp query heads, n_kv_heads/tp
                                   KV heads and ffn/tp MLP columns (rows of the [out, in] weight)
     wo, w_down                    row-parallel: each rank owns the matching K-slice; the partial sums are
-                                  added over the ranks — 2 all-reduces of [T, hidden] fp32 per layer
+                                  added over the ranks — 2 collectives over [T, hidden] per layer
     embed, norms, lm_head         replicated (every rank samples the same token, no gather)
     KV cache                      sharded by KV head: each rank stores only its heads' blocks
 
-The engine itself is TP-agnostic: it is created with the rank's LOCAL shapes and calls back into
-`TPGroup.allreduce` where the sums are needed (include/kafka_b200.h, kb_set_tensor_parallel). The
-all-reduce is NCCL over NVLink/NVSwitch through torch.distributed on the call's stream. All ranks
-issue identical kb_prefill / kb_decode calls (SPMD).
+The engine is created with the rank's LOCAL shapes. The sums over ranks are done by our own kernels
+over peer memory (csrc/kb_collective.cu; include/kafka_b200.h, kb_set_tensor_parallel_peers): this
+module only provides the symmetric region they work on (`PeerRegion`: torch's symmetric-memory
+rendezvous for allocation, peer mappings and the NVSwitch multicast mapping). Default: fp16 partial
+sums and ONE kernel per projection that reduces, adds to the residual, RMS-norms and gathers. The
+NCCL all-reduce through torch.distributed (`TPGroup`, kb_set_tensor_parallel) is kept as the
+alternative. All ranks issue identical kb_prefill / kb_decode calls (SPMD).
 
 The reference has no counterpart: its models run behind a gateway (/root/reference/src/llm/portkey.py:379).
 """
