@@ -78,6 +78,7 @@ class EngineCore:
 
     def close(self) -> None:
         if getattr(self, "_h", None):
+            torch.cuda.synchronize(self.device)     # nothing enqueued may outlive the buffers it borrows
             self.lib.kb_engine_destroy(self._h)
             self._h = None
 

@@ -52,14 +52,11 @@ class _Staging:
         d[:n].copy_(h[:n], non_blocking=True)
         return d[:n]
 
-    def stage(self, tokens: Optional[List[int]], cu: Optional[List[int]], ctx: List[int], reqs: Sequence[Request]):
-        torch = self.torch
-        n = len(reqs)
-        d_tok = self._up(self.h_tok, self.d_tok, tokens, torch.int32, torch) if tokens is not None else self.d_tok[:n]
-        d_cu = self._up(self.h_cu, self.d_cu, cu, torch.int32, torch) if cu is not None else None
-        d_ctx = self._up(self.h_ctx, self.d_ctx, ctx, torch.int32, torch)
+    def plan(self, reqs: Sequence[Request]) -> dict:
+        """Host-only: which per-membership arrays have to be uploaded again for this batch."""
         key = tuple((r.req_id, len(r.entry.blocks)) for r in reqs)
         mb = max(1, max(len(r.entry.blocks) for r in reqs))
+        p = {"mb": mb}
         if key != self.bt_key:
             flat: List[int] = []
             for r in reqs:
@@ -67,22 +64,37 @@ class _Staging:
                 flat += b
                 if len(b) < mb:
                     flat += [0] * (mb - len(b))
-            self._up(self.h_bt, self.d_bt, flat, torch.int32, torch)
+            p["bt"] = flat
             self.bt_key = key
         if key != self.sp_key:
-            self._up(self.h_temp, self.d_temp, [r.params.temperature for r in reqs], torch.float32, torch)
-            self._up(self.h_seed, self.d_seed,
-                     [(r.params.seed * 0x9E3779B97F4A7C15 + r.req_id) & 0x7FFFFFFFFFFFFFFF for r in reqs],
-                     torch.int64, torch)
+            p["temp"] = [r.params.temperature for r in reqs]
+            p["seed"] = [(r.params.seed * 0x9E3779B97F4A7C15 + r.req_id) & 0x7FFFFFFFFFFFFFFF for r in reqs]
             self.sp_key = key
-        return d_tok, d_cu, d_ctx, self.d_bt[:n * mb].view(n, mb)
+        return p
 
-    def stage_src(self, src: List[int]):
-        """Result slots the in-flight conversations' ids come from (-1: the host staged the id)."""
-        if src != self.src_key:
-            self._up(self.h_src, self.d_src, src, self.torch.int32, self.torch)
-            self.src_key = src
-        return self.d_src[:len(src)]
+    def plan_src(self, src: List[int]) -> Optional[List[int]]:
+        """Result slots the in-flight conversations' ids come from (-1: the host staged the id); None
+        when the device copy is still right."""
+        if src == self.src_key:
+            return None
+        self.src_key = src
+        return src
+
+    def apply(self, n: int, tokens: Optional[List[int]], cu: Optional[List[int]], ctx: List[int], p: dict):
+        """Upload what the plan carries; returns the device views the call needs."""
+        torch = self.torch
+        d_tok = self._up(self.h_tok, self.d_tok, tokens, torch.int32, torch) if tokens is not None else self.d_tok[:n]
+        d_cu = self._up(self.h_cu, self.d_cu, cu, torch.int32, torch) if cu is not None else None
+        d_ctx = self._up(self.h_ctx, self.d_ctx, ctx, torch.int32, torch)
+        if "bt" in p:
+            self._up(self.h_bt, self.d_bt, p["bt"], torch.int32, torch)
+        if "temp" in p:
+            self._up(self.h_temp, self.d_temp, p["temp"], torch.float32, torch)
+            self._up(self.h_seed, self.d_seed, p["seed"], torch.int64, torch)
+        if p.get("src") is not None:
+            self._up(self.h_src, self.d_src, p["src"], torch.int32, torch)
+        mb = p["mb"]
+        return d_tok, d_cu, d_ctx, self.d_bt[:n * mb].view(n, mb)
 
 
 class _Handle:
@@ -116,21 +128,6 @@ class GpuStepper(Stepper):
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
-    def _sampling(self, st: _Staging):
-        self.step_no += 1
-        lo, hi, ea, eb = self.cand
-        return self.cabi.make_sampling(temperature=0.0, seed=0, step=self.step_no, banned_token=self.banned_token,
-                                       allowed_lo=lo,
-                                       allowed_hi=hi, extra_a=ea, extra_b=eb, seq_temperature=st.d_temp,
-                                       seq_seed=st.d_seed)
-
-    def _finish_launch(self, st: _Staging, base: int, n: int, last) -> _Handle:
-        if n:
-            self.h_res[base:base + n].copy_(self.d_res[base:base + n], non_blocking=True)
-            self.d2h_bytes += 4 * n
-        st.event.record(self.stream)
-        return _Handle(st.event, base, n, last)
-
     def fetch(self, h: _Handle) -> List[Optional[int]]:
         h.event.synchronize()
         if h.last is None:                      # decode step: one id per sequence
@@ -140,39 +137,81 @@ class GpuStepper(Stepper):
         out = self.h_res[h.base:h.base + h.n].tolist()
         return [out[i] if is_last else None for i, is_last in enumerate(h.last)]
 
-    def prefill_launch(self, items: List[PrefillItem], parity: int) -> _Handle:
-        st = self.st_prefill[parity]
-        with self.torch.cuda.stream(self.stream):
-            toks: List[int] = []
-            cu = [0]
-            for it in items:
-                toks += it.tokens
-                cu.append(len(toks))
-            reqs = [it.req for it in items]
-            d_tok, d_cu, d_ctx, d_bt = st.stage(toks, cu, [it.ctx_len for it in items], reqs)
-            self.h2d_bytes += 4 * (len(toks) + 2 * len(items) + 1)
-            last = [it.is_last_chunk for it in items]
-            n = len(items) if any(last) else 0
-            base = self.slot(parity, True, 0)
-            self.core.prefill(d_tok, d_cu, d_ctx, d_bt, max(len(it.tokens) for it in items), self._sampling(st),
-                              None, self.d_res[base:base + n] if n else None)
-            return self._finish_launch(st, base, n, last)
+    # A launch is split in two: plan_*() turns the scheduler's objects into a plain dict (host only),
+    # run_plan() uploads and enqueues it. With tensor parallelism the leader publishes the dict and every
+    # rank runs the same plan (tp_serve.py); on one GPU `publish` stays None.
+    publish = None
 
-    def decode_launch(self, reqs: List[Request], parity: int) -> _Handle:
+    def plan_prefill(self, items: List[PrefillItem], parity: int) -> dict:
+        toks: List[int] = []
+        cu = [0]
+        for it in items:
+            toks += it.tokens
+            cu.append(len(toks))
+        p = self.st_prefill[parity].plan([it.req for it in items])
+        self.step_no += 1
+        p.update(op="prefill", parity=parity, n=len(items), tokens=toks, cu=cu, ctx=[it.ctx_len for it in items],
+                 last=[it.is_last_chunk for it in items], max_new=max(len(it.tokens) for it in items),
+                 step=self.step_no, banned=self.banned_token)
+        return p
+
+    def plan_decode(self, reqs: List[Request], parity: int) -> dict:
         st = self.st_decode[parity]
         n = len(reqs)
+        ctx = [r.ctx_len for r in reqs]
+        src = [r.out_slot if r.inflight > 0 else -1 for r in reqs]
+        n_dev = n - src.count(-1)
+        p = st.plan(reqs)
+        self.step_no += 1
+        p.update(op="decode", parity=parity, n=n, ctx=ctx, select=n_dev > 0, src=st.plan_src(src) if n_dev else None,
+                 tokens=None if n_dev == n else [r.generated[-1] if r.inflight == 0 else 0 for r in reqs],
+                 step=self.step_no, banned=self.banned_token)
+        return p
+
+    def run_plan(self, p: dict, read_back: bool = True) -> _Handle:
+        parity, n = p["parity"], p["n"]
+        lo, hi, ea, eb = self.cand
         with self.torch.cuda.stream(self.stream):
-            ctx = [r.ctx_len for r in reqs]
-            src = [r.out_slot if r.inflight > 0 else -1 for r in reqs]
-            n_dev = n - src.count(-1)
-            toks = None if n_dev == n else [r.generated[-1] if r.inflight == 0 else 0 for r in reqs]
-            d_tok, _, d_ctx, d_bt = st.stage(toks, None, ctx, reqs)
-            self.h2d_bytes += 4 * n + (4 * n if toks is not None else 0)
-            if n_dev:
-                self.cabi.select_tokens(d_tok, self.d_res, st.stage_src(src))
-            base = self.slot(parity, False, 0)
-            self.core.decode(d_tok, d_ctx, d_bt, self._sampling(st), self.d_res[base:base + n], max_ctx=max(ctx))
-            return self._finish_launch(st, base, n, None)
+            if p["op"] == "prefill":
+                st = self.st_prefill[parity]
+                d_tok, d_cu, d_ctx, d_bt = st.apply(n, p["tokens"], p["cu"], p["ctx"], p)
+                self.h2d_bytes += 4 * (len(p["tokens"]) + 2 * n + 1)
+                last = p["last"]
+                n_out = n if any(last) else 0
+                base = self.slot(parity, True, 0)
+            else:
+                st = self.st_decode[parity]
+                d_tok, d_cu, d_ctx, d_bt = st.apply(n, p["tokens"], None, p["ctx"], p)
+                self.h2d_bytes += 4 * n + (4 * n if p["tokens"] is not None else 0)
+                if p["select"]:
+                    self.cabi.select_tokens(d_tok, self.d_res, st.d_src[:n])
+                last, n_out = None, n
+                base = self.slot(parity, False, 0)
+            sp = self.cabi.make_sampling(temperature=0.0, seed=0, step=p["step"], banned_token=p["banned"],
+                                         allowed_lo=lo, allowed_hi=hi, extra_a=ea, extra_b=eb,
+                                         seq_temperature=st.d_temp, seq_seed=st.d_seed)
+            out = self.d_res[base:base + n_out] if n_out else None
+            if p["op"] == "prefill":
+                self.core.prefill(d_tok, d_cu, d_ctx, d_bt, p["max_new"], sp, None, out)
+            else:
+                self.core.decode(d_tok, d_ctx, d_bt, sp, out, max_ctx=max(p["ctx"]))
+            if n_out and read_back:
+                self.h_res[base:base + n_out].copy_(self.d_res[base:base + n_out], non_blocking=True)
+                self.d2h_bytes += 4 * n_out
+            st.event.record(self.stream)
+            return _Handle(st.event, base, n_out, last)
+
+    def prefill_launch(self, items: List[PrefillItem], parity: int) -> _Handle:
+        p = self.plan_prefill(items, parity)
+        if self.publish is not None:
+            self.publish(p)
+        return self.run_plan(p)
+
+    def decode_launch(self, reqs: List[Request], parity: int) -> _Handle:
+        p = self.plan_decode(reqs, parity)
+        if self.publish is not None:
+            self.publish(p)
+        return self.run_plan(p)
 
     def close(self) -> None:
         self.core.close()

@@ -226,3 +226,75 @@ def _fused_worker(rank, world, port, ret, use_multicast):
 def test_fused_reduce_norm_gather_matches_torch(use_multicast):
     ret, world = _spawn(_fused_worker, use_multicast)
     assert ret["ok"], f"fused reduce + residual + RMSNorm + gather over {world} ranks: worst rel err {ret['worst']}"
+
+
+def _serve_worker(rank, world, port, ret):
+    """Rank 0 serves completions through B200LLMProvider on a 2-way tensor-parallel model (scheduler,
+    pipelined loop, prefix reuse); rank 1 only mirrors the launch plans. Texts must equal the oracle's."""
+    import asyncio
+    import torch.distributed as dist
+    from kafka_b200.llm import Message
+    from kafka_b200.model_config import get_config
+    from kafka_b200.provider import B200LLMProvider
+    from kafka_b200.tokenizer import ByteTokenizer
+    from kafka_b200.tp_serve import build_tp_stepper, follow, lead
+    from kafka_b200.weights import generate_weights
+    from oracle.cpu_provider import CPUOracleProvider
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        cfg = get_config("tiny-test")
+        w = generate_weights(cfg, seed=0, init="margin")
+        stepper, chan = build_tp_stepper(cfg, dev, n_blocks=256, max_tokens=1024, max_seqs=16, weights=w)
+        if rank != 0:
+            ret["follower_plans"] = follow(stepper, chan)
+            return
+        eng = lead(stepper, chan)
+        gpu = B200LLMProvider(eng, ByteTokenizer(cfg.vocab), model=cfg.name, default_temperature=0.0)
+        cpu = CPUOracleProvider(cfg, w)
+
+        async def run():
+            import random
+            bad, cached = [], []
+            hist = {i: [Message(role="system", content="You are terse.")] for i in range(12)}
+            for turn in range(3):
+                for i in hist:
+                    rnd = random.Random(100 * i + turn)
+                    hist[i].append(Message(role="user", content="".join(chr(rnd.randrange(32, 127)) for _ in range(40))))
+                got = await asyncio.gather(*[gpu.completion(h, temperature=0.0, max_tokens=24, thread_id=f"t{i}")
+                                             for i, h in hist.items()])
+                for (i, h), r in zip(hist.items(), got):
+                    want = await cpu.completion(h, temperature=0.0, max_tokens=24)
+                    if (r.content, r.finish_reason) != (want.content, want.finish_reason):
+                        bad.append((i, turn, r.content, want.content))
+                    cached.append((turn, r.usage["cached_tokens"]))
+                    h.append(Message(role="assistant", content=r.content))
+            return bad, cached
+        bad, cached = asyncio.run(run())
+        ret["bad"], ret["mode"] = bad, stepper.tp_group.mode
+        ret["cached_later"] = min(c for t, c in cached if t > 0)
+        ret["decode_steps"] = eng.stats()["decode_steps"]
+        eng.shutdown()
+    except Exception as e:
+        ret[f"error{rank}"] = repr(e)
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+def test_tensor_parallel_serving_leader_and_follower():
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    try:
+        mp.spawn(_serve_worker, args=(2, 29650 + (os.getpid() + 11) % 300, ret), nprocs=2, join=True)
+    except Exception:
+        raise AssertionError(f"worker failed: { {k: v for k, v in ret.items() if k.startswith('error')} }")
+    assert ret["bad"] == [], ret["bad"][:2]
+    assert ret["mode"].startswith("peers-")                   # our collectives, not the NCCL fallback
+    assert ret["cached_later"] > 0 and ret["decode_steps"] > 20
+    assert ret["follower_plans"] >= ret["decode_steps"]

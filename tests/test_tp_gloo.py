@@ -75,3 +75,116 @@ def test_shard_shapes_and_fusion():
     f = fuse_for_engine(local_config(cfg, 2), parts[1], "cpu")
     assert f["l0.wqkv"].shape == (2 * 64 + 2 * 64, 256) and f["l0.w_gate_up"].shape == (512, 256)
     assert f["l0.wo"].shape == (256, 128) and f["l0.w_down"].shape == (256, 256)
+
+
+# ---- serving a tensor-parallel model: the leader's launch plans mirrored on a follower (tp_serve.py) ----
+def _serve_worker(rank, world, port, ret):
+    import hashlib
+    import pickle
+    import sys
+    sys.path.insert(0, os.path.dirname(__file__))
+    from fakes import FakeStepper, expected_tokens
+    from kafka_b200.scheduler import SamplingParams
+    from kafka_b200.tp_serve import PlanChannel, follow, lead
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        chan = PlanChannel(dist.new_group(backend="gloo"))
+
+        class PlanFake(FakeStepper):
+            """FakeStepper with the plan / run_plan split of GpuStepper: the plan carries what a shard
+            needs (tokens, positions, block ids), run_plan executes it on this rank's own fake KV."""
+            publish = None
+
+            def __init__(self, **kw):
+                super().__init__(**kw)
+                self.digest = hashlib.blake2b(digest_size=8)
+                self.n_plans = 0
+
+            def _plan(self, op, parity, rows):
+                return {"op": op, "parity": parity, "rows": rows}
+
+            def prefill_launch(self, items, parity):
+                p = self._plan("prefill", parity, [(list(it.req.entry.blocks), it.ctx_len, list(it.tokens),
+                                                     it.is_last_chunk) for it in items])
+                if self.publish:
+                    self.publish(p)
+                return self.run_plan(p)
+
+            def decode_launch(self, reqs, parity):
+                p = self._plan("decode", parity, [(list(r.entry.blocks), r.ctx_len,
+                                                    r.out_slot if r.inflight > 0 else None,
+                                                    None if r.inflight > 0 else r.generated[-1]) for r in reqs])
+                if self.publish:
+                    self.publish(p)
+                return self.run_plan(p)
+
+            def run_plan(self, p, read_back=True):
+                self.n_plans += 1
+                self.digest.update(pickle.dumps(p))
+                slots = []
+                if p["op"] == "prefill":
+                    for i, (blocks, ctx, toks, last) in enumerate(p["rows"]):
+                        for k, t in enumerate(toks):
+                            self._write(blocks, ctx + k, t)
+                        if last:
+                            s = self.slot(p["parity"], True, i)
+                            from fakes import next_token
+                            self.res[s] = next_token(self._read(blocks, ctx + len(toks)), self.eos_id, self.eos_every)
+                            slots.append(s)
+                        else:
+                            slots.append(None)
+                else:
+                    from fakes import next_token
+                    fed = [self.res[src] if src is not None else tok for _, _, src, tok in p["rows"]]
+                    for i, ((blocks, ctx, _, _), tok) in enumerate(zip(p["rows"], fed)):
+                        self._write(blocks, ctx, tok)
+                        s = self.slot(p["parity"], False, i)
+                        self.res[s] = next_token(self._read(blocks, ctx + 1), self.eos_id, self.eos_every)
+                        slots.append(s)
+                return slots
+
+            def fetch(self, handle):
+                return [None if s is None else self.res[s] for s in handle]
+
+        st = PlanFake(n_blocks=64, max_seqs=4, max_tokens=256, max_pos=1024, eos_id=511)
+        if rank != 0:
+            n = follow(st, chan)
+            ret["follower_plans"], ret["follower_digest"] = n, st.digest.hexdigest()
+            # the follower's own KV produced the same ids as the leader's (it never read any back)
+            ret["follower_res"] = dict(st.res)
+            return
+        eng = lead(st, chan, max_prefill_tokens=96)
+        import threading
+        prompts = [list(range(40 + i, 40 + i + 50 + 37 * i)) for i in range(6)]
+        done = [threading.Event() for _ in prompts]
+        outs = [[] for _ in prompts]
+
+        def cb(i):
+            def on_event(ev):
+                if ev[0] == "token":
+                    outs[i].append(ev[1])
+                elif ev[0] in ("finish", "error"):
+                    done[i].set()
+            return on_event
+        for i, p in enumerate(prompts):
+            eng.submit(p, SamplingParams(max_tokens=9 + i), cb(i), thread_hint=f"t{i}")
+        for d in done:
+            assert d.wait(20)
+        ret["leader_ok"] = all(o == expected_tokens(p, 9 + i, 511) for i, (p, o) in enumerate(zip(prompts, outs)))
+        eng.shutdown()
+        ret["leader_plans"], ret["leader_digest"], ret["leader_res"] = st.n_plans, st.digest.hexdigest(), dict(st.res)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_leader_plans_are_mirrored_on_the_follower():
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    port = 29500 + (os.getpid() + 7) % 400
+    mp.spawn(_serve_worker, args=(2, port, ret), nprocs=2, join=True)
+    assert ret["leader_ok"]
+    assert ret["leader_plans"] == ret["follower_plans"] > 10
+    assert ret["leader_digest"] == ret["follower_digest"]      # same plans, same order
+    assert ret["leader_res"] == ret["follower_res"]            # and the same ids on the follower's "device"
