@@ -68,14 +68,15 @@ __device__ __forceinline__ float silu_f(float g) { return g / (1.0f + __expf(-g)
 
 template <int EPI>
 __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* out, const float* resid, int row,
-                                                 int col0, int N) {
-    // 32 consecutive fp32 accumulator columns [col0, col0+32) of one row. N % 8 == 0.
+                                                 int col0, int N, int ncols) {
+    // 32 consecutive fp32 accumulator columns [col0, col0+32) of one row, of which the first `ncols`
+    // (a multiple of 8; of 16 for SwiGLU) belong to this tile and lie inside N.
     if (EPI == KB_EPI_BF16 || EPI == KB_EPI_F16) {
         uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)row * N + col0;
         constexpr int f16 = (EPI == KB_EPI_F16);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            if (col0 + j * 8 < N) {
+            if (j * 8 < ncols) {
                 uint4 v;
                 v.x = pack_act(__uint_as_float(r[j * 8 + 0]), __uint_as_float(r[j * 8 + 1]), f16);
                 v.y = pack_act(__uint_as_float(r[j * 8 + 2]), __uint_as_float(r[j * 8 + 3]), f16);
@@ -87,9 +88,24 @@ __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* 
     } else if (EPI == KB_EPI_F32 || EPI == KB_EPI_RESID_F32) {
         float* o = reinterpret_cast<float*>(out) + (size_t)row * N + col0;
         const float* rs = resid + (size_t)row * N + col0;
+        if (EPI == KB_EPI_RESID_F32 && rs == o) {
+            // in place (x += A W^T, the decode step's O and down projections): let L2 do the add —
+            // fire-and-forget vector reductions instead of a load / add / store round trip per chunk,
+            // which left the epilogue waiting on L2 latency (9 us of a 27 us kernel, tools/gemm_trace.py).
+            // Exactly one thread adds to each element, so the result is the same fp32 sum.
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j * 4 < ncols)
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j * 4),
+                                 "f"(__uint_as_float(r[j * 4 + 0])), "f"(__uint_as_float(r[j * 4 + 1])),
+                                 "f"(__uint_as_float(r[j * 4 + 2])), "f"(__uint_as_float(r[j * 4 + 3]))
+                                 : "memory");
+            }
+            return;
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            if (col0 + j * 4 < N) {
+            if (j * 4 < ncols) {
                 float4 v = make_float4(__uint_as_float(r[j * 4 + 0]), __uint_as_float(r[j * 4 + 1]),
                                        __uint_as_float(r[j * 4 + 2]), __uint_as_float(r[j * 4 + 3]));
                 if (EPI == KB_EPI_RESID_F32) {
@@ -104,7 +120,7 @@ __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* 
         uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)row * No + (col0 >> 1);
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-            if (col0 + j * 16 < N) {
+            if (j * 16 < ncols) {
                 float h[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
@@ -246,7 +262,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 tmem_ld_32x32(t_row + (uint32_t)c, r);
                 tmem_ld_wait();
                 const int col0 = n_blk * BN + c;
-                if (row < M && col0 < N) epilogue_store32<EPI>(r, out, resid, row, col0, N);
+                if (row < M && col0 < N) epilogue_store32<EPI>(r, out, resid, row, col0, N, N - col0);
             }
             tc_fence_before();
             __syncwarp();
@@ -265,6 +281,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---------------------------------------------------------------------------------------------
+// Phase timestamps of cluster 0 (profiling aid; build with `make EXTRA=-DKB_GEMM_TRACE`, read with
+// tools/gemm_trace.py through kb_debug_gemm_trace — not part of the ABI, absent from normal builds).
+#ifdef KB_GEMM_TRACE
+__device__ unsigned long long g_gemm_trace[16];
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define KB_TRACE(slot) do { if (blockIdx.x == 0) g_gemm_trace[slot] = globaltimer_ns(); } while (0)
+#else
+#define KB_TRACE(slot) do { } while (0)
+#endif
+
 // CTA-pair variant (cta_group::2): a cluster of two CTAs owns a 256 x BN output tile.
 //
 // Why: a 1-CTA 128 x BN tile moves 16 KB of A plus BN*128 B of B through its shared-memory port twice
@@ -279,23 +309,29 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 //                 the slot-free and accumulator-full barriers of BOTH CTAs (multicast).
 //   * accumulator-free: the epilogue warps of both CTAs arrive on the leader's barrier (8 arrivals).
 // ---------------------------------------------------------------------------------------------
-template <int BN>
+// The tile width `bn` is a RUN-TIME argument (a multiple of 16, 32..256; the B tensor map's box is bn/2
+// rows): the host picks it per shape so that the number of tiles fills whole rounds of the 74 CTA pairs —
+// with fixed 256-wide tiles the decode step's gate/up projection (224 tiles) spent a quarter of its time
+// in a fourth round that held 2 tiles (tools/gemm_trace.py).
 struct Gemm2Cfg {
-    static constexpr int HALF_N = BN / 2;                       // B rows staged by one CTA
+    static constexpr int BN_MAX = 256;
     static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
-    static constexpr int B_BYTES = HALF_N * GEMM_BK * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;       // per CTA
-    static constexpr int STAGES = (BN == 256) ? 6 : 8;          // 192 KB either way
-    static constexpr int TMEM_COLS = 2 * BN;                    // double-buffered accumulator
+    static constexpr int B_BYTES_MAX = (BN_MAX / 2) * GEMM_BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES_MAX;   // per CTA
+    static constexpr int STAGES = 6;                            // 192 KB
+    static constexpr int TMEM_COLS = 2 * BN_MAX;                // double-buffered accumulator
     static constexpr int BAR_BYTES = 256;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
 };
 
-template <int BN, int EPI>
+template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, void* out,
-                         const float* resid, int M, int N, int K, uint32_t is_bf16) {
-    using Cfg = Gemm2Cfg<BN>;
+                         const float* resid, int M, int N, int K, int bn, uint32_t is_bf16) {
+    using Cfg = Gemm2Cfg;
+    const int BN = bn;
+    const int half_n = bn >> 1;                       // B rows staged by one CTA
+    const uint32_t stage_tx = 2u * (uint32_t)(Cfg::A_BYTES + half_n * GEMM_BK * 2);
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
@@ -307,6 +343,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) KB_TRACE(0);               // kernel entry
     const uint32_t cta = cluster_ctarank();          // 0 = leader
     const int cluster_id = blockIdx.x >> 1;
     const int num_clusters = gridDim.x >> 1;
@@ -341,6 +378,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     cluster_sync_all();                              // peer barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) KB_TRACE(1);               // barriers, TMEM, cluster sync done
 
     if (warp == 0) {
         // ===== TMA producer (both CTAs) =====
@@ -351,12 +389,12 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 const int mp = tile % num_mp;
                 const int n_blk = tile / num_mp;
                 const int row0 = mp * 2 * GEMM_BM + (int)cta * GEMM_BM;        // this CTA's 128 rows of A
-                const int nrow0 = n_blk * BN + (int)cta * Cfg::HALF_N;         // this CTA's half of B
+                const int nrow0 = n_blk * BN + (int)cta * half_n;              // this CTA's half of B
                 for (int kb = 0; kb < num_k; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
                     uint8_t* sb = sa + Cfg::A_BYTES;
-                    if (cta == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+                    if (cta == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
                     tma_load_2d_2cta(sa, &tmA, kb * GEMM_BK, row0, &full_bar[stage]);
                     tma_load_2d_2cta(sb, &tmB, kb * GEMM_BK, nrow0, &full_bar[stage]);
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
@@ -374,10 +412,12 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
                 mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::BN_MAX);
                 for (int kb = 0; kb < num_k; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
+                    if (kb == 0) KB_TRACE(2);        // first operands landed
+                    if (kb == num_k - 1) KB_TRACE(3);  // last operands landed
                     const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
                     const uint64_t adesc = make_sw128_kmajor_desc(sa);
                     const uint64_t bdesc = make_sw128_kmajor_desc(sa + Cfg::A_BYTES);
@@ -404,19 +444,22 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int n_blk = tile / num_mp;
             mbar_wait(&tmem_full_bar[acc], acc_phase);
             tc_fence_after();
+            if (threadIdx.x == 128) KB_TRACE(4);     // accumulator complete
             const int row = mp * 2 * GEMM_BM + (int)cta * GEMM_BM + ew * 32 + lane;
-            const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN);
+            const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * Cfg::BN_MAX);
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 uint32_t r[32];
                 tmem_ld_32x32(t_row + (uint32_t)c, r);
                 tmem_ld_wait();
                 const int col0 = n_blk * BN + c;
-                if (row < M && col0 < N) epilogue_store32<EPI>(r, out, resid, row, col0, N);
+                const int ncols = (N - col0 < BN - c) ? N - col0 : BN - c;
+                if (row < M && ncols > 0) epilogue_store32<EPI>(r, out, resid, row, col0, N, ncols);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[acc], 0);   // the leader's barrier
+            if (threadIdx.x == 128) KB_TRACE(5);     // this warp's rows stored
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
@@ -425,10 +468,12 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();                              // nobody leaves while the peer may still touch its smem / TMEM
+    if (threadIdx.x == 0) KB_TRACE(6);
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc_2cta(tmem_base, Cfg::TMEM_COLS);
     }
+    if (threadIdx.x == 64) KB_TRACE(7);              // TMEM released
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -532,39 +577,38 @@ static int dispatch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, void* ou
     return KB_ERR_INVALID;
 }
 
-template <int BN, int EPI>
+template <int EPI>
 static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
-                            int N, int K, uint32_t is_bf16, cudaStream_t stream) {
-    using Cfg = Gemm2Cfg<BN>;
+                            int N, int K, int bn, uint32_t is_bf16, cudaStream_t stream) {
+    using Cfg = Gemm2Cfg;
     static bool configured[64] = {};
-    auto kern = gemm_tcgen05_2cta_kernel<BN, EPI>;
+    auto kern = gemm_tcgen05_2cta_kernel<EPI>;
     int dev = 0;
     KB_CUDA(cudaGetDevice(&dev));
     if (!configured[dev & 63]) {
         KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         configured[dev & 63] = true;
     }
-    const int num_tiles = ((M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((N + BN - 1) / BN);
+    const int num_tiles = ((M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((N + bn - 1) / bn);
     const int max_clusters = num_sms() / 2;
     const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
-    kern<<<2 * clusters, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K, is_bf16);
+    kern<<<2 * clusters, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K, bn, is_bf16);
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
 }
 
-template <int BN>
 static int dispatch_epi_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
-                             int N, int K, int epi, uint32_t ab, cudaStream_t stream) {
+                             int N, int K, int bn, int epi, uint32_t ab, cudaStream_t stream) {
     switch (epi) {
-        case KB_EPI_BF16: return launch_gemm_2cta<BN, KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
-        case KB_EPI_F32: return launch_gemm_2cta<BN, KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, ab, stream);
-        case KB_EPI_RESID_F32: return launch_gemm_2cta<BN, KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, ab, stream);
+        case KB_EPI_BF16: return launch_gemm_2cta<KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
+        case KB_EPI_F32: return launch_gemm_2cta<KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
+        case KB_EPI_RESID_F32: return launch_gemm_2cta<KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
         case KB_EPI_SWIGLU_BF16:
-            return launch_gemm_2cta<BN, KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+            return launch_gemm_2cta<KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
         case KB_EPI_SWIGLU_F16:
-            return launch_gemm_2cta<BN, KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
-        case KB_EPI_F16: return launch_gemm_2cta<BN, KB_EPI_F16>(tmA, tmB, out, resid, M, N, K, ab, stream);
+            return launch_gemm_2cta<KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
+        case KB_EPI_F16: return launch_gemm_2cta<KB_EPI_F16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
     }
     set_error("kb_gemm: unknown epilogue %d", epi);
     return KB_ERR_INVALID;
@@ -578,7 +622,8 @@ static int pick_bn(int M, int N) {
         const char* s = getenv("KB_GEMM_BN");
         forced = s ? atoi(s) : 0;
     }
-    if (forced == 64 || forced == 128 || forced == 256 || forced == -128 || forced == -256) return forced;
+    if (forced == 64 || forced == 128 || forced == 256 || (forced <= -32 && forced >= -256 && forced % 16 == 0))
+        return forced;
     const int sms = num_sms();
     const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
     long best_cost = -1;
@@ -599,11 +644,11 @@ static int pick_bn(int M, int N) {
     if (M > GEMM_BM) {
         // CTA pair, 256 x bn tile: each CTA stages 16 KB of A and bn*64 B of B per k-block -> 256 + bn
         // cycles of shared-memory port against 2 bn cycles of MMA
+        // ... any multiple of 16 (run-time tile width): take the width whose tile count wastes the least
+        // of the last round; wider wins ties (less A re-read)
         const int num_mp = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
         const int pairs = sms / 2;
-        const int cands2[2] = {256, 128};
-        for (int i = 0; i < 2; ++i) {
-            const int bn = cands2[i];
+        for (int bn = 256; bn >= 64; bn -= 16) {
             const long tiles = (long)num_mp * ((N + bn - 1) / bn);
             const long per_pair = (tiles + pairs - 1) / pairs;
             const long kblock = (2 * bn > 256 + bn) ? 2 * bn : 256 + bn;
@@ -627,8 +672,9 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     KB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(out) & 15) == 0,
              "kb_gemm: pointers must be 16-byte aligned");
-    KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256 || tile_n == -128 || tile_n == -256,
-             "kb_gemm: tile_n=%d not in {0, 64, 128, 256, -128, -256}", tile_n);
+    KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256 ||
+                 (tile_n <= -32 && tile_n >= -256 && tile_n % 16 == 0),
+             "kb_gemm: tile_n=%d not in {0, 64, 128, 256} or a negative multiple of 16 in [-256, -32]", tile_n);
     const int bn = tile_n ? tile_n : pick_bn(M, N);
     CUtensorMap tmA, tmB;
     int rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, GEMM_BM, &tmA);
@@ -636,8 +682,7 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     if (bn < 0) {   // CTA pair: every CTA stages half of the tile's B rows
         rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)(-bn / 2), &tmB);
         if (rc) return rc;
-        if (bn == -256) return dispatch_epi_2cta<256>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);
-        return dispatch_epi_2cta<128>(tmA, tmB, out, resid, M, N, K, epi, a_is_bf16, stream);
+        return dispatch_epi_2cta(tmA, tmB, out, resid, M, N, K, -bn, epi, a_is_bf16, stream);
     }
     rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)bn, &tmB);
     if (rc) return rc;
@@ -662,3 +707,9 @@ extern "C" int kb_gemm(const void* a_bf16, const void* w_bf16, void* out, const 
                        int32_t K, int32_t epilogue, kb_stream stream) {
     return kb::gemm(a_bf16, w_bf16, out, resid, M, N, K, epilogue, reinterpret_cast<cudaStream_t>(stream));
 }
+
+#ifdef KB_GEMM_TRACE
+extern "C" int kb_debug_gemm_trace(unsigned long long* host_out16) {
+    return cudaMemcpyFromSymbol(host_out16, kb::g_gemm_trace, sizeof(unsigned long long) * 16) == cudaSuccess ? 0 : 1;
+}
+#endif

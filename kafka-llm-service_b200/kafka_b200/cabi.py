@@ -198,6 +198,8 @@ def gemm(a, w, epilogue: int = EPI_BF16, resid=None, out=None, tile_n: int = 0):
             out = torch.empty((M, N // 2), dtype=torch.bfloat16, device=a.device)
         elif epi == EPI_SWIGLU_F16:
             out = torch.empty((M, N // 2), dtype=torch.float16, device=a.device)
+        elif epi == EPI_F16:
+            out = torch.empty((M, N), dtype=torch.float16, device=a.device)
         else:
             out = torch.empty((M, N), dtype=torch.float32, device=a.device)
     check(load().kb_gemm_ex(_ptr(a), _ptr(w), _ptr(out), _ptr(resid), M, N, K, epilogue, tile_n, _stream()),

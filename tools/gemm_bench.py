@@ -29,14 +29,20 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--m", type=int, nargs="+", default=[512])
     ap.add_argument("--iters", type=int, default=20)
-    ap.add_argument("--tiles", type=int, nargs="+", default=[0, 64, 128, 256])
+    ap.add_argument("--tiles", type=int, nargs="+", default=[0, 64, 128, 256],
+                    help="0 = heuristic; 64/128/256 = 1-CTA tile; negative multiple of 16 = CTA-pair tile width")
     ap.add_argument("--only", default=None)
+    ap.add_argument("--ksweep", type=int, nargs="*", default=None,
+                    help="override K with these values (time = fixed overhead + slope x K)")
     args = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     out = []
     for M in args.m:
-        for name, (N, K, epi) in SHAPES.items():
+        shapes = [(name, N, K, epi) for name, (N, K, epi) in SHAPES.items()]
+        if args.ksweep:
+            shapes = [(name, N, k, epi) for name, N, _, epi in shapes for k in args.ksweep]
+        for name, N, K, epi in shapes:
             if args.only and name != args.only:
                 continue
             nbuf = max(2, int(300e6 // (N * K * 2)) + 1)           # > 2 x L2 of distinct weights
@@ -44,7 +50,8 @@ def main():
             a = torch.randn(M, K, device=dev).half()
             resid = torch.zeros(M, N, device=dev) if epi == cabi.EPI_RESID_F32 else None
             for tile in args.tiles:
-                o = cabi.gemm(a, ws[0], epi, resid=resid, tile_n=tile)   # allocate output once
+                # allocate the output once; the residual projections run in place, as in the engine
+                o = resid if resid is not None else cabi.gemm(a, ws[0], epi, resid=resid, tile_n=tile)
                 for i in range(3):
                     cabi.gemm(a, ws[i % nbuf], epi, resid=resid, out=o, tile_n=tile)
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
