@@ -314,25 +314,36 @@ attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restric
 // ---------------------------------------------------------------------------------------------
 // prefill (incremental, causal)
 // ---------------------------------------------------------------------------------------------
+// One CTA = 128 query rows of one (sequence, KV head): row r = (query token q0 + r / GROUP, head r % GROUP),
+// 8 warps x 16 rows. Every 64-token K/V tile is brought into shared memory once per CTA by two bulk copies
+// (issued by lane 0 of warp 0, S-1 tiles ahead) and consumed by all 8 warps.
+//
+// Why 128 rows and no producer warp (ncu, round 1): the first version had 64 rows + a producer warp;
+// its 184 registers / thread let only ONE 5-warp CTA live on an SM (registers are per SM sub-partition:
+// 2 warps x 5 888 fit in 16 K, 3 do not), so 4 warps per SM issued MMAs (tensor pipe 43 % active) and
+// every K/V tile was re-streamed from L2 once per 64 rows. 8 consumer warps fill the two warp slots of
+// every sub-partition, and a tile now serves twice the rows.
 template <int HD>
 struct PrefillCfg {
     static constexpr int NT = 64;
-    static constexpr int STAGES = (HD == 128) ? 3 : 4;
+    static constexpr int ROWS = 128;                               // query rows per CTA
+    static constexpr int WARPS = ROWS / 16;
+    static constexpr int STAGES = (HD == 128) ? 5 : 8;             // 160 KB / 128 KB of K/V in flight
     static constexpr int TILE_BYTES = NT * HD * 2;
     static constexpr int RING_BYTES = STAGES * 2 * TILE_BYTES;
     static constexpr int SMEM_BYTES = RING_BYTES + 2 * STAGES * 8 + 128;
-    static constexpr int THREADS = 160;  // 4 consumer warps + 1 producer warp
+    static constexpr int THREADS = WARPS * 32;
 };
 
 template <int HD, int GROUP>
-__global__ void __launch_bounds__(PrefillCfg<HD>::THREADS)
+__global__ void __launch_bounds__(PrefillCfg<HD>::THREADS, 1)
 attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
                     const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ cu_seqlens,
                     const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
                     uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
     using Cfg = PrefillCfg<HD>;
     constexpr int NT = Cfg::NT, S = Cfg::STAGES;
-    constexpr int TQ = 64 / GROUP;  // query tokens per CTA
+    constexpr int TQ = Cfg::ROWS / GROUP;  // query tokens per CTA
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::RING_BYTES);
     uint64_t* empty_bar = full_bar + S;
@@ -341,43 +352,39 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __n
     const int seq = blockIdx.z, kvh = blockIdx.y;
     const int tok_begin = cu_seqlens[seq];
     const int n_new = cu_seqlens[seq + 1] - tok_begin;
-    const int q0 = blockIdx.x * TQ;
+    // later query tiles see more keys: schedule them first
+    const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * TQ;
     if (q0 >= n_new) return;
     const int ctx = ctx_lens[seq];
     const int q_end = min(n_new, q0 + TQ);
     const int kv_end = ctx + q_end;  // keys visible to the last query of this CTA
     const int n_tiles = (kv_end + NT - 1) / NT;
+    const int n_active = ((q_end - q0) * GROUP + 15) / 16;   // warps that own at least one real row
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; ++s) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 4);
+            mbar_init(&empty_bar[s], n_active);
         }
         fence_mbar_init();
     }
     __syncthreads();
+    if (warp >= n_active) return;
 
-    if (warp == 4) {
-        // ===== producer =====
-        if (lane == 0) {
-            const int* bt = block_tables + (size_t)seq * max_blocks;
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int i = 0; i < n_tiles; ++i) {
-                mbar_wait(&empty_bar[stage], phase ^ 1);
-                const int phys = bt[i];
-                const size_t off = ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * HD;
-                uint8_t* ks = smem + stage * 2 * Cfg::TILE_BYTES;
-                mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::TILE_BYTES);
-                bulk_g2s(ks, kpool + off, Cfg::TILE_BYTES, &full_bar[stage]);
-                bulk_g2s(ks + Cfg::TILE_BYTES, vpool + off, Cfg::TILE_BYTES, &full_bar[stage]);
-                if (++stage == S) { stage = 0; phase ^= 1; }
-            }
-        }
-        return;
-    }
+    const int* bt = block_tables + (size_t)seq * max_blocks;
+    auto issue = [&](int i) {   // lane 0 of warp 0: bring tile i into its ring slot
+        const int stage = i % S;
+        mbar_wait(&empty_bar[stage], (uint32_t)(((i / S) & 1) ^ 1));
+        const int phys = bt[i];
+        const size_t off = ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * HD;
+        uint8_t* ks = smem + stage * 2 * Cfg::TILE_BYTES;
+        mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::TILE_BYTES);
+        bulk_g2s(ks, kpool + off, Cfg::TILE_BYTES, &full_bar[stage]);
+        bulk_g2s(ks + Cfg::TILE_BYTES, vpool + off, Cfg::TILE_BYTES, &full_bar[stage]);
+    };
+    if (warp == 0 && lane == 0)
+        for (int i = 0; i < S - 1 && i < n_tiles; ++i) issue(i);
 
-    // ===== consumers: warp w owns rows 16w .. 16w+15; row r = (query token q0 + r / GROUP, head r % GROUP)
     const int g = lane >> 2, t = lane & 3;
     const int r0 = warp * 16 + g, r1 = r0 + 8;
     const int tl0 = q0 + r0 / GROUP, tl1 = q0 + r1 / GROUP;
@@ -385,9 +392,11 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __n
     const bool v0 = tl0 < n_new, v1 = tl1 < n_new;
     const int lim0 = v0 ? ctx + tl0 + 1 : kv_end;
     const int lim1 = v1 ? ctx + tl1 + 1 : kv_end;
-    // smallest limit of any row of this warp decides when masking starts
+    // smallest limit of any row of this warp decides when masking starts; the largest, when its work ends
     const int warp_first_tl = q0 + (warp * 16) / GROUP;
-    const int warp_min_lim = (warp_first_tl < n_new) ? ctx + warp_first_tl + 1 : kv_end;
+    const int warp_min_lim = ctx + warp_first_tl + 1;
+    const int warp_last_tl = min(n_new - 1, q0 + (warp * 16 + 15) / GROUP);
+    const int warp_tiles = (ctx + warp_last_tl + 1 + NT - 1) / NT;   // tiles beyond are fully masked for this warp
 
     uint32_t qa[HD / 16][4];
     {
@@ -409,16 +418,18 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __n
     float l[2] = {0.f, 0.f};
     const float sc = LOG2E * rsqrtf((float)HD);
 
-    int stage = 0;
-    uint32_t phase = 0;
     for (int i = 0; i < n_tiles; ++i) {
-        mbar_wait(&full_bar[stage], phase);
-        const uint32_t ks = smem_u32(smem + stage * 2 * Cfg::TILE_BYTES);
-        const bool need_mask = (i + 1) * NT > warp_min_lim;
-        attn_tile<HD, NT, true>(o, m, l, qa, ks, ks + Cfg::TILE_BYTES, i * NT, lim0, lim1, sc, need_mask, lane);
+        if (warp == 0 && lane == 0 && i + S - 1 < n_tiles) issue(i + S - 1);
         __syncwarp();
+        const int stage = i % S;
+        if (i < warp_tiles) {          // causal: this warp's rows see nothing of the later tiles
+            mbar_wait(&full_bar[stage], (uint32_t)((i / S) & 1));
+            const uint32_t ks = smem_u32(smem + stage * 2 * Cfg::TILE_BYTES);
+            const bool need_mask = (i + 1) * NT > warp_min_lim;
+            attn_tile<HD, NT, true>(o, m, l, qa, ks, ks + Cfg::TILE_BYTES, i * NT, lim0, lim1, sc, need_mask, lane);
+            __syncwarp();
+        }
         if (lane == 0) mbar_arrive(&empty_bar[stage]);
-        if (++stage == S) { stage = 0; phase ^= 1; }
     }
 
     l[0] += __shfl_xor_sync(0xffffffffu, l[0], 1);
@@ -537,7 +548,7 @@ static int launch_prefill(const void* q, int q_stride, const void* kp, const voi
         KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
         configured[dev & 63] = true;
     }
-    constexpr int TQ = 64 / GROUP;
+    constexpr int TQ = Cfg::ROWS / GROUP;
     dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>((const __nv_bfloat16*)q, q_stride,
                                                           (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, cu, ctx,
