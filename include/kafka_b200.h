@@ -228,9 +228,12 @@ int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x, int32_t n,
 #define KB_GEMM_F16 0x100
 int kb_gemm(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,
             int32_t K, int32_t epilogue, kb_stream stream);
-/* Same, with the tile forced: tile_n in {64, 128, 256} = one CTA per 128 x tile_n tile; {-128, -256} =
- * a CTA pair (tcgen05 cta_group::2) per 256 x |tile_n| tile; 0 = heuristic. For tuning and for tests
- * that must cover every instantiation. */
+/* Same, with the tile forced: tile_n in {64, 128, 256} = one CTA per 128 x tile_n tile; a negative
+ * multiple of 16 in [-256, -32] = a CTA pair (tcgen05 cta_group::2) per 256 x |tile_n| tile; {1, 2, 4} =
+ * the small-M kernel (M <= 128: operands swapped so the 128 MMA rows are weight rows, that many CTAs
+ * per tile sharing K through a cluster and adding their partial sums in rank order); 0 = heuristic
+ * (small-M kernel for M <= 32, else the cheapest tile under a per-SM ingress cost model). For tuning
+ * and for tests that must cover every instantiation. */
 int kb_gemm_ex(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,
                int32_t K, int32_t epilogue, int32_t tile_n, kb_stream stream);
 

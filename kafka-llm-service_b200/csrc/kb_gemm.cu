@@ -477,6 +477,284 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 }
 
 // ---------------------------------------------------------------------------------------------
+// Small-M variant ("skinny": M <= 128 tokens — decode at low concurrency, short prefill chunks).
+//
+// With few tokens the projections are pure weight streaming, and the 128 x BN kernel above wastes its
+// shared-memory ingress on a 128-row activation tile that is mostly zero fill (16 KB per k-block against
+// 8 KB of weights: ~2 TB/s of weights at best, tools/gemm_trace.py / bench --threads 1). Here the
+// operands trade places:  D^T[128 weight rows, T tokens] = W_tile[128, K] * X[T, K]^T
+//   * A operand = 128 weight rows (16 KB per k-block, all of it useful), B operand = the T-token
+//     activation tile (T = 16 / 32 / 64 / 128 >= M; rows beyond M are TMA zero fill: 2..16 KB),
+//     accumulator = T fp32 columns of TMEM;
+//   * the epilogue stores transposed: lane = weight row, so for one token a warp writes 32 consecutive
+//     outputs (coalesced); the SwiGLU pair (gate_j, up_j) sits in adjacent lanes;
+//   * N / 128 tiles are too few CTAs to pull the weights at HBM speed when N = hidden, so a cluster of
+//     `splits` CTAs shares one tile, each streaming 1/splits of K; the partial accumulators are added in
+//     rank order by the leader through distributed shared memory — deterministic, no atomics, no scratch.
+// ---------------------------------------------------------------------------------------------
+struct SkinnyCfg {
+    static constexpr int W_BYTES = GEMM_BM * GEMM_BK * 2;   // 16 KB
+    static constexpr int MAX_STAGES = 10;
+    static constexpr int BAR_BYTES = 512;
+    static constexpr int SMEM_BUDGET = 200 * 1024;          // ring + reduction buffers
+};
+
+__device__ __forceinline__ void mbar_arrive_release_cluster(uint64_t* bar, uint32_t cta) {
+    asm volatile(
+        "{\n"
+        ".reg .b32 ra;\n"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n"
+        "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(cta)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait_acquire_cluster(uint64_t* bar, uint32_t parity) {
+    const uint32_t a = smem_u32(bar);
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(a), "r"(parity)
+            : "memory");
+    }
+}
+__device__ __forceinline__ void st_cluster_f32x4(uint32_t local_saddr, uint32_t cta, float4 v) {
+    asm volatile(
+        "{\n"
+        ".reg .b32 ra;\n"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n"
+        "st.shared::cluster.v4.f32 [ra], {%2, %3, %4, %5};\n"
+        "}\n" ::"r"(local_saddr),
+        "r"(cta), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+        : "memory");
+}
+
+// r[j] = D[n (this lane's weight row)][token c + j]; stores the tokens < M of output column n.
+template <int EPI>
+__device__ __forceinline__ void skinny_store32(const float (&r)[32], void* out, const float* resid, int n, int c,
+                                               int M, int N, int lane) {
+    if (EPI == KB_EPI_RESID_F32) {
+        float* o = reinterpret_cast<float*>(out);
+        if (n >= N) return;
+        if (resid == o) {
+            // in place: fire-and-forget reductions in L2 (one adder per element: same fp32 sum), so the
+            // loop does not wait for one L2 round trip per token
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (c + j < M)
+                    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(o + (size_t)(c + j) * N + n), "f"(r[j]) : "memory");
+        } else {
+            float q[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) q[j] = (c + j < M) ? resid[(size_t)(c + j) * N + n] : 0.f;   // independent loads
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (c + j < M) o[(size_t)(c + j) * N + n] = q[j] + r[j];
+        }
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const int token = c + j;
+        if (token >= M) break;                      // warp-uniform
+        const float v = r[j];
+        if (EPI == KB_EPI_SWIGLU_BF16 || EPI == KB_EPI_SWIGLU_F16) {
+            const float up = __shfl_down_sync(0xffffffffu, v, 1);
+            if (!(lane & 1) && n < N) {
+                const float h = silu_f(v) * up;
+                uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)token * (N >> 1) + (n >> 1);
+                *o = (EPI == KB_EPI_SWIGLU_F16) ? __half_as_ushort(__float2half_rn(h))
+                                                : __bfloat16_as_ushort(__float2bfloat16(h));
+            }
+        } else if (n < N) {
+            const size_t idx = (size_t)token * N + n;
+            if (EPI == KB_EPI_BF16) reinterpret_cast<__nv_bfloat16*>(out)[idx] = __float2bfloat16(v);
+            else if (EPI == KB_EPI_F16) reinterpret_cast<__half*>(out)[idx] = __float2half_rn(v);
+            else reinterpret_cast<float*>(out)[idx] = v;   // KB_EPI_F32
+        }
+    }
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, void* out,
+                           const float* resid, int M, int N, int K, int T, int stages, int splits, uint32_t is_bf16) {
+    using Cfg = SkinnyCfg;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int stage_bytes = Cfg::W_BYTES + T * GEMM_BK * 2;
+    const int red_bytes_per_peer = GEMM_BM * T * 4;
+    float* red_buf = reinterpret_cast<float*>(smem + stages * stage_bytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes + (splits - 1) * red_bytes_per_peer);
+    uint64_t* empty_bar = full_bar + Cfg::MAX_STAGES;
+    uint64_t* tmem_full_bar = empty_bar + Cfg::MAX_STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
+    uint64_t* red_bar = tmem_empty_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(red_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = splits > 1 ? cluster_ctarank() : 0u;
+    const int num_tiles = (N + GEMM_BM - 1) / GEMM_BM;
+    const int num_k = K / GEMM_BK;
+    const int kb_lo = (int)rank * (num_k / splits);
+    const int kb_hi = kb_lo + num_k / splits;
+    const int acc_stride = T < 32 ? 32 : T;                  // TMEM columns between the two accumulators
+    const uint32_t tmem_cols = (uint32_t)(2 * acc_stride);   // 64 / 64 / 128 / 256
+    // persistent over tiles without split-K; exactly one tile per cluster with it
+    const int tile0 = splits > 1 ? (int)blockIdx.x / splits : (int)blockIdx.x;
+    const int tile_step = splits > 1 ? num_tiles : (int)gridDim.x;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            tma_prefetch_desc(&tmW);
+            tma_prefetch_desc(&tmX);
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            for (int s = 0; s < stages; ++s) {
+                mbar_init(&full_bar[s], 1);
+                mbar_init(&empty_bar[s], 1);
+            }
+            for (int a = 0; a < 2; ++a) {
+                mbar_init(&tmem_full_bar[a], 1);
+                mbar_init(&tmem_empty_bar[a], 4);
+            }
+            mbar_init(red_bar, (uint32_t)((splits - 1) * 4));   // one arrive per epilogue warp of every peer
+            fence_mbar_init();
+        }
+    } else if (warp == 2) {
+        tmem_alloc(tmem_slot, tmem_cols);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (splits > 1) cluster_sync_all();          // the leader's reduction barrier exists before a peer arrives on it
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+                for (int kb = kb_lo; kb < kb_hi; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sw = smem + stage * stage_bytes;
+                    mbar_arrive_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+                    tma_load_2d(sw, &tmW, kb * GEMM_BK, tile * GEMM_BM, &full_bar[stage]);
+                    tma_load_2d(sw + Cfg::W_BYTES, &tmX, kb * GEMM_BK, 0, &full_bar[stage]);
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: A = weights (M = 128), B = tokens (N = T) =====
+        if (elect_one()) {
+            const uint32_t idesc = make_idesc(GEMM_BM, T, is_bf16);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+                mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * acc_stride);
+                for (int kb = kb_lo; kb < kb_hi; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sw = smem_u32(smem + stage * stage_bytes);
+                    const uint64_t adesc = make_sw128_kmajor_desc(sw);
+                    const uint64_t bdesc = make_sw128_kmajor_desc(sw + Cfg::W_BYTES);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k)
+                        umma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                                  (uint32_t)((kb > kb_lo) | (k != 0)));
+                    umma_commit(&empty_bar[stage]);
+                    if (kb == kb_hi - 1) umma_commit(&tmem_full_bar[acc]);
+                    if (++stage == stages) { stage = 0; phase ^= 1; }
+                }
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: TMEM -> (cluster reduction) -> transposed store =====
+        const int ew = warp - 4;
+        const int row = ew * 32 + lane;              // weight row inside the tile = TMEM lane
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+            mbar_wait(&tmem_full_bar[acc], acc_phase);
+            tc_fence_after();
+            const int n = tile * GEMM_BM + row;
+            const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * acc_stride);
+            if (rank != 0) {
+                // peer: ship the partial accumulator to the leader's reduction buffer
+                const uint32_t dst = smem_u32(red_buf) + (uint32_t)(((int)rank - 1) * red_bytes_per_peer) +
+                                     (uint32_t)(row * T * 4);
+#pragma unroll 1
+                for (int c = 0; c < T; c += 32) {
+                    uint32_t u[32];
+                    tmem_ld_32x32(t_row + (uint32_t)c, u);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        if (c + j < T)
+                            st_cluster_f32x4(dst + (uint32_t)((c + j) * 4), 0,
+                                             make_float4(__uint_as_float(u[j]), __uint_as_float(u[j + 1]),
+                                                         __uint_as_float(u[j + 2]), __uint_as_float(u[j + 3])));
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive_release_cluster(red_bar, 0);
+            } else {
+                if (splits > 1) mbar_wait_acquire_cluster(red_bar, 0);
+#pragma unroll 1
+                for (int c = 0; c < T; c += 32) {
+                    uint32_t u[32];
+                    tmem_ld_32x32(t_row + (uint32_t)c, u);
+                    tmem_ld_wait();
+                    float r[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] = __uint_as_float(u[j]);
+                    for (int p = 0; p + 1 < splits; ++p) {      // partial sums in rank order: deterministic
+                        const float4* src = reinterpret_cast<const float4*>(
+                            reinterpret_cast<const uint8_t*>(red_buf) + p * red_bytes_per_peer + row * T * 4 + c * 4);
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            if (c + j < T) {
+                                const float4 q = src[j >> 2];
+                                r[j] += q.x; r[j + 1] += q.y; r[j + 2] += q.z; r[j + 3] += q.w;
+                            }
+                        }
+                    }
+                    skinny_store32<EPI>(r, out, resid, n, c, M, N, lane);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, tmem_cols);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
 static PFN_cuTensorMapEncodeTiled_v12000 g_encode = nullptr;
@@ -614,6 +892,89 @@ static int dispatch_epi_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, voi
     return KB_ERR_INVALID;
 }
 
+// Small-M path: T = padded token count, splits = CTAs per tile (cluster split-K), chosen so that at least
+// ~96 CTAs stream weights and the reduction buffers fit beside a >= 4-stage ring.
+static void skinny_plan(int M, int N, int K, int want_splits, int* T_out, int* splits_out, int* stages_out) {
+    const int T = M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : 128));
+    const int tiles = (N + GEMM_BM - 1) / GEMM_BM;
+    const int num_k = K / GEMM_BK;
+    const int stage_bytes = SkinnyCfg::W_BYTES + T * GEMM_BK * 2;
+    int splits = 1;
+    if (want_splits > 0) {
+        splits = want_splits;
+    } else {
+        while (splits < 4 && tiles * splits < 96) splits *= 2;
+    }
+    while (splits > 1 && (num_k % splits != 0 || tiles * splits > 65535 ||
+                          (SkinnyCfg::SMEM_BUDGET - (splits - 1) * GEMM_BM * T * 4) / stage_bytes < 4))
+        splits /= 2;
+    int stages = (SkinnyCfg::SMEM_BUDGET - (splits - 1) * GEMM_BM * T * 4) / stage_bytes;
+    if (stages > SkinnyCfg::MAX_STAGES) stages = SkinnyCfg::MAX_STAGES;
+    *T_out = T;
+    *splits_out = splits;
+    *stages_out = stages;
+}
+
+template <int EPI>
+static int launch_skinny(const void* a, const void* w, void* out, const float* resid, int M, int N, int K,
+                         int want_splits, uint32_t is_bf16, cudaStream_t stream) {
+    int T, splits, stages;
+    skinny_plan(M, N, K, want_splits, &T, &splits, &stages);
+    CUtensorMap tmW, tmX;
+    int rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, GEMM_BM, &tmW);
+    if (rc) return rc;
+    rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, (uint32_t)T, &tmX);
+    if (rc) return rc;
+    const size_t smem = (size_t)stages * (SkinnyCfg::W_BYTES + T * GEMM_BK * 2) + (size_t)(splits - 1) * GEMM_BM * T * 4 +
+                        SkinnyCfg::BAR_BYTES + 1024;
+    static bool configured[64] = {};
+    auto kern = gemm_tcgen05_skinny_kernel<EPI>;
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     SkinnyCfg::SMEM_BUDGET + SkinnyCfg::BAR_BYTES + 1024));
+        configured[dev & 63] = true;
+    }
+    const int tiles = (N + GEMM_BM - 1) / GEMM_BM;
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (splits > 1) {
+        cfg.gridDim = dim3(tiles * splits);
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = splits;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    } else {
+        cfg.gridDim = dim3(tiles < num_sms() ? tiles : num_sms());
+    }
+    KB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmW, tmX, out, resid, M, N, K, T, stages, splits, is_bf16));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+static int dispatch_skinny(const void* a, const void* w, void* out, const float* resid, int M, int N, int K, int epi,
+                           int want_splits, uint32_t ab, cudaStream_t stream) {
+    switch (epi) {
+        case KB_EPI_BF16: return launch_skinny<KB_EPI_BF16>(a, w, out, resid, M, N, K, want_splits, ab, stream);
+        case KB_EPI_F32: return launch_skinny<KB_EPI_F32>(a, w, out, resid, M, N, K, want_splits, ab, stream);
+        case KB_EPI_RESID_F32: return launch_skinny<KB_EPI_RESID_F32>(a, w, out, resid, M, N, K, want_splits, ab, stream);
+        case KB_EPI_SWIGLU_BF16:
+            return launch_skinny<KB_EPI_SWIGLU_BF16>(a, w, out, resid, M, N, K, want_splits, ab, stream);
+        case KB_EPI_SWIGLU_F16:
+            return launch_skinny<KB_EPI_SWIGLU_F16>(a, w, out, resid, M, N, K, want_splits, ab, stream);
+        case KB_EPI_F16: return launch_skinny<KB_EPI_F16>(a, w, out, resid, M, N, K, want_splits, ab, stream);
+    }
+    set_error("kb_gemm: unknown epilogue %d", epi);
+    return KB_ERR_INVALID;
+}
+
 // Tile choice: minimise the time of the busiest CTA (or CTA pair) under the static persistent schedule.
 // Returns BN for the 1-CTA kernel, -BN for the CTA-pair kernel.
 static int pick_bn(int M, int N) {
@@ -673,8 +1034,18 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
                  (reinterpret_cast<uintptr_t>(out) & 15) == 0,
              "kb_gemm: pointers must be 16-byte aligned");
     KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256 ||
-                 (tile_n <= -32 && tile_n >= -256 && tile_n % 16 == 0),
-             "kb_gemm: tile_n=%d not in {0, 64, 128, 256} or a negative multiple of 16 in [-256, -32]", tile_n);
+                 (tile_n <= -32 && tile_n >= -256 && tile_n % 16 == 0) || (tile_n >= 1 && tile_n <= 4 && tile_n != 3),
+             "kb_gemm: tile_n=%d not in {0, 64, 128, 256}, a negative multiple of 16 in [-256, -32], or 1 / 2 / 4 "
+             "(small-M kernel with that many CTAs per tile)", tile_n);
+    static int skinny_off = -1;
+    if (skinny_off < 0) skinny_off = getenv("KB_GEMM_NO_SKINNY") != nullptr;
+    // measured in the decode step (bench.py --threads 32 / 64 / 128, with and without KB_GEMM_NO_SKINNY):
+    // the small-M kernel wins up to 32 tokens (6.1 vs 6.6 ms per step), ties at 64, loses at 128
+    if ((tile_n >= 1 && tile_n <= 4) || (tile_n == 0 && M <= 32 && !skinny_off)) {
+        KB_CHECK(M <= GEMM_BM, "kb_gemm: the small-M kernel takes at most %d rows (got %d)", GEMM_BM, M);
+        // tile_n = 0: CTAs per tile chosen by skinny_plan; 1 / 2 / 4: forced (benchmarks, tests)
+        return dispatch_skinny(a, w, out, resid, M, N, K, epi, tile_n, a_is_bf16, stream);
+    }
     const int bn = tile_n ? tile_n : pick_bn(M, N);
     CUtensorMap tmA, tmB;
     int rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, GEMM_BM, &tmA);

@@ -128,6 +128,38 @@ def test_gemm_fp16_operands(kb, cuda, tile_n):
     torch.testing.assert_close(h.float(), want, rtol=2e-3, atol=2e-3)
 
 
+@pytest.mark.parametrize("splits", [0, 1, 2, 4])
+@pytest.mark.parametrize("M,N,K", [(1, 512, 256), (5, 4096, 4096), (16, 136, 192), (17, 1000, 320), (33, 6144, 1024),
+                                   (64, 4096, 14336), (100, 384, 512), (128, 4096, 4096)])
+def test_gemm_small_m_kernel(kb, cuda, M, N, K, splits):
+    """The small-M kernel (operands swapped, cluster split-K with a rank-ordered reduction through distributed
+    shared memory): every epilogue, forced and automatic split counts, ragged M / N."""
+    g = torch.Generator(device="cpu").manual_seed(M * 11 + N * 5 + K + splits)
+    a = torch.randn(M, K, generator=g).half().to(cuda)
+    w = _bf16(torch.randn(N, K, generator=g) / math.sqrt(K)).half().to(cuda)
+    ref = a.float() @ w.float().T
+    torch.testing.assert_close(kb.gemm(a, w, kb.EPI_F32, tile_n=splits), ref, rtol=2e-3, atol=2e-3)
+    torch.testing.assert_close(kb.gemm(a, w, kb.EPI_BF16, tile_n=splits).float(), ref, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(kb.gemm(a, w, kb.EPI_F16, tile_n=splits).float(), ref, rtol=2e-3, atol=2e-3)
+    resid = torch.randn(M, N, generator=g).to(cuda)
+    r2 = resid.clone()
+    kb.gemm(a, w, kb.EPI_RESID_F32, resid=r2, out=r2, tile_n=splits)          # in place, as the engine runs it
+    torch.testing.assert_close(r2, resid + ref, rtol=2e-3, atol=2e-3)
+    out3 = kb.gemm(a, w, kb.EPI_RESID_F32, resid=resid, tile_n=splits)
+    torch.testing.assert_close(out3, resid + ref, rtol=2e-3, atol=2e-3)
+    if N % 16 == 0:
+        F = N // 2
+        wg, wu = w[0::2].float(), w[1::2].float()                             # interleaved (gate_j, up_j) rows
+        want = torch.nn.functional.silu(a.float() @ wg.T) * (a.float() @ wu.T)
+        h = kb.gemm(a, w, kb.EPI_SWIGLU_F16, tile_n=splits)
+        assert h.shape == (M, F)
+        torch.testing.assert_close(h.float(), want, rtol=2e-3, atol=2e-3)
+        hb = kb.gemm(a, w, kb.EPI_SWIGLU_BF16, tile_n=splits)
+        torch.testing.assert_close(hb.float(), want, rtol=2e-2, atol=2e-2)
+    # the reduction order is fixed: two runs give the same bits
+    assert torch.equal(kb.gemm(a, w, kb.EPI_F32, tile_n=splits), kb.gemm(a, w, kb.EPI_F32, tile_n=splits))
+
+
 def test_fp16_activation_outputs_of_norm_and_attention(kb, cuda):
     from kafka_b200 import kv_layout
     g = torch.Generator(device="cpu").manual_seed(5)
