@@ -172,6 +172,8 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv
     uint8_t* ring = smem;
     float* merge = reinterpret_cast<float*>(smem + Cfg::RING_BYTES);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::RING_BYTES + Cfg::MERGE_FLOATS * 4);
+    pdl_wait();      // kv_lens, q and the appended K/V come from the kernels before this one
+    pdl_launch();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
@@ -296,6 +298,8 @@ template <int HD>
 __global__ void __launch_bounds__(HD)
 attn_split_merge_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                         uint16_t* __restrict__ out, int n_splits, int out_f16) {
+    pdl_wait();
+    pdl_launch();
     const size_t sh = blockIdx.x;
     const int dim = threadIdx.x;
     float M = -INFINITY;
@@ -347,6 +351,8 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __n
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::RING_BYTES);
     uint64_t* empty_bar = full_bar + S;
+    pdl_wait();
+    pdl_launch();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int seq = blockIdx.z, kvh = blockIdx.y;
@@ -469,14 +475,13 @@ static int launch_decode(const void* q, int q_stride, const void* kp, const void
         configured[dev & 63] = true;
     }
     dim3 grid(n_kv_heads, batch, n_splits);
-    kern<<<grid, Cfg::WARPS * 32, Cfg::SMEM_BYTES, stream>>>(
-        (const __nv_bfloat16*)q, q_stride, (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, kv_lens, bias, bt,
-        (uint16_t*)out, part_o, part_ml, max_blocks, n_heads, n_kv_heads, n_splits, halves_per_split, out_f16);
+    KB_CUDA(launch_kernel(kern, grid, dim3(Cfg::WARPS * 32), Cfg::SMEM_BYTES, stream, (const __nv_bfloat16*)q, q_stride, (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, kv_lens, bias, bt,
+        (uint16_t*)out, part_o, part_ml, max_blocks, n_heads, n_kv_heads, n_splits, halves_per_split, out_f16));
     count_launch();
     KB_LAUNCH_CHECK();
     if (n_splits > 1) {
-        attn_split_merge_kernel<HD><<<batch * n_heads, HD, 0, stream>>>(part_o, part_ml, (uint16_t*)out, n_splits,
-                                                                         out_f16);
+        KB_CUDA(launch_kernel(attn_split_merge_kernel<HD>, dim3(batch * n_heads), dim3(HD), 0, stream, part_o, part_ml, (uint16_t*)out, n_splits,
+                                                                         out_f16));
         count_launch();
         KB_LAUNCH_CHECK();
     }
@@ -550,10 +555,10 @@ static int launch_prefill(const void* q, int q_stride, const void* kp, const voi
     }
     constexpr int TQ = Cfg::ROWS / GROUP;
     dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>((const __nv_bfloat16*)q, q_stride,
+    KB_CUDA(launch_kernel(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, (const __nv_bfloat16*)q, q_stride,
                                                           (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, cu, ctx,
                                                           bt, (uint16_t*)out, max_blocks, n_heads, n_kv_heads,
-                                                          out_f16);
+                                                          out_f16));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;

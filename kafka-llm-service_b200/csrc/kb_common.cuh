@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include <stdlib.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
@@ -51,6 +52,36 @@ extern thread_local char g_err[512];
         }                                                                      \
     } while (0)
 
+// Programmatic dependent launch. Every kernel of the forward pass is launched with the
+// programmatic-stream-serialization attribute and begins with its private set-up (barrier init, TMEM
+// allocation, descriptor prefetch), then `pdl_wait()` — which returns once the PREVIOUS kernel in the
+// stream has completed and its writes are visible — and `pdl_launch()`, which lets the NEXT kernel start
+// its own set-up while this one runs. The chain is transitive because every kernel waits. Nothing before
+// pdl_wait() may touch global memory another kernel writes. KB_NO_PDL=1 launches without the attribute
+// (the two instructions are then no-ops). The tensor-parallel collectives are launched normally.
+inline bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) v = getenv("KB_NO_PDL") ? 0 : 1;
+    return v != 0;
+}
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 // Launch counter: how many of OUR kernels were enqueued (bench.py reports it as gpu_launches).
 extern unsigned long long g_launches;
 inline void count_launch(int n = 1) { g_launches += (unsigned long long)n; }
@@ -59,6 +90,9 @@ inline void count_launch(int n = 1) { g_launches += (unsigned long long)n; }
 // device-side PTX helpers
 // ---------------------------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -13,6 +13,8 @@ namespace kb {
 __global__ void __launch_bounds__(256)
 embed_kernel(const int* __restrict__ tokens, const __nv_bfloat16* __restrict__ embed, float* __restrict__ x,
              int hidden, int vocab) {
+    pdl_wait();
+    pdl_launch();
     const int t = blockIdx.x;
     int tok = tokens[t];
     tok = tok < 0 ? 0 : (tok >= vocab ? vocab - 1 : tok);
@@ -37,6 +39,8 @@ __global__ void __launch_bounds__(256)
 rmsnorm_kernel(float* __restrict__ x, const __nv_bfloat16* __restrict__ w, uint16_t* __restrict__ y,
                const int* __restrict__ last_rows, const __half* __restrict__ delta, int hidden, float eps,
                int out_f16) {
+    pdl_wait();
+    pdl_launch();
     const int i = blockIdx.x;
     const int row = last_rows ? last_rows[i + 1] - 1 : i;
     float4* xr = reinterpret_cast<float4*>(x + (size_t)row * hidden);
@@ -96,6 +100,8 @@ rope_append_kernel(__nv_bfloat16* __restrict__ qkv, const int* __restrict__ cu_s
                    const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
                    __nv_bfloat16* __restrict__ kpool, __nv_bfloat16* __restrict__ vpool, int n_seqs, int max_blocks,
                    int n_heads, int n_kv_heads, int head_dim, float log2_theta) {
+    pdl_wait();
+    pdl_launch();
     const int tkn = blockIdx.x;
     __shared__ float s_cos[64], s_sin[64];
     __shared__ int s_seq, s_pos;
@@ -190,6 +196,8 @@ sample_kernel(const float* __restrict__ logits, int vocab, float temperature, ui
               int banned, int lo, int hi, int extra_a, int extra_b, const float* __restrict__ seq_temperature,
               const uint64_t* __restrict__ seq_seed, int* __restrict__ out_tokens,
               int* __restrict__ ctx_lens_advance) {
+    pdl_wait();
+    pdl_launch();
     const int seq = blockIdx.x;
     const float* lg = logits + (size_t)seq * vocab;
     if (seq_temperature) temperature = seq_temperature[seq];
@@ -250,6 +258,8 @@ sample_kernel(const float* __restrict__ logits, int vocab, float temperature, ui
 // ---------------------------------------------------------------------------------------------
 __global__ void select_tokens_kernel(int* __restrict__ dst, const int* __restrict__ prev_out,
                                      const int* __restrict__ src, int n, int n_prev) {
+    pdl_wait();
+    pdl_launch();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int s = src[i];
@@ -261,7 +271,7 @@ __global__ void select_tokens_kernel(int* __restrict__ dst, const int* __restric
 // ---------------------------------------------------------------------------------------------
 int select_tokens(int* dst, const int* prev_out, const int* src, int n, int n_prev, cudaStream_t stream) {
     KB_CHECK(n > 0 && n_prev > 0 && dst && prev_out && src, "kb_select_tokens: bad arguments");
-    select_tokens_kernel<<<(n + 255) / 256, 256, 0, stream>>>(dst, prev_out, src, n, n_prev);
+    KB_CUDA(launch_kernel(select_tokens_kernel, dim3((n + 255) / 256), dim3(256), 0, stream, dst, prev_out, src, n, n_prev));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -269,7 +279,7 @@ int select_tokens(int* dst, const int* prev_out, const int* src, int n, int n_pr
 
 int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, int vocab, cudaStream_t stream) {
     KB_CHECK(n > 0 && hidden % 8 == 0, "kb_embed: bad shape n=%d hidden=%d", n, hidden);
-    embed_kernel<<<n, 256, 0, stream>>>(tokens, (const __nv_bfloat16*)embed_w, x, hidden, vocab);
+    KB_CUDA(launch_kernel(embed_kernel, dim3(n), dim3(256), 0, stream, tokens, (const __nv_bfloat16*)embed_w, x, hidden, vocab));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -278,8 +288,8 @@ int embed(const int* tokens, const void* embed_w, float* x, int n, int hidden, i
 int rmsnorm(float* x, const void* w, void* y, const int* last_rows, const void* delta_f16, int n, int hidden, float eps,
             int out_f16, cudaStream_t stream) {
     KB_CHECK(n > 0 && hidden % 4 == 0, "kb_rmsnorm: bad shape n=%d hidden=%d", n, hidden);
-    rmsnorm_kernel<<<n, 256, 0, stream>>>(x, (const __nv_bfloat16*)w, (uint16_t*)y, last_rows,
-                                          (const __half*)delta_f16, hidden, eps, out_f16);
+    KB_CUDA(launch_kernel(rmsnorm_kernel, dim3(n), dim3(256), 0, stream, x, (const __nv_bfloat16*)w, (uint16_t*)y, last_rows,
+                                          (const __half*)delta_f16, hidden, eps, out_f16));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -291,9 +301,9 @@ int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* k
     KB_CHECK(n_tokens > 0 && n_seqs > 0, "kb_rope_append: empty batch");
     KB_CHECK(head_dim == 64 || head_dim == 128, "kb_rope_append: head_dim must be 64 or 128 (got %d)", head_dim);
     KB_CHECK(cu != nullptr || n_tokens == n_seqs, "kb_rope_append: cu_seqlens == NULL means one token per sequence");
-    rope_append_kernel<<<n_tokens, 128, 0, stream>>>((__nv_bfloat16*)qkv, cu, ctx, bt, (__nv_bfloat16*)kp,
+    KB_CUDA(launch_kernel(rope_append_kernel, dim3(n_tokens), dim3(128), 0, stream, (__nv_bfloat16*)qkv, cu, ctx, bt, (__nv_bfloat16*)kp,
                                                       (__nv_bfloat16*)vp, n_seqs, max_blocks, n_heads, n_kv_heads,
-                                                      head_dim, log2f(theta));
+                                                      head_dim, log2f(theta)));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -311,9 +321,9 @@ int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, in
               sp->extra_b != ea) ? sp->extra_b : -1;
         KB_CHECK(hi > lo, "kb_sample: empty allowed range");
     }
-    sample_kernel<<<n_seqs, 1024, 0, stream>>>(logits, vocab, sp->temperature, sp->seed, sp->step, sp->banned_token,
+    KB_CUDA(launch_kernel(sample_kernel, dim3(n_seqs), dim3(1024), 0, stream, logits, vocab, sp->temperature, sp->seed, sp->step, sp->banned_token,
                                                lo, hi, ea, eb, sp->seq_temperature, sp->seq_seed, out_tokens,
-                                               ctx_advance);
+                                               ctx_advance));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;

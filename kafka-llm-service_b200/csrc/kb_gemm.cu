@@ -192,6 +192,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();      // set-up above overlapped the previous kernel; its outputs are visible from here on
+    pdl_launch();
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -378,6 +380,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     cluster_sync_all();                              // peer barriers are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();      // set-up above overlapped the previous kernel; its outputs are visible from here on
+    pdl_launch();
     if (threadIdx.x == 0) KB_TRACE(1);               // barriers, TMEM, cluster sync done
 
     if (warp == 0) {
@@ -638,6 +642,8 @@ gemm_tcgen05_skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid
     if (splits > 1) cluster_sync_all();          // the leader's reduction barrier exists before a peer arrives on it
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();      // set-up above overlapped the previous kernel; its outputs are visible from here on
+    pdl_launch();
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -834,7 +840,8 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out
     }
     const int num_tiles = ((M + GEMM_BM - 1) / GEMM_BM) * ((N + BN - 1) / BN);
     int grid = num_tiles < num_sms() ? num_tiles : num_sms();
-    kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K, a_is_bf16);
+    KB_CUDA(launch_kernel(kern, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, out, resid, M, N, K,
+                          a_is_bf16));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -870,7 +877,8 @@ static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void
     const int num_tiles = ((M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((N + bn - 1) / bn);
     const int max_clusters = num_sms() / 2;
     const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
-    kern<<<2 * clusters, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, out, resid, M, N, K, bn, is_bf16);
+    KB_CUDA(launch_kernel(kern, dim3(2 * clusters), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, out, resid, M,
+                          N, K, bn, is_bf16));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -941,18 +949,25 @@ static int launch_skinny(const void* a, const void* w, void* out, const float* r
     cfg.blockDim = dim3(GEMM_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
+    int n_attr = 0;
+    if (pdl_enabled()) {
+        attr[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n_attr].val.programmaticStreamSerializationAllowed = 1;
+        ++n_attr;
+    }
     if (splits > 1) {
         cfg.gridDim = dim3(tiles * splits);
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = splits;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        attr[n_attr].id = cudaLaunchAttributeClusterDimension;
+        attr[n_attr].val.clusterDim.x = splits;
+        attr[n_attr].val.clusterDim.y = 1;
+        attr[n_attr].val.clusterDim.z = 1;
+        ++n_attr;
     } else {
         cfg.gridDim = dim3(tiles < num_sms() ? tiles : num_sms());
     }
+    cfg.attrs = attr;
+    cfg.numAttrs = n_attr;
     KB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmW, tmX, out, resid, M, N, K, T, stages, splits, is_bf16));
     count_launch();
     KB_LAUNCH_CHECK();
