@@ -59,6 +59,9 @@ def parse_args():
     ap.add_argument("--no-provider", action="store_true", help="skip the provider-level (plugin API) turn")
     ap.add_argument("--gen-tokens", type=int, default=128, help="new tokens per turn in the provider-level leg")
     ap.add_argument("--no-ttft-sweep", action="store_true")
+    ap.add_argument("--agent-tool-rounds", type=int, default=0,
+                    help="provider-level leg as BASELINE configs[3]: every thread's turn is an AGENT turn with this "
+                         "many scripted tool rounds (64-token tool results) before the final text round")
     ap.add_argument("--no-pipeline", action="store_true",
                     help="serving loop reads every step back before enqueueing the next (A/B of the pipelined loop)")
     ap.add_argument("--tp-compare", action="store_true",
@@ -190,7 +193,7 @@ def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1):
 
 # ------------------------------------------------------------------------------------------------
 def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen_tokens: int, seed: int,
-                  pipeline: bool = True):
+                  pipeline: bool = True, tool_rounds: int = 0):
     """The call a user makes: B200LLMProvider.stream_completion for `n_threads` concurrent threads.
 
     Untimed set-up: every thread's ~`history`-token conversation is prefilled once through the provider
@@ -212,7 +215,18 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
     stepper.banned_token = tok.eot_id                   # EOS masked: every turn generates gen_tokens tokens
     stepper.close = lambda: None                        # the core outlives this leg
     engine = Engine(stepper, max_prefill_tokens=core.max_tokens, pipeline=pipeline)
-    provider = B200LLMProvider(engine, tok, model=cfg.name, default_temperature=0.0)
+    tools = tool_schemas = None
+    if tool_rounds > 0:
+        from kafka_b200.tools import LocalToolProvider, Tool
+
+        async def lookup(key: str = ""):
+            return "v" * 64                                   # a 64-token tool result (BASELINE configs[3])
+        tools = LocalToolProvider([Tool("lookup", "look something up",
+                                        {"type": "object", "properties": {"key": {"type": "string"}}}, lookup)])
+        from kafka_b200.agent import StreamingAgent
+        StreamingAgent(None, tools)                           # registers the agent's `idle` tool, as every turn will
+        tool_schemas = asyncio.run(tools.get_tools())         # the schemas are part of every prompt of these threads
+    provider = B200LLMProvider(engine, tok, model=cfg.name, default_temperature=0.0, tool_provider=tools)
 
     def text(rnd, n):
         return "".join(chr(rnd.randrange(32, 127)) for _ in range(n))
@@ -220,17 +234,17 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
     def make_history(i):
         rnd = random.Random(seed * 100003 + i)
         msgs = [Message(role="system", content="You are a helpful assistant.")]
-        while len(provider.render(msgs, None)) < history - 700:      # ~200 tokens per rendered message
+        while len(provider.render(msgs, tool_schemas)) < history - 700:      # ~200 tokens per rendered message
             msgs.append(Message(role="user", content=text(rnd, 180)))
             msgs.append(Message(role="assistant", content=text(rnd, 180)))
         # the last user message is sized so that the rendered prompt is exactly `history` tokens
-        short = history - len(provider.render(msgs + [Message(role="user", content="")], None))
+        short = history - len(provider.render(msgs + [Message(role="user", content="")], tool_schemas))
         msgs.append(Message(role="user", content=text(rnd, max(1, short))))
         return msgs
 
     async def run():
         hist = [make_history(i) for i in range(n_threads)]
-        n_hist = [len(provider.render(h, None)) for h in hist]
+        n_hist = [len(provider.render(h, tool_schemas)) for h in hist]
         t0 = time.perf_counter()
         first = await asyncio.gather(*[provider.completion(h, temperature=0.0, max_tokens=1, thread_id=f"bench-{i:04d}")
                                        for i, h in enumerate(hist)])
@@ -245,12 +259,28 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
         async def one(i, msgs):
             t_call = time.perf_counter()
             ttft, n = None, 0
-            async for ch in provider.stream_completion(msgs, temperature=0.0, max_tokens=gen_tokens,
-                                                       thread_id=f"bench-{i:04d}"):
-                if ch.content:
+            if tool_rounds <= 0:
+                async for ch in provider.stream_completion(msgs, temperature=0.0, max_tokens=gen_tokens,
+                                                           thread_id=f"bench-{i:04d}"):
+                    if ch.content:
+                        if ttft is None:
+                            ttft = time.perf_counter() - t_call
+                        n += len(ch.content)
+                return ttft, n, time.perf_counter() - t_call
+            # agent turn: tool_rounds x (16 tokens of text + one scripted tool call + its result), then text
+            from kafka_b200.agent import StreamingAgent
+            from kafka_b200.provider import B200LLMProvider as _P, ScriptedToolCallProvider
+            inner = _P(engine, tok, model=cfg.name, default_temperature=0.0, tool_provider=tools,
+                       thread_id=f"bench-{i:04d}")
+            agent = StreamingAgent(ScriptedToolCallProvider(inner, "lookup", {"key": "k"}, tool_rounds=tool_rounds,
+                                                            think_tokens=16), tools, system_prompt=None)
+            async for ev in agent.run(msgs, model=cfg.name, temperature=0.0, max_tokens=gen_tokens,
+                                      thread_id=f"bench-{i:04d}"):
+                ch = ev.get("choices")
+                if ch and ch[0].get("delta", {}).get("content"):
                     if ttft is None:
                         ttft = time.perf_counter() - t_call
-                    n += len(ch.content)
+                    n += len(ch[0]["delta"]["content"])
             return ttft, n, time.perf_counter() - t_call
 
         t0 = time.perf_counter()
@@ -271,7 +301,9 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
             "history_tokens_mean": sum(n_hist) / len(n_hist), "cached_fraction_of_prompt": cached / max(1, prompt),
             "prefilled_new_tokens": prompt - cached, "setup_prefill_s": setup_s,
             "engine_prefill_s": s1["prefill_s"] - stats0["prefill_s"], "engine_decode_s": s1["decode_s"] - stats0["decode_s"],
-            "api": "B200LLMProvider.stream_completion (LLMProvider plugin API), one coroutine per thread, "
+            "provider_calls": s1["requests"] - stats0["requests"], "agent_tool_rounds": tool_rounds,
+            "api": ("StreamingAgent.run over " if tool_rounds > 0 else "") +
+                   "B200LLMProvider.stream_completion (LLMProvider plugin API), one coroutine per thread, "
                    "pinned H2D of step inputs (ctx lens, block tables on membership change) and D2H of sampled "
                    "ids every step",
         }
@@ -279,6 +311,93 @@ def provider_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen
     try:
         return asyncio.run(run())
     finally:
+        engine.shutdown()
+
+
+# ------------------------------------------------------------------------------------------------
+def http_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen_tokens: int):
+    """HTTP-level TTFT: the repo's server (same routes as the reference's server.py) under
+    uvicorn on 127.0.0.1, `n_threads` concurrent POST /v1/threads/{id}/chat/completions with stream=true on
+    threads whose history (SQLite + KV) was built by an earlier request. TTFT = request sent -> first SSE
+    `data:` line carrying delta.content."""
+    import asyncio
+    import random
+    import socket
+    import statistics as st
+    import tempfile
+    import threading as th
+    import aiohttp
+    import uvicorn
+    from kafka_b200.db import ThreadStore
+    from kafka_b200.engine import Engine
+    from kafka_b200.gpu_stepper import GpuStepper
+    from kafka_b200.provider import B200LLMProvider
+    from kafka_b200.server import create_app
+    from kafka_b200.tokenizer import ByteTokenizer
+
+    tok = ByteTokenizer(cfg.vocab)
+    stepper = GpuStepper(core, tok, generable_only=True)
+    stepper.banned_token = tok.eot_id
+    stepper.close = lambda: None
+    engine = Engine(stepper, max_prefill_tokens=core.max_tokens)
+    tmp = tempfile.mkdtemp(prefix="kb-http-")
+
+    def factory(model, tool_provider=None, thread_id=None, **kw):
+        return B200LLMProvider(engine, tok, model=cfg.name, tool_provider=tool_provider, thread_id=thread_id,
+                               default_temperature=0.0)
+    app = create_app(factory, ThreadStore(os.path.join(tmp, "threads.db")), models=[cfg.name])
+    sock = socket.socket()
+    sock.bind(("127.0.0.1", 0))
+    port = sock.getsockname()[1]
+    sock.close()
+    server = uvicorn.Server(uvicorn.Config(app, host="127.0.0.1", port=port, log_level="error"))
+    t = th.Thread(target=server.run, daemon=True)
+    t.start()
+    for _ in range(200):
+        if server.started:
+            break
+        time.sleep(0.05)
+
+    def text(rnd, n):
+        return "".join(chr(rnd.randrange(97, 123)) for _ in range(n))
+
+    async def post(session, tid, content, max_tokens):
+        t0 = time.perf_counter()
+        ttft, n = None, 0
+        body = {"model": cfg.name, "stream": True, "temperature": 0, "max_tokens": max_tokens,
+                "messages": [{"role": "user", "content": content}]}
+        async with session.post(f"http://127.0.0.1:{port}/v1/threads/{tid}/chat/completions", json=body) as r:
+            async for raw in r.content:
+                line = raw.decode().strip()
+                if not line.startswith("data: ") or line == "data: [DONE]":
+                    continue
+                ev = json.loads(line[6:])
+                ch = ev.get("choices") or []
+                if ch and (ch[0].get("delta") or {}).get("content"):
+                    if ttft is None:
+                        ttft = time.perf_counter() - t0
+                    n += len(ch[0]["delta"]["content"])
+        return ttft, n, time.perf_counter() - t0
+
+    async def run():
+        async with aiohttp.ClientSession(timeout=aiohttp.ClientTimeout(total=600)) as session:
+            rnd = random.Random(7)
+            await asyncio.gather(*[post(session, f"http-{i:04d}", text(rnd, history - 64), 1) for i in range(n_threads)])
+            t0 = time.perf_counter()
+            res = await asyncio.gather(*[post(session, f"http-{i:04d}", text(rnd, user_tokens), gen_tokens)
+                                         for i in range(n_threads)])
+            wall = time.perf_counter() - t0
+        ttfts = sorted(x[0] for x in res if x[0] is not None)
+        return {"threads": n_threads, "history_tokens": history, "new_tokens_per_thread": gen_tokens,
+                "ttft_p50_ms": 1e3 * st.median(ttfts), "ttft_max_ms": 1e3 * ttfts[-1],
+                "turn_p50_ms": 1e3 * st.median(x[2] for x in res), "tokens_per_s": sum(x[1] for x in res) / wall,
+                "api": "POST /v1/threads/{id}/chat/completions stream=true over uvicorn on 127.0.0.1 (aiohttp client)"}
+
+    try:
+        return asyncio.run(run())
+    finally:
+        server.should_exit = True
+        t.join(timeout=10)
         engine.shutdown()
 
 
@@ -323,7 +442,8 @@ def run_b200(args, rank, world, local_rank):
     passes = 1 + (0 if args.no_profile else 1) + (0 if args.no_e2e else 1)
     tokens_per_thread = args.history + args.user_tokens + W * passes + K * passes + 8
     if not args.no_provider:  # the provider-level turn: history + re-templated turn (~90 tokens) + gen_tokens
-        tokens_per_thread = max(tokens_per_thread, args.history + 192 + args.gen_tokens)
+        tokens_per_thread = max(tokens_per_thread,
+                                args.history + 192 + args.gen_tokens + 320 * args.agent_tool_rounds)
     bpt = (tokens_per_thread + KB_BLOCK_TOKENS - 1) // KB_BLOCK_TOKENS
     B = args.threads
 
@@ -474,7 +594,8 @@ def run_b200(args, rank, world, local_rank):
     e2e_cabi = e2e
     if not args.no_provider:
         barrier()
-        pt = provider_turn(eng, cfg, B, args.history, U, args.gen_tokens, seed=rank, pipeline=not args.no_pipeline)
+        pt = provider_turn(eng, cfg, B, args.history, U, args.gen_tokens, seed=rank, pipeline=not args.no_pipeline,
+                           tool_rounds=args.agent_tool_rounds)
         pt["pipelined_loop"] = not args.no_pipeline
         wall = pt["wall_s"]
         if world > 1:
@@ -494,6 +615,10 @@ def run_b200(args, rank, world, local_rank):
                 sweep[str(h)] = {"ttft_p50_ms": r["ttft_p50_ms"], "cached_fraction": r["cached_fraction_of_prompt"],
                                  "prefilled_new_tokens": r["prefilled_new_tokens"]}
             e2e["ttft_vs_history_16_threads"] = sweep
+            try:    # the same turn through the HTTP server (first SSE line with content)
+                e2e["http_16_threads"] = http_turn(eng, cfg, 16, args.history, U, 32)
+            except Exception as ex:   # a missing HTTP dependency must not cost the bench line
+                e2e["http_16_threads"] = {"unavailable": repr(ex)}
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
