@@ -606,7 +606,7 @@ def run_b200(args, rank, world, local_rank):
         pt["ms_per_step"] = 1e3 * wall / pt["decode_steps"]
         e2e = pt
         # per-turn TTFT against history length (north_star: independent of it): 16 concurrent threads
-        if rank == 0 and not args.no_ttft_sweep:
+        if rank == 0 and world == 1 and not args.no_ttft_sweep:   # N = 1 only: no rank waits on rank 0's extras
             sweep = {}
             for h in (256, 1024, 2048, 4096):
                 if h + 192 + 32 > cfg.max_pos:

@@ -12,6 +12,12 @@
 //     warps 4-7: epilogue      (tcgen05.ld 32x32b.x32 -> registers -> fused epilogue -> global)
 //   * three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue).
 //
+// Three kernels share that anatomy (gemm_ex picks per shape):
+//   gemm_tcgen05_kernel<BN,EPI>      one CTA per 128 x BN tile (BN = 64 / 128 / 256)
+//   gemm_tcgen05_2cta_kernel<EPI>    a CTA pair (cta_group::2) per 256 x bn tile, bn chosen at run time
+//   gemm_tcgen05_skinny_kernel<EPI>  M <= 32 tokens: operands swapped, cluster split-K reduced through DSMEM
+// and every kernel starts with its private set-up, then griddepcontrol.wait / launch_dependents (PDL).
+//
 // Roofline: tensor pipe for M >= ~256 rows, weight bandwidth below that.
 // Algorithmic FLOPs per launch = 2*M*N*K.
 #include "kb_common.cuh"
@@ -299,11 +305,11 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // CTA-pair variant (cta_group::2): a cluster of two CTAs owns a 256 x BN output tile.
 //
-// Why: a 1-CTA 128 x BN tile moves 16 KB of A plus BN*128 B of B through its shared-memory port twice
-// per k-block (TMA in, tensor core out) and is bound by that port, not by the MMA (profiles/
-// r01_gemm_bench.md). In a pair each CTA stages its own 128 rows of A but only HALF of B (BN/2 rows);
-// the tensor cores of both SMs read both halves, so the traffic per CTA drops to 16 KB + BN*64 B for
-// twice the rows: balanced with the MMA at BN = 256.
+// Why: a 1-CTA 128 x BN tile has to bring 16 KB of A plus BN*128 B of B into shared memory per k-block,
+// and an SM takes in only ~50 B/clk by TMA (measured: tools/gemm_trace.py, profiles/r01_gemm_bench.md) —
+// that ingress, not the MMA, bounds the main loop. In a pair each CTA stages its own 128 rows of A but
+// only HALF of B (BN/2 rows); the tensor cores of both SMs read both halves, so the ingress per CTA drops
+// to 16 KB + BN*64 B for twice the rows: close to balanced with the MMA at BN = 256.
 //
 //   * both CTAs : TMA producer (own A rows, own half of B), completion bytes counted on the LEADER's
 //                 full barrier; epilogue of their own 128 accumulator rows (own TMEM).
@@ -1009,17 +1015,16 @@ static int pick_bn(int M, int N) {
         const int bn = cands[i];
         const long tiles = (long)num_m * ((N + bn - 1) / bn);
         const long per_cta = (tiles + sms - 1) / sms;
-        // Per k-block a 1-CTA tile moves (16 KB of A + bn*128 B of B) into shared memory by TMA and out
-        // again into the tensor core: 2*(128 + bn) cycles at the 128 B/clk shared-memory port, always
-        // more than the 2*bn cycles the MMA itself needs. So the tile time is ~ (256 + 2 bn) per
-        // k-block (measured: tools/gemm_bench.py, profiles/r01_gemm_bench.md) and wide tiles win
-        // unless they leave SMs idle.
+        // Per k-block a 1-CTA tile brings (16 KB of A + bn*128 B of B) into shared memory by TMA at
+        // ~50-64 B/clk per SM: ~(256 + 2 bn) cycles, always more than the 2*bn cycles the MMA itself
+        // needs (measured: tools/gemm_bench.py, tools/gemm_trace.py, profiles/r01_gemm_bench.md). Wide
+        // tiles win unless they leave SMs idle.
         const long cost = per_cta * (256 + 2 * bn);
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
     }
     if (M > GEMM_BM) {
         // CTA pair, 256 x bn tile: each CTA stages 16 KB of A and bn*64 B of B per k-block -> 256 + bn
-        // cycles of shared-memory port against 2 bn cycles of MMA
+        // cycles of TMA ingress against 2 bn cycles of MMA
         // ... any multiple of 16 (run-time tile width): take the width whose tile count wastes the least
         // of the last round; wider wins ties (less A re-read)
         const int num_mp = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);

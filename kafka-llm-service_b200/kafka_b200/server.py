@@ -35,8 +35,7 @@ from pydantic import BaseModel, Field
 
 from .agent import StreamingAgent
 from .db import ThreadStore
-from .history import assemble_turn, sanitize_messages, to_message
-from .llm.types import Message
+from .history import sanitize_messages, to_message
 from .orchestrator import ThreadRunner
 from .tools import LocalToolProvider, Tool
 
