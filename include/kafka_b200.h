@@ -102,8 +102,9 @@ void kb_engine_destroy(kb_engine* e);
 /* Takes over: nothing in the reference (weights live behind the gateway). Pointers are borrowed. */
 int kb_bind_weights(kb_engine* e, const kb_weight_ptrs* w);
 
-/* KV pools, layout [layer][block][kv_head][token_in_block][head_dim] bf16 with the 16-byte chunks of
- * each token row XOR-swizzled by (token & 7).  k_pool and v_pool each hold
+/* KV pools, layout [layer][block][kv_head][dim plane = dim / 64][token_in_block][64 dims] bf16 with the
+ * 16-byte chunks of each 128-byte row XOR-swizzled by (token & 7) — every plane of a (block, head) tile is
+ * a canonical SWIZZLE_128B K-major matrix.  k_pool and v_pool each hold
  * n_layers * n_blocks * n_kv_heads * KB_BLOCK_TOKENS * head_dim bf16.
  * Takes over: the thread history the reference re-sends in full on every call
  * (src/agents/base.py:222-223) — here it stays resident in HBM. */

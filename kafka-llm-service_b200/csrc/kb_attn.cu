@@ -44,7 +44,8 @@ __device__ __forceinline__ void attn_tile(float (&o)[HD / 8][4], float (&m)[2], 
                                           const uint32_t (&qa)[HD / 16][4], uint32_t ks, uint32_t vs, int tok0,
                                           int lim0, int lim1, float sc, bool need_mask, int lane) {
     constexpr int NJ = NT / 8;
-    constexpr int ROW_BYTES = HD * 2;
+    constexpr int ROW_BYTES = 128;            // one token's 64 dims of one plane
+    constexpr int PLANE_BYTES = NT * 128;     // [dim plane][token][64 dims]: see kv_swizzled_elem
     const int lrow = lane & 7;
     const int lmat = lane >> 3;
     const int t = lane & 3;
@@ -58,9 +59,9 @@ __device__ __forceinline__ void attn_tile(float (&o)[HD / 8][4], float (&m)[2], 
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
             const int token = 8 * j + lrow;
-            const int chunk = (4 * kk2 + lmat) ^ lrow;
+            const int c = 4 * kk2 + lmat;      // logical 16-byte chunk of the head: plane c / 8, chunk c % 8
             uint32_t b0, b1, b2, b3;
-            ldsm_x4(ks + token * ROW_BYTES + chunk * 16, b0, b1, b2, b3);
+            ldsm_x4(ks + (c >> 3) * PLANE_BYTES + token * ROW_BYTES + (((c & 7) ^ lrow) << 4), b0, b1, b2, b3);
             mma_bf16_16816(s[j], qa[2 * kk2][0], qa[2 * kk2][1], qa[2 * kk2][2], qa[2 * kk2][3], b0, b1);
             mma_bf16_16816(s[j], qa[2 * kk2 + 1][0], qa[2 * kk2 + 1][1], qa[2 * kk2 + 1][2], qa[2 * kk2 + 1][3], b2,
                            b3);
@@ -136,9 +137,9 @@ __device__ __forceinline__ void attn_tile(float (&o)[HD / 8][4], float (&m)[2], 
 #pragma unroll
         for (int d2 = 0; d2 < HD / 16; ++d2) {
             const int token = 16 * kk + (lmat & 1) * 8 + lrow;
-            const int chunk = (2 * d2 + (lmat >> 1)) ^ lrow;
+            const int c = 2 * d2 + (lmat >> 1);
             uint32_t b0, b1, b2, b3;
-            ldsm_x4_t(vs + token * ROW_BYTES + chunk * 16, b0, b1, b2, b3);
+            ldsm_x4_t(vs + (c >> 3) * PLANE_BYTES + token * ROW_BYTES + (((c & 7) ^ lrow) << 4), b0, b1, b2, b3);
             mma_bf16_16816(o[2 * d2], a0, a1, a2, a3, b0, b1);
             mma_bf16_16816(o[2 * d2 + 1], a0, a1, a2, a3, b2, b3);
         }
@@ -214,11 +215,16 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv
     auto issue = [&](int h, int stage) {
         // lane 0 only
         const int phys = bt[h >> 1];
-        const size_t off = (((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS + (size_t)(h & 1) * NT) * HD;
+        // 32 tokens of every 64-dim plane of the tile: HD/64 pieces of 4 KB each for K and for V
+        const size_t off = ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * HD + (size_t)(h & 1) * NT * 64;
         uint8_t* ks = my_ring + stage * 2 * Cfg::TILE_BYTES;
         mbar_arrive_expect_tx(&my_bars[stage], 2 * Cfg::TILE_BYTES);
-        bulk_g2s(ks, kpool + off, Cfg::TILE_BYTES, &my_bars[stage]);
-        bulk_g2s(ks + Cfg::TILE_BYTES, vpool + off, Cfg::TILE_BYTES, &my_bars[stage]);
+#pragma unroll
+        for (int p = 0; p < HD / 64; ++p) {
+            bulk_g2s(ks + p * (NT * 128), kpool + off + (size_t)p * KB_BLOCK_TOKENS * 64, NT * 128, &my_bars[stage]);
+            bulk_g2s(ks + Cfg::TILE_BYTES + p * (NT * 128), vpool + off + (size_t)p * KB_BLOCK_TOKENS * 64, NT * 128,
+                     &my_bars[stage]);
+        }
     };
 
     float o[HD / 8][4];

@@ -342,11 +342,18 @@ __device__ __forceinline__ float warp_sum(float v) {
 // ---------------------------------------------------------------------------------------------
 constexpr int KB_BLOCK_TOKENS_C = KB_BLOCK_TOKENS;
 
+// Element offset of (token, dim) inside one (block, kv head) tile of the paged pools:
+//     [dim plane = dim / 64][token 0..63][64 dims = 128 bytes, 16-byte chunks XOR-ed with (token & 7)]
+// i.e. every 64-dim plane of a tile is a canonical SWIZZLE_128B K-major matrix of 64 rows x 128 bytes
+// (what ldmatrix reads without bank conflicts AND what a tcgen05 shared-memory descriptor addresses), and a
+// flat bulk copy of the tile (or of 32 tokens of one plane) lands in shared memory ready to use.
 __host__ __device__ __forceinline__ int kv_swizzled_elem(int token_in_block, int dim, int head_dim) {
-    int chunk = dim >> 3;
-    int within = dim & 7;
-    int sw = chunk ^ (token_in_block & 7);
-    return token_in_block * head_dim + (sw << 3) + within;
+    (void)head_dim;
+    const int plane = dim >> 6;
+    const int chunk = (dim & 63) >> 3;
+    const int within = dim & 7;
+    const int sw = chunk ^ (token_in_block & 7);
+    return plane * (KB_BLOCK_TOKENS * 64) + token_in_block * 64 + (sw << 3) + within;
 }
 
 }  // namespace kb

@@ -2,9 +2,11 @@
 
     pool[layer][block][kv_head][token_in_block][head_dim]      bf16, K and V in separate pools
 
-One (block, kv_head) tile is ``KB_BLOCK_TOKENS * head_dim`` contiguous elements. Inside a tile the
-16-byte chunks (8 bf16) of a token row are XOR-swizzled with ``token & 7`` so the CUDA kernels can
-``ldmatrix`` from a tile staged by a plain 1-D TMA bulk copy without bank conflicts.
+One (block, kv_head) tile is ``KB_BLOCK_TOKENS * head_dim`` contiguous elements, stored as
+``[dim plane = dim // 64][token][64 dims]``: every 64-dim plane is a 64-row x 128-byte matrix whose
+16-byte chunks (8 bf16) are XOR-swizzled with ``token & 7`` — the canonical SWIZZLE_128B K-major form, so
+a plain 1-D TMA bulk copy of a tile lands in shared memory ready for ``ldmatrix`` (no bank conflicts)
+and for tcgen05 shared-memory descriptors alike.
 
 These helpers exist for tests, smoke and debugging tools; the product path never moves KV through
 the host (the append kernel writes the layout directly).
@@ -20,8 +22,9 @@ def tile_permutation(head_dim: int) -> torch.Tensor:
     """perm[t * head_dim + d] = physical element offset of logical (token t, dim d) inside a tile."""
     t = torch.arange(KB_BLOCK_TOKENS).view(-1, 1)
     d = torch.arange(head_dim).view(1, -1)
-    chunk = (d // 8) ^ (t & 7)
-    return (t * head_dim + chunk * 8 + (d % 8)).reshape(-1)
+    plane = d // 64
+    chunk = ((d % 64) // 8) ^ (t & 7)
+    return (plane * (KB_BLOCK_TOKENS * 64) + t * 64 + chunk * 8 + (d % 8)).reshape(-1)
 
 
 def pool_shape(n_layers: int, n_blocks: int, n_kv_heads: int, head_dim: int):

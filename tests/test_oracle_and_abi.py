@@ -158,7 +158,8 @@ def test_kv_layout_matches_kernel_swizzle():
         perm = tile_permutation(hd).view(64, hd)
         for t in (0, 1, 7, 8, 13, 63):
             for d in (0, 7, 8, 63, hd - 1):
-                want = t * hd + (((d >> 3) ^ (t & 7)) << 3) + (d & 7)                    # kb_common.cuh kv_swizzled_elem
+                # kb_common.cuh kv_swizzled_elem: [dim plane][token][64 dims], chunks XOR (token & 7)
+                want = (d >> 6) * 64 * 64 + t * 64 + ((((d & 63) >> 3) ^ (t & 7)) << 3) + (d & 7)
                 assert int(perm[t, d]) == want
         assert sorted(perm.view(-1).tolist()) == list(range(64 * hd))                    # a permutation of the tile
 
