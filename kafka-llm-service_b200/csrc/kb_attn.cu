@@ -570,6 +570,11 @@ static int launch_prefill(const void* q, int q_stride, const void* kp, const voi
     return KB_OK;
 }
 
+// kb_attn_tc.cu: the tcgen05 / TMEM formulation (head_dim 128); -1 = shape not covered
+int attn_prefill_tc(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+                    const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
+                    int head_dim, int out_f16, cudaStream_t stream);
+
 int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
                  const int* bt, void* out, int n_seqs, int n_tokens, int max_new, int max_blocks, int n_heads,
                  int n_kv_heads, int head_dim, int out_f16, cudaStream_t stream) {
@@ -577,6 +582,13 @@ int attn_prefill(const void* q, int q_stride, const void* kp, const void* vp, co
     KB_CHECK(n_kv_heads > 0 && n_heads % n_kv_heads == 0, "kb_attn_prefill: n_heads %% n_kv_heads != 0");
     KB_CHECK(n_seqs <= 65535, "kb_attn_prefill: n_seqs %d > 65535", n_seqs);
     const int group = n_heads / n_kv_heads;
+    static int legacy = -1;
+    if (legacy < 0) legacy = getenv("KB_ATTN_PREFILL_LEGACY") != nullptr;
+    if (!legacy) {
+        const int rc = attn_prefill_tc(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks, n_heads,
+                                       n_kv_heads, head_dim, out_f16, stream);
+        if (rc != -1) return rc;
+    }
 #define KB_PREFILL_CASE(HD_, G_)                                                                               \
     if (head_dim == HD_ && group == G_)                                                                        \
         return launch_prefill<HD_, G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks,    \

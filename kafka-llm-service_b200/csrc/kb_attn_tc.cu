@@ -1,0 +1,396 @@
+// kb_attn_tc.cu — causal prefill attention on the 5th-gen tensor cores (tcgen05 + TMEM), head_dim 128.
+//
+// One CTA = 128 query rows of one (sequence, KV head): row r = (query token q0 + r / GROUP, head r % GROUP),
+// i.e. TMEM lane r. Per 64-token K/V tile j of the paged pool:
+//
+//   warp 9 (producer) : two bulk copies (K tile, V tile: 16 KB each, already in the canonical
+//                       SWIZZLE_128B form — kv_swizzled_elem) into a 3-stage ring
+//   warp 8 (MMA)      : S_j  = Q K_j^T        8 x tcgen05.mma 128x64x16, A = Q (shared, K-major),
+//                                              B = K_j (shared, K-major)            -> TMEM S[j & 1]
+//                       OT_j = P_j V_j         4 x tcgen05.mma 128x128x16, A = P_j (shared, K-major),
+//                                              B = V_j (shared, MN-major descriptor) -> TMEM OT[j & 1]
+//                       issue order S_0, S_1, OT_0, S_2, OT_1, ...  (the softmax of tile j+1 never waits
+//                       for the P V product of tile j)
+//   warps 0-7 (softmax): TWO threads per query row (warp w and w + 4 share the TMEM lanes of quarter w & 3):
+//                       each takes 32 of the 64 S columns and 64 of the 128 output dims; tcgen05.ld S_j ->
+//                       causal mask, row max (the two halves meet through shared memory), running sum in fp32,
+//                       P_j = exp2((S_j - m_j) * scale) as bf16 into shared memory (swizzled K-major) -> then
+//                       fold the finished OT_{j-1} into the register accumulator:
+//                       o = (o + OT_{j-1}) * exp2(m_{j-1} - m_j).  Two warps per scheduler hide each other's
+//                       TMEM / MUFU latencies; the first version (one thread per row) ran at 3 350 cycles per tile.
+//
+// The P V product is computed fresh per tile and accumulated in registers, so no thread ever rescales
+// TMEM and no correction pass exists. TMEM: 2 x 64 (S) + 2 x 128 (OT) = 384 of 512 columns.
+//
+// Replaces the mma.sync prefill kernel of kb_attn.cu for head_dim 128 (that one stays for head_dim 64 and
+// as the A/B reference: KB_ATTN_PREFILL_LEGACY=1). Reference counterpart: none (src/llm/portkey.py:379).
+#include "kb_common.cuh"
+
+namespace kb {
+
+namespace {
+
+constexpr int TC_ROWS = 128;      // query rows per CTA = TMEM lanes
+constexpr int TC_NT = 64;         // tokens per K/V tile = one KV block
+constexpr int TC_HD = 128;
+constexpr int TC_STAGES = 3;
+constexpr int TC_TILE_BYTES = TC_NT * TC_HD * 2;          // 16 KB (K or V)
+constexpr int TC_Q_BYTES = TC_ROWS * TC_HD * 2;           // 32 KB: [plane][128 rows][128 B]
+constexpr int TC_P_BYTES = TC_ROWS * TC_NT * 2;           // 16 KB: [128 rows][128 B]
+constexpr int TC_THREADS = 320;     // 8 softmax warps + MMA warp + producer warp
+constexpr int TC_SOFTMAX_THREADS = 256;
+constexpr int TC_SMEM = 1024 + TC_Q_BYTES + 2 * TC_P_BYTES + TC_STAGES * 2 * TC_TILE_BYTES + 256 + 2 * 2 * TC_ROWS * 4;
+constexpr float TC_LOG2E = 1.4426950408889634f;
+
+// K-major, SWIZZLE_128B: rows of 128 bytes, 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// MN-major, SWIZZLE_128B (cute: Swizzle<3,4,3> o ((8,n),(8,k)) : ((1,LBO),(8,SBO)) in 16-byte units):
+// a K row holds 64 MN elements (128 bytes); 8-row K groups are `sbo` bytes apart, 64-element MN chunks
+// `lbo` bytes apart. For a V tile: rows = tokens, MN = head dims, lbo = plane stride, sbo = 1024.
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(lbo >> 4) << 16;
+    d |= (uint64_t)(sbo >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// bf16 x bf16 -> fp32, M = 128; b_mn: B operand is MN-major.
+__device__ __forceinline__ uint32_t idesc_bf16(int n, int b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) |
+           ((uint32_t)(TC_ROWS >> 4) << 24);
+}
+
+// The MMA and producer warps wait with one thread each; a tight try_wait loop in those warps competes for
+// issue slots with the two softmax warps on the same scheduler (20 % of the samples of the first version were
+// BRA / SYNCS / NOP), so they sleep between polls.
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(64);
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {   // one MUFU.EX2; ex2(-inf) = 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <int GROUP>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
+                       const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+                       const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
+                       uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
+    constexpr int TQ = TC_ROWS / GROUP;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_s = smem;                                   // [2 planes][128 rows][128 B]
+    uint8_t* p_s = q_s + TC_Q_BYTES;                       // 2 x [128 rows][128 B]
+    uint8_t* kv_s = p_s + 2 * TC_P_BYTES;                  // ring: stage x (K tile, V tile)
+    uint64_t* kv_full = reinterpret_cast<uint64_t*>(kv_s + TC_STAGES * 2 * TC_TILE_BYTES);
+    uint64_t* kv_empty = kv_full + TC_STAGES;
+    uint64_t* s_full = kv_empty + TC_STAGES;               // [2]
+    uint64_t* s_empty = s_full + 2;                        // [2]
+    uint64_t* p_full = s_empty + 2;                        // [2]
+    uint64_t* o_full = p_full + 2;                         // [2]
+    uint64_t* o_empty = o_full + 2;                        // [2]
+    uint64_t* q_ready = o_empty + 2;                       // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+    float* mx_x = reinterpret_cast<float*>(kv_s + TC_STAGES * 2 * TC_TILE_BYTES + 256);   // [tile parity][half][row]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 8 && lane == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&s_full[a], 1);
+            mbar_init(&s_empty[a], 8);
+            mbar_init(&p_full[a], 8);
+            mbar_init(&o_full[a], 1);
+            mbar_init(&o_empty[a], 8);
+        }
+        mbar_init(q_ready, 8);
+        fence_mbar_init();
+    } else if (warp == 9) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch();
+
+    const int seq = blockIdx.z, kvh = blockIdx.y;
+    const int tok_begin = cu_seqlens[seq];
+    const int n_new = cu_seqlens[seq + 1] - tok_begin;
+    const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * TQ;      // heavy (late) query tiles first
+    const bool active = q0 < n_new;
+    const int ctx = ctx_lens[seq];
+    const int q_end = min(n_new, q0 + TQ);
+    const int kv_end = ctx + q_end;
+    const int n_tiles = active ? (kv_end + TC_NT - 1) / TC_NT : 0;
+    const uint32_t s_tmem = tmem_base;                     // S[a]  at columns a * 64
+    const uint32_t o_tmem = tmem_base + 128;               // OT[a] at columns 128 + a * 128
+
+    if (warp == 9) {
+        // ===== producer =====
+        if (lane == 0) {
+            const int* bt = block_tables + (size_t)seq * max_blocks;
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % TC_STAGES;
+                mbar_wait_relaxed(&kv_empty[st], (uint32_t)(((j / TC_STAGES) & 1) ^ 1));
+                const size_t off = ((size_t)bt[j] * n_kv_heads + kvh) * KB_BLOCK_TOKENS * TC_HD;
+                uint8_t* ks = kv_s + st * 2 * TC_TILE_BYTES;
+                mbar_arrive_expect_tx(&kv_full[st], 2 * TC_TILE_BYTES);
+                bulk_g2s(ks, kpool + off, TC_TILE_BYTES, &kv_full[st]);
+                bulk_g2s(ks + TC_TILE_BYTES, vpool + off, TC_TILE_BYTES, &kv_full[st]);
+            }
+        }
+    } else if (warp == 8) {
+        // ===== MMA issuer =====
+        if (lane == 0 && n_tiles > 0) {
+            const uint32_t id_s = idesc_bf16(TC_NT, 0);        // S  = Q K^T : N = 64 tokens, B K-major
+            const uint32_t id_o = idesc_bf16(TC_HD, 1);        // OT = P V   : N = 128 dims,  B MN-major
+            const uint32_t qa = smem_u32(q_s);
+            mbar_wait(q_ready, 0);
+            tc_fence_after();
+            auto issue_s = [&](int j) {
+                const int st = j % TC_STAGES, a = j & 1;
+                mbar_wait_relaxed(&kv_full[st], (uint32_t)((j / TC_STAGES) & 1));
+                mbar_wait_relaxed(&s_empty[a], (uint32_t)(((j >> 1) & 1) ^ 1));
+                tc_fence_after();
+                const uint32_t kb = smem_u32(kv_s + st * 2 * TC_TILE_BYTES);
+#pragma unroll
+                for (int p = 0; p < 2; ++p)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16(s_tmem + (uint32_t)(a * 64), desc_kmajor(qa + p * (TC_ROWS * 128) + k * 32),
+                                  desc_kmajor(kb + p * (TC_NT * 128) + k * 32), id_s, (uint32_t)((p | k) != 0));
+                umma_commit(&s_full[a]);
+            };
+            auto issue_o = [&](int j) {
+                const int st = j % TC_STAGES, a = j & 1;
+                mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));
+                mbar_wait_relaxed(&o_empty[a], (uint32_t)(((j >> 1) & 1) ^ 1));
+                tc_fence_after();
+                const uint32_t vb = smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES);
+                const uint32_t pa = smem_u32(p_s + a * TC_P_BYTES);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)       // 16 tokens per step: two 8-row groups of the V tile
+                    umma_bf16(o_tmem + (uint32_t)(a * 128), desc_kmajor(pa + k * 32),
+                              desc_mnmajor(vb + k * 2048, TC_NT * 128, 1024), id_o, (uint32_t)(k != 0));
+                umma_commit(&o_full[a]);
+                umma_commit(&kv_empty[st]);       // K_j and V_j are both consumed
+            };
+            issue_s(0);
+            for (int j = 0; j < n_tiles; ++j) {
+                if (j + 1 < n_tiles) issue_s(j + 1);
+                issue_o(j);
+            }
+        }
+    } else {
+        // ===== softmax warps: two threads per query row (TMEM lane) =====
+        const int quarter = warp & 3, half = warp >> 2;
+        const int r = quarter * 32 + lane;                 // row = TMEM lane
+        const int tl = q0 + r / GROUP;
+        const int head = kvh * GROUP + r % GROUP;
+        const bool valid = active && tl < n_new;
+        const int lim = valid ? ctx + tl + 1 : kv_end;     // exclusive key limit of this row
+        // this thread's plane of the Q row -> shared memory, swizzled K-major
+        if (active) {
+            const uint4* src = reinterpret_cast<const uint4*>(q + (size_t)(tok_begin + min(tl, n_new - 1)) * q_stride +
+                                                              (size_t)head * TC_HD) + half * 8;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint4 v = valid ? src[c] : make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(q_s + half * (TC_ROWS * 128) + r * 128 + ((c ^ (r & 7)) << 4)) = v;
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_ready);
+        }
+        float o[64];                                       // output dims [half * 64, +64) of this row
+#pragma unroll
+        for (int d = 0; d < 64; ++d) o[d] = 0.f;
+        float m = -INFINITY, l = 0.f;                      // m: shared by both halves; l: this half's columns
+        const float sc = TC_LOG2E * rsqrtf((float)TC_HD);
+        const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+
+        for (int j = 0; j < n_tiles; ++j) {
+            const int a = j & 1;
+            // ---- softmax of tile j: this thread's 32 columns ----
+            mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
+            tc_fence_after();
+            uint32_t u[32];
+            float s[32];
+            tmem_ld_32x32(s_tmem + lane_off + (uint32_t)(a * 64 + half * 32), u);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_empty[a]);       // the MMA warp may overwrite S[a] with tile j + 2
+
+            const int tok0 = j * TC_NT + half * 32;
+            float mx = -INFINITY;
+            if (tok0 + 32 > lim) {                         // causal / length mask: only the last tiles of a row
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float v = (tok0 + i >= lim) ? -INFINITY : __uint_as_float(u[i]);
+                    s[i] = v;
+                    mx = fmaxf(mx, v);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    s[i] = __uint_as_float(u[i]);
+                    mx = fmaxf(mx, s[i]);
+                }
+            }
+            float* xb = mx_x + a * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = mx;
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
+            // Running max in scaled (log2) units, raised LAZILY: it only moves when the tile's max exceeds it by
+            // more than 8, so P stays below 2^8 (exact enough in bf16, sums in fp32) and most tiles need no
+            // rescaling of the accumulator at all (corr == 1).
+            const float tile_mx = fmaxf(mx, xb[(half ^ 1) * TC_ROWS + r]) * sc;
+            const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;
+            const float corr = ex2_approx(m - m_new);       // m = -inf on the first tile -> 0
+            m = m_new;
+            float sum = 0.f;
+            uint8_t* prow = p_s + a * TC_P_BYTES + r * 128;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                float pv[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    pv[i] = ex2_approx(fmaf(s[8 * c + i], sc, -m_new));
+                    sum += pv[i];
+                }
+                uint4 w;
+                w.x = pack_bf16(pv[0], pv[1]);
+                w.y = pack_bf16(pv[2], pv[3]);
+                w.z = pack_bf16(pv[4], pv[5]);
+                w.w = pack_bf16(pv[6], pv[7]);
+                *reinterpret_cast<uint4*>(prow + (((half * 4 + c) ^ (r & 7)) << 4)) = w;
+            }
+            l = l * corr + sum;
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[a]);
+
+            // ---- fold the finished product of tile j - 1:  o = (o + OT_{j-1}) * corr ----
+            if (j > 0) {
+                const int b = (j - 1) & 1;
+                mbar_wait(&o_full[b], (uint32_t)(((j - 1) >> 1) & 1));
+                tc_fence_after();
+                const bool rescale = __any_sync(0xffffffffu, corr != 1.f);   // rare after the first tiles
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    tmem_ld_32x32(o_tmem + lane_off + (uint32_t)(b * 128 + half * 64 + c * 32), u);
+                    tmem_ld_wait();
+                    if (rescale) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[32 * c + i] = (o[32 * c + i] + __uint_as_float(u[i])) * corr;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[32 * c + i] += __uint_as_float(u[i]);
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&o_empty[b]);
+            }
+        }
+        if (n_tiles > 0) {
+            const int b = (n_tiles - 1) & 1;
+            mbar_wait(&o_full[b], (uint32_t)(((n_tiles - 1) >> 1) & 1));
+            tc_fence_after();
+            uint32_t u[32];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                tmem_ld_32x32(o_tmem + lane_off + (uint32_t)(b * 128 + half * 64 + c * 32), u);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) o[32 * c + i] += __uint_as_float(u[i]);
+            }
+            tc_fence_before();
+            // the row sum is the sum of both halves' partial sums (same running max in both)
+            float* xb = mx_x + (n_tiles & 1) * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = l;
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
+            l += xb[(half ^ 1) * TC_ROWS + r];
+            if (valid) {
+                const float inv = 1.f / l;
+                uint16_t* op = out + ((size_t)(tok_begin + tl) * n_heads + head) * TC_HD + half * 64;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    uint4 w;
+                    w.x = pack_act(o[8 * c + 0] * inv, o[8 * c + 1] * inv, out_f16);
+                    w.y = pack_act(o[8 * c + 2] * inv, o[8 * c + 3] * inv, out_f16);
+                    w.z = pack_act(o[8 * c + 4] * inv, o[8 * c + 5] * inv, out_f16);
+                    w.w = pack_act(o[8 * c + 6] * inv, o[8 * c + 7] * inv, out_f16);
+                    *reinterpret_cast<uint4*>(op + 8 * c) = w;
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+template <int GROUP>
+int launch_tc(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+              const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
+              int out_f16, cudaStream_t stream) {
+    auto kern = attn_prefill_tc_kernel<GROUP>;
+    static bool configured[64] = {};
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+        configured[dev & 63] = true;
+    }
+    constexpr int TQ = TC_ROWS / GROUP;
+    dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
+    KB_CUDA(launch_kernel(kern, grid, dim3(TC_THREADS), TC_SMEM, stream, (const __nv_bfloat16*)q, q_stride,
+                          (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
+                          n_heads, n_kv_heads, out_f16));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+}  // namespace
+
+// Returns -1 when the shape is not covered (caller falls back to the mma.sync kernel).
+int attn_prefill_tc(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+                    const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
+                    int head_dim, int out_f16, cudaStream_t stream) {
+    if (head_dim != TC_HD) return -1;
+    const int group = n_heads / n_kv_heads;
+#define KB_TC_CASE(G_)                                                                                          \
+    if (group == G_)                                                                                            \
+        return launch_tc<G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks, n_heads,      \
+                             n_kv_heads, out_f16, stream);
+    KB_TC_CASE(1) KB_TC_CASE(2) KB_TC_CASE(4) KB_TC_CASE(8)
+#undef KB_TC_CASE
+    return -1;
+}
+
+}  // namespace kb

@@ -20,6 +20,8 @@ def main():
     ap.add_argument("--history", type=int, default=2048)
     ap.add_argument("--user-tokens", type=int, default=64)
     ap.add_argument("--chunk", type=int, default=4096)
+    ap.add_argument("--only", default=None, choices=["turn", "cold"])
+    ap.add_argument("--cold-seqs", type=int, default=32)
     args = ap.parse_args()
     from kafka_b200 import cabi
     from kafka_b200.engine_core import EngineCore
@@ -69,8 +71,10 @@ def main():
                      "kernels_ms": {k: round(v[0], 3) for k, v in prof.items() if v[1]},
                      "launches": {k: v[1] for k, v in prof.items() if v[1]}}
 
-    run("turn", B, U, H)
-    run("cold", min(B, 32), H, 0)
+    if args.only != "cold":
+        run("turn", B, U, H)
+    if args.only != "turn":
+        run("cold", min(B, args.cold_seqs), H, 0)
     print(json.dumps(out))
 
 
