@@ -4,23 +4,26 @@
 // i.e. TMEM lane r. Per 64-token K/V tile j of the paged pool:
 //
 //   warp 9 (producer) : two bulk copies (K tile, V tile: 16 KB each, already in the canonical
-//                       SWIZZLE_128B form — kv_swizzled_elem) into a 3-stage ring
-//   warp 8 (MMA)      : S_j  = Q K_j^T        8 x tcgen05.mma 128x64x16, A = Q (shared, K-major),
+//                       SWIZZLE_128B form — kv_swizzled_elem) into a 4-stage ring
+//   warp 8 (MMA)      : S_j  = Q K_j^T        8 x tcgen05.mma 128x64x16, A = Q in TENSOR MEMORY,
 //                                              B = K_j (shared, K-major)            -> TMEM S[j & 1]
-//                       OT_j = P_j V_j         4 x tcgen05.mma 128x128x16, A = P_j (shared, K-major),
+//                       OT_j = P_j V_j         4 x tcgen05.mma 128x128x16, A = P_j in TENSOR MEMORY,
 //                                              B = V_j (shared, MN-major descriptor) -> TMEM OT[j & 1]
 //                       issue order S_0, S_1, OT_0, S_2, OT_1, ...  (the softmax of tile j+1 never waits
 //                       for the P V product of tile j)
 //   warps 0-7 (softmax): TWO threads per query row (warp w and w + 4 share the TMEM lanes of quarter w & 3):
 //                       each takes 32 of the 64 S columns and 64 of the 128 output dims; tcgen05.ld S_j ->
 //                       causal mask, row max (the two halves meet through shared memory), running sum in fp32,
-//                       P_j = exp2((S_j - m_j) * scale) as bf16 into shared memory (swizzled K-major) -> then
+//                       P_j = exp2((S_j - m_j) * scale) as bf16 pairs into tensor memory (tcgen05.st) -> then
 //                       fold the finished OT_{j-1} into the register accumulator:
 //                       o = (o + OT_{j-1}) * exp2(m_{j-1} - m_j).  Two warps per scheduler hide each other's
 //                       TMEM / MUFU latencies; the first version (one thread per row) ran at 3 350 cycles per tile.
 //
 // The P V product is computed fresh per tile and accumulated in registers, so no thread ever rescales
-// TMEM and no correction pass exists. TMEM: 2 x 64 (S) + 2 x 128 (OT) = 384 of 512 columns.
+// TMEM and no correction pass exists. TMEM: 2 x 64 (S) + 2 x 128 (OT) + 64 (Q) + 2 x 32 (P) = 512 columns;
+// shared memory only holds the K / V ring. Measured per tile (tools/attn_trace.py): ~750 ns of MMA issue
+// (the 12 MMAs retire at about N + 24 cycles each) beside ~770 ns of softmax + fold, partly serialised:
+// ~980 ns per 128 x 64 tile.
 //
 // Replaces the mma.sync prefill kernel of kb_attn.cu for head_dim 128 (that one stays for head_dim 64 and
 // as the A/B reference: KB_ATTN_PREFILL_LEGACY=1). Reference counterpart: none (src/llm/portkey.py:379).
@@ -33,13 +36,11 @@ namespace {
 constexpr int TC_ROWS = 128;      // query rows per CTA = TMEM lanes
 constexpr int TC_NT = 64;         // tokens per K/V tile = one KV block
 constexpr int TC_HD = 128;
-constexpr int TC_STAGES = 3;
+constexpr int TC_STAGES = 4;
 constexpr int TC_TILE_BYTES = TC_NT * TC_HD * 2;          // 16 KB (K or V)
-constexpr int TC_Q_BYTES = TC_ROWS * TC_HD * 2;           // 32 KB: [plane][128 rows][128 B]
-constexpr int TC_P_BYTES = TC_ROWS * TC_NT * 2;           // 16 KB: [128 rows][128 B]
 constexpr int TC_THREADS = 320;     // 8 softmax warps + MMA warp + producer warp
 constexpr int TC_SOFTMAX_THREADS = 256;
-constexpr int TC_SMEM = 1024 + TC_Q_BYTES + 2 * TC_P_BYTES + TC_STAGES * 2 * TC_TILE_BYTES + 256 + 2 * 2 * TC_ROWS * 4;
+constexpr int TC_SMEM = 1024 + TC_STAGES * 2 * TC_TILE_BYTES + 256 + 2 * 2 * TC_ROWS * 4;
 constexpr float TC_LOG2E = 1.4426950408889634f;
 
 // K-major, SWIZZLE_128B: rows of 128 bytes, 8-row groups 1024 bytes apart.
@@ -77,11 +78,50 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
     while (!mbar_try_wait(bar, parity)) __nanosleep(64);
 }
 
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (Q, P) lives in tensor memory — lane = row, one 32-bit
+// column per two consecutive K elements — so an MMA only fetches B from shared memory.
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// thread i of the warp writes N consecutive 32-bit columns of TMEM lane (base_lane + i)
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+        "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 __device__ __forceinline__ float ex2_approx(float x) {   // one MUFU.EX2; ex2(-inf) = 0
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+
+// Per-tile timestamps of CTA (0,0,0) (profiling aid: `make EXTRA=-DKB_ATTN_TRACE`, tools/attn_trace.py).
+#ifdef KB_ATTN_TRACE
+__device__ unsigned long long g_attn_trace[64 * 8];
+#define KB_ATRACE(tile, slot)                                                                          \
+    do {                                                                                               \
+        if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (tile) < 64) {                    \
+            unsigned long long t__;                                                                    \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));                                    \
+            g_attn_trace[(tile) * 8 + (slot)] = t__;                                                   \
+        }                                                                                              \
+    } while (0)
+#else
+#define KB_ATRACE(tile, slot) do { } while (0)
+#endif
 
 template <int GROUP>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -92,9 +132,7 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
     constexpr int TQ = TC_ROWS / GROUP;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* q_s = smem;                                   // [2 planes][128 rows][128 B]
-    uint8_t* p_s = q_s + TC_Q_BYTES;                       // 2 x [128 rows][128 B]
-    uint8_t* kv_s = p_s + 2 * TC_P_BYTES;                  // ring: stage x (K tile, V tile)
+    uint8_t* kv_s = smem;                                  // ring: stage x (K tile, V tile)
     uint64_t* kv_full = reinterpret_cast<uint64_t*>(kv_s + TC_STAGES * 2 * TC_TILE_BYTES);
     uint64_t* kv_empty = kv_full + TC_STAGES;
     uint64_t* s_full = kv_empty + TC_STAGES;               // [2]
@@ -143,6 +181,8 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
     const int n_tiles = active ? (kv_end + TC_NT - 1) / TC_NT : 0;
     const uint32_t s_tmem = tmem_base;                     // S[a]  at columns a * 64
     const uint32_t o_tmem = tmem_base + 128;               // OT[a] at columns 128 + a * 128
+    const uint32_t q_tmem = tmem_base + 384;               // Q as the A operand of S: 128 bf16 = 64 columns
+    const uint32_t p_tmem = tmem_base + 448;               // P[a] as the A operand of OT: 64 bf16 = 32 columns each
 
     if (warp == 9) {
         // ===== producer =====
@@ -163,7 +203,6 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
         if (lane == 0 && n_tiles > 0) {
             const uint32_t id_s = idesc_bf16(TC_NT, 0);        // S  = Q K^T : N = 64 tokens, B K-major
             const uint32_t id_o = idesc_bf16(TC_HD, 1);        // OT = P V   : N = 128 dims,  B MN-major
-            const uint32_t qa = smem_u32(q_s);
             mbar_wait(q_ready, 0);
             tc_fence_after();
             auto issue_s = [&](int j) {
@@ -171,13 +210,14 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
                 mbar_wait_relaxed(&kv_full[st], (uint32_t)((j / TC_STAGES) & 1));
                 mbar_wait_relaxed(&s_empty[a], (uint32_t)(((j >> 1) & 1) ^ 1));
                 tc_fence_after();
+                KB_ATRACE(j > 0 ? j - 1 : 0, 7);      // waits of issue_s(j) over (recorded in row j - 1)
                 const uint32_t kb = smem_u32(kv_s + st * 2 * TC_TILE_BYTES);
 #pragma unroll
                 for (int p = 0; p < 2; ++p)
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16(s_tmem + (uint32_t)(a * 64), desc_kmajor(qa + p * (TC_ROWS * 128) + k * 32),
-                                  desc_kmajor(kb + p * (TC_NT * 128) + k * 32), id_s, (uint32_t)((p | k) != 0));
+                        umma_bf16_ts(s_tmem + (uint32_t)(a * 64), q_tmem + (uint32_t)(p * 32 + k * 8),
+                                     desc_kmajor(kb + p * (TC_NT * 128) + k * 32), id_s, (uint32_t)((p | k) != 0));
                 umma_commit(&s_full[a]);
             };
             auto issue_o = [&](int j) {
@@ -186,18 +226,20 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
                 mbar_wait_relaxed(&o_empty[a], (uint32_t)(((j >> 1) & 1) ^ 1));
                 tc_fence_after();
                 const uint32_t vb = smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES);
-                const uint32_t pa = smem_u32(p_s + a * TC_P_BYTES);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)       // 16 tokens per step: two 8-row groups of the V tile
-                    umma_bf16(o_tmem + (uint32_t)(a * 128), desc_kmajor(pa + k * 32),
-                              desc_mnmajor(vb + k * 2048, TC_NT * 128, 1024), id_o, (uint32_t)(k != 0));
+                    umma_bf16_ts(o_tmem + (uint32_t)(a * 128), p_tmem + (uint32_t)(a * 32 + k * 8),
+                                 desc_mnmajor(vb + k * 2048, TC_NT * 128, 1024), id_o, (uint32_t)(k != 0));
                 umma_commit(&o_full[a]);
                 umma_commit(&kv_empty[st]);       // K_j and V_j are both consumed
             };
             issue_s(0);
             for (int j = 0; j < n_tiles; ++j) {
+                KB_ATRACE(j, 0);                      // MMA thread: iteration j begins
                 if (j + 1 < n_tiles) issue_s(j + 1);
+                KB_ATRACE(j, 1);                      // S_{j+1} issued
                 issue_o(j);
+                KB_ATRACE(j, 2);                      // OT_j issued
             }
         }
     } else {
@@ -208,16 +250,22 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
         const int head = kvh * GROUP + r % GROUP;
         const bool valid = active && tl < n_new;
         const int lim = valid ? ctx + tl + 1 : kv_end;     // exclusive key limit of this row
-        // this thread's plane of the Q row -> shared memory, swizzled K-major
+        // this thread's 64 dims of the Q row -> tensor memory (A operand of S = Q K^T)
         if (active) {
             const uint4* src = reinterpret_cast<const uint4*>(q + (size_t)(tok_begin + min(tl, n_new - 1)) * q_stride +
                                                               (size_t)head * TC_HD) + half * 8;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const uint4 v = valid ? src[c] : make_uint4(0u, 0u, 0u, 0u);
-                *reinterpret_cast<uint4*>(q_s + half * (TC_ROWS * 128) + r * 128 + ((c ^ (r & 7)) << 4)) = v;
+            for (int c = 0; c < 2; ++c) {
+                uint32_t w[16];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint4 v = valid ? src[4 * c + i] : make_uint4(0u, 0u, 0u, 0u);
+                    w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+                }
+                tmem_st_32x16(q_tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32 + c * 16), w);
             }
-            fence_proxy_async();
+            tmem_st_wait();
+            tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(q_ready);
         }
@@ -231,8 +279,10 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
         for (int j = 0; j < n_tiles; ++j) {
             const int a = j & 1;
             // ---- softmax of tile j: this thread's 32 columns ----
+            if (threadIdx.x == 0) KB_ATRACE(j, 3);     // softmax: iteration j begins (waits for S_j)
             mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
             tc_fence_after();
+            if (threadIdx.x == 0) KB_ATRACE(j, 4);     // S_j ready
             uint32_t u[32];
             float s[32];
             tmem_ld_32x32(s_tmem + lane_off + (uint32_t)(a * 64 + half * 32), u);
@@ -268,32 +318,30 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
             const float corr = ex2_approx(m - m_new);       // m = -inf on the first tile -> 0
             m = m_new;
             float sum = 0.f;
-            uint8_t* prow = p_s + a * TC_P_BYTES + r * 128;
+            uint32_t pw[16];                               // this thread's 32 probabilities, bf16 pairs
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                float pv[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    pv[i] = ex2_approx(fmaf(s[8 * c + i], sc, -m_new));
-                    sum += pv[i];
-                }
-                uint4 w;
-                w.x = pack_bf16(pv[0], pv[1]);
-                w.y = pack_bf16(pv[2], pv[3]);
-                w.z = pack_bf16(pv[4], pv[5]);
-                w.w = pack_bf16(pv[6], pv[7]);
-                *reinterpret_cast<uint4*>(prow + (((half * 4 + c) ^ (r & 7)) << 4)) = w;
+            for (int i = 0; i < 16; ++i) {
+                const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
+                const float p1 = ex2_approx(fmaf(s[2 * i + 1], sc, -m_new));
+                sum += p0 + p1;
+                pw[i] = pack_bf16(p0, p1);
             }
             l = l * corr + sum;
-            fence_proxy_async();
+            // P_j -> tensor memory (A operand of OT_j = P_j V_j); OT_{j-2}, the last reader of this buffer, was
+            // folded one iteration ago
+            tmem_st_32x16(p_tmem + lane_off + (uint32_t)(a * 32 + half * 16), pw);
+            tmem_st_wait();
+            tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[a]);
+            if (threadIdx.x == 0) KB_ATRACE(j, 5);     // P_j written
 
             // ---- fold the finished product of tile j - 1:  o = (o + OT_{j-1}) * corr ----
             if (j > 0) {
                 const int b = (j - 1) & 1;
                 mbar_wait(&o_full[b], (uint32_t)(((j - 1) >> 1) & 1));
                 tc_fence_after();
+                if (threadIdx.x == 0) KB_ATRACE(j, 6); // OT_{j-1} ready
                 const bool rescale = __any_sync(0xffffffffu, corr != 1.f);   // rare after the first tiles
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
@@ -394,3 +442,9 @@ int attn_prefill_tc(const void* q, int q_stride, const void* kp, const void* vp,
 }
 
 }  // namespace kb
+
+#ifdef KB_ATTN_TRACE
+extern "C" int kb_debug_attn_trace(unsigned long long* host_out512) {
+    return cudaMemcpyFromSymbol(host_out512, kb::g_attn_trace, sizeof(unsigned long long) * 512) == cudaSuccess ? 0 : 1;
+}
+#endif
