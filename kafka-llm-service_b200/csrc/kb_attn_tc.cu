@@ -211,13 +211,15 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
                 mbar_wait_relaxed(&s_empty[a], (uint32_t)(((j >> 1) & 1) ^ 1));
                 tc_fence_after();
                 KB_ATRACE(j > 0 ? j - 1 : 0, 7);      // waits of issue_s(j) over (recorded in row j - 1)
-                const uint32_t kb = smem_u32(kv_s + st * 2 * TC_TILE_BYTES);
+                // one descriptor per tile; the 8 k-steps differ by constant offsets (16-byte units)
+                const uint64_t kdesc = desc_kmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES));
+                const uint32_t d = s_tmem + (uint32_t)(a * 64);
 #pragma unroll
                 for (int p = 0; p < 2; ++p)
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16_ts(s_tmem + (uint32_t)(a * 64), q_tmem + (uint32_t)(p * 32 + k * 8),
-                                     desc_kmajor(kb + p * (TC_NT * 128) + k * 32), id_s, (uint32_t)((p | k) != 0));
+                        umma_bf16_ts(d, q_tmem + (uint32_t)(p * 32 + k * 8),
+                                     kdesc + (uint64_t)((p * (TC_NT * 128) + k * 32) >> 4), id_s, (uint32_t)((p | k) != 0));
                 umma_commit(&s_full[a]);
             };
             auto issue_o = [&](int j) {
@@ -225,11 +227,12 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
                 mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));
                 mbar_wait_relaxed(&o_empty[a], (uint32_t)(((j >> 1) & 1) ^ 1));
                 tc_fence_after();
-                const uint32_t vb = smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES);
+                const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES), TC_NT * 128, 1024);
+                const uint32_t d = o_tmem + (uint32_t)(a * 128);
+                const uint32_t pa = p_tmem + (uint32_t)(a * 32);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)       // 16 tokens per step: two 8-row groups of the V tile
-                    umma_bf16_ts(o_tmem + (uint32_t)(a * 128), p_tmem + (uint32_t)(a * 32 + k * 8),
-                                 desc_mnmajor(vb + k * 2048, TC_NT * 128, 1024), id_o, (uint32_t)(k != 0));
+                    umma_bf16_ts(d, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o, (uint32_t)(k != 0));
                 umma_commit(&o_full[a]);
                 umma_commit(&kv_empty[st]);       // K_j and V_j are both consumed
             };
