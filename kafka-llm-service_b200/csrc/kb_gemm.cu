@@ -1061,7 +1061,10 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     if (skinny_off < 0) skinny_off = getenv("KB_GEMM_NO_SKINNY") != nullptr;
     // measured in the decode step (bench.py --threads 32 / 64 / 128, with and without KB_GEMM_NO_SKINNY):
     // the small-M kernel wins up to 32 tokens (6.1 vs 6.6 ms per step), ties at 64, loses at 128
-    if ((tile_n >= 1 && tile_n <= 4) || (tile_n == 0 && M <= 32 && !skinny_off)) {
+    // ... and between 33 and 64 tokens it still wins where the weight matrix is large in N or K (gate/up, down,
+    // lm_head: many tiles or a long K to split), and loses on the square QKV / O projections
+    const bool skinny_mid = M <= 64 && (N >= 16384 || K >= 8192);
+    if ((tile_n >= 1 && tile_n <= 4) || (tile_n == 0 && (M <= 32 || skinny_mid) && !skinny_off)) {
         KB_CHECK(M <= GEMM_BM, "kb_gemm: the small-M kernel takes at most %d rows (got %d)", GEMM_BM, M);
         // tile_n = 0: CTAs per tile chosen by skinny_plan; 1 / 2 / 4: forced (benchmarks, tests)
         return dispatch_skinny(a, w, out, resid, M, N, K, epi, tile_n, a_is_bf16, stream);
