@@ -46,45 +46,67 @@ rmsnorm_kernel(float* __restrict__ x, const __nv_bfloat16* __restrict__ w, uint1
     float4* xr = reinterpret_cast<float4*>(x + (size_t)row * hidden);
     const int n4 = hidden / 4;
     __shared__ float red[8];
+    // the row stays in registers between the two passes (hidden <= 8192: 8 float4 per thread); wider rows
+    // are re-read from L2
+    constexpr int KEEP = 8;
+    const bool keep = n4 <= KEEP * 256;
+    float4 v[KEEP];
     float ss = 0.f;
-    if (delta != nullptr) {
-        // tensor parallel, fp16 wire: the reduced projection output has not been added to the residual
-        // stream yet — do it here (x += delta, written back) instead of in a kernel of its own
-        const uint2* dr = reinterpret_cast<const uint2*>(delta + (size_t)row * hidden);
-        for (int j = threadIdx.x; j < n4; j += blockDim.x) {
-            float4 v = xr[j];
+    const uint2* dr = delta ? reinterpret_cast<const uint2*>(delta + (size_t)row * hidden) : nullptr;
+#pragma unroll
+    for (int k = 0; k < KEEP; ++k) {
+        const int j = threadIdx.x + k * 256;
+        if (j < n4) {
+            float4 t = xr[j];
+            if (dr != nullptr) {
+                // tensor parallel, fp16 wire: the reduced projection output has not been added to the residual
+                // stream yet — do it here (x += delta, written back) instead of in a kernel of its own
+                const uint2 d = dr[j];
+                const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&d.x));
+                const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&d.y));
+                t.x += d0.x; t.y += d0.y; t.z += d1.x; t.w += d1.y;
+                xr[j] = t;
+            }
+            v[k] = t;
+            ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
+        }
+    }
+    for (int j = threadIdx.x + KEEP * 256; j < n4; j += 256) {     // hidden > 8192 only
+        float4 t = xr[j];
+        if (dr != nullptr) {
             const uint2 d = dr[j];
             const float2 d0 = __half22float2(*reinterpret_cast<const __half2*>(&d.x));
             const float2 d1 = __half22float2(*reinterpret_cast<const __half2*>(&d.y));
-            v.x += d0.x; v.y += d0.y; v.z += d1.x; v.w += d1.y;
-            xr[j] = v;   // re-read below by the same thread
-            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+            t.x += d0.x; t.y += d0.y; t.z += d1.x; t.w += d1.y;
+            xr[j] = t;
         }
-    } else {
-        for (int j = threadIdx.x; j < n4; j += blockDim.x) {
-            const float4 v = xr[j];
-            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-        }
+        ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
     }
     ss = warp_sum(ss);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
     __syncthreads();
     float tot = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) tot += (k < (int)(blockDim.x >> 5)) ? red[k] : 0.f;
+    for (int k = 0; k < 8; ++k) tot += red[k];
     const float inv = rsqrtf(tot / (float)hidden + eps);
     const uint2* wr = reinterpret_cast<const uint2*>(w);
     uint2* yr = reinterpret_cast<uint2*>(y + (size_t)i * hidden);
-    for (int j = threadIdx.x; j < n4; j += blockDim.x) {
-        const float4 v = xr[j];
+    auto emit = [&](int j, const float4& t) {
         const uint2 wv = wr[j];
         const float2 w0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv.x));
         const float2 w1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv.y));
         uint2 o;
-        o.x = pack_act(v.x * inv * w0.x, v.y * inv * w0.y, out_f16);
-        o.y = pack_act(v.z * inv * w1.x, v.w * inv * w1.y, out_f16);
+        o.x = pack_act(t.x * inv * w0.x, t.y * inv * w0.y, out_f16);
+        o.y = pack_act(t.z * inv * w1.x, t.w * inv * w1.y, out_f16);
         yr[j] = o;
+    };
+#pragma unroll
+    for (int k = 0; k < KEEP; ++k) {
+        const int j = threadIdx.x + k * 256;
+        if (j < n4) emit(j, v[k]);
     }
+    if (!keep)
+        for (int j = threadIdx.x + KEEP * 256; j < n4; j += 256) emit(j, xr[j]);
 }
 
 // ---------------------------------------------------------------------------------------------
