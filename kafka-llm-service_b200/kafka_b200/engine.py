@@ -17,13 +17,25 @@ reference has no engine, queue or batching of its own.
 """
 from __future__ import annotations
 
+import gc
 import itertools
+import os
 import queue
 import threading
 import time
 from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 from .scheduler import ContextLengthError, PrefillItem, Request, SamplingParams, Scheduler, shard_of
+
+
+def tune_gc() -> None:
+    """The serving loop allocates a few thousand small containers per step (plans, events, chunks) next to
+    millions of long-lived ones (the token lists of resident conversations): with CPython's default
+    thresholds (700, 10, 10) the cyclic collector walks that heap several times per second, which cost
+    ~40 % of the host time of a 512-thread turn (tools/host_profile.py). Collect 70x less often; nothing on
+    this path builds reference cycles at a rate that matters. KB_GC_DEFAULT=1 leaves the interpreter alone."""
+    if os.environ.get("KB_GC_DEFAULT") != "1" and gc.get_threshold()[0] < 50_000:
+        gc.set_threshold(50_000, 20, 20)
 
 
 class Stepper:
@@ -82,6 +94,7 @@ class Engine:
 
     def __init__(self, stepper: Stepper, max_prefill_tokens: Optional[int] = None, name: str = "kb-engine",
                  pipeline: bool = True):
+        tune_gc()
         self.stepper = stepper
         self.pipeline = pipeline   # False: read every step back before enqueueing the next (for A/B timing)
         self.sched = Scheduler(n_blocks=stepper.n_blocks, max_pos=stepper.max_pos, eos_id=stepper.eos_id,

@@ -125,11 +125,14 @@ class PrefixIndex:
         self.by_hint: Dict[str, KVEntry] = {}
         self.entries: Dict[int, KVEntry] = {}
 
-    def add(self, e: KVEntry) -> None:
+    def add(self, e: KVEntry, known: Optional[List[int]] = None, n_known: int = 0) -> None:
+        """`known`: chain of a sequence that agrees with e.tokens on its first n_known tokens (the prompt's
+        chain, already computed at admission) — only the blocks after that are hashed."""
         self.entries[e.entry_id] = e
         if e.thread_hint:
             self.by_hint[e.thread_hint] = e
-        e.chain = _chain_hashes(e.tokens)
+        start = min(len(known), n_known // BLOCK_TOKENS, len(e.tokens) // BLOCK_TOKENS) if known else 0
+        e.chain = _chain_hashes(e.tokens, known, start)
         for h in e.chain:
             self.by_hash.setdefault(h, {})[e.entry_id] = e
 
@@ -154,6 +157,15 @@ class PrefixIndex:
         while i < n and a[i] == b[i]:
             i += 1
         return i
+
+    def chain_of(self, prompt: Sequence[int], thread_hint: Optional[str]) -> List[int]:
+        """The prompt's chain. A follow-up turn of a resident thread re-sends its whole conversation: the
+        blocks it has in common with the thread's entry are taken from that entry's chain, not hashed again."""
+        e = self.by_hint.get(thread_hint) if thread_hint else None
+        if e is None or not e.chain:
+            return _chain_hashes(prompt)
+        n = self._lcp(e.tokens, prompt)
+        return _chain_hashes(prompt, e.chain, min(len(e.chain), n // BLOCK_TOKENS))
 
     def donor(self, chain: Sequence[int], exclude: Optional[KVEntry] = None) -> Tuple[Optional[KVEntry], int]:
         """Entry (idle OR busy) whose leading full blocks equal the prompt's, and how many. Those blocks
@@ -222,6 +234,7 @@ class Request:
     generated: List[int] = field(default_factory=list)
     cancelled: bool = False
     done: bool = False                     # finished or released: results still in flight are dropped
+    chain: Optional[List[int]] = None      # block chain hashes of `prompt` (computed once, at admission)
     t_submit: float = 0.0
     t_first: Optional[float] = None
 
@@ -290,7 +303,7 @@ class Scheduler:
             if len(self.prefilling) + len(self.running) >= self.max_seqs:
                 still.append(req)
                 continue
-            chain = _chain_hashes(req.prompt)
+            chain = req.chain = self.index.chain_of(req.prompt, req.thread_hint)
             entry, lcp = self.index.lookup(req.prompt, req.thread_hint, chain)
             lcp = min(lcp, len(req.prompt) - 1)  # at least one token must run to produce logits
             donor, d_blocks = self.index.donor(chain, exclude=entry)
@@ -387,7 +400,7 @@ class Scheduler:
                 # start with the same blocks (a common system prompt) read it while this one decodes
                 if req.entry is not None:
                     req.entry.tokens = list(req.prompt)
-                    self.index.add(req.entry)
+                    self.index.add(req.entry, req.chain, len(req.prompt))
                 if not req.cancelled:
                     self._on_token(req, int(tok))
         self._reap()
@@ -452,7 +465,7 @@ class Scheduler:
         e.busy = False
         e.last_used = time.monotonic()
         if e.tokens:
-            self.index.add(e)
+            self.index.add(e, req.chain, min(req.n_prefilled, len(req.prompt)))
         else:
             self.alloc.free(e.blocks)
             e.blocks = []

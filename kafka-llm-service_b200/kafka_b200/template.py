@@ -30,11 +30,17 @@ def _field(msg: Any, key: str):
 class ChatTemplate:
     def __init__(self, tokenizer: ByteTokenizer):
         self.tok = tokenizer
+        self._headers: Dict[str, List[int]] = {}     # label -> ids (a handful of distinct labels per process)
 
     # ---- pieces ------------------------------------------------------------------------------
     def _header(self, label: str) -> List[int]:
-        t = self.tok
-        return [t.start_header_id] + t.encode(label) + [t.end_header_id] + t.encode("\n\n")
+        ids = self._headers.get(label)
+        if ids is None:
+            t = self.tok
+            ids = [t.start_header_id] + t.encode(label) + [t.end_header_id] + t.encode("\n\n")
+            if len(self._headers) < 4096:                # labels with tool_call_ids are unbounded: stop caching
+                self._headers[label] = ids
+        return ids
 
     def render_tools(self, tools: Optional[Sequence[Dict[str, Any]]]) -> List[int]:
         if not tools:
@@ -61,7 +67,11 @@ class ChatTemplate:
         tcid = _field(msg, "tool_call_id")
         if tcid:
             label += f" tool_call_id={tcid}"
-        return self._header(label) + self.tok.encode(self.message_body(msg)) + [self.tok.eot_id]
+        ids = list(self._header(label))
+        ids += self.message_body(msg).encode("utf-8") if type(self.tok) is ByteTokenizer \
+            else self.tok.encode(self.message_body(msg))
+        ids.append(self.tok.eot_id)
+        return ids
 
     def generation_prompt(self) -> List[int]:
         return self._header("assistant")

@@ -396,3 +396,30 @@ def test_cancel_with_a_step_in_flight_keeps_kv_consistent():
         assert c2.usage["cached_tokens"] >= len(p) + n - 2
     finally:
         e.shutdown()
+
+
+def test_incremental_chain_hashes_equal_a_full_rehash(engine):
+    """Chains are extended from what admission already hashed (the thread's resident entry, then the
+    prompt's own chain): after turns that continue, diverge from and share conversations, every entry's
+    chain must still be the chain of its tokens, and the index must hold exactly those hashes."""
+    from kafka_b200.scheduler import _chain_hashes
+    sys_prompt = list(range(40, 40 + 2 * BLOCK_TOKENS))
+    convs = {}
+    for turn in range(3):
+        for t in range(3):
+            hint = f"th-{t}"
+            prompt = convs.get(hint, sys_prompt + [100 + t] * (20 + 30 * t))
+            if turn == 2 and t == 1:
+                prompt = prompt[:BLOCK_TOKENS + 9] + [77] * 70          # history edited: diverges inside block 1
+            c = run(engine, prompt, n=37 + 11 * t, hint=hint)
+            assert c.tokens == expected_tokens(prompt, 37 + 11 * t, EOS)
+            convs[hint] = prompt + c.tokens + [200 + turn] * (5 + 64 * turn)
+    time.sleep(0.05)
+    idx = engine.sched.index
+    assert len(idx.entries) >= 3
+    registered = {}
+    for e in idx.entries.values():
+        assert e.chain == _chain_hashes(e.tokens), e.thread_hint
+        for h in e.chain:
+            registered.setdefault(h, set()).add(e.entry_id)
+    assert {h: set(d) for h, d in idx.by_hash.items()} == registered
