@@ -84,7 +84,7 @@ class BlockAllocator:
                 self._free.append(b)
 
 
-@dataclass
+@dataclass(eq=False)     # identity, not field-by-field: these sit in lists searched on the hot path
 class KVEntry:
     """KV of one conversation resident in HBM: `tokens[i]` is the id whose K/V sits at position i."""
     entry_id: int
@@ -218,7 +218,7 @@ class SamplingParams:
     ignore_eos: bool = False
 
 
-@dataclass
+@dataclass(eq=False)     # identity, not field-by-field: these sit in lists searched on the hot path
 class Request:
     req_id: int
     prompt: List[int]
@@ -245,7 +245,7 @@ class Request:
         return self.n_launched + max(0, len(self.generated) + self.inflight - 1)
 
 
-@dataclass
+@dataclass(eq=False)     # identity, not field-by-field: these sit in lists searched on the hot path
 class PrefillItem:
     req: Request
     tokens: List[int]
