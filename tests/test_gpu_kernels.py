@@ -399,6 +399,34 @@ def test_sample_greedy_and_masks(kb, cuda):
     assert torch.equal(out_r, want)
 
 
+@pytest.mark.parametrize("vocab", [1000, 1003, 128256])
+def test_sample_ragged_ranges_and_vector_path(kb, cuda, vocab):
+    """The aligned middle of the candidate range is scanned with 16-byte loads, its ragged ends and the extras
+    one by one: every (lo, hi) alignment must give the argmax of exactly the allowed ids, greedy and with Gumbel
+    noise (which depends on the id only, so masking logits to -inf must equal restricting the range)."""
+    g = torch.Generator(device="cpu").manual_seed(vocab)
+    n = 7
+    logits = torch.randn(n, vocab, generator=g).to(cuda)
+    assert torch.equal(kb.sample(logits), torch.argmax(logits, -1).int())
+    for lo, hi, ea, eb in [(0, vocab, -1, -1), (1, vocab - 1, -1, -1), (2, 7, 0, -1), (5, 6, -1, vocab - 1),
+                           (33, 127, 10, vocab - 2), (3, 4, -1, -1), (vocab - 9, vocab - 2, 1, 2), (4, 8, -1, -1),
+                           (6, 262, 300, 1)]:
+        ids = list(range(lo, hi)) + [e for e in (ea, eb) if e >= 0]
+        allowed = torch.tensor(ids, device=cuda)
+        want = allowed[torch.argmax(logits[:, allowed], -1)].int()
+        got = kb.sample(logits, allowed_lo=lo, allowed_hi=hi, extra_a=ea, extra_b=eb)
+        assert torch.equal(got, want), (lo, hi, ea, eb)
+        masked = torch.full_like(logits, float("-inf"))
+        masked[:, allowed] = logits[:, allowed]
+        a = kb.sample(logits, temperature=0.9, seed=3, step=2, allowed_lo=lo, allowed_hi=hi, extra_a=ea, extra_b=eb)
+        b = kb.sample(masked, temperature=0.9, seed=3, step=2)
+        assert torch.equal(a, b), (lo, hi, ea, eb)
+    banned = int(torch.argmax(logits[0]))
+    l0 = logits[0].clone()
+    l0[banned] = float("-inf")
+    assert int(kb.sample(logits, banned_token=banned)[0]) == int(torch.argmax(l0))
+
+
 def test_sample_temperature_distribution(kb, cuda):
     """Gumbel-max sampling: deterministic per (seed, step), and frequencies follow softmax(logits / T)."""
     probs = torch.tensor([0.5, 0.25, 0.125, 0.125])
