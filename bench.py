@@ -628,8 +628,10 @@ def run_b200(args, rank, world, local_rank):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "16-bit float operands (bf16 KV cache / q,k,v / attention; fp16 projection operands holding "
-                     "the bf16 weight values), fp32 accumulate and residual", "data": "synthetic",
+            "dtype": "bf16",
+            "dtype_detail": "bf16 weights, KV cache, q/k/v and attention; the projection GEMMs take the bf16 weight "
+                            "values re-encoded as fp16 and fp16 activations (10 mantissa bits instead of 7); fp32 "
+                            "accumulate and residual stream", "data": "synthetic",
             "config": {
                 "workload": f"{cfg.name} bf16 decode, {B} resident threads/GPU x {args.history}-token history + "
                             f"{U}-token turn (BASELINE configs[2], thread-sharded: 4096 threads at 8 GPUs)",
@@ -771,7 +773,8 @@ def run_tp(args, rank, world, local_rank):
     line = {
         "metric": METRIC, "value": B * K / (ms_total / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "16-bit float operands (bf16 KV / attention, fp16 projections), fp32 accumulate", "data": "synthetic",
+        "dtype": "bf16", "dtype_detail": "bf16 weights / KV / attention, fp16-encoded projection operands, fp32 accumulate",
+        "data": "synthetic",
         "config": {"workload": f"{cfg.name} tensor-parallel x{world} decode, {B} threads x {args.history}-token history "
                                f"+ {U}-token turn (BASELINE configs[4])", "model": cfg.name, "threads": B,
                    "history": args.history, "context_at_start": ctx_start, "resident_note": resident_note,
