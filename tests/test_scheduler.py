@@ -423,3 +423,24 @@ def test_incremental_chain_hashes_equal_a_full_rehash(engine):
         for h in e.chain:
             registered.setdefault(h, set()).add(e.entry_id)
     assert {h: set(d) for h, d in idx.by_hash.items()} == registered
+
+
+def test_engine_raises_gc_thresholds_unless_opted_out(monkeypatch):
+    """engine.tune_gc: the cyclic collector runs ~70x less often under a serving loop (host time of a
+    512-thread turn, tools/host_profile.py); KB_GC_DEFAULT=1 leaves the interpreter's setting alone."""
+    import gc
+    from kafka_b200 import engine as E
+    old = gc.get_threshold()
+    try:
+        gc.set_threshold(700, 10, 10)
+        monkeypatch.setenv("KB_GC_DEFAULT", "1")
+        E.tune_gc()
+        assert gc.get_threshold() == (700, 10, 10)
+        monkeypatch.delenv("KB_GC_DEFAULT")
+        E.tune_gc()
+        assert gc.get_threshold()[0] >= 50_000
+        gc.set_threshold(200_000, 5, 5)                     # a host that already tuned it higher keeps its value
+        E.tune_gc()
+        assert gc.get_threshold() == (200_000, 5, 5)
+    finally:
+        gc.set_threshold(*old)
