@@ -819,11 +819,9 @@ def main():
         return
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL is used for the barrier / max-over-ranks only; keep its version banner off stdout, which
-        # must carry exactly one JSON line
-        os.environ["NCCL_DEBUG"] = os.environ.get("KB_NCCL_DEBUG", "WARN")
-        # ...and whatever native code still prints (the NCCL version banner does) goes to stderr: fd 1 is
-        # pointed at stderr for the rest of the run and the JSON line is written to the saved descriptor
+        # NCCL is used for the barrier / max-over-ranks only. Its log level is the caller's (NCCL_DEBUG is
+        # left as exported); whatever native code prints (the NCCL banner, INFO lines) goes to stderr: fd 1
+        # is pointed at stderr for the rest of the run and the ONE JSON line is written to the saved descriptor
         global _JSON_FD
         sys.stdout.flush()
         _JSON_FD = os.dup(1)

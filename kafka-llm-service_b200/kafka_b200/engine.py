@@ -205,9 +205,10 @@ class Engine:
         sched = self.sched
         pending: Optional[_Flight] = None
         parity = 0
+        stalled = False     # requests are waiting but nothing could be launched: wait for the inbox, do not spin
         try:
             while not self._stop.is_set():
-                self._drain(block=sched.idle() and pending is None)
+                self._drain(block=(sched.idle() or stalled) and pending is None)
                 sched.admit()
                 flight = self._launch(parity)
                 if flight is not None:
@@ -215,6 +216,7 @@ class Engine:
                 if pending is not None:
                     self._retire(pending)
                 pending = flight
+                stalled = flight is None
                 if not self.pipeline and pending is not None:
                     self._retire(pending)
                     pending = None

@@ -167,16 +167,22 @@ class PrefixIndex:
         n = self._lcp(e.tokens, prompt)
         return _chain_hashes(prompt, e.chain, min(len(e.chain), n // BLOCK_TOKENS))
 
-    def donor(self, chain: Sequence[int], exclude: Optional[KVEntry] = None) -> Tuple[Optional[KVEntry], int]:
+    def donor(self, chain: Sequence[int], exclude: Optional[KVEntry] = None,
+              prompt: Optional[Sequence[int]] = None) -> Tuple[Optional[KVEntry], int]:
         """Entry (idle OR busy) whose leading full blocks equal the prompt's, and how many. Those blocks
         are immutable — a conversation only ever appends beyond what it registered — so another
-        conversation may read them (shared-prefix KV: a common system prompt is prefilled once)."""
+        conversation may read them (shared-prefix KV: a common system prompt is prefilled once).
+        A 64-bit chain hash only nominates the candidate: with `prompt` given the shared tokens themselves
+        are compared, so a hash collision can never hand one thread's context to another."""
         for k in range(len(chain) - 1, -1, -1):
             cands = self.by_hash.get(chain[k])
             if not cands:
                 continue
+            n = (k + 1) * BLOCK_TOKENS
             for e in cands.values():
                 if e is not exclude and len(e.blocks) > k:
+                    if prompt is not None and (len(e.tokens) < n or self._lcp(e.tokens, prompt[:n]) < n):
+                        continue
                     return e, k + 1
         return None, 0
 
@@ -277,6 +283,9 @@ class Scheduler:
         if len(req.prompt) + 1 > self.max_pos:
             raise ContextLengthError(len(req.prompt), self.max_pos)
         req.params.max_tokens = max(1, min(req.params.max_tokens, self.max_pos - len(req.prompt)))
+        need = (len(req.prompt) + req.params.max_tokens + BLOCK_TOKENS - 1) // BLOCK_TOKENS
+        if need > self.alloc.n_blocks:       # can never be resident, whatever gets evicted: fail now, not never
+            raise MemoryError(f"request needs {need} KV blocks but the pool has {self.alloc.n_blocks}")
         self.waiting.append(req)
         self.stats["requests"] += 1
 
@@ -306,7 +315,7 @@ class Scheduler:
             chain = req.chain = self.index.chain_of(req.prompt, req.thread_hint)
             entry, lcp = self.index.lookup(req.prompt, req.thread_hint, chain)
             lcp = min(lcp, len(req.prompt) - 1)  # at least one token must run to produce logits
-            donor, d_blocks = self.index.donor(chain, exclude=entry)
+            donor, d_blocks = self.index.donor(chain, exclude=entry, prompt=req.prompt)
             d_blocks = min(d_blocks, (len(req.prompt) - 1) // BLOCK_TOKENS)
             total = len(req.prompt) + req.params.max_tokens
             need_total = (total + BLOCK_TOKENS - 1) // BLOCK_TOKENS
@@ -326,12 +335,17 @@ class Scheduler:
                 replace = [i for i in range(lcp // BLOCK_TOKENS, len(blocks)) if self.alloc.is_shared(blocks[i])]
                 extra = max(0, need_total - len(blocks)) + len(replace)
             if not self._evict_until(extra, keep=(entry, donor)):
-                if not self.index.entries and not self.prefilling and not self.running:
-                    req.on_event(("error", MemoryError(
-                        f"request needs {need_total} KV blocks but the pool has {self.alloc.n_blocks}")))
+                if self.prefilling or self.running:
+                    still.append(req)             # blocks come back when a running conversation finishes
                     continue
-                still.append(req)
-                continue
+                # Nothing is running, so nothing will ever be freed by waiting: give up the reuse (the kept
+                # entry / donor is what stands in the way) and take the request as a new conversation.
+                entry, donor, share, lcp, replace, extra = None, None, False, 0, [], need_total
+                if not self._evict_until(extra):
+                    req.on_event(("error", MemoryError(
+                        f"request needs {need_total} KV blocks but only {self.alloc.n_free} of "
+                        f"{self.alloc.n_blocks} can be freed")))
+                    continue
             if share:
                 entry = KVEntry(entry_id=next(self._ids), thread_hint=req.thread_hint,
                                 blocks=list(donor.blocks[:d_blocks]))

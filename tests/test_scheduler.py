@@ -444,3 +444,52 @@ def test_engine_raises_gc_thresholds_unless_opted_out(monkeypatch):
         assert gc.get_threshold() == (200_000, 5, 5)
     finally:
         gc.set_threshold(*old)
+
+
+def test_request_larger_than_the_pool_fails_at_once_and_engine_does_not_spin():
+    """A follow-up of a resident thread that can never fit (8 blocks, pool of 4) must get an error event,
+    not wait forever; and while a request waits with nothing in flight the engine thread sleeps on its inbox."""
+    st = FakeStepper(n_blocks=4, max_seqs=4, max_tokens=256, max_pos=1024, eos_id=EOS)
+    e = Engine(st, max_prefill_tokens=128)
+    try:
+        first = run(e, list(range(100, 160)), n=4, hint="t")          # 1 block, stays resident
+        assert first.error is None and first.finish == "length"
+        big = run(e, list(range(100, 160)) + first.tokens + [7] * 420, n=16, hint="t")   # 8 blocks > 4
+        assert isinstance(big.error, MemoryError) and "pool has 4" in str(big.error)
+        ok = run(e, list(range(100, 160)) + first.tokens + [9] * 20, n=4, hint="t")       # engine still serves
+        assert ok.error is None and ok.tokens == expected_tokens(list(range(100, 160)) + first.tokens + [9] * 20, 4, EOS)
+        assert e.stats()["waiting"] == 0
+    finally:
+        e.shutdown()
+
+
+def test_reuse_is_given_up_when_the_kept_entry_blocks_admission():
+    """Pool of 4: an idle conversation u holds 3 blocks. A new thread that shares u's first block and needs 3
+    blocks would read that block from u (kept as donor) and then lacks one block that nobody will ever free —
+    the scheduler must drop the sharing, evict u and serve the request as a new conversation."""
+    st = FakeStepper(n_blocks=4, max_seqs=4, max_tokens=512, max_pos=1024, eos_id=EOS)
+    e = Engine(st, max_prefill_tokens=512)
+    try:
+        common = list(range(300, 364))                                # exactly one block
+        b = run(e, common + list(range(400, 500)), n=4, hint="u")     # 168 tokens -> 3 blocks
+        assert b.error is None and e.stats()["free_blocks"] == 1
+        prompt = common + [5] * 100                                   # 164 + 8 -> 3 blocks
+        c = run(e, prompt, n=8, hint="t")
+        assert c.error is None and c.tokens == expected_tokens(prompt, 8, EOS)
+        assert e.stats()["evictions"] == 1 and e.stats()["waiting"] == 0
+    finally:
+        e.shutdown()
+
+
+def test_donor_compares_tokens_not_only_the_chain_hash():
+    """Two different conversations forced onto the same chain hash (a simulated 64-bit collision): the index
+    must not offer one's blocks to the other."""
+    idx = PrefixIndex()
+    a = KVEntry(1, tokens=list(range(128)), blocks=[0, 1])
+    idx.add(a)
+    other = [7] * 128
+    forged = list(a.chain)                      # pretend `other` hashes to the same chain
+    e, n = idx.donor(forged, prompt=other)
+    assert e is None and n == 0
+    e, n = idx.donor(forged, prompt=list(range(128)) + [1, 2, 3])
+    assert e is a and n == 2
