@@ -102,10 +102,11 @@ void kb_engine_destroy(kb_engine* e);
 /* Takes over: nothing in the reference (weights live behind the gateway). Pointers are borrowed. */
 int kb_bind_weights(kb_engine* e, const kb_weight_ptrs* w);
 
-/* KV pools, layout [layer][block][kv_head][dim plane = dim / 64][token_in_block][64 dims] bf16 with the
+/* KV pools, layout [layer][block][kv_head][dim plane = dim / 64][token_in_block][64 dims] FP16 (values
+ * beyond +-65504 are stored saturated, see KB_GEMM_F16) with the
  * 16-byte chunks of each 128-byte row XOR-swizzled by (token & 7) — every plane of a (block, head) tile is
  * a canonical SWIZZLE_128B K-major matrix.  k_pool and v_pool each hold
- * n_layers * n_blocks * n_kv_heads * KB_BLOCK_TOKENS * head_dim bf16.
+ * n_layers * n_blocks * n_kv_heads * KB_BLOCK_TOKENS * head_dim fp16.
  * Takes over: the thread history the reference re-sends in full on every call
  * (src/agents/base.py:222-223) — here it stays resident in HBM. */
 int kb_bind_kv_pool(kb_engine* e, void* k_pool, void* v_pool, int32_t n_blocks);
@@ -225,7 +226,10 @@ int kb_embed(const int32_t* tokens, const void* embed_bf16, float* x, int32_t n,
  * attention output, MLP inner) in fp16 — 10 mantissa bits against bf16's 7 — because their rounding is
  * the largest error term of a bf16 pipeline, and therefore binds the projection weights
  * as fp16 re-encodings of the bf16 values (exact for |w| >= 2^-14).  q/k/v, the KV cache and the
- * attention arithmetic stay bf16; accumulation is fp32 throughout. */
+ * attention probabilities are fp16 too (round 2: at Llama-3-8B's layer geometry their bf16 rounding was the
+ * largest remaining term, 4.5e-3 relative on the attention output — profiles/r02_stage_errors.md);
+ * accumulation and the residual stream are fp32 throughout.  Every fp32 -> fp16 conversion SATURATES at
+ * +-65504 instead of producing inf. */
 #define KB_GEMM_F16 0x100
 int kb_gemm(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,
             int32_t K, int32_t epilogue, kb_stream stream);
@@ -239,15 +243,15 @@ int kb_gemm_ex(const void* a_bf16, const void* w_bf16, void* out, const float* r
                int32_t K, int32_t epilogue, int32_t tile_n, kb_stream stream);
 
 /* Rotate q and k (HF rotate-half convention), write q in place and k,v into the paged pools.
- *   qkv [n_tokens, (n_heads + 2 n_kv_heads) * head_dim] bf16;  token t of sequence s sits at position
+ *   qkv [n_tokens, (n_heads + 2 n_kv_heads) * head_dim] fp16;  token t of sequence s sits at position
  *   ctx_lens[s] + (t - cu_seqlens[s]).  k_pool_layer / v_pool_layer point at ONE layer's pool. */
-int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+int kb_rope_append(void* qkv_f16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
                    const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,
                    int32_t n_tokens, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
                    int32_t head_dim, float rope_theta, kb_stream stream);
 
 /* Paged attention, one query token per sequence, over kv_lens[s] + kv_len_bias cached tokens.
- *   q   [batch, q_stride] bf16 (first n_heads*head_dim columns are the heads);
+ *   q   [batch, q_stride] fp16 (first n_heads*head_dim columns are the heads); the pools are fp16;
  *   out [batch, n_heads*head_dim], fp16 when out_f16 != 0 (the hot path), else bf16
  *   max_kv_len : host-side bound on kv_lens[s] + kv_len_bias (0 = max_blocks * KB_BLOCK_TOKENS)
  *   scratch    : optional device buffer for split-KV partials (kb_attn_decode_scratch_bytes); NULL = no
@@ -255,8 +259,8 @@ int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx
  * The pools must hold finite values everywhere (zero-initialise them once): masked tail positions of
  * the last block are multiplied by an exact 0. */
 size_t kb_attn_decode_scratch_bytes(int32_t batch, int32_t n_heads, int32_t head_dim);
-int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
-                   const int32_t* kv_lens, int32_t kv_len_bias, const int32_t* block_tables, void* out_bf16,
+int kb_attn_decode(const void* q_f16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
+                   const int32_t* kv_lens, int32_t kv_len_bias, const int32_t* block_tables, void* out16,
                    int32_t batch, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads, int32_t head_dim,
                    int32_t max_kv_len, void* scratch, size_t scratch_bytes, int32_t out_f16, kb_stream stream);
 
@@ -278,18 +282,18 @@ int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* k_pool_laye
  *     race with each other and must be serialised by the caller. */
 #define KB_STATIC_SCRATCH_BYTES (2 * 1024 * 1024)
 size_t kb_static_scratch_capacity(void);
-int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+int kb_attn_decode_static_scratch(const void* q_f16, int32_t q_stride, const void* k_pool_layer,
                                   const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
-                                  const int32_t* block_tables, void* out_bf16, int32_t batch,
+                                  const int32_t* block_tables, void* out16, int32_t batch,
                                   int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads, int32_t head_dim,
                                   int32_t max_kv_len, int32_t out_f16, kb_stream stream);
 
 /* Paged causal attention for packed new tokens (incremental prefill): query i of sequence s attends
  * to the ctx_lens[s] cached tokens plus new tokens 0..i. K/V of the new tokens must already be
  * appended (kb_rope_append). */
-int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
+int kb_attn_prefill(const void* q_f16, int32_t q_stride, const void* k_pool_layer, const void* v_pool_layer,
                     const int32_t* cu_seqlens, const int32_t* ctx_lens, const int32_t* block_tables,
-                    void* out_bf16, int32_t n_seqs, int32_t n_tokens, int32_t max_new, int32_t max_blocks,
+                    void* out16, int32_t n_seqs, int32_t n_tokens, int32_t max_new, int32_t max_blocks,
                     int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t out_f16, kb_stream stream);
 
 /* out_tokens[s] = argmax_j (logits[s,j] / T + gumbel(seed, step, s, j)); greedy when T <= 0. */

@@ -3,7 +3,7 @@
 // Takes over the part of the remote completion (src/llm/portkey.py:379) that dominates decode:
 // every generated token re-reads the whole conversation's K and V.  In the reference the whole
 // conversation is re-sent as text on every call (src/agents/base.py:222-223); here it is
-// (ctx_len x 2 x n_kv_heads x head_dim) bf16 per layer, gathered block by block.
+// (ctx_len x 2 x n_kv_heads x head_dim) fp16 per layer, gathered block by block.
 //
 // Decode kernel (HBM-bound; algorithmic bytes = kv_len * n_kv_heads * head_dim * 2 * 2 per sequence
 // per layer):
@@ -27,16 +27,16 @@ namespace kb {
 
 constexpr float LOG2E = 1.4426950408889634f;
 
-// one 16-bit activation: fp16 when f16 != 0, else bf16
+// one 16-bit activation: fp16 (saturating) when f16 != 0, else bf16
 __device__ __forceinline__ uint16_t act16(float v, int f16) {
-    if (f16) return __half_as_ushort(__float2half_rn(v));
+    if (f16) return to_f16_sat(v);
     return __bfloat16_as_ushort(__float2bfloat16(v));
 }
 
 // One warp: S = Q K^T over an NT-token tile, online softmax, O += P V.
 //   o  : [HD/8][4] accumulators (m16n8 C layout; [0],[1] = row g, [2],[3] = row g+8)
 //   qa : [HD/16][4] Q A-fragments (pre-loaded)
-//   ks, vs : shared addresses of the swizzled K / V tiles ([token][HD] bf16)
+//   ks, vs : shared addresses of the swizzled K / V tiles ([token][HD] fp16)
 //   tok0 : absolute position of the tile's first token; lim0/lim1: exclusive position limit of
 //          rows g / g+8 (causal + length mask), applied only when need_mask.
 template <int HD, int NT, bool UPPER>
@@ -62,8 +62,8 @@ __device__ __forceinline__ void attn_tile(float (&o)[HD / 8][4], float (&m)[2], 
             const int c = 4 * kk2 + lmat;      // logical 16-byte chunk of the head: plane c / 8, chunk c % 8
             uint32_t b0, b1, b2, b3;
             ldsm_x4(ks + (c >> 3) * PLANE_BYTES + token * ROW_BYTES + (((c & 7) ^ lrow) << 4), b0, b1, b2, b3);
-            mma_bf16_16816(s[j], qa[2 * kk2][0], qa[2 * kk2][1], qa[2 * kk2][2], qa[2 * kk2][3], b0, b1);
-            mma_bf16_16816(s[j], qa[2 * kk2 + 1][0], qa[2 * kk2 + 1][1], qa[2 * kk2 + 1][2], qa[2 * kk2 + 1][3], b2,
+            mma_f16_16816(s[j], qa[2 * kk2][0], qa[2 * kk2][1], qa[2 * kk2][2], qa[2 * kk2][3], b0, b1);
+            mma_f16_16816(s[j], qa[2 * kk2 + 1][0], qa[2 * kk2 + 1][1], qa[2 * kk2 + 1][2], qa[2 * kk2 + 1][3], b2,
                            b3);
         }
     }
@@ -130,18 +130,18 @@ __device__ __forceinline__ void attn_tile(float (&o)[HD / 8][4], float (&m)[2], 
     // O += P V
 #pragma unroll
     for (int kk = 0; kk < NT / 16; ++kk) {
-        const uint32_t a0 = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
-        const uint32_t a1 = UPPER ? pack_bf16(s[2 * kk][2], s[2 * kk][3]) : 0u;
-        const uint32_t a2 = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
-        const uint32_t a3 = UPPER ? pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]) : 0u;
+        const uint32_t a0 = pack_f16(s[2 * kk][0], s[2 * kk][1]);          // P <= 1: fp16, 10 mantissa bits
+        const uint32_t a1 = UPPER ? pack_f16(s[2 * kk][2], s[2 * kk][3]) : 0u;
+        const uint32_t a2 = pack_f16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+        const uint32_t a3 = UPPER ? pack_f16(s[2 * kk + 1][2], s[2 * kk + 1][3]) : 0u;
 #pragma unroll
         for (int d2 = 0; d2 < HD / 16; ++d2) {
             const int token = 16 * kk + (lmat & 1) * 8 + lrow;
             const int c = 2 * d2 + (lmat >> 1);
             uint32_t b0, b1, b2, b3;
             ldsm_x4_t(vs + (c >> 3) * PLANE_BYTES + token * ROW_BYTES + (((c & 7) ^ lrow) << 4), b0, b1, b2, b3);
-            mma_bf16_16816(o[2 * d2], a0, a1, a2, a3, b0, b1);
-            mma_bf16_16816(o[2 * d2 + 1], a0, a1, a2, a3, b2, b3);
+            mma_f16_16816(o[2 * d2], a0, a1, a2, a3, b0, b1);
+            mma_f16_16816(o[2 * d2 + 1], a0, a1, a2, a3, b2, b3);
         }
     }
 }
@@ -162,8 +162,8 @@ struct DecodeCfg {
 
 template <int HD, int GROUP>
 __global__ void __launch_bounds__(DecodeCfg<HD>::WARPS * 32)
-attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
-                   const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ kv_lens, int kv_len_bias,
+attn_decode_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
+                   const __half* __restrict__ vpool, const int* __restrict__ kv_lens, int kv_len_bias,
                    const int* __restrict__ block_tables, uint16_t* __restrict__ out, float* __restrict__ part_o,
                    float* __restrict__ part_ml, int max_blocks, int n_heads, int n_kv_heads, int n_splits,
                    int halves_per_split, int out_f16) {
@@ -196,7 +196,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv
     // Q fragments: rows g < GROUP are the query heads of this KV head; the rest are zero.
     uint32_t qa[HD / 16][4];
     {
-        const __nv_bfloat16* qp = q + (size_t)seq * q_stride + (size_t)(kvh * GROUP + g) * HD;
+        const __half* qp = q + (size_t)seq * q_stride + (size_t)(kvh * GROUP + g) * HD;
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
             qa[kk][1] = 0u;
@@ -347,8 +347,8 @@ struct PrefillCfg {
 
 template <int HD, int GROUP>
 __global__ void __launch_bounds__(PrefillCfg<HD>::THREADS, 1)
-attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
-                    const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+attn_prefill_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
+                    const __half* __restrict__ vpool, const int* __restrict__ cu_seqlens,
                     const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
                     uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
     using Cfg = PrefillCfg<HD>;
@@ -412,8 +412,8 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __n
 
     uint32_t qa[HD / 16][4];
     {
-        const __nv_bfloat16* qp0 = q + (size_t)(tok_begin + tl0) * q_stride + (size_t)hd0 * HD;
-        const __nv_bfloat16* qp1 = q + (size_t)(tok_begin + tl1) * q_stride + (size_t)hd1 * HD;
+        const __half* qp0 = q + (size_t)(tok_begin + tl0) * q_stride + (size_t)hd0 * HD;
+        const __half* qp1 = q + (size_t)(tok_begin + tl1) * q_stride + (size_t)hd1 * HD;
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk) {
             qa[kk][0] = v0 ? *reinterpret_cast<const uint32_t*>(qp0 + 16 * kk + 2 * t) : 0u;
@@ -481,7 +481,7 @@ static int launch_decode(const void* q, int q_stride, const void* kp, const void
         configured[dev & 63] = true;
     }
     dim3 grid(n_kv_heads, batch, n_splits);
-    KB_CUDA(launch_kernel(kern, grid, dim3(Cfg::WARPS * 32), Cfg::SMEM_BYTES, stream, (const __nv_bfloat16*)q, q_stride, (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, kv_lens, bias, bt,
+    KB_CUDA(launch_kernel(kern, grid, dim3(Cfg::WARPS * 32), Cfg::SMEM_BYTES, stream, (const __half*)q, q_stride, (const __half*)kp, (const __half*)vp, kv_lens, bias, bt,
         (uint16_t*)out, part_o, part_ml, max_blocks, n_heads, n_kv_heads, n_splits, halves_per_split, out_f16));
     count_launch();
     KB_LAUNCH_CHECK();
@@ -561,8 +561,8 @@ static int launch_prefill(const void* q, int q_stride, const void* kp, const voi
     }
     constexpr int TQ = Cfg::ROWS / GROUP;
     dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
-    KB_CUDA(launch_kernel(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, (const __nv_bfloat16*)q, q_stride,
-                                                          (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, cu, ctx,
+    KB_CUDA(launch_kernel(kern, grid, dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, (const __half*)q, q_stride,
+                                                          (const __half*)kp, (const __half*)vp, cu, ctx,
                                                           bt, (uint16_t*)out, max_blocks, n_heads, n_kv_heads,
                                                           out_f16));
     count_launch();
@@ -606,22 +606,22 @@ extern "C" size_t kb_attn_decode_scratch_bytes(int32_t batch, int32_t n_heads, i
     return kb::attn_decode_scratch_bytes(batch, n_heads, head_dim, KB_MAX_SPLITS);
 }
 
-extern "C" int kb_attn_decode(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+extern "C" int kb_attn_decode(const void* q_f16, int32_t q_stride, const void* k_pool_layer,
                               const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
-                              const int32_t* block_tables, void* out_bf16, int32_t batch, int32_t max_blocks,
+                              const int32_t* block_tables, void* out16, int32_t batch, int32_t max_blocks,
                               int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t max_kv_len,
                               void* scratch, size_t scratch_bytes, int32_t out_f16, kb_stream stream) {
-    return kb::attn_decode(q_bf16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out_bf16,
+    return kb::attn_decode(q_f16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out16,
                            batch, max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, scratch, scratch_bytes,
                            out_f16, reinterpret_cast<cudaStream_t>(stream));
 }
 
-extern "C" int kb_attn_prefill(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+extern "C" int kb_attn_prefill(const void* q_f16, int32_t q_stride, const void* k_pool_layer,
                                const void* v_pool_layer, const int32_t* cu_seqlens, const int32_t* ctx_lens,
-                               const int32_t* block_tables, void* out_bf16, int32_t n_seqs, int32_t n_tokens,
+                               const int32_t* block_tables, void* out16, int32_t n_seqs, int32_t n_tokens,
                                int32_t max_new, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
                                int32_t head_dim, int32_t out_f16, kb_stream stream) {
-    return kb::attn_prefill(q_bf16, q_stride, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tables, out_bf16,
+    return kb::attn_prefill(q_f16, q_stride, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tables, out16,
                             n_seqs, n_tokens, max_new, max_blocks, n_heads, n_kv_heads, head_dim, out_f16,
                             reinterpret_cast<cudaStream_t>(stream));
 }
@@ -682,9 +682,9 @@ static int static_scratch_for_current_device(void** out) {
 
 extern "C" size_t kb_static_scratch_capacity(void) { return (size_t)KB_STATIC_SCRATCH_BYTES; }
 
-extern "C" int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_stride, const void* k_pool_layer,
+extern "C" int kb_attn_decode_static_scratch(const void* q_f16, int32_t q_stride, const void* k_pool_layer,
                                              const void* v_pool_layer, const int32_t* kv_lens, int32_t kv_len_bias,
-                                             const int32_t* block_tables, void* out_bf16, int32_t batch,
+                                             const int32_t* block_tables, void* out16, int32_t batch,
                                              int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
                                              int32_t head_dim, int32_t max_kv_len, int32_t out_f16,
                                              kb_stream stream) {
@@ -707,7 +707,7 @@ extern "C" int kb_attn_decode_static_scratch(const void* q_bf16, int32_t q_strid
                   batch, n_heads, head_dim, n_splits, need, (int)KB_STATIC_SCRATCH_BYTES);
         return KB_ERR_INVALID;
     }
-    return attn_decode(q_bf16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out_bf16,
+    return attn_decode(q_f16, q_stride, k_pool_layer, v_pool_layer, kv_lens, kv_len_bias, block_tables, out16,
                        batch, max_blocks, n_heads, n_kv_heads, head_dim, max_kv_len, scratch,
                        (size_t)KB_STATIC_SCRATCH_BYTES, out_f16, reinterpret_cast<cudaStream_t>(stream));
 }

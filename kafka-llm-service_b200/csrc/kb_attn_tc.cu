@@ -14,7 +14,7 @@
 //   warps 0-7 (softmax): TWO threads per query row (warp w and w + 4 share the TMEM lanes of quarter w & 3):
 //                       each takes 32 of the 64 S columns and 64 of the 128 output dims; tcgen05.ld S_j ->
 //                       causal mask, row max (the two halves meet through shared memory), running sum in fp32,
-//                       P_j = exp2((S_j - m_j) * scale) as bf16 pairs into tensor memory (tcgen05.st) -> then
+//                       P_j = exp2((S_j - m_j) * scale) as fp16 pairs into tensor memory (tcgen05.st) -> then
 //                       fold the finished OT_{j-1} into the register accumulator:
 //                       o = (o + OT_{j-1}) * exp2(m_{j-1} - m_j).  Two warps per scheduler hide each other's
 //                       TMEM / MUFU latencies; the first version (one thread per row) ran at 3 350 cycles per tile.
@@ -65,10 +65,9 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t saddr, uint32_t lbo, u
     d |= (uint64_t)2 << 61;
     return d;
 }
-// bf16 x bf16 -> fp32, M = 128; b_mn: B operand is MN-major.
-__device__ __forceinline__ uint32_t idesc_bf16(int n, int b_mn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) |
-           ((uint32_t)(TC_ROWS >> 4) << 24);
+// fp16 x fp16 -> fp32 (A and B format fields 0 = fp16), M = 128; b_mn: B operand is MN-major.
+__device__ __forceinline__ uint32_t idesc_f16(int n, int b_mn) {
+    return (1u << 4) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(TC_ROWS >> 4) << 24);
 }
 
 // The MMA and producer warps wait with one thread each; a tight try_wait loop in those warps competes for
@@ -80,7 +79,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
 
 // D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (Q, P) lives in tensor memory — lane = row, one 32-bit
 // column per two consecutive K elements — so an MMA only fetches B from shared memory.
-__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
                                              uint32_t accumulate) {
     asm volatile(
         "{\n"
@@ -125,8 +124,8 @@ __device__ unsigned long long g_attn_trace[64 * 8];
 
 template <int GROUP>
 __global__ void __launch_bounds__(TC_THREADS, 1)
-attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const __nv_bfloat16* __restrict__ kpool,
-                       const __nv_bfloat16* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
+                       const __half* __restrict__ vpool, const int* __restrict__ cu_seqlens,
                        const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
                        uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
     constexpr int TQ = TC_ROWS / GROUP;
@@ -181,8 +180,8 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
     const int n_tiles = active ? (kv_end + TC_NT - 1) / TC_NT : 0;
     const uint32_t s_tmem = tmem_base;                     // S[a]  at columns a * 64
     const uint32_t o_tmem = tmem_base + 128;               // OT[a] at columns 128 + a * 128
-    const uint32_t q_tmem = tmem_base + 384;               // Q as the A operand of S: 128 bf16 = 64 columns
-    const uint32_t p_tmem = tmem_base + 448;               // P[a] as the A operand of OT: 64 bf16 = 32 columns each
+    const uint32_t q_tmem = tmem_base + 384;               // Q as the A operand of S: 128 fp16 = 64 columns
+    const uint32_t p_tmem = tmem_base + 448;               // P[a] as the A operand of OT: 64 fp16 = 32 columns each
 
     if (warp == 9) {
         // ===== producer =====
@@ -201,8 +200,8 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
     } else if (warp == 8) {
         // ===== MMA issuer =====
         if (lane == 0 && n_tiles > 0) {
-            const uint32_t id_s = idesc_bf16(TC_NT, 0);        // S  = Q K^T : N = 64 tokens, B K-major
-            const uint32_t id_o = idesc_bf16(TC_HD, 1);        // OT = P V   : N = 128 dims,  B MN-major
+            const uint32_t id_s = idesc_f16(TC_NT, 0);        // S  = Q K^T : N = 64 tokens, B K-major
+            const uint32_t id_o = idesc_f16(TC_HD, 1);        // OT = P V   : N = 128 dims,  B MN-major
             mbar_wait(q_ready, 0);
             tc_fence_after();
             auto issue_s = [&](int j) {
@@ -218,7 +217,7 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
                 for (int p = 0; p < 2; ++p)
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16_ts(d, q_tmem + (uint32_t)(p * 32 + k * 8),
+                        umma_f16_ts(d, q_tmem + (uint32_t)(p * 32 + k * 8),
                                      kdesc + (uint64_t)((p * (TC_NT * 128) + k * 32) >> 4), id_s, (uint32_t)((p | k) != 0));
                 umma_commit(&s_full[a]);
             };
@@ -232,7 +231,7 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
                 const uint32_t pa = p_tmem + (uint32_t)(a * 32);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)       // 16 tokens per step: two 8-row groups of the V tile
-                    umma_bf16_ts(d, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o, (uint32_t)(k != 0));
+                    umma_f16_ts(d, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o, (uint32_t)(k != 0));
                 umma_commit(&o_full[a]);
                 umma_commit(&kv_empty[st]);       // K_j and V_j are both consumed
             };
@@ -314,20 +313,20 @@ attn_prefill_tc_kernel(const __nv_bfloat16* __restrict__ q, int q_stride, const 
             xb[half * TC_ROWS + r] = mx;
             asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
             // Running max in scaled (log2) units, raised LAZILY: it only moves when the tile's max exceeds it by
-            // more than 8, so P stays below 2^8 (exact enough in bf16, sums in fp32) and most tiles need no
+            // more than 8, so P stays below 2^8 (fp16: 10 mantissa bits from 2^-14 up, sums in fp32) and most tiles need no
             // rescaling of the accumulator at all (corr == 1).
             const float tile_mx = fmaxf(mx, xb[(half ^ 1) * TC_ROWS + r]) * sc;
             const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;
             const float corr = ex2_approx(m - m_new);       // m = -inf on the first tile -> 0
             m = m_new;
             float sum = 0.f;
-            uint32_t pw[16];                               // this thread's 32 probabilities, bf16 pairs
+            uint32_t pw[16];                               // this thread's 32 probabilities, fp16 pairs
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
                 const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
                 const float p1 = ex2_approx(fmaf(s[2 * i + 1], sc, -m_new));
                 sum += p0 + p1;
-                pw[i] = pack_bf16(p0, p1);
+                pw[i] = pack_f16(p0, p1);
             }
             l = l * corr + sum;
             // P_j -> tensor memory (A operand of OT_j = P_j V_j); OT_{j-2}, the last reader of this buffer, was
@@ -419,8 +418,8 @@ int launch_tc(const void* q, int q_stride, const void* kp, const void* vp, const
     }
     constexpr int TQ = TC_ROWS / GROUP;
     dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
-    KB_CUDA(launch_kernel(kern, grid, dim3(TC_THREADS), TC_SMEM, stream, (const __nv_bfloat16*)q, q_stride,
-                          (const __nv_bfloat16*)kp, (const __nv_bfloat16*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
+    KB_CUDA(launch_kernel(kern, grid, dim3(TC_THREADS), TC_SMEM, stream, (const __half*)q, q_stride,
+                          (const __half*)kp, (const __half*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
                           n_heads, n_kv_heads, out_f16));
     count_launch();
     KB_LAUNCH_CHECK();

@@ -302,14 +302,34 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// fp16 twin: q, K, V and the probabilities P are fp16 (10 mantissa bits; see DESIGN.md §5 for the error budget
+// that moved them off bf16)
+__device__ __forceinline__ void mma_f16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                              uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+        "{%0, %1, %2, %3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// Two fp32 -> one fp16 pair, round to nearest, SATURATING: a value beyond fp16's range becomes +-65504, not
+// inf (every 16-bit activation and the KV cache are fp16 — DESIGN.md §5 — and an inf would poison the
+// attention of every later token of the conversation; NaN stays NaN).
 __device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
-    __half2 v = __floats2half2_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&v);
+    uint32_t v;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(v) : "f"(hi), "f"(lo));
+    return v;
+}
+__device__ __forceinline__ uint16_t to_f16_sat(float x) {
+    uint16_t v;
+    asm("cvt.rn.satfinite.f16.f32 %0, %1;" : "=h"(v) : "f"(x));
+    return v;
 }
 // 16-bit activation pair: fp16 when f16 != 0, else bf16
 __device__ __forceinline__ uint32_t pack_act(float lo, float hi, int f16) {

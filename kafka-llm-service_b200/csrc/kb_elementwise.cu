@@ -118,13 +118,15 @@ rmsnorm_kernel(float* __restrict__ x, const __nv_bfloat16* __restrict__ w, uint1
 //   q heads : rotated in place in qkv
 //   k heads : rotated, written to k_pool (swizzled paged layout)
 //   v heads : copied to v_pool
+// qkv, and the pools, are FP16 (the QKV GEMM's KB_EPI_F16 epilogue): q and k are rounded to 16
+// bits exactly twice (GEMM output, rotation), each time with 10 mantissa bits.
 // HF "rotate_half" convention: pairs (i, i + hd/2), angle = pos * theta^(-2i/hd), fp32 math.
 //   bytes/token = (n_heads*2 + n_kv_heads*2*2) * head_dim * 2  (read+write q, read k/v, write pools)
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-rope_append_kernel(__nv_bfloat16* __restrict__ qkv, const int* __restrict__ cu_seqlens,
+rope_append_kernel(__half* __restrict__ qkv, const int* __restrict__ cu_seqlens,
                    const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
-                   __nv_bfloat16* __restrict__ kpool, __nv_bfloat16* __restrict__ vpool, int n_seqs, int max_blocks,
+                   __half* __restrict__ kpool, __half* __restrict__ vpool, int n_seqs, int max_blocks,
                    int n_heads, int n_kv_heads, int head_dim, float log2_theta) {
     pdl_wait();
     pdl_launch();
@@ -162,7 +164,7 @@ rope_append_kernel(__nv_bfloat16* __restrict__ qkv, const int* __restrict__ cu_s
     __syncthreads();
 
     const int qkv_dim = (n_heads + 2 * n_kv_heads) * head_dim;
-    __nv_bfloat16* row = qkv + (size_t)tkn * qkv_dim;
+    __half* row = qkv + (size_t)tkn * qkv_dim;
     const int blk = pos / KB_BLOCK_TOKENS, tib = pos % KB_BLOCK_TOKENS;
     const int phys = block_tables[(size_t)seq * max_blocks + blk];
     const int cph = head_dim >> 4;  // 16-byte chunks per half head
@@ -171,37 +173,37 @@ rope_append_kernel(__nv_bfloat16* __restrict__ qkv, const int* __restrict__ cu_s
     const int n_rot = (n_heads + n_kv_heads) * cph;
     for (int it = threadIdx.x; it < n_rot; it += blockDim.x) {
         const int head = it / cph, c = it % cph;
-        __nv_bfloat16* hp = row + (size_t)head * head_dim;
+        __half* hp = row + (size_t)head * head_dim;
         uint4 lo4 = *reinterpret_cast<const uint4*>(hp + c * 8);
         uint4 hi4 = *reinterpret_cast<const uint4*>(hp + half + c * 8);
-        __nv_bfloat162* lo2 = reinterpret_cast<__nv_bfloat162*>(&lo4);
-        __nv_bfloat162* hi2 = reinterpret_cast<__nv_bfloat162*>(&hi4);
+        uint32_t* lo2 = reinterpret_cast<uint32_t*>(&lo4);
+        uint32_t* hi2 = reinterpret_cast<uint32_t*>(&hi4);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const float2 a = __bfloat1622float2(lo2[j]);
-            const float2 b = __bfloat1622float2(hi2[j]);
+            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&lo2[j]));
+            const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&hi2[j]));
             const int i0 = c * 8 + 2 * j;
             const float c0 = s_cos[i0], n0 = s_sin[i0], c1 = s_cos[i0 + 1], n1 = s_sin[i0 + 1];
-            lo2[j] = __floats2bfloat162_rn(a.x * c0 - b.x * n0, a.y * c1 - b.y * n1);
-            hi2[j] = __floats2bfloat162_rn(b.x * c0 + a.x * n0, b.y * c1 + a.y * n1);
+            lo2[j] = pack_f16(a.x * c0 - b.x * n0, a.y * c1 - b.y * n1);
+            hi2[j] = pack_f16(b.x * c0 + a.x * n0, b.y * c1 + a.y * n1);
         }
         if (head < n_heads) {
             *reinterpret_cast<uint4*>(hp + c * 8) = lo4;
             *reinterpret_cast<uint4*>(hp + half + c * 8) = hi4;
         } else {
             const int kvh = head - n_heads;
-            __nv_bfloat16* tile = kpool + ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * head_dim;
+            __half* tile = kpool + ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * head_dim;
             *reinterpret_cast<uint4*>(tile + kv_swizzled_elem(tib, c * 8, head_dim)) = lo4;
             *reinterpret_cast<uint4*>(tile + kv_swizzled_elem(tib, half + c * 8, head_dim)) = hi4;
         }
     }
     // copy v heads
     const int n_v = n_kv_heads * (head_dim >> 3);
-    const __nv_bfloat16* vsrc = row + (size_t)(n_heads + n_kv_heads) * head_dim;
+    const __half* vsrc = row + (size_t)(n_heads + n_kv_heads) * head_dim;
     for (int it = threadIdx.x; it < n_v; it += blockDim.x) {
         const int kvh = it / (head_dim >> 3), c = it % (head_dim >> 3);
         const uint4 v = *reinterpret_cast<const uint4*>(vsrc + (size_t)kvh * head_dim + c * 8);
-        __nv_bfloat16* tile = vpool + ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * head_dim;
+        __half* tile = vpool + ((size_t)phys * n_kv_heads + kvh) * KB_BLOCK_TOKENS * head_dim;
         *reinterpret_cast<uint4*>(tile + kv_swizzled_elem(tib, c * 8, head_dim)) = v;
     }
 }
@@ -359,8 +361,8 @@ int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* k
     KB_CHECK(n_tokens > 0 && n_seqs > 0, "kb_rope_append: empty batch");
     KB_CHECK(head_dim == 64 || head_dim == 128, "kb_rope_append: head_dim must be 64 or 128 (got %d)", head_dim);
     KB_CHECK(cu != nullptr || n_tokens == n_seqs, "kb_rope_append: cu_seqlens == NULL means one token per sequence");
-    KB_CUDA(launch_kernel(rope_append_kernel, dim3(n_tokens), dim3(128), 0, stream, (__nv_bfloat16*)qkv, cu, ctx, bt, (__nv_bfloat16*)kp,
-                                                      (__nv_bfloat16*)vp, n_seqs, max_blocks, n_heads, n_kv_heads,
+    KB_CUDA(launch_kernel(rope_append_kernel, dim3(n_tokens), dim3(128), 0, stream, (__half*)qkv, cu, ctx, bt, (__half*)kp,
+                                                      (__half*)vp, n_seqs, max_blocks, n_heads, n_kv_heads,
                                                       head_dim, log2f(theta)));
     count_launch();
     KB_LAUNCH_CHECK();
@@ -398,11 +400,11 @@ extern "C" int kb_rmsnorm(const float* x, const void* w_bf16, void* y, int32_t n
     return kb::rmsnorm(const_cast<float*>(x), w_bf16, y, nullptr, nullptr, n, hidden, eps, out_f16,
                        reinterpret_cast<cudaStream_t>(stream));
 }
-extern "C" int kb_rope_append(void* qkv_bf16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+extern "C" int kb_rope_append(void* qkv_f16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
                               const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,
                               int32_t n_tokens, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
                               int32_t head_dim, float rope_theta, kb_stream stream) {
-    return kb::rope_append(qkv_bf16, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_seqs, n_tokens,
+    return kb::rope_append(qkv_f16, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_seqs, n_tokens,
                            max_blocks, n_heads, n_kv_heads, head_dim, rope_theta,
                            reinterpret_cast<cudaStream_t>(stream));
 }

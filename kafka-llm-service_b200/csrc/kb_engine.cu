@@ -52,11 +52,12 @@ static inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 struct Workspace {
     float* x = nullptr;           // [T, hidden] fp32 residual stream
     float* xr = nullptr;          // [T, hidden] fp32 partial sums of a row-sharded projection (tensor parallel)
-    __nv_bfloat16* xn = nullptr;  // [T, hidden] normed activations (GEMM A operand)
-    __nv_bfloat16* qkv = nullptr; // [T, qkv_dim]
-    __nv_bfloat16* attn = nullptr;// [T, n_heads*head_dim]
-    __nv_bfloat16* h = nullptr;   // [T, ffn]
-    __nv_bfloat16* xl = nullptr;  // [S, hidden] final-normed last rows
+    // every 16-bit activation is FP16
+    __half* xn = nullptr;         // [T, hidden] normed activations (GEMM A operand)
+    __half* qkv = nullptr;        // [T, qkv_dim]
+    __half* attn = nullptr;       // [T, n_heads*head_dim]
+    __half* h = nullptr;          // [T, ffn]
+    __half* xl = nullptr;         // [S, hidden] final-normed last rows
     float* logits = nullptr;      // [S, vocab]
     void* split = nullptr;        // split-KV partials
     size_t split_bytes = 0;
@@ -73,11 +74,11 @@ static void layout_workspace(const kb_model_cfg& c, int T, int S, uint8_t* base,
     const size_t qkv_dim = (size_t)(c.n_heads + 2 * c.n_kv_heads) * c.head_dim;
     w->x = reinterpret_cast<float*>(take((size_t)T * c.hidden * 4));
     w->xr = reinterpret_cast<float*>(take((size_t)T * c.hidden * 4));
-    w->xn = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.hidden * 2));
-    w->qkv = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * qkv_dim * 2));
-    w->attn = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.n_heads * c.head_dim * 2));
-    w->h = reinterpret_cast<__nv_bfloat16*>(take((size_t)T * c.ffn * 2));
-    w->xl = reinterpret_cast<__nv_bfloat16*>(take((size_t)S * c.hidden * 2));
+    w->xn = reinterpret_cast<__half*>(take((size_t)T * c.hidden * 2));
+    w->qkv = reinterpret_cast<__half*>(take((size_t)T * qkv_dim * 2));
+    w->attn = reinterpret_cast<__half*>(take((size_t)T * c.n_heads * c.head_dim * 2));
+    w->h = reinterpret_cast<__half*>(take((size_t)T * c.ffn * 2));
+    w->xl = reinterpret_cast<__half*>(take((size_t)S * c.hidden * 2));
     w->logits = reinterpret_cast<float*>(take((size_t)S * c.vocab * 4));
     w->split_bytes = attn_decode_scratch_bytes(S, c.n_heads, c.head_dim, KB_MAX_SPLITS);
     w->split = take(w->split_bytes);
@@ -109,8 +110,8 @@ struct kb_engine {
     const void* final_norm = nullptr;
     const void* lm_head = nullptr;
     bool have_weights = false;
-    __nv_bfloat16* k_pool = nullptr;
-    __nv_bfloat16* v_pool = nullptr;
+    __half* k_pool = nullptr;     // fp16 pools
+    __half* v_pool = nullptr;
     int n_blocks = 0;
     kb::Workspace ws;
     int max_tokens = 0, max_seqs = 0;
@@ -242,15 +243,15 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     if ((rc = embed(tokens, e->embed, x, n_tokens, c.hidden, c.vocab, stream))) return rc;
     for (int L = 0; L < c.n_layers; ++L) {
         const kb_layer_weights& lw = e->layers[L];
-        __nv_bfloat16* kp = e->k_pool + (size_t)L * layer_stride;
-        __nv_bfloat16* vp = e->v_pool + (size_t)L * layer_stride;
+        __half* kp = e->k_pool + (size_t)L * layer_stride;
+        __half* vp = e->v_pool + (size_t)L * layer_stride;
         if (!fused || L == 0) {
             mark(KB_PROF_RMSNORM);
             if ((rc = rmsnorm(x, lw.attn_norm, xn, nullptr, delta, n_tokens, c.hidden, c.rms_eps, 1, stream))) return rc;
             delta = nullptr;
         }
         mark(KB_PROF_GEMM_QKV);
-        if ((rc = gemm(xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_BF16 | KB_GEMM_F16, stream)))
+        if ((rc = gemm(xn, lw.wqkv, w.qkv, nullptr, n_tokens, qkv_dim, c.hidden, KB_EPI_F16 | KB_GEMM_F16, stream)))
             return rc;
         mark(KB_PROF_ROPE_APPEND);
         if ((rc = rope_append(w.qkv, cu_seqlens, ctx_lens, block_tables, kp, vp, n_seqs, n_tokens, max_blocks,
@@ -444,8 +445,8 @@ extern "C" int kb_bind_kv_pool(kb_engine* e, void* k_pool, void* v_pool, int32_t
     KB_CHECK(e && k_pool && v_pool && n_blocks > 0, "kb_bind_kv_pool: bad arguments");
     KB_CHECK((reinterpret_cast<uintptr_t>(k_pool) & 127) == 0 && (reinterpret_cast<uintptr_t>(v_pool) & 127) == 0,
              "kb_bind_kv_pool: pools must be 128-byte aligned");
-    e->k_pool = reinterpret_cast<__nv_bfloat16*>(k_pool);
-    e->v_pool = reinterpret_cast<__nv_bfloat16*>(v_pool);
+    e->k_pool = reinterpret_cast<__half*>(k_pool);
+    e->v_pool = reinterpret_cast<__half*>(v_pool);
     e->n_blocks = n_blocks;
     return KB_OK;
 }

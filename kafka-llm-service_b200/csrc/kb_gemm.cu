@@ -579,13 +579,12 @@ __device__ __forceinline__ void skinny_store32(const float (&r)[32], void* out, 
             if (!(lane & 1) && n < N) {
                 const float h = silu_f(v) * up;
                 uint16_t* o = reinterpret_cast<uint16_t*>(out) + (size_t)token * (N >> 1) + (n >> 1);
-                *o = (EPI == KB_EPI_SWIGLU_F16) ? __half_as_ushort(__float2half_rn(h))
-                                                : __bfloat16_as_ushort(__float2bfloat16(h));
+                *o = (EPI == KB_EPI_SWIGLU_F16) ? to_f16_sat(h) : __bfloat16_as_ushort(__float2bfloat16(h));
             }
         } else if (n < N) {
             const size_t idx = (size_t)token * N + n;
             if (EPI == KB_EPI_BF16) reinterpret_cast<__nv_bfloat16*>(out)[idx] = __float2bfloat16(v);
-            else if (EPI == KB_EPI_F16) reinterpret_cast<__half*>(out)[idx] = __float2half_rn(v);
+            else if (EPI == KB_EPI_F16) reinterpret_cast<uint16_t*>(out)[idx] = to_f16_sat(v);
             else reinterpret_cast<float*>(out)[idx] = v;   // KB_EPI_F32
         }
     }

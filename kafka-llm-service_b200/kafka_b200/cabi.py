@@ -207,8 +207,17 @@ def gemm(a, w, epilogue: int = EPI_BF16, resid=None, out=None, tile_n: int = 0):
     return out
 
 
+def _need_f16(what: str, *tensors) -> None:
+    """q / k / v and the KV pools are fp16 (include/kafka_b200.h); a bf16 tensor would be read as garbage."""
+    import torch
+    for t in tensors:
+        if t.dtype != torch.float16:
+            raise KafkaB200Error(f"{what}: q / k / v and the KV pools must be float16, got {t.dtype}")
+
+
 def rope_append(qkv, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_heads, n_kv_heads,
                 head_dim, theta):
+    _need_f16("kb_rope_append", qkv, k_pool_layer, v_pool_layer)
     n_tokens = qkv.shape[0]
     n_seqs, max_blocks = block_tables.shape
     check(load().kb_rope_append(_ptr(qkv), _ptr(cu_seqlens), _ptr(ctx_lens), _ptr(block_tables),
@@ -219,6 +228,7 @@ def rope_append(qkv, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_la
 def attn_decode(q, k_pool_layer, v_pool_layer, kv_lens, block_tables, n_heads, n_kv_heads, head_dim,
                 kv_len_bias: int = 0, max_kv_len: int = 0, scratch=None, out_f16: bool = False):
     import torch
+    _need_f16("kb_attn_decode", q, k_pool_layer, v_pool_layer)
     batch, max_blocks = block_tables.shape
     out = torch.empty((batch, n_heads * head_dim), dtype=torch.float16 if out_f16 else torch.bfloat16,
                       device=q.device)
@@ -235,6 +245,7 @@ def attn_decode_static_scratch(q, k_pool_layer, v_pool_layer, kv_lens, block_tab
     built-in 2 MiB device array instead of a caller buffer. Pass ``out`` to avoid any allocation on
     this side too (the default allocates the result with torch for convenience in tests)."""
     import torch
+    _need_f16("kb_attn_decode_static_scratch", q, k_pool_layer, v_pool_layer)
     batch, max_blocks = block_tables.shape
     if out is None:
         out = torch.empty((batch, n_heads * head_dim), dtype=torch.bfloat16, device=q.device)
@@ -253,6 +264,7 @@ def attn_decode_scratch_bytes(batch: int, n_heads: int, head_dim: int) -> int:
 def attn_prefill(q, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tables, max_new, n_heads, n_kv_heads,
                  head_dim, out_f16: bool = False):
     import torch
+    _need_f16("kb_attn_prefill", q, k_pool_layer, v_pool_layer)
     n_tokens = q.shape[0]
     n_seqs, max_blocks = block_tables.shape
     out = torch.empty((n_tokens, n_heads * head_dim), dtype=torch.float16 if out_f16 else torch.bfloat16,

@@ -16,7 +16,7 @@ import torch
 from . import cabi
 from .cabi import KB_BLOCK_TOKENS, KafkaB200Error
 from .model_config import LlamaConfig
-from .kv_layout import pool_shape
+from .kv_layout import KV_DTYPE, pool_shape
 
 
 class EngineCore:
@@ -58,8 +58,8 @@ class EngineCore:
 
         # KV pools: zero-initialised so masked tail positions are finite (see kb_attn_decode's contract)
         shape = pool_shape(cfg.n_layers, self.n_blocks, cfg.n_kv_heads, cfg.head_dim)
-        self.k_pool = torch.zeros(shape, dtype=torch.bfloat16, device=self.device)
-        self.v_pool = torch.zeros(shape, dtype=torch.bfloat16, device=self.device)
+        self.k_pool = torch.zeros(shape, dtype=KV_DTYPE, device=self.device)
+        self.v_pool = torch.zeros(shape, dtype=KV_DTYPE, device=self.device)
         cabi.check(self.lib.kb_bind_kv_pool(self._h, self.k_pool.data_ptr(), self.v_pool.data_ptr(), self.n_blocks),
                    "kb_bind_kv_pool")
 

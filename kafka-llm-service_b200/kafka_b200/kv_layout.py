@@ -1,10 +1,10 @@
 """Host-side description of the paged KV layout in HBM (DESIGN.md "Data layout in HBM").
 
-    pool[layer][block][kv_head][token_in_block][head_dim]      bf16, K and V in separate pools
+    pool[layer][block][kv_head][token_in_block][head_dim]      fp16 (KV_DTYPE), K and V in separate pools
 
 One (block, kv_head) tile is ``KB_BLOCK_TOKENS * head_dim`` contiguous elements, stored as
 ``[dim plane = dim // 64][token][64 dims]``: every 64-dim plane is a 64-row x 128-byte matrix whose
-16-byte chunks (8 bf16) are XOR-swizzled with ``token & 7`` — the canonical SWIZZLE_128B K-major form, so
+16-byte chunks (8 elements) are XOR-swizzled with ``token & 7`` — the canonical SWIZZLE_128B K-major form, so
 a plain 1-D TMA bulk copy of a tile lands in shared memory ready for ``ldmatrix`` (no bank conflicts)
 and for tcgen05 shared-memory descriptors alike.
 
@@ -16,6 +16,8 @@ from __future__ import annotations
 import torch
 
 from .cabi import KB_BLOCK_TOKENS
+
+KV_DTYPE = torch.float16   # q / k / v, the pools and the attention probabilities (include/kafka_b200.h, KB_GEMM_F16)
 
 
 def tile_permutation(head_dim: int) -> torch.Tensor:

@@ -79,3 +79,76 @@ class CPUOracleProvider(LLMProvider):
 
     async def close(self) -> None:
         return None
+
+
+class BatchedOracle:
+    """The same greedy oracle for MANY conversations at once (BASELINE config 2 at its stated size: 64
+    threads x 8 turns x 32 tokens on TinyLlama-1.1B shapes would take the one-conversation-at-a-time provider
+    above the better part of an hour on the host cores).  Two things differ, neither in the arithmetic per
+    token: the new tokens of all conversations are packed for the projections (OracleLlama.forward_packed /
+    decode_batch), and every conversation's fp32 K/V is kept between calls under a key, so a follow-up turn
+    only runs the tokens after the longest common prefix with what the key has seen.  Same tokenizer, chat
+    template, weights and candidate set as CPUOracleProvider; tests/test_oracle_and_abi.py checks that both
+    produce the same text."""
+
+    def __init__(self, cfg, weights, generable_only: bool = True):
+        self.cfg = cfg
+        self.oracle = OracleLlama(cfg, weights)
+        self.tokenizer = ByteTokenizer(cfg.vocab)
+        self.template = ChatTemplate(self.tokenizer)
+        self.allowed = generable_ids(cfg) if generable_only else None
+        self._state = {}          # key -> (tokens whose K/V is cached, KVCache)
+        self.tokens_generated = 0
+        self.tokens_prefilled = 0
+
+    def generate_ids(self, keys: List[str], prompts: List[List[int]], max_tokens: int):
+        """-> [(ids without a trailing eot, finish_reason)] in the order of `keys`."""
+        caches, news = [], []
+        for key, prompt in zip(keys, prompts):
+            seen, cache = self._state.get(key, ([], None))
+            if cache is None:
+                cache = self.oracle.new_cache()
+            n = 0
+            lim = min(len(seen), len(prompt) - 1)      # at least one token must run to produce logits
+            while n < lim and seen[n] == prompt[n]:
+                n += 1
+            cache.truncate(n)
+            caches.append(cache)
+            news.append(torch.tensor(prompt[n:]))
+            self.tokens_prefilled += len(prompt) - n
+        logits = self.oracle.forward_packed(news, caches)
+        n = len(keys)
+        out: List[List[int]] = [[] for _ in range(n)]
+        reason = ["length"] * n
+        active = list(range(n))
+        eot = self.tokenizer.eot_id
+        for step in range(max_tokens):
+            nxt = []
+            for row, i in enumerate(active):
+                t = masked_argmax(logits[row], self.allowed)
+                out[i].append(t)
+                if t == eot:
+                    reason[i] = "stop"
+                else:
+                    nxt.append(i)
+            active = nxt
+            if not active or step == max_tokens - 1:
+                break
+            logits = self.oracle.decode_batch(torch.tensor([out[i][-1] for i in active]), [caches[i] for i in active])
+        res = []
+        for i, (key, prompt) in enumerate(zip(keys, prompts)):
+            self._state[key] = (list(prompt) + out[i][:-1], caches[i])   # the last id was sampled, never fed
+            self.tokens_generated += len(out[i])
+            ids = out[i][:-1] if reason[i] == "stop" else out[i]
+            res.append((ids, reason[i]))
+        return res
+
+    def complete(self, keys: List[str], conversations, max_tokens: int, tools=None):
+        """conversations: one message list per key -> [(text, finish_reason)]."""
+        prompts = [self.template.render(m, tools=tools or None) for m in conversations]
+        out = []
+        for ids, reason in self.generate_ids(keys, prompts, max_tokens):
+            dec = self.tokenizer.stream_decoder()
+            text = "".join(dec.push(t) for t in ids) + dec.flush()
+            out.append((text, reason))
+        return out

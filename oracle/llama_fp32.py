@@ -143,7 +143,49 @@ class OracleLlama:
         return logits if all_logits else logits[0]
 
     @torch.no_grad()
-    def decode_batch(self, tokens: torch.Tensor, caches: List[KVCache]) -> torch.Tensor:
+    def forward_packed(self, seqs: List[torch.Tensor], caches: List[KVCache]) -> torch.Tensor:
+        """``forward`` for several sequences at once: the new tokens of all sequences are packed for the
+        projections (one [sum T, H] x [H, N] GEMM each, so the host cores run a config-2-sized turn in
+        minutes instead of tens of minutes), attention runs per sequence against its own cache. Same
+        arithmetic per row as ``forward``; returns the last position's logits of every sequence [n, V]."""
+        cfg, w = self.cfg, self.w
+        lens = [int(s.numel()) for s in seqs]
+        offs = [0]
+        for n in lens:
+            offs.append(offs[-1] + n)
+        pasts = [c.length for c in caches]
+        pos = torch.cat([torch.arange(p, p + n) for p, n in zip(pasts, lens)])
+        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta)
+        x = w["embed"][torch.cat([s.long() for s in seqs])]
+        T = x.shape[0]
+        scale = cfg.head_dim ** -0.5
+        for i in range(cfg.n_layers):
+            p = f"l{i}."
+            h = rmsnorm(x, w[p + "attn_norm"], cfg.rms_eps)
+            q = apply_rope((h @ w[p + "wq"].T).view(T, cfg.n_heads, cfg.head_dim), cos, sin)
+            k = apply_rope((h @ w[p + "wk"].T).view(T, cfg.n_kv_heads, cfg.head_dim), cos, sin)
+            v = (h @ w[p + "wv"].T).view(T, cfg.n_kv_heads, cfg.head_dim)
+            o = torch.empty(T, cfg.q_dim)
+            for b, c in enumerate(caches):
+                lo, hi = offs[b], offs[b + 1]
+                n = hi - lo
+                c.append(i, k[lo:hi], v[lo:hi])
+                K, V = c.k(i), c.v(i)                                      # [L, kvh, hd]
+                sc = torch.einsum("tkgd,lkd->kgtl", q[lo:hi].view(n, cfg.n_kv_heads, cfg.group, cfg.head_dim),
+                                  K) * scale
+                causal = torch.arange(K.shape[0])[None, :] > (pasts[b] + torch.arange(n))[:, None]
+                a = torch.softmax(sc.masked_fill(causal[None, None], float("-inf")), dim=-1)
+                o[lo:hi] = torch.einsum("kgtl,lkd->tkgd", a, V).reshape(n, cfg.q_dim)
+            x = self._residual(x, o @ w[p + "wo"].T)
+            h = rmsnorm(x, w[p + "mlp_norm"], cfg.rms_eps)
+            x = self._residual(x, (torch.nn.functional.silu(h @ w[p + "w_gate"].T) * (h @ w[p + "w_up"].T))
+                               @ w[p + "w_down"].T)
+        last = x[torch.tensor([o_ - 1 for o_ in offs[1:]])]
+        return rmsnorm(last, w["final_norm"], cfg.rms_eps) @ w["lm_head"].T
+
+    @torch.no_grad()
+    def decode_batch(self, tokens: torch.Tensor, caches: List[KVCache],
+                     taps: Optional[Dict[str, torch.Tensor]] = None) -> torch.Tensor:
         """One decode step for B sequences at once (projections batched over B, attention per
         sequence). Same arithmetic as ``forward`` with T=1 per sequence; returns logits [B, V].
         Used by bench.py's CPU baseline so the host cores see one [B,H]x[H,N] GEMM per projection."""
@@ -153,23 +195,42 @@ class OracleLlama:
         cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta)
         x = w["embed"][tokens.long()]
         scale = cfg.head_dim ** -0.5
+        padded = B > 1 and int(pos.max()) < 1024          # short contexts: one padded batch (see below)
+        pad = torch.arange(int(pos.max()) + 1)[None, :] > pos[:, None]
         for i in range(cfg.n_layers):
             p = f"l{i}."
             h = rmsnorm(x, w[p + "attn_norm"], cfg.rms_eps)
             q = apply_rope((h @ w[p + "wq"].T).view(B, cfg.n_heads, cfg.head_dim), cos, sin)
             k = apply_rope((h @ w[p + "wk"].T).view(B, cfg.n_kv_heads, cfg.head_dim), cos, sin)
             v = (h @ w[p + "wv"].T).view(B, cfg.n_kv_heads, cfg.head_dim)
-            o = torch.empty(B, cfg.n_heads, cfg.head_dim)
             for b, c in enumerate(caches):
                 c.append(i, k[b:b + 1], v[b:b + 1])
-                qb = q[b].view(cfg.n_kv_heads, cfg.group, cfg.head_dim)
-                s = torch.einsum("kgd,lkd->kgl", qb, c.k(i)) * scale
-                o[b] = torch.einsum("kgl,lkd->kgd", torch.softmax(s, -1), c.v(i)).reshape(cfg.n_heads, cfg.head_dim)
+            if padded:
+                # attention of all B sequences as one padded batch (B tiny per-sequence einsums cost more
+                # in dispatch than in arithmetic): padded key positions get -inf and contribute an exact 0
+                Kp = torch.nn.utils.rnn.pad_sequence([c.k(i) for c in caches], batch_first=True)   # [B, Lmax, kvh, hd]
+                Vp = torch.nn.utils.rnn.pad_sequence([c.v(i) for c in caches], batch_first=True)
+                s = torch.einsum("bkgd,blkd->bkgl", q.view(B, cfg.n_kv_heads, cfg.group, cfg.head_dim), Kp) * scale
+                s = s.masked_fill(pad[:, None, None, :], float("-inf"))
+                o = torch.einsum("bkgl,blkd->bkgd", torch.softmax(s, -1), Vp).reshape(B, cfg.n_heads, cfg.head_dim)
+            else:
+                # long contexts: per sequence, straight from each cache (no padded copy of the K/V)
+                o = torch.empty(B, cfg.n_heads, cfg.head_dim)
+                for b, c in enumerate(caches):
+                    qb = q[b].view(cfg.n_kv_heads, cfg.group, cfg.head_dim)
+                    s = torch.einsum("kgd,lkd->kgl", qb, c.k(i)) * scale
+                    o[b] = torch.einsum("kgl,lkd->kgd", torch.softmax(s, -1), c.v(i)).reshape(cfg.n_heads, cfg.head_dim)
             x = self._residual(x, o.view(B, cfg.q_dim) @ w[p + "wo"].T)
             h = rmsnorm(x, w[p + "mlp_norm"], cfg.rms_eps)
-            x = self._residual(x, (torch.nn.functional.silu(h @ w[p + "w_gate"].T) * (h @ w[p + "w_up"].T))
-                               @ w[p + "w_down"].T)
-        return rmsnorm(x, w["final_norm"], cfg.rms_eps) @ w["lm_head"].T
+            inner = torch.nn.functional.silu(h @ w[p + "w_gate"].T) * (h @ w[p + "w_up"].T)
+            if taps is not None and i == cfg.n_layers - 1:     # the LAST layer's intermediates (tools/stage_errors.py)
+                taps.update(q=q.reshape(B, -1).clone(), k=k.reshape(B, -1).clone(), v=v.reshape(B, -1).clone(),
+                            attn=o.reshape(B, -1).clone(), x_mid=x.clone(), xn_mlp=h.clone(), inner=inner.clone())
+            x = self._residual(x, inner @ w[p + "w_down"].T)
+        xl = rmsnorm(x, w["final_norm"], cfg.rms_eps)
+        if taps is not None:
+            taps.update(x_final=x.clone(), xl=xl.clone())
+        return xl @ w["lm_head"].T
 
     @torch.no_grad()
     def greedy(self, prompt: torch.Tensor, n_new: int, cache: Optional[KVCache] = None,

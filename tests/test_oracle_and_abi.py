@@ -171,3 +171,24 @@ def test_product_never_imports_the_oracle():
         assert "import oracle" not in src and "from oracle" not in src, f
     for f in (pkg / "csrc").glob("*.cu*"):
         assert "oracle" not in f.read_text().lower(), f
+
+
+def test_batched_oracle_equals_the_one_conversation_provider():
+    """oracle/cpu_provider.BatchedOracle (packed projections, K/V kept between turns) must produce exactly
+    the text of CPUOracleProvider (stateless, one conversation at a time) over several turns."""
+    import asyncio
+    from kafka_b200.llm import Message
+    from kafka_b200.model_config import get_config
+    from kafka_b200.weights import generate_weights
+    from oracle.cpu_provider import BatchedOracle, CPUOracleProvider
+    cfg = get_config("tiny-test")
+    w = generate_weights(cfg, 0, init="margin")
+    one, many = CPUOracleProvider(cfg, w), BatchedOracle(cfg, w)
+    convs = [[Message(role="user", content=f"hello {i} " * (i + 1))] for i in range(5)]
+    for turn in range(3):
+        want = [asyncio.run(one.completion(c, max_tokens=12)) for c in convs]
+        got = many.complete([f"k{i}" for i in range(5)], convs, 12)
+        assert [(x.content, x.finish_reason) for x in want] == got
+        for c, (t, _) in zip(convs, got):
+            c += [Message(role="assistant", content=t), Message(role="user", content="more " + t[:3])]
+    assert many.tokens_prefilled < sum(len(one.template.render(c)) for c in convs) * 2   # follow-ups reuse K/V

@@ -21,10 +21,10 @@ lib.kb_debug_attn_trace.argtypes = [C.POINTER(C.c_ulonglong)]
 n_seqs, ctx, new, n_heads, n_kv, hd = 64, 2048, 64, 32, 8, 128
 bpt = (ctx + new + 63) // 64
 g = torch.Generator(device="cpu").manual_seed(0)
-kp = torch.randn(n_seqs * bpt, n_kv, 64 * hd, device=dev).bfloat16()
-vp = torch.randn(n_seqs * bpt, n_kv, 64 * hd, device=dev).bfloat16()
+kp = torch.randn(n_seqs * bpt, n_kv, 64 * hd, device=dev).half()
+vp = torch.randn(n_seqs * bpt, n_kv, 64 * hd, device=dev).half()
 bt = torch.randperm(n_seqs * bpt, generator=g).int().view(n_seqs, bpt).to(dev)
-qkv = torch.randn(n_seqs * new, (n_heads + 2 * n_kv) * hd, device=dev).bfloat16()
+qkv = torch.randn(n_seqs * new, (n_heads + 2 * n_kv) * hd, device=dev).half()
 cu = torch.arange(0, (n_seqs + 1) * new, new, dtype=torch.int32, device=dev)
 ctxs = torch.full((n_seqs,), ctx, dtype=torch.int32, device=dev)
 for _ in range(3):
