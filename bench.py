@@ -51,10 +51,13 @@ def parse_args():
     ap.add_argument("--threads", type=int, default=512, help="concurrent threads per GPU")
     ap.add_argument("--history", type=int, default=2048)
     ap.add_argument("--user-tokens", type=int, default=64)
-    ap.add_argument("--cpu-threads", type=int, default=8, help="threads in the CPU sample")
+    ap.add_argument("--cpu-threads", type=int, default=0,
+                    help="threads in the CPU sample (0 = 64 when the host has the RAM for it, else 8)")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-reference-server", action="store_true",
+                    help="reference arm: skip the legs that run the reference's own host code (baseline/_ref)")
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-provider", action="store_true", help="skip the provider-level (plugin API) turn")
     ap.add_argument("--gen-tokens", type=int, default=128, help="new tokens per turn in the provider-level leg")
@@ -68,6 +71,9 @@ def parse_args():
                     help="tensor-parallel run: also time the other all-reduce implementations on the same state")
     ap.add_argument("--tp-allreduce", default=None, choices=["peers", "peers-f16", "peers-fused", "peers-p2p", "nccl"],
                     help="all-reduce of the tensor-parallel run (default: own peer-memory kernel, NCCL if unavailable)")
+    ap.add_argument("--config", type=int, default=3, choices=[2, 3],
+                    help="3 (default): the headline workload. 2: BASELINE configs[1] whole — TinyLlama-1.1B shapes, 64 "
+                         "threads x 8 turns x 32 tokens, B200 provider vs the fp32 CPU oracle, agreement + both tok/s")
     ap.add_argument("--tp", action="store_true",
                     help="tensor-parallel: ONE model sharded over all ranks (config 5: --model llama-3-70b --history 8192)")
     return ap.parse_args()
@@ -146,14 +152,57 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1):
+def pick_cpu_threads() -> int:
+    """All host cores, unless the machine punishes that: on an over-subscribed VM an OpenMP team as wide as
+    cpu_count() can spend milliseconds in the barrier of every small op (seen in the build container: 6.7 ms
+    per RMSNorm-sized op at 8 threads, 50 us at 4). Halve until a small op costs what it should."""
+    n = os.cpu_count() or 1
+    x = torch.randn(64, 2048)
+    while n > 1:
+        torch.set_num_threads(n)
+        for _ in range(5):
+            x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-5)
+        t0 = time.perf_counter()
+        for _ in range(50):
+            x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-5)
+        if (time.perf_counter() - t0) / 50 < 5e-4:
+            break
+        n //= 2
+    torch.set_num_threads(n)
+    return n
+
+
+def mem_available_gb() -> float:
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
+
+
+def cpu_sample_size(cfg, ctx: int, want: int):
+    """(threads, alias_weights) of the CPU sample. want <= 0 = automatic: 64 threads with every layer's fp32
+    weights in memory of its own when the host has the RAM for it (Llama-3-8B: 32 GB of weights + 36 GB of fp32
+    K/V), else 8 threads with one layer's tensors shared by all layers (872 MB, still far beyond the caches)."""
+    w_gb = 4 * (cfg.matmul_params() + 2 * cfg.vocab * cfg.hidden) / 1e9
+    kv_gb = lambda n: n * (ctx + 16) * cfg.kv_bytes_per_token * 2 / 1e9      # fp32 K/V
+    avail = mem_available_gb()
+    if want <= 0:
+        want = 64 if avail > 1.3 * (w_gb + kv_gb(64)) + 8 else 8
+    alias = avail < 1.3 * (w_gb + kv_gb(want)) + 8
+    return want, alias
+
+
+def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1, alias: bool = True):
     """The fp32 oracle (oracle/llama_fp32.py) decoding `n_threads` threads at context `ctx` on the host
-    cores. To stay bounded in time and host memory, ONE layer's fp32 weight tensors (872 MB for
-    Llama-3-8B, far larger than the last-level cache) are shared by all layers and embed/lm_head share
-    one table: same shapes, same FLOPs and DRAM traffic per step, values irrelevant for timing."""
+    cores. Values are irrelevant for timing, shapes, FLOPs and DRAM traffic are the workload's. With
+    `alias` (small hosts) ONE layer's fp32 weight tensors (872 MB for Llama-3-8B, far larger than the
+    last-level cache) are shared by all layers and embed / lm_head share one table; without it every layer
+    and both tables own their memory (copies of one draw)."""
     from oracle.llama_fp32 import OracleLlama
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
+    cores = pick_cpu_threads()
     g = torch.Generator().manual_seed(0)
     H, F = cfg.hidden, cfg.ffn
 
@@ -164,10 +213,10 @@ def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1):
     shared = {"attn_norm": torch.ones(H), "mlp_norm": torch.ones(H), "wq": rn(cfg.q_dim, H),
               "wk": rn(cfg.kv_dim, H), "wv": rn(cfg.kv_dim, H), "wo": rn(H, cfg.q_dim), "w_gate": rn(F, H),
               "w_up": rn(F, H), "w_down": rn(H, F)}
-    w = {"embed": table, "lm_head": table, "final_norm": torch.ones(H)}
+    w = {"embed": table, "lm_head": table if alias else table.clone(), "final_norm": torch.ones(H)}
     for i in range(cfg.n_layers):
         for k, v in shared.items():
-            w[f"l{i}.{k}"] = v
+            w[f"l{i}.{k}"] = v if (alias or i == 0) else v.clone()
     oracle = OracleLlama(cfg, w)
     caches = []
     for _ in range(n_threads):
@@ -187,7 +236,9 @@ def cpu_baseline(cfg, n_threads: int, ctx: int, steps: int, warmup: int = 1):
     dt = time.perf_counter() - t0
     return {"value": n_threads * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"{n_threads} threads x {steps} decode steps at context {ctx}, fp32 torch eager oracle, "
-                      f"{cfg.name} shapes, one layer's weights shared by all {cfg.n_layers} layers",
+                      f"{cfg.name} shapes, " + (f"one layer's weights shared by all {cfg.n_layers} layers"
+                                                if alias else "every layer's weights in memory of its own"),
+            "threads": n_threads, "weights_aliased": alias, "host_cpus": os.cpu_count(),
             "ms_per_step": dt / steps * 1e3}
 
 
@@ -402,6 +453,196 @@ def http_turn(core, cfg, n_threads: int, history: int, user_tokens: int, gen_tok
 
 
 # ------------------------------------------------------------------------------------------------
+def _load_reference():
+    """The reference's own host code: /root/reference where it is mounted (the build container), else its
+    unmodified copy under baseline/_ref (made by __graft_entry__.build(); the GPU box only has that)."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import ref_harness
+    ref_harness.ensure_copy()
+    return ref_harness if ref_harness.load() else None
+
+
+def reference_config1(n_threads: int = 64, n_turns: int = 8):
+    """BASELINE configs[0]: thread replay on CPU over SQLite with an echo provider — the host plumbing around
+    the path (history load, assembly, sanitising, persistence, agent loop), timed through the REFERENCE's
+    LocalDBClient + KafkaAgent.run_with_thread + Agent.run (/root/reference/src/db/local.py:87-177,
+    src/kafka/base.py:171-310, src/agents/base.py:160) and through this repo's ThreadStore + ThreadRunner +
+    StreamingAgent, same messages, fresh database files, one turn after the other."""
+    import asyncio
+    import contextlib
+    import random
+    import tempfile
+    ref = _load_reference()
+    from kafka_b200.agent import StreamingAgent
+    from kafka_b200.db import ThreadStore
+    from kafka_b200.orchestrator import ThreadRunner
+    from kafka_b200.provider import EchoLLMProvider
+    from kafka_b200.tools import LocalToolProvider
+    tmp = tempfile.mkdtemp(prefix="kb-config1-")
+
+    def text(i, turn):
+        rnd = random.Random(1234 + i * 100 + turn)
+        return "".join(chr(rnd.randrange(32, 127)) for _ in range(48))
+
+    async def ours():
+        store = ThreadStore(os.path.join(tmp, "ours.db"))
+        t0 = time.perf_counter()
+        for turn in range(n_turns):
+            for i in range(n_threads):
+                tools = LocalToolProvider([])
+                runner = ThreadRunner(StreamingAgent(EchoLLMProvider("echo", tools), tools), store, f"bench-{i:04d}")
+                async for _ in runner.run([{"role": "user", "content": text(i, turn)}], model="echo"):
+                    pass
+        dt = time.perf_counter() - t0
+        n = len(await store.get_thread_messages(f"bench-{n_threads - 1:04d}"))
+        return dt, n
+
+    async def theirs():
+        from src.agents.base import Agent
+        from src.db.local import LocalDBClient
+        from src.kafka.base import KafkaAgent
+        from src.llm.base import LLMProvider
+        from src.llm.types import CompletionResponse, Message, StreamChunk
+        from src.tools.agent import AgentToolProvider
+
+        class Echo(LLMProvider):
+            async def stream_completion(self, messages, *, temperature=None, max_tokens=None, stop=None, **kw):
+                last = next((m.content for m in reversed(messages) if m.role == "user" and m.content), "")
+                yield StreamChunk(role="assistant")
+                if last:
+                    yield StreamChunk(content=last)
+                yield StreamChunk(finish_reason="stop")
+
+            async def completion(self, messages, **kw):
+                return CompletionResponse(content="", finish_reason="stop")
+
+        class Kafka(KafkaAgent):
+            """Smallest concrete KafkaAgent: what KafkaV1Provider.initialize sets up (src/kafka/v1.py:177-194)
+            minus sandboxes, prompts and remote tools."""
+            def __init__(self, thread_id, db):
+                super().__init__(thread_id)
+                self._db = db
+
+            async def initialize(self):
+                self._db_client = self._db
+                self._tool_provider = AgentToolProvider()
+                await self._tool_provider.connect()
+                self._agent = Agent(llm_provider=Echo(), tool_provider=self._tool_provider)
+                self._initialized = True
+
+            async def cleanup(self):
+                await self._tool_provider.disconnect()
+
+            async def get_tools(self):
+                return await self._tool_provider.get_tools()
+
+            async def run(self, messages, model, temperature=0.7, max_tokens=None):
+                async for ev in self._agent.run(messages, model=model, temperature=temperature, max_tokens=max_tokens):
+                    yield ev
+
+        db = LocalDBClient(os.path.join(tmp, "ref.db"))
+        if hasattr(db, "initialize"):
+            await db.initialize()
+        t0 = time.perf_counter()
+        for turn in range(n_turns):
+            for i in range(n_threads):
+                async with Kafka(f"bench-{i:04d}", db) as k:      # a new agent per request, like server.py:237-245
+                    async for _ in k.run_with_thread([Message(role="user", content=text(i, turn))], model="echo"):
+                        pass
+        dt = time.perf_counter() - t0
+        n = len(await db.get_thread_messages(f"bench-{n_threads - 1:04d}"))
+        return dt, n
+
+    out = {"threads": n_threads, "turns": n_turns, "provider": "echo",
+           "what": "history load + assembly + persistence + agent loop per thread-turn, SQLite, no model"}
+    dt, n = asyncio.run(ours())
+    out["repo"] = {"turns_per_s": n_threads * n_turns / dt, "wall_s": dt, "messages_in_last_thread": n,
+                   "api": "ThreadStore + ThreadRunner + StreamingAgent"}
+    if ref is None:
+        out["reference"] = {"unavailable": "neither /root/reference nor baseline/_ref holds the reference tree"}
+        return out
+    with contextlib.redirect_stdout(sys.stderr):             # the reference's agent prints progress lines
+        dt, n = asyncio.run(theirs())
+    out["reference"] = {"turns_per_s": n_threads * n_turns / dt, "wall_s": dt, "messages_in_last_thread": n,
+                        "api": "LocalDBClient + KafkaAgent.run_with_thread + Agent.run (unmodified reference code, "
+                               "aiosqlite shim over sqlite3)", "tree": str(ref.REF)}
+    return out
+
+
+def reference_oracle_in_agent(model: str = "tinyllama-1.1b", n_threads: int = 4, max_tokens: int = 16):
+    """north_star's CPU baseline as worded: the fp32 CPU provider (oracle/cpu_provider.CPUOracleProvider)
+    running INSIDE the reference's own KafkaAgent.run_with_thread / Agent.run over the reference's
+    LocalDBClient, one turn per thread, config-2 shapes and message sizes. Bounded: a few threads."""
+    import asyncio
+    import contextlib
+    import random
+    import tempfile
+    ref = _load_reference()
+    if ref is None:
+        return {"unavailable": "neither /root/reference nor baseline/_ref holds the reference tree"}
+    from kafka_b200.llm import register_with_reference
+    from kafka_b200.model_config import get_config
+    from kafka_b200.weights import generate_weights
+    from oracle.cpu_provider import CPUOracleProvider
+    from src.agents.base import Agent
+    from src.db.local import LocalDBClient
+    from src.kafka.base import KafkaAgent
+    from src.llm.types import Message
+    from src.tools.agent import AgentToolProvider
+    register_with_reference()
+    cores = pick_cpu_threads()
+    cfg = get_config(model)
+    provider = CPUOracleProvider(cfg, generate_weights(cfg, seed=0, init="margin"), default_max_tokens=max_tokens)
+
+    class Kafka(KafkaAgent):
+        def __init__(self, thread_id, db):
+            super().__init__(thread_id)
+            self._db = db
+
+        async def initialize(self):
+            self._db_client = self._db
+            self._tool_provider = AgentToolProvider()
+            await self._tool_provider.connect()
+            self._agent = Agent(llm_provider=provider, tool_provider=self._tool_provider)
+            self._initialized = True
+
+        async def cleanup(self):
+            await self._tool_provider.disconnect()
+
+        async def get_tools(self):
+            return await self._tool_provider.get_tools()
+
+        async def run(self, messages, model, temperature=0.7, max_tokens=None):
+            async for ev in self._agent.run(messages, model=model, temperature=temperature, max_tokens=max_tokens):
+                yield ev
+
+    async def go():
+        db = LocalDBClient(os.path.join(tempfile.mkdtemp(prefix="kb-ref-oracle-"), "ref.db"))
+        if hasattr(db, "initialize"):
+            await db.initialize()
+        n_chars = 0
+        t0 = time.perf_counter()
+        for i in range(n_threads):
+            rnd = random.Random(1234 + i)
+            text = "".join(chr(rnd.randrange(32, 127)) for _ in range(48))
+            async with Kafka(f"bench-{i:04d}", db) as k:
+                async for ev in k.run_with_thread([Message(role="user", content=text)], model=provider.model,
+                                                  temperature=0.0, max_tokens=max_tokens):
+                    ch = ev.get("choices")
+                    if ch and ch[0].get("delta", {}).get("content"):
+                        n_chars += len(ch[0]["delta"]["content"])
+        return time.perf_counter() - t0, n_chars
+    before = provider.tokens_generated
+    with contextlib.redirect_stdout(sys.stderr):
+        dt, n_chars = asyncio.run(go())
+    n_tok = provider.tokens_generated - before
+    return {"model": cfg.name, "threads": n_threads, "max_tokens": max_tokens, "tokens": n_tok, "wall_s": dt,
+            "tokens_per_s": n_tok / dt, "cores": cores, "streamed_chars": n_chars,
+            "api": "CPUOracleProvider inside the reference's KafkaAgent.run_with_thread -> Agent.run -> "
+                   "stream_completion (unmodified reference host code), one thread after the other; every call "
+                   "re-runs its whole prompt (agent tool schemas included), as the reference's provider does"}
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -409,18 +650,31 @@ def run_reference(args, rank, world):
     cfg = get_config(args.model)
     ctx = args.history + args.user_tokens
     steps = max(1, min(args.steps, 8))
-    cb = cpu_baseline(cfg, args.cpu_threads, ctx, steps, warmup=max(1, min(args.warmup, 2)))
+    n_thr, alias = cpu_sample_size(cfg, ctx, args.cpu_threads)
+    cb = cpu_baseline(cfg, n_thr, ctx, steps, warmup=max(1, min(args.warmup, 2)), alias=alias)
+    server = {}
+    if not args.no_reference_server:
+        for name, fn in (("config1_thread_replay", reference_config1), ("cpu_provider_in_reference_agent",
+                                                                         reference_oracle_in_agent)):
+            try:
+                server[name] = fn()
+            except Exception as ex:          # the headline sample above must not be lost to a host-side surprise
+                server[name] = {"failed": repr(ex)}
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{cfg.name} decode, {args.cpu_threads} threads x {args.history}-token history "
+        "config": {"workload": f"{cfg.name} decode, {n_thr} threads x {args.history}-token history "
                                f"+ {args.user_tokens}-token turn (bounded CPU sample of the {args.threads}-thread "
-                               "workload)", "threads": args.cpu_threads, "context": ctx},
+                               "workload the B200 arm runs per GPU)", "threads": n_thr, "context": ctx,
+                   "b200_arm_threads_per_gpu": args.threads, "weights_aliased": alias},
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "reference's own path is a remote gateway call (src/llm/portkey.py:379), not runnable offline; "
-                "this arm is the CPU oracle port run on all host cores",
+        "reference_server": server or None,
+        "note": "the reference's own implementation of the path is a remote gateway call "
+                "(src/llm/portkey.py:379), not runnable offline: `value` is the fp32 CPU oracle port of the path on "
+                "the host cores; `reference_server` times the reference's own (unmodified) host code around the "
+                "path — config 1 whole, and the CPU provider inside its agent / thread loop",
     }
     emit(line)
 
@@ -622,7 +876,8 @@ def run_b200(args, rank, world, local_rank):
 
     cb = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cb = cpu_baseline(cfg, args.cpu_threads, ctx0, args.cpu_steps)
+        n_thr, alias = cpu_sample_size(cfg, ctx0, args.cpu_threads)
+        cb = cpu_baseline(cfg, n_thr, ctx0, args.cpu_steps, alias=alias)
 
     if rank == 0:
         line = {
@@ -649,6 +904,47 @@ def run_b200(args, rank, world, local_rank):
                         "launches": l0 - launches0},
         }
         emit(line)
+
+
+def run_config2(args):
+    """BASELINE configs[1] at its stated size (oracle/config2.py): the CPU-vs-B200 measurement SURVEY.md §8(d)
+    asks for, and the greedy-agreement criterion on the way."""
+    import asyncio
+    import tempfile
+    from kafka_b200.db import ThreadStore
+    from kafka_b200.factory import build_engine
+    from kafka_b200.model_config import get_config
+    from kafka_b200.provider import B200LLMProvider
+    from kafka_b200.tokenizer import ByteTokenizer
+    from kafka_b200.weights import generate_weights
+    from oracle.config2 import run_config2 as drive
+    from oracle.cpu_provider import BatchedOracle
+    cores = pick_cpu_threads()
+    cfg = get_config("tinyllama-1.1b")
+    w = generate_weights(cfg, seed=0, init="margin")
+    eng = build_engine(cfg, 0, n_blocks=64 * 16, max_seqs=64, max_tokens=8192, weights=w)
+    gpu = B200LLMProvider(eng, ByteTokenizer(cfg.vocab), model=cfg.name, default_temperature=0.0)
+    store = ThreadStore(os.path.join(tempfile.mkdtemp(prefix="kb-config2-"), "threads.db"))
+    from kafka_b200 import cabi
+    l0 = cabi.launch_count()
+    try:
+        r = asyncio.run(drive(gpu, BatchedOracle(cfg, w), store, n_threads=64, n_turns=8, max_tokens=32))
+    finally:
+        eng.shutdown()
+    r.pop("cached")
+    emit({"metric": METRIC, "value": r["b200_tokens_per_s"], "unit": UNIT, "n_gpus": 1, "steps": r["turns"],
+          "warmup": 0, "ms_per_step": 1e3 * r["b200_wall_s"] / r["turns"], "higher_is_better": True,
+          "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+          "config": {"workload": "BASELINE configs[1]: tinyllama-1.1b shapes (margin init), 64 threads x 8 turns x 32 "
+                                 "greedy tokens through B200LLMProvider.completion, histories in SQLite; a step is "
+                                 "one turn of all 64 threads; wall clock (first turn includes first-launch costs)"},
+          "gpu_launches": cabi.launch_count() - l0,
+          "cpu_baseline": {"value": r["cpu_tokens_per_s"], "unit": UNIT, "cores": cores, "kind": "port",
+                           "sample": "the same 512 thread-turns, whole: fp32 oracle with packed projections and "
+                                     "its K/V kept between turns (oracle/cpu_provider.BatchedOracle)",
+                           "wall_s": r["cpu_wall_s"]},
+          "parity": {k: r[k] for k in ("thread_turns", "mismatched_thread_turns", "diverged_threads",
+                                       "agreement_fraction_of_threads", "first_mismatches")}})
 
 
 def run_tp(args, rank, world, local_rank):
@@ -829,7 +1125,10 @@ def main():
         torch.cuda.set_device(local_rank)
         torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        if args.tp and world > 1:
+        if args.config == 2:
+            if rank == 0:
+                run_config2(args)
+        elif args.tp and world > 1:
             run_tp(args, rank, world, local_rank)
         else:
             run_b200(args, rank, world, local_rank)

@@ -102,6 +102,13 @@ class ThreadStore:
                 Path(self.db_path).parent.mkdir(parents=True, exist_ok=True)
             self._conn = sqlite3.connect(self.db_path, check_same_thread=False)
             self._conn.row_factory = sqlite3.Row
+            if self.db_path != ":memory:":
+                # write-ahead log + one fsync per checkpoint instead of per commit: a turn costs two commits
+                # (user message, assistant message), and with the rollback journal each is two fsyncs — 0.8 ms
+                # apiece, three quarters of the host time of a config-1 thread turn. Safe against a crash of
+                # this process; the file stays readable by the reference's client (any SQLite >= 3.7).
+                self._conn.execute("PRAGMA journal_mode=WAL")
+                self._conn.execute("PRAGMA synchronous=NORMAL")
             self._conn.executescript(SCHEMA)
             self._conn.commit()
         return self._conn

@@ -1,7 +1,8 @@
-"""Import the reference's host code (/root/reference) inside THIS container for cross-checks and for
-generating golden fixtures. The GPU box has no /root/reference: everything here degrades to
-`available() == False` and the tests that need it skip; the committed fixtures under tests/golden/
-carry what was learned.
+"""Import the reference's host code (/root/reference, or its unmodified copy under baseline/_ref) for
+cross-checks, for generating golden fixtures and for the reference arm of bench.py. The GPU box has no
+/root/reference: it sees the copy that `__graft_entry__.build()` / `ensure_copy()` left in baseline/_ref
+(git-ignored, shipped by gpurun); without either everything here degrades to `available() == False`, the
+tests that need it skip, and the committed fixtures under tests/golden/ carry what was learned.
 
 Three packages the reference imports at package-import time are missing from the image
 (SURVEY.md §0 item 11); in-memory stand-ins are installed for them:
@@ -15,7 +16,23 @@ import sys
 import types
 from pathlib import Path
 
-REF = Path("/root/reference")
+_MOUNT = Path("/root/reference")
+_COPY = Path(__file__).resolve().parent.parent / "baseline" / "_ref"      # git-ignored; travels to the GPU box
+REF = _MOUNT if (_MOUNT / "src" / "llm" / "base.py").exists() else _COPY
+
+
+def ensure_copy() -> bool:
+    """Copy the reference's Python tree to baseline/_ref (unmodified; the playground UI and VCS data are left
+    out) so that the GPU box, which has no /root/reference, can run the reference's own host code in the
+    reference arm of bench.py. Returns True when a usable tree exists afterwards."""
+    import shutil
+    if (_COPY / "src" / "llm" / "base.py").exists():
+        return True
+    if not (_MOUNT / "src" / "llm" / "base.py").exists():
+        return False
+    _COPY.parent.mkdir(parents=True, exist_ok=True)
+    shutil.copytree(_MOUNT, _COPY, ignore=shutil.ignore_patterns(".git", "playground", "node_modules", "__pycache__"))
+    return True
 
 
 def available() -> bool:

@@ -25,6 +25,13 @@ def test_reference_arm_prints_one_json_line():
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and "sample" in cb
     assert d["config"]["workload"].startswith("llama-3-8b")
+    # the reference's own host code around the path, timed where its tree is available (here: /root/reference)
+    c1 = d["reference_server"]["config1_thread_replay"]
+    assert c1["threads"] == 64 and c1["turns"] == 8 and c1["repo"]["messages_in_last_thread"] == 16
+    if "unavailable" not in c1["reference"]:
+        assert c1["reference"]["messages_in_last_thread"] == 16 and c1["reference"]["turns_per_s"] > 0
+        inside = d["reference_server"]["cpu_provider_in_reference_agent"]
+        assert inside["tokens"] == inside["threads"] * inside["max_tokens"] and inside["tokens_per_s"] > 0
 
 
 def test_b200_arm_has_no_cpu_fallback():
