@@ -329,6 +329,12 @@ int kb_select_tokens(int32_t* dst, const int32_t* prev_out, const int32_t* src_i
 int kb_profile_begin(kb_engine* e);
 int kb_profile_end(kb_engine* e, float* ms_by_cat, int32_t* launches_by_cat);
 
+/* Read-only bandwidth probe: streams `bytes` of `buf` (16-byte aligned device memory, caller-owned, not
+ * modified) through every SM and XORs what it read into `sink` (>= 4 * 148 * 4 bytes). bench.py times it over
+ * a slice of the KV pool much larger than L2 to report what a purely reading kernel reaches on this GPU (the
+ * driver's HBM peak is a copy measurement). Reference counterpart: none. */
+int kb_hbm_read_probe(const void* buf, size_t bytes, void* sink, size_t sink_bytes, kb_stream stream);
+
 const char* kb_last_error(void);
 int kb_abi_version(void);
 /* Number of kernels this library has enqueued since load (bench.py's gpu_launches). */

@@ -327,6 +327,47 @@ __global__ void select_tokens_kernel(int* __restrict__ dst, const int* __restric
 }
 
 // ---------------------------------------------------------------------------------------------
+// hbm_read_probe: a read-only stream over a caller buffer (16-byte loads, eight in flight per thread, persistent
+// grid), one 4-byte result per block so the loads cannot be optimised away. bench.py times it over a slice of
+// the KV pool far larger than L2 to know what a kernel that ONLY reads can reach on this GPU — the driver's
+// measured HBM peak is a copy (half reads, half writes), which the decode-attention kernel exceeds.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512)
+hbm_read_probe_kernel(const uint4* __restrict__ src, size_t n16, uint32_t* __restrict__ sink) {
+    uint32_t acc = 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 7 * stride < n16; i += 8 * stride) {
+        uint4 v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = __ldcs(src + i + k * stride);      // streaming: no reuse
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc ^= v[k].x ^ v[k].y ^ v[k].z ^ v[k].w;
+    }
+    for (; i < n16; i += stride) {
+        const uint4 v = __ldcs(src + i);
+        acc ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+    acc ^= __shfl_xor_sync(0xffffffffu, acc, 16);
+    if ((threadIdx.x & 31) == 0) atomicXor(&sink[blockIdx.x], acc);
+}
+
+int hbm_read_probe(const void* buf, size_t bytes, void* sink, size_t sink_bytes, cudaStream_t stream) {
+    KB_CHECK(buf && sink && bytes >= 16 && (reinterpret_cast<uintptr_t>(buf) & 15) == 0,
+             "kb_hbm_read_probe: need a 16-byte aligned buffer of at least 16 bytes");
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int blocks = sms * 4;
+    KB_CHECK(sink_bytes >= (size_t)blocks * 4, "kb_hbm_read_probe: sink needs %d bytes", blocks * 4);
+    hbm_read_probe_kernel<<<blocks, 512, 0, stream>>>(reinterpret_cast<const uint4*>(buf), bytes / 16,
+                                                      reinterpret_cast<uint32_t*>(sink));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // host launchers
 // ---------------------------------------------------------------------------------------------
 int select_tokens(int* dst, const int* prev_out, const int* src, int n, int n_prev, cudaStream_t stream) {
@@ -411,6 +452,9 @@ extern "C" int kb_rope_append(void* qkv_f16, const int32_t* cu_seqlens, const in
 extern "C" int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,
                          int32_t* out_tokens, kb_stream stream) {
     return kb::sample(logits, n_seqs, vocab, sampling, out_tokens, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int kb_hbm_read_probe(const void* buf, size_t bytes, void* sink, size_t sink_bytes, kb_stream stream) {
+    return kb::hbm_read_probe(buf, bytes, sink, sink_bytes, reinterpret_cast<cudaStream_t>(stream));
 }
 extern "C" int kb_select_tokens(int32_t* dst, const int32_t* prev_out, const int32_t* src_index, int32_t n,
                                 int32_t n_prev, kb_stream stream) {

@@ -92,6 +92,7 @@ SIGNATURES = {
                                   _i32, _i32, _vp]),
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
     "kb_select_tokens": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp]),
+    "kb_hbm_read_probe": (C.c_int, [_vp, _sz, _vp, _sz, _vp]),
     "kb_set_tensor_parallel": (C.c_int, [_vp, _i32, _i32, ALLREDUCE_FN, _vp]),
     "kb_set_tensor_parallel_peers": (C.c_int, [_vp, _i32, _i32, C.POINTER(TpPeers), _i32, _i32]),
     "kb_allreduce_peers": (C.c_int, [C.POINTER(TpPeers), _i32, _i32, _sz, _sz, _i32, C.c_uint32, _i32, _vp]),
@@ -299,3 +300,13 @@ def select_tokens(dst, prev_out, src_index, stream=None):
     check(load().kb_select_tokens(_ptr(dst), _ptr(prev_out), _ptr(src_index), dst.numel(), prev_out.numel(),
                                   _stream() if stream is None else stream), "kb_select_tokens")
     return dst
+
+
+def hbm_read_probe(buf, sink=None):
+    """Enqueue one read-only pass over `buf` (a CUDA tensor); returns the bytes read. See kb_hbm_read_probe."""
+    import torch
+    if sink is None:
+        sink = torch.zeros(4 * 160, dtype=torch.int32, device=buf.device)
+    n = buf.numel() * buf.element_size()
+    check(load().kb_hbm_read_probe(_ptr(buf), n, _ptr(sink), sink.numel() * 4, _stream()), "kb_hbm_read_probe")
+    return n
