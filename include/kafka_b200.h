@@ -236,7 +236,11 @@ int kb_gemm(const void* a_bf16, const void* w_bf16, void* out, const float* resi
 /* Same, with the tile forced: tile_n in {64, 128, 256} = one CTA per 128 x tile_n tile; a negative
  * multiple of 16 in [-256, -32] = a CTA pair (tcgen05 cta_group::2) per 256 x |tile_n| tile; {1, 2, 4} =
  * the small-M kernel (M <= 128: operands swapped so the 128 MMA rows are weight rows, that many CTAs
- * per tile sharing K through a cluster and adding their partial sums in rank order); 0 = heuristic
+ * per tile sharing K through a cluster and adding their partial sums in rank order); -(1024 * s + bn) with
+ * s in {2, 4} = the CTA-pair kernel with split-K: every 256 x bn tile is computed by s work units, each over 1/s
+ * of K, that add their partial sums to `out` one after the other in a fixed order (only for the in-place
+ * residual epilogue, out == resid; the heuristic picks it for the decode step's O and down projections);
+ * 0 = heuristic
  * (small-M kernel for M <= 32, and up to 64 for N >= 16384 or K >= 8192; else the cheapest tile under a per-SM ingress cost model). For tuning
  * and for tests that must cover every instantiation. */
 int kb_gemm_ex(const void* a_bf16, const void* w_bf16, void* out, const float* resid, int32_t M, int32_t N,

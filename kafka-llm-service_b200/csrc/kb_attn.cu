@@ -173,12 +173,18 @@ attn_decode_kernel(const __half* __restrict__ q, int q_stride, const __half* __r
     uint8_t* ring = smem;
     float* merge = reinterpret_cast<float*>(smem + Cfg::RING_BYTES);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::RING_BYTES + Cfg::MERGE_FLOATS * 4);
-    pdl_wait();      // kv_lens, q and the appended K/V come from the kernels before this one
-    pdl_launch();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
     const int kvh = blockIdx.x, seq = blockIdx.y, split = blockIdx.z;
+    // private set-up (this warp's barriers) overlaps the tail of the previous kernel ...
+    if (lane == 0) {
+        uint64_t* b = bars + warp * S;
+        for (int s = 0; s < S; ++s) mbar_init(&b[s], 1);
+        fence_mbar_init();
+    }
+    pdl_wait();      // ... kv_lens, q and the appended K/V come from the kernels before this one
+    pdl_launch();
 
     const int kv_len = kv_lens[seq] + kv_len_bias;
     const int n_half = (kv_len + NT - 1) / NT;
@@ -187,10 +193,6 @@ attn_decode_kernel(const __half* __restrict__ q, int q_stride, const __half* __r
 
     uint64_t* my_bars = bars + warp * S;
     uint8_t* my_ring = ring + warp * (S * 2 * Cfg::TILE_BYTES);
-    if (lane == 0) {
-        for (int s = 0; s < S; ++s) mbar_init(&my_bars[s], 1);
-        fence_mbar_init();
-    }
     __syncthreads();
 
     // Q fragments: rows g < GROUP are the query heads of this KV head; the rest are zero.

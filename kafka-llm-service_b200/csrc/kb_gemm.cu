@@ -22,6 +22,7 @@
 // Algorithmic FLOPs per launch = 2*M*N*K.
 #include "kb_common.cuh"
 
+#include <atomic>
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -321,6 +322,31 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // rows): the host picks it per shape so that the number of tiles fills whole rounds of the 74 CTA pairs —
 // with fixed 256-wide tiles the decode step's gate/up projection (224 tiles) spent a quarter of its time
 // in a fourth round that held 2 tiles (tools/gemm_trace.py).
+// Split-K for the in-place residual epilogue (x += A W^T: the O and down projections, N = hidden).
+//
+// At M = 512 those two launches have only 2 x N/256 = 32 tiles of 256 x 256 for 74 CTA pairs; filling the GPU with
+// narrower tiles (bn = 112) makes every tile pay 16 KB of A per 7 KB of W, and the main loop runs at the
+// shared-memory ingress rate (~50 B/clk per SM), not at the tensor rate. Instead the K range of a wide tile is
+// cut into `splits` work units that run on different CTA pairs at the same time. Their partial sums meet in
+// the output itself: every unit adds its accumulator to x with red.global.add — but in a FIXED order, unit s
+// after unit s - 1, so that the fp32 result does not depend on which unit finished first (the engine's outputs
+// are bit-reproducible, tests/test_gpu_full_size.py). The order is kept per (tile, CTA of the pair, epilogue
+// warp): warp w of unit s touches exactly the elements warp w of unit s - 1 touched, so one producer warp
+// hands over to one consumer warp through one 64-bit word: the producer publishes `tag + s + 1` after its
+// additions (atomicMax: words only ever grow, so launches on other streams that share the array can disturb the
+// order of two additions but can never make a waiter miss its value), the consumer spins until it sees it.
+// `tag` is unique per launch (host counter), nothing is ever reset. Units are scheduled in index order
+// (unit = tile * splits + s), every dependence points to a lower index and all clusters of the persistent grid
+// are resident together, so the wait cannot deadlock.
+constexpr int SPLITK_MAX_TILES = 1024;
+static __device__ unsigned long long g_splitk_flags[SPLITK_MAX_TILES * 8];   // [tile][cta of the pair][epilogue warp]
+
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
 struct Gemm2Cfg {
     static constexpr int BN_MAX = 256;
     static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
@@ -335,7 +361,8 @@ struct Gemm2Cfg {
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, void* out,
-                         const float* resid, int M, int N, int K, int bn, uint32_t is_bf16) {
+                         const float* resid, int M, int N, int K, int bn, uint32_t is_bf16, int splits,
+                         unsigned long long tag) {
     using Cfg = Gemm2Cfg;
     const int BN = bn;
     const int half_n = bn >> 1;                       // B rows staged by one CTA
@@ -359,6 +386,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const int num_n = (N + BN - 1) / BN;
     const int num_tiles = num_mp * num_n;
     const int num_k = K / GEMM_BK;
+    const int num_units = num_tiles * splits;         // unit = tile * splits + (which part of K)
+    const int kps = num_k / splits;                   // k-blocks per unit (host: num_k % splits == 0)
 
     if (warp == 0) {
         if (elect_one()) {
@@ -395,12 +424,14 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+            for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
+                const int tile = unit / splits;
+                const int kb_lo = (unit - tile * splits) * kps;
                 const int mp = tile % num_mp;
                 const int n_blk = tile / num_mp;
                 const int row0 = mp * 2 * GEMM_BM + (int)cta * GEMM_BM;        // this CTA's 128 rows of A
                 const int nrow0 = n_blk * BN + (int)cta * half_n;              // this CTA's half of B
-                for (int kb = 0; kb < num_k; ++kb) {
+                for (int kb = kb_lo; kb < kb_lo + kps; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
                     uint8_t* sb = sa + Cfg::A_BYTES;
@@ -419,15 +450,15 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+            for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
                 mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::BN_MAX);
-                for (int kb = 0; kb < num_k; ++kb) {
+                for (int kb = 0; kb < kps; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     if (kb == 0) KB_TRACE(2);        // first operands landed
-                    if (kb == num_k - 1) KB_TRACE(3);  // last operands landed
+                    if (kb == kps - 1) KB_TRACE(3);  // last operands landed
                     const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
                     const uint64_t adesc = make_sw128_kmajor_desc(sa);
                     const uint64_t bdesc = make_sw128_kmajor_desc(sa + Cfg::A_BYTES);
@@ -437,7 +468,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                                       (uint32_t)((kb | k) != 0));
                     }
                     umma_commit_2cta(&empty_bar[stage]);
-                    if (kb == num_k - 1) umma_commit_2cta(&tmem_full_bar[acc]);
+                    if (kb == kps - 1) umma_commit_2cta(&tmem_full_bar[acc]);
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                 }
                 acc ^= 1;
@@ -449,7 +480,9 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const int ew = warp - 4;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        for (int unit = cluster_id; unit < num_units; unit += num_clusters) {
+            const int tile = unit / splits;
+            const int part = unit - tile * splits;
             const int mp = tile % num_mp;
             const int n_blk = tile / num_mp;
             mbar_wait(&tmem_full_bar[acc], acc_phase);
@@ -457,18 +490,46 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             if (threadIdx.x == 128) KB_TRACE(4);     // accumulator complete
             const int row = mp * 2 * GEMM_BM + (int)cta * GEMM_BM + ew * 32 + lane;
             const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * Cfg::BN_MAX);
+            // Two register sets: the tcgen05.ld of chunk c + 1 is in flight while chunk c is converted and stored
+            // (with one set the load of the next chunk queued behind the 8 vector reductions of the previous one).
+            uint32_t ra[32], rb[32];
+            tmem_ld_32x32(t_row, ra);
+            unsigned long long* flag = nullptr;
+            if (splits > 1) {
+                // ordered split-K (see g_splitk_flags): wait until the unit that covers the K range before ours
+                // has added its partial sums to these rows
+                flag = &g_splitk_flags[((size_t)tile * 2 + cta) * 4 + ew];
+                if (part > 0) {
+                    if (lane == 0)
+                        while (ld_acquire_u64(flag) < tag + (unsigned long long)part) { }
+                    __syncwarp();
+                }
+            }
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                uint32_t r[32];
-                tmem_ld_32x32(t_row + (uint32_t)c, r);
-                tmem_ld_wait();
-                const int col0 = n_blk * BN + c;
-                const int ncols = (N - col0 < BN - c) ? N - col0 : BN - c;
-                if (row < M && ncols > 0) epilogue_store32<EPI>(r, out, resid, row, col0, N, ncols);
+            for (int c = 0; c < BN; c += 64) {
+                tmem_ld_wait();                                           // ra = chunk c
+                if (c + 32 < BN) tmem_ld_32x32(t_row + (uint32_t)(c + 32), rb);
+                {
+                    const int col0 = n_blk * BN + c;
+                    const int ncols = (N - col0 < BN - c) ? N - col0 : BN - c;
+                    if (row < M && ncols > 0) epilogue_store32<EPI>(ra, out, resid, row, col0, N, ncols);
+                }
+                if (c + 32 < BN) {
+                    tmem_ld_wait();                                       // rb = chunk c + 32
+                    if (c + 64 < BN) tmem_ld_32x32(t_row + (uint32_t)(c + 64), ra);
+                    const int col0 = n_blk * BN + c + 32;
+                    const int ncols = (N - col0 < BN - c - 32) ? N - col0 : BN - c - 32;
+                    if (row < M && ncols > 0) epilogue_store32<EPI>(rb, out, resid, row, col0, N, ncols);
+                }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(&tmem_empty_bar[acc], 0);   // the leader's barrier
+            if (splits > 1 && part + 1 < splits) {
+                __threadfence();                     // this lane's additions are performed before the hand-over
+                __syncwarp();
+                if (lane == 0) atomicMax(flag, tag + (unsigned long long)part + 1ull);
+            }
             if (threadIdx.x == 128) KB_TRACE(5);     // this warp's rows stored
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
@@ -867,9 +928,11 @@ static int dispatch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, void* ou
     return KB_ERR_INVALID;
 }
 
+static std::atomic<unsigned long long> g_splitk_epoch{1};   // tag of a split-K launch = epoch * 16
+
 template <int EPI>
 static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
-                            int N, int K, int bn, uint32_t is_bf16, cudaStream_t stream) {
+                            int N, int K, int bn, int splits, uint32_t is_bf16, cudaStream_t stream) {
     using Cfg = Gemm2Cfg;
     static bool configured[64] = {};
     auto kern = gemm_tcgen05_2cta_kernel<EPI>;
@@ -880,26 +943,36 @@ static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void
         configured[dev & 63] = true;
     }
     const int num_tiles = ((M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((N + bn - 1) / bn);
+    if (splits > 1) {
+        KB_CHECK(EPI == KB_EPI_RESID_F32 && resid == out, "kb_gemm: split-K needs the in-place residual epilogue");
+        KB_CHECK((K / GEMM_BK) % splits == 0 && splits <= 8, "kb_gemm: K / 64 = %d k-blocks do not divide into %d parts",
+                 K / GEMM_BK, splits);
+        KB_CHECK(num_tiles <= SPLITK_MAX_TILES, "kb_gemm: %d tiles exceed the split-K hand-over table (%d)", num_tiles,
+                 SPLITK_MAX_TILES);
+    }
+    const unsigned long long tag = splits > 1 ? g_splitk_epoch.fetch_add(1) * 16ull : 0ull;
+    const int num_units = num_tiles * splits;
     const int max_clusters = num_sms() / 2;
-    const int clusters = num_tiles < max_clusters ? num_tiles : max_clusters;
+    const int clusters = num_units < max_clusters ? num_units : max_clusters;
     KB_CUDA(launch_kernel(kern, dim3(2 * clusters), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, out, resid, M,
-                          N, K, bn, is_bf16));
+                          N, K, bn, is_bf16, splits, tag));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
 }
 
 static int dispatch_epi_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
-                             int N, int K, int bn, int epi, uint32_t ab, cudaStream_t stream) {
+                             int N, int K, int bn, int splits, int epi, uint32_t ab, cudaStream_t stream) {
     switch (epi) {
-        case KB_EPI_BF16: return launch_gemm_2cta<KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
-        case KB_EPI_F32: return launch_gemm_2cta<KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
-        case KB_EPI_RESID_F32: return launch_gemm_2cta<KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
+        case KB_EPI_BF16: return launch_gemm_2cta<KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
+        case KB_EPI_F32: return launch_gemm_2cta<KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
+        case KB_EPI_RESID_F32:
+            return launch_gemm_2cta<KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, bn, splits, ab, stream);
         case KB_EPI_SWIGLU_BF16:
-            return launch_gemm_2cta<KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
+            return launch_gemm_2cta<KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
         case KB_EPI_SWIGLU_F16:
-            return launch_gemm_2cta<KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
-        case KB_EPI_F16: return launch_gemm_2cta<KB_EPI_F16>(tmA, tmB, out, resid, M, N, K, bn, ab, stream);
+            return launch_gemm_2cta<KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
+        case KB_EPI_F16: return launch_gemm_2cta<KB_EPI_F16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
     }
     set_error("kb_gemm: unknown epilogue %d", epi);
     return KB_ERR_INVALID;
@@ -996,17 +1069,25 @@ static int dispatch_skinny(const void* a, const void* w, void* out, const float*
 }
 
 // Tile choice: minimise the time of the busiest CTA (or CTA pair) under the static persistent schedule.
-// Returns BN for the 1-CTA kernel, -BN for the CTA-pair kernel.
-static int pick_bn(int M, int N) {
-    static int forced = -1;
+// Returns BN for the 1-CTA kernel, -BN for the CTA-pair kernel; *splits_out > 1 = split-K work units (only
+// offered when `can_split`: the in-place residual epilogue, see g_splitk_flags).
+static int pick_bn(int M, int N, int K, bool can_split, int* splits_out) {
+    *splits_out = 1;
+    static int forced = -1, no_split = -1;
     if (forced < 0) {
         const char* s = getenv("KB_GEMM_BN");
         forced = s ? atoi(s) : 0;
+        no_split = getenv("KB_GEMM_NO_SPLITK") != nullptr;
     }
     if (forced == 64 || forced == 128 || forced == 256 || (forced <= -32 && forced >= -256 && forced % 16 == 0))
         return forced;
     const int sms = num_sms();
     const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
+    const int num_k = K / GEMM_BK;
+    // cycles per k-block of one CTA: `rows` 128-byte rows of operands staged by TMA at ~50 B/clk per SM
+    // (measured: tools/gemm_trace.py, profiles/r01_gemm_bench.md) against 2 * bn cycles of MMA
+    auto kblock = [](int rows, int bn) { const long ing = (long)rows * 128 * 100 / 5000; return ing > 2L * bn ? ing : 2L * bn; };
+    auto epilogue = [](int bn) { return 1200L + 6L * bn; };
     long best_cost = -1;
     int best = 128;
     const int cands[3] = {256, 128, 64};
@@ -1014,26 +1095,27 @@ static int pick_bn(int M, int N) {
         const int bn = cands[i];
         const long tiles = (long)num_m * ((N + bn - 1) / bn);
         const long per_cta = (tiles + sms - 1) / sms;
-        // Per k-block a 1-CTA tile brings (16 KB of A + bn*128 B of B) into shared memory by TMA at
-        // ~50-64 B/clk per SM: ~(256 + 2 bn) cycles, always more than the 2*bn cycles the MMA itself
-        // needs (measured: tools/gemm_bench.py, tools/gemm_trace.py, profiles/r01_gemm_bench.md). Wide
-        // tiles win unless they leave SMs idle.
-        const long cost = per_cta * (256 + 2 * bn);
+        // a 1-CTA tile brings 128 rows of A + bn rows of B per k-block: wide tiles win unless they leave SMs idle
+        const long cost = per_cta * (num_k * kblock(128 + bn, bn) + epilogue(bn));
         if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
     }
     if (M > GEMM_BM) {
-        // CTA pair, 256 x bn tile: each CTA stages 16 KB of A and bn*64 B of B per k-block -> 256 + bn
-        // cycles of TMA ingress against 2 bn cycles of MMA
-        // ... any multiple of 16 (run-time tile width): take the width whose tile count wastes the least
-        // of the last round; wider wins ties (less A re-read)
+        // CTA pair, 256 x bn tile: each CTA stages 128 rows of A and bn / 2 rows of B per k-block.
+        // ... any multiple of 16 (run-time tile width): take the width whose unit count wastes the least of the
+        // last round; wider wins ties (less A re-read). With split-K a unit is 1 / splits of a tile's K range and
+        // the epilogues of a tile's units run one after the other.
         const int num_mp = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
         const int pairs = sms / 2;
-        for (int bn = 256; bn >= 64; bn -= 16) {
-            const long tiles = (long)num_mp * ((N + bn - 1) / bn);
-            const long per_pair = (tiles + pairs - 1) / pairs;
-            const long kblock = (2 * bn > 256 + bn) ? 2 * bn : 256 + bn;
-            const long cost = per_pair * kblock;
-            if (cost < best_cost) { best_cost = cost; best = -bn; }
+        for (int splits = 1; splits <= (can_split && !no_split ? 4 : 1); splits *= 2) {
+            if (num_k % splits != 0 || num_k / splits < 8) break;
+            for (int bn = 256; bn >= 64; bn -= 16) {
+                const long tiles = (long)num_mp * ((N + bn - 1) / bn);
+                if (splits > 1 && tiles > SPLITK_MAX_TILES) continue;
+                const long rounds = (tiles * splits + pairs - 1) / pairs;
+                const long cost = rounds * ((num_k / splits) * kblock(128 + bn / 2, bn) + epilogue(bn)) +
+                                  (splits - 1) * epilogue(bn);
+                if (cost < best_cost) { best_cost = cost; best = -bn; *splits_out = splits; }
+            }
         }
     }
     return best;
@@ -1052,6 +1134,12 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     KB_CHECK((reinterpret_cast<uintptr_t>(a) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(out) & 15) == 0,
              "kb_gemm: pointers must be 16-byte aligned");
+    int forced_splits = 1;
+    if (tile_n <= -1024) {          // -(1024 * splits + bn): CTA-pair tile of width bn with split-K (tests, tuning)
+        forced_splits = (-tile_n) / 1024;
+        tile_n = -((-tile_n) % 1024);
+        KB_CHECK(forced_splits == 2 || forced_splits == 4, "kb_gemm: split-K takes 2 or 4 parts (got %d)", forced_splits);
+    }
     KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256 ||
                  (tile_n <= -32 && tile_n >= -256 && tile_n % 16 == 0) || (tile_n >= 1 && tile_n <= 4 && tile_n != 3),
              "kb_gemm: tile_n=%d not in {0, 64, 128, 256}, a negative multiple of 16 in [-256, -32], or 1 / 2 / 4 "
@@ -1068,14 +1156,18 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
         // tile_n = 0: CTAs per tile chosen by skinny_plan; 1 / 2 / 4: forced (benchmarks, tests)
         return dispatch_skinny(a, w, out, resid, M, N, K, epi, tile_n, a_is_bf16, stream);
     }
-    const int bn = tile_n ? tile_n : pick_bn(M, N);
+    int splits = forced_splits;
+    const bool in_place = epi == KB_EPI_RESID_F32 && resid == reinterpret_cast<const float*>(out);
+    KB_CHECK(forced_splits == 1 || (in_place && tile_n < 0),
+             "kb_gemm: split-K needs the CTA-pair kernel and the in-place residual epilogue (KB_EPI_RESID_F32, out == resid)");
+    const int bn = tile_n ? tile_n : pick_bn(M, N, K, in_place, &splits);
     CUtensorMap tmA, tmB;
     int rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, GEMM_BM, &tmA);
     if (rc) return rc;
     if (bn < 0) {   // CTA pair: every CTA stages half of the tile's B rows
         rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)(-bn / 2), &tmB);
         if (rc) return rc;
-        return dispatch_epi_2cta(tmA, tmB, out, resid, M, N, K, -bn, epi, a_is_bf16, stream);
+        return dispatch_epi_2cta(tmA, tmB, out, resid, M, N, K, -bn, splits, epi, a_is_bf16, stream);
     }
     rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)bn, &tmB);
     if (rc) return rc;

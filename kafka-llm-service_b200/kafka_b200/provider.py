@@ -117,6 +117,14 @@ class B200LLMProvider(LLMProvider):
         self.default_max_tokens = default_max_tokens
         self.thread_id = thread_id
         self.seed = seed
+        # token counts summed over this object's completions (the server builds one provider per request, so
+        # this is the request's usage, agent tool rounds included)
+        self.usage_total: Dict[str, int] = {"prompt_tokens": 0, "completion_tokens": 0, "total_tokens": 0,
+                                            "cached_tokens": 0}
+
+    def _add_usage(self, usage: Dict[str, int]) -> None:
+        for k in self.usage_total:
+            self.usage_total[k] += int(usage.get(k, 0))
 
     # ---- helpers -------------------------------------------------------------------------------
     def render(self, messages: List[Message], tools: Optional[List[Dict[str, Any]]]) -> List[int]:
@@ -141,6 +149,23 @@ class B200LLMProvider(LLMProvider):
                     return k
         return 0
 
+    def count_prompt_tokens(self, messages: List[Any]) -> int:
+        """Tokens the prompt of `messages` (Message objects or OpenAI-style dicts) would take, tool schemas of
+        the most recent call included — what a compaction provider needs to know whether its result fits."""
+        msgs = [m if isinstance(m, Message) else
+                Message(role=m.get("role", "user"), content=m.get("content"), name=m.get("name"),
+                        tool_calls=m.get("tool_calls"), tool_call_id=m.get("tool_call_id")) for m in messages]
+        return len(self.render(msgs, getattr(self, "_last_tools", None)))
+
+    def compaction_provider(self, keep_count: int = 50, fraction: float = 0.75, reserve: int = 0):
+        """The offline compaction for this provider's model (kafka_b200/compaction.py): the reference's
+        truncation rule, continued until the prompt takes at most `fraction` of the context minus `reserve`
+        tokens for the answer. Pass it to the agent as `context_compaction_provider`."""
+        from .compaction import TruncationCompactionProvider
+        budget = max(64, int(self.engine.max_pos * fraction) - reserve)
+        return TruncationCompactionProvider(keep_count=keep_count, count_tokens=self.count_prompt_tokens,
+                                            token_budget=budget)
+
     # ---- the plugin API ------------------------------------------------------------------------
     async def stream_completion(self, messages: List[Message], *, temperature: Optional[float] = None,
                                 max_tokens: Optional[int] = None, stop: Optional[List[str]] = None,
@@ -154,6 +179,7 @@ class B200LLMProvider(LLMProvider):
         req = None
         try:
             tools = await self.get_tools()
+            self._last_tools = tools                          # count_prompt_tokens() sizes prompts like this call
             prompt = self.render(validated, tools)
             temp = self.default_temperature if temperature is None else float(temperature)
             limit = max_tokens if max_tokens is not None else (self.default_max_tokens or 512)
@@ -182,10 +208,17 @@ class B200LLMProvider(LLMProvider):
             markers = [s for s in (stop or []) if s] + ([TOOL_OPEN] if tools else [])
             hold = max((len(s) for s in markers), default=1) - 1   # longest partial marker a tail can be
             collecting = -1                            # >= 0: index where a tool-call block opened
+            n_tokens = 0
+
+            def cut_short():       # the stream ends before the engine's own finish event (stop string, tool call)
+                req.cancelled = True
+                self._add_usage({"prompt_tokens": len(prompt), "completion_tokens": n_tokens,
+                                 "total_tokens": len(prompt) + n_tokens, "cached_tokens": req.n_cached})
             while True:
                 ev = await events.get()
                 kind = ev[0]
                 if kind == "token":
+                    n_tokens += 1
                     text += decoder.push(ev[1])
                     if collecting >= 0:
                         end = text.find(TOOL_CLOSE, collecting)
@@ -196,7 +229,7 @@ class B200LLMProvider(LLMProvider):
                             yield StreamChunk(content=text[emitted:], model=model, id=completion_id)
                             emitted, collecting = len(text), -1
                             continue
-                        req.cancelled = True
+                        cut_short()
                         for ch in tool_call_chunks(calls, model, completion_id):
                             yield ch
                         yield StreamChunk(finish_reason="tool_calls", model=model, id=completion_id)
@@ -211,7 +244,7 @@ class B200LLMProvider(LLMProvider):
                             continue
                         if cut > emitted:
                             yield StreamChunk(content=text[emitted:cut], model=model, id=completion_id)
-                        req.cancelled = True
+                        cut_short()
                         yield StreamChunk(finish_reason="stop", model=model, id=completion_id)
                         return
                     # keep back only a tail that is the beginning of a marker (usually nothing)
@@ -223,6 +256,7 @@ class B200LLMProvider(LLMProvider):
                     text += decoder.flush()
                     if len(text) > emitted:
                         yield StreamChunk(content=text[emitted:], model=model, id=completion_id)
+                    self._add_usage(ev[2])
                     if usage_out is not None:
                         usage_out.update(ev[2])
                     yield StreamChunk(finish_reason=ev[1], model=model, id=completion_id)

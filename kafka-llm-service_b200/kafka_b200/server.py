@@ -111,7 +111,12 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
     def make_agent(model: str, thread_id: Optional[str]) -> StreamingAgent:
         tool_provider = LocalToolProvider(list(tools or []))
         provider = provider_factory(model, tool_provider=tool_provider, thread_id=thread_id)
-        return StreamingAgent(provider, tool_provider, system_prompt=system_prompt)
+        # context overflow -> offline compaction (truncation at safe points until the prompt fits the model's
+        # context, kafka_b200/compaction.py) -> one retry; the reference builds a summarising provider here,
+        # which needs a remote LLM (src/kafka/v1.py:185-194)
+        compaction = provider.compaction_provider() if hasattr(provider, "compaction_provider") else None
+        return StreamingAgent(provider, tool_provider, system_prompt=system_prompt,
+                              context_compaction_provider=compaction)
 
     def make_runner(model: str, thread_id: str) -> ThreadRunner:
         agent = make_agent(model, thread_id)
@@ -159,13 +164,16 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
             yield _sse({"error": {"message": str(e), "type": "agent_error"}})
             yield _sse("[DONE]")
 
-    async def collect(events: AsyncGenerator[Dict[str, Any], None], model: str) -> Dict[str, Any]:
+    async def collect(events: AsyncGenerator[Dict[str, Any], None], model: str, provider: Any = None) -> Dict[str, Any]:
         final, finish, usage = "", "stop", None
         async for ev in events:
             if ev.get("type") == "agent_done":
                 final = ev.get("final_content", "") or ""
             elif ev.get("choices") and ev["choices"][0].get("finish_reason") in ("stop", "length"):
                 finish = ev["choices"][0]["finish_reason"]
+        total = getattr(provider, "usage_total", None)
+        if total:                                    # the request's real token counts, tool rounds included
+            usage = {k: int(total.get(k, 0)) for k in ("prompt_tokens", "completion_tokens", "total_tokens")}
         return {"id": f"chatcmpl-{uuid.uuid4().hex[:24]}", "object": "chat.completion", "created": int(time.time()),
                 "model": model, "choices": [{"index": 0, "message": {"role": "assistant", "content": final},
                                              "finish_reason": finish}],
@@ -182,7 +190,7 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
                                      headers={"Cache-Control": "no-cache", "Connection": "keep-alive",
                                               "X-Accel-Buffering": "no"})
         try:
-            return await collect(events, request.model)
+            return await collect(events, request.model, runner.agent.llm_provider)
         except Exception as e:
             raise HTTPException(status_code=500, detail=str(e))
 
@@ -195,7 +203,7 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
         if request.stream:
             return StreamingResponse(completion_stream(events, request.model), media_type="text/event-stream")
         try:
-            return await collect(events, request.model)
+            return await collect(events, request.model, agent.llm_provider)
         except Exception as e:
             raise HTTPException(status_code=500, detail=str(e))
 

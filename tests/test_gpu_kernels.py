@@ -198,16 +198,47 @@ def test_gemm_gate_up_at_llama3_8b_size(kb, cuda, tile_n):
     torch.testing.assert_close(h.float(), want, rtol=2e-3, atol=2e-3)      # fp16 output: 2^-11 relative
 
 
-@pytest.mark.parametrize("tile_n", [0, -112, -256, 128])
+SPLIT2, SPLIT4 = 2 * 1024, 4 * 1024      # kb_gemm_ex: tile_n = -(1024 * splits + bn) forces split-K on the CTA-pair kernel
+
+
+@pytest.mark.parametrize("tile_n", [0, -112, -256, 128, -(SPLIT2 + 240), -(SPLIT4 + 256), -(SPLIT2 + 112)])
 def test_gemm_down_in_place_residual_at_llama3_8b_size(kb, cuda, tile_n):
-    """512 x 4 096 x 14 336, x += h W^T in place (red.global.add epilogue), K = 14 336."""
+    """512 x 4 096 x 14 336, x += h W^T in place (red.global.add epilogue), K = 14 336; the heuristic (split-K in
+    2 parts on 256 x 240 tiles), plain tiles and forced split-K."""
     M, N, K = 512, 4096, 14336
     a, w = _llama_operands(M, N, K, 32, cuda)
     g = torch.Generator(device=cuda).manual_seed(33)
-    x = torch.randn(M, N, generator=g, device=cuda) * 4
-    want = x + _fp32_matmul(a, w)
+    x0 = torch.randn(M, N, generator=g, device=cuda) * 4
+    want = x0 + _fp32_matmul(a, w)
+    x = x0.clone()
     kb.gemm(a, w, kb.EPI_RESID_F32, resid=x, out=x, tile_n=tile_n)
     torch.testing.assert_close(x, want, rtol=2e-3, atol=2e-3)
+    # the partial sums of a tile are added in a fixed order: every run gives the same bits
+    for _ in range(3):
+        y = x0.clone()
+        kb.gemm(a, w, kb.EPI_RESID_F32, resid=y, out=y, tile_n=tile_n)
+        assert torch.equal(x, y)
+
+
+@pytest.mark.parametrize("M,N,K,tile_n", [(300, 1000, 512, -(SPLIT2 + 128)), (512, 4096, 4096, -(SPLIT2 + 240)),
+                                          (512, 4096, 4096, -(SPLIT4 + 256)), (1000, 768, 1024, -(SPLIT2 + 64)),
+                                          (200, 4096, 14336, 0), (130, 4096, 4096, 0)])
+def test_gemm_split_k_ragged_and_multi_round(kb, cuda, M, N, K, tile_n):
+    """Split-K work units: partial M / N tiles, more units than CTA pairs (several rounds: a unit may wait for a
+    unit of an earlier round), and the shapes where the heuristic picks it on its own."""
+    a, w = _llama_operands(M, N, K, 41, cuda)
+    g = torch.Generator(device=cuda).manual_seed(42)
+    x0 = torch.randn(M, N, generator=g, device=cuda)
+    want = x0 + _fp32_matmul(a, w)
+    x = x0.clone()
+    kb.gemm(a, w, kb.EPI_RESID_F32, resid=x, out=x, tile_n=tile_n)
+    torch.testing.assert_close(x, want, rtol=2e-3, atol=2e-3)
+    y = x0.clone()
+    kb.gemm(a, w, kb.EPI_RESID_F32, resid=y, out=y, tile_n=tile_n)
+    assert torch.equal(x, y)
+    if tile_n < -1024:      # split-K is only defined for the in-place residual epilogue
+        with pytest.raises(kb.KafkaB200Error, match="in-place residual"):
+            kb.gemm(a, w, kb.EPI_F32, tile_n=tile_n)
 
 
 @pytest.mark.parametrize("M,tile_n", [(512, 0), (512, -256), (200, 0), (8, 0), (8, 4), (1, 0)])

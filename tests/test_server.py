@@ -179,3 +179,36 @@ def test_config1_thread_replay_echo(tmp_path):
             assert len(msgs) == 16 and [m.role for m in msgs] == ["user", "assistant"] * 8
             assert len(await store.list_threads()) == 64
     asyncio.run(go())
+
+
+def test_non_streaming_response_carries_real_usage(fake_engine_app):
+    async def go():
+        async with _client(fake_engine_app) as c:
+            r = await c.post("/v1/threads/U1/chat/completions",
+                             json={"model": "tiny-test", "temperature": 0, "max_tokens": 7,
+                                   "messages": [{"role": "user", "content": "count my tokens"}]})
+            u = r.json()["usage"]
+            assert u["completion_tokens"] == 7 and u["prompt_tokens"] > 20
+            assert u["total_tokens"] == u["prompt_tokens"] + u["completion_tokens"]
+    asyncio.run(go())
+
+
+def test_thread_that_outgrew_the_context_is_compacted_and_answered(fake_engine_app):
+    """A stored history longer than the model's context: the provider raises the context-length error, the
+    server's agent compacts by truncation (kafka_b200/compaction.py) and the retry answers."""
+    app = fake_engine_app
+
+    async def go():
+        async with _client(app) as c:
+            msgs = []
+            for i in range(30):
+                msgs += [{"role": "user", "content": f"q{i} " + "x" * 40}, {"role": "assistant", "content": f"a{i} " + "y" * 40}]
+            for m in msgs:
+                assert (await c.post("/v1/threads/C1/messages", json=m)).status_code == 200
+            r = await c.post("/v1/threads/C1/chat/completions",
+                             json={"model": "tiny-test", "temperature": 0, "max_tokens": 6,
+                                   "messages": [{"role": "user", "content": "still there?"}]})
+            body = r.json()
+            assert r.status_code == 200 and len(body["choices"][0]["message"]["content"]) == 6
+            assert body["usage"]["prompt_tokens"] <= int(0.75 * 2048)
+    asyncio.run(go())
