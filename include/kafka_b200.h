@@ -140,7 +140,8 @@ int kb_set_tensor_parallel(kb_engine* e, int32_t tp_rank, int32_t tp_size, kb_al
  * align256(max_tokens * hidden * 4) bytes from offset 0) into the region and replaces the callback;
  * call it after kb_bind_workspace, on every rank.  kb_allreduce_peers is the bare collective (in
  * place, n fp32 at offset_bytes; `epoch` must be odd, equal on all ranks and grow by 2 per call).
- * A rank whose peers do not arrive within ~2 s traps instead of hanging.  No reference counterpart. */
+ * A rank whose peers do not arrive within the region's timeout (default 30 s) traps instead of hanging.
+ * No reference counterpart. */
 #define KB_TP_MAX_RANKS 8
 #define KB_TP_MAX_BLOCKS 128 /* grid bound of the collectives: all blocks must be co-resident (148 SMs) */
 #define KB_TP_FLAG_BYTES 2048
@@ -149,6 +150,15 @@ typedef struct kb_tp_peers {
     void* mc_base;
     size_t bytes;
     size_t flags_offset;
+    /* HOST word that holds the next barrier epoch of this region (odd, starts at 1, +2 per collective), shared by
+     * everything that launches collectives on the region — engines attached to it and direct kb_allreduce_peers
+     * callers — so that an epoch is never reused however often engines are re-attached. NULL: the engine keeps a
+     * private counter (one engine per region only). Never dereferenced on the device. */
+    uint32_t* epoch_counter;
+    /* SM cycles a rank waits for its peers before it gives up (prints the late rank and traps, which ends the
+     * CUDA context of this process). 0 = $KB_TP_TIMEOUT_S seconds (default 30) at ~2 GHz. The collectives assume
+     * nothing else occupies the GPUs: all blocks of all ranks must be running at the same time. */
+    unsigned long long timeout_cycles;
 } kb_tp_peers;
 int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32_t tp_size, const kb_tp_peers* peers,
                                  int32_t blocks /* grid of the collective, 0 = default */,

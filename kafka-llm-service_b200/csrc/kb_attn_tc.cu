@@ -14,16 +14,19 @@
 //   warps 0-7 (softmax): TWO threads per query row (warp w and w + 4 share the TMEM lanes of quarter w & 3):
 //                       each takes 32 of the 64 S columns and 64 of the 128 output dims; tcgen05.ld S_j ->
 //                       causal mask, row max (the two halves meet through shared memory), running sum in fp32,
-//                       P_j = exp2((S_j - m_j) * scale) as fp16 pairs into tensor memory (tcgen05.st) -> then
-//                       fold the finished OT_{j-1} into the register accumulator:
-//                       o = (o + OT_{j-1}) * exp2(m_{j-1} - m_j).  Two warps per scheduler hide each other's
-//                       TMEM / MUFU latencies; the first version (one thread per row) ran at 3 350 cycles per tile.
+//                       P_j = exp2((S_j - m_j) * scale) as fp16 pairs into tensor memory (tcgen05.st).
+//                       Two warps per scheduler hide each other's TMEM / MUFU latencies; the first version (one
+//                       thread per row) ran at 3 350 cycles per tile.
 //
-// The P V product is computed fresh per tile and accumulated in registers, so no thread ever rescales
-// TMEM and no correction pass exists. TMEM: 2 x 64 (S) + 2 x 128 (OT) + 64 (Q) + 2 x 32 (P) = 512 columns;
-// shared memory only holds the K / V ring. Measured per tile (tools/attn_trace.py): ~750 ns of MMA issue
-// (the 12 MMAs retire at about N + 24 cycles each) beside ~770 ns of softmax + fold, partly serialised:
-// ~980 ns per 128 x 64 tile.
+// O = sum_j P_j V_j ACCUMULATES IN TENSOR MEMORY over all tiles (one 128-column accumulator; the MMAs of tile j
+// add to what tiles 0..j-1 left). The running maximum m is raised lazily — only when a tile's maximum exceeds
+// it by more than 2^8 — so most tiles do not touch O at all; when a warp does raise it (the first tiles of a
+// row, rarely afterwards) it waits for the P V product of the previous tile, multiplies its rows of O by
+// exp2(m_old - m_new) in place (tcgen05.ld / tcgen05.st) and only then publishes P_j, which is what the MMA warp
+// waits for before it issues O += P_j V_j. Round 1 computed every tile's product into a fresh accumulator and
+// folded it into registers (two tcgen05.ld of 32 columns + 64 adds per thread per tile: ~300 of the ~770 ns a
+// tile's softmax took, beside ~750 ns of MMA issue; ~980 ns per 128 x 64 tile, tensor pipe 26 % busy).
+// TMEM: 2 x 64 (S) + 128 (O) + 64 (Q) + 2 x 32 (P) = 384 of 512 columns; shared memory only holds the K / V ring.
 //
 // Replaces the mma.sync prefill kernel of kb_attn.cu for head_dim 128 (that one stays for head_dim 64 and
 // as the A/B reference: KB_ATTN_PREFILL_LEGACY=1). Reference counterpart: none (src/llm/portkey.py:379).
@@ -137,9 +140,8 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
     uint64_t* s_full = kv_empty + TC_STAGES;               // [2]
     uint64_t* s_empty = s_full + 2;                        // [2]
     uint64_t* p_full = s_empty + 2;                        // [2]
-    uint64_t* o_full = p_full + 2;                         // [2]
-    uint64_t* o_empty = o_full + 2;                        // [2]
-    uint64_t* q_ready = o_empty + 2;                       // [1]
+    uint64_t* pv_done = p_full + 2;                        // [1] phase j completes when O += P_j V_j has retired
+    uint64_t* q_ready = pv_done + 1;                       // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
     float* mx_x = reinterpret_cast<float*>(kv_s + TC_STAGES * 2 * TC_TILE_BYTES + 256);   // [tile parity][half][row]
 
@@ -153,9 +155,8 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             mbar_init(&s_full[a], 1);
             mbar_init(&s_empty[a], 8);
             mbar_init(&p_full[a], 8);
-            mbar_init(&o_full[a], 1);
-            mbar_init(&o_empty[a], 8);
         }
+        mbar_init(pv_done, 1);
         mbar_init(q_ready, 8);
         fence_mbar_init();
     } else if (warp == 9) {
@@ -179,7 +180,7 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
     const int kv_end = ctx + q_end;
     const int n_tiles = active ? (kv_end + TC_NT - 1) / TC_NT : 0;
     const uint32_t s_tmem = tmem_base;                     // S[a]  at columns a * 64
-    const uint32_t o_tmem = tmem_base + 128;               // OT[a] at columns 128 + a * 128
+    const uint32_t o_tmem = tmem_base + 128;               // O (accumulated over all tiles) at columns 128..255
     const uint32_t q_tmem = tmem_base + 384;               // Q as the A operand of S: 128 fp16 = 64 columns
     const uint32_t p_tmem = tmem_base + 448;               // P[a] as the A operand of OT: 64 fp16 = 32 columns each
 
@@ -223,16 +224,15 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             };
             auto issue_o = [&](int j) {
                 const int st = j % TC_STAGES, a = j & 1;
-                mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));
-                mbar_wait_relaxed(&o_empty[a], (uint32_t)(((j >> 1) & 1) ^ 1));
+                mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));   // P_j written (and O rescaled if m moved)
                 tc_fence_after();
                 const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES), TC_NT * 128, 1024);
-                const uint32_t d = o_tmem + (uint32_t)(a * 128);
                 const uint32_t pa = p_tmem + (uint32_t)(a * 32);
 #pragma unroll
                 for (int k = 0; k < 4; ++k)       // 16 tokens per step: two 8-row groups of the V tile
-                    umma_f16_ts(d, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o, (uint32_t)(k != 0));
-                umma_commit(&o_full[a]);
+                    umma_f16_ts(o_tmem, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o,
+                                (uint32_t)((j | k) != 0));               // tile 0 starts O, every later MMA adds to it
+                umma_commit(pv_done);
                 umma_commit(&kv_empty[st]);       // K_j and V_j are both consumed
             };
             issue_s(0);
@@ -271,12 +271,10 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             __syncwarp();
             if (lane == 0) mbar_arrive(q_ready);
         }
-        float o[64];                                       // output dims [half * 64, +64) of this row
-#pragma unroll
-        for (int d = 0; d < 64; ++d) o[d] = 0.f;
         float m = -INFINITY, l = 0.f;                      // m: shared by both halves; l: this half's columns
         const float sc = TC_LOG2E * rsqrtf((float)TC_HD);
         const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+        const uint32_t o_mine = o_tmem + lane_off + (uint32_t)(half * 64);   // this thread's 64 dims of its row of O
 
         for (int j = 0; j < n_tiles; ++j) {
             const int a = j & 1;
@@ -313,8 +311,8 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             xb[half * TC_ROWS + r] = mx;
             asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
             // Running max in scaled (log2) units, raised LAZILY: it only moves when the tile's max exceeds it by
-            // more than 8, so P stays below 2^8 (fp16: 10 mantissa bits from 2^-14 up, sums in fp32) and most tiles need no
-            // rescaling of the accumulator at all (corr == 1).
+            // more than 8, so P stays below 2^8 (fp16: 10 mantissa bits from 2^-14 up, sums in fp32) and most
+            // tiles leave the accumulated O alone (corr == 1).
             const float tile_mx = fmaxf(mx, xb[(half ^ 1) * TC_ROWS + r]) * sc;
             const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;
             const float corr = ex2_approx(m - m_new);       // m = -inf on the first tile -> 0
@@ -329,70 +327,58 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
                 pw[i] = pack_f16(p0, p1);
             }
             l = l * corr + sum;
-            // P_j -> tensor memory (A operand of OT_j = P_j V_j); OT_{j-2}, the last reader of this buffer, was
-            // folded one iteration ago
+            // P_j -> tensor memory (A operand of O += P_j V_j); the product of tile j - 2, the last reader of this
+            // buffer, has retired: tile j - 1's P could only be published after S_{j-1}, issued behind it
             tmem_st_32x16(p_tmem + lane_off + (uint32_t)(a * 32 + half * 16), pw);
+            // ---- the running max moved: rescale this warp's rows of O in tensor memory (rare) ----
+            if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+                mbar_wait(pv_done, (uint32_t)((j - 1) & 1));       // O holds tiles 0 .. j-1, nothing is in flight
+                tc_fence_after();
+                if (threadIdx.x == 0) KB_ATRACE(j, 6);             // rescale begins
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * corr);
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32), reinterpret_cast<const uint32_t(&)[16]>(u[0]));
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32 + 16), reinterpret_cast<const uint32_t(&)[16]>(u[16]));
+                }
+            }
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&p_full[a]);
+            if (lane == 0) mbar_arrive(&p_full[a]);        // the MMA warp may issue O += P_j V_j
             if (threadIdx.x == 0) KB_ATRACE(j, 5);     // P_j written
-
-            // ---- fold the finished product of tile j - 1:  o = (o + OT_{j-1}) * corr ----
-            if (j > 0) {
-                const int b = (j - 1) & 1;
-                mbar_wait(&o_full[b], (uint32_t)(((j - 1) >> 1) & 1));
-                tc_fence_after();
-                if (threadIdx.x == 0) KB_ATRACE(j, 6); // OT_{j-1} ready
-                const bool rescale = __any_sync(0xffffffffu, corr != 1.f);   // rare after the first tiles
-#pragma unroll
-                for (int c = 0; c < 2; ++c) {
-                    tmem_ld_32x32(o_tmem + lane_off + (uint32_t)(b * 128 + half * 64 + c * 32), u);
-                    tmem_ld_wait();
-                    if (rescale) {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) o[32 * c + i] = (o[32 * c + i] + __uint_as_float(u[i])) * corr;
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) o[32 * c + i] += __uint_as_float(u[i]);
-                    }
-                }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&o_empty[b]);
-            }
         }
         if (n_tiles > 0) {
-            const int b = (n_tiles - 1) & 1;
-            mbar_wait(&o_full[b], (uint32_t)(((n_tiles - 1) >> 1) & 1));
+            mbar_wait(pv_done, (uint32_t)((n_tiles - 1) & 1));
             tc_fence_after();
-            uint32_t u[32];
-#pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                tmem_ld_32x32(o_tmem + lane_off + (uint32_t)(b * 128 + half * 64 + c * 32), u);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 32; ++i) o[32 * c + i] += __uint_as_float(u[i]);
-            }
-            tc_fence_before();
             // the row sum is the sum of both halves' partial sums (same running max in both)
             float* xb = mx_x + (n_tiles & 1) * (2 * TC_ROWS);
             xb[half * TC_ROWS + r] = l;
             asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
             l += xb[(half ^ 1) * TC_ROWS + r];
-            if (valid) {
-                const float inv = 1.f / l;
-                uint16_t* op = out + ((size_t)(tok_begin + tl) * n_heads + head) * TC_HD + half * 64;
+            const float inv = 1.f / l;
+            uint16_t* op = out + ((size_t)(tok_begin + tl) * n_heads + head) * TC_HD + half * 64;
+            uint32_t u[32];
 #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    uint4 w;
-                    w.x = pack_act(o[8 * c + 0] * inv, o[8 * c + 1] * inv, out_f16);
-                    w.y = pack_act(o[8 * c + 2] * inv, o[8 * c + 3] * inv, out_f16);
-                    w.z = pack_act(o[8 * c + 4] * inv, o[8 * c + 5] * inv, out_f16);
-                    w.w = pack_act(o[8 * c + 6] * inv, o[8 * c + 7] * inv, out_f16);
-                    *reinterpret_cast<uint4*>(op + 8 * c) = w;
+            for (int c = 0; c < 2; ++c) {
+                tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
+                tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        uint4 w;
+                        w.x = pack_act(__uint_as_float(u[8 * q4 + 0]) * inv, __uint_as_float(u[8 * q4 + 1]) * inv, out_f16);
+                        w.y = pack_act(__uint_as_float(u[8 * q4 + 2]) * inv, __uint_as_float(u[8 * q4 + 3]) * inv, out_f16);
+                        w.z = pack_act(__uint_as_float(u[8 * q4 + 4]) * inv, __uint_as_float(u[8 * q4 + 5]) * inv, out_f16);
+                        w.w = pack_act(__uint_as_float(u[8 * q4 + 6]) * inv, __uint_as_float(u[8 * q4 + 7]) * inv, out_f16);
+                        *reinterpret_cast<uint4*>(op + 32 * c + 8 * q4) = w;
+                    }
                 }
             }
+            tc_fence_before();
         }
     }
 

@@ -22,6 +22,8 @@
 // Reference counterpart: none (the reference's models sit behind a gateway, src/llm/portkey.py:379).
 #include "kb_common.cuh"
 
+#include <stdlib.h>
+
 namespace kb {
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -100,7 +102,7 @@ __device__ __forceinline__ void meet_ranks(const kb_tp_peers& P, int rank, int w
         const uint32_t* mine = flag_area(P, rank) + peer;
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0)
-            if (clock64() - t0 > 4000000000LL) barrier_timeout(rank, peer, epoch);   // ~2 s: a peer never arrived
+            if (clock64() - t0 > (long long)P.timeout_cycles) barrier_timeout(rank, peer, epoch);   // a peer never arrived
     }
 }
 
@@ -115,7 +117,7 @@ __device__ __forceinline__ void barrier_begin(const kb_tp_peers& P, int rank, in
         if (threadIdx.x == 0) {
             const long long t0 = clock64();
             while ((int32_t)(ld_acquire_gpu(mine + KB_FLAG_GO) - epoch) < 0)
-                if (clock64() - t0 > 4000000000LL) barrier_timeout(rank, -1, epoch);
+                if (clock64() - t0 > (long long)P.timeout_cycles) barrier_timeout(rank, -1, epoch);
         }
         __syncthreads();
     }
@@ -135,7 +137,7 @@ __device__ __forceinline__ void barrier_end(const kb_tp_peers& P, int rank, int 
     if (threadIdx.x == 0) {
         const long long t0 = clock64();
         while (ld_acquire_gpu(mine + KB_FLAG_COUNT) < gridDim.x)
-            if (clock64() - t0 > 4000000000LL) barrier_timeout(rank, -2, epoch);
+            if (clock64() - t0 > (long long)P.timeout_cycles) barrier_timeout(rank, -2, epoch);
         mine[KB_FLAG_COUNT] = 0;   // all blocks have arrived; the next call starts after this kernel
         __threadfence_system();
     }
@@ -207,6 +209,20 @@ __global__ void __launch_bounds__(512) allreduce_kernel(const kb_tp_peers P, int
     barrier_end(P, rank, world, epoch + 1);       // every slice has been written to every rank
 }
 
+// The region descriptor as the kernels get it: the caller's, with the timeout filled in.
+static kb_tp_peers with_timeout(const kb_tp_peers* P) {
+    static unsigned long long dflt = 0;
+    if (dflt == 0) {
+        const char* s = getenv("KB_TP_TIMEOUT_S");
+        double sec = s ? atof(s) : 30.0;
+        if (!(sec > 0.0)) sec = 30.0;
+        dflt = (unsigned long long)(sec * 2.0e9);      // SM clock <= ~2 GHz: at least `sec` seconds
+    }
+    kb_tp_peers Q = *P;
+    if (Q.timeout_cycles == 0) Q.timeout_cycles = dflt;
+    return Q;
+}
+
 int allreduce_peers(const kb_tp_peers* P, int rank, int world, size_t offset_bytes, size_t n, int f16, uint32_t epoch,
                     int blocks, cudaStream_t stream) {
     KB_CHECK(P != nullptr && world >= 2 && world <= KB_TP_MAX_RANKS && rank >= 0 && rank < world,
@@ -222,14 +238,15 @@ int allreduce_peers(const kb_tp_peers* P, int rank, int world, size_t offset_byt
     if (blocks > KB_TP_MAX_BLOCKS) blocks = KB_TP_MAX_BLOCKS;
     const size_t n_vec = bytes / 16;
     const bool mc = P->mc_base != nullptr;
+    const kb_tp_peers Q = with_timeout(P);
     if (mc && f16)
-        allreduce_kernel<true, true><<<blocks, 512, 0, stream>>>(*P, rank, world, offset_bytes, n_vec, epoch);
+        allreduce_kernel<true, true><<<blocks, 512, 0, stream>>>(Q, rank, world, offset_bytes, n_vec, epoch);
     else if (mc)
-        allreduce_kernel<true, false><<<blocks, 512, 0, stream>>>(*P, rank, world, offset_bytes, n_vec, epoch);
+        allreduce_kernel<true, false><<<blocks, 512, 0, stream>>>(Q, rank, world, offset_bytes, n_vec, epoch);
     else if (f16)
-        allreduce_kernel<false, true><<<blocks, 512, 0, stream>>>(*P, rank, world, offset_bytes, n_vec, epoch);
+        allreduce_kernel<false, true><<<blocks, 512, 0, stream>>>(Q, rank, world, offset_bytes, n_vec, epoch);
     else
-        allreduce_kernel<false, false><<<blocks, 512, 0, stream>>>(*P, rank, world, offset_bytes, n_vec, epoch);
+        allreduce_kernel<false, false><<<blocks, 512, 0, stream>>>(Q, rank, world, offset_bytes, n_vec, epoch);
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -405,8 +422,9 @@ int tp_reduce_norm_gather(const kb_tp_peers* P, int rank, int world, size_t part
     const bool mc = P->mc_base != nullptr;
     const int vpt = (hidden / 8 + 255) / 256;
     const __nv_bfloat16* w = static_cast<const __nv_bfloat16*>(norm_w);
+    const kb_tp_peers Q = with_timeout(P);
 #define KB_LAUNCH_RNG(MC, V)                                                                                     \
-    tp_reduce_norm_gather_kernel<MC, V><<<blocks, 256, 0, stream>>>(*P, rank, world, partial_off, xn_off, x, w, T, \
+    tp_reduce_norm_gather_kernel<MC, V><<<blocks, 256, 0, stream>>>(Q, rank, world, partial_off, xn_off, x, w, T, \
                                                                      hidden, eps, epoch)
     if (vpt <= 1) { if (mc) KB_LAUNCH_RNG(true, 1); else KB_LAUNCH_RNG(false, 1); }
     else if (vpt == 2) { if (mc) KB_LAUNCH_RNG(true, 2); else KB_LAUNCH_RNG(false, 2); }

@@ -125,7 +125,7 @@ struct kb_engine {
     int peer_blocks = 0;
     int peer_wire = 0;            // 0 fp32 partial sums | 1 fp16, added to the residual by the next RMSNorm |
                                   // 2 fp16, collective + residual add + RMSNorm fused (kb_tp_reduce_norm_gather)
-    uint32_t peer_epoch = 1;
+    uint32_t peer_epoch = 1;      // only used when the region carries no shared counter (kb_tp_peers.epoch_counter)
     // profiling: one event before every kernel (+ one closing event per call)
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_pool;  // reusable events
@@ -136,6 +136,16 @@ struct kb_engine {
 };
 
 namespace kb {
+
+// Epoch of the next collective on the engine's region: taken from the region's shared host counter when there
+// is one (so that every engine attached to the region, and direct kb_allreduce_peers callers, continue ONE
+// sequence — a reused epoch would let the flag barriers pass without waiting), else from the engine.
+static inline uint32_t next_epoch(kb_engine* e) {
+    uint32_t* c = e->peers.epoch_counter ? e->peers.epoch_counter : &e->peer_epoch;
+    const uint32_t v = *c;
+    *c = v + 2;
+    return v;
+}
 
 // One forward pass over n_tokens packed tokens of n_seqs sequences.
 //   decode == true : one token per sequence, cu_seqlens == nullptr
@@ -196,9 +206,8 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
             if (r) return r;
             mark(KB_PROF_ALLREDUCE);
             const size_t off = reinterpret_cast<char*>(w.xr) - static_cast<char*>(e->peers.peer_base[e->tp_rank]);
-            r = allreduce_peers(&e->peers, e->tp_rank, e->tp_size, off, (size_t)n_tokens * c.hidden, 1, e->peer_epoch,
+            r = allreduce_peers(&e->peers, e->tp_rank, e->tp_size, off, (size_t)n_tokens * c.hidden, 1, next_epoch(e),
                                 e->peer_blocks, stream);
-            e->peer_epoch += 2;
             delta = w.xr;
             return r;
         }
@@ -209,9 +218,8 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         mark(KB_PROF_ALLREDUCE);
         if (e->use_peers) {
             const size_t off = reinterpret_cast<char*>(xr) - static_cast<char*>(e->peers.peer_base[e->tp_rank]);
-            r = allreduce_peers(&e->peers, e->tp_rank, e->tp_size, off, (size_t)n_tokens * c.hidden, 0, e->peer_epoch,
+            r = allreduce_peers(&e->peers, e->tp_rank, e->tp_size, off, (size_t)n_tokens * c.hidden, 0, next_epoch(e),
                                 e->peer_blocks, stream);
-            e->peer_epoch += 2;
             if (r) return r;
         } else if (e->allreduce(e->allreduce_ctx, xr, (size_t)n_tokens * c.hidden, stream) != 0) {
             set_error("tensor-parallel all-reduce callback failed");
@@ -234,8 +242,7 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
         if (r) return r;
         mark(KB_PROF_ALLREDUCE);
         r = tp_reduce_norm_gather(&e->peers, e->tp_rank, e->tp_size, part_off, xn_off, x, next_norm, n_tokens, c.hidden,
-                                  c.rms_eps, e->peer_epoch, e->peer_blocks, stream);
-        e->peer_epoch += 2;
+                                  c.rms_eps, next_epoch(e), e->peer_blocks, stream);
         return r;
     };
 
@@ -376,8 +383,8 @@ extern "C" int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32
     KB_CHECK(wire_f16 >= 0 && wire_f16 <= 2, "kb_set_tensor_parallel_peers: wire mode %d not in {0,1,2}", wire_f16);
     KB_CHECK(wire_f16 != 2 || e->cfg.hidden <= 8192, "kb_set_tensor_parallel_peers: fused mode needs hidden <= 8192");
     e->peer_wire = wire_f16;
-    // peer_epoch is never reset: re-configuring (blocks, wire format, back from the callback) must continue
-    // the flag sequence of the region
+    // the epoch sequence is never reset: re-configuring (blocks, wire format, back from the callback) must
+    // continue the flag sequence of the region (next_epoch)
     e->use_peers = true;
     e->ws.x = reinterpret_cast<float*>(peers->peer_base[tp_rank]);
     e->ws.xr = reinterpret_cast<float*>(static_cast<char*>(peers->peer_base[tp_rank]) + each);

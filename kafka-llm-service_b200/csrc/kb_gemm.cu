@@ -1107,7 +1107,10 @@ static int pick_bn(int M, int N, int K, bool can_split, int* splits_out) {
         const int num_mp = (M + 2 * GEMM_BM - 1) / (2 * GEMM_BM);
         const int pairs = sms / 2;
         for (int splits = 1; splits <= (can_split && !no_split ? 4 : 1); splits *= 2) {
-            if (num_k % splits != 0 || num_k / splits < 8) break;
+            // measured (tools/gemm_bench.py, M = 512, profiles/r02_gemm_splitk.md): splitting pays when a unit
+            // still has a long main loop to amortise the second, ordered epilogue — the down projection
+            // (224 k-blocks: 58.9 -> 54.5 us); it loses on the O projection (64 k-blocks: 19.7 -> 24.4 us)
+            if (num_k % splits != 0 || (splits > 1 && num_k / splits < 96)) break;
             for (int bn = 256; bn >= 64; bn -= 16) {
                 const long tiles = (long)num_mp * ((N + bn - 1) / bn);
                 if (splits > 1 && tiles > SPLITK_MAX_TILES) continue;

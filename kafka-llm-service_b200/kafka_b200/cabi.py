@@ -63,7 +63,8 @@ TP_FLAG_BYTES = 2048
 
 class TpPeers(C.Structure):
     _fields_ = [("peer_base", C.c_void_p * TP_MAX_RANKS), ("mc_base", C.c_void_p), ("bytes", C.c_size_t),
-                ("flags_offset", C.c_size_t)]
+                ("flags_offset", C.c_size_t), ("epoch_counter", C.POINTER(C.c_uint32)),
+                ("timeout_cycles", C.c_ulonglong)]
 
 
 # name -> (restype, argtypes); kept in one table so tests can check every symbol the header declares.

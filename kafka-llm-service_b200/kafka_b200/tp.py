@@ -168,10 +168,25 @@ class PeerRegion:
         self.peers.mc_base = (mc + off) if self.multicast else None
         self.peers.bytes = self.bytes
         self.peers.flags_offset = self.flags_offset
+        # ONE epoch sequence per region, shared by allreduce_() and by every engine attached to it (the library
+        # reads and advances this host word, kb_tp_peers.epoch_counter): a second engine on the same region, or
+        # allreduce_() after attach(), continues where the last collective stopped instead of reusing an epoch
+        # the flags have already passed
+        self._epoch = C.c_uint32(1)
+        self.peers.epoch_counter = C.pointer(self._epoch)
+        self.peers.timeout_cycles = 0                    # library default: $KB_TP_TIMEOUT_S seconds (30)
         self.buf.zero_()
         torch.cuda.synchronize(device)
         dist.barrier(group)                              # every rank's flags are zero before anyone signals
-        self.epoch = 1
+
+    @property
+    def epoch(self) -> int:
+        """Epoch the next collective on this region must use (callers of the bare kernels advance it by 2)."""
+        return int(self._epoch.value)
+
+    @epoch.setter
+    def epoch(self, v: int) -> None:
+        self._epoch.value = v
 
     def payload(self, dtype=torch.float32) -> torch.Tensor:
         return self.buf[:self.flags_offset].view(dtype)
@@ -180,10 +195,10 @@ class PeerRegion:
         """In place on n fp32 (or fp16, added in fp32) at offset_bytes of the payload, on the current stream
         (all ranks, same order)."""
         cabi.check(cabi.load().kb_allreduce_peers(C.byref(self.peers), self.rank, self.size, offset_bytes, n,
-                                                  int(f16), self.epoch, blocks,
+                                                  int(f16), self._epoch.value, blocks,
                                                   torch.cuda.current_stream().cuda_stream),
                    "kb_allreduce_peers")
-        self.epoch += 2
+        self._epoch.value += 2
 
     WIRE = {"f32": 0, "f16": 1, "fused": 2}
 
@@ -231,18 +246,28 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
     if tp > 1:
         mode = allreduce or os.environ.get("KAFKA_B200_TP_ALLREDUCE", "auto")
         if mode in ("auto", "peers", "peers-f16", "peers-fused", "peers-p2p"):
+            err = None
             try:
                 grp = PeerRegion(residual_region_bytes(loc, max_tokens), device, group,
                                  use_multicast=(mode != "peers-p2p"))
+            except Exception as e:
+                err, grp = e, None
+            # the ranks must AGREE on the mode: if the region came up on some ranks only, those would spin in
+            # the peer barrier while the others call NCCL. One MIN over a success flag settles it.
+            import torch.distributed as dist
+            ok = torch.tensor([0 if grp is None else 1], dtype=torch.int32, device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
+                if mode != "auto":
+                    raise err if err is not None else RuntimeError(
+                        "another rank could not set up the symmetric region for the peer-memory all-reduce")
+                print(f"[kafka_b200.tp] symmetric memory unavailable on at least one rank ({err!r} here); every "
+                      "rank falls back to NCCL", file=sys.stderr)
+                grp = None
+            else:
                 grp.attach(core, int(os.environ.get("KAFKA_B200_TP_BLOCKS", "0")),
                            wire={"peers-f16": "f16", "peers-fused": "fused",
                                  "auto": "fused" if cfg.hidden <= 8192 else "f16"}.get(mode, "f32"))
-            except Exception as e:
-                if mode != "auto":
-                    raise
-                print(f"[kafka_b200.tp] symmetric memory unavailable ({e!r}); all-reduce falls back to NCCL",
-                      file=sys.stderr)
-                grp = None
         if grp is None:
             grp = TPGroup(group)
             grp.attach(core)

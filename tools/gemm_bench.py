@@ -30,7 +30,8 @@ def main():
     ap.add_argument("--m", type=int, nargs="+", default=[512])
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--tiles", type=int, nargs="+", default=[0, 64, 128, 256],
-                    help="0 = heuristic; 64/128/256 = 1-CTA tile; negative multiple of 16 = CTA-pair tile width")
+                    help="0 = heuristic; 64/128/256 = 1-CTA tile; negative multiple of 16 = CTA-pair tile width; "
+                         "-(1024 * s + bn) = CTA-pair tile of width bn with split-K in s parts (o / down only)")
     ap.add_argument("--only", default=None)
     ap.add_argument("--ksweep", type=int, nargs="*", default=None,
                     help="override K with these values (time = fixed overhead + slope x K)")
@@ -50,6 +51,8 @@ def main():
             a = torch.randn(M, K, device=dev).half()
             resid = torch.zeros(M, N, device=dev) if epi == cabi.EPI_RESID_F32 else None
             for tile in args.tiles:
+                if tile <= -1024 and epi != cabi.EPI_RESID_F32:
+                    continue                                       # split-K exists for the in-place residual epilogue only
                 # allocate the output once; the residual projections run in place, as in the engine
                 o = resid if resid is not None else cabi.gemm(a, ws[0], epi, resid=resid, tile_n=tile)
                 for i in range(3):
