@@ -851,6 +851,47 @@ def run_b200(args, rank, world, local_rank):
                      "frac": gemm_tf / tf_peak, "ms_per_step": gemm_ms},
         }
 
+        # The projections on their own: every layer's weights once per shape (32 distinct matrices = cold in L2,
+        # as in the step, where 4.5 GB of K/V pass between two GEMMs), back to back with programmatic dependent
+        # launch and NO event between launches. The per-kernel profile above brackets every launch with event
+        # records, which cost device time and keep a kernel's set-up from overlapping its predecessor's tail
+        # (~10 us per launch, profiles/r02_gemm_splitk.md) — it overstates the GEMMs' share of the real step.
+        try:
+            a_h = torch.randn(B, cfg.hidden, device=dev).half()
+            a_q = torch.randn(B, cfg.q_dim, device=dev).half()
+            a_f = torch.randn(B, cfg.ffn, device=dev).half()
+            xres = torch.zeros(B, cfg.hidden, device=dev)
+            o_qkv = torch.empty(B, cfg.qkv_dim, dtype=torch.float16, device=dev)
+            o_h = torch.empty(B, cfg.ffn, dtype=torch.float16, device=dev)
+            shapes = {"gemm_qkv": (a_h, "wqkv", cabi.EPI_F16, None, o_qkv),
+                      "gemm_o": (a_q, "wo", cabi.EPI_RESID_F32, xres, xres),
+                      "gemm_gate_up": (a_h, "w_gate_up", cabi.EPI_SWIGLU_F16, None, o_h),
+                      "gemm_down": (a_f, "w_down", cabi.EPI_RESID_F32, xres, xres)}
+            alone, tot_us = {}, 0.0
+            for name, (a_, wname, epi, resid, out_) in shapes.items():
+                ws_ = [weights[f"l{i}.{wname}"] for i in range(cfg.n_layers)]
+                for w_ in ws_[:3]:
+                    cabi.gemm(a_, w_, epi, resid=resid, out=out_)
+                g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                g0.record()
+                for w_ in ws_:
+                    cabi.gemm(a_, w_, epi, resid=resid, out=out_)
+                g1.record()
+                torch.cuda.synchronize()
+                us = g0.elapsed_time(g1) / len(ws_) * 1e3
+                n_, k_ = ws_[0].shape
+                alone[name] = {"us_per_launch": us, "tflops": 2.0 * B * n_ * k_ / (us * 1e-6) / 1e12}
+                tot_us += us
+            tf_alone = B * 2 * cfg.matmul_params() / cfg.n_layers / (tot_us * 1e-6) / 1e12
+            roofline["gemm"]["standalone"] = {
+                "achieved": tf_alone, "frac": tf_alone / tf_peak, "ms_per_step": tot_us * cfg.n_layers / 1e3,
+                "per_launch": alone,
+                "what": "each projection over all layers' weights back to back, no events between launches (the "
+                        "profile's per-kernel events add ~10 us to every launch)"}
+            del a_h, a_q, a_f, xres, o_qkv, o_h
+        except Exception as ex:      # a measurement aid must not cost the bench line
+            roofline["gemm"]["standalone"] = {"failed": repr(ex)}
         # what a kernel that only READS reaches here: one pass over ~16 GB of the K pool (>> L2), best of 3
         n_l = max(1, min(cfg.n_layers, int(16e9 // (eng.k_pool[0].numel() * 2))))
         region = eng.k_pool[:n_l]
