@@ -32,6 +32,8 @@
 // as the A/B reference: KB_ATTN_PREFILL_LEGACY=1). Reference counterpart: none (src/llm/portkey.py:379).
 #include "kb_common.cuh"
 
+#include <stdlib.h>
+
 namespace kb {
 
 namespace {
@@ -390,6 +392,324 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Two query tiles per CTA ("ping-pong"); opt-in with KB_ATTN_TC2=1 (see attn_prefill_tc for the measurement).
+//
+// One query tile keeps the tensor pipe ~27 % busy: per 64-token K/V tile the chain S = Q K^T -> tcgen05.ld of S
+// (TMEM reads at 64 B/clk: 512 cycles for 128 x 64 fp32) -> 8 192 exp2 (MUFU, 16 / clk: 512 cycles) -> P ->
+// O += P V is serial in one tile, ~1 900 cycles against 512 cycles of MMA. Here a CTA owns TWO consecutive query
+// tiles A and B (256 rows) of the same (sequence, KV head): each has its own S double buffer and O accumulator in
+// tensor memory and its own 8 softmax warps, and both share ONE K/V stream — every K/V tile is staged once for
+// 256 query rows instead of 128. The MMA warp issues  S_A(j) S_B(j) | O_A += P V (j-1)  O_B += P V (j-1) | S_A(j+1) ...
+// so while tile A's warps load, exponentiate and store, the tensor pipe works for tile B and vice versa.
+//
+//   TMEM (512 columns): per tile  S[2] (2 x 64)  +  O (128)  = 256;  P_j (fp16 pairs, 32 columns) is written over
+//   the first half of S[j & 1] once both halves of a row have S_j in registers — S_{j+2}, the next writer of that
+//   buffer, is issued after O += P_j V_j has read it (MMAs execute in issue order), so no "S buffer free" barrier.
+//   Shared memory: Q_A, Q_B as K-major SWIZZLE_128B A operands (2 x 32 KB; the softmax threads write them, the
+//   first round kept Q in tensor memory, which has no room for it any more) + a 4-stage K/V ring (128 KB).
+//   Threads: 16 softmax warps (A: 0-7, B: 8-15; warp w and w + 4 of a tile share the rows of TMEM quarter w & 3
+//   and take 32 of the 64 S columns / 64 of the 128 output dims each) + MMA warp + producer warp = 576.
+// ---------------------------------------------------------------------------------------------
+constexpr int TC2_THREADS = 576;
+constexpr int TC2_Q_BYTES = TC_ROWS * TC_HD * 2;           // 32 KB per query tile
+constexpr int TC2_SMEM = 1024 + 2 * TC2_Q_BYTES + TC_STAGES * 2 * TC_TILE_BYTES + 256 + 2 * 2 * 2 * TC_ROWS * 4;
+
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void umma_f16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+template <int GROUP>
+__global__ void __launch_bounds__(TC2_THREADS, 1)
+attn_prefill_tc2_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
+                        const __half* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+                        const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
+                        uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
+    constexpr int TQ = TC_ROWS / GROUP;                    // query tokens per tile
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_s = smem;                                   // Q_A | Q_B
+    uint8_t* kv_s = q_s + 2 * TC2_Q_BYTES;                 // ring: stage x (K tile, V tile)
+    uint64_t* kv_full = reinterpret_cast<uint64_t*>(kv_s + TC_STAGES * 2 * TC_TILE_BYTES);
+    uint64_t* kv_empty = kv_full + TC_STAGES;
+    uint64_t* s_full = kv_empty + TC_STAGES;               // [tile][2]
+    uint64_t* p_full = s_full + 4;                         // [tile][2]
+    uint64_t* pv_done = p_full + 4;                        // [tile]
+    uint64_t* q_ready = pv_done + 2;                       // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+    float* mx_x = reinterpret_cast<float*>(kv_s + TC_STAGES * 2 * TC_TILE_BYTES + 256);   // [tile][parity][half][row]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int seq = blockIdx.z, kvh = blockIdx.y;
+    if (warp == 16 && lane == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        for (int a = 0; a < 4; ++a) {
+            mbar_init(&s_full[a], 1);
+            mbar_init(&p_full[a], 8);
+        }
+        mbar_init(&pv_done[0], 1);
+        mbar_init(&pv_done[1], 1);
+        mbar_init(q_ready, 16);
+        fence_mbar_init();
+    } else if (warp == 17) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch();
+
+    const int tok_begin = cu_seqlens[seq];
+    const int n_new = cu_seqlens[seq + 1] - tok_begin;
+    const int pair = (int)gridDim.x - 1 - (int)blockIdx.x;          // heavy (late) query tiles first
+    const int q0_pair = pair * 2 * TQ;
+    const bool active = q0_pair < n_new;
+    const bool b_active = q0_pair + TQ < n_new;                     // the second tile has at least one real row
+    const int ctx = ctx_lens[seq];
+    const int q_end = min(n_new, q0_pair + 2 * TQ);
+    const int kv_end = ctx + q_end;                                 // keys visible to the last query of the pair
+    const int n_tiles = active ? (kv_end + TC_NT - 1) / TC_NT : 0;
+
+    if (warp == 17) {
+        // ===== producer =====
+        if (lane == 0) {
+            const int* bt = block_tables + (size_t)seq * max_blocks;
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % TC_STAGES;
+                mbar_wait_relaxed(&kv_empty[st], (uint32_t)(((j / TC_STAGES) & 1) ^ 1));
+                const size_t off = ((size_t)bt[j] * n_kv_heads + kvh) * KB_BLOCK_TOKENS * TC_HD;
+                uint8_t* ks = kv_s + st * 2 * TC_TILE_BYTES;
+                mbar_arrive_expect_tx(&kv_full[st], 2 * TC_TILE_BYTES);
+                bulk_g2s(ks, kpool + off, TC_TILE_BYTES, &kv_full[st]);
+                bulk_g2s(ks + TC_TILE_BYTES, vpool + off, TC_TILE_BYTES, &kv_full[st]);
+            }
+        }
+    } else if (warp == 16) {
+        // ===== MMA issuer =====
+        if (lane == 0 && n_tiles > 0) {
+            const uint32_t id_s = idesc_f16(TC_NT, 0);         // S = Q K^T : N = 64 tokens, B K-major
+            const uint32_t id_o = idesc_f16(TC_HD, 1);         // O += P V  : N = 128 dims,  B MN-major
+            const int n_x = b_active ? 2 : 1;
+            mbar_wait(q_ready, 0);
+            tc_fence_after();
+            auto issue_s = [&](int j) {                        // S_A(j), S_B(j)
+                const int st = j % TC_STAGES, a = j & 1;
+                mbar_wait_relaxed(&kv_full[st], (uint32_t)((j / TC_STAGES) & 1));
+                tc_fence_after();
+                const uint64_t kdesc = desc_kmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES));
+                for (int x = 0; x < n_x; ++x) {
+                    const uint64_t qdesc = desc_kmajor(smem_u32(q_s + x * TC2_Q_BYTES));
+                    const uint32_t d = tmem_base + (uint32_t)(x * 256 + a * 64);
+#pragma unroll
+                    for (int p = 0; p < 2; ++p)
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_f16_ss(d, qdesc + (uint64_t)((p * (TC_ROWS * 128) + k * 32) >> 4),
+                                        kdesc + (uint64_t)((p * (TC_NT * 128) + k * 32) >> 4), id_s, (uint32_t)((p | k) != 0));
+                    umma_commit(&s_full[x * 2 + a]);
+                }
+            };
+            auto issue_o = [&](int j) {                        // O_A += P_A(j) V_j, O_B += P_B(j) V_j
+                const int st = j % TC_STAGES, a = j & 1;
+                const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES), TC_NT * 128, 1024);
+                for (int x = 0; x < n_x; ++x) {
+                    mbar_wait_relaxed(&p_full[x * 2 + a], (uint32_t)((j >> 1) & 1));   // P written (O rescaled if m moved)
+                    tc_fence_after();
+                    const uint32_t pa = tmem_base + (uint32_t)(x * 256 + a * 64);      // P over the first half of S[a]
+                    const uint32_t d = tmem_base + (uint32_t)(x * 256 + 128);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16_ts(d, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o,
+                                    (uint32_t)((j | k) != 0));
+                    umma_commit(&pv_done[x]);
+                }
+                umma_commit(&kv_empty[st]);                    // K_j and V_j are consumed by both tiles
+            };
+            issue_s(0);
+            for (int j = 0; j < n_tiles; ++j) {
+                if (j + 1 < n_tiles) issue_s(j + 1);
+                issue_o(j);
+            }
+        }
+    } else {
+        // ===== softmax warps: tile x = warp / 8, two threads per query row (TMEM lane) =====
+        const int x = warp >> 3, w8 = warp & 7;
+        const int quarter = w8 & 3, half = w8 >> 2;
+        const int r = quarter * 32 + lane;                 // row of the tile = TMEM lane
+        const int q0 = q0_pair + x * TQ;
+        const int tl = q0 + r / GROUP;
+        const int head = kvh * GROUP + r % GROUP;
+        const bool tile_on = active && (x == 0 || b_active);
+        const bool valid = tile_on && tl < n_new;
+        const int lim = valid ? ctx + tl + 1 : kv_end;     // exclusive key limit of this row
+        // this thread's 64 dims of its Q row -> shared memory, the K-major SWIZZLE_128B A operand of S = Q K^T:
+        // [dim plane = half][row][64 dims], 16-byte chunks XOR-ed with (row & 7)
+        if (active) {
+            if (tile_on) {
+                const uint4* src = reinterpret_cast<const uint4*>(q + (size_t)(tok_begin + min(tl, n_new - 1)) * q_stride +
+                                                                  (size_t)head * TC_HD) + half * 8;
+                uint8_t* dst = q_s + x * TC2_Q_BYTES + half * (TC_ROWS * 128) + r * 128;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const uint4 v = valid ? src[c] : make_uint4(0u, 0u, 0u, 0u);
+                    *reinterpret_cast<uint4*>(dst + ((c ^ (r & 7)) << 4)) = v;
+                }
+                fence_proxy_async();                       // generic-proxy writes -> visible to the tensor core's reads
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_ready);
+        }
+        float m = -INFINITY, l = 0.f;                      // m: shared by both halves; l: this half's columns
+        const float sc = TC_LOG2E * rsqrtf((float)TC_HD);
+        const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+        const uint32_t t_x = tmem_base + lane_off + (uint32_t)(x * 256);
+        const uint32_t o_mine = t_x + 128u + (uint32_t)(half * 64);          // this thread's 64 dims of its row of O
+        float* mx_t = mx_x + x * (2 * 2 * TC_ROWS);
+        const int n_my = tile_on ? n_tiles : 0;
+
+        for (int j = 0; j < n_my; ++j) {
+            const int a = j & 1;
+            mbar_wait(&s_full[x * 2 + a], (uint32_t)((j >> 1) & 1));
+            tc_fence_after();
+            uint32_t u[32];
+            float s[32];
+            tmem_ld_32x32(t_x + (uint32_t)(a * 64 + half * 32), u);
+            tmem_ld_wait();
+
+            const int tok0 = j * TC_NT + half * 32;
+            float mx = -INFINITY;
+            if (tok0 + 32 > lim) {                         // causal / length mask: only the last tiles of a row
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float v = (tok0 + i >= lim) ? -INFINITY : __uint_as_float(u[i]);
+                    s[i] = v;
+                    mx = fmaxf(mx, v);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    s[i] = __uint_as_float(u[i]);
+                    mx = fmaxf(mx, s[i]);
+                }
+            }
+            float* xb = mx_t + a * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = mx;
+            // both halves of every row of this tile have S_j in registers from here on (P may overwrite it)
+            if (x == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
+            else asm volatile("bar.sync 2, 256;" ::: "memory");
+            const float tile_mx = fmaxf(mx, xb[(half ^ 1) * TC_ROWS + r]) * sc;
+            // lazily raised running max (log2 units): only when the tile's max exceeds it by more than 8. A row whose
+            // keys of this tile are all masked (tile A at the pair's last K/V tile) keeps m and gets P = 0.
+            const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;
+            const float corr = ex2_approx(m - m_new);       // m = -inf on the first tile -> 0
+            m = m_new;
+            float sum = 0.f;
+            uint32_t pw[16];                               // this thread's 32 probabilities, fp16 pairs
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
+                const float p1 = ex2_approx(fmaf(s[2 * i + 1], sc, -m_new));
+                sum += p0 + p1;
+                pw[i] = pack_f16(p0, p1);
+            }
+            l = l * corr + sum;
+            tmem_st_32x16(t_x + (uint32_t)(a * 64 + half * 16), pw);       // P_j over the first 32 columns of S[a]
+            // ---- the running max moved: rescale this warp's rows of O in tensor memory (rare) ----
+            if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+                mbar_wait(&pv_done[x], (uint32_t)((j - 1) & 1));   // O holds tiles 0 .. j-1, nothing is in flight
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * corr);
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32), reinterpret_cast<const uint32_t(&)[16]>(u[0]));
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32 + 16), reinterpret_cast<const uint32_t(&)[16]>(u[16]));
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[x * 2 + a]);    // the MMA warp may issue O += P_j V_j
+        }
+        if (n_my > 0) {
+            mbar_wait(&pv_done[x], (uint32_t)((n_my - 1) & 1));
+            tc_fence_after();
+            // the row sum is the sum of both halves' partial sums (same running max in both)
+            float* xb = mx_t + (n_my & 1) * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = l;
+            if (x == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
+            else asm volatile("bar.sync 2, 256;" ::: "memory");
+            l += xb[(half ^ 1) * TC_ROWS + r];
+            const float inv = 1.f / l;
+            uint16_t* op = out + ((size_t)(tok_begin + tl) * n_heads + head) * TC_HD + half * 64;
+            uint32_t u[32];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
+                tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        uint4 w;
+                        w.x = pack_act(__uint_as_float(u[8 * q4 + 0]) * inv, __uint_as_float(u[8 * q4 + 1]) * inv, out_f16);
+                        w.y = pack_act(__uint_as_float(u[8 * q4 + 2]) * inv, __uint_as_float(u[8 * q4 + 3]) * inv, out_f16);
+                        w.z = pack_act(__uint_as_float(u[8 * q4 + 4]) * inv, __uint_as_float(u[8 * q4 + 5]) * inv, out_f16);
+                        w.w = pack_act(__uint_as_float(u[8 * q4 + 6]) * inv, __uint_as_float(u[8 * q4 + 7]) * inv, out_f16);
+                        *reinterpret_cast<uint4*>(op + 32 * c + 8 * q4) = w;
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 17) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+template <int GROUP>
+int launch_tc2(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+               const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
+               int out_f16, cudaStream_t stream) {
+    auto kern = attn_prefill_tc2_kernel<GROUP>;
+    static bool configured[64] = {};
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC2_SMEM));
+        configured[dev & 63] = true;
+    }
+    constexpr int TQ2 = 2 * TC_ROWS / GROUP;               // query tokens per CTA (two tiles)
+    dim3 grid((max_new + TQ2 - 1) / TQ2, n_kv_heads, n_seqs);
+    KB_CUDA(launch_kernel(kern, grid, dim3(TC2_THREADS), TC2_SMEM, stream, (const __half*)q, q_stride,
+                          (const __half*)kp, (const __half*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
+                          n_heads, n_kv_heads, out_f16));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
 template <int GROUP>
 int launch_tc(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
               const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
@@ -420,6 +740,20 @@ int attn_prefill_tc(const void* q, int q_stride, const void* kp, const void* vp,
                     int head_dim, int out_f16, cudaStream_t stream) {
     if (head_dim != TC_HD) return -1;
     const int group = n_heads / n_kv_heads;
+    // KB_ATTN_TC2=1: two query tiles per CTA (attn_prefill_tc2_kernel) whenever some sequence can fill more than one
+    // (max_new * group > 128 rows). Measured on the turn prefill (512 x 64 new tokens on 2 048 cached,
+    // profiles/r02_prefill_attention.md) it is NOT faster than one tile per CTA — 83.7 vs 75.6 ms: the pair of tiles
+    // advances at the rate at which the one MMA-issuing thread gets its 24 small MMAs per K/V tile accepted, and with
+    // half as many CTAs the last wave is emptier — so it stays an option (read per call: tests cover both kernels).
+    const char* two = getenv("KB_ATTN_TC2");
+    if (two != nullptr && two[0] == '1' && max_new * group > TC_ROWS) {
+#define KB_TC2_CASE(G_)                                                                                         \
+    if (group == G_)                                                                                            \
+        return launch_tc2<G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks, n_heads,     \
+                              n_kv_heads, out_f16, stream);
+        KB_TC2_CASE(1) KB_TC2_CASE(2) KB_TC2_CASE(4) KB_TC2_CASE(8)
+#undef KB_TC2_CASE
+    }
 #define KB_TC_CASE(G_)                                                                                          \
     if (group == G_)                                                                                            \
         return launch_tc<G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks, n_heads,      \

@@ -484,12 +484,27 @@ PREFILL_CASES = [
     (64, 32, 4, [(0, 77), (500, 3)]),   # group 8
     (64, 4, 2, [(63, 2), (0, 1)]),
     (128, 16, 2, [(10, 200)]),
+    # the two-query-tiles-per-CTA kernel (head_dim 128, more than 128 query rows in some sequence): Llama-3-8B's
+    # grouping with the benchmark's turn, ragged pairs (second tile partly filled / empty / first tile only),
+    # several pairs per sequence, a pair whose first tile is fully masked in the last K/V tile
+    (128, 32, 8, [(2048, 64)]),
+    (128, 32, 8, [(2048, 64), (0, 40), (700, 33), (5, 32), (63, 1), (129, 97)]),
+    (128, 8, 2, [(0, 300), (4000, 65)]),
+    (128, 8, 8, [(100, 129), (0, 256)]),   # group 1: 128 query tokens per tile
+    (128, 16, 2, [(31, 16), (64, 17)]),    # group 8: 16 tokens per tile
 ]
 
 
+@pytest.mark.parametrize("two_tiles", [False, True])
 @pytest.mark.parametrize("hd,n_heads,n_kv,seqs", PREFILL_CASES)
-def test_attn_prefill(kb, cuda, hd, n_heads, n_kv, seqs):
+def test_attn_prefill(kb, cuda, hd, n_heads, n_kv, seqs, two_tiles, monkeypatch):
     from kafka_b200 import kv_layout
+    if two_tiles:
+        if hd != 128 or max(n for _, n in seqs) * (n_heads // n_kv) <= 128:
+            pytest.skip("the two-tile kernel only takes head_dim 128 with more than 128 query rows in a sequence")
+        monkeypatch.setenv("KB_ATTN_TC2", "1")          # attn_prefill_tc2_kernel (read per call)
+    else:
+        monkeypatch.delenv("KB_ATTN_TC2", raising=False)
     g = torch.Generator(device="cpu").manual_seed(hd + len(seqs) + seqs[0][1])
     B = len(seqs)
     max_blocks = max((c + n + 63) // 64 for c, n in seqs) + 1
