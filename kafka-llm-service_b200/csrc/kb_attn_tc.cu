@@ -688,6 +688,270 @@ attn_prefill_tc2_kernel(const __half* __restrict__ q, int q_stride, const __half
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Small-footprint variant: ONE query tile per CTA like attn_prefill_tc_kernel, but sized so that TWO CTAs fit an
+// SM (256 TMEM columns: S[2] + O, P written over S, Q in shared memory; 32 KB of Q + a 2-stage K/V ring = 96 KB;
+// 320 threads at <= 102 registers). A tile's chain  S -> tcgen05.ld -> exp2 -> P -> O += P V  is serial and takes
+// ~1 900 cycles of which the tensor pipe works ~740 (tools/mma_rate.cu: a 128 x 64 x 16 MMA costs as much issue
+// time as a 128 x 128 x 16 one, 62 cycles); two independent CTAs on the SM drift apart in phase, so one's
+// tcgen05.ld / MUFU phase overlaps the other's MMAs — the overlap the two-tiles-per-CTA kernel did not get because
+// its two tiles ran in lockstep.
+// ---------------------------------------------------------------------------------------------
+constexpr int TCS_STAGES = 2;
+constexpr int TCS_SMEM = 1024 + TC2_Q_BYTES + TCS_STAGES * 2 * TC_TILE_BYTES + 256 + 2 * 2 * TC_ROWS * 4;
+
+template <int GROUP>
+__global__ void __launch_bounds__(TC_THREADS, 2)
+attn_prefill_tcs_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
+                        const __half* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+                        const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
+                        uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
+    constexpr int TQ = TC_ROWS / GROUP;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_s = smem;
+    uint8_t* kv_s = q_s + TC2_Q_BYTES;
+    uint64_t* kv_full = reinterpret_cast<uint64_t*>(kv_s + TCS_STAGES * 2 * TC_TILE_BYTES);
+    uint64_t* kv_empty = kv_full + TCS_STAGES;
+    uint64_t* s_full = kv_empty + TCS_STAGES;              // [2]
+    uint64_t* p_full = s_full + 2;                         // [2]
+    uint64_t* pv_done = p_full + 2;                        // [1]
+    uint64_t* q_ready = pv_done + 1;                       // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+    float* mx_x = reinterpret_cast<float*>(kv_s + TCS_STAGES * 2 * TC_TILE_BYTES + 256);   // [parity][half][row]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 8 && lane == 0) {
+        for (int s = 0; s < TCS_STAGES; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&s_full[a], 1);
+            mbar_init(&p_full[a], 8);
+        }
+        mbar_init(pv_done, 1);
+        mbar_init(q_ready, 8);
+        fence_mbar_init();
+    } else if (warp == 9) {
+        tmem_alloc(tmem_slot, 256);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch();
+
+    const int seq = blockIdx.z, kvh = blockIdx.y;
+    const int tok_begin = cu_seqlens[seq];
+    const int n_new = cu_seqlens[seq + 1] - tok_begin;
+    const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * TQ;      // heavy (late) query tiles first
+    const bool active = q0 < n_new;
+    const int ctx = ctx_lens[seq];
+    const int q_end = min(n_new, q0 + TQ);
+    const int kv_end = ctx + q_end;
+    const int n_tiles = active ? (kv_end + TC_NT - 1) / TC_NT : 0;
+
+    if (warp == 9) {
+        if (lane == 0) {
+            const int* bt = block_tables + (size_t)seq * max_blocks;
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % TCS_STAGES;
+                mbar_wait_relaxed(&kv_empty[st], (uint32_t)(((j / TCS_STAGES) & 1) ^ 1));
+                const size_t off = ((size_t)bt[j] * n_kv_heads + kvh) * KB_BLOCK_TOKENS * TC_HD;
+                uint8_t* ks = kv_s + st * 2 * TC_TILE_BYTES;
+                mbar_arrive_expect_tx(&kv_full[st], 2 * TC_TILE_BYTES);
+                bulk_g2s(ks, kpool + off, TC_TILE_BYTES, &kv_full[st]);
+                bulk_g2s(ks + TC_TILE_BYTES, vpool + off, TC_TILE_BYTES, &kv_full[st]);
+            }
+        }
+    } else if (warp == 8) {
+        if (lane == 0 && n_tiles > 0) {
+            const uint32_t id_s = idesc_f16(TC_NT, 0);
+            const uint32_t id_o = idesc_f16(TC_HD, 1);
+            mbar_wait(q_ready, 0);
+            tc_fence_after();
+            const uint64_t qdesc = desc_kmajor(smem_u32(q_s));
+            auto issue_s = [&](int j) {
+                const int st = j % TCS_STAGES, a = j & 1;
+                mbar_wait_relaxed(&kv_full[st], (uint32_t)((j / TCS_STAGES) & 1));
+                tc_fence_after();
+                const uint64_t kdesc = desc_kmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES));
+                const uint32_t d = tmem_base + (uint32_t)(a * 64);
+#pragma unroll
+                for (int p = 0; p < 2; ++p)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16_ss(d, qdesc + (uint64_t)((p * (TC_ROWS * 128) + k * 32) >> 4),
+                                    kdesc + (uint64_t)((p * (TC_NT * 128) + k * 32) >> 4), id_s, (uint32_t)((p | k) != 0));
+                umma_commit(&s_full[a]);
+            };
+            auto issue_o = [&](int j) {
+                const int st = j % TCS_STAGES, a = j & 1;
+                mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));
+                tc_fence_after();
+                const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES), TC_NT * 128, 1024);
+                const uint32_t pa = tmem_base + (uint32_t)(a * 64);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_f16_ts(tmem_base + 128u, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o,
+                                (uint32_t)((j | k) != 0));
+                umma_commit(pv_done);
+                umma_commit(&kv_empty[st]);
+            };
+            issue_s(0);
+            for (int j = 0; j < n_tiles; ++j) {
+                if (j + 1 < n_tiles) issue_s(j + 1);
+                issue_o(j);
+            }
+        }
+    } else {
+        const int quarter = warp & 3, half = warp >> 2;
+        const int r = quarter * 32 + lane;
+        const int tl = q0 + r / GROUP;
+        const int head = kvh * GROUP + r % GROUP;
+        const bool valid = active && tl < n_new;
+        const int lim = valid ? ctx + tl + 1 : kv_end;
+        if (active) {
+            const uint4* src = reinterpret_cast<const uint4*>(q + (size_t)(tok_begin + min(tl, n_new - 1)) * q_stride +
+                                                              (size_t)head * TC_HD) + half * 8;
+            uint8_t* dst = q_s + half * (TC_ROWS * 128) + r * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint4 v = valid ? src[c] : make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(dst + ((c ^ (r & 7)) << 4)) = v;
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_ready);
+        }
+        float m = -INFINITY, l = 0.f;
+        const float sc = TC_LOG2E * rsqrtf((float)TC_HD);
+        const uint32_t t_x = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const uint32_t o_mine = t_x + 128u + (uint32_t)(half * 64);
+
+        for (int j = 0; j < n_tiles; ++j) {
+            const int a = j & 1;
+            mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
+            tc_fence_after();
+            uint32_t u[32];
+            float s[32];
+            tmem_ld_32x32(t_x + (uint32_t)(a * 64 + half * 32), u);
+            tmem_ld_wait();
+            const int tok0 = j * TC_NT + half * 32;
+            float mx = -INFINITY;
+            if (tok0 + 32 > lim) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float v = (tok0 + i >= lim) ? -INFINITY : __uint_as_float(u[i]);
+                    s[i] = v;
+                    mx = fmaxf(mx, v);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    s[i] = __uint_as_float(u[i]);
+                    mx = fmaxf(mx, s[i]);
+                }
+            }
+            float* xb = mx_x + a * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = mx;
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");   // both halves hold S_j in registers
+            const float tile_mx = fmaxf(mx, xb[(half ^ 1) * TC_ROWS + r]) * sc;
+            const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;
+            const float corr = ex2_approx(m - m_new);
+            m = m_new;
+            float sum = 0.f;
+            uint32_t pw[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
+                const float p1 = ex2_approx(fmaf(s[2 * i + 1], sc, -m_new));
+                sum += p0 + p1;
+                pw[i] = pack_f16(p0, p1);
+            }
+            l = l * corr + sum;
+            tmem_st_32x16(t_x + (uint32_t)(a * 64 + half * 16), pw);       // P_j over the first 32 columns of S[a]
+            if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+                mbar_wait(pv_done, (uint32_t)((j - 1) & 1));
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * corr);
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32), reinterpret_cast<const uint32_t(&)[16]>(u[0]));
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32 + 16), reinterpret_cast<const uint32_t(&)[16]>(u[16]));
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[a]);
+        }
+        if (n_tiles > 0) {
+            mbar_wait(pv_done, (uint32_t)((n_tiles - 1) & 1));
+            tc_fence_after();
+            float* xb = mx_x + (n_tiles & 1) * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = l;
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
+            l += xb[(half ^ 1) * TC_ROWS + r];
+            const float inv = 1.f / l;
+            uint16_t* op = out + ((size_t)(tok_begin + tl) * n_heads + head) * TC_HD + half * 64;
+            uint32_t u[32];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
+                tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        uint4 w;
+                        w.x = pack_act(__uint_as_float(u[8 * q4 + 0]) * inv, __uint_as_float(u[8 * q4 + 1]) * inv, out_f16);
+                        w.y = pack_act(__uint_as_float(u[8 * q4 + 2]) * inv, __uint_as_float(u[8 * q4 + 3]) * inv, out_f16);
+                        w.z = pack_act(__uint_as_float(u[8 * q4 + 4]) * inv, __uint_as_float(u[8 * q4 + 5]) * inv, out_f16);
+                        w.w = pack_act(__uint_as_float(u[8 * q4 + 6]) * inv, __uint_as_float(u[8 * q4 + 7]) * inv, out_f16);
+                        *reinterpret_cast<uint4*>(op + 32 * c + 8 * q4) = w;
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
+template <int GROUP>
+int launch_tcs(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+               const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
+               int out_f16, cudaStream_t stream) {
+    auto kern = attn_prefill_tcs_kernel<GROUP>;
+    static bool configured[64] = {};
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TCS_SMEM));
+        configured[dev & 63] = true;
+    }
+    constexpr int TQ = TC_ROWS / GROUP;
+    dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
+    KB_CUDA(launch_kernel(kern, grid, dim3(TC_THREADS), TCS_SMEM, stream, (const __half*)q, q_stride,
+                          (const __half*)kp, (const __half*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
+                          n_heads, n_kv_heads, out_f16));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
 template <int GROUP>
 int launch_tc2(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
                const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
@@ -745,6 +1009,15 @@ int attn_prefill_tc(const void* q, int q_stride, const void* kp, const void* vp,
     // profiles/r02_prefill_attention.md) it is NOT faster than one tile per CTA — 83.7 vs 75.6 ms: the pair of tiles
     // advances at the rate at which the one MMA-issuing thread gets its 24 small MMAs per K/V tile accepted, and with
     // half as many CTAs the last wave is emptier — so it stays an option (read per call: tests cover both kernels).
+    const char* small = getenv("KB_ATTN_TCS");        // read per call: "1" = two small-footprint CTAs per SM
+    if (small != nullptr && small[0] == '1') {
+#define KB_TCS_CASE(G_)                                                                                         \
+    if (group == G_)                                                                                            \
+        return launch_tcs<G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks, n_heads,     \
+                              n_kv_heads, out_f16, stream);
+        KB_TCS_CASE(1) KB_TCS_CASE(2) KB_TCS_CASE(4) KB_TCS_CASE(8)
+#undef KB_TCS_CASE
+    }
     const char* two = getenv("KB_ATTN_TC2");
     if (two != nullptr && two[0] == '1' && max_new * group > TC_ROWS) {
 #define KB_TC2_CASE(G_)                                                                                         \

@@ -495,16 +495,23 @@ PREFILL_CASES = [
 ]
 
 
-@pytest.mark.parametrize("two_tiles", [False, True])
+@pytest.mark.parametrize("variant", ["default", "two_tiles_per_cta", "two_ctas_per_sm"])
 @pytest.mark.parametrize("hd,n_heads,n_kv,seqs", PREFILL_CASES)
-def test_attn_prefill(kb, cuda, hd, n_heads, n_kv, seqs, two_tiles, monkeypatch):
+def test_attn_prefill(kb, cuda, hd, n_heads, n_kv, seqs, variant, monkeypatch):
+    """`variant`: the head_dim-128 tcgen05 kernel has two alternative forms, selected per call through the
+    environment (csrc/kb_attn_tc.cu): KB_ATTN_TC2 (two query tiles per CTA) and KB_ATTN_TCS (small footprint, two
+    CTAs per SM)."""
     from kafka_b200 import kv_layout
-    if two_tiles:
-        if hd != 128 or max(n for _, n in seqs) * (n_heads // n_kv) <= 128:
-            pytest.skip("the two-tile kernel only takes head_dim 128 with more than 128 query rows in a sequence")
-        monkeypatch.setenv("KB_ATTN_TC2", "1")          # attn_prefill_tc2_kernel (read per call)
-    else:
-        monkeypatch.delenv("KB_ATTN_TC2", raising=False)
+    monkeypatch.delenv("KB_ATTN_TC2", raising=False)
+    monkeypatch.delenv("KB_ATTN_TCS", raising=False)
+    if variant != "default" and hd != 128:
+        pytest.skip("head_dim 64 has one kernel (mma.sync)")
+    if variant == "two_tiles_per_cta":
+        if max(n for _, n in seqs) * (n_heads // n_kv) <= 128:
+            pytest.skip("needs more than 128 query rows in a sequence")
+        monkeypatch.setenv("KB_ATTN_TC2", "1")
+    elif variant == "two_ctas_per_sm":
+        monkeypatch.setenv("KB_ATTN_TCS", "1")
     g = torch.Generator(device="cpu").manual_seed(hd + len(seqs) + seqs[0][1])
     B = len(seqs)
     max_blocks = max((c + n + 63) // 64 for c, n in seqs) + 1
