@@ -422,6 +422,9 @@ DECODE_CASES = [
     (64, 8, 2, [1, 63, 64, 65, 500]),
     (64, 32, 4, [300, 2049]),         # TinyLlama grouping (8)
     (64, 4, 2, [90]),                 # group 2
+    (128, 32, 8, [8192]),             # Llama-3-8B heads at the context limit, alone: 16 KV splits
+    (128, 32, 8, [8191, 8192, 4097, 1, 64]),   # ragged around the limit and the block boundaries
+    (128, 8, 1, [3000, 5]),           # Llama-3-70B's per-GPU share at TP 8: one KV head, group 8
 ]
 
 
