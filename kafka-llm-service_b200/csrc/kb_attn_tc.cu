@@ -79,7 +79,11 @@ __device__ __forceinline__ uint32_t idesc_f16(int n, int b_mn) {
 // issue slots with the two softmax warps on the same scheduler (20 % of the samples of the first version were
 // BRA / SYNCS / NOP), so they sleep between polls.
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
+#ifdef KB_WHATIF_SPIN
+    while (!mbar_try_wait(bar, parity)) { }
+#else
     while (!mbar_try_wait(bar, parity)) __nanosleep(64);
+#endif
 }
 
 // D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (Q, P) lives in tensor memory — lane = row, one 32-bit
@@ -226,7 +230,9 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             };
             auto issue_o = [&](int j) {
                 const int st = j % TC_STAGES, a = j & 1;
+#ifndef KB_WHATIF_FREE_MMA
                 mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));   // P_j written (and O rescaled if m moved)
+#endif
                 tc_fence_after();
                 const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES), TC_NT * 128, 1024);
                 const uint32_t pa = p_tmem + (uint32_t)(a * 32);
@@ -285,6 +291,12 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
             tc_fence_after();
             if (threadIdx.x == 0) KB_ATRACE(j, 4);     // S_j ready
+#ifdef KB_WHATIF_EMPTY_SOFTMAX
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { mbar_arrive(&s_empty[a]); mbar_arrive(&p_full[a]); }
+            continue;
+#endif
             uint32_t u[32];
             float s[32];
             tmem_ld_32x32(s_tmem + lane_off + (uint32_t)(a * 64 + half * 32), u);
@@ -323,10 +335,22 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             uint32_t pw[16];                               // this thread's 32 probabilities, fp16 pairs
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
+#if defined(KB_WHATIF_HALF_MUFU)      // timing experiments only (tools/whatif.sh): results are wrong on purpose
+                const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
+                const float p1 = fmaf(s[2 * i + 1], sc, p0);
+#elif defined(KB_WHATIF_NO_MUFU)
+                const float p0 = fmaf(s[2 * i], sc, -m_new);
+                const float p1 = fmaf(s[2 * i + 1], sc, -m_new);
+#else
                 const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
                 const float p1 = ex2_approx(fmaf(s[2 * i + 1], sc, -m_new));
+#endif
                 sum += p0 + p1;
+#if defined(KB_WHATIF_NO_F2FP)
+                pw[i] = (__float_as_uint(p0) >> 16) | (__float_as_uint(p1) & 0xffff0000u);
+#else
                 pw[i] = pack_f16(p0, p1);
+#endif
             }
             l = l * corr + sum;
             // P_j -> tensor memory (A operand of O += P_j V_j); the product of tile j - 2, the last reader of this
@@ -393,6 +417,650 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
 }
 
 // ---------------------------------------------------------------------------------------------
+// 128-key K/V tiles, two MMA-issuing threads — the default since round 2.
+//
+// What bounds attn_prefill_tc_kernel is not the softmax arithmetic (removing every MUFU or F2FP left its time
+// unchanged) but its ONE MMA-issuing thread: with the softmax warps reduced to their barrier protocol the kernel
+// still took 78 % of its time. tools/mma_rate.cu: an MMA costs ~66 cycles of issue for any N <= 128 when one thread
+// issues (so the eight 128 x 64 x 16 MMAs of S = Q K^T cost as much as eight 128 x 128 x 16 ones), and two threads
+// issuing N = 128 MMAs reach the pipe's floor of 64 cycles each. Hence:
+//   * a K/V tile is 128 keys (two KV blocks): S = Q K^T is 8 MMAs of 128 x 128 x 16, O += P V is 8 MMAs of
+//     128 x 128 x 16 over 128 tokens — 16 instructions per 128 keys instead of 24, every one of full width, and the
+//     barrier protocol runs once per 128 keys;
+//   * warp 8 issues the S MMAs, warp 9 the P V MMAs, warp 10 feeds the K/V ring (8 bulk copies of 8 KB per tile:
+//     each 64-dim plane of the two blocks side by side, which is again the canonical SWIZZLE_128B form);
+//   * TMEM: S[2] (2 x 128 columns; P_j, 64 columns of fp16 pairs, is written over the first half of S[j & 1]) +
+//     O (128) + Q (64) = 448; shared memory: 3 stages x 64 KB.
+// S_{j+2} overwrites the buffer P_j lives in, and the two MMA threads are not ordered with each other: the S thread
+// waits for O += P_j V_j to retire (pv_done[j & 1]) before it issues S_{j+2}.
+// An odd number of KV blocks leaves the last tile half filled: its keys are masked (their S values are never
+// used, P = 0) and the V rows behind them are zeroed once at kernel start so that 0 x stale-memory stays 0.
+// ---------------------------------------------------------------------------------------------
+constexpr int TC2_Q_BYTES = TC_ROWS * TC_HD * 2;           // 32 KB per query tile
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void umma_f16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+constexpr int T128_NT = 128;
+constexpr int T128_STAGES = 3;
+constexpr int T128_HALF_BYTES = T128_NT * TC_HD * 2;        // K (or V) of one stage: 32 KB
+constexpr int T128_THREADS = 352;                           // 8 softmax warps + S-MMA warp + PV-MMA warp + producer
+constexpr int T128_SMEM = 1024 + T128_STAGES * 2 * T128_HALF_BYTES + 256 + 2 * 2 * TC_ROWS * 4;
+
+template <int GROUP>
+__global__ void __launch_bounds__(T128_THREADS, 1)
+attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
+                          const __half* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+                          const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
+                          uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
+    constexpr int TQ = TC_ROWS / GROUP;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* kv_s = smem;                                  // ring: stage x (K 32 KB | V 32 KB)
+    uint64_t* kv_full = reinterpret_cast<uint64_t*>(kv_s + T128_STAGES * 2 * T128_HALF_BYTES);
+    uint64_t* kv_empty = kv_full + T128_STAGES;
+    uint64_t* s_full = kv_empty + T128_STAGES;             // [2]
+    uint64_t* p_full = s_full + 2;                         // [2]
+    uint64_t* pv_done = p_full + 2;                        // [2]
+    uint64_t* q_ready = pv_done + 2;                       // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+    float* mx_x = reinterpret_cast<float*>(kv_s + T128_STAGES * 2 * T128_HALF_BYTES + 256);   // [parity][half][row]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 8 && lane == 0) {
+        for (int s = 0; s < T128_STAGES; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&s_full[a], 1);
+            mbar_init(&p_full[a], 8);
+            mbar_init(&pv_done[a], 1);
+        }
+        mbar_init(q_ready, 8);
+        fence_mbar_init();
+    } else if (warp == 9) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    } else if (warp < 8) {
+        // V rows of the second block of every stage: finite before anything multiplies them by P = 0
+        for (int st = 0; st < T128_STAGES; ++st)
+            for (int pl = 0; pl < 2; ++pl) {
+                uint4* z = reinterpret_cast<uint4*>(kv_s + st * 2 * T128_HALF_BYTES + T128_HALF_BYTES + pl * (T128_NT * 128) +
+                                                    64 * 128);
+                for (int i = threadIdx.x; i < 64 * 128 / 16; i += TC_SOFTMAX_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        fence_proxy_async();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch();
+
+    const int seq = blockIdx.z, kvh = blockIdx.y;
+    const int tok_begin = cu_seqlens[seq];
+    const int n_new = cu_seqlens[seq + 1] - tok_begin;
+    const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * TQ;      // heavy (late) query tiles first
+    const bool active = q0 < n_new;
+    const int ctx = ctx_lens[seq];
+    const int q_end = min(n_new, q0 + TQ);
+    const int kv_end = ctx + q_end;
+    const int n_blk = active ? (kv_end + TC_NT - 1) / TC_NT : 0;     // 64-token KV blocks this CTA reads
+    const int n_tiles = (n_blk + 1) >> 1;                            // 128-key tiles
+    const uint32_t s_tmem = tmem_base;                     // S[a] at columns a * 128 (P_a over its first 64)
+    const uint32_t o_tmem = tmem_base + 256;               // O, 128 columns
+    const uint32_t q_tmem = tmem_base + 384;               // Q as the A operand of S: 128 fp16 = 64 columns
+
+    if (warp == 10) {
+        // ===== producer =====
+        if (lane == 0) {
+            const int* bt = block_tables + (size_t)seq * max_blocks;
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % T128_STAGES;
+                mbar_wait_relaxed(&kv_empty[st], (uint32_t)(((j / T128_STAGES) & 1) ^ 1));
+                const int nb = min(2, n_blk - 2 * j);
+                uint8_t* ks = kv_s + st * 2 * T128_HALF_BYTES;
+                mbar_arrive_expect_tx(&kv_full[st], (uint32_t)(nb * 2 * TC_TILE_BYTES));
+                for (int b = 0; b < nb; ++b) {
+                    const size_t off = ((size_t)bt[2 * j + b] * n_kv_heads + kvh) * KB_BLOCK_TOKENS * TC_HD;
+#pragma unroll
+                    for (int pl = 0; pl < 2; ++pl) {       // plane pl of block b -> rows [64 b, 64 b + 64) of plane pl
+                        bulk_g2s(ks + pl * (T128_NT * 128) + b * (64 * 128), kpool + off + pl * (64 * 64), 64 * 128,
+                                 &kv_full[st]);
+                        bulk_g2s(ks + T128_HALF_BYTES + pl * (T128_NT * 128) + b * (64 * 128), vpool + off + pl * (64 * 64),
+                                 64 * 128, &kv_full[st]);
+                    }
+                }
+            }
+        }
+    } else if (warp == 8) {
+        // ===== S = Q K^T issuer =====
+        if (lane == 0 && n_tiles > 0) {
+            const uint32_t id_s = idesc_f16(T128_NT, 0);       // N = 128 keys, B K-major
+            mbar_wait(q_ready, 0);
+            tc_fence_after();
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % T128_STAGES, a = j & 1;
+                mbar_wait_relaxed(&kv_full[st], (uint32_t)((j / T128_STAGES) & 1));
+                if (j >= 2) mbar_wait_relaxed(&pv_done[a], (uint32_t)(((j - 2) >> 1) & 1));   // P_{j-2} has been consumed
+                tc_fence_after();
+                const uint64_t kdesc = desc_kmajor(smem_u32(kv_s + st * 2 * T128_HALF_BYTES));
+                const uint32_t d = s_tmem + (uint32_t)(a * 128);
+#pragma unroll
+                for (int pl = 0; pl < 2; ++pl)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16_ts(d, q_tmem + (uint32_t)(pl * 32 + k * 8),
+                                    kdesc + (uint64_t)((pl * (T128_NT * 128) + k * 32) >> 4), id_s, (uint32_t)((pl | k) != 0));
+                umma_commit(&s_full[a]);
+            }
+        }
+    } else if (warp == 9) {
+        // ===== O += P V issuer =====
+        if (lane == 0 && n_tiles > 0) {
+            const uint32_t id_o = idesc_f16(TC_HD, 1);         // N = 128 dims, B MN-major
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % T128_STAGES, a = j & 1;
+                mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));   // P_j written (and O rescaled if m moved)
+                tc_fence_after();
+                const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * T128_HALF_BYTES + T128_HALF_BYTES),
+                                                    T128_NT * 128, 1024);
+                const uint32_t pa = s_tmem + (uint32_t)(a * 128);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)       // 16 tokens per step: two 8-row groups of the V tile
+                    umma_f16_ts(o_tmem, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o,
+                                (uint32_t)((j | k) != 0));
+                umma_commit(&pv_done[a]);
+                umma_commit(&kv_empty[st]);       // K_j and V_j are both consumed
+            }
+        }
+    } else {
+        // ===== softmax warps: two threads per query row (TMEM lane), 64 of the 128 S columns each =====
+        const int quarter = warp & 3, half = warp >> 2;
+        const int r = quarter * 32 + lane;
+        const int tl = q0 + r / GROUP;
+        const int head = kvh * GROUP + r % GROUP;
+        const bool valid = active && tl < n_new;
+        const int lim = valid ? ctx + tl + 1 : kv_end;
+        const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+        if (active) {
+            const uint4* src = reinterpret_cast<const uint4*>(q + (size_t)(tok_begin + min(tl, n_new - 1)) * q_stride +
+                                                              (size_t)head * TC_HD) + half * 8;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t w[16];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint4 v = valid ? src[4 * c + i] : make_uint4(0u, 0u, 0u, 0u);
+                    w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+                }
+                tmem_st_32x16(q_tmem + lane_off + (uint32_t)(half * 32 + c * 16), w);
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_ready);
+        }
+        float m = -INFINITY, l = 0.f;
+        const float sc = TC_LOG2E * rsqrtf((float)TC_HD);
+        const uint32_t o_mine = o_tmem + lane_off + (uint32_t)(half * 64);
+
+        for (int j = 0; j < n_tiles; ++j) {
+            const int a = j & 1;
+            mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
+            tc_fence_after();
+            uint32_t u0[32], u1[32];
+            const uint32_t s_mine = s_tmem + lane_off + (uint32_t)(a * 128 + half * 64);
+            tmem_ld_32x32(s_mine, u0);
+            tmem_ld_32x32(s_mine + 32u, u1);
+            tmem_ld_wait();
+            const int tok0 = j * T128_NT + half * 64;
+            float mx = -INFINITY;
+            if (tok0 + 64 > lim) {                         // causal / length mask: only the last tiles of a row
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    if (tok0 + i >= lim) u0[i] = 0xff800000u;             // -inf
+                    if (tok0 + 32 + i >= lim) u1[i] = 0xff800000u;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaxf(__uint_as_float(u0[i]), __uint_as_float(u1[i])));
+            float* xb = mx_x + a * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = mx;
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");   // both halves hold S_j in registers
+            const float tile_mx = fmaxf(mx, xb[(half ^ 1) * TC_ROWS + r]) * sc;
+            const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;      // lazily raised running max (log2 units)
+            const float corr = ex2_approx(m - m_new);                   // m = -inf on the first tile -> 0
+            m = m_new;
+            float sum = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {                 // probabilities, packed in place as fp16 pairs
+                const float p0 = ex2_approx(fmaf(__uint_as_float(u0[2 * i]), sc, -m_new));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(u0[2 * i + 1]), sc, -m_new));
+                const float p2 = ex2_approx(fmaf(__uint_as_float(u1[2 * i]), sc, -m_new));
+                const float p3 = ex2_approx(fmaf(__uint_as_float(u1[2 * i + 1]), sc, -m_new));
+                sum += (p0 + p1) + (p2 + p3);
+                u0[i] = pack_f16(p0, p1);
+                u1[i] = pack_f16(p2, p3);
+            }
+            l = l * corr + sum;
+            // P_j (this thread's 64 probabilities = 32 columns) over the first half of S[a]
+            const uint32_t p_mine = s_tmem + lane_off + (uint32_t)(a * 128 + half * 32);
+            tmem_st_32x16(p_mine, reinterpret_cast<const uint32_t(&)[16]>(u0[0]));
+            tmem_st_32x16(p_mine + 16u, reinterpret_cast<const uint32_t(&)[16]>(u1[0]));
+            // ---- the running max moved: rescale this warp's rows of O in tensor memory (rare) ----
+            if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+                mbar_wait(&pv_done[(j - 1) & 1], (uint32_t)(((j - 1) >> 1) & 1));   // O holds tiles 0 .. j-1
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u0);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) u0[i] = __float_as_uint(__uint_as_float(u0[i]) * corr);
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32), reinterpret_cast<const uint32_t(&)[16]>(u0[0]));
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32 + 16), reinterpret_cast<const uint32_t(&)[16]>(u0[16]));
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[a]);        // the PV warp may issue O += P_j V_j
+        }
+        if (n_tiles > 0) {
+            mbar_wait(&pv_done[(n_tiles - 1) & 1], (uint32_t)(((n_tiles - 1) >> 1) & 1));
+            tc_fence_after();
+            float* xb = mx_x + (n_tiles & 1) * (2 * TC_ROWS);
+            xb[half * TC_ROWS + r] = l;
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
+            l += xb[(half ^ 1) * TC_ROWS + r];
+            const float inv = 1.f / l;
+            uint16_t* op = out + ((size_t)(tok_begin + tl) * n_heads + head) * TC_HD + half * 64;
+            uint32_t u[32];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
+                tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        uint4 w;
+                        w.x = pack_act(__uint_as_float(u[8 * q4 + 0]) * inv, __uint_as_float(u[8 * q4 + 1]) * inv, out_f16);
+                        w.y = pack_act(__uint_as_float(u[8 * q4 + 2]) * inv, __uint_as_float(u[8 * q4 + 3]) * inv, out_f16);
+                        w.z = pack_act(__uint_as_float(u[8 * q4 + 4]) * inv, __uint_as_float(u[8 * q4 + 5]) * inv, out_f16);
+                        w.w = pack_act(__uint_as_float(u[8 * q4 + 6]) * inv, __uint_as_float(u[8 * q4 + 7]) * inv, out_f16);
+                        *reinterpret_cast<uint4*>(op + 32 * c + 8 * q4) = w;
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// 128-key tiles with INDEPENDENT key halves (KB_ATTN_T128H, see attn_prefill_tc for which one is the default).
+//
+// In attn_prefill_tc128_kernel the two threads of a row still meet once per tile (row max through shared memory
+// + bar.sync), so all 8 softmax warps read tensor memory at the same time (64 KB of S at 64 B/clk = 1 024 cycles)
+// and then all exponentiate at the same time (16 384 exp2 at 16 / clk = 1 024 cycles): two throughput-bound
+// phases in series. Here the two halves never meet inside the loop: warps 0-3 own keys [0, 64) of every tile,
+// warps 4-7 keys [64, 128), each with its own running max, row sum and O accumulator in tensor memory
+// (O_h = sum_j P_{j,h} V_{j,h}, a split of the keys as in split-KV decode) and its own barriers, so they drift
+// apart and one half's tensor-memory reads run under the other half's MUFU phase. The halves are merged once, at
+// the end: out = (O_0 2^(m_0 - M) + O_1 2^(m_1 - M)) / (l_0 2^(m_0 - M) + l_1 2^(m_1 - M)).
+//   TMEM: S[2] (2 x 128) + O_0 (128) + O_1 (128) = 512 columns; P_{j,h} over the first 32 columns of ITS half of
+//   S[j & 1] (no other thread ever touches them). Q moves to shared memory (32 KB, K-major SWIZZLE_128B, SS-form
+//   MMA) and the K/V ring has 2 stages of 64 KB.
+// ---------------------------------------------------------------------------------------------
+constexpr int T128H_STAGES = 2;
+constexpr int T128H_SMEM = 1024 + TC2_Q_BYTES + T128H_STAGES * 2 * T128_HALF_BYTES + 256 + 2 * TC_ROWS * 2 * 4;
+
+template <int GROUP>
+__global__ void __launch_bounds__(T128_THREADS, 1)
+attn_prefill_tc128h_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
+                           const __half* __restrict__ vpool, const int* __restrict__ cu_seqlens,
+                           const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
+                           uint16_t* __restrict__ out, int max_blocks, int n_heads, int n_kv_heads, int out_f16) {
+    constexpr int TQ = TC_ROWS / GROUP;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_s = smem;
+    uint8_t* kv_s = q_s + TC2_Q_BYTES;
+    uint64_t* kv_full = reinterpret_cast<uint64_t*>(kv_s + T128H_STAGES * 2 * T128_HALF_BYTES);
+    uint64_t* kv_empty = kv_full + T128H_STAGES;
+    uint64_t* s_full = kv_empty + T128H_STAGES;            // [2]
+    uint64_t* p_full = s_full + 2;                         // [half][2]
+    uint64_t* pv_done = p_full + 4;                        // [half][2]
+    uint64_t* q_ready = pv_done + 4;                       // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
+    float* ml_x = reinterpret_cast<float*>(kv_s + T128H_STAGES * 2 * T128_HALF_BYTES + 256);   // [half][row][m, l]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 8 && lane == 0) {
+        for (int s = 0; s < T128H_STAGES; ++s) {
+            mbar_init(&kv_full[s], 1);
+            mbar_init(&kv_empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) mbar_init(&s_full[a], 1);
+        for (int a = 0; a < 4; ++a) {
+            mbar_init(&p_full[a], 4);
+            mbar_init(&pv_done[a], 1);
+        }
+        mbar_init(q_ready, 8);
+        fence_mbar_init();
+    } else if (warp == 9) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    } else if (warp < 8) {
+        // V rows of the second block of every stage: finite before anything multiplies them by P = 0
+        for (int st = 0; st < T128H_STAGES; ++st)
+            for (int pl = 0; pl < 2; ++pl) {
+                uint4* z = reinterpret_cast<uint4*>(kv_s + st * 2 * T128_HALF_BYTES + T128_HALF_BYTES + pl * (T128_NT * 128) +
+                                                    64 * 128);
+                for (int i = threadIdx.x; i < 64 * 128 / 16; i += TC_SOFTMAX_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        fence_proxy_async();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch();
+
+    const int seq = blockIdx.z, kvh = blockIdx.y;
+    const int tok_begin = cu_seqlens[seq];
+    const int n_new = cu_seqlens[seq + 1] - tok_begin;
+    const int q0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * TQ;      // heavy (late) query tiles first
+    const bool active = q0 < n_new;
+    const int ctx = ctx_lens[seq];
+    const int q_end = min(n_new, q0 + TQ);
+    const int kv_end = ctx + q_end;
+    const int n_blk = active ? (kv_end + TC_NT - 1) / TC_NT : 0;     // 64-token KV blocks this CTA reads
+    const int n_tiles = (n_blk + 1) >> 1;                            // 128-key tiles
+    const uint32_t s_tmem = tmem_base;                     // S[a] at columns a * 128; half h owns columns [64 h, 64 h + 64)
+    const uint32_t o_tmem = tmem_base + 256;               // O_h at columns 256 + 128 h
+
+    if (warp == 10) {
+        // ===== producer =====
+        if (lane == 0) {
+            const int* bt = block_tables + (size_t)seq * max_blocks;
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % T128H_STAGES;
+                mbar_wait_relaxed(&kv_empty[st], (uint32_t)(((j / T128H_STAGES) & 1) ^ 1));
+                const int nb = min(2, n_blk - 2 * j);
+                uint8_t* ks = kv_s + st * 2 * T128_HALF_BYTES;
+                mbar_arrive_expect_tx(&kv_full[st], (uint32_t)(nb * 2 * TC_TILE_BYTES));
+                for (int b = 0; b < nb; ++b) {
+                    const size_t off = ((size_t)bt[2 * j + b] * n_kv_heads + kvh) * KB_BLOCK_TOKENS * TC_HD;
+#pragma unroll
+                    for (int pl = 0; pl < 2; ++pl) {
+                        bulk_g2s(ks + pl * (T128_NT * 128) + b * (64 * 128), kpool + off + pl * (64 * 64), 64 * 128,
+                                 &kv_full[st]);
+                        bulk_g2s(ks + T128_HALF_BYTES + pl * (T128_NT * 128) + b * (64 * 128), vpool + off + pl * (64 * 64),
+                                 64 * 128, &kv_full[st]);
+                    }
+                }
+            }
+        }
+    } else if (warp == 8) {
+        // ===== S = Q K^T issuer =====
+        if (lane == 0 && n_tiles > 0) {
+            const uint32_t id_s = idesc_f16(T128_NT, 0);       // N = 128 keys, B K-major
+            mbar_wait(q_ready, 0);
+            tc_fence_after();
+            const uint64_t qdesc = desc_kmajor(smem_u32(q_s));
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % T128H_STAGES, a = j & 1;
+                mbar_wait_relaxed(&kv_full[st], (uint32_t)((j / T128H_STAGES) & 1));
+                if (j >= 2) {                                  // both halves' P_{j-2} have been consumed
+                    mbar_wait_relaxed(&pv_done[a], (uint32_t)(((j - 2) >> 1) & 1));
+                    mbar_wait_relaxed(&pv_done[2 + a], (uint32_t)(((j - 2) >> 1) & 1));
+                }
+                tc_fence_after();
+                const uint64_t kdesc = desc_kmajor(smem_u32(kv_s + st * 2 * T128_HALF_BYTES));
+                const uint32_t d = s_tmem + (uint32_t)(a * 128);
+#pragma unroll
+                for (int pl = 0; pl < 2; ++pl)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16_ss(d, qdesc + (uint64_t)((pl * (TC_ROWS * 128) + k * 32) >> 4),
+                                    kdesc + (uint64_t)((pl * (T128_NT * 128) + k * 32) >> 4), id_s, (uint32_t)((pl | k) != 0));
+                umma_commit(&s_full[a]);
+            }
+        }
+    } else if (warp == 9) {
+        // ===== O_h += P_h V_h issuer: whichever half publishes its P first goes first =====
+        if (lane == 0 && n_tiles > 0) {
+            const uint32_t id_o = idesc_f16(TC_HD, 1);         // N = 128 dims, B MN-major
+            for (int j = 0; j < n_tiles; ++j) {
+                const int st = j % T128H_STAGES, a = j & 1;
+                const uint32_t par = (uint32_t)((j >> 1) & 1);
+                const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * T128_HALF_BYTES + T128_HALF_BYTES),
+                                                    T128_NT * 128, 1024);
+                uint32_t todo = 3u;
+                while (todo) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        if ((todo >> h) & 1u) {
+                            if (!mbar_try_wait(&p_full[h * 2 + a], par)) continue;
+                            tc_fence_after();
+                            const uint32_t pa = s_tmem + (uint32_t)(a * 128 + h * 64);
+                            const uint32_t d = o_tmem + (uint32_t)(h * 128);
+#pragma unroll
+                            for (int k = 0; k < 4; ++k)       // this half's 64 tokens, 16 per step
+                                umma_f16_ts(d, pa + (uint32_t)(k * 8),
+                                            vdesc + (uint64_t)((h * (64 * 128) + k * 2048) >> 4), id_o, (uint32_t)((j | k) != 0));
+                            umma_commit(&pv_done[h * 2 + a]);
+                            todo &= ~(1u << h);
+                        }
+                    }
+                    if (todo == 3u) __nanosleep(32);
+                }
+                umma_commit(&kv_empty[st]);       // K_j and V_j are consumed by both halves
+            }
+        }
+    } else {
+        // ===== softmax warps: half h = warp / 4 owns keys [64 h, 64 h + 64) of every tile, one thread per row =====
+        const int quarter = warp & 3, half = warp >> 2;
+        const int r = quarter * 32 + lane;
+        const int tl = q0 + r / GROUP;
+        const int head = kvh * GROUP + r % GROUP;
+        const bool valid = active && tl < n_new;
+        const int lim = valid ? ctx + tl + 1 : kv_end;
+        const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+        if (active) {
+            const uint4* src = reinterpret_cast<const uint4*>(q + (size_t)(tok_begin + min(tl, n_new - 1)) * q_stride +
+                                                              (size_t)head * TC_HD) + half * 8;
+            uint8_t* dst = q_s + half * (TC_ROWS * 128) + r * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint4 v = valid ? src[c] : make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(dst + ((c ^ (r & 7)) << 4)) = v;
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_ready);
+        }
+        float m = -INFINITY, l = 0.f;                      // of THIS half's keys only
+        const float sc = TC_LOG2E * rsqrtf((float)TC_HD);
+        const uint32_t o_h = o_tmem + lane_off + (uint32_t)(half * 128);
+
+        for (int j = 0; j < n_tiles; ++j) {
+            const int a = j & 1;
+            mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
+            tc_fence_after();
+            uint32_t u0[32], u1[32];
+            const uint32_t s_mine = s_tmem + lane_off + (uint32_t)(a * 128 + half * 64);
+            tmem_ld_32x32(s_mine, u0);
+            tmem_ld_32x32(s_mine + 32u, u1);
+            tmem_ld_wait();
+            const int tok0 = j * T128_NT + half * 64;
+            if (tok0 + 64 > lim) {                         // causal / length mask: only the last tiles of a row
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    if (tok0 + i >= lim) u0[i] = 0xff800000u;             // -inf
+                    if (tok0 + 32 + i >= lim) u1[i] = 0xff800000u;
+                }
+            }
+            float mx = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaxf(__uint_as_float(u0[i]), __uint_as_float(u1[i])));
+            // lazily raised running max of this half (log2 units). A half whose keys are all masked so far keeps
+            // m = -inf: use 0 as the reference then (every P is exp2(-inf) = 0) instead of -inf - -inf.
+            const float tile_mx = mx * sc;
+            const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;
+            const float corr = (m_new == -INFINITY) ? 1.f : ex2_approx(m - m_new);
+            const float ref = (m_new == -INFINITY) ? 0.f : m_new;
+            m = m_new;
+            float sum = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float p0 = ex2_approx(fmaf(__uint_as_float(u0[2 * i]), sc, -ref));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(u0[2 * i + 1]), sc, -ref));
+                const float p2 = ex2_approx(fmaf(__uint_as_float(u1[2 * i]), sc, -ref));
+                const float p3 = ex2_approx(fmaf(__uint_as_float(u1[2 * i + 1]), sc, -ref));
+                sum += (p0 + p1) + (p2 + p3);
+                u0[i] = pack_f16(p0, p1);
+                u1[i] = pack_f16(p2, p3);
+            }
+            l = l * corr + sum;
+            tmem_st_32x16(s_mine, reinterpret_cast<const uint32_t(&)[16]>(u0[0]));          // P_{j,h}: 32 columns over
+            tmem_st_32x16(s_mine + 16u, reinterpret_cast<const uint32_t(&)[16]>(u1[0]));    // the S values just read
+            if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {       // this half's max moved: rescale ITS O (rare)
+                mbar_wait(&pv_done[half * 2 + ((j - 1) & 1)], (uint32_t)(((j - 1) >> 1) & 1));
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    tmem_ld_32x32(o_h + (uint32_t)(c * 32), u0);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) u0[i] = __float_as_uint(__uint_as_float(u0[i]) * corr);
+                    tmem_st_32x16(o_h + (uint32_t)(c * 32), reinterpret_cast<const uint32_t(&)[16]>(u0[0]));
+                    tmem_st_32x16(o_h + (uint32_t)(c * 32 + 16), reinterpret_cast<const uint32_t(&)[16]>(u0[16]));
+                }
+            }
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_full[half * 2 + a]);
+        }
+        if (n_tiles > 0) {
+            // merge the halves: each thread publishes (m, l) of its half, then takes 64 of the row's 128 dims
+            ml_x[(half * TC_ROWS + r) * 2] = m;
+            ml_x[(half * TC_ROWS + r) * 2 + 1] = l;
+            mbar_wait(&pv_done[(n_tiles - 1) & 1], (uint32_t)(((n_tiles - 1) >> 1) & 1));          // O_0 complete
+            mbar_wait(&pv_done[2 + ((n_tiles - 1) & 1)], (uint32_t)(((n_tiles - 1) >> 1) & 1));    // O_1 complete
+            tc_fence_after();
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");
+            const float m0 = ml_x[r * 2], l0 = ml_x[r * 2 + 1];
+            const float m1 = ml_x[(TC_ROWS + r) * 2], l1 = ml_x[(TC_ROWS + r) * 2 + 1];
+            const float M = fmaxf(m0, m1);                 // finite: key 0 of the row is never masked
+            const float w0 = (m0 == -INFINITY) ? 0.f : ex2_approx(m0 - M);
+            const float w1 = (m1 == -INFINITY) ? 0.f : ex2_approx(m1 - M);
+            const float inv = 1.f / (l0 * w0 + l1 * w1);
+            const float f0 = w0 * inv, f1 = w1 * inv;
+            uint16_t* op = out + ((size_t)(tok_begin + tl) * n_heads + head) * TC_HD + half * 64;
+            const uint32_t o0 = o_tmem + lane_off + (uint32_t)(half * 64);          // O_0, this thread's 64 dims
+            uint32_t u[32], v[32];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                tmem_ld_32x32(o0 + (uint32_t)(c * 32), u);
+                tmem_ld_32x32(o0 + 128u + (uint32_t)(c * 32), v);                   // O_1, same dims
+                tmem_ld_wait();
+                if (valid) {
+#pragma unroll
+                    for (int q4 = 0; q4 < 4; ++q4) {
+                        float y[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            y[e] = (w0 != 0.f ? __uint_as_float(u[8 * q4 + e]) * f0 : 0.f) +
+                                   (w1 != 0.f ? __uint_as_float(v[8 * q4 + e]) * f1 : 0.f);
+                        uint4 w;
+                        w.x = pack_act(y[0], y[1], out_f16);
+                        w.y = pack_act(y[2], y[3], out_f16);
+                        w.z = pack_act(y[4], y[5], out_f16);
+                        w.w = pack_act(y[6], y[7], out_f16);
+                        *reinterpret_cast<uint4*>(op + 32 * c + 8 * q4) = w;
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+template <int GROUP>
+int launch_tc128h(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+                  const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
+                  int out_f16, cudaStream_t stream) {
+    auto kern = attn_prefill_tc128h_kernel<GROUP>;
+    static bool configured[64] = {};
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, T128H_SMEM));
+        configured[dev & 63] = true;
+    }
+    constexpr int TQ = TC_ROWS / GROUP;
+    dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
+    KB_CUDA(launch_kernel(kern, grid, dim3(T128_THREADS), T128H_SMEM, stream, (const __half*)q, q_stride,
+                          (const __half*)kp, (const __half*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
+                          n_heads, n_kv_heads, out_f16));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+template <int GROUP>
+int launch_tc128(const void* q, int q_stride, const void* kp, const void* vp, const int* cu, const int* ctx,
+                 const int* bt, void* out, int n_seqs, int max_new, int max_blocks, int n_heads, int n_kv_heads,
+                 int out_f16, cudaStream_t stream) {
+    auto kern = attn_prefill_tc128_kernel<GROUP>;
+    static bool configured[64] = {};
+    int dev = 0;
+    KB_CUDA(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, T128_SMEM));
+        configured[dev & 63] = true;
+    }
+    constexpr int TQ = TC_ROWS / GROUP;
+    dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
+    KB_CUDA(launch_kernel(kern, grid, dim3(T128_THREADS), T128_SMEM, stream, (const __half*)q, q_stride,
+                          (const __half*)kp, (const __half*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
+                          n_heads, n_kv_heads, out_f16));
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Two query tiles per CTA ("ping-pong"); opt-in with KB_ATTN_TC2=1 (see attn_prefill_tc for the measurement).
 //
 // One query tile keeps the tensor pipe ~27 % busy: per 64-token K/V tile the chain S = Q K^T -> tcgen05.ld of S
@@ -412,21 +1080,7 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
 //   and take 32 of the 64 S columns / 64 of the 128 output dims each) + MMA warp + producer warp = 576.
 // ---------------------------------------------------------------------------------------------
 constexpr int TC2_THREADS = 576;
-constexpr int TC2_Q_BYTES = TC_ROWS * TC_HD * 2;           // 32 KB per query tile
 constexpr int TC2_SMEM = 1024 + 2 * TC2_Q_BYTES + TC_STAGES * 2 * TC_TILE_BYTES + 256 + 2 * 2 * 2 * TC_ROWS * 4;
-
-// D[tmem] (+)= A[smem desc] * B[smem desc]
-__device__ __forceinline__ void umma_f16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                            uint32_t accumulate) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(tmem_d),
-        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
 
 template <int GROUP>
 __global__ void __launch_bounds__(TC2_THREADS, 1)
@@ -1009,6 +1663,24 @@ int attn_prefill_tc(const void* q, int q_stride, const void* kp, const void* vp,
     // profiles/r02_prefill_attention.md) it is NOT faster than one tile per CTA — 83.7 vs 75.6 ms: the pair of tiles
     // advances at the rate at which the one MMA-issuing thread gets its 24 small MMAs per K/V tile accepted, and with
     // half as many CTAs the last wave is emptier — so it stays an option (read per call: tests cover both kernels).
+    const char* old64 = getenv("KB_ATTN_TC64");       // read per call: "1" = one of the 64-key-tile kernels below
+    const char* halves = getenv("KB_ATTN_T128H");     // read per call: "1" = 128-key tiles with independent key halves
+    if ((old64 == nullptr || old64[0] != '1') && halves != nullptr && halves[0] == '1') {
+#define KB_T128H_CASE(G_)                                                                                       \
+    if (group == G_)                                                                                            \
+        return launch_tc128h<G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks, n_heads,  \
+                                 n_kv_heads, out_f16, stream);
+        KB_T128H_CASE(1) KB_T128H_CASE(2) KB_T128H_CASE(4) KB_T128H_CASE(8)
+#undef KB_T128H_CASE
+    }
+    if (old64 == nullptr || old64[0] != '1') {
+#define KB_T128_CASE(G_)                                                                                        \
+    if (group == G_)                                                                                            \
+        return launch_tc128<G_>(q, q_stride, kp, vp, cu, ctx, bt, out, n_seqs, max_new, max_blocks, n_heads,   \
+                                n_kv_heads, out_f16, stream);
+        KB_T128_CASE(1) KB_T128_CASE(2) KB_T128_CASE(4) KB_T128_CASE(8)
+#undef KB_T128_CASE
+    }
     const char* small = getenv("KB_ATTN_TCS");        // read per call: "1" = two small-footprint CTAs per SM
     if (small != nullptr && small[0] == '1') {
 #define KB_TCS_CASE(G_)                                                                                         \

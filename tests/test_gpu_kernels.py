@@ -495,20 +495,26 @@ PREFILL_CASES = [
     (128, 8, 2, [(0, 300), (4000, 65)]),
     (128, 8, 8, [(100, 129), (0, 256)]),   # group 1: 128 query tokens per tile
     (128, 16, 2, [(31, 16), (64, 17)]),    # group 8: 16 tokens per tile
+    # 128-key tiles: odd and even numbers of KV blocks, a lone block, lengths at the block and tile boundaries
+    (128, 8, 2, [(0, 64), (0, 65), (64, 64), (100, 28), (127, 1), (128, 1), (191, 2), (320, 64)]),
 ]
 
 
-@pytest.mark.parametrize("variant", ["default", "two_tiles_per_cta", "two_ctas_per_sm"])
+@pytest.mark.parametrize("variant", ["default", "independent_halves", "tiles_of_64", "two_tiles_per_cta", "two_ctas_per_sm"])
 @pytest.mark.parametrize("hd,n_heads,n_kv,seqs", PREFILL_CASES)
 def test_attn_prefill(kb, cuda, hd, n_heads, n_kv, seqs, variant, monkeypatch):
-    """`variant`: the head_dim-128 tcgen05 kernel has two alternative forms, selected per call through the
-    environment (csrc/kb_attn_tc.cu): KB_ATTN_TC2 (two query tiles per CTA) and KB_ATTN_TCS (small footprint, two
-    CTAs per SM)."""
+    """`variant`: the head_dim-128 tcgen05 kernel exists in four forms, selected per call through the environment
+    (csrc/kb_attn_tc.cu): the default (128-key tiles, two MMA-issuing threads) and, behind KB_ATTN_TC64=1, the
+    64-key-tile kernels: one tile per CTA, KB_ATTN_TC2 (two query tiles per CTA) and KB_ATTN_TCS (two CTAs per SM)."""
     from kafka_b200 import kv_layout
-    monkeypatch.delenv("KB_ATTN_TC2", raising=False)
-    monkeypatch.delenv("KB_ATTN_TCS", raising=False)
+    for k in ("KB_ATTN_TC64", "KB_ATTN_TC2", "KB_ATTN_TCS", "KB_ATTN_T128H"):
+        monkeypatch.delenv(k, raising=False)
     if variant != "default" and hd != 128:
         pytest.skip("head_dim 64 has one kernel (mma.sync)")
+    if variant == "independent_halves":
+        monkeypatch.setenv("KB_ATTN_T128H", "1")       # 128-key tiles, the two key halves never meet inside the loop
+    elif variant != "default":
+        monkeypatch.setenv("KB_ATTN_TC64", "1")
     if variant == "two_tiles_per_cta":
         if max(n for _, n in seqs) * (n_heads // n_kv) <= 128:
             pytest.skip("needs more than 128 query rows in a sequence")

@@ -42,15 +42,36 @@ __global__ void __launch_bounds__(128, 1) mma_rate_kernel(const Case* cases, int
     uint8_t* a_s = smem;                       // 128 x 64 fp16, 16 KB
     uint8_t* b_s = smem + 16384;               // up to 256 x 64 fp16, 32 KB (or a 64 x 128 V tile)
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 16384 + 32768);
-    uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
+    uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 4);
     for (int i = threadIdx.x; i < (16384 + 32768) / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
-    if (threadIdx.x == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+    if (threadIdx.x == 0) { mbar_init(bar, 1); mbar_init(bar + 2, 1); slot[1] = 0; slot[2] = 0; fence_mbar_init(); }
     if (threadIdx.x < 32) { tmem_alloc(slot, 512); tmem_relinquish(); }
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tm = *slot;
+    uint64_t* bar2 = bar + 2;
+    if (threadIdx.x == 32) {          // second issuing thread (mode 8 only): its own accumulator and barrier
+        uint32_t phase2 = 0;
+        const uint64_t ad = desc_k(smem_u32(a_s)), bk = desc_k(smem_u32(b_s));
+        for (int c = 0; c < n_cases; ++c) {
+            const Case cs = cases[c];
+            if (cs.mode != 8) continue;
+            const uint32_t id = idesc(cs.n_cols, 0);
+            for (int r = 0; r < reps; ++r) {
+                while (*reinterpret_cast<volatile int*>(slot + 1) != c * 1000 + r + 1) { }      // start together
+                for (int i = 0; i < cs.chain; i += 8) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) mma_ss(tm + 256, ad + (uint64_t)((k & 3) * 2), bk + (uint64_t)((k & 3) * 2), id, 1);
+                }
+                umma_commit(bar2);
+                mbar_wait(bar2, phase2);
+                phase2 ^= 1;
+                *reinterpret_cast<volatile int*>(slot + 2) = c * 1000 + r + 1;                    // done
+            }
+        }
+    }
     if (threadIdx.x == 0) {
         uint32_t phase = 0;
         const uint64_t ad = desc_k(smem_u32(a_s)), bk = desc_k(smem_u32(b_s)), bm = desc_mn(smem_u32(b_s), 64 * 128, 1024);
@@ -74,6 +95,13 @@ __global__ void __launch_bounds__(128, 1) mma_rate_kernel(const Case* cases, int
                     const uint32_t id = idesc(cs.n_cols, 0);
                     for (int i = 0; i < cs.chain; ++i)
                         mma_ss(tm, ad + (uint64_t)((i & 3) * 2), bk + (uint64_t)((i & 3) * 2), id, 0);
+                } else if (cs.mode == 8) {                        // like mode 7, while thread 32 issues the same chain too
+                    const uint32_t id = idesc(cs.n_cols, 0);
+                    *reinterpret_cast<volatile int*>(slot + 1) = c * 1000 + r + 1;
+                    for (int i = 0; i < cs.chain; i += 8) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) mma_ss(tm, ad + (uint64_t)((k & 3) * 2), bk + (uint64_t)((k & 3) * 2), id, 1);
+                    }
                 } else if (cs.mode == 7) {                        // SS accumulate, fully unrolled by 8 (no loop overhead)
                     const uint32_t id = idesc(cs.n_cols, 0);
                     for (int i = 0; i < cs.chain; i += 8) {
@@ -93,6 +121,7 @@ __global__ void __launch_bounds__(128, 1) mma_rate_kernel(const Case* cases, int
                 umma_commit(bar);
                 mbar_wait(bar, phase);
                 phase ^= 1;
+                if (cs.mode == 8) while (*reinterpret_cast<volatile int*>(slot + 2) != c * 1000 + r + 1) { }
                 const long long dt = clock64() - t0;
                 best = dt < best ? dt : best;
             }
@@ -107,7 +136,8 @@ __global__ void __launch_bounds__(128, 1) mma_rate_kernel(const Case* cases, int
 int main() {
     const char* names[] = {"SS  (A, B K-major in smem)", "TS  (A in TMEM, B K-major)", "TS  (A in TMEM, B MN-major)",
                            "SS  two accumulators alternating", "attention tile: 8 x SS N=64 + 4 x TS N=128 MN-major",
-                           "SS  chains of 8, first overwrites", "SS  always overwrite", "SS  accumulate, unrolled x8"};
+                           "SS  chains of 8, first overwrites", "SS  always overwrite", "SS  accumulate, unrolled x8",
+                           "SS  TWO threads, a chain each (per thread)"};
     Case h[96];
     int n = 0;
     const int chains[3] = {8, 64, 512};
@@ -117,8 +147,8 @@ int main() {
             for (int ch : chains) h[n++] = {mode, nc, ch};
         }
     for (int ch : {1, 8, 64}) h[n++] = {4, 0, ch};
-    for (int mode = 5; mode < 8; ++mode)
-        for (int nc : {64, 256}) h[n++] = {mode, nc, 512};
+    for (int mode = 5; mode < 9; ++mode)
+        for (int nc : {64, 128, 256}) h[n++] = {mode, nc, 512};
     Case* d;
     long long* out;
     cudaMalloc(&d, sizeof(h));
