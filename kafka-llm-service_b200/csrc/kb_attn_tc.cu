@@ -79,11 +79,7 @@ __device__ __forceinline__ uint32_t idesc_f16(int n, int b_mn) {
 // issue slots with the two softmax warps on the same scheduler (20 % of the samples of the first version were
 // BRA / SYNCS / NOP), so they sleep between polls.
 __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity) {
-#ifdef KB_WHATIF_SPIN
-    while (!mbar_try_wait(bar, parity)) { }
-#else
     while (!mbar_try_wait(bar, parity)) __nanosleep(64);
-#endif
 }
 
 // D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (Q, P) lives in tensor memory — lane = row, one 32-bit
@@ -230,9 +226,7 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             };
             auto issue_o = [&](int j) {
                 const int st = j % TC_STAGES, a = j & 1;
-#ifndef KB_WHATIF_FREE_MMA
                 mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));   // P_j written (and O rescaled if m moved)
-#endif
                 tc_fence_after();
                 const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * TC_TILE_BYTES + TC_TILE_BYTES), TC_NT * 128, 1024);
                 const uint32_t pa = p_tmem + (uint32_t)(a * 32);
@@ -291,12 +285,6 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
             tc_fence_after();
             if (threadIdx.x == 0) KB_ATRACE(j, 4);     // S_j ready
-#ifdef KB_WHATIF_EMPTY_SOFTMAX
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) { mbar_arrive(&s_empty[a]); mbar_arrive(&p_full[a]); }
-            continue;
-#endif
             uint32_t u[32];
             float s[32];
             tmem_ld_32x32(s_tmem + lane_off + (uint32_t)(a * 64 + half * 32), u);
@@ -335,22 +323,10 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
             uint32_t pw[16];                               // this thread's 32 probabilities, fp16 pairs
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-#if defined(KB_WHATIF_HALF_MUFU)      // timing experiments only (tools/whatif.sh): results are wrong on purpose
-                const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
-                const float p1 = fmaf(s[2 * i + 1], sc, p0);
-#elif defined(KB_WHATIF_NO_MUFU)
-                const float p0 = fmaf(s[2 * i], sc, -m_new);
-                const float p1 = fmaf(s[2 * i + 1], sc, -m_new);
-#else
                 const float p0 = ex2_approx(fmaf(s[2 * i], sc, -m_new));
                 const float p1 = ex2_approx(fmaf(s[2 * i + 1], sc, -m_new));
-#endif
                 sum += p0 + p1;
-#if defined(KB_WHATIF_NO_F2FP)
-                pw[i] = (__float_as_uint(p0) >> 16) | (__float_as_uint(p1) & 0xffff0000u);
-#else
                 pw[i] = pack_f16(p0, p1);
-#endif
             }
             l = l * corr + sum;
             // P_j -> tensor memory (A operand of O += P_j V_j); the product of tile j - 2, the last reader of this
