@@ -982,9 +982,12 @@ def run_b200(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16",
-            "dtype_detail": "bf16 weights, KV cache, q/k/v and attention; the projection GEMMs take the bf16 weight "
-                            "values re-encoded as fp16 and fp16 activations (10 mantissa bits instead of 7); fp32 "
-                            "accumulate and residual stream", "data": "synthetic",
+            "dtype_detail": "16-bit operands, fp32 accumulation and residual stream: the weights are bf16 VALUES (the "
+                            "five projection matrices bound re-encoded as fp16, exact for |w| >= 2^-14); every other "
+                            "16-bit value — GEMM activations, q / k / v, the KV cache, the attention probabilities — "
+                            "is fp16 (10 mantissa bits instead of 7, same bytes and MMA rate; conversions saturate at "
+                            "65504). Reason and error budget: DESIGN.md §5, profiles/r02_stage_errors.md",
+            "data": "synthetic",
             "config": {
                 "workload": f"{cfg.name} bf16 decode, {B} resident threads/GPU x {args.history}-token history + "
                             f"{U}-token turn (BASELINE configs[2], thread-sharded: 4096 threads at 8 GPUs)",
@@ -1167,7 +1170,8 @@ def run_tp(args, rank, world, local_rank):
     line = {
         "metric": METRIC, "value": B * K / (ms_total / 1e3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "bf16", "dtype_detail": "bf16 weights / KV / attention, fp16-encoded projection operands, fp32 accumulate",
+        "dtype": "bf16", "dtype_detail": "bf16 weight values (projection matrices bound as fp16 re-encodings); activations, "
+                                         "q / k / v, KV cache and attention probabilities fp16; fp32 accumulate",
         "data": "synthetic",
         "config": {"workload": f"{cfg.name} tensor-parallel x{world} decode, {B} threads x {args.history}-token history "
                                f"+ {U}-token turn (BASELINE configs[4])", "model": cfg.name, "threads": B,
