@@ -403,10 +403,11 @@ attn_prefill_tc_kernel(const __half* __restrict__ q, int q_stride, const __half*
 //   * a K/V tile is 128 keys (two KV blocks): S = Q K^T is 8 MMAs of 128 x 128 x 16, O += P V is 8 MMAs of
 //     128 x 128 x 16 over 128 tokens — 16 instructions per 128 keys instead of 24, every one of full width, and the
 //     barrier protocol runs once per 128 keys;
-//   * warp 8 issues the S MMAs, warp 9 the P V MMAs, warp 10 feeds the K/V ring (8 bulk copies of 8 KB per tile:
-//     each 64-dim plane of the two blocks side by side, which is again the canonical SWIZZLE_128B form);
-//   * TMEM: S[2] (2 x 128 columns; P_j, 64 columns of fp16 pairs, is written over the first half of S[j & 1]) +
-//     O (128) + Q (64) = 448; shared memory: 3 stages x 64 KB.
+//   * warp 8 issues the S MMAs, warp 9 the P V MMAs, warps 10 / 11 feed a K ring (4 slots) and a V ring (2 slots) of
+//     32 KB each (4 bulk copies of 8 KB per tile and ring: each 64-dim plane of the two blocks side by side, which
+//     is again the canonical SWIZZLE_128B form);
+//   * TMEM: S[2] (2 x 128 columns; each thread writes its 32 columns of P_j over the S values it alone has read) +
+//     O (128) + Q (64) = 448; shared memory: 6 x 32 KB.
 // S_{j+2} overwrites the buffer P_j lives in, and the two MMA threads are not ordered with each other: the S thread
 // waits for O += P_j V_j to retire (pv_done[j & 1]) before it issues S_{j+2}.
 // An odd number of KV blocks leaves the last tile half filled: its keys are masked (their S values are never
@@ -427,13 +428,20 @@ __device__ __forceinline__ void umma_f16_ss(uint32_t tmem_d, uint64_t desc_a, ui
 }
 
 constexpr int T128_NT = 128;
-constexpr int T128_STAGES = 3;
-constexpr int T128_HALF_BYTES = T128_NT * TC_HD * 2;        // K (or V) of one stage: 32 KB
+constexpr int T128_STAGES = 3;                              // (independent-halves variant below: one joint K/V ring)
+constexpr int T128_HALF_BYTES = T128_NT * TC_HD * 2;        // K (or V) of one 128-key tile: 32 KB
 constexpr int T128_THREADS = 352;                           // 8 softmax warps + S-MMA warp + PV-MMA warp + producer
-constexpr int T128_SMEM = 1024 + T128_STAGES * 2 * T128_HALF_BYTES + 256 + 2 * 2 * TC_ROWS * 4;
+// The default kernel keeps K and V in SEPARATE rings (tools/attn_trace.py: with one joint ring of three 64 KB stages the
+// S thread waited 0.2 - 1.3 us per tile for K to land — a stage was only handed back when O += P V of its tile had
+// retired, one tile period before the K of the tile that reuses it is needed, and a bulk copy from L2 / HBM takes about
+// that long). A K slot is free as soon as S = Q K^T of its tile has retired, a V slot when O += P V has.
+constexpr int T128_K_STAGES = 4;
+constexpr int T128_V_STAGES = 2;
+constexpr int T128D_THREADS = 384;                          // ... + a second producer warp (one per ring)
+constexpr int T128_SMEM = 1024 + (T128_K_STAGES + T128_V_STAGES) * T128_HALF_BYTES + 256 + 2 * 2 * TC_ROWS * 4;
 
 template <int GROUP>
-__global__ void __launch_bounds__(T128_THREADS, 1)
+__global__ void __launch_bounds__(T128D_THREADS, 1)
 attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __half* __restrict__ kpool,
                           const __half* __restrict__ vpool, const int* __restrict__ cu_seqlens,
                           const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
@@ -441,21 +449,29 @@ attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __ha
     constexpr int TQ = TC_ROWS / GROUP;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* kv_s = smem;                                  // ring: stage x (K 32 KB | V 32 KB)
-    uint64_t* kv_full = reinterpret_cast<uint64_t*>(kv_s + T128_STAGES * 2 * T128_HALF_BYTES);
-    uint64_t* kv_empty = kv_full + T128_STAGES;
-    uint64_t* s_full = kv_empty + T128_STAGES;             // [2]
+    constexpr int KS = T128_K_STAGES, VS = T128_V_STAGES;
+    uint8_t* k_s = smem;                                   // K ring: KS slots of 32 KB
+    uint8_t* v_s = k_s + KS * T128_HALF_BYTES;             // V ring: VS slots of 32 KB
+    uint64_t* k_full = reinterpret_cast<uint64_t*>(v_s + VS * T128_HALF_BYTES);
+    uint64_t* k_empty = k_full + KS;
+    uint64_t* v_full = k_empty + KS;
+    uint64_t* v_empty = v_full + VS;
+    uint64_t* s_full = v_empty + VS;                       // [2]
     uint64_t* p_full = s_full + 2;                         // [2]
     uint64_t* pv_done = p_full + 2;                        // [2]
     uint64_t* q_ready = pv_done + 2;                       // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_ready + 1);
-    float* mx_x = reinterpret_cast<float*>(kv_s + T128_STAGES * 2 * T128_HALF_BYTES + 256);   // [parity][half][row]
+    float* mx_x = reinterpret_cast<float*>(v_s + VS * T128_HALF_BYTES + 256);   // [parity][half][row]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 8 && lane == 0) {
-        for (int s = 0; s < T128_STAGES; ++s) {
-            mbar_init(&kv_full[s], 1);
-            mbar_init(&kv_empty[s], 1);
+        for (int s = 0; s < KS; ++s) {
+            mbar_init(&k_full[s], 1);
+            mbar_init(&k_empty[s], 1);
+        }
+        for (int s = 0; s < VS; ++s) {
+            mbar_init(&v_full[s], 1);
+            mbar_init(&v_empty[s], 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(&s_full[a], 1);
@@ -468,11 +484,10 @@ attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __ha
         tmem_alloc(tmem_slot, 512);
         tmem_relinquish();
     } else if (warp < 8) {
-        // V rows of the second block of every stage: finite before anything multiplies them by P = 0
-        for (int st = 0; st < T128_STAGES; ++st)
+        // V rows of the second block of every slot: finite before anything multiplies them by P = 0
+        for (int st = 0; st < VS; ++st)
             for (int pl = 0; pl < 2; ++pl) {
-                uint4* z = reinterpret_cast<uint4*>(kv_s + st * 2 * T128_HALF_BYTES + T128_HALF_BYTES + pl * (T128_NT * 128) +
-                                                    64 * 128);
+                uint4* z = reinterpret_cast<uint4*>(v_s + st * T128_HALF_BYTES + pl * (T128_NT * 128) + 64 * 128);
                 for (int i = threadIdx.x; i < 64 * 128 / 16; i += TC_SOFTMAX_THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
             }
         fence_proxy_async();
@@ -498,25 +513,28 @@ attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __ha
     const uint32_t o_tmem = tmem_base + 256;               // O, 128 columns
     const uint32_t q_tmem = tmem_base + 384;               // Q as the A operand of S: 128 fp16 = 64 columns
 
-    if (warp == 10) {
-        // ===== producer =====
+    if (warp >= 10) {
+        // ===== producers: warp 10 feeds the K ring, warp 11 the V ring =====
         if (lane == 0) {
+            const bool is_v = warp == 11;
+            const int ns = is_v ? VS : KS;
+            uint64_t* full = is_v ? v_full : k_full;
+            uint64_t* empty = is_v ? v_empty : k_empty;
+            uint8_t* ring = is_v ? v_s : k_s;
+            const __half* pool = is_v ? vpool : kpool;
             const int* bt = block_tables + (size_t)seq * max_blocks;
             for (int j = 0; j < n_tiles; ++j) {
-                const int st = j % T128_STAGES;
-                mbar_wait_relaxed(&kv_empty[st], (uint32_t)(((j / T128_STAGES) & 1) ^ 1));
+                const int st = j % ns;
+                mbar_wait_relaxed(&empty[st], (uint32_t)(((j / ns) & 1) ^ 1));
                 const int nb = min(2, n_blk - 2 * j);
-                uint8_t* ks = kv_s + st * 2 * T128_HALF_BYTES;
-                mbar_arrive_expect_tx(&kv_full[st], (uint32_t)(nb * 2 * TC_TILE_BYTES));
+                uint8_t* dst = ring + st * T128_HALF_BYTES;
+                mbar_arrive_expect_tx(&full[st], (uint32_t)(nb * TC_TILE_BYTES));
                 for (int b = 0; b < nb; ++b) {
                     const size_t off = ((size_t)bt[2 * j + b] * n_kv_heads + kvh) * KB_BLOCK_TOKENS * TC_HD;
 #pragma unroll
-                    for (int pl = 0; pl < 2; ++pl) {       // plane pl of block b -> rows [64 b, 64 b + 64) of plane pl
-                        bulk_g2s(ks + pl * (T128_NT * 128) + b * (64 * 128), kpool + off + pl * (64 * 64), 64 * 128,
-                                 &kv_full[st]);
-                        bulk_g2s(ks + T128_HALF_BYTES + pl * (T128_NT * 128) + b * (64 * 128), vpool + off + pl * (64 * 64),
-                                 64 * 128, &kv_full[st]);
-                    }
+                    for (int pl = 0; pl < 2; ++pl)         // plane pl of block b -> rows [64 b, 64 b + 64) of plane pl
+                        bulk_g2s(dst + pl * (T128_NT * 128) + b * (64 * 128), pool + off + pl * (64 * 64), 64 * 128,
+                                 &full[st]);
                 }
             }
         }
@@ -527,11 +545,13 @@ attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __ha
             mbar_wait(q_ready, 0);
             tc_fence_after();
             for (int j = 0; j < n_tiles; ++j) {
-                const int st = j % T128_STAGES, a = j & 1;
-                mbar_wait_relaxed(&kv_full[st], (uint32_t)((j / T128_STAGES) & 1));
+                const int st = j % KS, a = j & 1;
+                mbar_wait_relaxed(&k_full[st], (uint32_t)((j / KS) & 1));
+                KB_ATRACE(j, 0);                               // S thread: K of tile j landed
                 if (j >= 2) mbar_wait_relaxed(&pv_done[a], (uint32_t)(((j - 2) >> 1) & 1));   // P_{j-2} has been consumed
                 tc_fence_after();
-                const uint64_t kdesc = desc_kmajor(smem_u32(kv_s + st * 2 * T128_HALF_BYTES));
+                KB_ATRACE(j, 1);                               // S thread: O += P V of tile j - 2 seen retired
+                const uint64_t kdesc = desc_kmajor(smem_u32(k_s + st * T128_HALF_BYTES));
                 const uint32_t d = s_tmem + (uint32_t)(a * 128);
 #pragma unroll
                 for (int pl = 0; pl < 2; ++pl)
@@ -540,6 +560,8 @@ attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __ha
                         umma_f16_ts(d, q_tmem + (uint32_t)(pl * 32 + k * 8),
                                     kdesc + (uint64_t)((pl * (T128_NT * 128) + k * 32) >> 4), id_s, (uint32_t)((pl | k) != 0));
                 umma_commit(&s_full[a]);
+                umma_commit(&k_empty[st]);                     // K_j is consumed as soon as S_j has retired
+                KB_ATRACE(j, 2);                               // S thread: S_j issued and committed
             }
         }
     } else if (warp == 9) {
@@ -547,18 +569,20 @@ attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __ha
         if (lane == 0 && n_tiles > 0) {
             const uint32_t id_o = idesc_f16(TC_HD, 1);         // N = 128 dims, B MN-major
             for (int j = 0; j < n_tiles; ++j) {
-                const int st = j % T128_STAGES, a = j & 1;
+                const int st = j % VS, a = j & 1;
+                mbar_wait_relaxed(&v_full[st], (uint32_t)((j / VS) & 1));
                 mbar_wait_relaxed(&p_full[a], (uint32_t)((j >> 1) & 1));   // P_j written (and O rescaled if m moved)
                 tc_fence_after();
-                const uint64_t vdesc = desc_mnmajor(smem_u32(kv_s + st * 2 * T128_HALF_BYTES + T128_HALF_BYTES),
-                                                    T128_NT * 128, 1024);
+                KB_ATRACE(j, 5);                               // PV thread: V_j landed and P_j seen
+                const uint64_t vdesc = desc_mnmajor(smem_u32(v_s + st * T128_HALF_BYTES), T128_NT * 128, 1024);
                 const uint32_t pa = s_tmem + (uint32_t)(a * 128);
 #pragma unroll
-                for (int k = 0; k < 8; ++k)       // 16 tokens per step: two 8-row groups of the V tile
-                    umma_f16_ts(o_tmem, pa + (uint32_t)(k * 8), vdesc + (uint64_t)((k * 2048) >> 4), id_o,
-                                (uint32_t)((j | k) != 0));
+                for (int k = 0; k < 8; ++k)       // 16 tokens per step; P of keys [64 h, 64 h + 64) sits at columns 64 h ..
+                    umma_f16_ts(o_tmem, pa + (uint32_t)((k >> 2) * 64 + (k & 3) * 8), vdesc + (uint64_t)((k * 2048) >> 4),
+                                id_o, (uint32_t)((j | k) != 0));
                 umma_commit(&pv_done[a]);
-                umma_commit(&kv_empty[st]);       // K_j and V_j are both consumed
+                umma_commit(&v_empty[st]);        // V_j is consumed
+                KB_ATRACE(j, 6);                               // PV thread: O += P_j V_j issued and committed
             }
         }
     } else {
@@ -596,63 +620,92 @@ attn_prefill_tc128_kernel(const __half* __restrict__ q, int q_stride, const __ha
             const int a = j & 1;
             mbar_wait(&s_full[a], (uint32_t)((j >> 1) & 1));
             tc_fence_after();
-            uint32_t u0[32], u1[32];
+            if (threadIdx.x == 0) KB_ATRACE(j, 3);         // softmax: S_j seen complete
             const uint32_t s_mine = s_tmem + lane_off + (uint32_t)(a * 128 + half * 64);
-            tmem_ld_32x32(s_mine, u0);
-            tmem_ld_32x32(s_mine + 32u, u1);
-            tmem_ld_wait();
             const int tok0 = j * T128_NT + half * 64;
-            float mx = -INFINITY;
-            if (tok0 + 64 > lim) {                         // causal / length mask: only the last tiles of a row
+            const bool masked = tok0 + 64 > lim;           // causal / length mask: only the last tiles of a row
+            // OPTIMISTIC pass: exponentiate against the running max of the tiles before (m), 32 columns at a time,
+            // without waiting for this tile's row max. After the first tiles of a row the max rarely moves by more than
+            // the lazy threshold, so this is usually the final result — and with no barrier between the tensor-memory
+            // loads and the MUFU work the warps drift apart, so one warp's tcgen05.ld (64 B/clk per SM: 64 KB of S per
+            // tile) runs under another's exponentials instead of all warps doing first the one, then the other.
+            uint32_t pk[32];                               // this thread's 64 probabilities, fp16 pairs
+            float mx = -INFINITY, sum = 0.f;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    if (tok0 + i >= lim) u0[i] = 0xff800000u;             // -inf
-                    if (tok0 + 32 + i >= lim) u1[i] = 0xff800000u;
+            for (int c = 0; c < 2; ++c) {
+                uint32_t u[32];
+                tmem_ld_32x32(s_mine + (uint32_t)(c * 32), u);
+                tmem_ld_wait();
+                if (masked) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (tok0 + c * 32 + i >= lim) u[i] = 0xff800000u;     // -inf
+                }
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const float s0 = __uint_as_float(u[2 * i]), s1 = __uint_as_float(u[2 * i + 1]);
+                    mx = fmaxf(mx, fmaxf(s0, s1));
+                    const float p0 = ex2_approx(fmaf(s0, sc, -m));           // m = -inf on the first tile: redone below
+                    const float p1 = ex2_approx(fmaf(s1, sc, -m));
+                    sum += p0 + p1;
+                    pk[c * 16 + i] = pack_f16(p0, p1);
                 }
             }
-#pragma unroll
-            for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaxf(__uint_as_float(u0[i]), __uint_as_float(u1[i])));
             float* xb = mx_x + a * (2 * TC_ROWS);
             xb[half * TC_ROWS + r] = mx;
-            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");   // both halves hold S_j in registers
+            asm volatile("bar.sync 1, %0;" ::"n"(TC_SOFTMAX_THREADS) : "memory");   // both halves hold S_j's row max
             const float tile_mx = fmaxf(mx, xb[(half ^ 1) * TC_ROWS + r]) * sc;
             const float m_new = (tile_mx > m + 8.f) ? tile_mx : m;      // lazily raised running max (log2 units)
             const float corr = ex2_approx(m - m_new);                   // m = -inf on the first tile -> 0
-            m = m_new;
-            float sum = 0.f;
+            if (__any_sync(0xffffffffu, m_new != m)) {
+                // the max moved for some row of this warp (both threads of a row decide alike): second pass against
+                // the new max, from S itself — P has not been written over it yet
+                sum = 0.f;
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {                 // probabilities, packed in place as fp16 pairs
-                const float p0 = ex2_approx(fmaf(__uint_as_float(u0[2 * i]), sc, -m_new));
-                const float p1 = ex2_approx(fmaf(__uint_as_float(u0[2 * i + 1]), sc, -m_new));
-                const float p2 = ex2_approx(fmaf(__uint_as_float(u1[2 * i]), sc, -m_new));
-                const float p3 = ex2_approx(fmaf(__uint_as_float(u1[2 * i + 1]), sc, -m_new));
-                sum += (p0 + p1) + (p2 + p3);
-                u0[i] = pack_f16(p0, p1);
-                u1[i] = pack_f16(p2, p3);
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t u[32];
+                    tmem_ld_32x32(s_mine + (uint32_t)(c * 32), u);
+                    tmem_ld_wait();
+                    if (masked) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (tok0 + c * 32 + i >= lim) u[i] = 0xff800000u;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float p0 = ex2_approx(fmaf(__uint_as_float(u[2 * i]), sc, -m_new));
+                        const float p1 = ex2_approx(fmaf(__uint_as_float(u[2 * i + 1]), sc, -m_new));
+                        sum += p0 + p1;
+                        pk[c * 16 + i] = pack_f16(p0, p1);
+                    }
+                }
             }
+            m = m_new;
             l = l * corr + sum;
-            // P_j (this thread's 64 probabilities = 32 columns) over the first half of S[a]
-            const uint32_t p_mine = s_tmem + lane_off + (uint32_t)(a * 128 + half * 32);
-            tmem_st_32x16(p_mine, reinterpret_cast<const uint32_t(&)[16]>(u0[0]));
-            tmem_st_32x16(p_mine + 16u, reinterpret_cast<const uint32_t(&)[16]>(u1[0]));
+            // P_j: this thread's 64 probabilities = 32 columns, written over the first half of ITS OWN 64 columns of
+            // S[a] — columns no other thread reads, so a second pass of the row's other thread cannot be overtaken
+            tmem_st_32x16(s_mine, reinterpret_cast<const uint32_t(&)[16]>(pk[0]));
+            tmem_st_32x16(s_mine + 16u, reinterpret_cast<const uint32_t(&)[16]>(pk[16]));
             // ---- the running max moved: rescale this warp's rows of O in tensor memory (rare) ----
             if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
                 mbar_wait(&pv_done[(j - 1) & 1], (uint32_t)(((j - 1) >> 1) & 1));   // O holds tiles 0 .. j-1
                 tc_fence_after();
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
-                    tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u0);
+                    uint32_t u[32];
+                    tmem_ld_32x32(o_mine + (uint32_t)(c * 32), u);
                     tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) u0[i] = __float_as_uint(__uint_as_float(u0[i]) * corr);
-                    tmem_st_32x16(o_mine + (uint32_t)(c * 32), reinterpret_cast<const uint32_t(&)[16]>(u0[0]));
-                    tmem_st_32x16(o_mine + (uint32_t)(c * 32 + 16), reinterpret_cast<const uint32_t(&)[16]>(u0[16]));
+                    for (int i = 0; i < 32; ++i) u[i] = __float_as_uint(__uint_as_float(u[i]) * corr);
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32), reinterpret_cast<const uint32_t(&)[16]>(u[0]));
+                    tmem_st_32x16(o_mine + (uint32_t)(c * 32 + 16), reinterpret_cast<const uint32_t(&)[16]>(u[16]));
                 }
             }
             tmem_st_wait();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_full[a]);        // the PV warp may issue O += P_j V_j
+            if (threadIdx.x == 0) KB_ATRACE(j, 4);         // softmax: P_j published (warp 0)
         }
         if (n_tiles > 0) {
             mbar_wait(&pv_done[(n_tiles - 1) & 1], (uint32_t)(((n_tiles - 1) >> 1) & 1));
@@ -1028,7 +1081,7 @@ int launch_tc128(const void* q, int q_stride, const void* kp, const void* vp, co
     }
     constexpr int TQ = TC_ROWS / GROUP;
     dim3 grid((max_new + TQ - 1) / TQ, n_kv_heads, n_seqs);
-    KB_CUDA(launch_kernel(kern, grid, dim3(T128_THREADS), T128_SMEM, stream, (const __half*)q, q_stride,
+    KB_CUDA(launch_kernel(kern, grid, dim3(T128D_THREADS), T128_SMEM, stream, (const __half*)q, q_stride,
                           (const __half*)kp, (const __half*)vp, cu, ctx, bt, (uint16_t*)out, max_blocks,
                           n_heads, n_kv_heads, out_f16));
     count_launch();

@@ -1,9 +1,11 @@
 """Per-tile timeline of the tcgen05 prefill attention kernel (CTA 0): who waits for whom.
 Needs a trace build:  make -C kafka-llm-service_b200/csrc clean all EXTRA=-DKB_ATTN_TRACE   (rebuild without EXTRA afterwards).
 
-Slots per tile j (ns, relative to the MMA thread's start of tile 8):
-  0 MMA thread begins iteration j | 1 S_{j+1} issued | 2 OT_j issued
-  3 softmax begins iteration j    | 4 S_j ready      | 5 P_j written | 6 OT_{j-1} ready | 7 waits of issue_s(j+1) over
+Slots per 128-key tile j of the default kernel (attn_prefill_tc128_kernel), ns relative to slot 0 of tile 4:
+  0 S thread: K/V of tile j landed   | 1 S thread: O += P V of tile j-2 seen retired | 2 S_j issued + committed
+  3 softmax (warp 0): S_j seen done  | 4 softmax (warp 0): P_j published
+  5 PV thread: P_j seen              | 6 PV thread: O += P_j V_j issued + committed
+(The 64-key kernels, KB_ATTN_TC64=1, use their own slot meanings: see KB_ATRACE in csrc/kb_attn_tc.cu.)
 """
 import ctypes as C
 import json
@@ -32,9 +34,14 @@ for _ in range(3):
 torch.cuda.synchronize()
 t = (C.c_ulonglong * 512)()
 assert lib.kb_debug_attn_trace(t) == 0
-rows = [[int(t[j * 8 + s]) for s in range(8)] for j in range(34)]
-base = rows[8][0]
-for j in range(8, 16):
-    print(j, [v - base if v else None for v in rows[j]])
-per = (rows[30][3] - rows[10][3]) / 20
-print(json.dumps({"ns_per_tile": per}))
+rows = [[int(t[j * 8 + s]) for s in range(8)] for j in range(17)]
+base = rows[4][0]
+for j in range(4, 12):
+    print(j, [v - base if v else None for v in rows[j][:7]])
+d = lambda a, b: sum(rows[j][b] - rows[j][a] for j in range(4, 14)) / 10
+print(json.dumps({"ns_per_tile": (rows[14][3] - rows[4][3]) / 10,
+                  "S issue (1->2)": d(1, 2), "S committed -> softmax sees it (2->3)": d(2, 3),
+                  "softmax (3->4)": d(3, 4), "P published -> PV thread sees it (4->5)": d(4, 5),
+                  "PV issue (5->6)": d(5, 6),
+                  "PV_j committed -> S thread sees it retired, tile j+2 (6->1)":
+                      sum(rows[j + 2][1] - rows[j][6] for j in range(4, 12)) / 8}))
