@@ -889,6 +889,22 @@ def run_b200(args, rank, world, local_rank):
                 "per_launch": alone,
                 "what": "each projection over all layers' weights back to back, no events between launches (the "
                         "profile's per-kernel events add ~10 us to every launch)"}
+            # Which of the two GEMM figures the un-instrumented step agrees with: the profile's per-kernel times
+            # sum to MORE than the step the headline `value` was timed on (events between launches), the
+            # standalone figure plus the profile's other kernels should land on it.
+            prof_sum = sum(v[0] for v in prof.values()) / K
+            roofline["gemm"]["consistency"] = {
+                "step_ms_timed_without_events": ms_step, "sum_of_profiled_kernels_ms": prof_sum,
+                "profiled_non_gemm_ms_plus_standalone_gemm_ms": prof_sum - gemm_ms + tot_us * cfg.n_layers / 1e3}
+            est = roofline["gemm"]["consistency"]["profiled_non_gemm_ms_plus_standalone_gemm_ms"]
+            g = roofline["gemm"]
+            g["in_step_profile"] = {"achieved": g["achieved"], "frac": g["frac"], "ms_per_step": g["ms_per_step"]}
+            if abs(est - ms_step) < abs(prof_sum - ms_step):
+                # the standalone times explain the un-instrumented step better: they are the GEMM roofline figure
+                g.update(achieved=tf_alone, frac=tf_alone / tf_peak, ms_per_step=tot_us * cfg.n_layers / 1e3,
+                         source="standalone (see consistency)")
+            else:
+                g["source"] = "in-step profile"
             del a_h, a_q, a_f, xres, o_qkv, o_h
         except Exception as ex:      # a measurement aid must not cost the bench line
             roofline["gemm"]["standalone"] = {"failed": repr(ex)}
@@ -960,11 +976,16 @@ def run_b200(args, rank, world, local_rank):
         # per-turn TTFT against history length (north_star: independent of it): 16 concurrent threads
         if rank == 0 and world == 1 and not args.no_ttft_sweep:   # N = 1 only: no rank waits on rank 0's extras
             sweep = {}
-            for h in (256, 1024, 2048, 4096):
+            for h in (256, 1024, 2048, 4096, 7936):      # 7936 + turn = the 8192-position limit
                 if h + 192 + 32 > cfg.max_pos:
                     continue
-                r = provider_turn(eng, cfg, 16, h, U, 32, seed=1000 + h)
-                sweep[str(h)] = {"ttft_p50_ms": r["ttft_p50_ms"], "cached_fraction": r["cached_fraction_of_prompt"],
+                # three turns on fresh threads per length, the median of their p50s: one turn of 16 threads is a
+                # single prefill call, and a one-off (first launch of a GEMM shape, a GC pass) is ~10 ms of it
+                rs = [provider_turn(eng, cfg, 16, h, U, 32, seed=1000 + h + 7919 * k) for k in range(3)]
+                p50s = sorted(r["ttft_p50_ms"] for r in rs)
+                r = rs[0]
+                sweep[str(h)] = {"ttft_p50_ms": p50s[1], "ttft_p50_ms_each_turn": [x["ttft_p50_ms"] for x in rs],
+                                 "cached_fraction": r["cached_fraction_of_prompt"],
                                  "prefilled_new_tokens": r["prefilled_new_tokens"]}
             e2e["ttft_vs_history_16_threads"] = sweep
             try:    # the same turn through the HTTP server (first SSE line with content)

@@ -5,7 +5,7 @@ random init, against the fp32 CPU oracle (oracle/llama_fp32.py) on the same seed
 Two layers instead of 32 keep the fp32 side at ~6 GB and a few seconds per forward; every kernel variant the
 32-layer benchmark launches is exercised at its real problem size:
   * prefill of 300 tokens and an incremental prefill of 100 tokens on the cached prefix
-    (attn_prefill_tc_kernel<4>, the CTA-pair / 1-CTA GEMMs at M = 300 / 100, lm_head at M = 1);
+    (attn_prefill_tc128_kernel, the CTA-pair / 1-CTA GEMMs at M = 300 / 100, lm_head at M = 1);
   * teacher-forced decode at batch 1 (small-M GEMM with cluster split-K, split-KV attention on a 2 200-token
     context), batch 40 (1-CTA GEMM) and batch 200 (CTA-pair GEMM at N = 6 144 / 28 672 / 4 096, K = 14 336,
     lm_head at N = 128 256; unsplit attention) from the same resident state.
