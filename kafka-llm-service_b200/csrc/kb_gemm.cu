@@ -347,32 +347,54 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
     return v;
 }
 
+// Tiles up to 256 columns wide: ring of 6 x 32 KB stages, two accumulators of 256 tensor-memory columns (the
+// epilogue of tile i runs under the main loop of tile i + 1).
+// WIDE tiles, 256 < bn <= 512: the accumulator takes all 512 columns and every k-step issues TWO MMAs that share
+// the A operand — N = 256 into columns [0, 256) and N = bn - 256 into [256, bn). Why: an SM takes in ~49 B/clk
+// through TMA whatever the source and however many SMs ask (tools/tma_ingress.cu), and a 256 x 256 tile needs
+// 32 KB per CTA per k-block for 512 cycles of MMA = 64 B/clk — the main loop of every tile up to 256 wide is paced
+// by operand staging, not by the tensor pipe. At 256 x 512 the same 16 KB of A feed twice the math: 48 KB per
+// 1024 cycles = 47 B/clk. The price: one accumulator, so the epilogue no longer hides under the next tile's main
+// loop, and a ring of 4 - 6 deeper stages (40 - 48 KB each).
 struct Gemm2Cfg {
-    static constexpr int BN_MAX = 256;
+    static constexpr int BN_MAX = 256;                          // widest single MMA
+    static constexpr int BN_WIDE_MAX = 512;
     static constexpr int A_BYTES = GEMM_BM * GEMM_BK * 2;
     static constexpr int B_BYTES_MAX = (BN_MAX / 2) * GEMM_BK * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES_MAX;   // per CTA
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES_MAX;   // per CTA, tiles up to 256 wide
     static constexpr int STAGES = 6;                            // 192 KB
-    static constexpr int TMEM_COLS = 2 * BN_MAX;                // double-buffered accumulator
+    static constexpr int MAX_STAGES = 6;
+    static constexpr int TMEM_COLS = 2 * BN_MAX;                // two accumulators, or one wide one
     static constexpr int BAR_BYTES = 256;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
+    static constexpr int WIDE_RING_BYTES = 216 * 1024;          // wide tiles: as many stages as fit in this
+    static constexpr int SMEM_BYTES_WIDE = WIDE_RING_BYTES + BAR_BYTES + 1024;
+    // bytes of one stage of a wide tile: A + this CTA's bn / 2 rows of B, kept 1024-aligned for SWIZZLE_128B
+    __host__ __device__ static constexpr int wide_stage_bytes(int bn) { return A_BYTES + (((bn / 2) * GEMM_BK * 2 + 1023) & ~1023); }
+    __host__ __device__ static constexpr int wide_stages(int bn) {
+        return WIDE_RING_BYTES / wide_stage_bytes(bn) < MAX_STAGES ? WIDE_RING_BYTES / wide_stage_bytes(bn) : MAX_STAGES;
+    }
 };
 
 template <int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, void* out,
-                         const float* resid, int M, int N, int K, int bn, uint32_t is_bf16, int splits,
-                         unsigned long long tag) {
+gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmB2, void* out, const float* resid, int M, int N, int K,
+                         int bn, uint32_t is_bf16, int splits, unsigned long long tag) {
     using Cfg = Gemm2Cfg;
     const int BN = bn;
     const int half_n = bn >> 1;                       // B rows staged by one CTA
+    const bool wide = bn > Cfg::BN_MAX;               // one 512-column accumulator, two MMAs per k-step
+    const int n2 = wide ? bn - Cfg::BN_MAX : 0;       // width of the second MMA
+    const int stage_bytes = wide ? Cfg::wide_stage_bytes(bn) : Cfg::STAGE_BYTES;
+    const int n_stages = wide ? Cfg::wide_stages(bn) : Cfg::STAGES;
     const uint32_t stage_tx = 2u * (uint32_t)(Cfg::A_BYTES + half_n * GEMM_BK * 2);
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
 
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
-    uint64_t* empty_bar = full_bar + Cfg::STAGES;
-    uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + n_stages * stage_bytes);
+    uint64_t* empty_bar = full_bar + Cfg::MAX_STAGES;
+    uint64_t* tmem_full_bar = empty_bar + Cfg::MAX_STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
 
@@ -393,10 +415,11 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (elect_one()) {
             tma_prefetch_desc(&tmA);
             tma_prefetch_desc(&tmB);
+            if (wide) tma_prefetch_desc(&tmB2);
         }
     } else if (warp == 1) {
         if (elect_one()) {
-            for (int s = 0; s < Cfg::STAGES; ++s) {
+            for (int s = 0; s < n_stages; ++s) {
                 mbar_init(&full_bar[s], 1);      // leader's producer arms it; both CTAs' TMA bytes land on it
                 mbar_init(&empty_bar[s], 1);     // one multicast commit per use
             }
@@ -430,22 +453,27 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 const int mp = tile % num_mp;
                 const int n_blk = tile / num_mp;
                 const int row0 = mp * 2 * GEMM_BM + (int)cta * GEMM_BM;        // this CTA's 128 rows of A
-                const int nrow0 = n_blk * BN + (int)cta * half_n;              // this CTA's half of B
+                // this CTA's half of B. Wide tile: its half of the first 256 columns (128 rows) and, behind them,
+                // its half of the remaining n2 — accumulator column j is output column n_blk * BN + j either way
+                const int nrow0 = n_blk * BN + (int)cta * (wide ? Cfg::BN_MAX / 2 : half_n);
+                const int nrow1 = n_blk * BN + Cfg::BN_MAX + (int)cta * (n2 >> 1);
                 for (int kb = kb_lo; kb < kb_lo + kps; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+                    uint8_t* sa = smem + stage * stage_bytes;
                     uint8_t* sb = sa + Cfg::A_BYTES;
                     if (cta == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
                     tma_load_2d_2cta(sa, &tmA, kb * GEMM_BK, row0, &full_bar[stage]);
                     tma_load_2d_2cta(sb, &tmB, kb * GEMM_BK, nrow0, &full_bar[stage]);
-                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                    if (wide) tma_load_2d_2cta(sb + Cfg::B_BYTES_MAX, &tmB2, kb * GEMM_BK, nrow1, &full_bar[stage]);
+                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer (leader CTA only) =====
         if (cta == 0 && elect_one()) {
-            const uint32_t idesc = make_idesc(2 * GEMM_BM, BN, is_bf16);
+            const uint32_t idesc = make_idesc(2 * GEMM_BM, wide ? Cfg::BN_MAX : BN, is_bf16);
+            const uint32_t idesc2 = make_idesc(2 * GEMM_BM, wide ? n2 : BN, is_bf16);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
@@ -459,20 +487,35 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     tc_fence_after();
                     if (kb == 0) KB_TRACE(2);        // first operands landed
                     if (kb == kps - 1) KB_TRACE(3);  // last operands landed
-                    const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+                    const uint32_t sa = smem_u32(smem + stage * stage_bytes);
                     const uint64_t adesc = make_sw128_kmajor_desc(sa);
                     const uint64_t bdesc = make_sw128_kmajor_desc(sa + Cfg::A_BYTES);
+                    if (!wide) {
 #pragma unroll
-                    for (int k = 0; k < GEMM_BK / 16; ++k) {
-                        umma_f16_2cta(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
-                                      (uint32_t)((kb | k) != 0));
+                        for (int k = 0; k < GEMM_BK / 16; ++k) {
+                            umma_f16_2cta(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                                          (uint32_t)((kb | k) != 0));
+                        }
+                    } else {
+                        const uint64_t bdesc2 = make_sw128_kmajor_desc(sa + Cfg::A_BYTES + Cfg::B_BYTES_MAX);
+#pragma unroll
+                        for (int k = 0; k < GEMM_BK / 16; ++k) {
+                            umma_f16_2cta(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
+                                          (uint32_t)((kb | k) != 0));
+                            umma_f16_2cta(d_tmem + (uint32_t)Cfg::BN_MAX, adesc + (uint64_t)(k * 2),
+                                          bdesc2 + (uint64_t)(k * 2), idesc2, (uint32_t)((kb | k) != 0));
+                        }
                     }
                     umma_commit_2cta(&empty_bar[stage]);
                     if (kb == kps - 1) umma_commit_2cta(&tmem_full_bar[acc]);
-                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
                 }
-                acc ^= 1;
-                if (acc == 0) acc_phase ^= 1;
+                if (wide) {                          // one accumulator: the same barrier pair every unit
+                    acc_phase ^= 1;
+                } else {
+                    acc ^= 1;
+                    if (acc == 0) acc_phase ^= 1;
+                }
             }
         }
     } else if (warp >= 4) {
@@ -531,8 +574,12 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 if (lane == 0) atomicMax(flag, tag + (unsigned long long)part + 1ull);
             }
             if (threadIdx.x == 128) KB_TRACE(5);     // this warp's rows stored
-            acc ^= 1;
-            if (acc == 0) acc_phase ^= 1;
+            if (wide) {
+                acc_phase ^= 1;
+            } else {
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
         }
     }
 
@@ -931,17 +978,19 @@ static int dispatch_epi(const CUtensorMap& tmA, const CUtensorMap& tmB, void* ou
 static std::atomic<unsigned long long> g_splitk_epoch{1};   // tag of a split-K launch = epoch * 16
 
 template <int EPI>
-static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
-                            int N, int K, int bn, int splits, uint32_t is_bf16, cudaStream_t stream) {
+static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmB2, void* out,
+                            const float* resid, int M, int N, int K, int bn, int splits, uint32_t is_bf16,
+                            cudaStream_t stream) {
     using Cfg = Gemm2Cfg;
     static bool configured[64] = {};
     auto kern = gemm_tcgen05_2cta_kernel<EPI>;
     int dev = 0;
     KB_CUDA(cudaGetDevice(&dev));
     if (!configured[dev & 63]) {
-        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        KB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES_WIDE));
         configured[dev & 63] = true;
     }
+    const int smem_bytes = bn > Cfg::BN_MAX ? Cfg::SMEM_BYTES_WIDE : Cfg::SMEM_BYTES;
     const int num_tiles = ((M + 2 * GEMM_BM - 1) / (2 * GEMM_BM)) * ((N + bn - 1) / bn);
     if (splits > 1) {
         KB_CHECK(EPI == KB_EPI_RESID_F32 && resid == out, "kb_gemm: split-K needs the in-place residual epilogue");
@@ -954,25 +1003,26 @@ static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void
     const int num_units = num_tiles * splits;
     const int max_clusters = num_sms() / 2;
     const int clusters = num_units < max_clusters ? num_units : max_clusters;
-    KB_CUDA(launch_kernel(kern, dim3(2 * clusters), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, stream, tmA, tmB, out, resid, M,
-                          N, K, bn, is_bf16, splits, tag));
+    KB_CUDA(launch_kernel(kern, dim3(2 * clusters), dim3(GEMM_THREADS), smem_bytes, stream, tmA, tmB, tmB2, out, resid,
+                          M, N, K, bn, is_bf16, splits, tag));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
 }
 
-static int dispatch_epi_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, void* out, const float* resid, int M,
-                             int N, int K, int bn, int splits, int epi, uint32_t ab, cudaStream_t stream) {
+static int dispatch_epi_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmB2, void* out,
+                             const float* resid, int M, int N, int K, int bn, int splits, int epi, uint32_t ab,
+                             cudaStream_t stream) {
     switch (epi) {
-        case KB_EPI_BF16: return launch_gemm_2cta<KB_EPI_BF16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
-        case KB_EPI_F32: return launch_gemm_2cta<KB_EPI_F32>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
+        case KB_EPI_BF16: return launch_gemm_2cta<KB_EPI_BF16>(tmA, tmB, tmB2, out, resid, M, N, K, bn, 1, ab, stream);
+        case KB_EPI_F32: return launch_gemm_2cta<KB_EPI_F32>(tmA, tmB, tmB2, out, resid, M, N, K, bn, 1, ab, stream);
         case KB_EPI_RESID_F32:
-            return launch_gemm_2cta<KB_EPI_RESID_F32>(tmA, tmB, out, resid, M, N, K, bn, splits, ab, stream);
+            return launch_gemm_2cta<KB_EPI_RESID_F32>(tmA, tmB, tmB2, out, resid, M, N, K, bn, splits, ab, stream);
         case KB_EPI_SWIGLU_BF16:
-            return launch_gemm_2cta<KB_EPI_SWIGLU_BF16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
+            return launch_gemm_2cta<KB_EPI_SWIGLU_BF16>(tmA, tmB, tmB2, out, resid, M, N, K, bn, 1, ab, stream);
         case KB_EPI_SWIGLU_F16:
-            return launch_gemm_2cta<KB_EPI_SWIGLU_F16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
-        case KB_EPI_F16: return launch_gemm_2cta<KB_EPI_F16>(tmA, tmB, out, resid, M, N, K, bn, 1, ab, stream);
+            return launch_gemm_2cta<KB_EPI_SWIGLU_F16>(tmA, tmB, tmB2, out, resid, M, N, K, bn, 1, ab, stream);
+        case KB_EPI_F16: return launch_gemm_2cta<KB_EPI_F16>(tmA, tmB, tmB2, out, resid, M, N, K, bn, 1, ab, stream);
     }
     set_error("kb_gemm: unknown epilogue %d", epi);
     return KB_ERR_INVALID;
@@ -1079,7 +1129,7 @@ static int pick_bn(int M, int N, int K, bool can_split, int* splits_out) {
         forced = s ? atoi(s) : 0;
         no_split = getenv("KB_GEMM_NO_SPLITK") != nullptr;
     }
-    if (forced == 64 || forced == 128 || forced == 256 || (forced <= -32 && forced >= -256 && forced % 16 == 0))
+    if (forced == 64 || forced == 128 || forced == 256 || (forced <= -32 && forced >= -512 && forced % 16 == 0))
         return forced;
     const int sms = num_sms();
     const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
@@ -1144,8 +1194,9 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
         KB_CHECK(forced_splits == 2 || forced_splits == 4, "kb_gemm: split-K takes 2 or 4 parts (got %d)", forced_splits);
     }
     KB_CHECK(tile_n == 0 || tile_n == 64 || tile_n == 128 || tile_n == 256 ||
-                 (tile_n <= -32 && tile_n >= -256 && tile_n % 16 == 0) || (tile_n >= 1 && tile_n <= 4 && tile_n != 3),
-             "kb_gemm: tile_n=%d not in {0, 64, 128, 256}, a negative multiple of 16 in [-256, -32], or 1 / 2 / 4 "
+                 (tile_n <= -32 && tile_n >= -Gemm2Cfg::BN_WIDE_MAX && tile_n % 16 == 0) ||
+                 (tile_n >= 1 && tile_n <= 4 && tile_n != 3),
+             "kb_gemm: tile_n=%d not in {0, 64, 128, 256}, a negative multiple of 16 in [-512, -32], or 1 / 2 / 4 "
              "(small-M kernel with that many CTAs per tile)", tile_n);
     static int skinny_off = -1;
     if (skinny_off < 0) skinny_off = getenv("KB_GEMM_NO_SKINNY") != nullptr;
@@ -1168,9 +1219,18 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     int rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, GEMM_BM, &tmA);
     if (rc) return rc;
     if (bn < 0) {   // CTA pair: every CTA stages half of the tile's B rows
-        rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)(-bn / 2), &tmB);
+        const int w_ = -bn;
+        if (w_ > Gemm2Cfg::BN_MAX) {   // wide tile: half of the first 256 columns and half of the rest, two loads
+            CUtensorMap tmB2;
+            rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)(Gemm2Cfg::BN_MAX / 2), &tmB);
+            if (rc) return rc;
+            rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)((w_ - Gemm2Cfg::BN_MAX) / 2), &tmB2);
+            if (rc) return rc;
+            return dispatch_epi_2cta(tmA, tmB, tmB2, out, resid, M, N, K, w_, splits, epi, a_is_bf16, stream);
+        }
+        rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)(w_ / 2), &tmB);
         if (rc) return rc;
-        return dispatch_epi_2cta(tmA, tmB, out, resid, M, N, K, -bn, splits, epi, a_is_bf16, stream);
+        return dispatch_epi_2cta(tmA, tmB, tmB, out, resid, M, N, K, w_, splits, epi, a_is_bf16, stream);
     }
     rc = get_tensor_map(w, (uint64_t)N, (uint64_t)K, (uint32_t)bn, &tmB);
     if (rc) return rc;

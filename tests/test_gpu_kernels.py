@@ -64,7 +64,9 @@ GEMM_SHAPES = [
 ]
 
 
-@pytest.mark.parametrize("tile_n", [0, 64, 128, 256, -128, -256])
+# negative tile_n = CTA-pair kernel, 256 x |tile_n| tile; beyond 256 = the wide tile (one 512-column accumulator,
+# two MMAs per k-step: N = 256 and N = |tile_n| - 256)
+@pytest.mark.parametrize("tile_n", [0, 64, 128, 256, -128, -256, -272, -400, -512])
 @pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
 def test_gemm_bf16(kb, cuda, M, N, K, tile_n):
     g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
@@ -75,7 +77,7 @@ def test_gemm_bf16(kb, cuda, M, N, K, tile_n):
     torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
 
 
-@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256])
+@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256, -320, -512])
 @pytest.mark.parametrize("M,N,K", [(17, 136, 192), (300, 1000, 320), (512, 4096, 1024)])
 def test_gemm_f32_and_residual(kb, cuda, M, N, K, tile_n):
     g = torch.Generator(device="cpu").manual_seed(M + N + K)
@@ -94,7 +96,7 @@ def test_gemm_f32_and_residual(kb, cuda, M, N, K, tile_n):
     torch.testing.assert_close(r2, want, rtol=2e-3, atol=2e-3)
 
 
-@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256])
+@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256, -384, -512])
 @pytest.mark.parametrize("M,F,K", [(17, 80, 192), (300, 512, 256), (512, 1408, 1024)])
 def test_gemm_swiglu(kb, cuda, M, F, K, tile_n):
     g = torch.Generator(device="cpu").manual_seed(M + F + K)
@@ -107,7 +109,7 @@ def test_gemm_swiglu(kb, cuda, M, F, K, tile_n):
     torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
 
 
-@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256])
+@pytest.mark.parametrize("tile_n", [64, 128, 256, -128, -256, -288, -512])
 def test_gemm_fp16_operands(kb, cuda, tile_n):
     """The hot path's operand format: A (activations) and W (bf16 values re-encoded as fp16) both fp16,
     fp32 accumulate. The fp32 epilogue must match an fp32 matmul of the same values to
@@ -185,7 +187,7 @@ def _fp32_matmul(a, w):
         torch.backends.cuda.matmul.allow_tf32 = prev
 
 
-@pytest.mark.parametrize("tile_n", [0, -208, -256, 256])
+@pytest.mark.parametrize("tile_n", [0, -208, -256, 256, -392, -448, -512])
 def test_gemm_gate_up_at_llama3_8b_size(kb, cuda, tile_n):
     """512 x 28 672 x 4 096 with the SwiGLU fp16 epilogue: the heuristic's tile, the run-time width the
     decode step uses (bn = 208), the widest pair tile and the 1-CTA tile."""
@@ -201,7 +203,8 @@ def test_gemm_gate_up_at_llama3_8b_size(kb, cuda, tile_n):
 SPLIT2, SPLIT4 = 2 * 1024, 4 * 1024      # kb_gemm_ex: tile_n = -(1024 * splits + bn) forces split-K on the CTA-pair kernel
 
 
-@pytest.mark.parametrize("tile_n", [0, -112, -256, 128, -(SPLIT2 + 240), -(SPLIT4 + 256), -(SPLIT2 + 112)])
+@pytest.mark.parametrize("tile_n", [0, -112, -256, 128, -(SPLIT2 + 240), -(SPLIT4 + 256), -(SPLIT2 + 112), -512,
+                                    -(SPLIT4 + 512)])
 def test_gemm_down_in_place_residual_at_llama3_8b_size(kb, cuda, tile_n):
     """512 x 4 096 x 14 336, x += h W^T in place (red.global.add epilogue), K = 14 336; the heuristic (split-K in
     2 parts on 256 x 240 tiles), plain tiles and forced split-K."""

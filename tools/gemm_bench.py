@@ -18,7 +18,7 @@ import torch  # noqa: E402
 from kafka_b200 import cabi  # noqa: E402
 
 SHAPES = {  # name: (N, K, epilogue)
-    "qkv": (6144, 4096, cabi.EPI_BF16),
+    "qkv": (6144, 4096, cabi.EPI_F16),
     "o": (4096, 4096, cabi.EPI_RESID_F32),
     "gate_up": (28672, 4096, cabi.EPI_SWIGLU_F16),
     "down": (4096, 14336, cabi.EPI_RESID_F32),
