@@ -499,12 +499,13 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     } else {
                         const uint64_t bdesc2 = make_sw128_kmajor_desc(sa + Cfg::A_BYTES + Cfg::B_BYTES_MAX);
 #pragma unroll
-                        for (int k = 0; k < GEMM_BK / 16; ++k) {
+                        for (int k = 0; k < GEMM_BK / 16; ++k)
                             umma_f16_2cta(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc,
                                           (uint32_t)((kb | k) != 0));
+#pragma unroll
+                        for (int k = 0; k < GEMM_BK / 16; ++k)
                             umma_f16_2cta(d_tmem + (uint32_t)Cfg::BN_MAX, adesc + (uint64_t)(k * 2),
                                           bdesc2 + (uint64_t)(k * 2), idesc2, (uint32_t)((kb | k) != 0));
-                        }
                     }
                     umma_commit_2cta(&empty_bar[stage]);
                     if (kb == kps - 1) umma_commit_2cta(&tmem_full_bar[acc]);
@@ -1121,7 +1122,7 @@ static int dispatch_skinny(const void* a, const void* w, void* out, const float*
 // Tile choice: minimise the time of the busiest CTA (or CTA pair) under the static persistent schedule.
 // Returns BN for the 1-CTA kernel, -BN for the CTA-pair kernel; *splits_out > 1 = split-K work units (only
 // offered when `can_split`: the in-place residual epilogue, see g_splitk_flags).
-static int pick_bn(int M, int N, int K, bool can_split, int* splits_out) {
+static int pick_bn(int M, int N, int K, bool can_split, bool allow_wide, int* splits_out) {
     *splits_out = 1;
     static int forced = -1, no_split = -1;
     if (forced < 0) {
@@ -1129,7 +1130,8 @@ static int pick_bn(int M, int N, int K, bool can_split, int* splits_out) {
         forced = s ? atoi(s) : 0;
         no_split = getenv("KB_GEMM_NO_SPLITK") != nullptr;
     }
-    if (forced == 64 || forced == 128 || forced == 256 || (forced <= -32 && forced >= -512 && forced % 16 == 0))
+    if (forced == 64 || forced == 128 || forced == 256 || (forced <= -32 && forced >= -256 && forced % 16 == 0) ||
+        (forced < -256 && forced >= -512 && forced % 16 == 0 && M > GEMM_BM))
         return forced;
     const int sms = num_sms();
     const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
@@ -1164,11 +1166,34 @@ static int pick_bn(int M, int N, int K, bool can_split, int* splits_out) {
             for (int bn = 256; bn >= 64; bn -= 16) {
                 const long tiles = (long)num_mp * ((N + bn - 1) / bn);
                 if (splits > 1 && tiles > SPLITK_MAX_TILES) continue;
+                // ... and only while the tiles alone cannot fill the machine: with 256 tiles on 74 pairs
+                // (M = 4 096) two parts per tile cost 423 us against 386 without (tools/gemm_bench.py)
+                if (splits > 1 && tiles >= pairs) continue;
                 const long rounds = (tiles * splits + pairs - 1) / pairs;
                 const long cost = rounds * ((num_k / splits) * kblock(128 + bn / 2, bn) + epilogue(bn)) +
                                   (splits - 1) * epilogue(bn);
                 if (cost < best_cost) { best_cost = cost; best = -bn; *splits_out = splits; }
             }
+        }
+        // Wide tiles (256 < bn <= 512, one accumulator, two MMAs per k-step; see Gemm2Cfg). Per k-block a CTA moves
+        // through its shared memory, at 128 B/clk: the A rows once per MMA that reads them, all bn rows of B (its own
+        // half and the peer's), its half again for the peer, and what TMA writes — (256 + 2 bn) x 128 B for a tile up
+        // to 256 wide, (384 + 2 bn) x 128 B for a wide one: 768 cycles at bn = 256 (measured 783), ~1 310 at 464 for
+        // 1.8 x the math. Measured (tools/gemm_bench.py, sustained): the down projection (K = 14 336) gains 7 - 12 %
+        // from M = 2 048 up (806 -> 737 us at M = 8 192, the prefill chunk), loses at M = 1 024; K = 4 096 shapes
+        // gain nothing (the epilogue of a wide tile does not hide under the next main loop), SwiGLU loses 30 - 50 %.
+        if (allow_wide && best < 0 && *splits_out == 1 && num_k >= 128 && num_mp >= 8) {
+            const int nb = -best;
+            const long n_rounds = ((long)num_mp * ((N + nb - 1) / nb) + pairs - 1) / pairs;
+            const long narrow = n_rounds * (256 + 2 * nb);
+            long wbest = -1;
+            int wbn = 0;
+            for (int bn = 512; bn >= 448; bn -= 16) {
+                const long rounds = ((long)num_mp * ((N + bn - 1) / bn) + pairs - 1) / pairs;
+                const long c = rounds * (384 + 2 * bn);
+                if (wbest < 0 || c < wbest) { wbest = c; wbn = bn; }
+            }
+            if (wbest * 93 < narrow * 100) best = -wbn;
         }
     }
     return best;
@@ -1214,7 +1239,8 @@ int gemm_ex(const void* a, const void* w, void* out, const float* resid, int M, 
     const bool in_place = epi == KB_EPI_RESID_F32 && resid == reinterpret_cast<const float*>(out);
     KB_CHECK(forced_splits == 1 || (in_place && tile_n < 0),
              "kb_gemm: split-K needs the CTA-pair kernel and the in-place residual epilogue (KB_EPI_RESID_F32, out == resid)");
-    const int bn = tile_n ? tile_n : pick_bn(M, N, K, in_place, &splits);
+    const bool swiglu = epi == KB_EPI_SWIGLU_BF16 || epi == KB_EPI_SWIGLU_F16;
+    const int bn = tile_n ? tile_n : pick_bn(M, N, K, in_place, !swiglu, &splits);
     CUtensorMap tmA, tmB;
     int rc = get_tensor_map(a, (uint64_t)M, (uint64_t)K, GEMM_BM, &tmA);
     if (rc) return rc;

@@ -187,7 +187,7 @@ def _fp32_matmul(a, w):
         torch.backends.cuda.matmul.allow_tf32 = prev
 
 
-@pytest.mark.parametrize("tile_n", [0, -208, -256, 256, -392, -448, -512])
+@pytest.mark.parametrize("tile_n", [0, -208, -256, 256, -400, -448, -512])
 def test_gemm_gate_up_at_llama3_8b_size(kb, cuda, tile_n):
     """512 x 28 672 x 4 096 with the SwiGLU fp16 epilogue: the heuristic's tile, the run-time width the
     decode step uses (bn = 208), the widest pair tile and the 1-CTA tile."""

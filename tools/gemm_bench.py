@@ -22,6 +22,7 @@ SHAPES = {  # name: (N, K, epilogue)
     "o": (4096, 4096, cabi.EPI_RESID_F32),
     "gate_up": (28672, 4096, cabi.EPI_SWIGLU_F16),
     "down": (4096, 14336, cabi.EPI_RESID_F32),
+    "lm_head": (128256, 4096, cabi.EPI_F32),
 }
 
 
