@@ -71,7 +71,10 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n, uint32_t is_bf16
            | ((uint32_t)(m >> 4) << 24);   // M / 16
 }
 
-__device__ __forceinline__ float silu_f(float g) { return g / (1.0f + __expf(-g)); }
+// silu(g) = g / (1 + e^-g) with the approximate reciprocal (MUFU.RCP, 2 ulp; the result is rounded to 16 bits right
+// after): an IEEE division costs ~3x the instructions, and the epilogue warps run one per scheduler with nothing
+// to hide their latency. Denominators beyond 2^126 (g < -87) give 0 where the exact value is ~ -1e-36.
+__device__ __forceinline__ float silu_f(float g) { return __fdividef(g, 1.0f + __expf(-g)); }
 
 template <int EPI>
 __device__ __forceinline__ void epilogue_store32(const uint32_t (&r)[32], void* out, const float* resid, int row,
