@@ -808,7 +808,16 @@ def run_b200(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank)
     sampler.start()
     l0 = cabi.launch_count()
+    # KB_PROFILER_RANGE=1: cudaProfilerStart / Stop around exactly the timed steps, so that
+    # `ncu --profile-from-start off` lists the launches of the timed region and nothing of the set-up
+    ranged = os.environ.get("KB_PROFILER_RANGE") == "1"
+    if ranged:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     ms_total, ctx_start = timed(K)
+    if ranged:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     gpu_launches = cabi.launch_count() - l0
     clocks = sampler.stop()
     ms_step = ms_total / K
@@ -1162,12 +1171,13 @@ def run_tp(args, rank, world, local_rank):
         from kafka_b200.tp import TPGroup
         blocks = int(os.environ.get("KAFKA_B200_TP_BLOCKS", "0"))
         main_wire = grp.wire
-        nccl = TPGroup()
-        nccl.attach(core, extra_base=grp.buf)
-        grp.mode = "nccl"
-        r = measure()
-        others["nccl"] = {"ms_per_step": r["ms_total"] / K, "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K,
-                          "rmsnorm_ms_per_step": r["prof"]["rmsnorm"][0] / K}
+        if core.lm_head_slice is None:      # the NCCL callback needs a replicated lm_head (KAFKA_B200_TP_LM_HEAD)
+            nccl = TPGroup()
+            nccl.attach(core, extra_base=grp.buf)
+            grp.mode = "nccl"
+            r = measure()
+            others["nccl"] = {"ms_per_step": r["ms_total"] / K, "allreduce_ms_per_step": r["prof"]["allreduce"][0] / K,
+                              "rmsnorm_ms_per_step": r["prof"]["rmsnorm"][0] / K}
         for wire in ("f32", "f16", "fused"):
             if wire == main_wire:
                 continue
@@ -1197,7 +1207,9 @@ def run_tp(args, rank, world, local_rank):
         "config": {"workload": f"{cfg.name} tensor-parallel x{world} decode, {B} threads x {args.history}-token history "
                                f"+ {U}-token turn (BASELINE configs[4])", "model": cfg.name, "threads": B,
                    "history": args.history, "context_at_start": ctx_start, "resident_note": resident_note,
-                   "parallelism": f"tp{world}: heads/ffn sharded, 2 all-reduces ({grp.mode}) of [T,{cfg.hidden}] per layer",
+                   "parallelism": f"tp{world}: heads/ffn sharded, 2 all-reduces ({grp.mode}) of [T,{cfg.hidden}] per layer, "
+                                  + ("lm_head by vocabulary slice (local winner + exchange of (value, id) pairs)"
+                                     if core.lm_head_slice else "lm_head replicated"),
                    "l2": "inputs larger than L2; no explicit flush"},
         "clocks": clocks, "gpu_launches": launches, "e2e": None,
         "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel<128,8>", "achieved": achieved, "peak": hbm_peak,

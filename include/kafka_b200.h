@@ -171,6 +171,25 @@ int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32_t tp_size,
                                                         [r*ceil(T/size), ...) of the residual stream, norms them
                                                         once and multicasts the normed fp16 rows; hidden <= 8192.
                                                         Region use: x fp32 | partial fp16 | normed fp16 */);
+/* Vocabulary-sharded lm_head under tensor parallelism ("local top-1 + max-reduce"): the lm_head
+ * bound with kb_bind_weights holds only rows [vocab_offset, vocab_offset + vocab_local) of the vocabulary (both
+ * multiples of 8). kb_prefill / kb_decode then compute this rank's slice of the logits ([n_seqs, vocab_local]; a
+ * caller's logits_out receives that slice), pick the local winner per sequence (same Gumbel noise, banned id and
+ * lowest-id tie rule as the unsharded sampler, all on GLOBAL ids) and compare the ranks' (value, id) pairs through
+ * the peer region: every rank ends with the token the unsharded sampler would have picked, 8 bytes per (rank,
+ * sequence) cross NVLink, and each GPU holds 1/size of the matrix. `pairs_offset`: 2 x max_seqs x 8 bytes of the
+ * region's payload, 256-byte aligned, behind the two residual buffers. Needs kb_set_tensor_parallel_peers first;
+ * vocab_local = 0 goes back to a replicated lm_head.  No reference counterpart. */
+int kb_set_lm_head_shard(kb_engine* e, int32_t vocab_offset, int32_t vocab_local, size_t pairs_offset);
+/* The two steps on their own (unit tests). kb_sample_slice: `logits_slice` = [n_seqs, vocab_local] fp32 holding ids
+ * [vocab_offset, +vocab_local) of a `vocab`-wide vocabulary; writes per sequence {fp32 winning value, int32 global id}
+ * (8 bytes; id 0x7fffffff and value -inf when the slice holds no candidate) to out_pairs. kb_tp_argmax_pairs: every
+ * rank has such pairs at `pairs_offset` of ITS part of the region; out_tokens[s] = id of the largest value over the
+ * ranks (ties: lowest id). `epoch` as for kb_allreduce_peers (advance by 2). */
+int kb_sample_slice(const float* logits_slice, int32_t n_seqs, int32_t vocab, int32_t vocab_offset, int32_t vocab_local,
+                    const kb_sampling* sampling, void* out_pairs, kb_stream stream);
+int kb_tp_argmax_pairs(const kb_tp_peers* peers, int32_t rank, int32_t world, size_t pairs_offset, int32_t n_seqs,
+                       uint32_t epoch, int32_t* out_tokens, kb_stream stream);
 /* The fused kernel of mode 2 on its own (unit tests): reduces n_rows x hidden fp16 partial sums at
  * partial_offset of the region over all ranks, adds the sums of this rank's rows to x (local fp32,
  * [n_rows, hidden]), writes fp16(rmsnorm(x) * norm_w) of those rows to xn_offset on EVERY rank.

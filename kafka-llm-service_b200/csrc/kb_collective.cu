@@ -386,6 +386,61 @@ tp_reduce_norm_gather_kernel(const kb_tp_peers P, int rank, int world, size_t pa
     barrier_end(P, rank, world, epoch + 1);       // every row of xn has reached every rank
 }
 
+// ---------------------------------------------------------------------------------------------
+// Vocabulary-sharded lm_head: every rank has sampled inside ITS slice of the vocabulary and left, per
+// sequence, the pair (winning value, global id) in its own part of the region (sample_kernel, pair_out).
+// One block per rank: meet the other ranks (their pairs are written), read the `world` pairs of every
+// sequence straight from the peers' mappings, keep the largest value (ties: lowest id — the rule of the
+// unsharded kernel, so the result is the token the unsharded kernel picks), write the token. Every rank
+// computes the same answer; 8 bytes per (rank, sequence) cross NVLink instead of the rank's logits.
+// The pairs are double-buffered by the caller (two consecutive exchanges never share a buffer), and at
+// least one full-barrier collective of the next forward pass lies between two uses of the same buffer.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint2 ld_relaxed_sys_u32x2(const void* p) {
+    uint2 v;
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(1024)
+tp_argmax_kernel(const kb_tp_peers P, int rank, int world, size_t pairs_off, int n_seqs, uint32_t epoch,
+                 int* __restrict__ out_tokens, int* __restrict__ ctx_lens_advance) {
+    __threadfence_system();                       // the pairs (previous kernel on this stream) before the flag
+    meet_ranks(P, rank, world, epoch);
+    __syncthreads();
+    for (int seq = threadIdx.x; seq < n_seqs; seq += blockDim.x) {
+        float best = -INFINITY;
+        uint32_t best_i = 0x7fffffffu;
+#pragma unroll
+        for (int r = 0; r < KB_TP_MAX_RANKS; ++r) {
+            if (r < world) {
+                const uint2 pr = ld_relaxed_sys_u32x2(static_cast<const char*>(P.peer_base[r]) + pairs_off + (size_t)seq * 8);
+                const float v = __uint_as_float(pr.x);
+                if (v > best || (v == best && pr.y < best_i)) { best = v; best_i = pr.y; }
+            }
+        }
+        out_tokens[seq] = best_i == 0x7fffffffu ? 0 : (int)best_i;
+        if (ctx_lens_advance) ctx_lens_advance[seq] += 1;
+    }
+}
+
+int tp_argmax(const kb_tp_peers* P, int rank, int world, size_t pairs_off, int n_seqs, uint32_t epoch, int* out_tokens,
+              int* ctx_advance, cudaStream_t stream) {
+    KB_CHECK(P != nullptr && world >= 2 && world <= KB_TP_MAX_RANKS && rank >= 0 && rank < world,
+             "kb_tp_argmax: bad rank %d of %d", rank, world);
+    KB_CHECK(n_seqs > 0 && out_tokens != nullptr, "kb_tp_argmax: bad arguments");
+    KB_CHECK(pairs_off % 8 == 0 && pairs_off + (size_t)n_seqs * 8 <= P->flags_offset,
+             "kb_tp_argmax: pairs at %zu (+%zu) leave the region's payload (%zu)", pairs_off, (size_t)n_seqs * 8,
+             P->flags_offset);
+    for (int r = 0; r < world; ++r) KB_CHECK(P->peer_base[r] != nullptr, "kb_tp_argmax: no mapping of rank %d", r);
+    const kb_tp_peers Q = with_timeout(P);
+    const int threads = n_seqs < 32 ? 32 : (n_seqs > 1024 ? 1024 : ((n_seqs + 31) & ~31));
+    tp_argmax_kernel<<<1, threads, 0, stream>>>(Q, rank, world, pairs_off, n_seqs, epoch, out_tokens, ctx_advance);
+    count_launch();
+    KB_LAUNCH_CHECK();
+    return KB_OK;
+}
+
 __global__ void __launch_bounds__(256)
 gather_last_rows_kernel(const uint4* __restrict__ src, const int* __restrict__ cu_seqlens, uint4* __restrict__ dst,
                         int vecs) {
@@ -441,6 +496,12 @@ extern "C" int kb_allreduce_peers(const kb_tp_peers* peers, int32_t rank, int32_
                                   size_t n, int32_t f16, uint32_t epoch, int32_t blocks, kb_stream stream) {
     return kb::allreduce_peers(peers, rank, world, offset_bytes, n, f16, epoch, blocks,
                                reinterpret_cast<cudaStream_t>(stream));
+}
+
+extern "C" int kb_tp_argmax_pairs(const kb_tp_peers* peers, int32_t rank, int32_t world, size_t pairs_offset,
+                                  int32_t n_seqs, uint32_t epoch, int32_t* out_tokens, kb_stream stream) {
+    return kb::tp_argmax(peers, rank, world, pairs_offset, n_seqs, epoch, out_tokens, nullptr,
+                         reinterpret_cast<cudaStream_t>(stream));
 }
 
 extern "C" int kb_tp_reduce_norm_gather(const kb_tp_peers* peers, int32_t rank, int32_t world, size_t partial_offset,

@@ -220,14 +220,19 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
 }
 
 __global__ void __launch_bounds__(1024)
-sample_kernel(const float* __restrict__ logits, int vocab, float temperature, uint64_t seed, uint64_t step,
+sample_kernel(const float* __restrict__ logits, int vocab, int v0, float temperature, uint64_t seed, uint64_t step,
               int banned, int lo, int hi, int extra_a, int extra_b, const float* __restrict__ seq_temperature,
               const uint64_t* __restrict__ seq_seed, int* __restrict__ out_tokens,
-              int* __restrict__ ctx_lens_advance) {
+              int* __restrict__ ctx_lens_advance, uint2* __restrict__ pair_out) {
+    // `logits` holds `vocab` columns per row, the ids [v0, v0 + vocab) of the vocabulary (v0 = 0: all of it;
+    // a vocabulary-sharded lm_head under tensor parallelism: this rank's slice, v0 a multiple of 4). Every id
+    // below is a GLOBAL id — the Gumbel noise, the banned id and the tie rule (lowest id) are those of the
+    // unsharded kernel, so the best of the ranks' local winners IS the unsharded winner. pair_out != nullptr:
+    // write (winning value, id) for that exchange instead of the token (kb_collective.cu, tp_argmax_kernel).
     pdl_wait();
     pdl_launch();
     const int seq = blockIdx.x;
-    const float* lg = logits + (size_t)seq * vocab;
+    const float* lg = logits + (size_t)seq * vocab - v0;
     if (seq_temperature) temperature = seq_temperature[seq];
     if (seq_seed) seed ^= seq_seed[seq];
     const bool greedy = !(temperature > 0.f);
@@ -306,8 +311,12 @@ sample_kernel(const float* __restrict__ logits, int vocab, float temperature, ui
             if (ov > best || (ov == best && oi < best_i)) { best = ov; best_i = oi; }
         }
         if (lane == 0) {
-            out_tokens[seq] = best_i == 0x7fffffff ? 0 : best_i;
-            if (ctx_lens_advance) ctx_lens_advance[seq] += 1;
+            if (pair_out != nullptr) {
+                pair_out[seq] = make_uint2(__float_as_uint(best), (uint32_t)best_i);
+            } else {
+                out_tokens[seq] = best_i == 0x7fffffff ? 0 : best_i;
+                if (ctx_lens_advance) ctx_lens_advance[seq] += 1;
+            }
         }
     }
 }
@@ -410,9 +419,13 @@ int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* k
     return KB_OK;
 }
 
-int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, int* out_tokens, int* ctx_advance,
-           cudaStream_t stream) {
-    KB_CHECK(n_seqs > 0 && vocab > 0 && sp != nullptr && out_tokens != nullptr, "kb_sample: bad arguments");
+// Slice form: `logits` holds the `n_local` vocabulary ids from `v0` on (of `vocab` in all); pair_out as in the kernel.
+int sample_slice(const float* logits, int n_seqs, int vocab, int v0, int n_local, const kb_sampling* sp, int* out_tokens,
+                 int* ctx_advance, void* pair_out, cudaStream_t stream) {
+    KB_CHECK(n_seqs > 0 && vocab > 0 && sp != nullptr && (out_tokens != nullptr || pair_out != nullptr),
+             "kb_sample: bad arguments");
+    KB_CHECK(v0 >= 0 && n_local > 0 && v0 + n_local <= vocab && v0 % 4 == 0, "kb_sample: bad vocabulary slice [%d, +%d) of %d",
+             v0, n_local, vocab);
     int lo = 0, hi = vocab, ea = -1, eb = -1;
     if (sp->allowed_hi > sp->allowed_lo) {
         lo = sp->allowed_lo < 0 ? 0 : sp->allowed_lo;
@@ -422,12 +435,25 @@ int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, in
               sp->extra_b != ea) ? sp->extra_b : -1;
         KB_CHECK(hi > lo, "kb_sample: empty allowed range");
     }
-    KB_CUDA(launch_kernel(sample_kernel, dim3(n_seqs), dim3(1024), 0, stream, logits, vocab, sp->temperature, sp->seed, sp->step, sp->banned_token,
-                                               lo, hi, ea, eb, sp->seq_temperature, sp->seq_seed, out_tokens,
-                                               ctx_advance));
+    // this slice's part of the candidates (possibly none: the kernel then reports -inf / no id)
+    const int v1 = v0 + n_local;
+    if (lo < v0) lo = v0;
+    if (hi > v1) hi = v1;
+    if (hi < lo) hi = lo;
+    if (ea >= 0 && (ea < v0 || ea >= v1)) ea = -1;
+    if (eb >= 0 && (eb < v0 || eb >= v1)) eb = -1;
+    KB_CUDA(launch_kernel(sample_kernel, dim3(n_seqs), dim3(1024), 0, stream, logits, n_local, v0, sp->temperature, sp->seed,
+                          sp->step, sp->banned_token, lo, hi, ea, eb, sp->seq_temperature, sp->seq_seed, out_tokens,
+                          ctx_advance, static_cast<uint2*>(pair_out)));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
+}
+
+int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, int* out_tokens, int* ctx_advance,
+           cudaStream_t stream) {
+    KB_CHECK(out_tokens != nullptr, "kb_sample: bad arguments");
+    return sample_slice(logits, n_seqs, vocab, 0, vocab, sp, out_tokens, ctx_advance, nullptr, stream);
 }
 
 }  // namespace kb
@@ -452,6 +478,11 @@ extern "C" int kb_rope_append(void* qkv_f16, const int32_t* cu_seqlens, const in
 extern "C" int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,
                          int32_t* out_tokens, kb_stream stream) {
     return kb::sample(logits, n_seqs, vocab, sampling, out_tokens, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int kb_sample_slice(const float* logits_slice, int32_t n_seqs, int32_t vocab, int32_t vocab_offset,
+                               int32_t vocab_local, const kb_sampling* sampling, void* out_pairs, kb_stream stream) {
+    return kb::sample_slice(logits_slice, n_seqs, vocab, vocab_offset, vocab_local, sampling, nullptr, nullptr, out_pairs,
+                            reinterpret_cast<cudaStream_t>(stream));
 }
 extern "C" int kb_hbm_read_probe(const void* buf, size_t bytes, void* sink, size_t sink_bytes, kb_stream stream) {
     return kb::hbm_read_probe(buf, bytes, sink, sink_bytes, reinterpret_cast<cudaStream_t>(stream));

@@ -32,6 +32,10 @@ int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* k
                 cudaStream_t stream);
 int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, int* out_tokens, int* ctx_advance,
            cudaStream_t stream);
+int sample_slice(const float* logits, int n_seqs, int vocab, int v0, int n_local, const kb_sampling* sp, int* out_tokens,
+                 int* ctx_advance, void* pair_out, cudaStream_t stream);
+int tp_argmax(const kb_tp_peers* P, int rank, int world, size_t pairs_off, int n_seqs, uint32_t epoch, int* out_tokens,
+              int* ctx_advance, cudaStream_t stream);
 int attn_decode(const void* q, int q_stride, const void* kp, const void* vp, const int* kv_lens, int bias,
                 const int* bt, void* out, int batch, int max_blocks, int n_heads, int n_kv_heads, int head_dim,
                 int max_kv_len, void* scratch, size_t scratch_bytes, int out_f16, cudaStream_t stream);
@@ -126,6 +130,10 @@ struct kb_engine {
     int peer_wire = 0;            // 0 fp32 partial sums | 1 fp16, added to the residual by the next RMSNorm |
                                   // 2 fp16, collective + residual add + RMSNorm fused (kb_tp_reduce_norm_gather)
     uint32_t peer_epoch = 1;      // only used when the region carries no shared counter (kb_tp_peers.epoch_counter)
+    // vocabulary-sharded lm_head (kb_set_lm_head_shard): the bound lm_head holds rows [lm_v0, lm_v0 + lm_local)
+    int lm_v0 = 0, lm_local = 0;  // lm_local == 0: the whole vocabulary (replicated)
+    size_t lm_pairs_off = 0;      // region offset of 2 x max_seqs x 8 bytes: this rank's (value, id) pairs
+    int lm_parity = 0;
     // profiling: one event before every kernel (+ one closing event per call)
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_pool;  // reusable events
@@ -311,6 +319,26 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
     }
     float* lg = logits_out ? logits_out : w.logits;
     mark(KB_PROF_LM_HEAD);
+    if (e->lm_local > 0) {
+        // vocabulary-sharded lm_head: logits of this rank's slice only ([n_seqs, lm_local]; a caller's logits_out
+        // receives that slice), local winner per sequence, then the ranks' winners are compared over the region
+        KB_CHECK(e->use_peers && e->tp_size > 1, "sharded lm_head without the peer region (kb_set_tensor_parallel_peers)");
+        if ((rc = gemm(xl, e->lm_head, lg, nullptr, n_seqs, e->lm_local, c.hidden, KB_EPI_F32 | KB_GEMM_F16, stream)))
+            return rc;
+        if (out_tokens) {
+            mark(KB_PROF_SAMPLE);
+            const size_t off = e->lm_pairs_off + (size_t)e->lm_parity * e->max_seqs * 8;
+            e->lm_parity ^= 1;
+            void* pairs = static_cast<char*>(e->peers.peer_base[e->tp_rank]) + off;
+            if ((rc = sample_slice(lg, n_seqs, c.vocab, e->lm_v0, e->lm_local, sampling, nullptr, nullptr, pairs, stream)))
+                return rc;
+            if ((rc = tp_argmax(&e->peers, e->tp_rank, e->tp_size, off, n_seqs, next_epoch(e), out_tokens,
+                                advance_ctx ? ctx_lens : nullptr, stream)))
+                return rc;
+        }
+        mark(-1);
+        return KB_OK;
+    }
     if ((rc = gemm(xl, e->lm_head, lg, nullptr, n_seqs, c.vocab, c.hidden, KB_EPI_F32 | KB_GEMM_F16, stream)))
         return rc;
     if (out_tokens) {
@@ -360,6 +388,31 @@ extern "C" void kb_engine_destroy(kb_engine* e) {
     if (!e) return;
     for (cudaEvent_t ev : e->prof_pool) cudaEventDestroy(ev);
     delete e;
+}
+
+extern "C" int kb_set_lm_head_shard(kb_engine* e, int32_t vocab_offset, int32_t vocab_local, size_t pairs_offset) {
+    using namespace kb;
+    KB_CHECK(e != nullptr, "kb_set_lm_head_shard: null engine");
+    if (vocab_local <= 0) {          // back to a replicated lm_head
+        e->lm_v0 = e->lm_local = 0;
+        return KB_OK;
+    }
+    KB_CHECK(e->use_peers && e->tp_size > 1, "kb_set_lm_head_shard: configure the peer region first "
+             "(kb_set_tensor_parallel_peers)");
+    KB_CHECK(vocab_offset >= 0 && vocab_offset % 8 == 0 && vocab_local % 8 == 0 &&
+                 vocab_offset + vocab_local <= e->cfg.vocab,
+             "kb_set_lm_head_shard: slice [%d, +%d) of %d (offset and size multiples of 8)", vocab_offset, vocab_local,
+             e->cfg.vocab);
+    const size_t each = align256((size_t)e->max_tokens * e->cfg.hidden * 4);
+    const size_t need = 2 * (size_t)e->max_seqs * 8;
+    KB_CHECK(pairs_offset % 256 == 0 && pairs_offset >= 2 * each && pairs_offset + need <= e->peers.flags_offset,
+             "kb_set_lm_head_shard: %zu bytes of pairs at %zu overlap the residual buffers (2 x %zu) or the flags (%zu)",
+             need, pairs_offset, each, e->peers.flags_offset);
+    e->lm_v0 = vocab_offset;
+    e->lm_local = vocab_local;
+    e->lm_pairs_off = pairs_offset;
+    e->lm_parity = 0;
+    return KB_OK;
 }
 
 extern "C" int kb_set_tensor_parallel_peers(kb_engine* e, int32_t tp_rank, int32_t tp_size, const kb_tp_peers* peers,

@@ -92,11 +92,14 @@ SIGNATURES = {
     "kb_attn_prefill": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                   _i32, _i32, _vp]),
     "kb_sample": (C.c_int, [_vp, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
+    "kb_sample_slice": (C.c_int, [_vp, _i32, _i32, _i32, _i32, C.POINTER(Sampling), _vp, _vp]),
     "kb_select_tokens": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp]),
     "kb_hbm_read_probe": (C.c_int, [_vp, _sz, _vp, _sz, _vp]),
     "kb_set_tensor_parallel": (C.c_int, [_vp, _i32, _i32, ALLREDUCE_FN, _vp]),
     "kb_set_tensor_parallel_peers": (C.c_int, [_vp, _i32, _i32, C.POINTER(TpPeers), _i32, _i32]),
     "kb_allreduce_peers": (C.c_int, [C.POINTER(TpPeers), _i32, _i32, _sz, _sz, _i32, C.c_uint32, _i32, _vp]),
+    "kb_set_lm_head_shard": (C.c_int, [_vp, _i32, _i32, _sz]),
+    "kb_tp_argmax_pairs": (C.c_int, [C.POINTER(TpPeers), _i32, _i32, _sz, _i32, C.c_uint32, _vp, _vp]),
     "kb_tp_reduce_norm_gather": (C.c_int, [C.POINTER(TpPeers), _i32, _i32, _sz, _sz, _vp, _vp, _i32, _i32, _f,
                                            C.c_uint32, _i32, _vp]),
     "kb_profile_begin": (C.c_int, [_vp]),
@@ -293,6 +296,21 @@ def sample(logits, temperature: float = 0.0, seed: int = 0, step: int = 0, banne
     out = torch.empty((n,), dtype=torch.int32, device=logits.device)
     sp = make_sampling(temperature, seed, step, banned_token, allowed_lo, allowed_hi, extra_a, extra_b)
     check(load().kb_sample(_ptr(logits), n, vocab, C.byref(sp), _ptr(out), _stream()), "kb_sample")
+    return out
+
+
+def sample_slice(logits_slice, vocab: int, vocab_offset: int, temperature: float = 0.0, seed: int = 0, step: int = 0,
+                 banned_token: int = -1, allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1,
+                 out_pairs=None):
+    """One rank's half of vocabulary-sharded sampling: `logits_slice` [n, vocab_local] holds ids
+    [vocab_offset, +vocab_local) of a `vocab`-wide vocabulary. Returns an int32 [n, 2] tensor of
+    (fp32 bits of the winning value, global id); id 0x7fffffff when the slice holds no candidate."""
+    import torch
+    n, local = logits_slice.shape
+    out = out_pairs if out_pairs is not None else torch.empty((n, 2), dtype=torch.int32, device=logits_slice.device)
+    sp = make_sampling(temperature, seed, step, banned_token, allowed_lo, allowed_hi, extra_a, extra_b)
+    check(load().kb_sample_slice(_ptr(logits_slice), n, vocab, vocab_offset, local, C.byref(sp), _ptr(out), _stream()),
+          "kb_sample_slice")
     return out
 
 

@@ -100,11 +100,22 @@ class EngineCore:
         cabi.check(self.lib.kb_profile_end(self._h, ms, cnt), "kb_profile_end")
         return {name: (float(ms[i]), int(cnt[i])) for i, name in enumerate(cabi.PROF_CATS)}
 
+    lm_head_slice = None     # (first id, ids) when tp.build_tp_core bound a vocabulary slice of the lm_head
+
+    def _check_logits(self, logits_out, n_seqs: int) -> None:
+        if logits_out is None:
+            return
+        width = self.lm_head_slice[1] if self.lm_head_slice else self.cfg.vocab
+        if logits_out.dim() != 2 or logits_out.shape[0] < n_seqs or logits_out.shape[1] != width:
+            raise ValueError(f"logits_out must be [>= {n_seqs}, {width}] fp32 (this rank's vocabulary slice when the "
+                             f"lm_head is sharded), got {tuple(logits_out.shape)}")
+
     # ---- hot path ----------------------------------------------------------------------------
     def prefill(self, tokens: torch.Tensor, cu_seqlens: torch.Tensor, ctx_lens: torch.Tensor,
                 block_tables: torch.Tensor, max_new: int, sampling: Optional[cabi.Sampling] = None,
                 logits_out: Optional[torch.Tensor] = None, out_tokens: Optional[torch.Tensor] = None) -> None:
         n_seqs, max_blocks = block_tables.shape
+        self._check_logits(logits_out, n_seqs)
         cabi.check(self.lib.kb_prefill(self._h, tokens.data_ptr(), cu_seqlens.data_ptr(), ctx_lens.data_ptr(),
                                        block_tables.data_ptr(), n_seqs, tokens.numel(), max_blocks, int(max_new),
                                        C.byref(sampling) if sampling is not None else None,
@@ -116,6 +127,7 @@ class EngineCore:
                sampling: cabi.Sampling, out_tokens: torch.Tensor, max_ctx: int = 0,
                logits_out: Optional[torch.Tensor] = None, advance_ctx: bool = False) -> None:
         batch, max_blocks = block_tables.shape
+        self._check_logits(logits_out, batch)
         cabi.check(self.lib.kb_decode(self._h, last_tokens.data_ptr(), ctx_lens.data_ptr(),
                                       block_tables.data_ptr(), batch, max_blocks, int(max_ctx), C.byref(sampling),
                                       out_tokens.data_ptr(),

@@ -6,7 +6,11 @@ Megatron-style sharding, one process per GPU:
                                   KV heads and ffn/tp MLP columns (rows of the [out, in] weight)
     wo, w_down                    row-parallel: each rank owns the matching K-slice; the partial sums are
                                   added over the ranks — 2 collectives over [T, hidden] per layer
-    embed, norms, lm_head         replicated (every rank samples the same token, no gather)
+    embed, norms                  replicated
+    lm_head                       sharded by vocabulary rows when the peer region is in use: every rank computes
+                                  its slice of the logits and its local winner, the ranks' (value, id) pairs are
+                                  compared through the region (kb_set_lm_head_shard) — every rank ends with the
+                                  token the unsharded sampler picks; replicated with the NCCL callback
     KV cache                      sharded by KV head: each rank stores only its heads' blocks
 
 The engine is created with the rank's LOCAL shapes. The sums over ranks are done by our own kernels
@@ -43,7 +47,17 @@ def local_config(cfg: LlamaConfig, tp: int) -> LlamaConfig:
                    ffn=cfg.ffn // tp)
 
 
-def shard_weights(cfg: LlamaConfig, w: Dict[str, torch.Tensor], rank: int, tp: int) -> Dict[str, torch.Tensor]:
+def lm_head_slice(cfg: LlamaConfig, rank: int, tp: int):
+    """(first row, rows) of the vocabulary slice rank `rank` holds, or None when the vocabulary does not cut into
+    `tp` slices of a multiple of 8 rows."""
+    if tp <= 1 or cfg.vocab % (8 * tp):
+        return None
+    n = cfg.vocab // tp
+    return rank * n, n
+
+
+def shard_weights(cfg: LlamaConfig, w: Dict[str, torch.Tensor], rank: int, tp: int,
+                  shard_lm_head: bool = False) -> Dict[str, torch.Tensor]:
     """Canonical (unfused) weights of the full model -> the canonical weights of rank `rank`'s shard."""
     if tp == 1:
         return w
@@ -52,6 +66,9 @@ def shard_weights(cfg: LlamaConfig, w: Dict[str, torch.Tensor], rank: int, tp: i
     k0, k1 = rank * loc.kv_dim, (rank + 1) * loc.kv_dim
     f0, f1 = rank * loc.ffn, (rank + 1) * loc.ffn
     out = {k: w[k] for k in ("embed", "final_norm", "lm_head")}
+    sl = lm_head_slice(cfg, rank, tp) if shard_lm_head else None
+    if sl is not None:
+        out["lm_head"] = w["lm_head"][sl[0]:sl[0] + sl[1]]
     for i in range(cfg.n_layers):
         p = f"l{i}."
         out[p + "attn_norm"], out[p + "mlp_norm"] = w[p + "attn_norm"], w[p + "mlp_norm"]
@@ -65,7 +82,8 @@ def shard_weights(cfg: LlamaConfig, w: Dict[str, torch.Tensor], rank: int, tp: i
     return out
 
 
-def generate_sharded_on_device(cfg: LlamaConfig, seed: int, rank: int, tp: int, device) -> Dict[str, torch.Tensor]:
+def generate_sharded_on_device(cfg: LlamaConfig, seed: int, rank: int, tp: int, device,
+                               shard_lm_head: bool = False) -> Dict[str, torch.Tensor]:
     """Benchmark path for shapes too large for the host: every rank draws the FULL tensor of a layer on
     its GPU from the same per-tensor seed, keeps its slice and frees the rest — ranks agree on the model
     without any transfer."""
@@ -77,6 +95,9 @@ def generate_sharded_on_device(cfg: LlamaConfig, seed: int, rank: int, tp: int, 
         "final_norm": _randn((H,), seed, "final_norm", 0.1, dev, mean=1.0),
         "lm_head": _randn((cfg.vocab, H), seed, "lm_head", 1.0 / (H ** 0.5), dev).to(f16),
     }
+    sl = lm_head_slice(cfg, rank, tp) if shard_lm_head else None
+    if sl is not None:
+        out["lm_head"] = out["lm_head"][sl[0]:sl[0] + sl[1]].clone()
     q0, k0, f0 = rank * loc.q_dim, rank * loc.kv_dim, rank * loc.ffn
     for i in range(cfg.n_layers):
         p = f"l{i}."
@@ -217,9 +238,15 @@ class PeerRegion:
         self.mode = ("peers-multicast" if self.multicast else "peers-p2p") + ("" if wire == "f32" else "-" + wire)
 
 
-def residual_region_bytes(cfg: LlamaConfig, max_tokens: int) -> int:
+def residual_region_bytes(cfg: LlamaConfig, max_tokens: int, max_seqs: int = 0) -> int:
+    """Payload of the engine's region: two [max_tokens, hidden] fp32 buffers, then (max_seqs > 0) the two
+    (value, id) pair buffers of the vocabulary-sharded sampler, then 512 spare bytes."""
     each = (max_tokens * cfg.hidden * 4 + 255) & ~255
-    return 2 * each + 512
+    return 2 * each + lm_pairs_bytes(max_seqs) + 512
+
+
+def lm_pairs_bytes(max_seqs: int) -> int:
+    return (2 * max_seqs * 8 + 255) & ~255
 
 
 def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, max_tokens: int, max_seqs: int,
@@ -237,18 +264,24 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
     import sys
     from .engine_core import EngineCore
     loc = local_config(cfg, tp)
+    mode = (allreduce or os.environ.get("KAFKA_B200_TP_ALLREDUCE", "auto")) if tp > 1 else "none"
+    # lm_head by vocabulary slice: only with the peer region (the winners are compared through it), decided before
+    # the weights are cut. "auto" may still fall back to NCCL below: then the slice cannot be used and the ranks
+    # fail together, loudly (set KAFKA_B200_TP_LM_HEAD=replicated on such a machine).
+    shard_lm = (tp > 1 and mode != "nccl" and lm_head_slice(cfg, rank, tp) is not None and
+                os.environ.get("KAFKA_B200_TP_LM_HEAD", "sharded") != "replicated")
     if weights is not None:
-        fused = fuse_for_engine(loc, shard_weights(cfg, weights, rank, tp), device)
+        fused = fuse_for_engine(loc, shard_weights(cfg, weights, rank, tp, shard_lm_head=shard_lm), device)
     else:
-        fused = generate_sharded_on_device(cfg, seed, rank, tp, device)
+        fused = generate_sharded_on_device(cfg, seed, rank, tp, device, shard_lm_head=shard_lm)
     core = EngineCore(loc, fused, device, n_blocks=n_blocks, max_tokens=max_tokens, max_seqs=max_seqs)
+    core.lm_head_slice = None
     grp = None
     if tp > 1:
-        mode = allreduce or os.environ.get("KAFKA_B200_TP_ALLREDUCE", "auto")
         if mode in ("auto", "peers", "peers-f16", "peers-fused", "peers-p2p"):
             err = None
             try:
-                grp = PeerRegion(residual_region_bytes(loc, max_tokens), device, group,
+                grp = PeerRegion(residual_region_bytes(loc, max_tokens, max_seqs), device, group,
                                  use_multicast=(mode != "peers-p2p"))
             except Exception as e:
                 err, grp = e, None
@@ -261,6 +294,10 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
                 if mode != "auto":
                     raise err if err is not None else RuntimeError(
                         "another rank could not set up the symmetric region for the peer-memory all-reduce")
+                if shard_lm:
+                    raise RuntimeError("symmetric memory unavailable on at least one rank, and the lm_head was cut by "
+                                       "vocabulary for the peer region: set KAFKA_B200_TP_LM_HEAD=replicated (or "
+                                       f"KAFKA_B200_TP_ALLREDUCE=nccl) on this machine ({err!r} here)")
                 print(f"[kafka_b200.tp] symmetric memory unavailable on at least one rank ({err!r} here); every "
                       "rank falls back to NCCL", file=sys.stderr)
                 grp = None
@@ -268,6 +305,11 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
                 grp.attach(core, int(os.environ.get("KAFKA_B200_TP_BLOCKS", "0")),
                            wire={"peers-f16": "f16", "peers-fused": "fused",
                                  "auto": "fused" if cfg.hidden <= 8192 else "f16"}.get(mode, "f32"))
+                if shard_lm:
+                    v0, n = lm_head_slice(cfg, rank, tp)
+                    each = (max_tokens * loc.hidden * 4 + 255) & ~255
+                    cabi.check(core.lib.kb_set_lm_head_shard(core._h, v0, n, 2 * each), "kb_set_lm_head_shard")
+                    core.lm_head_slice = (v0, n)      # logits_out of prefill / decode is [n_seqs, n] on this rank
         if grp is None:
             grp = TPGroup(group)
             grp.attach(core)

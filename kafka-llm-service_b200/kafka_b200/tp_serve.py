@@ -4,8 +4,9 @@
                 (a plain dict of token ids, positions, block-table updates, sampling arrays) is published
                 to the other ranks before rank 0 enqueues it on its own GPU
     rank 1..n   follow(): receive a plan, enqueue the same call on the local shard. No scheduler, no
-                read-back: lm_head and the sampler are replicated, so every rank holds the same ids on its
-                device and the next plan can refer to them by slot (kb_select_tokens).
+                read-back: every rank ends a step with the same sampled ids on its device (the lm_head is cut
+                by vocabulary and the ranks' winners are compared through the peer region, or replicated with
+                NCCL), so the next plan can refer to them by slot (kb_select_tokens).
 
 The plans travel over a CPU (gloo) process group — a few hundred bytes per decode step of a stable batch —
 and the GPUs meet in the collectives of the forward pass (csrc/kb_collective.cu), which also keeps the

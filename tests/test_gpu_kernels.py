@@ -614,3 +614,35 @@ def test_sample_temperature_distribution(kb, cuda):
     freq = torch.bincount(a.long(), minlength=4).float().cpu() / 4096
     # 4096 draws: std of a frequency <= sqrt(.25/4096) = 0.0078; allow 5 sigma
     assert torch.all((freq - probs).abs() < 0.04), freq
+
+
+@pytest.mark.parametrize("n_slices", [2, 8])
+def test_sample_by_vocabulary_slices_picks_the_unsharded_token(kb, cuda, n_slices):
+    """kb_sample_slice (one rank's part of vocabulary-sharded sampling under tensor parallelism): the largest of
+    the slices' (value, id) pairs — ties to the lowest id, the rule tp_argmax_kernel applies across the ranks —
+    is exactly kb_sample's token on the full row: greedy, with Gumbel noise, with a candidate range + extras,
+    a banned id, and rows full of exact ties. The cross-GPU exchange itself is tests/test_gpu_tp.py."""
+    S, V = 257, 4096
+    nv = V // n_slices
+    g = torch.Generator(device="cpu").manual_seed(17 + n_slices)
+    cases = [dict(), dict(temperature=0.8, seed=3, step=9), dict(allowed_lo=100, allowed_hi=360, extra_a=4000, extra_b=7),
+             dict(temperature=1.3, seed=1, step=2, allowed_lo=nv - 3, allowed_hi=nv + 5, banned_token=nv),
+             dict(allowed_lo=10, allowed_hi=20), dict(banned_token=0)]
+    for it, kw in enumerate(cases * 2):
+        logits = torch.randn(S, V, generator=g)
+        if it % 2 == 1:
+            logits = (logits * 2).round() / 2
+        full = logits.to(cuda)
+        want = kb.sample(full, **kw).cpu()
+        best_v = torch.full((S,), float("-inf"))
+        best_i = torch.full((S,), 0x7fffffff, dtype=torch.int64)
+        for r in range(n_slices):
+            pairs = kb.sample_slice(full[:, r * nv:(r + 1) * nv].contiguous(), V, r * nv, **kw).cpu()
+            val = pairs[:, 0].contiguous().view(torch.float32)
+            idx = pairs[:, 1].long()
+            assert bool(((idx == 0x7fffffff) | ((idx >= r * nv) & (idx < (r + 1) * nv))).all())
+            better = (val > best_v) | ((val == best_v) & (idx < best_i))
+            best_v = torch.where(better, val, best_v)
+            best_i = torch.where(better, idx, best_i)
+        got = torch.where(best_i == 0x7fffffff, torch.zeros_like(best_i), best_i).int()
+        assert torch.equal(got, want), (kw, it)

@@ -42,8 +42,19 @@ def _worker(rank, world, port, ret, mode, model="tiny-test", n_layers=None):
         assert core.cfg.n_heads == cfg.n_heads // world and core.k_pool.shape[2] == cfg.n_kv_heads // world
         bt = torch.arange(B * mb, dtype=torch.int32).view(B, mb).to(dev)
         i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=dev)
-        logits = torch.empty(B, cfg.vocab, dtype=torch.float32, device=dev)
+        # with the peer region the lm_head is cut by vocabulary: this rank's logits are its slice [v0, v0 + nv)
+        v0, nv = core.lm_head_slice if core.lm_head_slice else (0, cfg.vocab)
+        assert (core.lm_head_slice is None) == (mode == "nccl")
+        logits = torch.empty(B, nv, dtype=torch.float32, device=dev)
         out = torch.empty(B, dtype=torch.int32, device=dev)
+        wrong = []
+
+        def check_tokens(ref_logits):
+            # the ranks' local winners, compared through the region, must be the full model's arg-max wherever the
+            # oracle's own top-2 gap leaves no doubt (2 x the logit tolerance)
+            top2 = ref_logits.topk(2, dim=-1)
+            sure = (top2.values[:, 0] - top2.values[:, 1]) > 4e-2
+            wrong.append(int((out.cpu()[sure] != top2.indices[sure, 0].int()).sum()))
         sp = cabi.make_sampling()
         cu = [0]
         for n in lens:
@@ -54,7 +65,8 @@ def _worker(rank, world, port, ret, mode, model="tiny-test", n_layers=None):
         del w
         caches = [oracle.new_cache() for _ in prompts]
         ref = oracle.forward_packed(prompts, caches)
-        errs = [(logits.cpu() - ref).abs().max().item()]
+        errs = [(logits.cpu() - ref[:, v0:v0 + nv]).abs().max().item()]
+        check_tokens(ref)
         toks = [out.cpu().clone()]
         ctx = i32(lens)
         cur = ref.argmax(-1)
@@ -63,7 +75,8 @@ def _worker(rank, world, port, ret, mode, model="tiny-test", n_layers=None):
                         advance_ctx=True)
             torch.cuda.synchronize()
             ref = oracle.decode_batch(cur, caches)
-            errs.append((logits.cpu() - ref).abs().max().item())
+            errs.append((logits.cpu() - ref[:, v0:v0 + nv]).abs().max().item())
+            check_tokens(ref)
             toks.append(out.cpu().clone())
             cur = ref.argmax(-1)
         if hasattr(grp, "allreduce_"):
@@ -81,12 +94,18 @@ def _worker(rank, world, port, ret, mode, model="tiny-test", n_layers=None):
             core.decode(cur.int().to(dev), ctx, bt, sp, out, max_ctx=max(lens) + 4, logits_out=logits, advance_ctx=True)
             torch.cuda.synchronize()
             ref = oracle.decode_batch(cur, caches)
-            errs.append((logits.cpu() - ref).abs().max().item())
+            errs.append((logits.cpu() - ref[:, v0:v0 + nv]).abs().max().item())
+            check_tokens(ref)
             assert grp.epoch > e0 + 2
         mine = torch.stack(toks).to(dev)
         gathered = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(gathered, mine)
+        errs_all = torch.tensor([max(errs), float(sum(wrong))], device=dev)
+        dist.all_reduce(errs_all, op=dist.ReduceOp.MAX)            # every rank checked its own slice
+        errs = [float(errs_all[0])]
         if rank == 0:
+            ret["wrong_tokens"] = int(errs_all[1])
+            ret["lm_head"] = "sharded" if core.lm_head_slice else "replicated"
             ret["max_err"] = max(errs)
             ret["ranks_agree"] = all(torch.equal(gathered[0], x) for x in gathered)
             ret["allreduce_calls"] = getattr(grp, "calls", None)
@@ -133,6 +152,7 @@ def test_llama3_70b_geometry_two_layers_tp2_matches_full_oracle(mode):
     print(f"llama-3-70b geometry, 2 layers, TP 2, {ret['mode']}: logits max-abs err {ret['max_err']:.3e}")
     assert ret["max_err"] <= 2e-2, ret["max_err"]
     assert ret["ranks_agree"] and ret["mode"].endswith(mode[6:])
+    assert ret["lm_head"] == "sharded" and ret["wrong_tokens"] == 0
 
 
 @needs2
@@ -146,7 +166,8 @@ def test_tensor_parallel_matches_full_oracle(mode):
     except Exception:
         raise AssertionError(f"worker failed: { {k: v for k, v in ret.items() if k.startswith('error')} }")
     assert ret["max_err"] <= 2e-2, ret["max_err"]
-    assert ret["ranks_agree"]
+    assert ret["ranks_agree"] and ret["wrong_tokens"] == 0
+    assert ret["lm_head"] == ("replicated" if mode == "nccl" else "sharded")
     if mode == "nccl":
         assert ret["allreduce_calls"] == 5 * 2 * 2    # 5 calls x 2 layers x 2 row-parallel projections
     elif mode == "peers-p2p":
@@ -200,6 +221,62 @@ def _allreduce_worker(rank, world, port, ret, use_multicast):
         raise
     finally:
         dist.destroy_process_group()
+
+
+def _argmax_worker(rank, world, port, ret):
+    """Vocabulary-sharded sampling: kb_sample_slice on this rank's columns + kb_tp_argmax_pairs over the region
+    must give exactly kb_sample's token on the full logits — greedy, with Gumbel noise, with a candidate range
+    plus extras, with a banned id, and with ties across ranks (lowest id wins)."""
+    import ctypes as C
+    import torch.distributed as dist
+    from kafka_b200 import cabi
+    from kafka_b200.tp import PeerRegion
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dev = torch.device("cuda", rank)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        S, V = 300, 4096
+        nv = V // world
+        v0 = rank * nv
+        reg = PeerRegion(2 * S * 8 + 256, dev)
+        pairs = reg.payload(torch.int32)
+        g = torch.Generator(device="cpu").manual_seed(5)
+        ok = True
+        cases = [dict(), dict(temperature=0.8, seed=3, step=9), dict(allowed_lo=100, allowed_hi=360, extra_a=4000, extra_b=7),
+                 dict(temperature=1.3, seed=1, step=2, allowed_lo=nv - 3, allowed_hi=nv + 5, banned_token=nv),
+                 dict(allowed_lo=10, allowed_hi=20), dict(banned_token=0)]
+        for it, kw in enumerate(cases * 2):
+            logits = torch.randn(S, V, generator=g)
+            if it % 2 == 1:
+                logits = (logits * 2).round() / 2            # many exact ties, within and across the slices
+            full = logits.to(dev)
+            want = cabi.sample(full, **kw)
+            mine = full[:, v0:v0 + nv].contiguous()
+            off = (it & 1) * S * 8                           # two buffers, alternately (as the engine does)
+            cabi.sample_slice(mine, V, v0, out_pairs=pairs[off // 4: off // 4 + 2 * S].view(S, 2), **kw)
+            got = torch.empty(S, dtype=torch.int32, device=dev)
+            cabi.check(cabi.load().kb_tp_argmax_pairs(C.byref(reg.peers), rank, world, off, S, reg.epoch, got.data_ptr(),
+                                                      torch.cuda.current_stream().cuda_stream), "kb_tp_argmax_pairs")
+            reg.epoch += 2
+            torch.cuda.synchronize()
+            ok &= bool(torch.equal(got, want))
+            dist.barrier()                                   # keep the ranks' case order aligned with the host RNG
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            ret["ok"] = bool(flag.item())
+    except Exception as e:
+        ret[f"error{rank}"] = repr(e)
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@needs2
+def test_sharded_sampling_equals_the_unsharded_sampler():
+    ret, world = _spawn(_argmax_worker)
+    assert ret["ok"], f"winner of {world} vocabulary slices differs from kb_sample on the full logits"
 
 
 @needs2
