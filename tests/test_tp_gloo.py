@@ -10,7 +10,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from kafka_b200.model_config import get_config
-from kafka_b200.tp import local_config, shard_weights
+from kafka_b200.tp import lm_head_slice, lm_pairs_bytes, local_config, residual_region_bytes, shard_weights
 from kafka_b200.weights import fuse_for_engine, generate_weights
 from oracle.llama_fp32 import OracleLlama
 
@@ -47,6 +47,24 @@ def _worker(rank, world, port, ret):
         dist.all_gather(gathered, got)
         if rank == 0:
             ret["ranks_agree"] = all(torch.equal(gathered[0], x) for x in gathered)
+        # the vocabulary-sharded sampler's decomposition (kb_set_lm_head_shard): every rank multiplies only ITS rows
+        # of the lm_head, keeps the winner of its slice, and the largest of the ranks' (value, id) pairs — ties to
+        # the lowest id — is the full model's arg-max
+        v0, nv = lm_head_slice(cfg, rank, world)
+        cut = shard_weights(cfg, w, rank, world, shard_lm_head=True)["lm_head"].float()
+        assert cut.shape == (nv, cfg.hidden) and torch.equal(cut, w["lm_head"][v0:v0 + nv].float())
+        xl = torch.linalg.lstsq(w["lm_head"].float(), got.T).solution.T        # some hidden rows with these logits
+        local = xl @ cut.T
+        val, idx = local.max(-1)
+        pair = torch.stack([val, (idx + v0).float()], -1)
+        pairs = [torch.empty_like(pair) for _ in range(world)]
+        dist.all_gather(pairs, pair)
+        best_v, best_i = pairs[0][:, 0], pairs[0][:, 1]
+        for p in pairs[1:]:
+            better = (p[:, 0] > best_v) | ((p[:, 0] == best_v) & (p[:, 1] < best_i))
+            best_v, best_i = torch.where(better, p[:, 0], best_v), torch.where(better, p[:, 1], best_i)
+        if rank == 0:
+            ret["sharded_argmax_ok"] = bool(torch.equal(best_i.long(), (xl @ w["lm_head"].float().T).argmax(-1)))
     finally:
         dist.destroy_process_group()
 
@@ -57,7 +75,7 @@ def test_two_rank_tensor_parallel_equals_full_model():
     port = 29500 + os.getpid() % 400
     mp.spawn(_worker, args=(2, port, ret), nprocs=2, join=True)
     assert ret["err"] < 1e-4, ret["err"]          # fp32 sums in a different order
-    assert ret["kv_heads_local"] == 1 and ret["ranks_agree"]
+    assert ret["kv_heads_local"] == 1 and ret["ranks_agree"] and ret["sharded_argmax_ok"]
 
 
 def test_shard_shapes_and_fusion():
@@ -72,6 +90,14 @@ def test_shard_shapes_and_fusion():
     parts = [shard_weights(cfg, w, r, 2) for r in range(2)]
     assert torch.equal(torch.cat([p["l0.wq"] for p in parts]), w["l0.wq"])
     assert torch.equal(torch.cat([p["l1.w_down"] for p in parts], dim=1), w["l1.w_down"])
+    # lm_head by vocabulary: the slices partition the rows; a vocabulary that does not cut evenly stays whole
+    cut = [shard_weights(cfg, w, r, 2, shard_lm_head=True)["lm_head"] for r in range(2)]
+    assert torch.equal(torch.cat(cut), w["lm_head"]) and parts[0]["lm_head"] is w["lm_head"]
+    assert lm_head_slice(get_config("llama-3-70b"), 3, 8) == (3 * 16032, 16032)
+    import dataclasses
+    assert lm_head_slice(dataclasses.replace(cfg, vocab=520), 0, 2) is None and lm_head_slice(cfg, 0, 1) is None
+    assert residual_region_bytes(cfg, 64, 16) == residual_region_bytes(cfg, 64) + lm_pairs_bytes(16) == \
+        2 * 64 * cfg.hidden * 4 + 256 + 512
     f = fuse_for_engine(local_config(cfg, 2), parts[1], "cpu")
     assert f["l0.wqkv"].shape == (2 * 64 + 2 * 64, 256) and f["l0.w_gate_up"].shape == (512, 256)
     assert f["l0.wo"].shape == (256, 128) and f["l0.w_down"].shape == (256, 256)
