@@ -11,6 +11,8 @@ Environment (same style as the reference's env-var configuration)
   KAFKA_B200_KV_FRACTION fraction of free HBM given to the KV pools (default 0.85)
   KAFKA_B200_MAX_SEQS    concurrent sequences per GPU (default 512)
   KAFKA_B200_MAX_TOKENS  packed tokens per prefill call (default 8192)
+  KAFKA_B200_CHECKPOINTS comma-separated name=dir pairs: Hugging Face Llama checkpoints (safetensors) served under
+                         `name` with their own weights and tokenizer instead of seeded random ones (checkpoint.py)
 """
 from __future__ import annotations
 
@@ -23,6 +25,22 @@ from .tokenizer import ByteTokenizer
 
 _lock = threading.Lock()
 _engines: Dict[Tuple[str, Tuple[int, ...], int, str], Any] = {}
+_tokenizers: Dict[str, Any] = {}
+
+
+def tokenizer_for(cfg: LlamaConfig):
+    """The model's tokenizer: its checkpoint's tokenizer.json when it is served from one, else the byte tokenizer."""
+    from . import checkpoint
+    tok = _tokenizers.get(cfg.name)
+    if tok is None:
+        tok = _tokenizers[cfg.name] = checkpoint.load_tokenizer(checkpoint.checkpoint_dir(cfg), cfg)
+    return tok
+
+
+def _config(model: str) -> LlamaConfig:
+    from . import checkpoint
+    checkpoint.register_from_env()
+    return get_config(model)
 
 
 def _devices() -> List[int]:
@@ -37,6 +55,7 @@ def build_engine(cfg: LlamaConfig, device_index: int, seed: int = 0, init: str =
     from .engine import Engine
     from .engine_core import EngineCore
     from .gpu_stepper import GpuStepper
+    from . import checkpoint
     from .weights import fuse_for_engine, generate_fused_on_device, generate_weights
 
     dev = torch.device("cuda", device_index)
@@ -45,6 +64,8 @@ def build_engine(cfg: LlamaConfig, device_index: int, seed: int = 0, init: str =
     max_tokens = max(max_tokens or int(os.environ.get("KAFKA_B200_MAX_TOKENS", "8192")), max_seqs)
     if weights is not None:
         fused = fuse_for_engine(cfg, weights, dev)
+    elif checkpoint.checkpoint_dir(cfg):
+        fused = checkpoint.load_fused(checkpoint.checkpoint_dir(cfg), cfg, dev)      # real weights, layer by layer
     elif cfg.weight_bytes() > (4 << 30) and init == "iid":
         fused = generate_fused_on_device(cfg, seed, dev)       # large shapes: draw on the GPU
     else:
@@ -56,14 +77,14 @@ def build_engine(cfg: LlamaConfig, device_index: int, seed: int = 0, init: str =
         frac = float(os.environ.get("KAFKA_B200_KV_FRACTION", "0.85"))
         n_blocks = max(8, int(free * frac) // EngineCore.kv_block_bytes(cfg))
     core = EngineCore(cfg, fused, dev, n_blocks=n_blocks, max_tokens=max_tokens, max_seqs=max_seqs)
-    return Engine(GpuStepper(core, ByteTokenizer(cfg.vocab), generable_only=generable_only),
+    return Engine(GpuStepper(core, tokenizer_for(cfg), generable_only=generable_only),
                   name=f"kb-engine-gpu{device_index}")
 
 
 def get_engine(model: str, **opts):
     """Process-wide engine for `model` on the configured devices (sharded when more than one)."""
     from .engine import ShardedEngine
-    cfg = get_config(model)
+    cfg = _config(model)
     devs = tuple(opts.pop("devices", None) or _devices())
     seed = int(opts.pop("seed", os.environ.get("KAFKA_B200_SEED", "0")))
     init = opts.pop("init", os.environ.get("KAFKA_B200_INIT", "iid"))
@@ -97,8 +118,8 @@ def make_provider(model: str, tool_provider: Optional[Any] = None, thread_id: Op
     from .provider import B200LLMProvider, EchoLLMProvider
     if model == "echo":
         return EchoLLMProvider(model=model, tool_provider=tool_provider)
-    cfg = get_config(model)  # KeyError for names that are not local
+    cfg = _config(model)  # KeyError for names that are not local
     engine = get_engine(model, **engine_opts)
-    return B200LLMProvider(engine, ByteTokenizer(cfg.vocab), model=model, tool_provider=tool_provider,
+    return B200LLMProvider(engine, tokenizer_for(cfg), model=model, tool_provider=tool_provider,
                            default_temperature=default_temperature, default_max_tokens=default_max_tokens,
                            thread_id=thread_id)

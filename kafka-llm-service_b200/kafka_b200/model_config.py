@@ -98,6 +98,8 @@ def get_config(name: str) -> LlamaConfig:
 
 def is_local_model(name: str) -> bool:
     try:
+        from . import checkpoint            # names given through $KAFKA_B200_CHECKPOINTS count as local models
+        checkpoint.register_from_env()
         get_config(name)
         return True
     except KeyError:

@@ -78,3 +78,102 @@ class StreamDecoder:
 
     def flush(self) -> str:
         return self._dec.decode(b"", final=True)
+
+
+class HFTokenizer:
+    """A checkpoint's own tokenizer (`tokenizer.json`, read with the `tokenizers` library) behind the interface the
+    template, the provider and the sampler use. The four control tokens are looked up by their Llama-3 spellings;
+    a tokenizer without them (Llama-2's sentencepiece vocabulary, say) is refused, since the chat template is built
+    from them. As with the byte tokenizer, text is encoded WITHOUT parsing control-token spellings out of it."""
+
+    CONTROL = {"bos_id": "<|begin_of_text|>", "start_header_id": "<|start_header_id|>",
+               "end_header_id": "<|end_header_id|>", "eot_id": "<|eot_id|>"}
+
+    def __init__(self, tokenizer_json: str, vocab_size: int):
+        from tokenizers import Tokenizer
+        self._tok = Tokenizer.from_file(tokenizer_json)
+        self.vocab_size = vocab_size
+        missing = []
+        for attr, text in self.CONTROL.items():
+            i = self._tok.token_to_id(text)
+            if i is None:
+                missing.append(text)
+            setattr(self, attr, i)
+        if missing:
+            raise ValueError(f"{tokenizer_json}: control tokens {missing} not in the vocabulary — the chat template "
+                             "needs Llama-3's")
+        if self._tok.get_vocab_size(with_added_tokens=True) > vocab_size:
+            raise ValueError(f"{tokenizer_json}: {self._tok.get_vocab_size(with_added_tokens=True)} tokens, the model's "
+                             f"embedding has {vocab_size} rows")
+        added = self._tok.get_added_tokens_decoder()
+        self.special = {int(i): t.content for i, t in added.items() if t.special}
+        # ordinary tokens = everything below the first control / special id (Llama-3: 0 .. 127 999)
+        self._first_special = min(self.special) if self.special else vocab_size
+
+    def encode(self, text: str) -> List[int]:
+        if not text:
+            return []
+        # split on control-token spellings so that none of them is ever produced from text: each spelling is
+        # encoded piecewise ("<|", "eot_id", "|>" ...) like any other characters
+        ids: List[int] = []
+        for piece in self._split_specials(text):
+            ids += self._tok.encode(piece, add_special_tokens=False).ids
+        return ids
+
+    def _split_specials(self, text: str) -> List[str]:
+        pieces = [text]
+        for spelling in set(self.special.values()):
+            nxt: List[str] = []
+            for p in pieces:
+                if spelling not in p:
+                    nxt.append(p)
+                    continue
+                parts = p.split(spelling)
+                for k, part in enumerate(parts):
+                    if part:
+                        nxt.append(part)
+                    if k + 1 < len(parts):        # the spelling itself, cut in two so that it cannot match
+                        nxt += [spelling[:2], spelling[2:]]
+            pieces = nxt
+        return pieces
+
+    def decode(self, ids: Iterable[int], skip_special: bool = True) -> str:
+        ids = [int(i) for i in ids if 0 <= int(i) < self.vocab_size]
+        return self._tok.decode(ids, skip_special_tokens=skip_special)
+
+    def stream_decoder(self) -> "HFStreamDecoder":
+        return HFStreamDecoder(self)
+
+    def generable_range(self):
+        """Every ordinary token, plus <|eot_id|>."""
+        return 0, self._first_special, self.eot_id, -1
+
+
+class HFStreamDecoder:
+    """Token-by-token detokeniser for a BPE vocabulary: a token may end in the middle of a UTF-8 sequence, and the
+    spacing of a token can depend on its left neighbour, so the text emitted for a new token is the difference
+    between decoding the pending ids with and without it, held back while it ends in a replacement character."""
+
+    def __init__(self, tok: HFTokenizer):
+        self.tok = tok
+        self._ids: List[int] = []
+        self._emitted = ""
+
+    def push(self, token_id: int) -> str:
+        if token_id in self.tok.special:
+            return ""
+        self._ids.append(int(token_id))
+        text = self.tok.decode(self._ids)
+        if text.endswith("�"):
+            return ""                              # an incomplete multi-byte character: wait for its remaining bytes
+        new = text[len(self._emitted):]
+        self._emitted = text
+        if len(self._ids) > 64 and "\n" in new:    # keep the re-decoded window short: restart after a line break
+            self._ids, self._emitted = [], ""
+        return new
+
+    def flush(self) -> str:
+        text = self.tok.decode(self._ids)
+        new = text[len(self._emitted):]
+        self._ids, self._emitted = [], ""
+        return new

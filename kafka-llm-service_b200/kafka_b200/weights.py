@@ -118,14 +118,25 @@ def fuse_for_engine(cfg: LlamaConfig, w: Dict[str, torch.Tensor], device) -> Dic
         out[k] = w[k].to(device=device, dtype=torch.bfloat16).contiguous()
     out["lm_head"] = w["lm_head"].to(device=device, dtype=f16).contiguous()
     for i in range(cfg.n_layers):
-        p = f"l{i}."
-        out[p + "attn_norm"] = w[p + "attn_norm"].to(device).contiguous()
-        out[p + "mlp_norm"] = w[p + "mlp_norm"].to(device).contiguous()
-        out[p + "wqkv"] = torch.cat([w[p + "wq"], w[p + "wk"], w[p + "wv"]], dim=0).to(device, f16).contiguous()
-        out[p + "wo"] = w[p + "wo"].to(device, f16).contiguous()
-        gu = torch.stack([w[p + "w_gate"], w[p + "w_up"]], dim=1).reshape(2 * cfg.ffn, cfg.hidden)
-        out[p + "w_gate_up"] = gu.to(device, f16).contiguous()
-        out[p + "w_down"] = w[p + "w_down"].to(device, f16).contiguous()
+        out.update(fuse_layer(cfg, w, i, device))
+    return out
+
+
+def fuse_layer(cfg: LlamaConfig, w: Dict[str, torch.Tensor], i: int, device, src_index: Optional[int] = None
+               ) -> Dict[str, torch.Tensor]:
+    """Layer `i`'s tensors in the engine's layout, read from `w`'s layer `src_index` (default i) — so that a loader
+    can stream one layer at a time through a small dict (checkpoint.load_fused)."""
+    f16 = GEMM_WEIGHT_DTYPE
+    s = f"l{i if src_index is None else src_index}."
+    p = f"l{i}."
+    out: Dict[str, torch.Tensor] = {}
+    out[p + "attn_norm"] = w[s + "attn_norm"].to(device=device, dtype=torch.bfloat16).contiguous()
+    out[p + "mlp_norm"] = w[s + "mlp_norm"].to(device=device, dtype=torch.bfloat16).contiguous()
+    out[p + "wqkv"] = torch.cat([w[s + "wq"], w[s + "wk"], w[s + "wv"]], dim=0).to(device, f16).contiguous()
+    out[p + "wo"] = w[s + "wo"].to(device, f16).contiguous()
+    gu = torch.stack([w[s + "w_gate"], w[s + "w_up"]], dim=1).reshape(2 * cfg.ffn, cfg.hidden)
+    out[p + "w_gate_up"] = gu.to(device, f16).contiguous()
+    out[p + "w_down"] = w[s + "w_down"].to(device, f16).contiguous()
     return out
 
 
