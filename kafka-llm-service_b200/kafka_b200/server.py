@@ -264,3 +264,32 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
 
     app.state.store = store
     return app
+
+
+def main(argv: Optional[List[str]] = None) -> None:
+    """`python -m kafka_b200.server`: the app on uvicorn, the way the reference starts its own
+    (/root/reference/server.py:627-631: 0.0.0.0, $PORT, default 8081), with the process-wide engines of
+    kafka_b200.factory behind it. Models: the built-in shapes (seeded random weights) plus every checkpoint
+    named in $KAFKA_B200_CHECKPOINTS (real weights and tokenizer); threads in $LOCAL_DB_PATH (data/threads.db)."""
+    import argparse
+    import os
+    import uvicorn
+    from . import checkpoint, factory
+    from .model_config import REGISTRY
+    ap = argparse.ArgumentParser(prog="python -m kafka_b200.server")
+    ap.add_argument("--host", default="0.0.0.0")
+    ap.add_argument("--port", type=int, default=int(os.environ.get("PORT", 8081)))
+    ap.add_argument("--db", default=None, help="SQLite thread store (default: $LOCAL_DB_PATH or data/threads.db)")
+    ap.add_argument("--system-prompt", default=None)
+    args = ap.parse_args(argv)
+    checkpoint.register_from_env()
+    models = sorted(checkpoint.CHECKPOINTS) + [m for m in sorted(REGISTRY) if m not in checkpoint.CHECKPOINTS] + ["echo"]
+    app = create_app(factory.make_provider, store=ThreadStore(args.db), system_prompt=args.system_prompt, models=models)
+    try:
+        uvicorn.run(app, host=args.host, port=args.port)
+    finally:
+        factory.shutdown_engines()
+
+
+if __name__ == "__main__":
+    main()

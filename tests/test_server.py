@@ -212,3 +212,54 @@ def test_thread_that_outgrew_the_context_is_compacted_and_answered(fake_engine_a
             assert r.status_code == 200 and len(body["choices"][0]["message"]["content"]) == 6
             assert body["usage"]["prompt_tokens"] <= int(0.75 * 2048)
     asyncio.run(go())
+
+
+def test_module_entry_point_serves_over_http(tmp_path):
+    """`python -m kafka_b200.server` (the counterpart of the reference's `python server.py`, server.py:627-631):
+    a real process, a real socket; the echo model keeps it GPU-free. Health, the model list (built-in shapes + echo)
+    and one streamed thread completion whose SSE lines end in [DONE]."""
+    import json
+    import os
+    import socket
+    import subprocess
+    import sys
+    import time
+    import urllib.request
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "kafka-llm-service_b200")
+    env = dict(os.environ, PYTHONPATH=pkg + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    proc = subprocess.Popen([sys.executable, "-m", "kafka_b200.server", "--host", "127.0.0.1", "--port", str(port),
+                             "--db", str(tmp_path / "threads.db")], env=env, stdout=subprocess.PIPE,
+                            stderr=subprocess.STDOUT)
+    base = f"http://127.0.0.1:{port}"
+    try:
+        for _ in range(200):
+            try:
+                with urllib.request.urlopen(base + "/health", timeout=1) as r:
+                    assert json.load(r)["status"] == "healthy"
+                break
+            except OSError:
+                assert proc.poll() is None, proc.stdout.read().decode()[-2000:]
+                time.sleep(0.1)
+        else:
+            raise AssertionError("server did not come up")
+        with urllib.request.urlopen(base + "/v1/models", timeout=5) as r:
+            ids = [m["id"] for m in json.load(r)["data"]]
+        assert "echo" in ids and "llama-3-8b" in ids
+        req = urllib.request.Request(base + "/v1/threads/t-main/chat/completions", method="POST",
+                                     headers={"Content-Type": "application/json"},
+                                     data=json.dumps({"model": "echo", "stream": True,
+                                                      "messages": [{"role": "user", "content": "ping 123"}]}).encode())
+        with urllib.request.urlopen(req, timeout=20) as r:
+            lines = [ln.decode().strip() for ln in r if ln.strip()]
+        assert lines[-1] == "data: [DONE]"
+        text = "".join(json.loads(ln[6:])["choices"][0]["delta"].get("content") or "" for ln in lines[:-1])
+        assert "ping 123" in text
+    finally:
+        proc.terminate()
+        try:
+            proc.wait(timeout=10)
+        except subprocess.TimeoutExpired:
+            proc.kill()
