@@ -201,6 +201,32 @@ def load_fused(path: str, cfg: LlamaConfig, device) -> Dict[str, "object"]:
     return out
 
 
+def load_fused_shard(path: str, cfg: LlamaConfig, rank: int, tp: int, device, shard_lm_head: bool = False
+                     ) -> Dict[str, "object"]:
+    """Rank `rank`'s tensor-parallel shard (tp.shard_weights) in the engine's layout, cut while loading: one full
+    layer passes through host memory at a time, so a 70B checkpoint needs ~2 GB of host memory per rank, not 141."""
+    from .tp import lm_head_slice, local_config, shard_weights
+    from .weights import fuse_for_engine, fuse_layer
+    if tp <= 1:
+        return load_fused(path, cfg, device)
+    loc = local_config(cfg, tp)
+    top = dict(iter_canonical(path, cfg, {"embed", "final_norm", "lm_head"}))
+    sl = lm_head_slice(cfg, rank, tp) if shard_lm_head else None
+    if sl is not None:
+        top["lm_head"] = top["lm_head"][sl[0]:sl[0] + sl[1]]
+    out = fuse_for_engine(LlamaConfig(**{**loc.to_dict(), "n_layers": 0}), top, device)
+    del top
+    layer_keys = ("attn_norm", "mlp_norm", "wq", "wk", "wv", "wo", "w_gate", "w_up", "w_down")
+    one = LlamaConfig(**{**cfg.to_dict(), "n_layers": 1})
+    for i in range(cfg.n_layers):
+        src = dict(iter_canonical(path, cfg, {f"l{i}.{k}" for k in layer_keys}))
+        full = {f"l0.{k}": src[f"l{i}.{k}"] for k in layer_keys}
+        full.update({"embed": None, "final_norm": None, "lm_head": None})      # not touched per layer
+        cut = shard_weights(one, full, rank, tp)
+        out.update(fuse_layer(loc, cut, i, device, src_index=0))
+    return out
+
+
 def load_tokenizer(path: Optional[str], cfg: LlamaConfig):
     """The checkpoint's tokenizer (tokenizer.json with Llama-3's control tokens) or, without one, the byte tokenizer."""
     from .tokenizer import ByteTokenizer, HFTokenizer
@@ -210,4 +236,4 @@ def load_tokenizer(path: Optional[str], cfg: LlamaConfig):
 
 
 __all__ = ["CHECKPOINTS", "CheckpointError", "REGISTRY", "canonical_name", "checkpoint_dir", "config_from_hf",
-           "iter_canonical", "load_canonical", "load_fused", "load_tokenizer", "register_checkpoint", "register_from_env"]
+           "iter_canonical", "load_canonical", "load_fused", "load_fused_shard", "load_tokenizer", "register_checkpoint", "register_from_env"]

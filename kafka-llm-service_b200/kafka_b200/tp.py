@@ -270,8 +270,11 @@ def build_tp_core(cfg: LlamaConfig, rank: int, tp: int, device, n_blocks: int, m
     # fail together, loudly (set KAFKA_B200_TP_LM_HEAD=replicated on such a machine).
     shard_lm = (tp > 1 and mode != "nccl" and lm_head_slice(cfg, rank, tp) is not None and
                 os.environ.get("KAFKA_B200_TP_LM_HEAD", "sharded") != "replicated")
+    from . import checkpoint
     if weights is not None:
         fused = fuse_for_engine(loc, shard_weights(cfg, weights, rank, tp, shard_lm_head=shard_lm), device)
+    elif checkpoint.checkpoint_dir(cfg):        # real weights ($KAFKA_B200_CHECKPOINTS), cut while loading
+        fused = checkpoint.load_fused_shard(checkpoint.checkpoint_dir(cfg), cfg, rank, tp, device, shard_lm_head=shard_lm)
     else:
         fused = generate_sharded_on_device(cfg, seed, rank, tp, device, shard_lm_head=shard_lm)
     core = EngineCore(loc, fused, device, n_blocks=n_blocks, max_tokens=max_tokens, max_seqs=max_seqs)

@@ -54,12 +54,12 @@ def build_tp_stepper(cfg, device, n_blocks: int, max_tokens: int, max_seqs: int,
     """This rank's shard + stepper + plan channel. Collective call on all ranks of the default group."""
     import torch.distributed as dist
     from .gpu_stepper import GpuStepper
-    from .tokenizer import ByteTokenizer
     from .tp import build_tp_core
     rank, world = dist.get_rank(), dist.get_world_size()
     core, grp = build_tp_core(cfg, rank, world, device, n_blocks=n_blocks, max_tokens=max_tokens, max_seqs=max_seqs,
                               weights=weights, seed=seed, allreduce=allreduce)
-    stepper = GpuStepper(core, ByteTokenizer(cfg.vocab), generable_only=generable_only)
+    from .factory import tokenizer_for
+    stepper = GpuStepper(core, tokenizer_for(cfg), generable_only=generable_only)
     stepper.tp_group = grp                      # keeps the symmetric region / callback alive
     chan = PlanChannel(dist.new_group(backend="gloo"))
     return stepper, chan
@@ -111,6 +111,8 @@ def main() -> None:
     torch.cuda.set_device(dev)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("nccl", device_id=dev)
+    from . import checkpoint
+    checkpoint.register_from_env()              # --model may name a checkpoint of $KAFKA_B200_CHECKPOINTS
     cfg = get_config(args.model)
     loc = local_config(cfg, dist.get_world_size())
     free, _ = torch.cuda.mem_get_info(dev)
@@ -127,9 +129,9 @@ def main() -> None:
         from .db import ThreadStore
         from .provider import B200LLMProvider
         from .server import create_app
-        from .tokenizer import ByteTokenizer
+        from .factory import tokenizer_for
         engine = lead(stepper, chan)
-        tok = ByteTokenizer(cfg.vocab)
+        tok = tokenizer_for(cfg)
 
         def provider_factory(model, tool_provider=None, thread_id=None, **kw):
             return B200LLMProvider(engine, tok, model=cfg.name, tool_provider=tool_provider, thread_id=thread_id, **kw)

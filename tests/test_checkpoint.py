@@ -61,6 +61,21 @@ def test_loaded_weights_reproduce_transformers_forward(tmp_path, layout):
     assert a.keys() == b.keys() and all(torch.equal(a[k], b[k]) for k in a)
 
 
+def test_tensor_parallel_shards_are_cut_while_loading(tmp_path):
+    """load_fused_shard = tp.shard_weights + fuse_for_engine on the whole model, without ever holding it."""
+    from kafka_b200.tp import local_config, shard_weights
+    from kafka_b200.weights import fuse_for_engine
+    _hf_model().save_pretrained(tmp_path, safe_serialization=True, max_shard_size="600KB")
+    cfg = checkpoint.config_from_hf(str(tmp_path), "hf-tiny")
+    w = checkpoint.load_canonical(str(tmp_path), cfg)
+    for rank in range(2):
+        for cut_lm in (False, True):
+            a = checkpoint.load_fused_shard(str(tmp_path), cfg, rank, 2, "cpu", shard_lm_head=cut_lm)
+            b = fuse_for_engine(local_config(cfg, 2), shard_weights(cfg, w, rank, 2, shard_lm_head=cut_lm), "cpu")
+            assert a.keys() == b.keys() and all(torch.equal(a[k], b[k]) for k in a), (rank, cut_lm)
+            assert a["lm_head"].shape[0] == (cfg.vocab // 2 if cut_lm else cfg.vocab)
+
+
 def test_unsupported_checkpoints_are_refused_by_name(tmp_path):
     m = _hf_model()
     m.save_pretrained(tmp_path, safe_serialization=True)
