@@ -282,6 +282,14 @@ int kb_rope_append(void* qkv_f16, const int32_t* cu_seqlens, const int32_t* ctx_
                    const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,
                    int32_t n_tokens, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
                    int32_t head_dim, float rope_theta, kb_stream stream);
+/* The same with the head_dim / 2 rotary frequencies given as a device table instead of theta^(-2i/head_dim) — scaled
+ * RoPE (Llama-3.1's "llama3" rule and the like are applied by the host to the table; kafka_b200.model_config.inv_freq).
+ * kb_set_rope_inv_freq makes the engine's kb_prefill / kb_decode use such a table (the pointer must stay valid; NULL
+ * returns to the theta rule).  No reference counterpart. */
+int kb_rope_append_freqs(void* qkv_f16, const int32_t* cu_seqlens, const int32_t* ctx_lens, const int32_t* block_tables,
+                         void* k_pool_layer, void* v_pool_layer, int32_t n_seqs, int32_t n_tokens, int32_t max_blocks,
+                         int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, const float* inv_freq, kb_stream stream);
+int kb_set_rope_inv_freq(kb_engine* e, const float* inv_freq);
 
 /* Paged attention, one query token per sequence, over kv_lens[s] + kv_len_bias cached tokens.
  *   q   [batch, q_stride] fp16 (first n_heads*head_dim columns are the heads); the pools are fp16;

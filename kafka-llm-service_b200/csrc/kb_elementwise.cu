@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(128)
 rope_append_kernel(__half* __restrict__ qkv, const int* __restrict__ cu_seqlens,
                    const int* __restrict__ ctx_lens, const int* __restrict__ block_tables,
                    __half* __restrict__ kpool, __half* __restrict__ vpool, int n_seqs, int max_blocks,
-                   int n_heads, int n_kv_heads, int head_dim, float log2_theta) {
+                   int n_heads, int n_kv_heads, int head_dim, float log2_theta, const float* __restrict__ inv_freq_table) {
     pdl_wait();
     pdl_launch();
     const int tkn = blockIdx.x;
@@ -154,8 +154,9 @@ rope_append_kernel(__half* __restrict__ qkv, const int* __restrict__ cu_seqlens,
     const int seq = s_seq, pos = s_pos;
     const int half = head_dim >> 1;
     if ((int)threadIdx.x < half) {
-        // inv_freq = theta^(-2i/hd)
-        const float inv_freq = exp2f(-log2_theta * (float)(2 * threadIdx.x) / (float)head_dim);
+        // inv_freq = theta^(-2i/hd), or the caller's table (scaled RoPE: Llama-3.1's rule is applied on the host)
+        const float inv_freq = inv_freq_table ? inv_freq_table[threadIdx.x]
+                                              : exp2f(-log2_theta * (float)(2 * threadIdx.x) / (float)head_dim);
         float sn, cs;
         sincosf((float)pos * inv_freq, &sn, &cs);
         s_cos[threadIdx.x] = cs;
@@ -407,13 +408,13 @@ int rmsnorm(float* x, const void* w, void* y, const int* last_rows, const void* 
 
 int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* kp, void* vp, int n_seqs,
                 int n_tokens, int max_blocks, int n_heads, int n_kv_heads, int head_dim, float theta,
-                cudaStream_t stream) {
+                const float* inv_freq, cudaStream_t stream) {
     KB_CHECK(n_tokens > 0 && n_seqs > 0, "kb_rope_append: empty batch");
     KB_CHECK(head_dim == 64 || head_dim == 128, "kb_rope_append: head_dim must be 64 or 128 (got %d)", head_dim);
     KB_CHECK(cu != nullptr || n_tokens == n_seqs, "kb_rope_append: cu_seqlens == NULL means one token per sequence");
     KB_CUDA(launch_kernel(rope_append_kernel, dim3(n_tokens), dim3(128), 0, stream, (__half*)qkv, cu, ctx, bt, (__half*)kp,
                                                       (__half*)vp, n_seqs, max_blocks, n_heads, n_kv_heads,
-                                                      head_dim, log2f(theta)));
+                                                      head_dim, log2f(theta), inv_freq));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;
@@ -472,7 +473,16 @@ extern "C" int kb_rope_append(void* qkv_f16, const int32_t* cu_seqlens, const in
                               int32_t n_tokens, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
                               int32_t head_dim, float rope_theta, kb_stream stream) {
     return kb::rope_append(qkv_f16, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_seqs, n_tokens,
-                           max_blocks, n_heads, n_kv_heads, head_dim, rope_theta,
+                           max_blocks, n_heads, n_kv_heads, head_dim, rope_theta, nullptr,
+                           reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int kb_rope_append_freqs(void* qkv_f16, const int32_t* cu_seqlens, const int32_t* ctx_lens,
+                                    const int32_t* block_tables, void* k_pool_layer, void* v_pool_layer, int32_t n_seqs,
+                                    int32_t n_tokens, int32_t max_blocks, int32_t n_heads, int32_t n_kv_heads,
+                                    int32_t head_dim, const float* inv_freq, kb_stream stream) {
+    KB_CHECK(inv_freq != nullptr, "kb_rope_append_freqs: null frequency table");
+    return kb::rope_append(qkv_f16, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_seqs, n_tokens,
+                           max_blocks, n_heads, n_kv_heads, head_dim, 10000.f, inv_freq,
                            reinterpret_cast<cudaStream_t>(stream));
 }
 extern "C" int kb_sample(const float* logits, int32_t n_seqs, int32_t vocab, const kb_sampling* sampling,

@@ -29,7 +29,7 @@ int rmsnorm(float* x, const void* w, void* y, const int* last_rows, const void* 
             int out_f16, cudaStream_t stream);
 int rope_append(void* qkv, const int* cu, const int* ctx, const int* bt, void* kp, void* vp, int n_seqs,
                 int n_tokens, int max_blocks, int n_heads, int n_kv_heads, int head_dim, float theta,
-                cudaStream_t stream);
+                const float* inv_freq, cudaStream_t stream);
 int sample(const float* logits, int n_seqs, int vocab, const kb_sampling* sp, int* out_tokens, int* ctx_advance,
            cudaStream_t stream);
 int sample_slice(const float* logits, int n_seqs, int vocab, int v0, int n_local, const kb_sampling* sp, int* out_tokens,
@@ -134,6 +134,7 @@ struct kb_engine {
     int lm_v0 = 0, lm_local = 0;  // lm_local == 0: the whole vocabulary (replicated)
     size_t lm_pairs_off = 0;      // region offset of 2 x max_seqs x 8 bytes: this rank's (value, id) pairs
     int lm_parity = 0;
+    const float* rope_inv_freq = nullptr;   // head_dim / 2 rotary frequencies (kb_set_rope_inv_freq), else theta^(-2i/hd)
     // profiling: one event before every kernel (+ one closing event per call)
     bool prof_on = false;
     std::vector<cudaEvent_t> prof_pool;  // reusable events
@@ -270,7 +271,7 @@ static int forward(kb_engine* e, const int* tokens, const int* cu_seqlens, int* 
             return rc;
         mark(KB_PROF_ROPE_APPEND);
         if ((rc = rope_append(w.qkv, cu_seqlens, ctx_lens, block_tables, kp, vp, n_seqs, n_tokens, max_blocks,
-                              c.n_heads, c.n_kv_heads, c.head_dim, c.rope_theta, stream)))
+                              c.n_heads, c.n_kv_heads, c.head_dim, c.rope_theta, e->rope_inv_freq, stream)))
             return rc;
         mark(KB_PROF_ATTENTION);
         if (decode) {
@@ -388,6 +389,12 @@ extern "C" void kb_engine_destroy(kb_engine* e) {
     if (!e) return;
     for (cudaEvent_t ev : e->prof_pool) cudaEventDestroy(ev);
     delete e;
+}
+
+extern "C" int kb_set_rope_inv_freq(kb_engine* e, const float* inv_freq) {
+    KB_CHECK(e != nullptr, "kb_set_rope_inv_freq: null engine");
+    e->rope_inv_freq = inv_freq;     // head_dim / 2 floats on the engine's device, owned by the caller; NULL = theta rule
+    return KB_OK;
 }
 
 extern "C" int kb_set_lm_head_shard(kb_engine* e, int32_t vocab_offset, int32_t vocab_local, size_t pairs_offset) {

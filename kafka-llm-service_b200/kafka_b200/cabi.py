@@ -83,6 +83,8 @@ SIGNATURES = {
     "kb_gemm": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "kb_gemm_ex": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
     "kb_rope_append": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _f, _vp]),
+    "kb_rope_append_freqs": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "kb_set_rope_inv_freq": (C.c_int, [_vp, _vp]),
     "kb_attn_decode_scratch_bytes": (_sz, [_i32, _i32, _i32]),
     "kb_attn_decode": (C.c_int, [_vp, _i32, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32,
                                  _vp, _sz, _i32, _vp]),
@@ -228,6 +230,19 @@ def rope_append(qkv, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_la
     check(load().kb_rope_append(_ptr(qkv), _ptr(cu_seqlens), _ptr(ctx_lens), _ptr(block_tables),
                                 _ptr(k_pool_layer), _ptr(v_pool_layer), n_seqs, n_tokens, max_blocks, n_heads,
                                 n_kv_heads, head_dim, theta, _stream()), "kb_rope_append")
+
+
+def rope_append_freqs(qkv, cu_seqlens, ctx_lens, block_tables, k_pool_layer, v_pool_layer, n_heads, n_kv_heads,
+                      head_dim, inv_freq):
+    """rope_append with the head_dim / 2 rotary frequencies as a float32 device tensor (scaled RoPE)."""
+    _need_f16("kb_rope_append_freqs", qkv, k_pool_layer, v_pool_layer)
+    if inv_freq.dtype != __import__("torch").float32 or inv_freq.numel() != head_dim // 2 or not inv_freq.is_cuda:
+        raise ValueError(f"inv_freq must be {head_dim // 2} float32 values on the device")
+    n_tokens = qkv.shape[0]
+    n_seqs, max_blocks = block_tables.shape
+    check(load().kb_rope_append_freqs(_ptr(qkv), _ptr(cu_seqlens), _ptr(ctx_lens), _ptr(block_tables),
+                                      _ptr(k_pool_layer), _ptr(v_pool_layer), n_seqs, n_tokens, max_blocks, n_heads,
+                                      n_kv_heads, head_dim, _ptr(inv_freq), _stream()), "kb_rope_append_freqs")
 
 
 def attn_decode(q, k_pool_layer, v_pool_layer, kv_lens, block_tables, n_heads, n_kv_heads, head_dim,

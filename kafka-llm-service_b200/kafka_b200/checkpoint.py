@@ -11,8 +11,9 @@ registers each directory under its name (factory.py reads the variable; `registe
 Tensor names follow `transformers`' LlamaForCausalLM; its q / k projections are already in the rotate-half layout this
 engine and the oracle use (tests/test_checkpoint.py: the oracle on loaded weights equals `transformers`' own forward).
 
-Unsupported checkpoint features are refused by name instead of being ignored: RoPE scaling (Llama-3.1's "llama3" rule),
-attention / MLP biases, a head_dim other than 64 / 128, non-Llama architectures.
+RoPE: plain, or Llama-3.1's "llama3" scaling rule (the frequencies are reshaped on the host, model_config.inv_freq, and
+handed to the kernel as a table). Unsupported checkpoint features are refused by name instead of being ignored: other
+RoPE scaling rules, attention / MLP biases, a head_dim other than 64 / 128, non-Llama architectures.
 """
 from __future__ import annotations
 
@@ -43,8 +44,13 @@ def config_from_hf(path: str, name: Optional[str] = None) -> LlamaConfig:
     rp = hf.get("rope_parameters") or {}
     scaling = hf.get("rope_scaling") or ({k: v for k, v in rp.items() if k != "rope_theta"}
                                          if rp.get("rope_type", "default") != "default" else None)
+    llama3 = None
     if scaling:
-        raise CheckpointError(f"{path}: rope_scaling {scaling} is not implemented (plain RoPE only)")
+        kind = scaling.get("rope_type", scaling.get("type"))
+        if kind != "llama3":
+            raise CheckpointError(f"{path}: rope_scaling {scaling} is not implemented (plain RoPE and the llama3 rule only)")
+        llama3 = (float(scaling["factor"]), float(scaling["low_freq_factor"]), float(scaling["high_freq_factor"]),
+                  int(scaling["original_max_position_embeddings"]))
     theta = float(rp.get("rope_theta", hf.get("rope_theta", 10000.0)))
     for key in ("attention_bias", "mlp_bias"):
         if hf.get(key):
@@ -59,7 +65,7 @@ def config_from_hf(path: str, name: Optional[str] = None) -> LlamaConfig:
                       n_kv_heads=int(hf.get("num_key_value_heads") or heads), head_dim=head_dim,
                       ffn=int(hf["intermediate_size"]), vocab=int(hf["vocab_size"]),
                       rope_theta=theta, rms_eps=float(hf.get("rms_norm_eps", 1e-5)),
-                      max_pos=int(hf.get("max_position_embeddings", 8192)))
+                      max_pos=int(hf.get("max_position_embeddings", 8192)), rope_llama3=llama3)
     if cfg.vocab % 8:
         raise CheckpointError(f"{path}: vocab_size {cfg.vocab} must be a multiple of 8")
     return cfg

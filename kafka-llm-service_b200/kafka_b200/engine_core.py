@@ -69,6 +69,12 @@ class EngineCore:
         self.workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device)
         cabi.check(self.lib.kb_bind_workspace(self._h, self.workspace.data_ptr(), ws_bytes, self.max_tokens,
                                               self.max_seqs), "kb_bind_workspace")
+        # scaled RoPE (Llama-3.1's rule): the frequencies are reshaped here and handed over as a table
+        self.rope_inv_freq = None
+        if cfg.rope_llama3 is not None:
+            from .model_config import inv_freq
+            self.rope_inv_freq = torch.tensor(inv_freq(cfg), dtype=torch.float32, device=self.device)
+            cabi.check(self.lib.kb_set_rope_inv_freq(self._h, self.rope_inv_freq.data_ptr()), "kb_set_rope_inv_freq")
 
     # ---- sizing helpers ----------------------------------------------------------------------
     @staticmethod

@@ -103,6 +103,7 @@ def shutdown_engines() -> None:
         for eng in _engines.values():
             eng.shutdown()
         _engines.clear()
+        _tokenizers.clear()
 
 
 def make_provider(model: str, tool_provider: Optional[Any] = None, thread_id: Optional[str] = None,

@@ -8,8 +8,9 @@ reference's remote provider.
 """
 from __future__ import annotations
 
+import math
 from dataclasses import dataclass, asdict
-from typing import Dict
+from typing import Dict, List, Optional, Tuple
 
 
 @dataclass(frozen=True)
@@ -25,6 +26,9 @@ class LlamaConfig:
     rope_theta: float = 10000.0
     rms_eps: float = 1e-5
     max_pos: int = 8192
+    # Llama-3.1's RoPE scaling rule: (factor, low_freq_factor, high_freq_factor, original_max_position_embeddings);
+    # None = plain RoPE. The rule only reshapes the head_dim / 2 frequencies (inv_freq below); nothing else changes.
+    rope_llama3: Optional[Tuple[float, float, float, int]] = None
 
     @property
     def group(self) -> int:
@@ -62,6 +66,24 @@ class LlamaConfig:
 
     def to_dict(self) -> Dict:
         return asdict(self)
+
+
+def inv_freq(cfg: LlamaConfig) -> List[float]:
+    """The head_dim / 2 rotary frequencies, in float32 steps like `transformers` computes them
+    (modeling_rope_utils: theta^(-2i/d), then for the "llama3" rule: wavelengths beyond original_max / low_freq_factor
+    are slowed by `factor`, those below original_max / high_freq_factor are kept, the band between is blended)."""
+    import torch
+    d = cfg.head_dim
+    f = 1.0 / (cfg.rope_theta ** (torch.arange(0, d, 2, dtype=torch.int64).to(torch.float32) / d))
+    if cfg.rope_llama3 is not None:
+        factor, low, high, orig = cfg.rope_llama3
+        wavelen = 2 * math.pi / f
+        scaled = torch.where(wavelen > orig / low, f / factor, f)
+        smooth = (orig / wavelen - low) / (high - low)
+        blended = (1 - smooth) * scaled / factor + smooth * scaled
+        medium = ~(wavelen < orig / high) & ~(wavelen > orig / low)
+        f = torch.where(medium, blended, scaled)
+    return [float(x) for x in f]
 
 
 REGISTRY: Dict[str, LlamaConfig] = {}

@@ -29,8 +29,10 @@ def rmsnorm(x: torch.Tensor, w: torch.Tensor, eps: float) -> torch.Tensor:
     return x * torch.rsqrt(var + eps) * w
 
 
-def rope_cos_sin(positions: torch.Tensor, head_dim: int, theta: float):
-    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32) / head_dim))
+def rope_cos_sin(positions: torch.Tensor, head_dim: int, theta: float, inv_freq=None):
+    """`inv_freq`: the head_dim / 2 frequencies when they are not the plain theta^(-2i/d) (scaled RoPE)."""
+    if inv_freq is None:
+        inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32) / head_dim))
     freqs = positions.to(torch.float32)[:, None] * inv_freq[None, :]
     return freqs.cos(), freqs.sin()  # [T, hd/2]
 
@@ -93,6 +95,11 @@ class OracleLlama:
         self.w = {k: v.detach().to("cpu", torch.float32) for k, v in weights.items()}
         self.allreduce = allreduce
         self.tp_rank = tp_rank
+        # scaled RoPE (Llama-3.1's rule): the frequencies come from the config; plain RoPE computes them in place
+        self.inv_freq = None
+        if getattr(cfg, "rope_llama3", None) is not None:
+            from kafka_b200.model_config import inv_freq
+            self.inv_freq = torch.tensor(inv_freq(cfg), dtype=torch.float32)
 
     def _residual(self, x: torch.Tensor, delta: torch.Tensor) -> torch.Tensor:
         if self.allreduce is None:
@@ -111,7 +118,7 @@ class OracleLlama:
         T = tokens.numel()
         past = cache.length
         pos = torch.arange(past, past + T)
-        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta)
+        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta, self.inv_freq)
         x = w["embed"][tokens.long()]
         scale = cfg.head_dim ** -0.5
         for i in range(cfg.n_layers):
@@ -155,7 +162,7 @@ class OracleLlama:
             offs.append(offs[-1] + n)
         pasts = [c.length for c in caches]
         pos = torch.cat([torch.arange(p, p + n) for p, n in zip(pasts, lens)])
-        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta)
+        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta, self.inv_freq)
         x = w["embed"][torch.cat([s.long() for s in seqs])]
         T = x.shape[0]
         scale = cfg.head_dim ** -0.5
@@ -192,7 +199,7 @@ class OracleLlama:
         cfg, w = self.cfg, self.w
         B = tokens.numel()
         pos = torch.tensor([c.length for c in caches])
-        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta)
+        cos, sin = rope_cos_sin(pos, cfg.head_dim, cfg.rope_theta, self.inv_freq)
         x = w["embed"][tokens.long()]
         scale = cfg.head_dim ** -0.5
         padded = B > 1 and int(pos.max()) < 1024          # short contexts: one padded batch (see below)

@@ -35,14 +35,20 @@ def _hf_model(tie=False, **kw):
     return m.eval()
 
 
-@pytest.mark.parametrize("layout", ["one_file", "sharded", "tied"])
+LLAMA3_ROPE = {"rope_theta": 50000.0, "rope_type": "llama3", "factor": 4.0, "low_freq_factor": 1.0,
+               "high_freq_factor": 4.0, "original_max_position_embeddings": 64}
+
+
+@pytest.mark.parametrize("layout", ["one_file", "sharded", "tied", "llama3_rope"])
 def test_loaded_weights_reproduce_transformers_forward(tmp_path, layout):
-    m = _hf_model(tie=(layout == "tied"))
+    # llama3_rope: Llama-3.1's scaled RoPE (wavelengths beyond 64 / 1 positions slowed 4x, the band down to 64 / 4 blended)
+    m = _hf_model(tie=(layout == "tied"), **({"rope_parameters": LLAMA3_ROPE} if layout == "llama3_rope" else {}))
     m.save_pretrained(tmp_path, safe_serialization=True, max_shard_size="600KB" if layout == "sharded" else "10GB")
     assert (tmp_path / "model.safetensors.index.json").exists() == (layout == "sharded")
     cfg = checkpoint.config_from_hf(str(tmp_path), "hf-tiny")
     assert (cfg.hidden, cfg.n_layers, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.ffn, cfg.vocab, cfg.max_pos) == \
         (256, 2, 4, 2, 64, 512, 512, 2048) and cfg.rope_theta == 50000.0 and cfg.rms_eps == 1e-5
+    assert cfg.rope_llama3 == ((4.0, 1.0, 4.0, 64) if layout == "llama3_rope" else None)
     w = checkpoint.load_canonical(str(tmp_path), cfg)
     sd = m.state_dict()
     assert w["l1.wk"].dtype == torch.bfloat16 and torch.equal(w["l1.wk"].float(), sd["model.layers.1.self_attn.k_proj.weight"])
@@ -80,8 +86,8 @@ def test_unsupported_checkpoints_are_refused_by_name(tmp_path):
     m = _hf_model()
     m.save_pretrained(tmp_path, safe_serialization=True)
     conf = json.loads((tmp_path / "config.json").read_text())
-    for patch, word in [({"rope_scaling": {"rope_type": "llama3", "factor": 8.0}}, "rope_scaling"),        # transformers 4
-                        ({"rope_parameters": {"rope_theta": 5e5, "rope_type": "llama3", "factor": 8.0}}, "rope_scaling"),
+    for patch, word in [({"rope_scaling": {"rope_type": "yarn", "factor": 8.0}}, "rope_scaling"),          # transformers 4
+                        ({"rope_parameters": {"rope_theta": 5e5, "rope_type": "linear", "factor": 8.0}}, "rope_scaling"),
                         ({"attention_bias": True}, "attention_bias"), ({"model_type": "mistral", "architectures": ["X"]}, "Llama"),
                         ({"head_dim": 96}, "head_dim")]:
         (tmp_path / "config.json").write_text(json.dumps({**conf, **patch}))
@@ -90,6 +96,10 @@ def test_unsupported_checkpoints_are_refused_by_name(tmp_path):
     old_style = {k: v for k, v in conf.items() if k != "rope_parameters"}                # a transformers-4 config.json
     (tmp_path / "config.json").write_text(json.dumps({**old_style, "rope_theta": 123456.0, "rope_scaling": None}))
     assert checkpoint.config_from_hf(str(tmp_path)).rope_theta == 123456.0
+    t4 = {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+          "original_max_position_embeddings": 8192}
+    (tmp_path / "config.json").write_text(json.dumps({**old_style, "rope_theta": 5e5, "rope_scaling": t4}))
+    assert checkpoint.config_from_hf(str(tmp_path)).rope_llama3 == (8.0, 1.0, 4.0, 8192)
     (tmp_path / "config.json").write_text(json.dumps({**conf, "num_hidden_layers": 3}))
     with pytest.raises(checkpoint.CheckpointError, match="missing"):
         checkpoint.load_canonical(str(tmp_path), checkpoint.config_from_hf(str(tmp_path)))

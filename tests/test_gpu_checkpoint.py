@@ -16,16 +16,20 @@ sys.path.insert(0, os.path.dirname(__file__))
 TOL = 2e-2
 
 
-@pytest.fixture(scope="module")
-def ckpt(tmp_path_factory):
+@pytest.fixture(scope="module", params=["plain_rope", "llama3_rope"])
+def ckpt(tmp_path_factory, request):
     from test_checkpoint import _bpe_tokenizer_json
     from kafka_b200 import checkpoint
     from kafka_b200.model_config import REGISTRY
     d = tmp_path_factory.mktemp("hf-ckpt")
     # head_dim 128 (the tcgen05 prefill-attention path), GQA group 4, tied-free, 3 layers
+    # llama3_rope: Llama-3.1's scaled RoPE — the engine then rotates with a frequency table (kb_set_rope_inv_freq)
+    rope = ({"rope_parameters": {"rope_theta": 500000.0, "rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0,
+                                 "high_freq_factor": 4.0, "original_max_position_embeddings": 128}}
+            if request.param == "llama3_rope" else {"rope_theta": 500000.0})
     hf_cfg = transformers.LlamaConfig(hidden_size=512, intermediate_size=1024, num_hidden_layers=3, num_attention_heads=4,
                                       num_key_value_heads=1, head_dim=128, vocab_size=512, max_position_embeddings=4096,
-                                      rope_theta=500000.0, rms_norm_eps=1e-5, tie_word_embeddings=False)
+                                      rms_norm_eps=1e-5, tie_word_embeddings=False, **rope)
     torch.manual_seed(7)
     m = transformers.LlamaForCausalLM(hf_cfg)
     with torch.no_grad():
@@ -36,6 +40,7 @@ def ckpt(tmp_path_factory):
     m.eval().save_pretrained(d, safe_serialization=True, max_shard_size="2MB")
     _bpe_tokenizer_json(d / "tokenizer.json")
     cfg = checkpoint.register_checkpoint(str(d), "hf-tiny-ckpt")
+    assert (cfg.rope_llama3 is not None) == (request.param == "llama3_rope")
     yield cfg, m, str(d)
     REGISTRY.pop(cfg.name, None)
     checkpoint.CHECKPOINTS.pop(cfg.name, None)
