@@ -728,7 +728,7 @@ def run_b200(args, rank, world, local_rank):
     torch.cuda.empty_cache()
     free, total = torch.cuda.mem_get_info(dev)
     block_bytes = EngineCore.kv_block_bytes(cfg)
-    prefill_chunk = 8192
+    prefill_chunk = 4096      # measured (tools/prefill_profile.py --chunk): 433 ms per 32 768-token turn prefill against 452 at 8 192 and 444 at 2 048
     ws_guess = 3 * (1 << 30)
     fit = int((free - ws_guess) // (block_bytes * bpt))
     resident_note = None

@@ -10,7 +10,7 @@ Environment (same style as the reference's env-var configuration)
   KAFKA_B200_SEED        weight seed (default 0);  KAFKA_B200_INIT  "iid" | "margin" (default iid)
   KAFKA_B200_KV_FRACTION fraction of free HBM given to the KV pools (default 0.85)
   KAFKA_B200_MAX_SEQS    concurrent sequences per GPU (default 512)
-  KAFKA_B200_MAX_TOKENS  packed tokens per prefill call (default 8192)
+  KAFKA_B200_MAX_TOKENS  packed tokens per prefill call (default 4096: the fastest chunk, tools/prefill_profile.py)
   KAFKA_B200_CHECKPOINTS comma-separated name=dir pairs: Hugging Face Llama checkpoints (safetensors) served under
                          `name` with their own weights and tokenizer instead of seeded random ones (checkpoint.py)
 """
@@ -61,7 +61,7 @@ def build_engine(cfg: LlamaConfig, device_index: int, seed: int = 0, init: str =
     dev = torch.device("cuda", device_index)
     torch.cuda.set_device(dev)
     max_seqs = max_seqs or int(os.environ.get("KAFKA_B200_MAX_SEQS", "512"))
-    max_tokens = max(max_tokens or int(os.environ.get("KAFKA_B200_MAX_TOKENS", "8192")), max_seqs)
+    max_tokens = max(max_tokens or int(os.environ.get("KAFKA_B200_MAX_TOKENS", "4096")), max_seqs)
     if weights is not None:
         fused = fuse_for_engine(cfg, weights, dev)
     elif checkpoint.checkpoint_dir(cfg):
