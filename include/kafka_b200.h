@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define KB_ABI_VERSION 1
+#define KB_ABI_VERSION 2
 #define KB_BLOCK_TOKENS 64 /* tokens per KV block (one TMA bulk tile = 64 tokens x head_dim) */
 #define KB_MAX_SPLITS 16   /* upper bound on split-KV partitions of one sequence in decode attention */
 
@@ -91,6 +91,12 @@ typedef struct kb_sampling {
      * n_seqs entries, NULL = use the scalars above): temperature and a seed XOR-ed into `seed`. */
     const float* seq_temperature;
     const uint64_t* seq_seed;
+    /* Nucleus sampling (the `top_p` the reference's provider API documents, src/llm/portkey.py:246): with 0 < top_p < 1
+     * and temperature > 0 only the most probable candidates whose probabilities (softmax of logit / T over the candidate
+     * set) add up to top_p are sampled from. 0 or >= 1 = off. seq_top_p: optional per-sequence device array. Needs the
+     * whole vocabulary on one GPU (refused with a vocabulary-sharded lm_head). */
+    float top_p;
+    const float* seq_top_p;
 } kb_sampling;
 
 /* ---- engine lifetime ------------------------------------------------------------------------- */

@@ -220,11 +220,95 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
     return x ^ (x >> 31);
 }
 
+// Nucleus (top-p) threshold of one row, for the block that samples it. Candidates are visited through `scan`
+// (the same visitor the sampling pass uses); v = logit / T. Returns the smallest v that stays a candidate: the
+// candidates with the largest probabilities whose mass reaches `top_p` of the total (the usual "smallest set
+// whose cumulative probability is >= top_p"; candidates within ~3e-5 in log-probability of the cut are kept too).
+// Masses are summed in 40-bit fixed point with integer atomics, so the threshold does not depend on the order in
+// which threads arrive — sampling with a seed stays reproducible.
+constexpr int NUCLEUS_BINS = 1024;
+constexpr float NUCLEUS_SPAN = 32.f;      // log-probability range resolved below the row maximum
+
+template <typename Scan>
+__device__ float nucleus_threshold(Scan& scan, float top_p, int banned, float inv_t) {
+    __shared__ unsigned long long hist[NUCLEUS_BINS];
+    __shared__ float s_red[32];
+    __shared__ float s_lo;
+    __shared__ unsigned long long s_above, s_target;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    // row maximum of v over the candidates
+    float m = -INFINITY;
+    scan([&](int j, float raw) { if (j != banned) m = fmaxf(m, raw * inv_t); });
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) s_red[warp] = m;
+    __syncthreads();
+    m = -INFINITY;
+    for (int k = 0; k < nw; ++k) m = fmaxf(m, s_red[k]);
+    __syncthreads();
+    if (!(m > -INFINITY)) return -INFINITY;                   // no candidate at all
+    auto mass = [](float u) { return (unsigned long long)(__expf(u) * 1099511627776.f); };   // 2^40 fixed point, u <= 0
+    // level 0: bins over [-SPAN, 0] (anything lower falls into bin 0, u = 0 into the top bin); level 1: the bin in
+    // which the cumulative mass (from the top) crosses the target, subdivided again. A candidate belongs to the
+    // crossing bin iff its LEVEL-0 index says so — the same arithmetic both times, so no candidate is lost or
+    // counted twice at a bin edge.
+    const float w0 = NUCLEUS_SPAN / NUCLEUS_BINS, w1 = w0 / NUCLEUS_BINS;
+    auto bin0 = [&](float u) {
+        int b = (int)floorf((u + NUCLEUS_SPAN) / w0);
+        return b < 0 ? 0 : (b >= NUCLEUS_BINS ? NUCLEUS_BINS - 1 : b);
+    };
+    __shared__ int s_bin;
+    unsigned long long above = 0, target = 0;
+    float lo_u = -NUCLEUS_SPAN;
+    int cross = 0;
+    for (int level = 0; level < 2; ++level) {
+        for (int b = threadIdx.x; b < NUCLEUS_BINS; b += blockDim.x) hist[b] = 0;
+        __syncthreads();
+        scan([&](int j, float raw) {
+            if (j == banned) return;
+            const float u = raw * inv_t - m;
+            int b = bin0(u);
+            if (level == 1) {
+                if (b != cross) return;
+                b = (int)floorf((u - lo_u) / w1);
+                b = b < 0 ? 0 : (b >= NUCLEUS_BINS ? NUCLEUS_BINS - 1 : b);
+            }
+            atomicAdd(&hist[b], mass(u));
+        });
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            if (level == 0) {
+                unsigned long long z = 0;
+                for (int b = 0; b < NUCLEUS_BINS; ++b) z += hist[b];
+                target = (unsigned long long)((double)z * (double)top_p);
+                if (target < 1) target = 1;
+            }
+            unsigned long long acc = above;
+            int b = NUCLEUS_BINS - 1;
+            for (; b > 0; --b) {                               // from the most probable bin downwards
+                if (acc + hist[b] >= target) break;
+                acc += hist[b];
+            }
+            s_above = acc;                                     // mass strictly above bin b
+            s_target = target;
+            s_bin = b;
+            s_lo = lo_u + (float)b * (level == 0 ? w0 : w1);
+        }
+        __syncthreads();
+        above = s_above;
+        target = s_target;
+        lo_u = s_lo;
+        cross = s_bin;
+        __syncthreads();
+    }
+    return m + lo_u;       // lower edge of the crossing sub-bin: that whole sub-bin stays in
+}
+
 __global__ void __launch_bounds__(1024)
 sample_kernel(const float* __restrict__ logits, int vocab, int v0, float temperature, uint64_t seed, uint64_t step,
               int banned, int lo, int hi, int extra_a, int extra_b, const float* __restrict__ seq_temperature,
-              const uint64_t* __restrict__ seq_seed, int* __restrict__ out_tokens,
-              int* __restrict__ ctx_lens_advance, uint2* __restrict__ pair_out) {
+              const uint64_t* __restrict__ seq_seed, float top_p, const float* __restrict__ seq_top_p,
+              int* __restrict__ out_tokens, int* __restrict__ ctx_lens_advance, uint2* __restrict__ pair_out) {
     // `logits` holds `vocab` columns per row, the ids [v0, v0 + vocab) of the vocabulary (v0 = 0: all of it;
     // a vocabulary-sharded lm_head under tensor parallelism: this rank's slice, v0 a multiple of 4). Every id
     // below is a GLOBAL id — the Gumbel noise, the banned id and the tie rule (lowest id) are those of the
@@ -236,21 +320,10 @@ sample_kernel(const float* __restrict__ logits, int vocab, int v0, float tempera
     const float* lg = logits + (size_t)seq * vocab - v0;
     if (seq_temperature) temperature = seq_temperature[seq];
     if (seq_seed) seed ^= seq_seed[seq];
+    if (seq_top_p) top_p = seq_top_p[seq];
     const bool greedy = !(temperature > 0.f);
     const float inv_t = greedy ? 1.f : 1.f / temperature;
     const uint64_t base = splitmix64(seed ^ splitmix64(step * 0x100000001b3ull + (uint64_t)seq));
-    float best = -INFINITY;
-    int best_i = 0x7fffffff;
-    auto consider = [&](int j, float raw) {
-        float v = raw * inv_t;
-        if (!greedy) {
-            const uint64_t r = splitmix64(base + (uint64_t)j);
-            const float u = ((float)(r >> 40) + 0.5f) * (1.0f / 16777216.0f);  // (0,1)
-            v += -__logf(-__logf(u));
-        }
-        if (j == banned) v = -INFINITY;
-        if (v > best || (v == best && j < best_i)) { best = v; best_i = j; }
-    };
     // candidates: ids in [lo, hi) and the (at most two) extra ids. The 16-byte aligned middle [v_lo, v_hi) of the
     // range is read as float4, four loads in flight per thread (a full-vocabulary row is 0.5 MB: with one 4-byte
     // load per thread in flight the kernel ran at 1.6 TB/s); the ragged ends and the extras go one by one.
@@ -259,7 +332,7 @@ sample_kernel(const float* __restrict__ logits, int vocab, int v0, float tempera
         v_lo = (lo + 3) & ~3;
         v_hi = hi & ~3;
     }
-    {
+    auto scan = [&](auto&& fn) {
         const float4* p4 = reinterpret_cast<const float4*>(lg + v_lo);
         const int n4 = (v_hi - v_lo) >> 2;
         const int bd = blockDim.x;
@@ -272,24 +345,40 @@ sample_kernel(const float* __restrict__ logits, int vocab, int v0, float tempera
             for (int k = 0; k < 4; ++k) {
                 if (i0 + k * bd < n4) {
                     const int j = v_lo + 4 * (i0 + k * bd);
-                    consider(j, t[k].x);
-                    consider(j + 1, t[k].y);
-                    consider(j + 2, t[k].z);
-                    consider(j + 3, t[k].w);
+                    fn(j, t[k].x);
+                    fn(j + 1, t[k].y);
+                    fn(j + 2, t[k].z);
+                    fn(j + 3, t[k].w);
                 }
             }
         }
-    }
-    const int n_head = v_lo - lo, n_tail = hi - v_hi;        // v_lo == v_hi == lo: everything is "tail"
-    const int n_edge = n_head + n_tail + (extra_a >= 0 ? 1 : 0) + (extra_b >= 0 ? 1 : 0);
-    for (int c = threadIdx.x; c < n_edge; c += blockDim.x) {
-        int j;
-        if (c < n_head) j = lo + c;
-        else if (c < n_head + n_tail) j = v_hi + (c - n_head);
-        else if (c == n_head + n_tail && extra_a >= 0) j = extra_a;
-        else j = extra_b;
-        consider(j, lg[j]);
-    }
+        const int n_head = v_lo - lo, n_tail = hi - v_hi;        // v_lo == v_hi == lo: everything is "tail"
+        const int n_edge = n_head + n_tail + (extra_a >= 0 ? 1 : 0) + (extra_b >= 0 ? 1 : 0);
+        for (int c = threadIdx.x; c < n_edge; c += blockDim.x) {
+            int j;
+            if (c < n_head) j = lo + c;
+            else if (c < n_head + n_tail) j = v_hi + (c - n_head);
+            else if (c == n_head + n_tail && extra_a >= 0) j = extra_a;
+            else j = extra_b;
+            fn(j, lg[j]);
+        }
+    };
+    // nucleus sampling: candidates below the top-p cut are dropped before the noise is added (block-uniform branch)
+    float cut = -INFINITY;
+    if (!greedy && top_p > 0.f && top_p < 1.f) cut = nucleus_threshold(scan, top_p, banned, inv_t);
+    float best = -INFINITY;
+    int best_i = 0x7fffffff;
+    scan([&](int j, float raw) {
+        float v = raw * inv_t;
+        if (v < cut || j == banned) {
+            v = -INFINITY;
+        } else if (!greedy) {
+            const uint64_t r = splitmix64(base + (uint64_t)j);
+            const float u = ((float)(r >> 40) + 0.5f) * (1.0f / 16777216.0f);  // (0,1)
+            v += -__logf(-__logf(u));
+        }
+        if (v > best || (v == best && j < best_i)) { best = v; best_i = j; }
+    });
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const float ov = __shfl_xor_sync(0xffffffffu, best, o);
@@ -427,6 +516,9 @@ int sample_slice(const float* logits, int n_seqs, int vocab, int v0, int n_local
              "kb_sample: bad arguments");
     KB_CHECK(v0 >= 0 && n_local > 0 && v0 + n_local <= vocab && v0 % 4 == 0, "kb_sample: bad vocabulary slice [%d, +%d) of %d",
              v0, n_local, vocab);
+    // nucleus sampling needs the probability mass of the WHOLE vocabulary: a rank that holds a slice cannot cut it
+    KB_CHECK(n_local == vocab || (!(sp->top_p > 0.f && sp->top_p < 1.f) && sp->seq_top_p == nullptr),
+             "kb_sample: top_p needs the whole vocabulary on one GPU (replicated lm_head)");
     int lo = 0, hi = vocab, ea = -1, eb = -1;
     if (sp->allowed_hi > sp->allowed_lo) {
         lo = sp->allowed_lo < 0 ? 0 : sp->allowed_lo;
@@ -444,8 +536,8 @@ int sample_slice(const float* logits, int n_seqs, int vocab, int v0, int n_local
     if (ea >= 0 && (ea < v0 || ea >= v1)) ea = -1;
     if (eb >= 0 && (eb < v0 || eb >= v1)) eb = -1;
     KB_CUDA(launch_kernel(sample_kernel, dim3(n_seqs), dim3(1024), 0, stream, logits, n_local, v0, sp->temperature, sp->seed,
-                          sp->step, sp->banned_token, lo, hi, ea, eb, sp->seq_temperature, sp->seq_seed, out_tokens,
-                          ctx_advance, static_cast<uint2*>(pair_out)));
+                          sp->step, sp->banned_token, lo, hi, ea, eb, sp->seq_temperature, sp->seq_seed, sp->top_p,
+                          sp->seq_top_p, out_tokens, ctx_advance, static_cast<uint2*>(pair_out)));
     count_launch();
     KB_LAUNCH_CHECK();
     return KB_OK;

@@ -5,6 +5,8 @@
 // Takes over `await client.chat.completions.create(**params)` (src/llm/portkey.py:379, :616).
 #include "kb_common.cuh"
 
+#include <cstddef>
+
 #include <vector>
 #include <new>
 #include <string.h>
@@ -52,6 +54,10 @@ int allreduce_peers(const kb_tp_peers* P, int rank, int world, size_t offset_byt
                     int blocks, cudaStream_t stream);
 
 static inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+// layout the ctypes binding mirrors (kafka_b200/cabi.py: Sampling, ModelCfg; tests/test_oracle_and_abi.py)
+static_assert(sizeof(kb_sampling) == 80 && offsetof(kb_sampling, top_p) == 64 && offsetof(kb_sampling, seq_top_p) == 72,
+              "kb_sampling layout changed: update the binding and KB_ABI_VERSION");
 
 struct Workspace {
     float* x = nullptr;           // [T, hidden] fp32 residual stream

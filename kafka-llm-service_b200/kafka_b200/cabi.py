@@ -18,7 +18,7 @@ from typing import Optional
 
 KB_BLOCK_TOKENS = 64
 KB_MAX_SPLITS = 16
-KB_ABI_VERSION = 1
+KB_ABI_VERSION = 2
 PROF_CATS = ("embed", "rmsnorm", "gemm_qkv", "rope_append", "attention", "gemm_o", "gemm_gate_up", "gemm_down",
              "lm_head", "sample", "allreduce")
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
@@ -54,7 +54,8 @@ class Sampling(C.Structure):
     _fields_ = [("temperature", C.c_float), ("seed", C.c_uint64), ("step", C.c_uint64),
                 ("banned_token", C.c_int32), ("allowed_lo", C.c_int32), ("allowed_hi", C.c_int32),
                 ("extra_a", C.c_int32), ("extra_b", C.c_int32),
-                ("seq_temperature", C.c_void_p), ("seq_seed", C.c_void_p)]
+                ("seq_temperature", C.c_void_p), ("seq_seed", C.c_void_p),
+                ("top_p", C.c_float), ("seq_top_p", C.c_void_p)]
 
 
 TP_MAX_RANKS, TP_MAX_BLOCKS = 8, 128
@@ -298,18 +299,21 @@ def attn_prefill(q, k_pool_layer, v_pool_layer, cu_seqlens, ctx_lens, block_tabl
 
 def make_sampling(temperature: float = 0.0, seed: int = 0, step: int = 0, banned_token: int = -1,
                   allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1,
-                  seq_temperature=None, seq_seed=None) -> Sampling:
-    """seq_temperature (float32) / seq_seed (int64 bit patterns) are optional per-sequence device tensors."""
+                  seq_temperature=None, seq_seed=None, top_p: float = 0.0, seq_top_p=None) -> Sampling:
+    """seq_temperature / seq_top_p (float32) and seq_seed (int64 bit patterns) are optional per-sequence device
+    tensors. top_p in (0, 1): nucleus sampling (0 or >= 1: off)."""
     return Sampling(float(temperature), int(seed), int(step), int(banned_token), int(allowed_lo), int(allowed_hi),
-                    int(extra_a), int(extra_b), _ptr(seq_temperature), _ptr(seq_seed))
+                    int(extra_a), int(extra_b), _ptr(seq_temperature), _ptr(seq_seed), float(top_p), _ptr(seq_top_p))
 
 
 def sample(logits, temperature: float = 0.0, seed: int = 0, step: int = 0, banned_token: int = -1,
-           allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1):
+           allowed_lo: int = 0, allowed_hi: int = 0, extra_a: int = -1, extra_b: int = -1, top_p: float = 0.0,
+           seq_top_p=None):
     import torch
     n, vocab = logits.shape
     out = torch.empty((n,), dtype=torch.int32, device=logits.device)
-    sp = make_sampling(temperature, seed, step, banned_token, allowed_lo, allowed_hi, extra_a, extra_b)
+    sp = make_sampling(temperature, seed, step, banned_token, allowed_lo, allowed_hi, extra_a, extra_b, top_p=top_p,
+                       seq_top_p=seq_top_p)
     check(load().kb_sample(_ptr(logits), n, vocab, C.byref(sp), _ptr(out), _stream()), "kb_sample")
     return out
 

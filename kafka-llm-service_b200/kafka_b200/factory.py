@@ -107,7 +107,8 @@ def shutdown_engines() -> None:
 
 
 def make_provider(model: str, tool_provider: Optional[Any] = None, thread_id: Optional[str] = None,
-                  default_temperature: float = 0.7, default_max_tokens: Optional[int] = None, **engine_opts):
+                  default_temperature: float = 0.7, default_max_tokens: Optional[int] = None,
+                  default_top_p: Optional[float] = None, **engine_opts):
     """The equivalent of `PortkeyLLMProvider(model=..., tool_provider=...)` at
     /root/reference/src/kafka/v1.py:177 for model names this repo serves locally:
 
@@ -123,4 +124,4 @@ def make_provider(model: str, tool_provider: Optional[Any] = None, thread_id: Op
     engine = get_engine(model, **engine_opts)
     return B200LLMProvider(engine, tokenizer_for(cfg), model=model, tool_provider=tool_provider,
                            default_temperature=default_temperature, default_max_tokens=default_max_tokens,
-                           thread_id=thread_id)
+                           thread_id=thread_id, default_top_p=default_top_p)

@@ -39,6 +39,8 @@ class _Staging:
         self.h_bt, self.d_bt = pair(S * max_blocks, i32)
         self.h_temp, self.d_temp = pair(S, torch.float32)
         self.h_seed, self.d_seed = pair(S, torch.int64)
+        self.h_top, self.d_top = pair(S, torch.float32)
+        self.nucleus = False      # some sequence of the current membership samples with 0 < top_p < 1
         self.h_src, self.d_src = pair(S, i32)
         self.bt_key = None
         self.sp_key = None
@@ -69,7 +71,10 @@ class _Staging:
         if key != self.sp_key:
             p["temp"] = [r.params.temperature for r in reqs]
             p["seed"] = [(r.params.seed * 0x9E3779B97F4A7C15 + r.req_id) & 0x7FFFFFFFFFFFFFFF for r in reqs]
+            p["top_p"] = [r.params.top_p if 0.0 < r.params.top_p < 1.0 else 0.0 for r in reqs]
+            self.nucleus = any(p["top_p"])
             self.sp_key = key
+        p["nucleus"] = self.nucleus
         return p
 
     def plan_src(self, src: List[int]) -> Optional[List[int]]:
@@ -91,6 +96,7 @@ class _Staging:
         if "temp" in p:
             self._up(self.h_temp, self.d_temp, p["temp"], torch.float32, torch)
             self._up(self.h_seed, self.d_seed, p["seed"], torch.int64, torch)
+            self._up(self.h_top, self.d_top, p.get("top_p") or [0.0] * len(p["temp"]), torch.float32, torch)
         if p.get("src") is not None:
             self._up(self.h_src, self.d_src, p["src"], torch.int32, torch)
         mb = p["mb"]
@@ -189,7 +195,11 @@ class GpuStepper(Stepper):
                 base = self.slot(parity, False, 0)
             sp = self.cabi.make_sampling(temperature=0.0, seed=0, step=p["step"], banned_token=p["banned"],
                                          allowed_lo=lo, allowed_hi=hi, extra_a=ea, extra_b=eb,
-                                         seq_temperature=st.d_temp, seq_seed=st.d_seed)
+                                         seq_temperature=st.d_temp, seq_seed=st.d_seed,
+                                         # nucleus sampling needs the whole vocabulary on this GPU: with a
+                                         # vocabulary-sharded lm_head (tensor parallel) top_p is not applied
+                                         seq_top_p=st.d_top if (p.get("nucleus") and not self.core.lm_head_slice)
+                                         else None)
             out = self.d_res[base:base + n_out] if n_out else None
             if p["op"] == "prefill":
                 self.core.prefill(d_tok, d_cu, d_ctx, d_bt, p["max_new"], sp, None, out)

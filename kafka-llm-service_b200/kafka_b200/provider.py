@@ -107,7 +107,7 @@ class _LoopMailbox:
 class B200LLMProvider(LLMProvider):
     def __init__(self, engine, tokenizer: ByteTokenizer, model: str, tool_provider: Optional[Any] = None,
                  default_temperature: float = 0.7, default_max_tokens: Optional[int] = None,
-                 thread_id: Optional[str] = None, seed: int = 0):
+                 thread_id: Optional[str] = None, seed: int = 0, default_top_p: Optional[float] = None):
         super().__init__(tool_provider=tool_provider)
         self.engine = engine            # Engine or ShardedEngine (process-wide, shared by providers)
         self.tokenizer = tokenizer
@@ -117,6 +117,7 @@ class B200LLMProvider(LLMProvider):
         self.default_max_tokens = default_max_tokens
         self.thread_id = thread_id
         self.seed = seed
+        self.default_top_p = default_top_p
         # token counts summed over this object's completions (the server builds one provider per request, so
         # this is the request's usage, agent tool rounds included)
         self.usage_total: Dict[str, int] = {"prompt_tokens": 0, "completion_tokens": 0, "total_tokens": 0,
@@ -175,6 +176,11 @@ class B200LLMProvider(LLMProvider):
         thread_id = kwargs.pop("thread_id", None) or self.thread_id
         seed = int(kwargs.pop("seed", self.seed) or 0)
         usage_out = kwargs.pop("_usage_out", None)            # completion() collects usage through this
+        # `top_p`: one of the extra parameters the reference's provider documents and forwards
+        # (/root/reference/src/llm/portkey.py:245-249, :375); applied by the sampling kernel
+        top_p = kwargs.pop("top_p", None)
+        top_p = self.default_top_p if top_p is None else top_p
+        top_p = float(top_p) if top_p is not None and 0.0 < float(top_p) < 1.0 else 0.0
         completion_id = f"chatcmpl-{uuid.uuid4().hex[:24]}"
         req = None
         try:
@@ -189,7 +195,7 @@ class B200LLMProvider(LLMProvider):
             def on_event(ev, _post=mailbox.post, _q=events):
                 _post(_q, ev)
 
-            req = self.engine.submit(prompt, SamplingParams(temperature=temp, seed=seed, max_tokens=int(limit)),
+            req = self.engine.submit(prompt, SamplingParams(temperature=temp, seed=seed, max_tokens=int(limit), top_p=top_p),
                                      on_event, thread_hint=thread_id)
         except ContextLengthError as e:
             raise LLMProviderError(str(e), status_code=400, provider=PROVIDER_NAME, original_error=e) from e

@@ -222,6 +222,7 @@ class SamplingParams:
     seed: int = 0
     max_tokens: int = 128
     ignore_eos: bool = False
+    top_p: float = 0.0          # nucleus sampling when 0 < top_p < 1 (and temperature > 0); 0 = off
 
 
 @dataclass(eq=False)     # identity, not field-by-field: these sit in lists searched on the hot path

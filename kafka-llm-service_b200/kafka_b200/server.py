@@ -108,9 +108,13 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
     store = store or ThreadStore()
     models = models or ["llama-3-8b", "tinyllama-1.1b", "echo"]
 
-    def make_agent(model: str, thread_id: Optional[str]) -> StreamingAgent:
+    def make_agent(model: str, thread_id: Optional[str], top_p: Optional[float] = None) -> StreamingAgent:
         tool_provider = LocalToolProvider(list(tools or []))
-        provider = provider_factory(model, tool_provider=tool_provider, thread_id=thread_id)
+        # the request's `top_p` becomes the per-request provider's default (the reference accepts the field,
+        # src/kafka/types.py:35, and drops it; here the sampling kernel applies it). Only passed when given, so that
+        # provider factories without the argument keep working.
+        extra = {"default_top_p": top_p} if top_p is not None and 0.0 < top_p < 1.0 else {}
+        provider = provider_factory(model, tool_provider=tool_provider, thread_id=thread_id, **extra)
         # context overflow -> offline compaction (truncation at safe points until the prompt fits the model's
         # context, kafka_b200/compaction.py) -> one retry; the reference builds a summarising provider here,
         # which needs a remote LLM (src/kafka/v1.py:185-194)
@@ -118,8 +122,8 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
         return StreamingAgent(provider, tool_provider, system_prompt=system_prompt,
                               context_compaction_provider=compaction)
 
-    def make_runner(model: str, thread_id: str) -> ThreadRunner:
-        agent = make_agent(model, thread_id)
+    def make_runner(model: str, thread_id: str, top_p: Optional[float] = None) -> ThreadRunner:
+        agent = make_agent(model, thread_id, top_p)
         prov = agent.llm_provider
         engine = getattr(prov, "engine", None) or getattr(getattr(prov, "inner", None), "engine", None)
         return ThreadRunner(agent, store, thread_id, engine=engine)   # engine: feeds the kv_residency table
@@ -182,7 +186,7 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
     # ---- completions -----------------------------------------------------------------------------
     @app.post("/v1/threads/{thread_id}/chat/completions")
     async def chat_completions(thread_id: str, request: ChatCompletionRequest):
-        runner = make_runner(request.model, thread_id)
+        runner = make_runner(request.model, thread_id, request.top_p)
         events = runner.run(request.messages, model=request.model, temperature=temperature_of(request),
                             max_tokens=request.max_tokens)
         if request.stream:
@@ -196,7 +200,7 @@ def create_app(provider_factory: Callable[..., Any], store: Optional[ThreadStore
 
     @app.post("/v1/chat/completions")
     async def chat_completions_standard(request: ChatCompletionRequest):
-        agent = make_agent(request.model, None)
+        agent = make_agent(request.model, None, request.top_p)
         msgs = sanitize_messages([to_message(m) for m in request.messages])
         events = agent.run(msgs, model=request.model, temperature=temperature_of(request),
                            max_tokens=request.max_tokens)

@@ -646,3 +646,84 @@ def test_sample_by_vocabulary_slices_picks_the_unsharded_token(kb, cuda, n_slice
             best_i = torch.where(better, idx, best_i)
         got = torch.where(best_i == 0x7fffffff, torch.zeros_like(best_i), best_i).int()
         assert torch.equal(got, want), (kw, it)
+
+
+def _nucleus(logits_row, top_p, T=1.0):
+    """The ids nucleus sampling may return: the most probable ones whose probabilities reach top_p (torch restatement)."""
+    p = torch.softmax(logits_row.double() / T, -1)
+    order = torch.argsort(p, descending=True)
+    cum = torch.cumsum(p[order], 0)
+    n = int((cum < top_p).sum()) + 1
+    return set(order[:n].tolist()), p, float(p[order[n - 1]])
+
+
+def test_sample_top_p_known_distribution(kb, cuda):
+    """Nucleus sampling (the `top_p` of the reference's provider API): only the smallest set of most probable tokens
+    whose mass reaches top_p is sampled, with the probabilities renormalised; top_p = 0 / 1 leave the sampler as it
+    was (bit-equal), a tiny top_p is the arg-max whatever the seed, and a seed reproduces."""
+    probs = torch.tensor([0.4, 0.3, 0.15, 0.1, 0.03, 0.01, 0.005, 0.005])
+    logits = probs.log().repeat(8192, 1).to(cuda).contiguous()
+    a = kb.sample(logits, temperature=1.0, seed=4, step=1, top_p=0.8)
+    assert torch.equal(a, kb.sample(logits, temperature=1.0, seed=4, step=1, top_p=0.8))
+    assert int(a.max()) <= 2                                    # {0.4, 0.3, 0.15}: 0.85 >= 0.8, two of them only 0.7
+    freq = torch.bincount(a.long(), minlength=8).float().cpu() / 8192
+    want = torch.tensor([0.4, 0.3, 0.15, 0, 0, 0, 0, 0]) / 0.85
+    assert torch.all((freq - want).abs() < 0.03), freq
+    plain = kb.sample(logits, temperature=1.0, seed=4, step=1)
+    assert torch.equal(plain, kb.sample(logits, temperature=1.0, seed=4, step=1, top_p=1.0))
+    assert torch.equal(plain, kb.sample(logits, temperature=1.0, seed=4, step=1, top_p=0.0))
+    assert int(plain.max()) > 2                                 # without the cut the tail is sampled
+    for seed in (1, 2, 3):
+        assert bool((kb.sample(logits, temperature=1.0, seed=seed, step=7, top_p=0.05) == 0).all())
+    # temperature reshapes the distribution before the cut: at T = 0.5 p ~ probs^2 -> {0.4, 0.3} hold 0.87 of the mass
+    hot = kb.sample(logits * 1.0, temperature=0.5, seed=9, step=3, top_p=0.8)
+    assert int(hot.max()) <= 1
+    # greedy ignores top_p
+    assert bool((kb.sample(logits, temperature=0.0, top_p=0.5) == 0).all())
+    # near-ties at the top (1 % apart: the same coarse histogram bin, resolved by the second level): the cut still
+    # falls between them
+    close = torch.tensor([0.300, 0.297, 0.2, 0.1, 0.05, 0.03, 0.013, 0.01]).log().repeat(2048, 1).to(cuda).contiguous()
+    for seed in (1, 2):
+        assert bool((kb.sample(close, temperature=1.0, seed=seed, step=1, top_p=0.2) == 0).all())
+        assert int(kb.sample(close, temperature=1.0, seed=seed, step=1, top_p=0.5).max()) == 1
+    # per-sequence values: row 0 off, row 1 cut to the arg-max
+    two = logits[:2].contiguous()
+    seq_tp = torch.tensor([0.0, 0.05], device=cuda)
+    outs = torch.stack([kb.sample(two, temperature=1.0, seed=s, step=0, seq_top_p=seq_tp) for s in range(200)])
+    assert int(outs[:, 1].max()) == 0 and int(outs[:, 0].max()) > 0
+
+
+@pytest.mark.parametrize("vocab,lo,hi,banned", [(128256, 0, 0, -1), (128256, 1000, 90000, -2), (4096, 0, 0, -1), (520, 3, 517, -2)])
+def test_sample_top_p_on_wide_rows_matches_the_sorted_definition(kb, cuda, vocab, lo, hi, banned):
+    """Full-vocabulary rows with a peaked distribution: every sampled id lies in the nucleus computed by sorting (or
+    within 1e-4 in log-probability of its cut — the kernel resolves the cut to ~3e-5), and ids outside are never
+    produced over many draws; with a candidate range and a banned id the nucleus is that of the remaining candidates."""
+    g = torch.Generator(device="cpu").manual_seed(vocab + lo)
+    S, T, top_p = 16, 0.9, 0.9
+    logits = (torch.randn(S, vocab, generator=g) * 3.0)
+    dev_logits = logits.to(cuda)
+    kw = {}
+    masked = logits.clone()
+    if hi > lo:
+        kw.update(allowed_lo=lo, allowed_hi=hi)
+        masked[:, :lo] = float("-inf")
+        masked[:, hi:] = float("-inf")
+    if banned == -2:                                            # ban each row's favourite... of row 0 (one id for the call)
+        banned = int(masked[0].argmax())
+    if banned >= 0:
+        kw.update(banned_token=banned)
+        masked[:, banned] = float("-inf")
+    allowed, slack = [], []
+    for r in range(S):
+        keep, p, p_cut = _nucleus(masked[r], top_p, T)
+        allowed.append(keep)
+        near = ((p.log() - torch.log(torch.tensor(p_cut, dtype=torch.float64))).abs() < 1e-4).nonzero().flatten().tolist()
+        slack.append(set(near))
+    seen = [set() for _ in range(S)]
+    for step in range(300):
+        out = kb.sample(dev_logits, temperature=T, seed=11, step=step, top_p=top_p, **kw).cpu().tolist()
+        for r, t in enumerate(out):
+            assert t in allowed[r] or t in slack[r], (r, t, step, len(allowed[r]))
+            seen[r].add(t)
+    # the draws really spread over the nucleus (not just its head)
+    assert all(len(s) >= min(len(a), 20) // 2 for s, a in zip(seen, allowed))

@@ -120,6 +120,31 @@ def test_sampling_with_temperature_is_reproducible_per_seed(cuda):
         eng.shutdown()
 
 
+def test_top_p_reaches_the_sampling_kernel_through_the_provider(cuda):
+    """`top_p` as the reference's provider API takes it (a keyword of stream_completion / completion,
+    /root/reference/src/llm/portkey.py:245-249): a nucleus so small that only the most probable token is left makes
+    a temperature-1 completion equal to the greedy one, whatever the seed — in a batch whose other requests sample
+    without it (per-sequence values, continuous batching) — and a provider-level default does the same."""
+    from kafka_b200.llm import Message
+    from kafka_b200.provider import B200LLMProvider
+    cfg, eng, gpu, _ = _build("tiny-test", cuda, "iid", n_blocks=64, max_seqs=8)
+    try:
+        msgs = [Message(role="user", content="nucleus")]
+
+        async def go():
+            greedy = gpu.completion(msgs, temperature=0.0, max_tokens=20)
+            cut = [gpu.completion(msgs, temperature=1.0, max_tokens=20, seed=s, top_p=1e-4) for s in (1, 2, 3)]
+            free = [gpu.completion(msgs, temperature=1.0, max_tokens=20, seed=s) for s in (1, 2, 3)]
+            return await asyncio.gather(greedy, *cut, *free)
+        r = [x.content for x in asyncio.run(go())]
+        assert len(r[0]) >= 1 and r[1] == r[0] and r[2] == r[0] and r[3] == r[0]
+        assert any(x != r[0] for x in r[4:])                # without the cut, temperature 1 wanders off
+        dflt = B200LLMProvider(eng, gpu.tokenizer, model="tiny-test", default_temperature=1.0, default_top_p=1e-4)
+        assert asyncio.run(dflt.completion(msgs, max_tokens=20, seed=5)).content == r[0]
+    finally:
+        eng.shutdown()
+
+
 def test_shared_system_prompt_blocks_match_oracle(cuda):
     """Shared-prefix KV on the real kernels: threads that start with the same system prompt read the
     first thread's KV blocks (block tables of different sequences point at the same physical blocks)."""

@@ -131,7 +131,7 @@ def test_header_constants_match_binding():
     assert int(re.search(r"#define KB_BLOCK_TOKENS (\d+)", text).group(1)) == cabi.KB_BLOCK_TOKENS
     assert int(re.search(r"#define KB_MAX_SPLITS (\d+)", text).group(1)) == cabi.KB_MAX_SPLITS
     assert int(re.search(r"#define KB_PROF_CATS (\d+)", text).group(1)) == len(cabi.PROF_CATS)
-    assert ctypes.sizeof(cabi.ModelCfg) == 40 and ctypes.sizeof(cabi.Sampling) == 64
+    assert ctypes.sizeof(cabi.ModelCfg) == 40 and ctypes.sizeof(cabi.Sampling) == 80     # 64 + top_p (4, padded to 8) + seq_top_p
 
 
 def test_no_gpu_means_loud_failure():
