@@ -55,7 +55,7 @@ int allreduce_peers(const kb_tp_peers* P, int rank, int world, size_t offset_byt
 
 static inline size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
-// layout the ctypes binding mirrors (kafka_b200/cabi.py: Sampling, ModelCfg; tests/test_oracle_and_abi.py)
+// layout the ctypes binding mirrors (kafka_b200/cabi.py: Sampling; the ABI tests check the size from that side)
 static_assert(sizeof(kb_sampling) == 80 && offsetof(kb_sampling, top_p) == 64 && offsetof(kb_sampling, seq_top_p) == 72,
               "kb_sampling layout changed: update the binding and KB_ABI_VERSION");
 
