@@ -80,6 +80,29 @@ def test_config2_64_threads_8_turns(cuda, tmp_path):
         eng.shutdown()
 
 
+def test_kv_pressure_evictions_and_queueing_keep_every_answer_exact(cuda, tmp_path):
+    """Far less KV than the threads need (48 blocks for 32 threads whose conversations grow to ~9 blocks each) and
+    far fewer batch slots than concurrent requests (8 for 32): conversations are evicted, their blocks handed to
+    others, evicted threads re-prefilled from their stored history, requests queue for a slot — and every
+    thread-turn must still equal the fp32 oracle's text. A stale K/V row surviving in a recycled block, or a
+    block-table mix-up under churn, would show here."""
+    from kafka_b200.db import ThreadStore
+    cfg, eng, gpu, cpu = _build("tiny-test", cuda, "margin", n_blocks=48, max_seqs=8)
+    store = ThreadStore(str(tmp_path / "threads.db"))
+    try:
+        mism, cached, turns = asyncio.run(_run_threads(gpu, cpu, store, n_threads=32, n_turns=5, max_tokens=32))
+        assert turns == 160
+        assert not mism, f"{len(mism)} of 160 thread-turns differ from the oracle, e.g. {mism[:2]}"
+        st = eng.stats()
+        assert st["evictions"] > 20, st                      # the pool really churned
+        assert st["resident_entries"] <= 48 and st["free_blocks"] >= 0
+        # later turns were re-prefilled from their stored history after an eviction (threads take turns in the same
+        # order, the worst case for least-recently-used eviction: a thread's blocks are gone by the time it returns)
+        assert any(c == 0 for t, c, p in cached if t >= 1)
+    finally:
+        eng.shutdown()
+
+
 def test_streaming_ttft_and_chunks(cuda):
     """One StreamChunk per token, the first content chunk right after the first sampled token."""
     import time
