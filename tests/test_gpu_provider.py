@@ -127,6 +127,48 @@ def test_streaming_ttft_and_chunks(cuda):
         eng.shutdown()
 
 
+def test_cancelling_a_stream_mid_generation_leaves_the_others_and_the_thread_intact(cuda):
+    """The provider contract the reference writes down (src/llm/base.py:100-126): a stream MUST be safe to cancel
+    mid-way. Three threads stream at once on the GPU; one consumer walks away after 5 tokens (aclose). The other two
+    must finish with the oracle's text, the engine must let go of the cancelled request (its batch slot frees), and
+    the cancelled thread's NEXT turn — which finds a KV prefix that stops wherever the cancelled turn got to —
+    must again equal the oracle's."""
+    from kafka_b200.llm import Message
+    cfg, eng, gpu, cpu = _build("tiny-test", cuda, "margin", n_blocks=64, max_seqs=8)
+    try:
+        convs = {f"t{i}": [Message(role="user", content=f"question number {i} please")] for i in range(3)}
+
+        async def stream(tid, stop_after=None):
+            text, agen = "", gpu.stream_completion(convs[tid], temperature=0.0, max_tokens=40, thread_id=tid)
+            async for ch in agen:
+                text += ch.content or ""
+                if stop_after is not None and len(text) >= stop_after:
+                    await agen.aclose()                     # the consumer is gone
+                    break
+            return text
+
+        async def go():
+            return await asyncio.gather(stream("t0"), stream("t1", stop_after=5), stream("t2"))
+        t0, t1, t2 = asyncio.run(go())
+        want = {tid: asyncio.run(cpu.completion(convs[tid], max_tokens=40)).content for tid in convs}
+        assert t0 == want["t0"] and t2 == want["t2"]
+        assert 5 <= len(t1) < 40 and want["t1"].startswith(t1)
+        for _ in range(200):                                # the engine drops the request within a few iterations
+            st = eng.stats()
+            if st["running"] == 0 and st["waiting"] == 0:
+                break
+            import time
+            time.sleep(0.01)
+        assert st["running"] == 0 and st["waiting"] == 0, st
+        # next turn of the cancelled thread: the client kept what it saw; the answer must be the oracle's
+        convs["t1"] += [Message(role="assistant", content=t1), Message(role="user", content="and then?")]
+        nxt = asyncio.run(gpu.completion(convs["t1"], temperature=0.0, max_tokens=24, thread_id="t1"))
+        assert nxt.content == asyncio.run(cpu.completion(convs["t1"], max_tokens=24)).content
+        assert nxt.usage["cached_tokens"] > 0               # and it did start from the resident prefix
+    finally:
+        eng.shutdown()
+
+
 def test_sampling_with_temperature_is_reproducible_per_seed(cuda):
     from kafka_b200.llm import Message
     cfg, eng, gpu, _ = _build("tiny-test", cuda, "iid", n_blocks=64, max_seqs=8)
