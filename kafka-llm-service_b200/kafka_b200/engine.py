@@ -93,10 +93,22 @@ class Engine:
     shutdown(), stats(). Everything else runs on the engine thread."""
 
     def __init__(self, stepper: Stepper, max_prefill_tokens: Optional[int] = None, name: str = "kb-engine",
-                 pipeline: bool = True):
+                 pipeline: bool = True, prefill_first: Optional[bool] = None, max_prefill_streak: int = 16):
         tune_gc()
         self.stepper = stepper
         self.pipeline = pipeline   # False: read every step back before enqueueing the next (for A/B timing)
+        # Prompts before tokens: while admitted prompts still wait for (the rest of) their prefill, an iteration
+        # launches the prefill chunk only and leaves the running conversations' decode step out — a burst of
+        # arrivals gets its first tokens after the prefill work alone instead of prefill + one decode step of an
+        # ever larger batch per chunk (512 simultaneous turns: TTFT p50 ~0.37 s -> ~0.2 s), and the decode steps
+        # that follow run at the full batch. Bounded: after `max_prefill_streak` such iterations in a row a decode
+        # step is forced, so a steady stream of arrivals cannot starve the conversations that are generating
+        # (at 4 096-token chunks a stall of at most ~0.7 s). KAFKA_B200_PREFILL_FIRST=0 interleaves as before.
+        if prefill_first is None:
+            prefill_first = os.environ.get("KAFKA_B200_PREFILL_FIRST", "1") != "0"
+        self.prefill_first = prefill_first
+        self.max_prefill_streak = max_prefill_streak
+        self._prefill_streak = 0
         self.sched = Scheduler(n_blocks=stepper.n_blocks, max_pos=stepper.max_pos, eos_id=stepper.eos_id,
                                max_seqs=stepper.max_seqs,
                                max_prefill_tokens=max_prefill_tokens or stepper.max_tokens)
@@ -177,6 +189,10 @@ class Engine:
             sched.on_prefill_launched(f.items, [st.slot(parity, True, i) for i in range(len(f.items))])
             self.timing["prefill_s"] += time.perf_counter() - t0
             self.timing["prefill_tokens"] += sum(len(i.tokens) for i in f.items)
+        if self.prefill_first and f.items and sched.prefilling and self._prefill_streak < self.max_prefill_streak:
+            self._prefill_streak += 1        # more prompt chunks are ready: they go before the next decode step
+            return f
+        self._prefill_streak = 0
         f.reqs = sched.next_decode_batch()   # includes conversations whose last prefill chunk was just enqueued
         if f.reqs:
             t0 = time.perf_counter()

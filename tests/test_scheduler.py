@@ -1,5 +1,6 @@
 """Host logic of one replica: block allocation, thread -> KV residency, longest-prefix reuse,
 continuous batching, eviction, cancellation — on CPU against FakeStepper (tests/fakes.py)."""
+import random
 import threading
 import time
 
@@ -493,3 +494,53 @@ def test_donor_compares_tokens_not_only_the_chain_hash():
     assert e is None and n == 0
     e, n = idx.donor(forged, prompt=list(range(128)) + [1, 2, 3])
     assert e is a and n == 2
+
+
+@pytest.mark.parametrize("prefill_first,streak", [(True, 16), (True, 2), (False, 16)])
+def test_prompts_go_before_tokens_but_cannot_starve_them(prefill_first, streak):
+    """Engine(prefill_first=...): while admitted prompts still have chunks to prefill, iterations launch the chunk
+    alone; after `max_prefill_streak` such iterations a decode step is forced. Whatever the policy, every request's
+    tokens are the same."""
+    log = []
+
+    class Logged(FakeStepper):
+        def prefill_launch(self, items, parity):
+            log.append("P")
+            return super().prefill_launch(items, parity)
+
+        def decode_launch(self, reqs, parity):
+            log.append("D")
+            return super().decode_launch(reqs, parity)
+
+    st = Logged(n_blocks=256, max_seqs=16, max_tokens=256, max_pos=1024, eos_id=EOS)
+    e = Engine(st, max_prefill_tokens=64, prefill_first=prefill_first, max_prefill_streak=streak)
+    try:
+        rnd = random.Random(5)
+        prompts = [[rnd.randrange(32, 127) for _ in range(100)] for _ in range(8)]     # 800 tokens = 13 chunks of 64
+        gate = threading.Event()
+        orig = st.prefill_launch
+
+        def held(items, parity):                      # all eight are queued before the first chunk is planned
+            gate.wait(5)
+            return orig(items, parity)
+        st.prefill_launch = held
+        cols = [Collector() for _ in prompts]
+        for p, c in zip(prompts, cols):
+            e.submit(p, SamplingParams(max_tokens=6), c)
+        time.sleep(0.2)
+        gate.set()
+        outs = [c.wait() for c in cols]
+        for p, o in zip(prompts, outs):
+            assert o.tokens == expected_tokens(p, 6, EOS)
+        first_d = log.index("D")
+        n_p = log.count("P")
+        assert n_p >= 12
+        if not prefill_first:
+            assert first_d <= 2                       # a decode step rides along from the second iteration on
+        elif streak >= n_p:
+            assert first_d >= n_p - 1                 # every chunk but possibly the last went before any decode step
+        else:
+            runs = [len(r) for r in "".join(log[:log.index("D", first_d)]).split("D")]
+            assert first_d == streak + 1 and max(runs) <= streak + 1     # forced decode after `streak` prompt-only iterations
+    finally:
+        e.shutdown()
