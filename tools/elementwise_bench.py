@@ -57,6 +57,14 @@ def main():
     sp2 = cabi.make_sampling(allowed_lo=32, allowed_hi=127, extra_a=10, extra_b=V - 1)
     out["sample_byte_range_us"] = round(timed(lambda: lib.kb_sample(cabi._ptr(logits), R, V, C.byref(sp2),
                                                                     cabi._ptr(toks), st), n=50, warm=5), 2)
+    # temperature sampling over the whole vocabulary, without and with a nucleus cut (two histogram passes + the
+    # row maximum before the sampling pass: four reads of the row instead of one)
+    sp3 = cabi.make_sampling(temperature=0.8, seed=1, step=1)
+    out["sample_temperature_full_vocab_us"] = round(timed(lambda: lib.kb_sample(cabi._ptr(logits), R, V, C.byref(sp3),
+                                                                                cabi._ptr(toks), st), n=50, warm=5), 2)
+    sp4 = cabi.make_sampling(temperature=0.8, seed=1, step=1, top_p=0.9)
+    out["sample_top_p_full_vocab_us"] = round(timed(lambda: lib.kb_sample(cabi._ptr(logits), R, V, C.byref(sp4),
+                                                                          cabi._ptr(toks), st), n=50, warm=5), 2)
     print(json.dumps(out))
 
 
