@@ -109,6 +109,10 @@ class HFTokenizer:
         self.special = {int(i): t.content for i, t in added.items() if t.special}
         # ordinary tokens = everything below the first control / special id (Llama-3: 0 .. 127 999)
         self._first_special = min(self.special) if self.special else vocab_size
+        # what every control spelling starts with ("<|" for Llama-3's 256): text without it needs no splitting, and
+        # that one substring test replaces one per spelling on every message
+        import os.path
+        self._probe = os.path.commonprefix(list(self.special.values())) if self.special else ""
 
     def encode(self, text: str) -> List[int]:
         if not text:
@@ -121,6 +125,8 @@ class HFTokenizer:
         return ids
 
     def _split_specials(self, text: str) -> List[str]:
+        if self._probe and self._probe not in text:
+            return [text]
         pieces = [text]
         for spelling in set(self.special.values()):
             nxt: List[str] = []
