@@ -353,12 +353,13 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
 // Tiles up to 256 columns wide: ring of 6 x 32 KB stages, two accumulators of 256 tensor-memory columns (the
 // epilogue of tile i runs under the main loop of tile i + 1).
 // WIDE tiles, 256 < bn <= 512: the accumulator takes all 512 columns and every k-step issues TWO MMAs that share
-// the A operand — N = 256 into columns [0, 256) and N = bn - 256 into [256, bn). Why: an SM takes in ~49 B/clk
-// through TMA whatever the source and however many SMs ask (tools/tma_ingress.cu), and a 256 x 256 tile needs
-// 32 KB per CTA per k-block for 512 cycles of MMA = 64 B/clk — the main loop of every tile up to 256 wide is paced
-// by operand staging, not by the tensor pipe. At 256 x 512 the same 16 KB of A feed twice the math: 48 KB per
-// 1024 cycles = 47 B/clk. The price: one accumulator, so the epilogue no longer hides under the next tile's main
-// loop, and a ring of 4 - 6 deeper stages (40 - 48 KB each).
+// the A operand — N = 256 into columns [0, 256) and N = bn - 256 into [256, bn). What it buys at large M: fewer,
+// fuller rounds of the 74 CTA pairs (N = 4 096 at M = 4 096: 144 units = 2 rounds instead of 256 = 4, the last one
+// 46 % full) and a third less L2 / DRAM traffic. It does not make an MMA faster: ncu shows the tensor pipe busy in
+// 90 - 95 % of the active cycles for both shapes, ~185 cycles per 128 x 256 x 16 MMA per SM (nominal 128) — the
+// chip's real dense-fp16 rate, the same 0.70 of nominal that cuBLAS's burst figure shows
+// (profiles/r02_gemm_operand_staging.md). The price: one accumulator, so the epilogue no longer hides under the
+// next tile's main loop, and a ring of 4 - 5 deeper stages (40 - 48 KB each).
 struct Gemm2Cfg {
     static constexpr int BN_MAX = 256;                          // widest single MMA
     static constexpr int BN_WIDE_MAX = 512;
@@ -1178,13 +1179,13 @@ static int pick_bn(int M, int N, int K, bool can_split, bool allow_wide, int* sp
                 if (cost < best_cost) { best_cost = cost; best = -bn; *splits_out = splits; }
             }
         }
-        // Wide tiles (256 < bn <= 512, one accumulator, two MMAs per k-step; see Gemm2Cfg). Per k-block a CTA moves
-        // through its shared memory, at 128 B/clk: the A rows once per MMA that reads them, all bn rows of B (its own
-        // half and the peer's), its half again for the peer, and what TMA writes — (256 + 2 bn) x 128 B for a tile up
-        // to 256 wide, (384 + 2 bn) x 128 B for a wide one: 768 cycles at bn = 256 (measured 783), ~1 310 at 464 for
-        // 1.8 x the math. Measured (tools/gemm_bench.py, sustained): the down projection (K = 14 336) gains 7 - 12 %
-        // from M = 2 048 up (806 -> 737 us at M = 8 192, the prefill chunk), loses at M = 1 024; K = 4 096 shapes
-        // gain nothing (the epilogue of a wide tile does not hide under the next main loop), SwiGLU loses 30 - 50 %.
+        // Wide tiles (256 < bn <= 512, one accumulator, two MMAs per k-step; see Gemm2Cfg). Cost per k-block as
+        // MEASURED at M = 4 096 (tools/gemm_bench.py, ncu): ~(256 + 2 bn) cycles for a tile up to 256 wide (783 at
+        // bn = 256), ~(384 + 2 bn) for a wide one (1 478 at bn = 480) — an MMA of 256 columns takes ~185 cycles
+        // whichever tile it belongs to, so a wide tile wins through fewer, fuller rounds, not through faster math.
+        // Sustained: the down projection (K = 14 336) gains 7 - 12 % from M = 2 048 up (806 -> 737 us at M = 8 192),
+        // loses at M = 1 024; K = 4 096 shapes gain nothing (the epilogue of a wide tile does not hide under the next
+        // main loop), SwiGLU loses.
         if (allow_wide && best < 0 && *splits_out == 1 && num_k >= 128 && num_mp >= 8) {
             const int nb = -best;
             const long n_rounds = ((long)num_mp * ((N + nb - 1) / nb) + pairs - 1) / pairs;
