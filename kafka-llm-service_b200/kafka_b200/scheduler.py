@@ -309,6 +309,7 @@ class Scheduler:
         still = []
         for req in self.waiting:
             if req.cancelled:
+                req.done = True          # dropped before it ever held a slot or a block: nothing to release
                 continue
             if len(self.prefilling) + len(self.running) >= self.max_seqs:
                 still.append(req)

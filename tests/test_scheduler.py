@@ -544,3 +544,74 @@ def test_prompts_go_before_tokens_but_cannot_starve_them(prefill_first, streak):
             assert first_d == streak + 1 and max(runs) <= streak + 1     # forced decode after `streak` prompt-only iterations
     finally:
         e.shutdown()
+
+
+@pytest.mark.parametrize("seed", list(range(1, 13)))
+def test_random_traffic_soak_keeps_tokens_and_block_accounting_exact(seed):
+    """A few hundred random operations on a pool far too small for them: threads with a common system prompt take
+    multi-turn conversations, some edit their history, some cancel mid-generation, some stop on EOS, requests
+    arrive in bursts larger than the batch; blocks are shared, copied on write, evicted and recycled. Every
+    request that finishes must produce exactly the tokens that are a pure function of its prompt (FakeStepper reads
+    them back through the block tables, so any stale, lost or wrongly shared block changes them), and in the end
+    every block is either free or held by a resident entry, with the reference counts matching."""
+    rnd = random.Random(seed)
+    st = FakeStepper(n_blocks=40, max_seqs=6, max_tokens=192, max_pos=1024, eos_id=EOS, eos_every=23)
+    e = Engine(st, max_prefill_tokens=96, prefill_first=bool(seed % 2), max_prefill_streak=3)
+    try:
+        system = [300 + (i % 29) for i in range(rnd.choice([70, 130, 200]))]
+        convs = {f"th{i}": list(system) + [65 + i] * rnd.randrange(3, 40) for i in range(10)}
+        finished = 0
+        for burst in range(30):
+            batch = []
+            for tid in rnd.sample(sorted(convs), rnd.randrange(1, 9)):
+                prompt = convs[tid]
+                if rnd.random() < 0.15 and len(prompt) > len(system) + 10:      # the client edited its history
+                    cut = rnd.randrange(len(system) // 2, len(prompt) - 1)
+                    prompt = prompt[:cut] + [rnd.randrange(32, 127) for _ in range(rnd.randrange(1, 30))]
+                if len(prompt) > 700:                                           # a fresh conversation on this thread
+                    prompt = list(system) + [rnd.randrange(32, 127) for _ in range(5)]
+                convs[tid] = prompt
+                c = Collector()
+                n = rnd.randrange(1, 24)
+                req = e.submit(prompt, SamplingParams(max_tokens=n), c, thread_hint=tid)
+                batch.append((tid, prompt, n, c, req, rnd.random() < 0.2))
+            for tid, prompt, n, c, req, cancel in batch:
+                if cancel:
+                    time.sleep(rnd.random() * 0.003)
+                    req.cancelled = True
+            for tid, prompt, n, c, req, cancel in batch:
+                # a cancelled request is dropped without a final event (its consumer is gone): wait for the
+                # scheduler to let go of it; everything else must finish
+                t_end = time.time() + 20
+                while not c.done.is_set() and not (cancel and req.done):
+                    assert time.time() < t_end, ("request neither finished nor was released", tid, burst)
+                    time.sleep(0.001)
+                assert c.error is None, c.error
+                want = expected_tokens(prompt, n, EOS, eos_every=23)
+                if want and want[-1] == EOS:
+                    want = want[:-1]                                            # the EOS itself is not streamed
+                if cancel and not c.done.is_set():
+                    assert c.tokens == want[:len(c.tokens)]                     # whatever it got before the cancel
+                else:
+                    assert c.tokens == want, (tid, burst)
+                    finished += 1
+                # the thread continues with what it saw (like a chat client), plus a new user message
+                seen = list(c.tokens)
+                convs[tid] = prompt + seen + [EOS] + [rnd.randrange(32, 127) for _ in range(rnd.randrange(1, 25))]
+        assert finished > 60
+        sched = e.sched
+        for _ in range(200):                                                    # let the loop retire the last flight
+            if sched.idle():
+                break
+            time.sleep(0.005)
+        assert sched.idle()
+        held = {}
+        for ent in sched.index.entries.values():
+            assert not ent.busy
+            for b in ent.blocks:
+                held[b] = held.get(b, 0) + 1
+        assert sched.alloc.n_free + len(held) == sched.alloc.n_blocks
+        assert all(sched.alloc.refs[b] == n for b, n in held.items())
+        assert sum(1 for r in sched.alloc.refs if r == 0) == sched.alloc.n_free
+    finally:
+        e.shutdown()
