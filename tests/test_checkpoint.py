@@ -170,3 +170,31 @@ def test_hf_tokenizer_adapter(tmp_path):
     with pytest.raises(ValueError, match="control tokens"):
         HFTokenizer(str(tmp_path / "plain.json"), vocab_size=512)
     del raw2
+
+
+def test_hf_tokenizer_round_trips_arbitrary_text(tmp_path):
+    """Property test (hypothesis): any Unicode text — control-token spellings, lone surrogates excluded — encodes to
+    ordinary ids only, decodes back to itself, and the token-by-token streaming decoder emits exactly that text
+    without ever putting out half a character."""
+    hypothesis = pytest.importorskip("hypothesis")
+    from hypothesis import given, settings, strategies as st
+    _bpe_tokenizer_json(tmp_path / "tokenizer.json")
+    tok = HFTokenizer(str(tmp_path / "tokenizer.json"), vocab_size=512)
+    specials = list(tok.special.values())
+    pieces = st.one_of(st.text(alphabet=st.characters(blacklist_categories=("Cs",)), max_size=40),
+                       st.sampled_from(specials + ["<|", "|>", "\n\n", " ", "<tool_calls>", "😀", "é"]))
+
+    @settings(max_examples=300, deadline=None)
+    @given(st.lists(pieces, max_size=8).map("".join))
+    def check(text):
+        ids = tok.encode(text)
+        assert not set(ids) & set(tok.special)
+        assert tok.decode(ids) == text
+        dec, out = tok.stream_decoder(), ""
+        for i in ids:
+            piece = dec.push(i)
+            assert "�" not in piece or "�" in text
+            out += piece
+        assert out + dec.flush() == text
+
+    check()
