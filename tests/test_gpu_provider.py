@@ -103,6 +103,62 @@ def test_kv_pressure_evictions_and_queueing_keep_every_answer_exact(cuda, tmp_pa
         eng.shutdown()
 
 
+@pytest.mark.parametrize("seed", [1, 2])
+def test_random_traffic_on_the_gpu_matches_the_oracle(cuda, seed):
+    """The host-side soak (tests/test_scheduler.py) with the real kernels underneath: ten threads with a common
+    system prompt take random multi-turn conversations in bursts larger than the batch on a KV pool that cannot hold
+    them all; some consumers cancel mid-stream, some edit their history. Every completion that runs to its end must
+    be the fp32 oracle's text for that exact history."""
+    from kafka_b200.llm import Message
+    rnd = random.Random(seed)
+    cfg, eng, gpu, cpu = _build("tiny-test", cuda, "margin", n_blocks=28, max_seqs=6)
+    try:
+        def text(n):
+            return "".join(chr(rnd.randrange(32, 127)) for _ in range(n))
+        system = Message(role="system", content=text(rnd.choice([60, 150])))
+        convs = {f"s{i}": [system, Message(role="user", content=text(rnd.randrange(5, 60)))] for i in range(10)}
+        checked = 0
+
+        async def one(tid, msgs, n, cancel_after):
+            out, agen = "", gpu.stream_completion(msgs, temperature=0.0, max_tokens=n, thread_id=tid)
+            async for ch in agen:
+                out += ch.content or ""
+                if cancel_after is not None and len(out) >= cancel_after:
+                    await agen.aclose()
+                    return out, True
+            return out, False
+
+        for burst in range(8):
+            jobs = []
+            for tid in rnd.sample(sorted(convs), rnd.randrange(2, 10)):
+                msgs = convs[tid]
+                if rnd.random() < 0.15 and len(msgs) > 3:                     # the client drops its last exchange
+                    msgs = msgs[:-2] + [Message(role="user", content=text(rnd.randrange(5, 40)))]
+                if sum(len(m.content) for m in msgs) > 600:
+                    msgs = [system, Message(role="user", content=text(20))]
+                convs[tid] = msgs
+                n = rnd.randrange(1, 28)
+                jobs.append((tid, msgs, n, rnd.randrange(1, n + 1) if rnd.random() < 0.2 else None))
+
+            async def go():
+                return await asyncio.gather(*[one(*j) for j in jobs])
+            for (tid, msgs, n, _), (out, cancelled) in zip(jobs, asyncio.run(go())):
+                want = asyncio.run(cpu.completion(msgs, max_tokens=n)).content
+                if cancelled:
+                    assert want.startswith(out), (tid, burst)
+                else:
+                    assert out == want, (tid, burst, out, want)
+                    checked += 1
+                convs[tid] = msgs + [Message(role="assistant", content=out),
+                                     Message(role="user", content=text(rnd.randrange(3, 50)))]
+        assert checked > 25
+        st = eng.stats()
+        assert st["cached_tokens"] > 0
+        print(f"seed {seed}: {checked} completions checked, {st['evictions']} evictions")
+    finally:
+        eng.shutdown()
+
+
 def test_streaming_ttft_and_chunks(cuda):
     """One StreamChunk per token, the first content chunk right after the first sampled token."""
     import time
