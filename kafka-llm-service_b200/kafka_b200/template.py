@@ -42,10 +42,19 @@ class ChatTemplate:
                 self._headers[label] = ids
         return ids
 
+    # How a model is told to call the tools: the block provider.py parses out of the generated text and turns into
+    # StreamChunk.tool_calls (`<tool_calls>[...]</tool_calls>`, the form assistant tool calls are rendered in below,
+    # so a call that comes back as history is the same tokens). A real instruction-tuned checkpoint needs to be told;
+    # the random-init models of the tests ignore it.
+    TOOLS_PREAMBLE = ('You may call the tools described below. To call tools, end your reply with '
+                      '<tool_calls>[{"name": "<tool name>", "arguments": {<arguments as JSON>}}]</tool_calls> '
+                      '(one list entry per call) and write nothing after it; the results come back as tool messages.\n')
+
     def render_tools(self, tools: Optional[Sequence[Dict[str, Any]]]) -> List[int]:
         if not tools:
             return []
-        return self._header("tools") + self.tok.encode(canonical_json(list(tools))) + [self.tok.eot_id]
+        return (self._header("tools") + self.tok.encode(self.TOOLS_PREAMBLE + canonical_json(list(tools))) +
+                [self.tok.eot_id])
 
     def message_body(self, msg: Any) -> str:
         content = _field(msg, "content")

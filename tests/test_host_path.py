@@ -104,7 +104,10 @@ def test_template_renders_every_field_and_tools():
     msgs = [Message(role="assistant", content=None, tool_calls=[{"id": "c1", "function": {"name": "f", "arguments": "{}"}}]),
             Message(role="tool", content="42", tool_call_id="c1", name="f")]
     text = t.decode(tmpl.render(msgs, tools=tools), skip_special=False)
-    assert text.startswith("<|begin_of_text|><|start_header_id|>tools<|end_header_id|>\n\n" + canonical_json(tools))
+    # the tools block: how to call them (the syntax provider.parse_tool_calls reads back), then the schemas
+    assert text.startswith("<|begin_of_text|><|start_header_id|>tools<|end_header_id|>\n\n" + ChatTemplate.TOOLS_PREAMBLE +
+                           canonical_json(tools) + "<|eot_id|>")
+    assert "<tool_calls>[" in ChatTemplate.TOOLS_PREAMBLE and "</tool_calls>" in ChatTemplate.TOOLS_PREAMBLE
     assert '<tool_calls>[{"function":{"arguments":"{}","name":"f"},"id":"c1"}]</tool_calls><|eot_id|>' in text
     assert "<|start_header_id|>tool name=f tool_call_id=c1<|end_header_id|>\n\n42<|eot_id|>" in text
     assert text.endswith("<|start_header_id|>assistant<|end_header_id|>\n\n")
