@@ -128,8 +128,9 @@ class B200LLMProvider(LLMProvider):
             self.usage_total[k] += int(usage.get(k, 0))
 
     # ---- helpers -------------------------------------------------------------------------------
-    def render(self, messages: List[Message], tools: Optional[List[Dict[str, Any]]]) -> List[int]:
-        return self.template.render(messages, tools=tools or None, add_generation_prompt=True)
+    def render(self, messages: List[Message], tools: Optional[List[Dict[str, Any]]],
+               thread_id: Optional[str] = None) -> List[int]:
+        return self.template.render(messages, tools=tools or None, add_generation_prompt=True, cache_key=thread_id)
 
     @staticmethod
     def _first_marker(text: str, markers: List[str], start: int) -> int:
@@ -186,7 +187,7 @@ class B200LLMProvider(LLMProvider):
         try:
             tools = await self.get_tools()
             self._last_tools = tools                          # count_prompt_tokens() sizes prompts like this call
-            prompt = self.render(validated, tools)
+            prompt = self.render(validated, tools, thread_id)
             temp = self.default_temperature if temperature is None else float(temperature)
             limit = max_tokens if max_tokens is not None else (self.default_max_tokens or 512)
             events: "asyncio.Queue" = asyncio.Queue()

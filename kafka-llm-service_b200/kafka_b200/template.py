@@ -87,7 +87,12 @@ class ChatTemplate:
 
     # ---- whole conversation ------------------------------------------------------------------
     def render(self, messages: Sequence[Any], tools: Optional[Sequence[Dict[str, Any]]] = None,
-               add_generation_prompt: bool = True) -> List[int]:
+               add_generation_prompt: bool = True, cache_key: Optional[str] = None) -> List[int]:
+        """`cache_key` (a thread id): a follow-up turn re-sends the whole conversation, and because every message
+        renders independently of what follows, the tokens of the messages it has in common with the thread's
+        previous call are taken from RenderCache instead of being tokenised again (the result is the same list)."""
+        if cache_key is not None and RenderCache.enabled:
+            return RenderCache.render(self, cache_key, messages, tools, add_generation_prompt)
         ids: List[int] = [self.tok.bos_id]
         ids += self.render_tools(tools)
         for m in messages:
@@ -95,3 +100,70 @@ class ChatTemplate:
         if add_generation_prompt:
             ids += self.generation_prompt()
         return ids
+
+
+def _message_key(msg: Any):
+    """Everything render_message looks at, cheap to compare (strings compare at memcmp speed)."""
+    tc = _field(msg, "tool_calls")
+    content = _field(msg, "content")
+    if content is not None and not isinstance(content, str):
+        content = canonical_json(content)
+    return (str(_field(msg, "role")), content, _field(msg, "name"), _field(msg, "tool_call_id"),
+            canonical_json(tc) if tc else None)
+
+
+class RenderCache:
+    """Per (tokenizer, thread): the message keys of the last rendered conversation, the token offset after each
+    message, and the tokens. Process-wide (the server builds a provider — and a ChatTemplate — per request),
+    least-recently-used, bounded by a total token count. KAFKA_B200_RENDER_CACHE=0 switches it off."""
+    import os as _os
+    enabled = _os.environ.get("KAFKA_B200_RENDER_CACHE", "1") != "0"
+    max_tokens = 64_000_000
+    _lock = __import__("threading").Lock()
+    _entries: "Dict[Any, Any]" = {}          # (tokenizer.cache_id, cache_key) -> [tools_key, keys, ends, ids]; dict order = LRU
+    _total = 0
+
+    @classmethod
+    def clear(cls) -> None:
+        with cls._lock:
+            cls._entries.clear()
+            cls._total = 0
+
+    @classmethod
+    def render(cls, tmpl: "ChatTemplate", cache_key: str, messages, tools, add_generation_prompt: bool) -> List[int]:
+        tok_id = getattr(tmpl.tok, "cache_id", None)      # which vocabulary the cached ids belong to
+        if tok_id is None:
+            return tmpl.render(messages, tools, add_generation_prompt)
+        tools_key = canonical_json(list(tools)) if tools else ""
+        keys = [_message_key(m) for m in messages]
+        k = (tok_id, cache_key)
+        with cls._lock:
+            ent = cls._entries.pop(k, None)
+            if ent is not None:
+                cls._total -= len(ent[3])
+        n_same = 0
+        if ent is not None and ent[0] == tools_key:
+            old_keys = ent[1]
+            lim = min(len(old_keys), len(keys))
+            while n_same < lim and old_keys[n_same] == keys[n_same]:
+                n_same += 1
+        if n_same:
+            ends = ent[2][:n_same]
+            ids = ent[3][:ends[-1]]
+        else:
+            ids = [tmpl.tok.bos_id] + tmpl.render_tools(tools)
+            ends = []
+        for m in messages[n_same:]:
+            ids += tmpl.render_message(m)
+            ends.append(len(ids))
+        with cls._lock:
+            cls._entries[k] = [tools_key, keys, ends, ids]
+            cls._total += len(ids)
+            while cls._total > cls.max_tokens and len(cls._entries) > 1:
+                _, old = next(iter(cls._entries.items()))
+                cls._total -= len(old[3])
+                del cls._entries[next(iter(cls._entries))]
+        out = list(ids)                      # the cache keeps its own list: callers may mutate what they get
+        if add_generation_prompt:
+            out += tmpl.generation_prompt()
+        return out

@@ -23,6 +23,7 @@ class ByteTokenizer:
         if vocab_size < self.N_BYTES + 4:
             raise ValueError(f"vocab_size {vocab_size} too small for the byte tokenizer (needs >= 260)")
         self.vocab_size = vocab_size
+        self.cache_id = ("byte", vocab_size)   # identifies the vocabulary (template.RenderCache)
         self.bos_id = vocab_size - 4           # <|begin_of_text|>
         self.start_header_id = vocab_size - 3  # <|start_header_id|>
         self.end_header_id = vocab_size - 2    # <|end_header_id|>
@@ -93,6 +94,8 @@ class HFTokenizer:
         from tokenizers import Tokenizer
         self._tok = Tokenizer.from_file(tokenizer_json)
         self.vocab_size = vocab_size
+        import os
+        self.cache_id = ("hf", os.path.abspath(tokenizer_json), os.path.getmtime(tokenizer_json), vocab_size)
         missing = []
         for attr, text in self.CONTROL.items():
             i = self._tok.token_to_id(text)

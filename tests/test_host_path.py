@@ -480,3 +480,64 @@ def _config4_body(provider):
     assert provider.engine.sched.stats["requests"] == 3
     cached, prompt = provider.engine.sched.stats["cached_tokens"], provider.engine.sched.stats["prompt_tokens"]
     assert cached / prompt > 0.45 and st.prefilled_tokens == prompt - cached
+
+
+def test_render_cache_is_invisible():
+    """template.RenderCache (tokens of the messages a thread's previous call already rendered are reused): whatever
+    happens to a thread's conversation between calls — messages appended, the tail dropped, a message in the middle
+    edited, tool calls, a different tool list, another vocabulary under the same thread id — the cached render is
+    the same token list as a render from scratch."""
+    import random
+    from kafka_b200.template import RenderCache
+    rnd = random.Random(3)
+    toks = [ByteTokenizer(512), ByteTokenizer(32000)]
+    tmpls = [ChatTemplate(t) for t in toks]
+    tool_sets = [None, [{"type": "function", "function": {"name": "f", "parameters": {"a": 1}}}],
+                 [{"type": "function", "function": {"name": "g", "parameters": {}}}]]
+
+    def msg():
+        r = rnd.random()
+        text = "".join(chr(rnd.randrange(32, 127)) for _ in range(rnd.randrange(0, 40)))
+        if r < 0.15:
+            return Message(role="assistant", content=text or None,
+                           tool_calls=[{"id": f"c{rnd.randrange(9)}", "function": {"name": "f", "arguments": "{}"}}])
+        if r < 0.3:
+            return {"role": "tool", "content": text, "tool_call_id": f"c{rnd.randrange(9)}", "name": "f"}
+        return Message(role=rnd.choice(["user", "assistant", "system"]), content=text)
+    RenderCache.clear()
+    convs = {f"t{i}": [msg() for _ in range(rnd.randrange(1, 6))] for i in range(4)}
+    hits = 0
+    for step in range(600):
+        tid = rnd.choice(sorted(convs))
+        c = convs[tid]
+        r = rnd.random()
+        if r < 0.5:
+            c = c + [msg() for _ in range(rnd.randrange(1, 4))]
+        elif r < 0.65 and len(c) > 1:
+            c = c[:rnd.randrange(1, len(c))]
+        elif r < 0.8 and c:
+            i = rnd.randrange(len(c))
+            c = c[:i] + [msg()] + c[i + 1:]
+        if len(c) > 30:
+            c = c[-3:]
+        convs[tid] = c
+        which = rnd.randrange(2)
+        tools = rnd.choice(tool_sets)
+        gen = rnd.random() < 0.7
+        before = RenderCache._total
+        got = tmpls[which].render(c, tools=tools, add_generation_prompt=gen, cache_key=tid)
+        assert got == tmpls[which].render(c, tools=tools, add_generation_prompt=gen), (step, tid)
+        got.append(-1)                                       # callers may mutate the list they get
+        hits += RenderCache._total >= before
+    assert RenderCache._total == sum(len(e[3]) for e in RenderCache._entries.values()) and hits > 100
+    # bounded: least recently used threads go first
+    old_max = RenderCache.max_tokens
+    try:
+        RenderCache.max_tokens = 200
+        for i in range(20):
+            tmpls[0].render([Message(role="user", content="x" * 50)], cache_key=f"lru{i}")
+        assert RenderCache._total <= 200 + 80 and ("byte", 512), "lru19" in RenderCache._entries
+        assert (("byte", 512), "lru0") not in RenderCache._entries
+    finally:
+        RenderCache.max_tokens = old_max
+        RenderCache.clear()
