@@ -355,9 +355,9 @@ __device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long
 // WIDE tiles, 256 < bn <= 512: the accumulator takes all 512 columns and every k-step issues TWO MMAs that share
 // the A operand — N = 256 into columns [0, 256) and N = bn - 256 into [256, bn). What it buys at large M: fewer,
 // fuller rounds of the 74 CTA pairs (N = 4 096 at M = 4 096: 144 units = 2 rounds instead of 256 = 4, the last one
-// 46 % full) and a third less L2 / DRAM traffic. It does not make an MMA faster: ncu shows the tensor pipe busy in
-// 90 - 95 % of the active cycles for both shapes, ~185 cycles per 128 x 256 x 16 MMA per SM (nominal 128) — the
-// chip's real dense-fp16 rate, the same 0.70 of nominal that cuBLAS's burst figure shows
+// 46 % full) and a third less L2 / DRAM traffic. It does not make an MMA faster: a 128 x 256 x 16 MMA takes ~95 ns
+// per SM whatever the SM clock reads (1.64 PFLOP/s over the chip, cuBLAS's burst figure), an SM takes in ~97 GB/s
+// through TMA, and t(k-block) = max of the two explains the narrow, the 256-wide and the wide tiles alike
 // (profiles/r02_gemm_operand_staging.md). The price: one accumulator, so the epilogue no longer hides under the
 // next tile's main loop, and a ring of 4 - 5 deeper stages (40 - 48 KB each).
 struct Gemm2Cfg {
@@ -1179,10 +1179,10 @@ static int pick_bn(int M, int N, int K, bool can_split, bool allow_wide, int* sp
                 if (cost < best_cost) { best_cost = cost; best = -bn; *splits_out = splits; }
             }
         }
-        // Wide tiles (256 < bn <= 512, one accumulator, two MMAs per k-step; see Gemm2Cfg). Cost per k-block as
-        // MEASURED at M = 4 096 (tools/gemm_bench.py, ncu): ~(256 + 2 bn) cycles for a tile up to 256 wide (783 at
-        // bn = 256), ~(384 + 2 bn) for a wide one (1 478 at bn = 480) — an MMA of 256 columns takes ~185 cycles
-        // whichever tile it belongs to, so a wide tile wins through fewer, fuller rounds, not through faster math.
+        // Wide tiles (256 < bn <= 512, one accumulator, two MMAs per k-step; see Gemm2Cfg). Per k-block both kinds
+        // are MMA-bound at these widths (~95 ns per 256 columns: 398 ns measured at bn = 256, 752 ns at bn = 480);
+        // (256 + 2 bn) and (384 + 2 bn) below are those costs in units that only need to be comparable with each
+        // other — a wide tile wins through fewer, fuller rounds, not through faster math.
         // Sustained: the down projection (K = 14 336) gains 7 - 12 % from M = 2 048 up (806 -> 737 us at M = 8 192),
         // loses at M = 1 024; K = 4 096 shapes gain nothing (the epilogue of a wide tile does not hide under the next
         // main loop), SwiGLU loses.
