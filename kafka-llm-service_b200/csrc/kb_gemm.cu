@@ -310,7 +310,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // CTA-pair variant (cta_group::2): a cluster of two CTAs owns a 256 x BN output tile.
 //
 // Why: a 1-CTA 128 x BN tile has to bring 16 KB of A plus BN*128 B of B into shared memory per k-block,
-// and an SM takes in only ~50 B/clk by TMA (measured: tools/gemm_trace.py, profiles/r01_gemm_bench.md) —
+// and an SM takes in only ~97 GB/s by TMA (~50 B/clk at boost clock; profiles/r02_gemm_operand_staging.md) —
 // that ingress, not the MMA, bounds the main loop. In a pair each CTA stages its own 128 rows of A but
 // only HALF of B (BN/2 rows); the tensor cores of both SMs read both halves, so the ingress per CTA drops
 // to 16 KB + BN*64 B for twice the rows: close to balanced with the MMA at BN = 256.
@@ -329,7 +329,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 //
 // At M = 512 those two launches have only 2 x N/256 = 32 tiles of 256 x 256 for 74 CTA pairs; filling the GPU with
 // narrower tiles (bn = 112) makes every tile pay 16 KB of A per 7 KB of W, and the main loop runs at the
-// shared-memory ingress rate (~50 B/clk per SM), not at the tensor rate. Instead the K range of a wide tile is
+// TMA intake rate (~97 GB/s per SM), not at the tensor rate. Instead the K range of a wide tile is
 // cut into `splits` work units that run on different CTA pairs at the same time. Their partial sums meet in
 // the output itself: every unit adds its accumulator to x with red.global.add — but in a FIXED order, unit s
 // after unit s - 1, so that the fp32 result does not depend on which unit finished first (the engine's outputs
@@ -1140,7 +1140,7 @@ static int pick_bn(int M, int N, int K, bool can_split, bool allow_wide, int* sp
     const int sms = num_sms();
     const int num_m = (M + GEMM_BM - 1) / GEMM_BM;
     const int num_k = K / GEMM_BK;
-    // cycles per k-block of one CTA: `rows` 128-byte rows of operands staged by TMA at ~50 B/clk per SM
+    // cycles per k-block of one CTA: `rows` 128-byte rows of operands staged by TMA at ~97 GB/s per SM (~50 B/clk at the boost clock)
     // (measured: tools/gemm_trace.py, profiles/r01_gemm_bench.md) against 2 * bn cycles of MMA
     auto kblock = [](int rows, int bn) { const long ing = (long)rows * 128 * 100 / 5000; return ing > 2L * bn ? ing : 2L * bn; };
     auto epilogue = [](int bn) { return 1200L + 6L * bn; };
