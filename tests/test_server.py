@@ -263,3 +263,17 @@ def test_module_entry_point_serves_over_http(tmp_path):
             proc.wait(timeout=10)
         except subprocess.TimeoutExpired:
             proc.kill()
+
+
+def test_example_script_runs_on_the_echo_model():
+    """examples/agent.py (the shape of the reference's examples/agent.py: two local tools, a stateless run and two
+    turns on a thread) end to end with the echo model — no GPU."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "examples", "agent.py"), "--model", "echo"], cwd=root,
+                         capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "What is the weather in Paris?" in out.stdout and "Which number did I mention?" in out.stdout
+    assert "stored messages: 4" in out.stdout
