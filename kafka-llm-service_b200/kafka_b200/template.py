@@ -118,7 +118,7 @@ class RenderCache:
     least-recently-used, bounded by a total token count. KAFKA_B200_RENDER_CACHE=0 switches it off."""
     import os as _os
     enabled = _os.environ.get("KAFKA_B200_RENDER_CACHE", "1") != "0"
-    max_tokens = 64_000_000
+    max_tokens = 16_000_000      # ~36 B per cached id in CPython: at most ~0.6 GB
     _lock = __import__("threading").Lock()
     _entries: "Dict[Any, Any]" = {}          # (tokenizer.cache_id, cache_key) -> [tools_key, keys, ends, ids]; dict order = LRU
     _total = 0
